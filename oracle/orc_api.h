@@ -1,0 +1,109 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h header). C interface used by tests/ and bench.py via ctypes.
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+// Network shape (configs/nerf/base.json, configs/geometry/base.json). MLP width is 64, outputs 16-padded.
+typedef struct {
+	uint32_t n_levels;
+	uint32_t n_features_per_level;
+	uint32_t log2_hashmap_size;
+	uint32_t base_resolution;
+	float per_level_scale;
+	uint32_t density_hidden_layers; // "network.n_hidden_layers"
+	uint32_t rgb_hidden_layers;     // "rgb_network.n_hidden_layers"
+} orc_net_config;
+
+typedef struct {
+	int32_t width, height;
+	uint32_t spp; // sample index (render_buffer.spp)
+	float cam0[12], cam1[12];
+	float rolling_shutter[4];
+	float screen_center[2];
+	float focal[2]; // pixels
+	int32_t snap_to_pixel_centers;
+	float near_distance;
+	// NeRF
+	float render_aabb[6];
+	float train_aabb[6];
+	uint32_t max_mip;
+	float cone_angle_constant;
+	float min_transmittance;
+	int32_t rgb_activation;     // 0 None 1 ReLU 2 Logistic 3 Exponential (ENerfActivation order)
+	int32_t density_activation;
+	int32_t linear_colors;      // nerf.training.linear_colors
+	int32_t dda_iter_cap;       // 0 = unlimited (nerf_device.cuh:461), 200 = the _geometry variant (:497)
+	// Mesh
+	float mesh_aabb[6];
+	float sun_dir[3];
+	float up_dir[3];
+	float floor_y;
+	float brdf[15]; // metallic subsurface specular roughness sheen clearcoat clearcoat_gloss basecolor[3] ambientcolor[3] pad[2]
+	int32_t compat_nearest_aabb_only; // 1 = reference top-level rule (geometry_bvh.cu:166-200)
+	int32_t depth_merge_clip;         // 0 = reference per-pixel depth test, 1 = stop marching at the mesh depth
+	int32_t n_threads;                // host threads for the frame loops (cpu baseline)
+} orc_render_params;
+
+// ---- scalar pieces (pinned against oracle/_ref) ----
+float orc_ld_random_val(uint32_t index, uint32_t seed);
+void orc_ld_random_pixel_offset(uint32_t spp, float out[2]);
+void orc_bbox_ray_intersect(const float bb[6], const float o[3], const float d[3], float out[2]);
+float orc_triangle_ray_intersect(const float tri[9], const float o[3], const float d[3]);
+uint32_t orc_morton3D(uint32_t x, uint32_t y, uint32_t z);
+float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const float d[3], const uint8_t* bitfield,
+	uint32_t min_mip, uint32_t max_mip, const float aabb[6], int32_t iter_cap);
+float orc_calc_dt(float t, float cone_angle);
+float orc_srgb_to_linear(float v);
+
+// ---- occupancy (a-20) ----
+// grid: float[128^3 * n_cascades] Morton order. out: uint8[128^3/8 * 8]. Returns the threshold used.
+float orc_bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out);
+
+// ---- ray generation (a-2..a-6) ----
+// per pixel: origin[3], dir[3], t (after AABB entry, start jitter and advance to first occupied voxel), alive
+void orc_init_rays(const orc_render_params* p, const uint8_t* bitfield, float* origins, float* dirs, float* t, uint8_t* alive);
+
+// ---- marching without termination (a-7,a-8): all samples a ray emits until it leaves the box ----
+// returns per-ray counts; if positions != NULL writes up to max_per_ray samples as {x,y,z,dt} (un-warped).
+void orc_march_all(const orc_render_params* p, const uint8_t* bitfield, uint32_t n_rays, const float* origins, const float* dirs,
+	const float* t0, const uint8_t* alive, uint32_t* counts, float* samples, uint32_t max_per_ray);
+
+// ---- network (a-10..a-13) ----
+size_t orc_n_params(const orc_net_config* c);            // number of fp16 parameters in the blob
+size_t orc_grid_param_offset(const orc_net_config* c);   // offset of the hash table in the blob (elements)
+void orc_grid_layout(const orc_net_config* c, uint32_t* offsets /*L+1*/, float* scales /*L*/, uint32_t* resolutions /*L*/);
+void orc_encode(const orc_net_config* c, const uint16_t* params, const float* positions /*[n][3] in [0,1]*/, uint32_t n, uint16_t* out /*[n][32]*/);
+void orc_sh4(const float* dirs01 /*[n][3] warped dirs in [0,1]*/, uint32_t n, uint16_t* out /*[n][16]*/);
+// coords: [n][7] = warped pos, warped dt, warped dir. out: [n][4] fp16 raw network output (r,g,b,sigma) before activations.
+void orc_network(const orc_net_config* c, const uint16_t* params, const float* coords, uint32_t n, uint16_t* out);
+
+// ---- full NeRF pass (3.2) into an existing frame/depth buffer ----
+// n_steps_out (optional, per pixel): number of samples composited.
+uint64_t orc_render_nerf(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
+	float* frame /*[h][w][4]*/, float* depth /*[h][w]*/, uint32_t* n_steps_out, int32_t depth_test);
+
+// ---- meshes (a-17..a-19) ----
+typedef struct orc_scene orc_scene;
+orc_scene* orc_scene_create(void);
+void orc_scene_destroy(orc_scene*);
+// triangles: [n][9] already in scene space (normalisation is the loader's job).
+void orc_scene_add_mesh(orc_scene*, const float* triangles, uint32_t n_tris, const float center[3]);
+void orc_scene_build(orc_scene*);
+void orc_scene_aabb(const orc_scene*, float out[6]);
+// nearest hit per ray; brute = 1 tests every triangle (no BVH). t = MAX_DIST(100) and tri=-1 on miss.
+void orc_scene_trace(const orc_scene*, const orc_render_params* p, uint32_t n, const float* origins, const float* dirs,
+	int32_t* mesh_idx, int32_t* tri_idx, float* t, int32_t brute);
+// mesh pass (3.3): writes frame/depth.
+void orc_render_mesh(const orc_scene*, const orc_render_params* p, float* frame, float* depth);
+
+// ---- whole frame (3.1): clear, mesh pass (if scene), NeRF pass (if params) ----
+uint64_t orc_render_frame(const orc_scene* scene, const orc_render_params* p, const orc_net_config* c, const uint16_t* params,
+	const uint8_t* bitfield, float* frame, float* depth, uint32_t* n_steps_out);
+
+#ifdef __cplusplus
+}
+#endif

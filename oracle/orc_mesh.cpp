@@ -1,0 +1,359 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h). Mesh half of the path: triangle test, nearest-hit search
+// (brute force = ground truth, plus a plain binary BVH so the 1 M-triangle CPU baseline finishes), top-level mesh
+// selection, sun shadow rays, Disney-style shading, and the whole-frame driver.
+#include "orc_common.h"
+#include "orc_api.h"
+#include <thread>
+#include <atomic>
+#include <numeric>
+
+namespace orc {
+
+// defined in orc_nerf.cpp
+Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y);
+vec2 ld_random_pixel_offset(uint32_t spp);
+Ray uv_to_ray_pinhole(vec2 uv, int w, int h, vec2 focal, const cam_t& cam, vec2 screen_center, float near_distance);
+struct Net;
+
+struct Triangle { vec3 a, b, c; };
+
+// triangle.cuh:44-58
+static float tri_ray_intersect(const Triangle& tr, vec3 ro, vec3 rd) {
+	vec3 v1v0 = tr.b - tr.a;
+	vec3 v2v0 = tr.c - tr.a;
+	vec3 rov0 = ro - tr.a;
+	vec3 n = cross(v1v0, v2v0);
+	vec3 q = cross(rov0, rd);
+	float d = 1.0f / dot(rd, n);
+	float u = d * -dot(q, v2v0);
+	float v = d * dot(q, v1v0);
+	float t = d * -dot(n, rov0);
+	if (u < 0.0f || u > 1.0f || v < 0.0f || (u + v) > 1.0f || t < 0.0f) t = FLT_MAX;
+	return t;
+}
+static vec3 tri_normal(const Triangle& tr) { return normalize(cross(tr.b - tr.a, tr.c - tr.a)); }
+
+struct BvhNode {
+	BoundingBox bb;
+	int left, right; // inner: child node indices; leaf: left = -(first+1), right = count
+};
+
+struct Mesh {
+	std::vector<Triangle> tris; // original order
+	vec3 center;
+	BoundingBox bb;
+	std::vector<BvhNode> nodes;
+	std::vector<uint32_t> order; // BVH leaf order -> original triangle index
+};
+
+static BoundingBox tri_bounds(const Mesh& m, const uint32_t* begin, const uint32_t* end) {
+	BoundingBox bb = {{FLT_MAX, FLT_MAX, FLT_MAX}, {-FLT_MAX, -FLT_MAX, -FLT_MAX}};
+	for (const uint32_t* it = begin; it != end; ++it) {
+		bb.enlarge(m.tris[*it].a); bb.enlarge(m.tris[*it].b); bb.enlarge(m.tris[*it].c);
+	}
+	return bb;
+}
+static void pad(BoundingBox& bb) {
+	// conservative padding so that the slab test can never reject a ray the triangle test accepts
+	vec3 d = bb.diag();
+	float e = 1e-5f * std::max(std::max(d.x, d.y), d.z) + 1e-6f;
+	bb.min = bb.min - e; bb.max = bb.max + e;
+}
+static int build_rec(Mesh& m, uint32_t first, uint32_t count) {
+	int idx = (int)m.nodes.size();
+	m.nodes.emplace_back();
+	BoundingBox bb = tri_bounds(m, m.order.data() + first, m.order.data() + first + count);
+	BoundingBox padded = bb; pad(padded);
+	m.nodes[idx].bb = padded;
+	if (count <= 4) {
+		m.nodes[idx].left = -(int)(first + 1);
+		m.nodes[idx].right = (int)count;
+		return idx;
+	}
+	vec3 d = bb.diag();
+	int axis = d.x >= d.y && d.x >= d.z ? 0 : (d.y >= d.z ? 1 : 2);
+	auto centroid = [&](uint32_t t) { return m.tris[t].a[axis] + m.tris[t].b[axis] + m.tris[t].c[axis]; };
+	uint32_t mid = count / 2;
+	std::nth_element(m.order.begin() + first, m.order.begin() + first + mid, m.order.begin() + first + count,
+		[&](uint32_t x, uint32_t y) { float cx = centroid(x), cy = centroid(y); return cx < cy || (cx == cy && x < y); });
+	int l = build_rec(m, first, mid);
+	int r = build_rec(m, first + mid, count - mid);
+	m.nodes[idx].left = l; m.nodes[idx].right = r;
+	return idx;
+}
+
+// robust slab test (NaN-safe): returns entry distance or FLT_MAX
+static float slab_entry(const BoundingBox& bb, vec3 o, vec3 inv, float tmax) {
+	float t0 = 0.0f, t1 = tmax;
+	for (int a = 0; a < 3; ++a) {
+		float ta = (bb.min[a] - o[a]) * inv[a], tb = (bb.max[a] - o[a]) * inv[a];
+		float lo = std::fmin(ta, tb), hi = std::fmax(ta, tb);
+		t0 = std::fmax(t0, lo); t1 = std::fmin(t1, hi);
+	}
+	return t0 <= t1 ? t0 : FLT_MAX;
+}
+
+// Nearest hit inside one mesh. Tie rule shared with the product: smallest t, then smallest original triangle index.
+// Same acceptance as triangle_bvh.cu:150-193: mint starts at MAX_DIST, strict t < mint.
+static void mesh_nearest(const Mesh& m, vec3 o, vec3 d, bool brute, int& best, float& mint) {
+	best = -1; mint = MAX_DIST;
+	if (brute) {
+		for (uint32_t i = 0; i < m.tris.size(); ++i) {
+			float t = tri_ray_intersect(m.tris[i], o, d);
+			if (t < mint) { mint = t; best = (int)i; }
+		}
+		return;
+	}
+	vec3 inv = vec3{1.0f, 1.0f, 1.0f} / d;
+	int stack[64]; int sp = 0; stack[sp++] = 0;
+	while (sp) {
+		const BvhNode& n = m.nodes[stack[--sp]];
+		if (slab_entry(n.bb, o, inv, mint) == FLT_MAX) continue;
+		if (n.left < 0) {
+			uint32_t first = (uint32_t)(-n.left - 1);
+			for (uint32_t k = 0; k < (uint32_t)n.right; ++k) {
+				uint32_t ti = m.order[first + k];
+				float t = tri_ray_intersect(m.tris[ti], o, d);
+				if (t < mint || (t == mint && best >= 0 && (int)ti < best)) { mint = t; best = (int)ti; }
+			}
+		} else {
+			stack[sp++] = n.left; stack[sp++] = n.right;
+		}
+	}
+}
+
+} // namespace orc
+
+using namespace orc;
+
+struct orc_scene {
+	std::vector<Mesh> meshes;
+	BoundingBox root;
+};
+
+namespace orc {
+
+// geometry_bvh.cu:646-676 + :166-200. Returns mesh index (or -1), triangle index (or -1) and t (MAX_DIST on a miss
+// inside the chosen mesh). `touched` says whether the reference kernel would have modified the ray at all.
+static void scene_nearest(const orc_scene& s, bool compat, vec3 o, vec3 d, bool brute, int& mesh, int& tri, float& t, bool& touched) {
+	mesh = -1; tri = -1; t = MAX_DIST; touched = false;
+	if (compat) {
+		float mint = MAX_DIST;
+		for (size_t i = 0; i < s.meshes.size(); ++i) {
+			vec2 tt = s.meshes[i].bb.ray_intersect(o, d);
+			if (tt.x < mint && tt.x > -FLT_MAX) { mint = tt.x; mesh = (int)i; }
+		}
+		if (mesh < 0) return;
+		touched = true;
+		mesh_nearest(s.meshes[mesh], o, d, brute, tri, t);
+		return;
+	}
+	for (size_t i = 0; i < s.meshes.size(); ++i) {
+		int ti; float tt;
+		mesh_nearest(s.meshes[i], o, d, brute, ti, tt);
+		if (ti >= 0 && tt < t) { t = tt; tri = ti; mesh = (int)i; }
+	}
+	touched = true; // the default mode always advances the ray (to the hit, or by MAX_DIST on a miss)
+	if (tri < 0) mesh = -1;
+}
+
+// testbed_geometry_training.cu:50-144
+static float sqr(float x) { return x * x; }
+static float saturate(float x) { return std::min(std::max(x, 0.0f), 1.0f); }
+static float SchlickFresnel(float u) { float m = saturate(1.0f - u); return sqr(sqr(m)) * m; }
+static const float PI_F = 3.14159265358979323846f;
+static float G1(float NdotH, float a) {
+	if (a >= 1.0f) return 1.0f / PI_F;
+	float a2 = sqr(a);
+	float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+	return (a2 - 1.0f) / (PI_F * std::log(a2) * t);
+}
+static float G2(float NdotH, float a) {
+	float a2 = sqr(a);
+	float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+	return a2 / (PI_F * t * t);
+}
+static float SmithG_GGX(float NdotV, float alphaG) {
+	float a = alphaG * alphaG, b = NdotV * NdotV;
+	return 1.0f / (NdotV + std::sqrt(a + b - a * b));
+}
+static vec3 v3(float s) { return {s, s, s}; }
+static vec3 evaluate_shading(vec3 base_color, vec3 ambient_color, vec3 light_color, float metallic, float subsurface, float specular,
+	float roughness, float specular_tint, float sheen, float sheen_tint, float clearcoat, float clearcoat_gloss, vec3 L, vec3 V, vec3 N) {
+	float NdotL = dot(N, L), NdotV = dot(N, V);
+	vec3 H = normalize(L + V);
+	float NdotH = dot(N, H), LdotH = dot(L, H);
+	float FL = SchlickFresnel(NdotL), FV = SchlickFresnel(NdotV);
+	vec3 amb = ambient_color * mixf(0.2f, FV, metallic);
+	amb = amb * base_color;
+	if (NdotL < 0.f || NdotV < 0.f) return amb;
+	float luminance = dot(base_color, vec3{0.3f, 0.6f, 0.1f});
+	vec3 Ctint = base_color * (1.f / (luminance + 0.00001f));
+	vec3 Cspec0 = mix(mix(v3(1.0f), Ctint, specular_tint) * specular * 0.08f, base_color, metallic);
+	vec3 Csheen = mix(v3(1.0f), Ctint, sheen_tint);
+	float Fd90 = 0.5f + 2.0f * LdotH * LdotH * roughness;
+	float Fd = mixf(1, Fd90, FL) * mixf(1.f, Fd90, FV);
+	float Fss90 = LdotH * LdotH * roughness;
+	float Fss = mixf(1.0f, Fss90, FL) * mixf(1.0f, Fss90, FV);
+	float ss = 1.25f * (Fss * (1.f / (NdotL + NdotV) - 0.5f) + 0.5f);
+	float a = std::max(0.001f, sqr(roughness));
+	float Ds = G2(NdotH, a);
+	float FH = SchlickFresnel(LdotH);
+	vec3 Fs = mix(Cspec0, v3(1.0f), FH);
+	float Gs = SmithG_GGX(NdotL, a) * SmithG_GGX(NdotV, a);
+	vec3 Fsheen = FH * sheen * Csheen;
+	float Dr = G1(NdotH, mixf(0.1f, 0.001f, clearcoat_gloss));
+	float Fr = mixf(0.04f, 1.0f, FH);
+	float Gr = SmithG_GGX(NdotL, 0.25f) * SmithG_GGX(NdotV, 0.25f);
+	float CCs = 0.25f * clearcoat * Gr * Fr * Dr;
+	vec3 brdf = ((1.0f / PI_F) * mixf(Fd, ss, subsurface) * base_color + Fsheen) * (1.0f - metallic) + Gs * Fs * Ds + v3(CCs);
+	return (brdf * light_color) * NdotL + amb;
+}
+
+template <typename F>
+static void parallel_rows(int n_rows, int n_threads, F&& f) {
+	if (n_threads <= 1) { for (int y = 0; y < n_rows; ++y) f(y); return; }
+	std::atomic<int> next{0};
+	std::vector<std::thread> th;
+	for (int i = 0; i < n_threads; ++i) th.emplace_back([&] { for (int y; (y = next.fetch_add(1)) < n_rows;) f(y); });
+	for (auto& t : th) t.join();
+}
+
+// testbed_geometry_training.cu:2202-2320 (render_geometry_mesh), Shade mode with sun shadow rays.
+static void render_mesh(const orc_scene& s, const orc_render_params& p, float* frame, float* depth) {
+	BoundingBox aabb = bb_from(p.mesh_aabb);
+	cam_t cam = cam_from(p.cam0);
+	vec3 cam_pos = cam.c[3], cam_fwd = cam.c[2];
+	vec3 sun = normalize(vec3{p.sun_dir[0], p.sun_dir[1], p.sun_dir[2]});
+	vec3 up = normalize(vec3{p.up_dir[0], p.up_dir[1], p.up_dir[2]});
+	const float* B = p.brdf;
+	vec3 basecolor = {B[7], B[8], B[9]}, ambientcolor = {B[10], B[11], B[12]};
+	bool compat = p.compat_nearest_aabb_only != 0;
+	parallel_rows(p.height, p.n_threads, [&](int y) {
+		for (int x = 0; x < p.width; ++x) {
+			uint32_t idx = x + p.width * y;
+			// :488-579 init_rays_with_payload_kernel_mesh_geometry (pixel_to_ray: no rolling shutter, camera_matrix as is)
+			vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
+			vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
+			Ray ray = uv_to_ray_pinhole(uv, p.width, p.height, {p.focal[0], p.focal[1]}, cam, {p.screen_center[0], p.screen_center[1]}, p.near_distance);
+			depth[idx] = MAX_DEPTH;
+			ray.d = normalize(ray.d);
+			float t0 = std::max(aabb.ray_intersect(ray.o, ray.d).x, 0.0f);
+			vec3 pos = ray.o + (t0 + 1e-6f) * ray.d;
+			vec3 dir = ray.d;
+			// :2140-2155 trace_mesh_bvh: every pixel is traced (alive or not), n_hit == n_pixels
+			int mi, ti; float t; bool touched;
+			scene_nearest(s, compat, pos, dir, false, mi, ti, t, touched);
+			vec3 nrm = dir; // direction smuggled through the normal buffer
+			if (touched) {
+				pos = pos + t * dir;
+				if (ti >= 0) nrm = tri_normal(s.meshes[mi].tris[ti]);
+			}
+			// :222-278 shadow ray
+			float shadow;
+			{
+				float sgn = -std::copysign(1.0f, dot(dir, nrm)); // faceforward(n, i, nref) = n * -sign(dot(i, nref))
+				vec3 view_pos = pos + normalize(nrm * sgn) * 1e-3f;
+				float ts = std::fmax(aabb.ray_intersect(view_pos, sun).x + 1e-6f, 0.0f);
+				view_pos = view_pos + ts * sun;
+				// :239-244: a shadow origin outside the box keeps payload.dir (= the primary direction) and is still
+				// traced by trace_mesh_bvh (:2149 copies payload.dir for every ray, alive or not).
+				vec3 sdir = aabb.contains(view_pos) ? sun : dir;
+				int smi, sti; float st; bool stouched;
+				scene_nearest(s, compat, view_pos, sdir, false, smi, sti, st, stouched);
+				vec3 end = stouched ? view_pos + st * sdir : view_pos;
+				shadow = aabb.contains(end) ? 0.0f : 1.0f;
+			}
+			// :280-355 shade_kernel_mesh_geometry
+			if (!aabb.contains(pos)) continue;
+			vec3 normal = normalize(nrm);
+			bool floor = false;
+			if (pos.y < p.floor_y + 0.001f && dir.y < 0.f) { normal = {0.0f, 1.0f, 0.0f}; floor = true; }
+			float skyam = -dot(normal, up) * 0.5f + 0.5f;
+			vec3 suncol = vec3{255.f / 255.0f, 225.f / 255.0f, 195.f / 255.0f} * 4.f * shadow;
+			vec3 skycol = vec3{195.f / 255.0f, 215.f / 255.0f, 255.f / 255.0f} * 4.f * skyam;
+			float check_size = 8.f / aabb.diag().x;
+			float check = ((int(std::floor(check_size * (pos.x - aabb.min.x))) ^ int(std::floor(check_size * (pos.z - aabb.min.z)))) & 1) ? 0.8f : 0.2f;
+			vec3 floorcol = {check * check * check, check * check, check};
+			vec3 color = evaluate_shading(floor ? floorcol : basecolor * basecolor, ambientcolor * skycol, suncol,
+				floor ? 0.f : B[0], floor ? 0.f : B[1], floor ? 1.f : B[2], floor ? 0.5f : B[3], 0.f, floor ? 0.f : B[4], 0.f,
+				floor ? 0.f : B[5], B[6], sun, -normalize(dir), normal);
+			float* fb = frame + 4 * (size_t)idx;
+			fb[0] = color.x; fb[1] = color.y; fb[2] = color.z; fb[3] = 1.0f;
+			depth[idx] = dot(cam_fwd, pos - cam_pos);
+		}
+	});
+}
+
+} // namespace orc
+
+extern "C" {
+
+float orc_triangle_ray_intersect(const float tri[9], const float o[3], const float d[3]) {
+	Triangle t = {{tri[0], tri[1], tri[2]}, {tri[3], tri[4], tri[5]}, {tri[6], tri[7], tri[8]}};
+	return tri_ray_intersect(t, {o[0], o[1], o[2]}, {d[0], d[1], d[2]});
+}
+
+orc_scene* orc_scene_create(void) { return new orc_scene(); }
+void orc_scene_destroy(orc_scene* s) { delete s; }
+void orc_scene_add_mesh(orc_scene* s, const float* tr, uint32_t n, const float center[3]) {
+	s->meshes.emplace_back();
+	Mesh& m = s->meshes.back();
+	m.tris.resize(n);
+	for (uint32_t i = 0; i < n; ++i) {
+		const float* f = tr + 9 * (size_t)i;
+		m.tris[i] = {{f[0], f[1], f[2]}, {f[3], f[4], f[5]}, {f[6], f[7], f[8]}};
+	}
+	m.center = {center[0], center[1], center[2]};
+}
+void orc_scene_build(orc_scene* s) {
+	bool first = true;
+	for (Mesh& m : s->meshes) {
+		m.order.resize(m.tris.size());
+		std::iota(m.order.begin(), m.order.end(), 0u);
+		// geometry_bvh.cu:18-35: mesh box = exact min/max over its vertices
+		m.bb = tri_bounds(m, m.order.data(), m.order.data() + m.order.size());
+		m.nodes.clear();
+		m.nodes.reserve(m.tris.size());
+		build_rec(m, 0, (uint32_t)m.tris.size());
+		if (first) { s->root = m.bb; first = false; }
+		else { s->root.enlarge(m.bb.min); s->root.enlarge(m.bb.max); }
+	}
+}
+void orc_scene_aabb(const orc_scene* s, float out[6]) {
+	out[0] = s->root.min.x; out[1] = s->root.min.y; out[2] = s->root.min.z;
+	out[3] = s->root.max.x; out[4] = s->root.max.y; out[5] = s->root.max.z;
+}
+void orc_scene_trace(const orc_scene* s, const orc_render_params* p, uint32_t n, const float* o, const float* d,
+	int32_t* mesh_idx, int32_t* tri_idx, float* t, int32_t brute) {
+	int nt = p->n_threads > 1 ? p->n_threads : 1;
+	std::atomic<uint32_t> next{0};
+	auto work = [&] {
+		for (uint32_t b; (b = next.fetch_add(1024)) < n;) {
+			for (uint32_t i = b; i < std::min(n, b + 1024); ++i) {
+				int mi, ti; float tt; bool touched;
+				scene_nearest(*s, p->compat_nearest_aabb_only != 0, {o[3 * i], o[3 * i + 1], o[3 * i + 2]}, {d[3 * i], d[3 * i + 1], d[3 * i + 2]}, brute != 0, mi, ti, tt, touched);
+				mesh_idx[i] = mi; tri_idx[i] = ti; t[i] = tt;
+			}
+		}
+	};
+	std::vector<std::thread> th;
+	for (int i = 1; i < nt; ++i) th.emplace_back(work);
+	work();
+	for (auto& x : th) x.join();
+}
+void orc_render_mesh(const orc_scene* s, const orc_render_params* p, float* frame, float* depth) { render_mesh(*s, *p, frame, depth); }
+
+uint64_t orc_render_frame(const orc_scene* scene, const orc_render_params* p, const orc_net_config* c, const uint16_t* params,
+	const uint8_t* bitfield, float* frame, float* depth, uint32_t* n_steps_out) {
+	size_t n = (size_t)p->width * p->height;
+	std::memset(frame, 0, n * 4 * sizeof(float)); // render_buffer.cu:603 clear
+	std::memset(depth, 0, n * sizeof(float));
+	bool has_mesh = scene && !scene->meshes.empty();
+	if (has_mesh) render_mesh(*scene, *p, frame, depth);
+	uint64_t total = 0;
+	if (params) total = orc_render_nerf(p, c, params, bitfield, frame, depth, n_steps_out, has_mesh ? 1 : 0);
+	return total;
+}
+
+} // extern "C"

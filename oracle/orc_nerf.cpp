@@ -1,0 +1,653 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_common.h). NeRF half of the path: Sobol jitter, ray generation,
+// occupancy DDA, hash grid, SH, MLPs, compositing, final blend. Build with -ffp-contract=off (no FMA contraction),
+// every function cites the reference file:line it restates (paths relative to /root/reference).
+#include "orc_common.h"
+#include "orc_api.h"
+#include <thread>
+#include <atomic>
+
+namespace orc {
+
+// ---------------------------------------------------------------- random_val.cuh:207-370
+// Sobol direction numbers, dimensions 0 and 1 (the only ones the path consumes): dim 0 is the identity
+// (bit-reversal) sequence, dim 1 follows v_j = v_{j-1} ^ (v_{j-1} >> 1) (Joe & Kuo primitive polynomial x+1).
+static uint32_t sobol_dir(uint32_t dim, uint32_t bit) {
+	if (dim == 0) return 0x80000000u >> bit;
+	uint32_t v = 0x80000000u;
+	for (uint32_t i = 0; i < bit; ++i) v ^= v >> 1;
+	return v;
+}
+static uint32_t sobol(uint32_t index, uint32_t dim) {
+	uint32_t X = 0;
+	for (uint32_t bit = 0; bit < 32; ++bit) {
+		if ((index >> bit) & 1) X ^= sobol_dir(dim, bit);
+	}
+	return X;
+}
+static uint32_t hash_combine(uint32_t seed, uint32_t v) { return seed ^ (v + (seed << 6) + (seed >> 2)); }
+static uint32_t reverse_bits(uint32_t x) {
+	x = ((x & 0xaaaaaaaau) >> 1) | ((x & 0x55555555u) << 1);
+	x = ((x & 0xccccccccu) >> 2) | ((x & 0x33333333u) << 2);
+	x = ((x & 0xf0f0f0f0u) >> 4) | ((x & 0x0f0f0f0fu) << 4);
+	x = ((x & 0xff00ff00u) >> 8) | ((x & 0x00ff00ffu) << 8);
+	return (x >> 16) | (x << 16);
+}
+static uint32_t laine_karras(uint32_t x, uint32_t seed) {
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+static uint32_t owen_scramble(uint32_t x, uint32_t seed) { return reverse_bits(laine_karras(reverse_bits(x), seed)); }
+static const float TWO_M32 = (float)(1.0 / 4294967296.0);
+float ld_random_val(uint32_t index, uint32_t seed, uint32_t dim = 0) {
+	index = owen_scramble(index, seed);
+	return (float)owen_scramble(sobol(index, dim), hash_combine(seed, dim)) * TWO_M32;
+}
+vec2 ld_random_val_2d(uint32_t index, uint32_t seed) {
+	index = owen_scramble(index, seed);
+	uint32_t x = owen_scramble(sobol(index, 0), hash_combine(seed, 0));
+	uint32_t y = owen_scramble(sobol(index, 1), hash_combine(seed, 1));
+	return {(float)x * TWO_M32, (float)y * TWO_M32};
+}
+static float fractf(float x) { return x - std::floor(x); }
+vec2 ld_random_pixel_offset(uint32_t spp) {
+	vec2 a = ld_random_val_2d(0, 0xdeadbeefu), b = ld_random_val_2d(spp, 0xdeadbeefu);
+	return {fractf(0.5f - a.x + b.x), fractf(0.5f - a.y + b.y)};
+}
+
+// ---------------------------------------------------------------- tcnn vec.h:1060-1187 (quaternion slerp of the camera)
+struct quat { float w, x, y, z; };
+static quat quat_from(const mat3& m) {
+	quat q;
+	float tr = m.c[0].x + m.c[1].y + m.c[2].z;
+	if (tr > 0.0f) {
+		float S = std::sqrt(tr + 1.0f) * 2.0f;
+		q.w = 0.25f * S;
+		q.x = (m.c[1].z - m.c[2].y) / S;
+		q.y = (m.c[2].x - m.c[0].z) / S;
+		q.z = (m.c[0].y - m.c[1].x) / S;
+	} else if (m.c[0].x > m.c[1].y && m.c[0].x > m.c[2].z) {
+		float S = std::sqrt(1.0f + m.c[0].x - m.c[1].y - m.c[2].z) * 2.0f;
+		q.w = (m.c[1].z - m.c[2].y) / S;
+		q.x = 0.25f * S;
+		q.y = (m.c[1].x + m.c[0].y) / S;
+		q.z = (m.c[2].x + m.c[0].z) / S;
+	} else if (m.c[1].y > m.c[2].z) {
+		float S = std::sqrt(1.0f + m.c[1].y - m.c[0].x - m.c[2].z) * 2.0f;
+		q.w = (m.c[2].x - m.c[0].z) / S;
+		q.x = (m.c[1].x + m.c[0].y) / S;
+		q.y = 0.25f * S;
+		q.z = (m.c[2].y + m.c[1].z) / S;
+	} else {
+		float S = std::sqrt(1.0f + m.c[2].z - m.c[0].x - m.c[1].y) * 2.0f;
+		q.w = (m.c[0].y - m.c[1].x) / S;
+		q.x = (m.c[2].x + m.c[0].z) / S;
+		q.y = (m.c[2].y + m.c[1].z) / S;
+		q.z = 0.25f * S;
+	}
+	return q;
+}
+static float qdot(quat a, quat b) { return (a.w * b.w + a.x * b.x) + (a.y * b.y + a.z * b.z); }
+static quat qnormalize(quat a) {
+	float len = std::sqrt(qdot(a, a));
+	if (len <= 0.0f) return {1.0f, 0.0f, 0.0f, 0.0f};
+	return {a.w / len, a.x / len, a.y / len, a.z / len};
+}
+static quat qscale(quat a, float s) { return {a.w * s, a.x * s, a.y * s, a.z * s}; }
+static quat qadd(quat a, quat b) { return {a.w + b.w, a.x + b.x, a.y + b.y, a.z + b.z}; }
+static quat qslerp(quat x, quat y, float t) {
+	quat z = y;
+	float cos_theta = qdot(x, y);
+	if (cos_theta < 0.0f) {
+		z = {-y.w, -y.x, -y.y, -y.z};
+		cos_theta = -cos_theta;
+	}
+	if (cos_theta > 1.0f - FLT_EPSILON) {
+		return qadd(qscale(x, 1.0f - t), qscale(z, t));
+	}
+	float angle = std::acos(cos_theta);
+	quat r = qadd(qscale(x, std::sin((1.0f - t) * angle)), qscale(z, std::sin(t * angle)));
+	float s = std::sin(angle);
+	return {r.w / s, r.x / s, r.y / s, r.z / s};
+}
+static mat3 quat_to_mat3(quat q) {
+	float qxx = q.x * q.x, qyy = q.y * q.y, qzz = q.z * q.z;
+	float qxz = q.x * q.z, qxy = q.x * q.y, qyz = q.y * q.z;
+	float qwx = q.w * q.x, qwy = q.w * q.y, qwz = q.w * q.z;
+	mat3 m;
+	m.c[0] = {1.0f - 2.0f * (qyy + qzz), 2.0f * (qxy + qwz), 2.0f * (qxz - qwy)};
+	m.c[1] = {2.0f * (qxy - qwz), 1.0f - 2.0f * (qxx + qzz), 2.0f * (qyz + qwx)};
+	m.c[2] = {2.0f * (qxz + qwy), 2.0f * (qyz - qwx), 1.0f - 2.0f * (qxx + qyy)};
+	return m;
+}
+// common_device.cuh:651-659
+static cam_t camera_slerp(const cam_t& a, const cam_t& b, float t) {
+	mat3 ma = {{a.c[0], a.c[1], a.c[2]}}, mb = {{b.c[0], b.c[1], b.c[2]}};
+	mat3 rot = quat_to_mat3(qnormalize(qslerp(qnormalize(quat_from(ma)), qnormalize(quat_from(mb)), t)));
+	cam_t r;
+	r.c[0] = rot.c[0]; r.c[1] = rot.c[1]; r.c[2] = rot.c[2];
+	r.c[3] = mix(a.c[3], b.c[3], t);
+	return r;
+}
+
+// common_device.cuh:416-483 (pinhole lens, no foveation / distortion / DoF / parallax) — direction not normalised.
+Ray uv_to_ray_pinhole(vec2 uv, int w, int h, vec2 focal, const cam_t& cam, vec2 screen_center, float near_distance) {
+	vec3 dir = {
+		(uv.x - screen_center.x) * (float)w / focal.x,
+		(uv.y - screen_center.y) * (float)h / focal.y,
+		1.0f,
+	};
+	vec3 head_pos = {0.0f, 0.0f, 0.0f};
+	dir = dir - head_pos * 0.0f;
+	mat3 m = {{cam.c[0], cam.c[1], cam.c[2]}};
+	dir = mul(m, dir);
+	vec3 origin = mul(m, head_pos) + cam.c[3];
+	origin = origin + dir * near_distance;
+	return {origin, dir};
+}
+
+// testbed_nerf.cu:1428-1476: uv + per-pixel rolling-shutter camera
+Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y) {
+	uint32_t idx = x + (uint32_t)p.width * y;
+	vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
+	vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
+	float mb = ld_random_val(p.spp, idx * 72239731u);
+	const float* rs = p.rolling_shutter;
+	float pixel_t = rs[0] + rs[1] * uv.x + rs[2] * uv.y + rs[3] * mb;
+	cam_t cam = camera_slerp(cam_from(p.cam0), cam_from(p.cam1), pixel_t);
+	return uv_to_ray_pinhole(uv, p.width, p.height, {p.focal[0], p.focal[1]}, cam, {p.screen_center[0], p.screen_center[1]}, p.near_distance);
+}
+
+// ---------------------------------------------------------------- nerf_device.cuh:316-534 (occupancy DDA)
+static uint32_t expand_bits(uint32_t v) {
+	v = (v * 0x00010001u) & 0xFF0000FFu;
+	v = (v * 0x00000101u) & 0x0F00F00Fu;
+	v = (v * 0x00000011u) & 0xC30C30C3u;
+	v = (v * 0x00000005u) & 0x49249249u;
+	return v;
+}
+uint32_t morton3D(uint32_t x, uint32_t y, uint32_t z) { return expand_bits(x) | (expand_bits(y) << 1) | (expand_bits(z) << 2); }
+static uint32_t morton3D_invert(uint32_t x) {
+	x = x & 0x49249249u;
+	x = (x | (x >> 2)) & 0xc30c30c3u;
+	x = (x | (x >> 4)) & 0x0f00f00fu;
+	x = (x | (x >> 8)) & 0xff0000ffu;
+	x = (x | (x >> 16)) & 0x0000ffffu;
+	return x;
+}
+static uint32_t cascaded_grid_idx_at(vec3 pos, uint32_t mip) {
+	float mip_scale = std::scalbnf(1.0f, -(int)mip);
+	pos = pos - 0.5f;
+	pos = pos * mip_scale;
+	pos = pos + 0.5f;
+	int ix = (int)(pos.x * (float)NERF_GRIDSIZE), iy = (int)(pos.y * (float)NERF_GRIDSIZE), iz = (int)(pos.z * (float)NERF_GRIDSIZE);
+	if (ix < 0 || ix >= (int)NERF_GRIDSIZE || iy < 0 || iy >= (int)NERF_GRIDSIZE || iz < 0 || iz >= (int)NERF_GRIDSIZE) return 0xFFFFFFFFu;
+	return morton3D(ix, iy, iz);
+}
+static bool occupied_at(vec3 pos, const uint8_t* bits, uint32_t mip) {
+	uint32_t idx = cascaded_grid_idx_at(pos, mip);
+	if (idx == 0xFFFFFFFFu) return false;
+	return bits[idx / 8 + (NERF_GRID_N_CELLS * mip) / 8] & (1 << (idx % 8));
+}
+static float signf(float a) { return std::copysign(1.0f, a); }
+static float distance_to_next_voxel(vec3 pos, vec3 dir, vec3 idir, float res) {
+	vec3 p = res * (pos - 0.5f);
+	float tx = (std::floor(p.x + 0.5f + 0.5f * signf(dir.x)) - p.x) * idir.x;
+	float ty = (std::floor(p.y + 0.5f + 0.5f * signf(dir.y)) - p.y) * idir.y;
+	float tz = (std::floor(p.z + 0.5f + 0.5f * signf(dir.z)) - p.z) * idir.z;
+	float t = std::min(std::min(tx, ty), tz);
+	return std::fmax(t / res, 0.0f);
+}
+static float to_stepping_space(float t, float cone_angle) {
+	if (cone_angle <= 1e-5f) return t / MIN_CONE_STEPSIZE;
+	float log1p_c = std::log(1.0f + cone_angle);
+	float a = (std::log(MIN_CONE_STEPSIZE) - std::log(log1p_c)) / log1p_c;
+	float b = (std::log(MAX_CONE_STEPSIZE) - std::log(log1p_c)) / log1p_c;
+	float at = std::exp(a * log1p_c), bt = std::exp(b * log1p_c);
+	if (t <= at) return (t - at) / MIN_CONE_STEPSIZE + a;
+	if (t <= bt) return std::log(t) / log1p_c;
+	return (t - bt) / MAX_CONE_STEPSIZE + b;
+}
+static float from_stepping_space(float n, float cone_angle) {
+	if (cone_angle <= 1e-5f) return n * MIN_CONE_STEPSIZE;
+	float log1p_c = std::log(1.0f + cone_angle);
+	float a = (std::log(MIN_CONE_STEPSIZE) - std::log(log1p_c)) / log1p_c;
+	float b = (std::log(MAX_CONE_STEPSIZE) - std::log(log1p_c)) / log1p_c;
+	float at = std::exp(a * log1p_c), bt = std::exp(b * log1p_c);
+	if (n <= a) return (n - a) * MIN_CONE_STEPSIZE + at;
+	if (n <= b) return std::exp(n * log1p_c);
+	return (n - b) * MAX_CONE_STEPSIZE + bt;
+}
+static float advance_n_steps(float t, float cone_angle, float n) { return from_stepping_space(to_stepping_space(t, cone_angle) + n, cone_angle); }
+float calc_dt(float t, float cone_angle) { return advance_n_steps(t, cone_angle, 1.0f) - t; }
+static float advance_to_next_voxel(float t, float cone_angle, vec3 pos, vec3 dir, vec3 idir, uint32_t mip) {
+	float res = std::scalbnf((float)NERF_GRIDSIZE, -(int)mip);
+	float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+	t = to_stepping_space(t, cone_angle);
+	t_target = to_stepping_space(t_target, cone_angle);
+	return from_stepping_space(t + std::ceil(std::fmax(t_target - t, 0.5f)), cone_angle);
+}
+static uint32_t mip_from_pos(vec3 pos, uint32_t max_cascade = NERF_CASCADES - 1) {
+	int exponent;
+	float maxval = std::max(std::max(std::fabs(pos.x - 0.5f), std::fabs(pos.y - 0.5f)), std::fabs(pos.z - 0.5f));
+	std::frexp(maxval, &exponent);
+	return (uint32_t)std::min(std::max(exponent + 1, 0), (int)max_cascade);
+}
+// nerf_device.cuh:461-495 (iter_cap == 0) and :497-534 (iter_cap == 200, loop runs for i in [1, cap))
+float advance_to_occupied(float t, float cone_angle, const Ray& ray, vec3 idir, const uint8_t* bits, uint32_t min_mip, uint32_t max_mip,
+	const BoundingBox& aabb, int iter_cap) {
+	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
+		vec3 pos = ray.at(t);
+		if (t >= MAX_DEPTH || !aabb.contains(pos)) return MAX_DEPTH;
+		uint32_t mip = std::min(std::max(mip_from_pos(pos), min_mip), max_mip);
+		if (!bits || occupied_at(pos, bits, mip)) return t;
+		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
+		t = advance_to_next_voxel(t, cone_angle, pos, ray.d, idir, mip);
+	}
+	return MAX_DEPTH;
+}
+
+// ---------------------------------------------------------------- testbed_nerf.cu:284-331, 2863-2880
+float bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out) {
+	// mean of max(v,0) over cascade 0 (reduce_sum; summation order: the oracle uses double, the threshold only
+	// matters when it drops below 0.01 — tests use grids whose mean is well above or feed 0/1 grids).
+	double sum = 0.0;
+	for (uint32_t i = 0; i < NERF_GRID_N_CELLS; ++i) sum += std::max(grid[i], 0.0f);
+	float mean = (float)(sum / NERF_GRID_N_CELLS);
+	float thresh = std::min(NERF_MIN_OPTICAL_THICKNESS, mean);
+	const uint32_t n_bytes_per_mip = NERF_GRID_N_CELLS / 8;
+	std::memset(out, 0, (size_t)n_bytes_per_mip * NERF_CASCADES);
+	for (uint32_t i = 0; i < n_bytes_per_mip * n_cascades; ++i) {
+		uint8_t b = 0;
+		for (int j = 0; j < 8; ++j) b |= grid[(size_t)i * 8 + j] > thresh ? (uint8_t)(1 << j) : 0;
+		out[i] = b;
+	}
+	for (uint32_t level = 1; level < NERF_CASCADES; ++level) {
+		const uint8_t* prev = out + (size_t)n_bytes_per_mip * (level - 1);
+		uint8_t* next = out + (size_t)n_bytes_per_mip * level;
+		for (uint32_t i = 0; i < n_bytes_per_mip / 8; ++i) {
+			uint8_t b = 0;
+			for (int j = 0; j < 8; ++j) b |= prev[i * 8 + j] > 0 ? (uint8_t)(1 << j) : 0;
+			uint32_t x = morton3D_invert(i >> 0) + NERF_GRIDSIZE / 8;
+			uint32_t y = morton3D_invert(i >> 1) + NERF_GRIDSIZE / 8;
+			uint32_t z = morton3D_invert(i >> 2) + NERF_GRIDSIZE / 8;
+			next[morton3D(x, y, z)] |= b;
+		}
+	}
+	return thresh;
+}
+
+// ---------------------------------------------------------------- tcnn grid.h:48-212, 668-721; common_device.h:651-718, 842-854
+struct GridLayout {
+	uint32_t L, F;
+	std::vector<uint32_t> offsets, res;
+	std::vector<float> scales;
+};
+GridLayout grid_layout(const orc_net_config& c) {
+	GridLayout g;
+	g.L = c.n_levels; g.F = c.n_features_per_level;
+	g.offsets.resize(g.L + 1); g.res.resize(g.L); g.scales.resize(g.L);
+	float log2_scale = std::log2(c.per_level_scale);
+	uint32_t offset = 0;
+	for (uint32_t i = 0; i < g.L; ++i) {
+		float scale = std::exp2f(i * log2_scale) * c.base_resolution - 1.0f;
+		uint32_t resolution = (uint32_t)std::ceil(scale) + 1;
+		uint32_t max_params = UINT32_MAX / 2;
+		uint32_t n = std::pow((float)resolution, 3) > (float)max_params ? max_params : resolution * resolution * resolution;
+		n = (n + 7) / 8 * 8;
+		n = std::min(n, 1u << c.log2_hashmap_size);
+		g.offsets[i] = offset;
+		offset += n;
+		g.scales[i] = scale;
+		g.res[i] = resolution;
+	}
+	g.offsets[g.L] = offset;
+	return g;
+}
+static uint32_t grid_index(uint32_t hashmap_size, uint32_t res, uint32_t x, uint32_t y, uint32_t z) {
+	uint32_t p[3] = {x, y, z};
+	uint32_t stride = 1, index = 0;
+	for (uint32_t dim = 0; dim < 3 && stride <= hashmap_size; ++dim) {
+		index += p[dim] * stride;
+		stride *= res;
+	}
+	if (hashmap_size < stride) index = (x * 1u) ^ (y * 2654435761u) ^ (z * 805459861u);
+	return index % hashmap_size;
+}
+// One sample: out[L*F] fp16. Weight is rounded to fp16, accumulation is an fp16 fma per corner (grid.h:162).
+static void encode_one(const GridLayout& g, const half_t* table, const float* pos_in, half_t* out) {
+	for (uint32_t level = 0; level < g.L; ++level) {
+		const half_t* grid = table + (size_t)g.offsets[level] * g.F;
+		uint32_t hashmap_size = g.offsets[level + 1] - g.offsets[level];
+		float scale = g.scales[level];
+		uint32_t res = g.res[level];
+		float pos[3];
+		uint32_t pg[3];
+		for (int d = 0; d < 3; ++d) {
+			float v = std::fmaf(scale, pos_in[d], 0.5f);
+			float fl = std::floor(v);
+			pg[d] = (uint32_t)(int)fl;
+			pos[d] = v - fl;
+		}
+		half_t acc[8] = {};
+		for (uint32_t idx = 0; idx < 8; ++idx) {
+			float weight = 1;
+			uint32_t pl[3];
+			for (int d = 0; d < 3; ++d) {
+				if ((idx & (1u << d)) == 0) { weight *= 1 - pos[d]; pl[d] = pg[d]; }
+				else { weight *= pos[d]; pl[d] = pg[d] + 1; }
+			}
+			uint32_t index = grid_index(hashmap_size, res, pl[0], pl[1], pl[2]) * g.F;
+			half_t w = f2h(weight);
+			for (uint32_t f = 0; f < g.F; ++f) acc[f] = hfma(w, grid[index + f], acc[f]);
+		}
+		for (uint32_t f = 0; f < g.F; ++f) out[level * g.F + f] = acc[f];
+	}
+}
+
+// ---------------------------------------------------------------- tcnn common_device.h:340-366 (degree 4 real SH)
+static void sh4(float x, float y, float z, half_t* out) {
+	float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+	out[0] = f2h(0.28209479177387814f);
+	out[1] = f2h(-0.48860251190291987f * y);
+	out[2] = f2h(0.48860251190291987f * z);
+	out[3] = f2h(-0.48860251190291987f * x);
+	out[4] = f2h(1.0925484305920792f * xy);
+	out[5] = f2h(-1.0925484305920792f * yz);
+	out[6] = f2h(0.94617469575755997f * z2 - 0.31539156525251999f);
+	out[7] = f2h(-1.0925484305920792f * xz);
+	out[8] = f2h(0.54627421529603959f * x2 - 0.54627421529603959f * y2);
+	out[9] = f2h(0.59004358992664352f * y * (-3.0f * x2 + y2));
+	out[10] = f2h(2.8906114426405538f * xy * z);
+	out[11] = f2h(0.45704579946446572f * y * (1.0f - 5.0f * z2));
+	out[12] = f2h(0.3731763325901154f * z * (5.0f * z2 - 3.0f));
+	out[13] = f2h(0.45704579946446572f * x * (1.0f - 5.0f * z2));
+	out[14] = f2h(1.4453057213202769f * z * (x2 - y2));
+	out[15] = f2h(0.59004358992664352f * x * (-x2 + 3.0f * y2));
+}
+
+// ---------------------------------------------------------------- tcnn fully_fused_mlp.cu:47-129,315-476,635-678
+// No biases; ReLU on hidden layers; weights row-major [out][in]; activations stored as fp16 between layers.
+// The reference accumulates in fp16 (wmma half accumulator); the oracle accumulates in fp32.
+struct MlpShape { uint32_t in, hidden_layers, out_padded; };
+static size_t mlp_n_params(const MlpShape& s) { return (size_t)64 * s.in + (size_t)(s.hidden_layers - 1) * 64 * 64 + (size_t)s.out_padded * 64; }
+static void mlp_forward(const MlpShape& s, const half_t* w, const half_t* in, half_t* out) {
+	half_t a[64], b[64];
+	for (uint32_t o = 0; o < 64; ++o) {
+		float acc = 0.0f;
+		for (uint32_t i = 0; i < s.in; ++i) acc += h2f(w[o * s.in + i]) * h2f(in[i]);
+		a[o] = f2h(std::max(acc, 0.0f));
+	}
+	w += 64 * s.in;
+	for (uint32_t l = 0; l + 1 < s.hidden_layers; ++l) {
+		for (uint32_t o = 0; o < 64; ++o) {
+			float acc = 0.0f;
+			for (uint32_t i = 0; i < 64; ++i) acc += h2f(w[o * 64 + i]) * h2f(a[i]);
+			b[o] = f2h(std::max(acc, 0.0f));
+		}
+		std::memcpy(a, b, sizeof(a));
+		w += 64 * 64;
+	}
+	for (uint32_t o = 0; o < s.out_padded; ++o) {
+		float acc = 0.0f;
+		for (uint32_t i = 0; i < 64; ++i) acc += h2f(w[o * 64 + i]) * h2f(a[i]);
+		out[o] = f2h(acc);
+	}
+}
+
+struct Net {
+	orc_net_config cfg;
+	GridLayout grid;
+	MlpShape density, rgb;
+	const half_t *w_density, *w_rgb, *table;
+};
+Net make_net(const orc_net_config& c, const uint16_t* params) {
+	Net n;
+	n.cfg = c;
+	n.grid = grid_layout(c);
+	n.density = {c.n_levels * c.n_features_per_level, c.density_hidden_layers, 16};
+	n.rgb = {32, c.rgb_hidden_layers, 16};
+	// nerf_network.h:356-371: [density MLP | rgb MLP | pos encoding | dir encoding (0 params)]
+	n.w_density = (const half_t*)params;
+	n.w_rgb = n.w_density + mlp_n_params(n.density);
+	n.table = n.w_rgb + mlp_n_params(n.rgb);
+	return n;
+}
+// nerf_network.h:105-139: coords = {warped pos[3], warped dt, warped dir[3]} -> raw (r,g,b,sigma) fp16
+void network_one(const Net& n, const float* coord, half_t out[4]) {
+	half_t enc[32], rgb_in[32], rgb_out[16];
+	encode_one(n.grid, n.table, coord, enc);
+	mlp_forward(n.density, n.w_density, enc, rgb_in); // 16 density outputs -> rgb input rows 0..15
+	sh4(coord[4] * 2.f - 1.f, coord[5] * 2.f - 1.f, coord[6] * 2.f - 1.f, rgb_in + 16);
+	mlp_forward(n.rgb, n.w_rgb, rgb_in, rgb_out);
+	out[0] = rgb_out[0]; out[1] = rgb_out[1]; out[2] = rgb_out[2];
+	out[3] = rgb_in[0]; // extract_density: density MLP channel 0 -> output row 3
+}
+
+// ---------------------------------------------------------------- nerf_device.cuh:203-314
+static float logistic(float x) { return 1.0f / (1.0f + std::exp(-x)); }
+static float network_to_rgb(float v, int act) {
+	switch (act) {
+		case 0: return v;
+		case 1: return v > 0.0f ? v : 0.0f;
+		case 2: return logistic(v);
+		case 3: return std::exp(clampf(v, -10.0f, 10.0f));
+	}
+	return 0.0f;
+}
+static float network_to_density(float v, int act) {
+	switch (act) {
+		case 0: return v;
+		case 1: return v > 0.0f ? v : 0.0f;
+		case 2: return logistic(v);
+		case 3: return std::exp(v);
+	}
+	return 0.0f;
+}
+static float warp_dt(float dt) {
+	float max_stepsize = MIN_CONE_STEPSIZE * (1 << (NERF_CASCADES - 1));
+	return (dt - MIN_CONE_STEPSIZE) / (max_stepsize - MIN_CONE_STEPSIZE);
+}
+static float unwarp_dt(float dt) {
+	float max_stepsize = MIN_CONE_STEPSIZE * (1 << (NERF_CASCADES - 1));
+	return dt * (max_stepsize - MIN_CONE_STEPSIZE) + MIN_CONE_STEPSIZE;
+}
+float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
+
+// ---------------------------------------------------------------- per-pixel ray set-up: testbed_nerf.cu:1428-1544 + 333-381
+struct RayState { vec3 o, d; float t; bool alive; };
+RayState init_ray(const orc_render_params& p, const uint8_t* bits, uint32_t x, uint32_t y, float* depth_px) {
+	RayState r = {};
+	uint32_t idx = x + (uint32_t)p.width * y;
+	Ray ray = pixel_ray(p, x, y);
+	if (depth_px && *depth_px < 0.01f) *depth_px = MAX_DEPTH; // :1490-1493 (keeps a mesh depth already present)
+	ray.d = normalize(ray.d);
+	BoundingBox render_aabb = bb_from(p.render_aabb);
+	float t = std::fmax(render_aabb.ray_intersect(ray.o, ray.d).x, 0.0f) + 1e-6f;
+	r.o = ray.o; r.d = ray.d;
+	if (!render_aabb.contains(ray.at(t))) { r.alive = false; return r; }
+	// advance_pos_nerf :333-362
+	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / ray.d;
+	float cone = p.cone_angle_constant;
+	t = advance_n_steps(t, cone, ld_random_val(p.spp, idx * 786433u));
+	t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, 0);
+	if (t >= MAX_DEPTH) { r.alive = false; return r; }
+	r.t = t; r.alive = true;
+	return r;
+}
+
+template <typename F>
+static void parallel_rows(int n_rows, int n_threads, F&& f) {
+	if (n_threads <= 1) { for (int y = 0; y < n_rows; ++y) f(y); return; }
+	std::atomic<int> next{0};
+	std::vector<std::thread> th;
+	for (int i = 0; i < n_threads; ++i) th.emplace_back([&] { for (int y; (y = next.fetch_add(1)) < n_rows;) f(y); });
+	for (auto& t : th) t.join();
+}
+
+// testbed_nerf.cu:2022-2144 (trace) + 430-477 (inputs) + 528-735 (composite) + 1361-1401 / geometry :1826-1871 (shade).
+// The pass/compaction chunking of the reference does not change a ray's result, so the oracle walks each ray to its end.
+uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* bits, float* frame, float* depth, uint32_t* n_steps_out, bool depth_test) {
+	BoundingBox render_aabb = bb_from(p.render_aabb), train_aabb = bb_from(p.train_aabb);
+	cam_t cam1 = cam_from(p.cam1);
+	vec3 cam_fwd = cam1.c[2], cam_pos = cam1.c[3];
+	std::atomic<uint64_t> total{0};
+	parallel_rows(p.height, p.n_threads, [&](int y) {
+		uint64_t row_total = 0;
+		for (int x = 0; x < p.width; ++x) {
+			uint32_t idx = x + p.width * y;
+			if (n_steps_out) n_steps_out[idx] = 0;
+			RayState r = init_ray(p, bits, x, y, &depth[idx]);
+			if (!r.alive) continue;
+			Ray ray = {r.o, r.d};
+			vec3 idir = vec3{1.0f, 1.0f, 1.0f} / r.d;
+			float cone = p.cone_angle_constant;
+			float t = r.t;
+			vec4 rgba = {0, 0, 0, 0};
+			float local_depth = 0.0f, max_weight = 0.0f;
+			uint32_t n = 0;
+			float clip_depth = (p.depth_merge_clip && depth_test) ? depth[idx] : MAX_DEPTH;
+			while (true) {
+				t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap);
+				if (t >= MAX_DEPTH) break;
+				float dt = calc_dt(t, cone);
+				vec3 wp = train_aabb.relative_pos(ray.at(t));
+				if (p.depth_merge_clip && depth_test) {
+					vec3 up = train_aabb.min + wp * train_aabb.diag();
+					if (dot(cam_fwd, up - cam_pos) > clip_depth) break;
+				}
+				vec3 wd = (r.d + 1.0f) * 0.5f;
+				float coord[7] = {wp.x, wp.y, wp.z, warp_dt(dt), wd.x, wd.y, wd.z};
+				half_t out[4];
+				network_one(net, coord, out);
+				++n;
+				vec3 pos = train_aabb.min + wp * train_aabb.diag();
+				float T = 1.f - rgba.w;
+				float dtu = unwarp_dt(coord[3]);
+				float alpha = 1.f - std::exp(-network_to_density(h2f(out[3]), p.density_activation) * dtu);
+				float weight = alpha * T;
+				vec3 rgb = {network_to_rgb(h2f(out[0]), p.rgb_activation), network_to_rgb(h2f(out[1]), p.rgb_activation), network_to_rgb(h2f(out[2]), p.rgb_activation)};
+				rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
+				if (weight > max_weight) { max_weight = weight; local_depth = dot(cam_fwd, pos - cam_pos); }
+				if (rgba.w > (1.0f - p.min_transmittance)) {
+					float a = rgba.w;
+					rgba.x /= a; rgba.y /= a; rgba.z /= a; rgba.w /= a;
+					break;
+				}
+				t += dt;
+			}
+			row_total += n;
+			if (n_steps_out) n_steps_out[idx] = n;
+			if (!(rgba.w > 0.001f)) continue;                    // compact_kernel_nerf :1419
+			if (depth_test && !p.depth_merge_clip && local_depth > depth[idx]) continue; // geometry :1843-1846
+			vec4 tmp = rgba;
+			if (!p.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+			float* fb = frame + 4 * (size_t)idx;
+			float ia = 1.0f - tmp.w;
+			fb[0] = tmp.x + fb[0] * ia; fb[1] = tmp.y + fb[1] * ia; fb[2] = tmp.z + fb[2] * ia; fb[3] = tmp.w + fb[3] * ia;
+			if (tmp.w > 0.2f) depth[idx] = local_depth;
+		}
+		total += row_total;
+	});
+	return total;
+}
+
+} // namespace orc
+
+using namespace orc;
+
+extern "C" {
+
+float orc_ld_random_val(uint32_t index, uint32_t seed) { return ld_random_val(index, seed); }
+void orc_ld_random_pixel_offset(uint32_t spp, float out[2]) { vec2 v = ld_random_pixel_offset(spp); out[0] = v.x; out[1] = v.y; }
+void orc_bbox_ray_intersect(const float bb[6], const float o[3], const float d[3], float out[2]) {
+	vec2 r = bb_from(bb).ray_intersect({o[0], o[1], o[2]}, {d[0], d[1], d[2]});
+	out[0] = r.x; out[1] = r.y;
+}
+uint32_t orc_morton3D(uint32_t x, uint32_t y, uint32_t z) { return morton3D(x, y, z); }
+float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const float d[3], const uint8_t* bitfield,
+	uint32_t min_mip, uint32_t max_mip, const float aabb[6], int32_t iter_cap) {
+	Ray ray = {{o[0], o[1], o[2]}, {d[0], d[1], d[2]}};
+	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / ray.d;
+	return advance_to_occupied(t, cone_angle, ray, idir, bitfield, min_mip, max_mip, bb_from(aabb), iter_cap);
+}
+float orc_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
+float orc_srgb_to_linear(float v) { return srgb_to_linear(v); }
+
+float orc_bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out) { return bitfield_from_grid(grid, n_cascades, out); }
+
+void orc_init_rays(const orc_render_params* p, const uint8_t* bitfield, float* origins, float* dirs, float* t, uint8_t* alive) {
+	parallel_rows(p->height, p->n_threads, [&](int y) {
+		for (int x = 0; x < p->width; ++x) {
+			uint32_t idx = x + p->width * y;
+			RayState r = init_ray(*p, bitfield, x, y, nullptr);
+			origins[3 * idx] = r.o.x; origins[3 * idx + 1] = r.o.y; origins[3 * idx + 2] = r.o.z;
+			dirs[3 * idx] = r.d.x; dirs[3 * idx + 1] = r.d.y; dirs[3 * idx + 2] = r.d.z;
+			t[idx] = r.alive ? r.t : MAX_DEPTH;
+			alive[idx] = r.alive;
+		}
+	});
+}
+
+void orc_march_all(const orc_render_params* p, const uint8_t* bitfield, uint32_t n_rays, const float* origins, const float* dirs,
+	const float* t0, const uint8_t* alive, uint32_t* counts, float* samples, uint32_t max_per_ray) {
+	BoundingBox render_aabb = bb_from(p->render_aabb);
+	for (uint32_t i = 0; i < n_rays; ++i) {
+		counts[i] = 0;
+		if (!alive[i]) continue;
+		Ray ray = {{origins[3 * i], origins[3 * i + 1], origins[3 * i + 2]}, {dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]}};
+		vec3 idir = vec3{1.0f, 1.0f, 1.0f} / ray.d;
+		float t = t0[i];
+		uint32_t n = 0;
+		while (true) {
+			t = advance_to_occupied(t, p->cone_angle_constant, ray, idir, bitfield, 0, p->max_mip, render_aabb, p->dda_iter_cap);
+			if (t >= MAX_DEPTH) break;
+			float dt = calc_dt(t, p->cone_angle_constant);
+			if (samples && n < max_per_ray) {
+				vec3 pos = ray.at(t);
+				float* s = samples + ((size_t)i * max_per_ray + n) * 4;
+				s[0] = pos.x; s[1] = pos.y; s[2] = pos.z; s[3] = dt;
+			}
+			++n;
+			t += dt;
+		}
+		counts[i] = n;
+	}
+}
+
+size_t orc_n_params(const orc_net_config* c) {
+	GridLayout g = grid_layout(*c);
+	MlpShape d = {c->n_levels * c->n_features_per_level, c->density_hidden_layers, 16}, r = {32, c->rgb_hidden_layers, 16};
+	return mlp_n_params(d) + mlp_n_params(r) + (size_t)g.offsets[g.L] * g.F;
+}
+size_t orc_grid_param_offset(const orc_net_config* c) {
+	MlpShape d = {c->n_levels * c->n_features_per_level, c->density_hidden_layers, 16}, r = {32, c->rgb_hidden_layers, 16};
+	return mlp_n_params(d) + mlp_n_params(r);
+}
+void orc_grid_layout(const orc_net_config* c, uint32_t* offsets, float* scales, uint32_t* resolutions) {
+	GridLayout g = grid_layout(*c);
+	for (uint32_t i = 0; i <= g.L; ++i) offsets[i] = g.offsets[i];
+	for (uint32_t i = 0; i < g.L; ++i) { scales[i] = g.scales[i]; resolutions[i] = g.res[i]; }
+}
+void orc_encode(const orc_net_config* c, const uint16_t* params, const float* positions, uint32_t n, uint16_t* out) {
+	Net net = make_net(*c, params);
+	for (uint32_t i = 0; i < n; ++i) encode_one(net.grid, net.table, positions + 3 * (size_t)i, (half_t*)out + 32 * (size_t)i);
+}
+void orc_sh4(const float* d, uint32_t n, uint16_t* out) {
+	for (uint32_t i = 0; i < n; ++i) sh4(d[3 * i] * 2.f - 1.f, d[3 * i + 1] * 2.f - 1.f, d[3 * i + 2] * 2.f - 1.f, (half_t*)out + 16 * (size_t)i);
+}
+void orc_network(const orc_net_config* c, const uint16_t* params, const float* coords, uint32_t n, uint16_t* out) {
+	Net net = make_net(*c, params);
+	for (uint32_t i = 0; i < n; ++i) network_one(net, coords + 7 * (size_t)i, (half_t*)out + 4 * (size_t)i);
+}
+
+uint64_t orc_render_nerf(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
+	float* frame, float* depth, uint32_t* n_steps_out, int32_t depth_test) {
+	Net net = make_net(*c, params);
+	return render_nerf(*p, net, bitfield, frame, depth, n_steps_out, depth_test != 0);
+}
+
+} // extern "C"

@@ -1,0 +1,84 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY. Thin C wrapper that compiles the reference's OWN NGP_HOST_DEVICE functions for
+// the host (nvcc, no GPU needed to run them) straight from /root/reference, so the CPU restatement in orc_*.cpp can be
+// pinned against them bit for bit. No reference source is copied: this file only #includes the headers where they lie.
+// Output goes to oracle/_ref/ (git-ignored). Built by `make -C oracle ref`.
+#include <cstdio>
+#include <neural-graphics-primitives/common.h>
+#include <neural-graphics-primitives/common_device.cuh>
+#include <neural-graphics-primitives/bounding_box.cuh>
+#include <neural-graphics-primitives/random_val.cuh>
+#include <neural-graphics-primitives/nerf_device.cuh>
+#include <neural-graphics-primitives/triangle.cuh>
+
+using namespace ngp;
+
+extern "C" {
+
+float ref_ld_random_val(uint32_t index, uint32_t seed) { return ld_random_val(index, seed); }
+
+void ref_ld_random_pixel_offset(uint32_t spp, float out[2]) {
+	vec2 v = ld_random_pixel_offset(spp);
+	out[0] = v.x; out[1] = v.y;
+}
+
+void ref_bbox_ray_intersect(const float bb[6], const float o[3], const float d[3], float out[2]) {
+	BoundingBox b(vec3(bb[0], bb[1], bb[2]), vec3(bb[3], bb[4], bb[5]));
+	vec2 r = b.ray_intersect(vec3(o[0], o[1], o[2]), vec3(d[0], d[1], d[2]));
+	out[0] = r.x; out[1] = r.y;
+}
+
+float ref_triangle_ray_intersect(const float tri[9], const float o[3], const float d[3]) {
+	Triangle t{vec3(tri[0], tri[1], tri[2]), vec3(tri[3], tri[4], tri[5]), vec3(tri[6], tri[7], tri[8])};
+	return t.ray_intersect(vec3(o[0], o[1], o[2]), vec3(d[0], d[1], d[2]));
+}
+
+uint32_t ref_morton3D(uint32_t x, uint32_t y, uint32_t z) { return tcnn::morton3D(x, y, z); }
+
+float ref_advance_to_occupied(float t, float cone_angle, const float o[3], const float d[3], const uint8_t* bitfield,
+	uint32_t min_mip, uint32_t max_mip, const float aabb[6], int32_t iter_cap) {
+	Ray ray{vec3(o[0], o[1], o[2]), vec3(d[0], d[1], d[2])};
+	vec3 idir = vec3(1.0f) / ray.d;
+	BoundingBox b(vec3(aabb[0], aabb[1], aabb[2]), vec3(aabb[3], aabb[4], aabb[5]));
+	if (iter_cap > 0) {
+		return if_unoccupied_advance_to_next_occupied_voxel_geometry(t, cone_angle, ray, idir, bitfield, min_mip, max_mip, b);
+	}
+	return if_unoccupied_advance_to_next_occupied_voxel(t, cone_angle, ray, idir, bitfield, min_mip, max_mip, b);
+}
+
+float ref_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
+float ref_advance_n_steps(float t, float cone_angle, float n) { return advance_n_steps(t, cone_angle, n); }
+float ref_srgb_to_linear(float v) { return srgb_to_linear(v); }
+float ref_warp_dt(float dt) { return warp_dt(dt); }
+float ref_unwarp_dt(float dt) { return unwarp_dt(dt); }
+
+// init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1428-1544) up to the normalised ray: the kernel itself is
+// __global__, but every function it calls for the pinhole path is host-callable.
+void ref_pixel_ray(uint32_t spp, uint32_t x, uint32_t y, int32_t w, int32_t h, const float focal[2], const float cam0[12], const float cam1[12],
+	const float rolling_shutter[4], const float screen_center[2], int32_t snap_to_pixel_centers, float near_distance, float out_o[3], float out_d[3]) {
+	ivec2 resolution(w, h);
+	uint32_t idx = x + resolution.x * y;
+	mat4x3 c0, c1;
+	for (int i = 0; i < 4; ++i) { c0[i] = vec3(cam0[3*i], cam0[3*i+1], cam0[3*i+2]); c1[i] = vec3(cam1[3*i], cam1[3*i+1], cam1[3*i+2]); }
+	vec4 rs(rolling_shutter[0], rolling_shutter[1], rolling_shutter[2], rolling_shutter[3]);
+	vec2 pixel_offset = ld_random_pixel_offset(snap_to_pixel_centers ? 0 : spp);
+	vec2 uv = vec2{(float)x + pixel_offset.x, (float)y + pixel_offset.y} / vec2(resolution);
+	mat4x3 camera = get_xform_given_rolling_shutter({c0, c1}, rs, uv, ld_random_val(spp, idx * 72239731));
+	Ray ray = uv_to_ray(spp, uv, resolution, vec2(focal[0], focal[1]), camera, vec2(screen_center[0], screen_center[1]), vec3(0.0f), near_distance, 1.0f, 0.0f);
+	ray.d = normalize(ray.d);
+	out_o[0] = ray.o.x; out_o[1] = ray.o.y; out_o[2] = ray.o.z;
+	out_d[0] = ray.d.x; out_d[1] = ray.d.y; out_d[2] = ray.d.z;
+}
+
+// advance_pos_nerf (src/testbed_nerf.cu:333-362) body, host-callable pieces only.
+float ref_start_t(uint32_t spp, uint32_t idx, const float o[3], const float d[3], const float aabb[6], float cone_angle,
+	const uint8_t* bitfield, uint32_t max_mip) {
+	Ray ray{vec3(o[0], o[1], o[2]), vec3(d[0], d[1], d[2])};
+	BoundingBox b(vec3(aabb[0], aabb[1], aabb[2]), vec3(aabb[3], aabb[4], aabb[5]));
+	float t = fmaxf(b.ray_intersect(ray.o, ray.d).x, 0.0f) + 1e-6f;
+	if (!b.contains(ray(t))) return MAX_DEPTH();
+	vec3 idir = vec3(1.0f) / ray.d;
+	t = advance_n_steps(t, cone_angle, ld_random_val(spp, idx * 786433));
+	return if_unoccupied_advance_to_next_occupied_voxel(t, cone_angle, ray, idir, bitfield, 0, max_mip, b);
+}
+
+}

@@ -1,0 +1,120 @@
+/* hybrid_nerf.h — C ABI of the B200-native hybrid NeRF + mesh render path.
+ *
+ * Drop-in boundary for the render path of ngp::Testbed (reference: include/neural-graphics-primitives/testbed.h).
+ * Plain pointers and sizes only; no C++/torch types. Every call returns 0 on success, non-zero on failure;
+ * hn_last_error() gives the message (the reference throws std::runtime_error instead, src/main.cu:209-223).
+ * The library has no CPU fallback: every entry point that computes needs a CUDA device (sm_100a).
+ *
+ * Conventions (identical to the reference):
+ *  - camera: float[12] = mat4x3, 4 columns x vec3 {right, down, forward, position} in NeRF space
+ *  - frame buffer: float4 per pixel, row-major idx = x + W*y, premultiplied linear RGBA (CudaRenderBufferView,
+ *    render_buffer.h:162-171); depth buffer: float per pixel, view-space z, 16384 = nothing
+ *  - parameter blob: fp16 [density MLP | rgb MLP | hash grid] (nerf_network.h:356-371), MLP weights row-major [out][in]
+ */
+#ifndef HYBRID_NERF_H
+#define HYBRID_NERF_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hn_context hn_context;
+
+/* ---- lifetime / errors ---- */
+int hn_create(hn_context** out, int cuda_device);            /* replaces Testbed::Testbed(ETestbedMode), testbed.h:69 */
+void hn_destroy(hn_context* ctx);
+const char* hn_last_error(const hn_context* ctx);             /* replaces exceptions across the boundary */
+const char* hn_version(void);
+
+/* ---- network configuration (configs/nerf/*.json, configs/geometry/*.json incl. "parent" merge) ---- */
+int hn_load_network_config(hn_context* ctx, const char* json_path);        /* Testbed::reload_network_from_file, testbed.h:607 */
+int hn_load_network_config_string(hn_context* ctx, const char* json_text); /* Testbed::reload_network_from_json, testbed.h:608 */
+int hn_set_aabb_scale(hn_context* ctx, int aabb_scale);                    /* nerf.training.dataset.aabb_scale (drives per_level_scale, max_cascade, cone angle) */
+
+typedef struct {
+	uint32_t n_levels, n_features_per_level, log2_hashmap_size, base_resolution;
+	float per_level_scale;
+	uint32_t density_hidden_layers, rgb_hidden_layers;
+	uint64_t n_params;            /* fp16 elements in the blob */
+	uint64_t grid_param_offset;   /* element offset of the hash table */
+	uint32_t level_offsets[17];   /* GridOffsetTable, tcnn grid.h:692-721 */
+	float level_scales[16];
+	uint32_t level_resolutions[16];
+} hn_network_info;
+int hn_get_network_info(const hn_context* ctx, hn_network_info* out);
+
+/* dtype: 0 = fp16, 1 = fp32 (converted to fp16 like Trainer's inference copy). Host pointer. */
+int hn_set_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype);   /* Trainer::set_params / deserialize, tcnn trainer.h:275-351 */
+
+/* ---- occupancy (a-20) ---- */
+/* grid: float[128^3 * n_cascades] in Morton order (host). Builds the 8-mip bitfield on the device. */
+int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades);     /* update_density_grid_mean_and_bitfield, src/testbed_nerf.cu:2863-2880 */
+int hn_set_occupancy_bitfield(hn_context* ctx, const uint8_t* bits, size_t n_bytes);  /* 128^3/8*8 bytes */
+int hn_get_occupancy_bitfield(hn_context* ctx, uint8_t* out, size_t n_bytes);
+
+/* ---- scene (data/geometry/*.json: {"geometry":[{"center","path","type":"Mesh"|"Nerf"}]}) ---- */
+int hn_load_scene(hn_context* ctx, const char* scene_json_path);                      /* Testbed::load_scene, src/testbed_geometry_training.cu:3101-3210 */
+/* triangles: float[n][9] host. normalize != 0 applies load_mesh's unit-cube normalisation + centre offset (:2805-2823). */
+int hn_add_mesh(hn_context* ctx, const float* triangles, size_t n_triangles, const float center[3], int normalize);
+int hn_load_mesh_file(hn_context* ctx, const char* obj_or_stl_path, const float center[3]); /* Testbed::load_mesh, :2786-2866 */
+int hn_build_scene(hn_context* ctx);                                                  /* GeometryBvh::build_mesh + m_aabb = root inflated by 4 (:3180-3189) */
+int hn_clear_scene(hn_context* ctx);
+int hn_get_scene_aabb(const hn_context* ctx, float out[6]);                           /* root box of all meshes (before inflation) */
+
+/* ---- render state (public Testbed members; names follow src/python_api.cu:482-567) ---- */
+int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values);
+int hn_get_option(const hn_context* ctx, const char* name, float* values, int n_values);
+
+/* ---- rendering ---- */
+/* Testbed::render_frame(stream, cam0, cam1, prev, screen_center, relative_focal_length, rolling_shutter, ...) testbed.h:561-575
+ * = clear + mesh pass + NeRF pass (render_frame_main, src/testbed.cu:4722-4894). frame_dev/depth_dev are DEVICE pointers
+ * (W*H*4 floats / W*H floats). Asynchronous on `cuda_stream` (a cudaStream_t, NULL = default stream) except for the
+ * marching loop's alive-ray read-backs. spp_index = CudaRenderBufferView::spp. */
+int hn_render_frame(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2],
+	const float relative_focal_length[2], const float rolling_shutter[4], uint32_t spp_index,
+	int width, int height, float* frame_dev, float* depth_dev, void* cuda_stream);
+
+/* pyngp.Testbed.render(width, height, spp, linear) -> float32[h][w][4] (src/python_api.cu:124-202, 417-426):
+ * spp passes accumulated (render_buffer.cu:228), optional sRGB tonemap (linear == 0), result copied to HOST memory. */
+int hn_render_to_host(hn_context* ctx, int width, int height, int spp, int linear, float* rgba_host, float* depth_host);
+int hn_set_camera(hn_context* ctx, const float cam[12]);                              /* set_nerf_camera_matrix, python_api.cu:443 */
+
+/* multi-GPU: this process renders only the screen tiles t with t % world == rank (tile_w x tile_h pixels). */
+int hn_set_tile_shard(hn_context* ctx, int rank, int world, int tile_w, int tile_h);
+/* pack this rank's tiles of (frame, depth) into a contiguous buffer [n_tiles][tile_h*tile_w][5 floats] and back. */
+int hn_tile_count(const hn_context* ctx, int width, int height, int rank, int world, uint32_t* n_tiles);
+int hn_pack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev, float* packed_dev, void* cuda_stream);
+int hn_unpack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* packed_dev, float* frame_dev, float* depth_dev, void* cuda_stream);
+
+typedef struct {
+	uint64_t n_samples;        /* network samples evaluated in the last frame (ERenderMode::Cost sum) */
+	uint64_t n_samples_composited;
+	uint32_t n_rays_alive;     /* rays that entered the volume */
+	uint32_t n_passes;         /* march/eval/composite rounds */
+	uint32_t n_kernel_launches;
+	float ms_mesh, ms_raygen, ms_march, ms_eval, ms_composite, ms_total; /* filled when option "profile" = 1 */
+} hn_frame_stats;
+int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out);
+
+/* ---- operator-level entry points (the reference's kernels taken one at a time; used by the parity tests) ---- */
+/* a-4..a-6: per pixel origin[3], dir[3], t, alive after init_rays + advance_pos (host outputs). */
+int hn_op_init_rays(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2], const float relative_focal_length[2],
+	const float rolling_shutter[4], uint32_t spp_index, int width, int height, float* origins, float* dirs, float* t, uint8_t* alive);
+/* a-7/a-8: march every ray to the end of the box without termination; counts[n], samples [n][max_per_ray][4] = x,y,z,dt (host). */
+int hn_op_march_all(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t0, const uint8_t* alive,
+	uint32_t* counts, float* samples, uint32_t max_per_ray);
+/* a-10: hash-grid encoding of n positions in [0,1]^3 -> fp16 [n][32] (host). */
+int hn_op_encode(hn_context* ctx, const float* positions, uint32_t n, uint16_t* out);
+/* a-10..a-13: samples come in ray chunks of 32 sharing one direction. positions [n][4] = un-warped x,y,z,dt (n % 32 == 0),
+ * dirs [n/32][3] unit vectors; out fp16 [n][4] raw (r,g,b,sigma). */
+int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, uint32_t n, uint16_t* out);
+/* a-17/a-18: nearest hit per ray: mesh index, ORIGINAL triangle index, t (100 = miss) (host in/out). */
+int hn_op_trace(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, int32_t* mesh_idx, int32_t* tri_idx, float* t);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,500 @@
+// C ABI (include/hybrid_nerf.h): host orchestration of the hybrid frame. One context per process/GPU; all per-frame
+// scratch comes from a persistent workspace owned by the context (the reference re-allocates from tcnn's arena per frame).
+#include "hn_context.h"
+#include "hn_device_math.cuh"
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <chrono>
+
+using namespace hn;
+
+#define HN_TRY(ctx) try {
+#define HN_CATCH(ctx) return 0; } catch (const std::exception& e) { if (ctx) (ctx)->error = e.what(); return 1; } catch (...) { if (ctx) (ctx)->error = "unknown error"; return 1; }
+
+static void need(bool cond, const char* msg) { if (!cond) throw std::runtime_error(msg); }
+
+extern "C" {
+
+const char* hn_version(void) { return "hybrid-nerf-b200 0.1 (sm_100a)"; }
+
+int hn_create(hn_context** out, int cuda_device) {
+	if (!out) return 1;
+	*out = nullptr;
+	hn_context* ctx = new hn_context();
+	*out = ctx; // returned even on failure so that hn_last_error can explain
+	HN_TRY(ctx)
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) throw std::runtime_error(std::string("no CUDA device: this library has no CPU fallback (") + cudaGetErrorString(e) + ")");
+	need(cuda_device >= 0 && cuda_device < n, "invalid CUDA device ordinal");
+	ctx->device = cuda_device;
+	HN_CUDA(cudaSetDevice(cuda_device));
+	cudaDeviceProp prop;
+	HN_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
+	if (prop.major != 10) throw std::runtime_error(std::string("device '") + prop.name + "' is not sm_100: kernels are built for sm_100a only");
+	HN_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+	HN_CUDA(cudaMallocHost((void**)&ctx->pinned_counters, CNT_N * sizeof(uint32_t) * 2));
+	ctx->counters.ensure(CNT_N);
+	ctx->bitfield.ensure(BITFIELD_BYTES);
+	HN_CATCH(ctx)
+}
+
+void hn_destroy(hn_context* ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaDeviceSynchronize();
+	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+const char* hn_last_error(const hn_context* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
+
+// ---------------------------------------------------------------- network
+int hn_load_network_config(hn_context* ctx, const char* json_path) {
+	HN_TRY(ctx)
+	std::string path = json_path;
+	size_t p = path.find_last_of('/');
+	load_network_config_text(ctx, read_text_file(path), p == std::string::npos ? "." : path.substr(0, p));
+	HN_CATCH(ctx)
+}
+int hn_load_network_config_string(hn_context* ctx, const char* json_text) {
+	HN_TRY(ctx)
+	load_network_config_text(ctx, json_text, ".");
+	HN_CATCH(ctx)
+}
+int hn_set_aabb_scale(hn_context* ctx, int aabb_scale) {
+	HN_TRY(ctx)
+	need(aabb_scale >= 1 && aabb_scale <= 128 && (aabb_scale & (aabb_scale - 1)) == 0, "aabb_scale must be a power of two in [1,128]");
+	ctx->aabb_scale = aabb_scale;
+	if (ctx->has_net) load_network_config_text(ctx, ctx->config_text, ctx->config_dir);
+	// the render box follows the training box: [0.5 - s/2, 0.5 + s/2]^3 (src/testbed_nerf.cu:2722-2727)
+	for (int d = 0; d < 3; ++d) { ctx->opt.render_aabb[d] = 0.5f - 0.5f * aabb_scale; ctx->opt.render_aabb[3 + d] = 0.5f + 0.5f * aabb_scale; }
+	HN_CATCH(ctx)
+}
+int hn_get_network_info(const hn_context* ctx, hn_network_info* out) {
+	if (!ctx || !out || !ctx->has_net) return 1;
+	const NetCfg& n = ctx->net;
+	std::memset(out, 0, sizeof(*out));
+	out->n_levels = n.L; out->n_features_per_level = n.F; out->log2_hashmap_size = n.log2_T; out->base_resolution = n.base_res;
+	out->per_level_scale = n.per_level_scale; out->density_hidden_layers = n.density_hidden; out->rgb_hidden_layers = n.rgb_hidden;
+	out->n_params = n.n_params; out->grid_param_offset = n.grid_offset;
+	for (uint32_t i = 0; i <= n.L; ++i) out->level_offsets[i] = n.offsets[i];
+	for (uint32_t i = 0; i < n.L; ++i) { out->level_scales[i] = n.scales[i]; out->level_resolutions[i] = n.res[i]; }
+	return 0;
+}
+int hn_set_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype) {
+	HN_TRY(ctx)
+	need(ctx->has_net, "load a network config first");
+	need(n_elements == ctx->net.n_params, "parameter blob has the wrong number of elements");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	ctx->params.ensure(n_elements);
+	if (dtype == 0) {
+		HN_CUDA(cudaMemcpy(ctx->params.p, blob, n_elements * sizeof(__half), cudaMemcpyHostToDevice));
+	} else if (dtype == 1) {
+		std::vector<__half> tmp(n_elements);
+		const float* f = (const float*)blob;
+		for (size_t i = 0; i < n_elements; ++i) tmp[i] = __float2half_rn(f[i]);
+		HN_CUDA(cudaMemcpy(ctx->params.p, tmp.data(), n_elements * sizeof(__half), cudaMemcpyHostToDevice));
+	} else {
+		throw std::runtime_error("dtype must be 0 (fp16) or 1 (fp32)");
+	}
+	ctx->has_params = true;
+	HN_CATCH(ctx)
+}
+
+// ---------------------------------------------------------------- occupancy
+int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades) {
+	HN_TRY(ctx)
+	need(n_cascades >= 1 && n_cascades <= CASCADES, "n_cascades must be in [1,8]");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	DevBuf<float> d_grid;
+	d_grid.ensure((size_t)GRID_CELLS * n_cascades);
+	DevBuf<double> d_sum;
+	d_sum.ensure(1);
+	HN_CUDA(cudaMemcpyAsync(d_grid.p, grid, (size_t)GRID_CELLS * n_cascades * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	launch_grid_mean(d_grid.p, (float*)d_sum.p, ctx->stream);
+	double sum = 0.0;
+	HN_CUDA(cudaMemcpyAsync(&sum, d_sum.p, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	const float mean = (float)(sum / GRID_CELLS);
+	const float thresh = std::min(0.01f, mean); // NERF_MIN_OPTICAL_THICKNESS, src/testbed_nerf.cu:297
+	launch_grid_to_bitfield(d_grid.p, n_cascades, thresh, ctx->bitfield.p, ctx->stream);
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CUDA(cudaGetLastError());
+	ctx->has_bitfield = true;
+	HN_CATCH(ctx)
+}
+int hn_set_occupancy_bitfield(hn_context* ctx, const uint8_t* bits, size_t n_bytes) {
+	HN_TRY(ctx)
+	need(n_bytes == BITFIELD_BYTES, "bitfield must be 128^3/8*8 bytes");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaMemcpy(ctx->bitfield.p, bits, n_bytes, cudaMemcpyHostToDevice));
+	ctx->has_bitfield = true;
+	HN_CATCH(ctx)
+}
+int hn_get_occupancy_bitfield(hn_context* ctx, uint8_t* out, size_t n_bytes) {
+	HN_TRY(ctx)
+	need(n_bytes == BITFIELD_BYTES && ctx->has_bitfield, "no bitfield / wrong size");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaMemcpy(out, ctx->bitfield.p, n_bytes, cudaMemcpyDeviceToHost));
+	HN_CATCH(ctx)
+}
+
+// ---------------------------------------------------------------- scene
+int hn_load_scene(hn_context* ctx, const char* path) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); load_scene_file(ctx, path); HN_CATCH(ctx) }
+int hn_add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], int normalize) { HN_TRY(ctx) add_mesh(ctx, tris, n, center, normalize != 0); HN_CATCH(ctx) }
+int hn_load_mesh_file(hn_context* ctx, const char* path, const float center[3]) { HN_TRY(ctx) load_mesh_file(ctx, path, center); HN_CATCH(ctx) }
+int hn_build_scene(hn_context* ctx) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); build_scene(ctx); HN_CATCH(ctx) }
+int hn_clear_scene(hn_context* ctx) { HN_TRY(ctx) ctx->meshes.clear(); ctx->scene_built = false; HN_CATCH(ctx) }
+int hn_get_scene_aabb(const hn_context* ctx, float out[6]) { if (!ctx || !ctx->scene_built) return 1; std::memcpy(out, ctx->scene_bb, 24); return 0; }
+
+// ---------------------------------------------------------------- options
+struct OptRef { void* p; int n; bool is_int; };
+static std::map<std::string, OptRef> option_table(hn_context* c) {
+	Options& o = c->opt;
+	return {
+		{"snap_to_pixel_centers", {&o.snap_to_pixel_centers, 1, true}}, {"render_near_distance", {&o.near_distance, 1, false}},
+		{"render_aabb", {o.render_aabb, 6, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
+		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
+		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
+		{"linear_colors", {&o.linear_colors, 1, true}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
+		{"sun_dir", {o.sun_dir, 3, false}}, {"up_dir", {o.up_dir, 3, false}}, {"floor_enable", {&o.floor_enable, 1, true}},
+		{"brdf", {o.brdf, 13, false}}, {"compat_nearest_aabb_only", {&o.compat_nearest_aabb_only, 1, true}},
+		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
+		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
+		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
+		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+	};
+}
+int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
+	HN_TRY(ctx)
+	auto t = option_table(ctx);
+	auto it = t.find(name);
+	if (it == t.end()) throw std::runtime_error(std::string("unknown option '") + name + "'");
+	need(n_values == it->second.n, "wrong number of values for option");
+	for (int i = 0; i < n_values; ++i) {
+		if (it->second.is_int) ((int*)it->second.p)[i] = (int)values[i];
+		else ((float*)it->second.p)[i] = values[i];
+	}
+	if (std::string(name) == "mesh_aabb") ctx->opt.mesh_aabb_user = 1;
+	HN_CATCH(ctx)
+}
+int hn_get_option(const hn_context* cctx, const char* name, float* values, int n_values) {
+	hn_context* ctx = const_cast<hn_context*>(cctx);
+	HN_TRY(ctx)
+	auto t = option_table(ctx);
+	auto it = t.find(name);
+	if (it == t.end()) throw std::runtime_error(std::string("unknown option '") + name + "'");
+	need(n_values == it->second.n, "wrong number of values for option");
+	for (int i = 0; i < n_values; ++i) values[i] = it->second.is_int ? (float)((int*)it->second.p)[i] : ((float*)it->second.p)[i];
+	HN_CATCH(ctx)
+}
+int hn_set_camera(hn_context* ctx, const float cam[12]) { if (!ctx) return 1; std::memcpy(ctx->camera, cam, 48); return 0; }
+int hn_set_tile_shard(hn_context* ctx, int rank, int world, int tile_w, int tile_h) {
+	HN_TRY(ctx)
+	need(world >= 1 && rank >= 0 && rank < world && tile_w > 0 && tile_h > 0, "bad tile shard");
+	ctx->rank = rank; ctx->world = world; ctx->tile_w = tile_w; ctx->tile_h = tile_h;
+	HN_CATCH(ctx)
+}
+int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out) { if (!ctx || !out) return 1; *out = ctx->stats; return 0; }
+
+} // extern "C"
+
+// ---------------------------------------------------------------- frame
+namespace {
+
+// Sobol dimension 1 (v_j = v_{j-1} ^ (v_{j-1} >> 1)) for ld_random_pixel_offset (random_val.cuh:360-366); per-frame, host side.
+uint32_t sobol_dim1(uint32_t index) {
+	uint32_t X = 0, v = 0x80000000u;
+	for (uint32_t bit = 0; bit < 32; ++bit) {
+		if ((index >> bit) & 1u) X ^= v;
+		v ^= v >> 1;
+	}
+	return X;
+}
+void ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) {
+	index = hn_owen(index, seed);
+	out[0] = (float)hn_owen(hn_reverse_bits(index), hn_hash_combine(seed, 0u)) * 2.3283064365386963e-10f;
+	out[1] = (float)hn_owen(sobol_dim1(index), hn_hash_combine(seed, 1u)) * 2.3283064365386963e-10f;
+}
+void ld_random_pixel_offset(uint32_t spp, float out[2]) {
+	float a[2], b[2];
+	ld_random_val_2d(0, 0xdeadbeefu, a);
+	ld_random_val_2d(spp, 0xdeadbeefu, b);
+	for (int i = 0; i < 2; ++i) { float o = 0.5f - a[i] + b[i]; out[i] = o - std::floor(o); }
+}
+
+FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2], const float rel_focal[2],
+	const float rolling_shutter[4], uint32_t spp, int w, int h) {
+	const Options& o = ctx->opt;
+	FrameArgs a;
+	std::memset(&a, 0, sizeof(a));
+	a.w = w; a.h = h; a.spp = spp;
+	std::memcpy(a.cam0, cam0, 48); std::memcpy(a.cam1, cam1, 48);
+	std::memcpy(a.rolling_shutter, rolling_shutter, 16);
+	const int res_axis = ((int)o.fov_axis == 0) ? w : h;
+	for (int i = 0; i < 2; ++i) {
+		a.focal[i] = rel_focal[i] * (float)res_axis * o.zoom;             // calc_focal_length, src/testbed.cu:4474-4476
+		a.screen_center[i] = (0.5f - screen_center[i]) * o.zoom + 0.5f;    // render_screen_center, :4478-4481
+	}
+	ld_random_pixel_offset(o.snap_to_pixel_centers ? 0 : spp, a.pixel_offset);
+	a.near_distance = o.near_distance;
+	std::memcpy(a.render_aabb, o.render_aabb, 24); std::memcpy(a.train_aabb, o.train_aabb, 24);
+	a.max_mip = (uint32_t)o.max_cascade; a.cone_angle = o.cone_angle_constant; a.min_transmittance = o.min_transmittance;
+	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
+	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;
+	a.rank = ctx->rank; a.world = ctx->world; a.tile_w = ctx->tile_w; a.tile_h = ctx->tile_h;
+	std::memcpy(a.mesh_aabb, o.mesh_aabb, 24);
+	std::memcpy(a.sun, o.sun_dir, 12); std::memcpy(a.up, o.up_dir, 12);
+	a.floor_y = o.floor_enable ? o.mesh_aabb[1] + 0.001f : -10000.f; // get_floor_y, testbed.h:1019
+	std::memcpy(a.brdf, o.brdf, sizeof(a.brdf));
+	a.compat_nearest_aabb_only = o.compat_nearest_aabb_only;
+	return a;
+}
+
+RaySoA ray_soa(hn_context* ctx) {
+	RaySoA r;
+	r.o_t = ctx->ray_o_t.p; r.d_mw = ctx->ray_d_mw.p; r.rgba = ctx->ray_rgba.p; r.depth = ctx->ray_depth.p;
+	r.pixel = ctx->ray_pixel.p; r.n_steps = ctx->ray_nsteps.p;
+	return r;
+}
+
+void ensure_rays(hn_context* ctx, size_t n) {
+	ctx->ray_o_t.ensure(n); ctx->ray_d_mw.ensure(n); ctx->ray_rgba.ensure(n); ctx->ray_depth.ensure(n);
+	ctx->ray_pixel.ensure(n); ctx->ray_nsteps.ensure(n); ctx->alive_a.ensure(n); ctx->alive_b.ensure(n); ctx->sample_counts.ensure(n);
+}
+
+template <typename T> T* scratch(hn_context* ctx, int slot, size_t count) { ctx->scratch[slot].ensure(count * sizeof(T) + 16); return (T*)ctx->scratch[slot].p; }
+
+struct Timer {
+	cudaEvent_t a = nullptr, b = nullptr; bool on; cudaStream_t s;
+	Timer(bool enabled, cudaStream_t st) : on(enabled), s(st) { if (on) { cudaEventCreate(&a); cudaEventCreate(&b); } }
+	~Timer() { if (on) { cudaEventDestroy(a); cudaEventDestroy(b); } }
+	void start() { if (on) cudaEventRecord(a, s); }
+	void stop(float& acc) { if (on) { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); acc += ms; } }
+};
+
+void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame, float* depth, cudaStream_t s) {
+	FrameArgs a = args_in;
+	const size_t n_px = (size_t)a.w * a.h;
+	hn_frame_stats& st = ctx->stats;
+	st = hn_frame_stats{};
+	Timer tm(ctx->opt.profile != 0, s), total(ctx->opt.profile != 0, s);
+	total.start();
+	// CudaRenderBufferView::clear (render_buffer.cu:603-607)
+	HN_CUDA(cudaMemsetAsync(frame, 0, n_px * sizeof(float4), s));
+	HN_CUDA(cudaMemsetAsync(depth, 0, n_px * sizeof(float), s));
+	const bool do_mesh = ctx->opt.render_mesh && !ctx->meshes.empty();
+	if (do_mesh) {
+		need(ctx->scene_built, "scene has meshes but hn_build_scene was not called");
+		tm.start();
+		launch_mesh_pass(a, ctx->scene_dev(), frame, depth, s);
+		st.n_kernel_launches += 1;
+		tm.stop(st.ms_mesh);
+		a.depth_test = 1;
+	}
+	if (ctx->opt.render_nerf && ctx->has_net) {
+		need(ctx->has_params, "network parameters not set");
+		need(ctx->has_bitfield, "occupancy grid not set");
+		ensure_rays(ctx, n_px);
+		uint32_t* cnt = ctx->counters.p;
+		HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
+		RaySoA rays = ray_soa(ctx);
+		tm.start();
+		launch_raygen(a, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth, s);
+		st.n_kernel_launches += 1;
+		tm.stop(st.ms_raygen);
+		uint32_t* lists[2] = {ctx->alive_a.p, ctx->alive_b.p};
+		int cur = 0;
+		while (true) {
+			// the one host read-back per pass (the reference does the same, src/testbed_nerf.cu:2071-2072)
+			HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+			HN_CUDA(cudaStreamSynchronize(s));
+			const uint32_t n_alive = ctx->pinned_counters[cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B];
+			if (st.n_passes == 0) st.n_rays_alive = n_alive;
+			if (n_alive == 0) break;
+			need(n_alive <= n_px, "alive counter corrupt");
+			ctx->samples.ensure((size_t)n_alive * CHUNK);
+			ctx->net_out.ensure((size_t)n_alive * CHUNK);
+			uint32_t* n_alive_ptr = cnt + (cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B);
+			uint32_t* n_next_ptr = cnt + (cur == 0 ? CNT_ALIVE_B : CNT_ALIVE_A);
+			HN_CUDA(cudaMemsetAsync(n_next_ptr, 0, sizeof(uint32_t), s));
+			tm.start();
+			launch_march(a, ctx->bitfield.p, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, cnt, depth, n_alive, s);
+			tm.stop(st.ms_march);
+			tm.start();
+			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p, s);
+			tm.stop(st.ms_eval);
+			tm.start();
+			launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
+			tm.stop(st.ms_composite);
+			st.n_kernel_launches += 3;
+			st.n_passes += 1;
+			cur ^= 1;
+		}
+		st.n_samples = (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);
+		st.n_samples_composited = (uint64_t)ctx->pinned_counters[CNT_COMPOSITED_LO] | ((uint64_t)ctx->pinned_counters[CNT_COMPOSITED_HI] << 32);
+	}
+	total.stop(st.ms_total);
+	HN_CUDA(cudaGetLastError());
+}
+
+} // namespace
+
+extern "C" {
+
+int hn_render_frame(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2],
+	const float relative_focal_length[2], const float rolling_shutter[4], uint32_t spp_index,
+	int width, int height, float* frame_dev, float* depth_dev, void* cuda_stream) {
+	HN_TRY(ctx)
+	need(width > 0 && height > 0 && frame_dev && depth_dev, "bad frame arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	FrameArgs a = make_args(ctx, cam0, cam1, screen_center, relative_focal_length, rolling_shutter, spp_index, width, height);
+	render_frame_impl(ctx, a, (float4*)frame_dev, depth_dev, (cudaStream_t)cuda_stream);
+	HN_CATCH(ctx)
+}
+
+int hn_render_to_host(hn_context* ctx, int width, int height, int spp, int linear, float* rgba_host, float* depth_host) {
+	HN_TRY(ctx)
+	need(width > 0 && height > 0 && spp > 0 && rgba_host, "bad render arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const size_t n = (size_t)width * height;
+	ctx->frame.ensure(n); ctx->accum.ensure(n); ctx->tonemapped.ensure(n); ctx->depth.ensure(n);
+	const float rs[4] = {0.f, 0.f, 0.f, 1.f}; // python_api.cu:177
+	uint32_t launches = 0;
+	hn_frame_stats acc = {};
+	for (int i = 0; i < spp; ++i) {
+		FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, (uint32_t)i, width, height);
+		render_frame_impl(ctx, a, ctx->frame.p, ctx->depth.p, ctx->stream);
+		launch_accumulate(ctx->frame.p, ctx->accum.p, (uint32_t)n, (uint32_t)i, ctx->stream);
+		launches += ctx->stats.n_kernel_launches + 1;
+		acc.n_samples += ctx->stats.n_samples; acc.n_samples_composited += ctx->stats.n_samples_composited; acc.n_passes += ctx->stats.n_passes;
+		acc.n_rays_alive = ctx->stats.n_rays_alive;
+		acc.ms_mesh += ctx->stats.ms_mesh; acc.ms_raygen += ctx->stats.ms_raygen; acc.ms_march += ctx->stats.ms_march; acc.ms_eval += ctx->stats.ms_eval;
+		acc.ms_composite += ctx->stats.ms_composite; acc.ms_total += ctx->stats.ms_total;
+	}
+	launch_tonemap(ctx->accum.p, ctx->tonemapped.p, (uint32_t)n, linear ? 0 : 1, ctx->opt.exposure, ctx->opt.background_color, ctx->stream);
+	launches += 1;
+	HN_CUDA(cudaMemcpyAsync(rgba_host, ctx->tonemapped.p, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+	if (depth_host) HN_CUDA(cudaMemcpyAsync(depth_host, ctx->depth.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->stats = acc;
+	ctx->stats.n_kernel_launches = launches;
+	HN_CATCH(ctx)
+}
+
+// ---------------------------------------------------------------- tiles
+int hn_tile_count(const hn_context* ctx, int width, int height, int rank, int world, uint32_t* n_tiles) {
+	if (!ctx || !n_tiles || world < 1) return 1;
+	uint32_t tiles = ((width + ctx->tile_w - 1) / ctx->tile_w) * ((height + ctx->tile_h - 1) / ctx->tile_h);
+	*n_tiles = (tiles + world - 1 - rank) / world;
+	return 0;
+}
+int hn_pack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev, float* packed_dev, void* cuda_stream) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	launch_pack_tiles(width, height, rank, world, ctx->tile_w, ctx->tile_h, (const float4*)frame_dev, depth_dev, packed_dev, false, (cudaStream_t)cuda_stream);
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+int hn_unpack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* packed_dev, float* frame_dev, float* depth_dev, void* cuda_stream) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	launch_pack_tiles(width, height, rank, world, ctx->tile_w, ctx->tile_h, (const float4*)frame_dev, depth_dev, (float*)packed_dev, true, (cudaStream_t)cuda_stream);
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+
+// ---------------------------------------------------------------- operator-level entry points
+
+int hn_op_init_rays(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2], const float relative_focal_length[2],
+	const float rolling_shutter[4], uint32_t spp_index, int width, int height, float* origins, float* dirs, float* t, uint8_t* alive) {
+	HN_TRY(ctx)
+	need(ctx->has_bitfield, "occupancy grid not set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	FrameArgs a = make_args(ctx, cam0, cam1, screen_center, relative_focal_length, rolling_shutter, spp_index, width, height);
+	a.world = 1;
+	const size_t n = (size_t)width * height;
+	float* d_o = scratch<float>(ctx, 0, n * 3); float* d_d = scratch<float>(ctx, 1, n * 3); float* d_t = scratch<float>(ctx, 2, n); uint8_t* d_a = scratch<uint8_t>(ctx, 3, n);
+	launch_raygen_debug(a, ctx->bitfield.p, d_o, d_d, d_t, d_a, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(origins, d_o, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(dirs, d_d, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(t, d_t, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(alive, d_a, n, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+int hn_op_march_all(hn_context* ctx, uint32_t n, const float* origins, const float* dirs, const float* t0, const uint8_t* alive,
+	uint32_t* counts, float* samples, uint32_t max_per_ray) {
+	HN_TRY(ctx)
+	need(ctx->has_bitfield, "occupancy grid not set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const float rs[4] = {0, 0, 0, 1};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	float* d_o = scratch<float>(ctx, 0, (size_t)n * 3); float* d_d = scratch<float>(ctx, 1, (size_t)n * 3); float* d_t = scratch<float>(ctx, 2, n);
+	uint8_t* d_a = scratch<uint8_t>(ctx, 3, n); uint32_t* d_c = scratch<uint32_t>(ctx, 4, n);
+	float* d_s = samples ? scratch<float>(ctx, 5, (size_t)n * max_per_ray * 4) : nullptr;
+	HN_CUDA(cudaMemcpyAsync(d_o, origins, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(d_d, dirs, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(d_t, t0, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(d_a, alive, n, cudaMemcpyHostToDevice, ctx->stream));
+	if (d_s) HN_CUDA(cudaMemsetAsync(d_s, 0, (size_t)n * max_per_ray * 16, ctx->stream));
+	launch_march_all(a, ctx->bitfield.p, n, d_o, d_d, d_t, d_a, d_c, d_s, max_per_ray, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(counts, d_c, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (d_s) HN_CUDA(cudaMemcpyAsync(samples, d_s, (size_t)n * max_per_ray * 16, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+int hn_op_encode(hn_context* ctx, const float* positions, uint32_t n, uint16_t* out) {
+	HN_TRY(ctx)
+	need(ctx->has_params, "network parameters not set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	float* d_p = scratch<float>(ctx, 0, (size_t)n * 3); __half* d_o = scratch<__half>(ctx, 1, (size_t)n * 32);
+	HN_CUDA(cudaMemcpyAsync(d_p, positions, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	launch_encode(ctx->levels, ctx->net.F, ctx->params.p + ctx->net.grid_offset, d_p, n, d_o, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 64, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, uint32_t n, uint16_t* out) {
+	HN_TRY(ctx)
+	need(ctx->has_params, "network parameters not set");
+	need(n % CHUNK == 0, "samples must come in ray chunks of 32");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const uint32_t chunks = n / CHUNK;
+	float4* d_p = scratch<float4>(ctx, 0, n); float* d_d = scratch<float>(ctx, 1, (size_t)chunks * 3); uint2* d_o = scratch<uint2>(ctx, 2, n);
+	HN_CUDA(cudaMemcpyAsync(d_p, positions, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(d_d, dirs, (size_t)chunks * 12, cudaMemcpyHostToDevice, ctx->stream));
+	const float rs[4] = {0, 0, 0, 1};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	RaySoA none = {};
+	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+
+int hn_op_trace(hn_context* ctx, uint32_t n, const float* origins, const float* dirs, int32_t* mesh_idx, int32_t* tri_idx, float* t) {
+	HN_TRY(ctx)
+	need(ctx->scene_built && !ctx->meshes.empty(), "scene not built");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	float* d_o = scratch<float>(ctx, 0, (size_t)n * 3); float* d_d = scratch<float>(ctx, 1, (size_t)n * 3);
+	int32_t* d_m = scratch<int32_t>(ctx, 2, n); int32_t* d_i = scratch<int32_t>(ctx, 3, n); float* d_t = scratch<float>(ctx, 4, n);
+	HN_CUDA(cudaMemcpyAsync(d_o, origins, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(d_d, dirs, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	launch_trace(ctx->scene_dev(), ctx->opt.compat_nearest_aabb_only, n, d_o, d_d, d_m, d_i, d_t, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(mesh_idx, d_m, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(tri_idx, d_i, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaMemcpyAsync(t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+
+} // extern "C"

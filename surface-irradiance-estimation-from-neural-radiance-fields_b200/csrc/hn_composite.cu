@@ -1,0 +1,235 @@
+// (d) Alpha compositing as a warp-segmented scan + warp-level compaction of live rays + final depth-merged blend.
+// A warp owns 32 consecutive live rays (lane k keeps ray k's state in registers, loaded/stored coalesced). For each of its
+// rays in turn the 32 lanes take the ray's 32 samples of this pass: transmittance is a warp product scan, the early-out
+// sample is found with a ballot, colour/alpha are warp reductions, depth is a warp arg-max. Survivors are appended to the
+// next pass's list with ONE atomic per warp; rays that finish are blended straight into the frame buffer with the
+// mesh depth test (composite_kernel_nerf src/testbed_nerf.cu:528-735, compact_kernel_nerf :1403-1426,
+// shade_kernel_nerf_geometry src/testbed_geometry_training.cu:1826-1871).
+#include "hn_internal.h"
+
+namespace hn {
+
+#define HN_MIN_STEP (1.73205080757f / 1024.0f)
+
+__device__ __forceinline__ float act_rgb(float v, int act) {
+	switch (act) {
+		case 1: return fmaxf(v, 0.0f);
+		case 2: return 1.0f / (1.0f + __expf(-v));
+		case 3: return __expf(fminf(fmaxf(v, -10.0f), 10.0f));
+		default: return v;
+	}
+}
+__device__ __forceinline__ float act_density(float v, int act) {
+	switch (act) {
+		case 1: return fmaxf(v, 0.0f);
+		case 2: return 1.0f / (1.0f + __expf(-v));
+		case 3: return __expf(v);
+		default: return v;
+	}
+}
+__device__ __forceinline__ float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
+__device__ __forceinline__ float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
+
+__global__ void __launch_bounds__(256) composite_kernel(FrameArgs a, RaySoA rays, const uint32_t* __restrict__ alive_in, const uint32_t* __restrict__ n_alive_ptr,
+	uint32_t* __restrict__ alive_out, uint32_t* __restrict__ n_alive_out, uint32_t* __restrict__ counters, const float4* __restrict__ samples,
+	const uint32_t* __restrict__ sample_counts, const uint2* __restrict__ net_out, float4* __restrict__ frame, float* __restrict__ depth_buffer) {
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t n_alive = *n_alive_ptr;
+	const uint32_t p0 = warp_global * 32u;
+	if (p0 >= n_alive) return;
+	const uint32_t p = p0 + lane;
+	const bool valid = p < n_alive;
+
+	uint32_t r = 0, count = 0, n_steps = 0;
+	float4 rgba = make_float4(0.f, 0.f, 0.f, 0.f);
+	float depth = 0.f, max_weight = 0.f;
+	if (valid) {
+		r = alive_in[p];
+		count = sample_counts[p];
+		rgba = rays.rgba[r];
+		depth = rays.depth[r];
+		max_weight = rays.d_mw[r].w;
+		n_steps = rays.n_steps[r];
+	}
+	bool terminated = false;
+	const float cfx = a.cam1[6], cfy = a.cam1[7], cfz = a.cam1[8];
+	const float cpx = a.cam1[9], cpy = a.cam1[10], cpz = a.cam1[11];
+	const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP); // unwarp_dt range, nerf_device.cuh:306-314
+	uint32_t composited_total = 0;
+
+	const uint32_t n_here = min(32u, n_alive - p0);
+	for (uint32_t rr = 0; rr < n_here; ++rr) {
+		const uint32_t cnt = __shfl_sync(0xffffffffu, count, rr);
+		if (cnt == 0) continue;
+		const float A_in = __shfl_sync(0xffffffffu, rgba.w, rr);
+		const float mw_in = __shfl_sync(0xffffffffu, max_weight, rr);
+		const bool has = lane < cnt;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, zview = 0.f;
+		if (has) {
+			const size_t si = (size_t)(p0 + rr) * CHUNK + lane;
+			const uint2 o = __ldg(net_out + si);
+			const float4 s = __ldg(samples + si);
+			const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
+			const float sigma = act_density(__high2float(bs), a.density_act);
+			// warp_dt then unwarp_dt, as the value travels through the network input in the reference
+			const float wdt = __fdiv_rn(__fsub_rn(s.w, HN_MIN_STEP), dt_range);
+			const float dt = __fadd_rn(__fmul_rn(wdt, dt_range), HN_MIN_STEP);
+			alpha = 1.f - __expf(-sigma * dt);
+			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
+			// unwarp_position(warp_position(pos)) (nerf_device.cuh:265-279), view depth along the camera forward axis
+			const float lx = a.train_aabb[0], ly = a.train_aabb[1], lz = a.train_aabb[2];
+			const float dx = a.train_aabb[3] - lx, dy = a.train_aabb[4] - ly, dz = a.train_aabb[5] - lz;
+			const float ux = __fadd_rn(lx, __fmul_rn(__fdiv_rn(__fsub_rn(s.x, lx), dx), dx));
+			const float uy = __fadd_rn(ly, __fmul_rn(__fdiv_rn(__fsub_rn(s.y, ly), dy), dy));
+			const float uz = __fadd_rn(lz, __fmul_rn(__fdiv_rn(__fsub_rn(s.z, lz), dz), dz));
+			zview = cfx * (ux - cpx) + cfy * (uy - cpy) + cfz * (uz - cpz);
+		}
+		// inclusive product scan of (1 - alpha): P_j = prod_{k<=j}
+		float P = 1.f - alpha;
+		#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			float up = __shfl_up_sync(0xffffffffu, P, d);
+			if (lane >= (uint32_t)d) P *= up;
+		}
+		float Pex = __shfl_up_sync(0xffffffffu, P, 1);
+		if (lane == 0) Pex = 1.f;
+		const float T_in = 1.f - A_in;
+		const float weight = alpha * (T_in * Pex);
+		const float A_after = 1.f - T_in * P;
+		// first sample whose accumulated alpha exceeds 1 - min_transmittance ends the ray (:716-719)
+		const uint32_t term_mask = __ballot_sync(0xffffffffu, has && (A_after > (1.0f - a.min_transmittance)));
+		const bool term = term_mask != 0;
+		const uint32_t last = term ? (uint32_t)(__ffs(term_mask) - 1) : cnt - 1;
+		const bool use = has && lane <= last;
+		float sw = use ? weight : 0.f, sr = use ? cr * weight : 0.f, sg = use ? cg * weight : 0.f, sb = use ? cb * weight : 0.f;
+		// arg-max of the weights (earliest sample wins ties, strict > against the carried max, :711-714)
+		float bw = use ? weight : -1.f;
+		uint32_t bj = lane;
+		#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			sw += __shfl_xor_sync(0xffffffffu, sw, d);
+			sr += __shfl_xor_sync(0xffffffffu, sr, d);
+			sg += __shfl_xor_sync(0xffffffffu, sg, d);
+			sb += __shfl_xor_sync(0xffffffffu, sb, d);
+			float ow = __shfl_xor_sync(0xffffffffu, bw, d);
+			uint32_t oj = __shfl_xor_sync(0xffffffffu, bj, d);
+			if (ow > bw || (ow == bw && oj < bj)) { bw = ow; bj = oj; }
+		}
+		const float zbest = __shfl_sync(0xffffffffu, zview, bj);
+		if (lane == rr) {
+			rgba.x += sr; rgba.y += sg; rgba.z += sb; rgba.w += sw;
+			if (bw > mw_in) { max_weight = bw; depth = zbest; }
+			n_steps += last + 1;
+			composited_total = last + 1;
+			if (term) {
+				const float inv = rgba.w;
+				rgba.x /= inv; rgba.y /= inv; rgba.z /= inv; rgba.w /= inv;
+				terminated = true;
+			}
+		}
+	}
+
+	// ---- state write-back, compaction of survivors (one atomic per warp), blend of finished rays
+	const bool alive_next = valid && !terminated && count == CHUNK;
+	if (valid) {
+		rays.rgba[r] = rgba;
+		rays.depth[r] = depth;
+		rays.d_mw[r].w = max_weight;
+		rays.n_steps[r] = n_steps;
+	}
+	const uint32_t amask = __ballot_sync(0xffffffffu, alive_next);
+	if (amask) {
+		uint32_t base = 0;
+		const int leader = __ffs(amask) - 1;
+		if ((int)lane == leader) base = atomicAdd(n_alive_out, __popc(amask));
+		base = __shfl_sync(0xffffffffu, base, leader);
+		if (alive_next) alive_out[base + __popc(amask & ((1u << lane) - 1u))] = r;
+	}
+	uint32_t ct = composited_total;
+	#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) ct += __shfl_xor_sync(0xffffffffu, ct, d);
+	if (lane == 0 && ct) atomicAdd((unsigned long long*)&counters[CNT_COMPOSITED_LO], (unsigned long long)ct);
+
+	if (valid && !alive_next && rgba.w > 0.001f) { // compact_kernel_nerf keeps finished rays with alpha > 0.001
+		const uint32_t pix = rays.pixel[r];
+		if (a.depth_test && !a.depth_clip && depth > depth_buffer[pix]) return; // NeRF behind the mesh: drop (per-pixel rule)
+		float4 tmp = rgba;
+		if (!a.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+		const float4 fb = frame[pix];
+		const float ia = 1.0f - tmp.w;
+		frame[pix] = make_float4(tmp.x + fb.x * ia, tmp.y + fb.y * ia, tmp.z + fb.z * ia, tmp.w + fb.w * ia);
+		if (tmp.w > 0.2f) depth_buffer[pix] = depth;
+	}
+}
+
+// render_buffer.cu:228-262 (Linear colour space): running mean over spp
+__global__ void accumulate_kernel(const float4* __restrict__ frame, float4* __restrict__ accum, uint32_t n, float sample_count) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 c = frame[i], t = sample_count > 0.f ? accum[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+	float inv = sample_count + 1.f;
+	t.x = (t.x * sample_count + c.x) / inv; t.y = (t.y * sample_count + c.y) / inv;
+	t.z = (t.z * sample_count + c.z) / inv; t.w = (t.w * sample_count + c.w) / inv;
+	accum[i] = t;
+}
+// render_buffer.cu:529-560: background blend, exposure, optional sRGB, clamp; linear device buffer instead of a surface
+__global__ void tonemap_kernel(const float4* __restrict__ accum, float4* __restrict__ out, uint32_t n, int to_srgb, float exposure_scale, float4 bg) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 c = accum[i];
+	float w = (1.f - c.w) * bg.w;
+	c.x += srgb_to_linear(bg.x) * w; c.y += srgb_to_linear(bg.y) * w; c.z += srgb_to_linear(bg.z) * w; c.w += w;
+	c.x *= exposure_scale; c.y *= exposure_scale; c.z *= exposure_scale;
+	if (to_srgb) { c.x = linear_to_srgb(c.x); c.y = linear_to_srgb(c.y); c.z = linear_to_srgb(c.z); }
+	c.x = fminf(fmaxf(c.x, 0.f), 1.f); c.y = fminf(fmaxf(c.y, 0.f), 1.f); c.z = fminf(fmaxf(c.z, 0.f), 1.f); c.w = fminf(fmaxf(c.w, 0.f), 1.f);
+	out[i] = c;
+}
+
+// tile (un)packing for the multi-GPU gather: packed = [owned tile][tile_h*tile_w] x (rgba, depth)
+__global__ void pack_tiles_kernel(int w, int h, int rank, int world, int tw, int th, float4* frame, float* depth, float* packed, int unpack) {
+	uint32_t tiles_x = (w + tw - 1) / tw, tiles_y = (h + th - 1) / th;
+	uint32_t n_tiles = tiles_x * tiles_y;
+	uint32_t per_tile = tw * th;
+	uint32_t local_tile = blockIdx.x;
+	uint32_t tile = local_tile * world + rank;
+	if (tile >= n_tiles) return;
+	uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+	for (uint32_t k = threadIdx.x; k < per_tile; k += blockDim.x) {
+		uint32_t x = tx * tw + k % tw, y = ty * th + k / tw;
+		if (x >= (uint32_t)w || y >= (uint32_t)h) continue;
+		float* dst = packed + ((size_t)local_tile * per_tile + k) * 5;
+		uint32_t pix = x + w * y;
+		if (unpack) {
+			frame[pix] = make_float4(dst[0], dst[1], dst[2], dst[3]);
+			depth[pix] = dst[4];
+		} else {
+			float4 c = frame[pix];
+			dst[0] = c.x; dst[1] = c.y; dst[2] = c.z; dst[3] = c.w; dst[4] = depth[pix];
+		}
+	}
+}
+
+void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in, const uint32_t* n_alive_ptr, uint32_t* alive_out,
+	uint32_t* counters, const float4* samples, const uint32_t* sample_counts, const uint2* net_out,
+	float4* frame, float* depth_buffer, uint32_t max_rays, cudaStream_t s) {
+	if (!max_rays) return;
+	// n_alive_ptr points at one of counters[CNT_ALIVE_A/B]; the other one receives the survivors
+	uint32_t* n_out = (n_alive_ptr == counters + CNT_ALIVE_A) ? counters + CNT_ALIVE_B : counters + CNT_ALIVE_A;
+	uint32_t warps = (max_rays + 31) / 32;
+	composite_kernel<<<(warps + 7) / 8, 256, 0, s>>>(a, rays, alive_in, n_alive_ptr, alive_out, n_out, counters, samples, sample_counts, net_out, frame, depth_buffer);
+}
+void launch_accumulate(const float4* frame, float4* accum, uint32_t n, uint32_t spp_index, cudaStream_t s) {
+	accumulate_kernel<<<(n + 255) / 256, 256, 0, s>>>(frame, accum, n, (float)spp_index);
+}
+void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* bg, cudaStream_t s) {
+	tonemap_kernel<<<(n + 255) / 256, 256, 0, s>>>(accum, out, n, to_srgb, exp2f(exposure), make_float4(bg[0], bg[1], bg[2], bg[3]));
+}
+void launch_pack_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float* packed, bool unpack, cudaStream_t s) {
+	uint32_t tiles = ((w + tw - 1) / tw) * ((h + th - 1) / th);
+	uint32_t mine = (tiles + world - 1 - rank) / world;
+	if (!mine) return;
+	pack_tiles_kernel<<<mine, 256, 0, s>>>(w, h, rank, world, tw, th, (float4*)frame, (float*)depth, packed, unpack ? 1 : 0);
+}
+
+} // namespace hn

@@ -1,0 +1,141 @@
+// Host-side state behind the C ABI (the render-relevant subset of ngp::Testbed, testbed.h:67-1345).
+#pragma once
+#include "hn_internal.h"
+#include "../../include/hybrid_nerf.h"
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include <array>
+
+namespace hn {
+
+struct CudaError : std::runtime_error { using std::runtime_error::runtime_error; };
+#define HN_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) throw hn::CudaError(std::string(#expr) + " failed: " + cudaGetErrorString(e__)); } while (0)
+
+template <typename T>
+struct DevBuf {
+	T* p = nullptr;
+	size_t n = 0;
+	void ensure(size_t count) {
+		if (count <= n) return;
+		release();
+		HN_CUDA(cudaMalloc((void**)&p, count * sizeof(T)));
+		n = count;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+	~DevBuf() { release(); }
+	DevBuf() = default;
+	DevBuf(const DevBuf&) = delete;
+	DevBuf& operator=(const DevBuf&) = delete;
+};
+
+struct Tri { float a[3], b[3], c[3]; };
+
+struct HostMesh {
+	std::vector<Tri> tris;      // original order, scene space
+	float center[3] = {0, 0, 0};
+	float bb[6];                // exact box
+	float mesh_scale = 1.f;
+	// built BVH
+	std::vector<Node4> nodes;   // local node indices, root = 0
+	std::vector<uint32_t> order; // leaf order -> original triangle index
+};
+
+struct Options {
+	// defaults follow testbed.h:852-1091 and nerf.h:150-186
+	int snap_to_pixel_centers = 0;
+	float near_distance = 0.0f;
+	float render_aabb[6] = {0, 0, 0, 1, 1, 1};
+	float train_aabb[6] = {0, 0, 0, 1, 1, 1};   // m_geometry.nerfBoundingBox / m_aabb
+	int max_cascade = 0;
+	float cone_angle_constant = 0.0f;           // 0 for aabb_scale <= 1 (src/testbed_nerf.cu:2736), else 1/256
+	float min_transmittance = 0.01f;
+	int rgb_activation = 2;                     // Logistic
+	int density_activation = 3;                 // Exponential
+	int linear_colors = 0;
+	int dda_iter_cap = 0;
+	float sun_dir[3] = {0.57735026919f, 0.57735026919f, 0.57735026919f};
+	float up_dir[3] = {0, 1, 0};
+	int floor_enable = 0;
+	float brdf[13] = {0.f, 0.f, 1.f, 0.5f, 0.f, 0.f, 0.f, 0.8f, 0.8f, 0.8f, 0.f, 0.f, 0.f};
+	int compat_nearest_aabb_only = 0;
+	int depth_merge_clip = 0;
+	int render_nerf = 1, render_mesh = 1;
+	float exposure = 0.f;
+	float background_color[4] = {0, 0, 0, 1};
+	float fov_axis = 1;
+	float relative_focal_length[2] = {1.05729f, 1.05729f};
+	float screen_center[2] = {0.5f, 0.5f};
+	float zoom = 1.f;
+	int profile = 0;
+	int mesh_aabb_user = 0;
+	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
+};
+
+} // namespace hn
+
+struct hn_context {
+	int device = 0;
+	std::string error;
+	cudaStream_t stream = nullptr; // own stream for the non-frame calls
+
+	// network
+	hn::NetCfg net;
+	bool has_net = false;
+	int aabb_scale = 1;
+	std::string config_text, config_dir; // config source kept so hn_set_aabb_scale can re-derive per_level_scale
+	hn::GridLevels levels;
+	hn::DevBuf<__half> params;
+	bool has_params = false;
+
+	// occupancy
+	hn::DevBuf<uint8_t> bitfield;
+	bool has_bitfield = false;
+
+	// scene
+	std::vector<hn::HostMesh> meshes;
+	bool scene_built = false;
+	float scene_bb[6] = {0, 0, 0, 1, 1, 1};
+	hn::DevBuf<hn::Node4> d_nodes;
+	hn::DevBuf<float4> d_tris;
+	hn::DevBuf<hn::MeshDev> d_meshes;
+
+	hn::Options opt;
+	float camera[12] = {1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5f, 0.5f, 2.0f}; // reset_camera default (src/testbed.cu:541-568)
+
+	// tile shard
+	int rank = 0, world = 1, tile_w = 64, tile_h = 32;
+
+	// per-frame workspace (persistent, grows to the largest frame seen; no per-frame allocation)
+	hn::DevBuf<float4> ray_o_t, ray_d_mw, ray_rgba;
+	hn::DevBuf<float> ray_depth;
+	hn::DevBuf<uint32_t> ray_pixel, ray_nsteps, alive_a, alive_b, sample_counts, counters;
+	hn::DevBuf<float4> samples;
+	hn::DevBuf<uint2> net_out;
+	uint32_t* pinned_counters = nullptr; // CNT_N uint32
+	// render_to_host buffers
+	hn::DevBuf<float4> frame, accum, tonemapped;
+	hn::DevBuf<float> depth;
+	// scratch for operator entry points
+	hn::DevBuf<uint8_t> scratch[8];
+
+	hn_frame_stats stats = {};
+
+	hn::SceneDev scene_dev() const {
+		hn::SceneDev s;
+		s.nodes = d_nodes.p; s.tris = d_tris.p; s.meshes = d_meshes.p; s.n_meshes = (uint32_t)meshes.size();
+		return s;
+	}
+};
+
+namespace hn {
+// hn_config.cpp
+void load_network_config_text(hn_context* ctx, const std::string& text, const std::string& base_dir);
+void finalize_network(hn_context* ctx);
+// hn_scene.cpp
+void add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], bool normalize);
+void load_mesh_file(hn_context* ctx, const std::string& path, const float center[3]);
+void load_scene_file(hn_context* ctx, const std::string& path);
+void build_scene(hn_context* ctx);
+std::string read_text_file(const std::string& path);
+} // namespace hn

@@ -1,0 +1,84 @@
+// Device math for the IEEE-exact translation units (compiled with -fmad=false, no fast math): every expression is written
+// in the operation order of the reference's host-callable functions so results match the CPU oracle bit for bit.
+#pragma once
+#include "hn_internal.h"
+#include <cfloat>
+
+namespace hn {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 mk(float x, float y, float z) { return {x, y, z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ V3 operator/(V3 a, V3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, float s) { return {a.x - s, a.y - s, a.z - s}; }
+__device__ __forceinline__ V3 operator+(V3 a, float s) { return {a.x + s, a.y + s, a.z + s}; }
+__device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
+// tcnn vec.h:425 dot: ((0 + a0*b0) + a1*b1) + a2*b2
+__device__ __forceinline__ float dot3(V3 a, V3 b) { float r = 0.0f; r += a.x * b.x; r += a.y * b.y; r += a.z * b.z; return r; }
+__device__ __forceinline__ float length3(V3 a) { return sqrtf(dot3(a, a)); }
+__device__ __forceinline__ V3 normalize3(V3 v) { float l = length3(v); if (l <= 0.0f) return {1.0f, 0.0f, 0.0f}; return v / l; }
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ float mixf(float a, float b, float c) { return a * (1.0f - c) + b * c; }
+__device__ __forceinline__ V3 mix3(V3 a, V3 b, float c) { return a * (1.0f - c) + b * c; }
+__device__ __forceinline__ V3 mix3(V3 a, V3 b, V3 c) { return {mixf(a.x, b.x, c.x), mixf(a.y, b.y, c.y), mixf(a.z, b.z, c.z)}; }
+__device__ __forceinline__ V3 ld3(const float* f) { return {f[0], f[1], f[2]}; }
+
+struct Box { V3 lo, hi; };
+__device__ __forceinline__ Box ldbox(const float* f) { return {{f[0], f[1], f[2]}, {f[3], f[4], f[5]}}; }
+// bounding_box.cuh:313
+__device__ __forceinline__ bool box_contains(const Box& b, V3 p) {
+	return p.x >= b.lo.x && p.x <= b.hi.x && p.y >= b.lo.y && p.y <= b.hi.y && p.z >= b.lo.z && p.z <= b.hi.z;
+}
+// bounding_box.cuh:172-219: returns (tmin, tmax), (FLT_MAX, FLT_MAX) on a miss
+__device__ __forceinline__ float2 box_ray_intersect(const Box& b, V3 pos, V3 dir) {
+	float tmin = (b.lo.x - pos.x) / dir.x;
+	float tmax = (b.hi.x - pos.x) / dir.x;
+	if (tmin > tmax) { float t = tmin; tmin = tmax; tmax = t; }
+	float tymin = (b.lo.y - pos.y) / dir.y;
+	float tymax = (b.hi.y - pos.y) / dir.y;
+	if (tymin > tymax) { float t = tymin; tymin = tymax; tymax = t; }
+	if (tmin > tymax || tymin > tmax) return {FLT_MAX, FLT_MAX};
+	if (tymin > tmin) tmin = tymin;
+	if (tymax < tmax) tmax = tymax;
+	float tzmin = (b.lo.z - pos.z) / dir.z;
+	float tzmax = (b.hi.z - pos.z) / dir.z;
+	if (tzmin > tzmax) { float t = tzmin; tzmin = tzmax; tzmax = t; }
+	if (tmin > tzmax || tzmin > tmax) return {FLT_MAX, FLT_MAX};
+	if (tzmin > tmin) tmin = tzmin;
+	if (tzmax < tmax) tmax = tzmax;
+	return {tmin, tmax};
+}
+
+// ---- Owen-scrambled Sobol, dimension 0 (random_val.cuh:207-345). sobol(index, 0) is the bit reversal of index. ----
+__host__ __device__ __forceinline__ uint32_t hn_reverse_bits(uint32_t x) {
+#ifdef __CUDA_ARCH__
+	return __brev(x);
+#else
+	x = ((x & 0xaaaaaaaau) >> 1) | ((x & 0x55555555u) << 1);
+	x = ((x & 0xccccccccu) >> 2) | ((x & 0x33333333u) << 2);
+	x = ((x & 0xf0f0f0f0u) >> 4) | ((x & 0x0f0f0f0fu) << 4);
+	x = ((x & 0xff00ff00u) >> 8) | ((x & 0x00ff00ffu) << 8);
+	return (x >> 16) | (x << 16);
+#endif
+}
+__host__ __device__ __forceinline__ uint32_t hn_laine_karras(uint32_t x, uint32_t seed) {
+	x += seed;
+	x ^= x * 0x6c50b47cu;
+	x ^= x * 0xb82f1e52u;
+	x ^= x * 0xc7afe638u;
+	x ^= x * 0x8d22f6e6u;
+	return x;
+}
+__host__ __device__ __forceinline__ uint32_t hn_owen(uint32_t x, uint32_t seed) { return hn_reverse_bits(hn_laine_karras(hn_reverse_bits(x), seed)); }
+__host__ __device__ __forceinline__ uint32_t hn_hash_combine(uint32_t seed, uint32_t v) { return seed ^ (v + (seed << 6) + (seed >> 2)); }
+__host__ __device__ __forceinline__ float hn_ld_random_val(uint32_t index, uint32_t seed) {
+	index = hn_owen(index, seed);
+	return (float)hn_owen(hn_reverse_bits(index), hn_hash_combine(seed, 0u)) * 2.3283064365386963e-10f; // 2^-32
+}
+
+} // namespace hn

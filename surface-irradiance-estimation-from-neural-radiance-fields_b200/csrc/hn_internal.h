@@ -1,0 +1,131 @@
+// Internal declarations shared by the host side (hn_*.cpp) and the CUDA translation units (hn_*.cu).
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+
+namespace hn {
+
+constexpr uint32_t GRIDSIZE = 128;                     // NERF_GRIDSIZE, nerf_device.cuh:23
+constexpr uint32_t GRID_CELLS = GRIDSIZE * GRIDSIZE * GRIDSIZE;
+constexpr uint32_t CASCADES = 8;                       // NERF_CASCADES, nerf_device.cuh:28
+constexpr uint32_t BITFIELD_BYTES = GRID_CELLS / 8 * CASCADES;
+constexpr float MAX_DEPTH_F = 16384.0f;                // MAX_DEPTH(), common_device.cuh:32
+constexpr float MAX_DIST_F = 100.0f;                   // MAX_DIST in triangle_bvh.cu / geometry_bvh.cu
+constexpr uint32_t CHUNK = 32;                         // samples per ray per pass (one warp = one ray chunk)
+constexpr uint32_t MAX_LEVELS = 16;
+
+// ---- network ----
+struct NetCfg {
+	uint32_t L = 0, F = 0, log2_T = 0, base_res = 0;
+	float per_level_scale = 0.f;
+	uint32_t density_hidden = 1, rgb_hidden = 2;
+	uint32_t offsets[MAX_LEVELS + 1] = {};
+	float scales[MAX_LEVELS] = {};
+	uint32_t res[MAX_LEVELS] = {};
+	size_t n_params = 0, grid_offset = 0, density_w_offset = 0, rgb_w_offset = 0;
+};
+
+// Level table handed to the gather kernel by value.
+struct GridLevels {
+	uint32_t offset[MAX_LEVELS];   // entry offset of the level
+	uint32_t size[MAX_LEVELS];     // hashmap_size of the level
+	uint32_t res[MAX_LEVELS];
+	float scale[MAX_LEVELS];
+	uint32_t hashed[MAX_LEVELS];   // 1 = coherent prime hash, 0 = dense index
+	uint32_t L;
+};
+
+// ---- per-frame arguments (by value to kernels) ----
+struct FrameArgs {
+	int w, h;
+	uint32_t spp;
+	float cam0[12], cam1[12];
+	float rolling_shutter[4];
+	float screen_center[2];
+	float focal[2];
+	float pixel_offset[2]; // ld_random_pixel_offset(snap ? 0 : spp), computed on the host
+	float near_distance;
+	float render_aabb[6], train_aabb[6];
+	uint32_t max_mip;
+	float cone_angle;
+	float min_transmittance;
+	int rgb_act, density_act, linear_colors, dda_iter_cap;
+	int depth_test, depth_clip;
+	int rank, world, tile_w, tile_h;
+	// mesh pass
+	float mesh_aabb[6];
+	float sun[3], up[3];
+	float floor_y;
+	float brdf[13]; // metallic subsurface specular roughness sheen clearcoat clearcoat_gloss basecolor[3] ambientcolor[3]
+	int compat_nearest_aabb_only;
+};
+
+// ---- ray state, SoA, indexed by ray id (assigned at ray generation) ----
+struct RaySoA {
+	float4* o_t;     // origin.xyz, t
+	float4* d_mw;    // dir.xyz, max_weight
+	float4* rgba;
+	float* depth;
+	uint32_t* pixel;
+	uint32_t* n_steps;
+};
+
+// ---- BVH (4-wide, 128 B nodes) ----
+struct alignas(16) Node4 {
+	float lo_x[4], lo_y[4], lo_z[4], hi_x[4], hi_y[4], hi_z[4];
+	int32_t child[4];  // inner: node index (>0); leaf: ~first_triangle; unused slot: count == 0 and child == 0
+	int32_t count[4];  // leaf: number of triangles (> 0); inner: -1; unused: 0
+};
+static_assert(sizeof(Node4) == 128, "Node4 must be one 128-byte line");
+
+struct MeshDev {
+	uint32_t node_root;   // index of the mesh's root node in the shared node array
+	uint32_t tri_first;   // first triangle of the mesh in the shared (leaf-ordered) triangle array
+	float bb[6];          // exact box of the mesh (geometry_bvh.cu:18-35)
+};
+
+struct SceneDev {
+	const Node4* nodes;
+	const float4* tris;   // 3 float4 per triangle: (a, orig_idx bits), (b, 0), (c, 0), leaf order
+	const MeshDev* meshes;
+	uint32_t n_meshes;
+};
+
+// ---- launchers (defined in the .cu files) ----
+// exact TU (compiled with -fmad=false, no fast math): bit-exact against the oracle
+void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thresh, uint8_t* bits, cudaStream_t s);
+void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s);
+void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters,
+	float* depth_buffer, cudaStream_t s);
+void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s);
+void launch_march(const FrameArgs& a, const uint8_t* bits, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr,
+	float4* samples, uint32_t* sample_counts, uint32_t* counters, const float* depth_buffer, uint32_t max_rays, cudaStream_t s);
+void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const float* o, const float* d, const float* t0, const uint8_t* alive,
+	uint32_t* counts, float* samples, uint32_t max_per_ray, cudaStream_t s);
+
+// network TU
+void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
+void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
+	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
+	uint32_t max_chunks, uint2* out, cudaStream_t s);
+
+// composite TU
+void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in, const uint32_t* n_alive_ptr, uint32_t* alive_out,
+	uint32_t* counters, const float4* samples, const uint32_t* sample_counts, const uint2* net_out,
+	float4* frame, float* depth_buffer, uint32_t max_rays, cudaStream_t s);
+void launch_accumulate(const float4* frame, float4* accum, uint32_t n, uint32_t spp_index, cudaStream_t s);
+void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* background, cudaStream_t s);
+void launch_pack_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float* packed, bool unpack, cudaStream_t s);
+
+// mesh TU (exact flags as well)
+void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, cudaStream_t s);
+void launch_trace(SceneDev scene, int compat, uint32_t n, const float* o, const float* d, int32_t* mesh, int32_t* tri, float* t, cudaStream_t s);
+
+// counters layout (uint32 array on the device)
+enum Counter : uint32_t { CNT_ALIVE_A = 0, CNT_ALIVE_B = 1, CNT_SAMPLES_LO = 2, CNT_SAMPLES_HI = 3, CNT_COMPOSITED_LO = 4, CNT_COMPOSITED_HI = 5, CNT_RAYS = 6, CNT_ERR = 7, CNT_N = 8 };
+
+} // namespace hn

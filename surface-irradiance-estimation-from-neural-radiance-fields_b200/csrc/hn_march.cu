@@ -1,0 +1,405 @@
+// (a) Ray generation + occupancy-grid DDA marching for sm_100a.
+// IEEE-exact translation unit: built with -fmad=false and without fast math so that ray origins/directions, start t,
+// per-ray sample counts and sample positions are bit-identical to the CPU oracle.
+// Layout: SoA ray state (float4 loads/stores), warp-aggregated compaction of live rays (one atomic per warp).
+#include "hn_device_math.cuh"
+
+namespace hn {
+
+// ---------------------------------------------------------------- camera (tcnn vec.h:1060-1187, common_device.cuh:651-659)
+struct Quat { float w, x, y, z; };
+struct M3 { V3 c[3]; };
+struct Cam { V3 c[4]; };
+
+__device__ __forceinline__ Cam ldcam(const float* f) {
+	Cam m;
+	#pragma unroll
+	for (int i = 0; i < 4; ++i) m.c[i] = {f[3 * i], f[3 * i + 1], f[3 * i + 2]};
+	return m;
+}
+__device__ __forceinline__ V3 mul3(const M3& m, V3 v) {
+	V3 r = {0.0f, 0.0f, 0.0f};
+	r.x += m.c[0].x * v.x; r.y += m.c[0].y * v.x; r.z += m.c[0].z * v.x;
+	r.x += m.c[1].x * v.y; r.y += m.c[1].y * v.y; r.z += m.c[1].z * v.y;
+	r.x += m.c[2].x * v.z; r.y += m.c[2].y * v.z; r.z += m.c[2].z * v.z;
+	return r;
+}
+__device__ Quat quat_from(const M3& m) {
+	Quat q;
+	float tr = m.c[0].x + m.c[1].y + m.c[2].z;
+	if (tr > 0.0f) {
+		float S = sqrtf(tr + 1.0f) * 2.0f;
+		q.w = 0.25f * S;
+		q.x = (m.c[1].z - m.c[2].y) / S;
+		q.y = (m.c[2].x - m.c[0].z) / S;
+		q.z = (m.c[0].y - m.c[1].x) / S;
+	} else if (m.c[0].x > m.c[1].y && m.c[0].x > m.c[2].z) {
+		float S = sqrtf(1.0f + m.c[0].x - m.c[1].y - m.c[2].z) * 2.0f;
+		q.w = (m.c[1].z - m.c[2].y) / S;
+		q.x = 0.25f * S;
+		q.y = (m.c[1].x + m.c[0].y) / S;
+		q.z = (m.c[2].x + m.c[0].z) / S;
+	} else if (m.c[1].y > m.c[2].z) {
+		float S = sqrtf(1.0f + m.c[1].y - m.c[0].x - m.c[2].z) * 2.0f;
+		q.w = (m.c[2].x - m.c[0].z) / S;
+		q.x = (m.c[1].x + m.c[0].y) / S;
+		q.y = 0.25f * S;
+		q.z = (m.c[2].y + m.c[1].z) / S;
+	} else {
+		float S = sqrtf(1.0f + m.c[2].z - m.c[0].x - m.c[1].y) * 2.0f;
+		q.w = (m.c[0].y - m.c[1].x) / S;
+		q.x = (m.c[2].x + m.c[0].z) / S;
+		q.y = (m.c[2].y + m.c[1].z) / S;
+		q.z = 0.25f * S;
+	}
+	return q;
+}
+__device__ __forceinline__ float qdot(Quat a, Quat b) { return (a.w * b.w + a.x * b.x) + (a.y * b.y + a.z * b.z); }
+__device__ __forceinline__ Quat qnormalize(Quat a) {
+	float len = sqrtf(qdot(a, a));
+	if (len <= 0.0f) return {1.0f, 0.0f, 0.0f, 0.0f};
+	return {a.w / len, a.x / len, a.y / len, a.z / len};
+}
+__device__ __forceinline__ Quat qscale(Quat a, float s) { return {a.w * s, a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ Quat qadd(Quat a, Quat b) { return {a.w + b.w, a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ Quat qslerp(Quat x, Quat y, float t) {
+	Quat z = y;
+	float cos_theta = qdot(x, y);
+	if (cos_theta < 0.0f) { z = {-y.w, -y.x, -y.y, -y.z}; cos_theta = -cos_theta; }
+	if (cos_theta > 1.0f - FLT_EPSILON) return qadd(qscale(x, 1.0f - t), qscale(z, t));
+	// cam0 != cam1: acosf/sinf are not bit-identical between libm and CUDA -> tolerance parity only in this branch
+	float angle = acosf(cos_theta);
+	Quat r = qadd(qscale(x, sinf((1.0f - t) * angle)), qscale(z, sinf(t * angle)));
+	float s = sinf(angle);
+	return {r.w / s, r.x / s, r.y / s, r.z / s};
+}
+__device__ __forceinline__ M3 quat_to_mat3(Quat q) {
+	float qxx = q.x * q.x, qyy = q.y * q.y, qzz = q.z * q.z;
+	float qxz = q.x * q.z, qxy = q.x * q.y, qyz = q.y * q.z;
+	float qwx = q.w * q.x, qwy = q.w * q.y, qwz = q.w * q.z;
+	M3 m;
+	m.c[0] = {1.0f - 2.0f * (qyy + qzz), 2.0f * (qxy + qwz), 2.0f * (qxz - qwy)};
+	m.c[1] = {2.0f * (qxy - qwz), 1.0f - 2.0f * (qxx + qzz), 2.0f * (qyz + qwx)};
+	m.c[2] = {2.0f * (qxz + qwy), 2.0f * (qyz - qwx), 1.0f - 2.0f * (qxx + qyy)};
+	return m;
+}
+
+// init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1428-1476) + uv_to_ray pinhole (common_device.cuh:416-483)
+__device__ void pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& dir) {
+	uint32_t idx = x + (uint32_t)a.w * y;
+	float u = ((float)x + a.pixel_offset[0]) / (float)a.w;
+	float v = ((float)y + a.pixel_offset[1]) / (float)a.h;
+	float mb = hn_ld_random_val(a.spp, idx * 72239731u);
+	float pixel_t = a.rolling_shutter[0] + a.rolling_shutter[1] * u + a.rolling_shutter[2] * v + a.rolling_shutter[3] * mb;
+	Cam c0 = ldcam(a.cam0), c1 = ldcam(a.cam1);
+	M3 m0 = {{c0.c[0], c0.c[1], c0.c[2]}}, m1 = {{c1.c[0], c1.c[1], c1.c[2]}};
+	M3 rot = quat_to_mat3(qnormalize(qslerp(qnormalize(quat_from(m0)), qnormalize(quat_from(m1)), pixel_t)));
+	V3 pos = mix3(c0.c[3], c1.c[3], pixel_t);
+	V3 d = {(u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f};
+	V3 head = {0.0f, 0.0f, 0.0f};
+	d = d - head * 0.0f;
+	d = mul3(rot, d);
+	V3 o = mul3(rot, head) + pos;
+	o = o + d * a.near_distance;
+	origin = o;
+	dir = normalize3(d);
+}
+
+// ---------------------------------------------------------------- occupancy DDA (nerf_device.cuh:316-534)
+__device__ __forceinline__ uint32_t expand_bits(uint32_t v) {
+	v = (v * 0x00010001u) & 0xFF0000FFu;
+	v = (v * 0x00000101u) & 0x0F00F00Fu;
+	v = (v * 0x00000011u) & 0xC30C30C3u;
+	v = (v * 0x00000005u) & 0x49249249u;
+	return v;
+}
+__device__ __forceinline__ uint32_t morton3D(uint32_t x, uint32_t y, uint32_t z) { return expand_bits(x) | (expand_bits(y) << 1) | (expand_bits(z) << 2); }
+__device__ __forceinline__ uint32_t morton3D_invert(uint32_t x) {
+	x = x & 0x49249249u;
+	x = (x | (x >> 2)) & 0xc30c30c3u;
+	x = (x | (x >> 4)) & 0x0f00f00fu;
+	x = (x | (x >> 8)) & 0xff0000ffu;
+	x = (x | (x >> 16)) & 0x0000ffffu;
+	return x;
+}
+__device__ __forceinline__ bool occupied_at(V3 pos, const uint8_t* __restrict__ bits, uint32_t mip) {
+	float mip_scale = scalbnf(1.0f, -(int)mip);
+	pos = pos - 0.5f;
+	pos = pos * mip_scale;
+	pos = pos + 0.5f;
+	int ix = (int)(pos.x * (float)GRIDSIZE), iy = (int)(pos.y * (float)GRIDSIZE), iz = (int)(pos.z * (float)GRIDSIZE);
+	if (ix < 0 || ix >= (int)GRIDSIZE || iy < 0 || iy >= (int)GRIDSIZE || iz < 0 || iz >= (int)GRIDSIZE) return false;
+	uint32_t idx = morton3D(ix, iy, iz);
+	return __ldg(bits + idx / 8 + (GRID_CELLS * mip) / 8) & (1 << (idx % 8));
+}
+#define HN_STEPSIZE (1.73205080757f / 1024.0f)
+#define HN_MAX_CONE_STEPSIZE (HN_STEPSIZE * 128 * 1024u / 128u)
+__device__ __forceinline__ float to_stepping_space(float t, float cone) {
+	if (cone <= 1e-5f) return t / HN_STEPSIZE;
+	float log1p_c = logf(1.0f + cone);
+	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+	if (t <= at) return (t - at) / HN_STEPSIZE + a;
+	if (t <= bt) return logf(t) / log1p_c;
+	return (t - bt) / HN_MAX_CONE_STEPSIZE + b;
+}
+__device__ __forceinline__ float from_stepping_space(float n, float cone) {
+	if (cone <= 1e-5f) return n * HN_STEPSIZE;
+	float log1p_c = logf(1.0f + cone);
+	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+	if (n <= a) return (n - a) * HN_STEPSIZE + at;
+	if (n <= b) return expf(n * log1p_c);
+	return (n - b) * HN_MAX_CONE_STEPSIZE + bt;
+}
+__device__ __forceinline__ float advance_n_steps(float t, float cone, float n) { return from_stepping_space(to_stepping_space(t, cone) + n, cone); }
+__device__ __forceinline__ float calc_dt(float t, float cone) { return advance_n_steps(t, cone, 1.0f) - t; }
+__device__ __forceinline__ float min_ba(float a, float b) { return b < a ? b : a; } // std::min
+__device__ __forceinline__ float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
+	V3 p = res * (pos - 0.5f);
+	float tx = (floorf(p.x + 0.5f + 0.5f * copysignf(1.0f, dir.x)) - p.x) * idir.x;
+	float ty = (floorf(p.y + 0.5f + 0.5f * copysignf(1.0f, dir.y)) - p.y) * idir.y;
+	float tz = (floorf(p.z + 0.5f + 0.5f * copysignf(1.0f, dir.z)) - p.z) * idir.z;
+	float t = min_ba(min_ba(tx, ty), tz);
+	return fmaxf(t / res, 0.0f);
+}
+__device__ __forceinline__ float advance_to_next_voxel(float t, float cone, V3 pos, V3 dir, V3 idir, uint32_t mip) {
+	float res = scalbnf((float)GRIDSIZE, -(int)mip);
+	float t_target = t + distance_to_next_voxel(pos, dir, idir, res);
+	t = to_stepping_space(t, cone);
+	t_target = to_stepping_space(t_target, cone);
+	return from_stepping_space(t + ceilf(fmaxf(t_target - t, 0.5f)), cone);
+}
+__device__ __forceinline__ uint32_t mip_from_pos(V3 pos) {
+	int exponent;
+	float maxval = fmaxf(fmaxf(fabsf(pos.x - 0.5f), fabsf(pos.y - 0.5f)), fabsf(pos.z - 0.5f));
+	frexpf(maxval, &exponent);
+	return (uint32_t)min(max(exponent + 1, 0), (int)CASCADES - 1);
+}
+// nerf_device.cuh:461-495 (iter_cap == 0) / :497-534 (iter_cap == 200)
+__device__ float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bits, uint32_t min_mip, uint32_t max_mip,
+	const Box& aabb, int iter_cap) {
+	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
+		V3 pos = o + t * d;
+		if (t >= MAX_DEPTH_F || !box_contains(aabb, pos)) return MAX_DEPTH_F;
+		uint32_t mip = min(max(mip_from_pos(pos), min_mip), max_mip);
+		if (!bits || occupied_at(pos, bits, mip)) return t;
+		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
+		t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
+	}
+	return MAX_DEPTH_F;
+}
+
+// per-pixel start state: init_rays (:1478-1543) + advance_pos_nerf (:333-362). Returns alive.
+__device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out) {
+	pixel_ray(a, x, y, o, d);
+	uint32_t idx = x + (uint32_t)a.w * y;
+	Box aabb = ldbox(a.render_aabb);
+	float t = fmaxf(box_ray_intersect(aabb, o, d).x, 0.0f) + 1e-6f;
+	t_out = MAX_DEPTH_F;
+	if (!box_contains(aabb, o + t * d)) return false;
+	V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+	t = advance_n_steps(t, a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
+	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0);
+	if (t >= MAX_DEPTH_F) return false;
+	t_out = t;
+	return true;
+}
+
+__device__ __forceinline__ bool tile_owned(const FrameArgs& a, uint32_t x, uint32_t y) {
+	if (a.world <= 1) return true;
+	uint32_t tiles_x = (a.w + a.tile_w - 1) / a.tile_w;
+	uint32_t tile = (y / a.tile_h) * tiles_x + (x / a.tile_w);
+	return (int)(tile % (uint32_t)a.world) == a.rank;
+}
+
+// ---------------------------------------------------------------- kernels
+// One thread per pixel. Live rays are appended to the SoA ray buffers through a warp-aggregated atomic (one atomicAdd
+// per warp); the ray id is the slot. Order is non-deterministic, results are keyed by pixel so the image is not.
+__global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, uint32_t* __restrict__ alive_list,
+	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer) {
+	uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	bool alive = false;
+	V3 o, d; float t = 0.0f;
+	if (idx < n) {
+		uint32_t x = idx % (uint32_t)a.w, y = idx / (uint32_t)a.w;
+		if (tile_owned(a, x, y)) {
+			// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
+			if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
+			alive = start_ray(a, bits, x, y, o, d, t);
+		}
+	}
+	uint32_t mask = __ballot_sync(0xffffffffu, alive);
+	if (mask == 0) return;
+	uint32_t lane = threadIdx.x & 31u;
+	uint32_t base = 0;
+	if (lane == (uint32_t)(__ffs(mask) - 1)) base = atomicAdd(&counters[CNT_ALIVE_A], __popc(mask));
+	base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+	if (alive) {
+		uint32_t r = base + __popc(mask & ((1u << lane) - 1u));
+		rays.o_t[r] = make_float4(o.x, o.y, o.z, t);
+		rays.d_mw[r] = make_float4(d.x, d.y, d.z, 0.0f);
+		rays.rgba[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+		rays.depth[r] = 0.0f;
+		rays.pixel[r] = idx;
+		rays.n_steps[r] = 0;
+		alive_list[r] = r;
+	}
+}
+
+__global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const uint8_t* __restrict__ bits, float* __restrict__ o_out, float* __restrict__ d_out,
+	float* __restrict__ t_out, uint8_t* __restrict__ alive_out) {
+	uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= (uint32_t)a.w * (uint32_t)a.h) return;
+	V3 o, d; float t;
+	bool alive = start_ray(a, bits, idx % (uint32_t)a.w, idx / (uint32_t)a.w, o, d, t);
+	o_out[3 * idx] = o.x; o_out[3 * idx + 1] = o.y; o_out[3 * idx + 2] = o.z;
+	d_out[3 * idx] = d.x; d_out[3 * idx + 1] = d.y; d_out[3 * idx + 2] = d.z;
+	t_out[idx] = t;
+	alive_out[idx] = alive ? 1 : 0;
+}
+
+// generate_next_nerf_network_inputs (src/testbed_nerf.cu:430-477): up to CHUNK samples per live ray per pass.
+// Sample slot of list position p, step j = p*CHUNK + j (ray-major, so a warp of the network kernel owns one ray chunk).
+__global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, const uint32_t* __restrict__ alive_list,
+	const uint32_t* __restrict__ n_alive_ptr, float4* __restrict__ samples, uint32_t* __restrict__ sample_counts, uint32_t* __restrict__ counters,
+	const float* __restrict__ depth_buffer) {
+	uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t n_alive = *n_alive_ptr;
+	uint32_t count = 0;
+	if (p < n_alive) {
+		uint32_t r = alive_list[p];
+		float4 ot = rays.o_t[r];
+		float4 dm = rays.d_mw[r];
+		V3 o = {ot.x, ot.y, ot.z}, d = {dm.x, dm.y, dm.z};
+		V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+		Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
+		V3 tdiag = train.hi - train.lo;
+		V3 cam_fwd = ld3(a.cam1 + 6), cam_pos = ld3(a.cam1 + 9);
+		float clip = (a.depth_clip && a.depth_test) ? depth_buffer[rays.pixel[r]] : MAX_DEPTH_F;
+		float t = ot.w;
+		float4* dst = samples + (size_t)p * CHUNK;
+		for (uint32_t j = 0; j < CHUNK; ++j) {
+			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap);
+			if (t >= MAX_DEPTH_F) break;
+			float dt = calc_dt(t, a.cone_angle);
+			V3 pos = o + t * d;
+			if (a.depth_clip && a.depth_test) {
+				V3 up = train.lo + ((pos - train.lo) / tdiag) * tdiag;
+				if (dot3(cam_fwd, up - cam_pos) > clip) break;
+			}
+			dst[j] = make_float4(pos.x, pos.y, pos.z, dt);
+			++count;
+			t += dt;
+		}
+		rays.o_t[r].w = t;
+		sample_counts[p] = count;
+	}
+	// frame statistics: one 64-bit atomic per warp
+	uint32_t total = count;
+	#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) total += __shfl_xor_sync(0xffffffffu, total, s);
+	if ((threadIdx.x & 31u) == 0 && total) atomicAdd((unsigned long long*)&counters[CNT_SAMPLES_LO], (unsigned long long)total);
+}
+
+__global__ void __launch_bounds__(128) march_all_kernel(FrameArgs a, const uint8_t* __restrict__ bits, uint32_t n, const float* __restrict__ o_in,
+	const float* __restrict__ d_in, const float* __restrict__ t0, const uint8_t* __restrict__ alive, uint32_t* __restrict__ counts, float* __restrict__ samples, uint32_t max_per_ray) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	uint32_t c = 0;
+	if (alive[i]) {
+		V3 o = ld3(o_in + 3 * i), d = ld3(d_in + 3 * i);
+		V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+		Box aabb = ldbox(a.render_aabb);
+		float t = t0[i];
+		while (true) {
+			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap);
+			if (t >= MAX_DEPTH_F) break;
+			float dt = calc_dt(t, a.cone_angle);
+			if (samples && c < max_per_ray) {
+				V3 pos = o + t * d;
+				float* s = samples + ((size_t)i * max_per_ray + c) * 4;
+				s[0] = pos.x; s[1] = pos.y; s[2] = pos.z; s[3] = dt;
+			}
+			++c;
+			t += dt;
+		}
+	}
+	counts[i] = c;
+}
+
+// ---------------------------------------------------------------- occupancy bitfield (src/testbed_nerf.cu:284-331)
+__global__ void grid_to_bitfield_kernel(uint32_t n_elements, uint32_t n_nonzero, const float* __restrict__ grid, uint8_t* __restrict__ bits, float thresh) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_elements) return;
+	if (i >= n_nonzero) { bits[i] = 0; return; }
+	const float4* g = (const float4*)(grid + (size_t)i * 8);
+	float4 v0 = g[0], v1 = g[1];
+	uint8_t b = 0;
+	b |= v0.x > thresh ? 1 : 0; b |= v0.y > thresh ? 2 : 0; b |= v0.z > thresh ? 4 : 0; b |= v0.w > thresh ? 8 : 0;
+	b |= v1.x > thresh ? 16 : 0; b |= v1.y > thresh ? 32 : 0; b |= v1.z > thresh ? 64 : 0; b |= v1.w > thresh ? 128 : 0;
+	bits[i] = b;
+}
+__global__ void bitfield_max_pool_kernel(uint32_t n_elements, const uint8_t* __restrict__ prev, uint8_t* __restrict__ next) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_elements) return;
+	uint2 v = ((const uint2*)prev)[i];
+	uint8_t b = 0;
+	#pragma unroll
+	for (int j = 0; j < 4; ++j) {
+		b |= ((v.x >> (8 * j)) & 0xffu) ? (uint8_t)(1 << j) : 0;
+		b |= ((v.y >> (8 * j)) & 0xffu) ? (uint8_t)(16 << j) : 0;
+	}
+	uint32_t x = morton3D_invert(i >> 0) + GRIDSIZE / 8;
+	uint32_t y = morton3D_invert(i >> 1) + GRIDSIZE / 8;
+	uint32_t z = morton3D_invert(i >> 2) + GRIDSIZE / 8;
+	// each thread owns a distinct byte of the next level (Morton is a bijection), zeroed by the previous kernel
+	next[morton3D(x, y, z)] |= b;
+}
+// mean of max(v, 0) over cascade 0, accumulated in double for an order-independent result (the threshold is
+// min(0.01, mean): src/testbed_nerf.cu:297)
+__global__ void grid_mean_kernel(const float* __restrict__ grid, double* __restrict__ sum) {
+	double acc = 0.0;
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < GRID_CELLS; i += gridDim.x * blockDim.x) acc += (double)fmaxf(grid[i], 0.0f);
+	#pragma unroll
+	for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+	if ((threadIdx.x & 31u) == 0) atomicAdd(sum, acc);
+}
+
+// ---------------------------------------------------------------- launchers
+void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s) {
+	// mean_out is reinterpreted as a double accumulator (8 bytes, zeroed here)
+	cudaMemsetAsync(mean_out, 0, sizeof(double), s);
+	grid_mean_kernel<<<148 * 4, 256, 0, s>>>(grid, (double*)mean_out);
+}
+void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thresh, uint8_t* bits, cudaStream_t s) {
+	const uint32_t per_mip = GRID_CELLS / 8;
+	uint32_t n = per_mip * CASCADES;
+	grid_to_bitfield_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, per_mip * n_cascades, grid, bits, thresh);
+	for (uint32_t level = 1; level < CASCADES; ++level) {
+		bitfield_max_pool_kernel<<<(per_mip / 8 + 255) / 256, 256, 0, s>>>(per_mip / 8, bits + (size_t)per_mip * (level - 1), bits + (size_t)per_mip * level);
+	}
+}
+void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters, float* depth_buffer, cudaStream_t s) {
+	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer);
+}
+void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {
+	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	raygen_debug_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, o, d, t, alive);
+}
+void launch_march(const FrameArgs& a, const uint8_t* bits, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr,
+	float4* samples, uint32_t* sample_counts, uint32_t* counters, const float* depth_buffer, uint32_t max_rays, cudaStream_t s) {
+	if (!max_rays) return;
+	march_kernel<<<(max_rays + 127) / 128, 128, 0, s>>>(a, bits, rays, alive_list, n_alive_ptr, samples, sample_counts, counters, depth_buffer);
+}
+void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const float* o, const float* d, const float* t0, const uint8_t* alive,
+	uint32_t* counts, float* samples, uint32_t max_per_ray, cudaStream_t s) {
+	if (!n) return;
+	march_all_kernel<<<(n + 127) / 128, 128, 0, s>>>(a, bits, n, o, d, t0, alive, counts, samples, max_per_ray);
+}
+
+} // namespace hn

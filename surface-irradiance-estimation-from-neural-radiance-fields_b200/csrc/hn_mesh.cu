@@ -1,0 +1,266 @@
+// (e) Ray-mesh and shadow-ray traversal + mesh shading, fused into ONE kernel per frame for sm_100a:
+// pixel -> primary ray -> 4-wide BVH traversal -> sun shadow ray through the same BVH -> Disney-style BRDF -> frame/depth.
+// No intermediate ray buffers (the reference runs 6 kernels and 6 D2D copies over three RaysMeshSoa sets,
+// src/testbed_geometry_training.cu:2202-2320). IEEE-exact translation unit (-fmad=false): hit (mesh, triangle, t) is
+// bit-identical to the oracle's brute-force search. Nodes are 128-byte lines (4 child boxes SoA), triangles 3 x float4 in
+// leaf order carrying their ORIGINAL index; the traversal stack lives in shared memory, one bank-conflict-free column
+// per thread, the nearest-first child order comes from a register sorting network.
+#include "hn_device_math.cuh"
+
+namespace hn {
+
+constexpr int MESH_BLOCK = 128;
+constexpr int STACK_DEPTH = 40;
+
+struct Hit { float t; int mesh; int tri; uint32_t slot; }; // tri = ORIGINAL triangle index, slot = position in the leaf-ordered array
+
+// triangle.cuh:44-58, same operation order
+__device__ __forceinline__ float tri_intersect(V3 a, V3 b, V3 c, V3 ro, V3 rd) {
+	V3 v1v0 = b - a, v2v0 = c - a, rov0 = ro - a;
+	V3 n = cross3(v1v0, v2v0);
+	V3 q = cross3(rov0, rd);
+	float d = 1.0f / dot3(rd, n);
+	float u = d * -dot3(q, v2v0);
+	float v = d * dot3(q, v1v0);
+	float t = d * -dot3(n, rov0);
+	if (u < 0.0f || u > 1.0f || v < 0.0f || (u + v) > 1.0f || t < 0.0f) t = FLT_MAX;
+	return t;
+}
+
+__device__ __forceinline__ void cswap(float& da, int& ia, float& db, int& ib) {
+	if (da < db) { float t = da; da = db; db = t; int k = ia; ia = ib; ib = k; } // descending: nearest ends up last = popped first
+}
+
+// Nearest hit inside one mesh. Acceptance as triangle_bvh.cu:150-193 (mint starts at the caller's best, strict <) plus the
+// shared tie rule: equal t inside the same mesh -> lower original triangle index.
+__device__ void traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& best, int* stack /* shared, stride MESH_BLOCK */) {
+	const MeshDev m = sc.meshes[mesh];
+	const V3 inv = mk(1.0f, 1.0f, 1.0f) / d;
+	int sp = 0;
+	stack[0] = (int)m.node_root; sp = 1;
+	while (sp > 0) {
+		const int code = stack[(--sp) * MESH_BLOCK];
+		if (code < 0) {
+			const uint32_t v = (uint32_t)(-1 - code);
+			const uint32_t first = m.tri_first + (v >> 4), cnt = v & 15u;
+			for (uint32_t k = 0; k < cnt; ++k) {
+				const float4 A = __ldg(sc.tris + (size_t)(first + k) * 3), B = __ldg(sc.tris + (size_t)(first + k) * 3 + 1), C = __ldg(sc.tris + (size_t)(first + k) * 3 + 2);
+				const float t = tri_intersect(mk(A.x, A.y, A.z), mk(B.x, B.y, B.z), mk(C.x, C.y, C.z), o, d);
+				const int orig = __float_as_int(A.w);
+				if (t < best.t || (t == best.t && best.mesh == mesh && orig < best.tri)) { best.t = t; best.mesh = mesh; best.tri = orig; best.slot = first + k; }
+			}
+			continue;
+		}
+		const float4* np = reinterpret_cast<const float4*>(sc.nodes + code);
+		const float4 lox = __ldg(np), loy = __ldg(np + 1), loz = __ldg(np + 2), hix = __ldg(np + 3), hiy = __ldg(np + 4), hiz = __ldg(np + 5);
+		const int4 child = __ldg(reinterpret_cast<const int4*>(np + 6)), count = __ldg(reinterpret_cast<const int4*>(np + 7));
+		float dist[4]; int idx[4];
+		const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+		const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+		const int ch[4] = {child.x, child.y, child.z, child.w}, cn[4] = {count.x, count.y, count.z, count.w};
+		#pragma unroll
+		for (int i = 0; i < 4; ++i) {
+			// NaN-safe slab test on the (conservatively padded) child box; keep it when entry <= current best t
+			float t0x = (lx[i] - o.x) * inv.x, t1x = (hx[i] - o.x) * inv.x;
+			float t0y = (ly[i] - o.y) * inv.y, t1y = (hy[i] - o.y) * inv.y;
+			float t0z = (lz[i] - o.z) * inv.z, t1z = (hz[i] - o.z) * inv.z;
+			float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
+			float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best.t));
+			bool hit = cn[i] != 0 && tn <= tf;
+			dist[i] = hit ? tn : -1.0f;
+			idx[i] = ch[i];
+		}
+		// sorting network N=4 (5 compare-exchanges), descending by distance; misses (-1) sink to the end and are skipped
+		cswap(dist[0], idx[0], dist[2], idx[2]);
+		cswap(dist[1], idx[1], dist[3], idx[3]);
+		cswap(dist[0], idx[0], dist[1], idx[1]);
+		cswap(dist[2], idx[2], dist[3], idx[3]);
+		cswap(dist[1], idx[1], dist[2], idx[2]);
+		#pragma unroll
+		for (int i = 0; i < 4; ++i) {
+			if (dist[i] >= 0.0f && sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+		}
+	}
+}
+
+// geometry_bvh.cu:646-676 with the top level of :166-200. compat = pick the ONE mesh with the nearest box entry
+// (reference rule, BoundingBox::ray_intersect on the exact mesh boxes); default = nearest hit over all meshes.
+// `touched` = whether the reference kernel would have moved the ray at all.
+__device__ void scene_nearest(const SceneDev& sc, int compat, V3 o, V3 d, Hit& h, bool& touched, int* stack) {
+	h.t = MAX_DIST_F; h.mesh = -1; h.tri = -1; h.slot = 0;
+	touched = false;
+	if (compat) {
+		float mint = MAX_DIST_F; int mesh = -1;
+		for (uint32_t i = 0; i < sc.n_meshes; ++i) {
+			Box b = ldbox(sc.meshes[i].bb);
+			float2 tt = box_ray_intersect(b, o, d);
+			if (tt.x < mint && tt.x > -FLT_MAX) { mint = tt.x; mesh = (int)i; }
+		}
+		if (mesh < 0) return;
+		touched = true;
+		traverse_mesh(sc, mesh, o, d, h, stack);
+		return;
+	}
+	touched = true;
+	for (uint32_t i = 0; i < sc.n_meshes; ++i) traverse_mesh(sc, (int)i, o, d, h, stack);
+}
+
+__global__ void __launch_bounds__(MESH_BLOCK) trace_kernel(SceneDev sc, int compat, uint32_t n, const float* __restrict__ o_in, const float* __restrict__ d_in,
+	int32_t* __restrict__ mesh_out, int32_t* __restrict__ tri_out, float* __restrict__ t_out) {
+	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	Hit h; bool touched;
+	scene_nearest(sc, compat, ld3(o_in + 3 * i), ld3(d_in + 3 * i), h, touched, stack_s + threadIdx.x);
+	if (h.tri < 0) h.mesh = compat ? h.mesh : -1;
+	mesh_out[i] = h.mesh; tri_out[i] = h.tri; t_out[i] = h.t;
+}
+
+// ---------------------------------------------------------------- shading (testbed_geometry_training.cu:50-144)
+__device__ __forceinline__ float sqr(float x) { return x * x; }
+__device__ __forceinline__ float saturate1(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+__device__ __forceinline__ float schlick(float u) { float m = saturate1(1.0f - u); return sqr(sqr(m)) * m; }
+#define HN_PI 3.14159265358979323846f
+__device__ __forceinline__ float G1f(float NdotH, float a) {
+	if (a >= 1.0f) return 1.0f / HN_PI;
+	float a2 = sqr(a);
+	float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+	return (a2 - 1.0f) / (HN_PI * logf(a2) * t);
+}
+__device__ __forceinline__ float G2f(float NdotH, float a) {
+	float a2 = sqr(a);
+	float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+	return a2 / (HN_PI * t * t);
+}
+__device__ __forceinline__ float smithG(float NdotV, float alphaG) {
+	float a = alphaG * alphaG, b = NdotV * NdotV;
+	return 1.0f / (NdotV + sqrtf(a + b - a * b));
+}
+__device__ V3 evaluate_shading(V3 base_color, V3 ambient_color, V3 light_color, float metallic, float subsurface, float specular, float roughness,
+	float specular_tint, float sheen, float sheen_tint, float clearcoat, float clearcoat_gloss, V3 L, V3 V, V3 N) {
+	float NdotL = dot3(N, L), NdotV = dot3(N, V);
+	V3 H = normalize3(L + V);
+	float NdotH = dot3(N, H), LdotH = dot3(L, H);
+	float FL = schlick(NdotL), FV = schlick(NdotV);
+	V3 amb = ambient_color * mixf(0.2f, FV, metallic);
+	amb = amb * base_color;
+	if (NdotL < 0.f || NdotV < 0.f) return amb;
+	float luminance = dot3(base_color, mk(0.3f, 0.6f, 0.1f));
+	V3 one = mk(1.0f, 1.0f, 1.0f);
+	V3 Ctint = base_color * (1.f / (luminance + 0.00001f));
+	V3 Cspec0 = mix3(mix3(one, Ctint, specular_tint) * specular * 0.08f, base_color, metallic);
+	V3 Csheen = mix3(one, Ctint, sheen_tint);
+	float Fd90 = 0.5f + 2.0f * LdotH * LdotH * roughness;
+	float Fd = mixf(1, Fd90, FL) * mixf(1.f, Fd90, FV);
+	float Fss90 = LdotH * LdotH * roughness;
+	float Fss = mixf(1.0f, Fss90, FL) * mixf(1.0f, Fss90, FV);
+	float ss = 1.25f * (Fss * (1.f / (NdotL + NdotV) - 0.5f) + 0.5f);
+	float a = fmaxf(0.001f, sqr(roughness));
+	float Ds = G2f(NdotH, a);
+	float FH = schlick(LdotH);
+	V3 Fs = mix3(Cspec0, one, FH);
+	float Gs = smithG(NdotL, a) * smithG(NdotV, a);
+	V3 Fsheen = FH * sheen * Csheen;
+	float Dr = G1f(NdotH, mixf(0.1f, 0.001f, clearcoat_gloss));
+	float Fr = mixf(0.04f, 1.0f, FH);
+	float Gr = smithG(NdotL, 0.25f) * smithG(NdotV, 0.25f);
+	float CCs = 0.25f * clearcoat * Gr * Fr * Dr;
+	V3 brdf = ((1.0f / HN_PI) * mixf(Fd, ss, subsurface) * base_color + Fsheen) * (1.0f - metallic) + Gs * Fs * Ds + mk(CCs, CCs, CCs);
+	return (brdf * light_color) * NdotL + amb;
+}
+
+// Triangle::normal (triangle.cuh:40-42)
+__device__ __forceinline__ V3 tri_normal(const SceneDev& sc, uint32_t slot) {
+	const float4 A = __ldg(sc.tris + (size_t)slot * 3), B = __ldg(sc.tris + (size_t)slot * 3 + 1), C = __ldg(sc.tris + (size_t)slot * 3 + 2);
+	V3 a = mk(A.x, A.y, A.z), b = mk(B.x, B.y, B.z), c = mk(C.x, C.y, C.z);
+	return normalize3(cross3(b - a, c - a));
+}
+
+__device__ __forceinline__ bool mesh_tile_owned(const FrameArgs& a, uint32_t x, uint32_t y) {
+	if (a.world <= 1) return true;
+	uint32_t tiles_x = (a.w + a.tile_w - 1) / a.tile_w;
+	uint32_t tile = (y / a.tile_h) * tiles_x + (x / a.tile_w);
+	return (int)(tile % (uint32_t)a.world) == a.rank;
+}
+
+// render_geometry_mesh (src/testbed_geometry_training.cu:2202-2320), Shade mode, one thread per pixel.
+__global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, SceneDev sc, float4* __restrict__ frame, float* __restrict__ depth_buffer) {
+	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
+	int* stack = stack_s + threadIdx.x;
+	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= (uint32_t)a.w * (uint32_t)a.h) return;
+	const uint32_t x = idx % (uint32_t)a.w, y = idx / (uint32_t)a.w;
+	if (!mesh_tile_owned(a, x, y)) return;
+	const Box aabb = ldbox(a.mesh_aabb);
+	// init_rays_with_payload_kernel_mesh_geometry (:488-579): pixel_to_ray with camera_matrix0 as is (no rolling shutter)
+	const float u = ((float)x + a.pixel_offset[0]) / (float)a.w, v = ((float)y + a.pixel_offset[1]) / (float)a.h;
+	V3 dir = mk((u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f);
+	const V3 c0 = ld3(a.cam0), c1 = ld3(a.cam0 + 3), c2 = ld3(a.cam0 + 6), cam_pos = ld3(a.cam0 + 9);
+	{
+		V3 head = mk(0.0f, 0.0f, 0.0f);
+		dir = dir - head * 0.0f;
+		V3 r = mk(0.0f, 0.0f, 0.0f);
+		r.x += c0.x * dir.x; r.y += c0.y * dir.x; r.z += c0.z * dir.x;
+		r.x += c1.x * dir.y; r.y += c1.y * dir.y; r.z += c1.z * dir.y;
+		r.x += c2.x * dir.z; r.y += c2.y * dir.z; r.z += c2.z * dir.z;
+		dir = r;
+	}
+	V3 org = mk(0.0f, 0.0f, 0.0f) + cam_pos; // mat3(camera) * head_pos (= 0) + camera[3]
+	org = org + dir * a.near_distance;
+	depth_buffer[idx] = MAX_DEPTH_F;
+	dir = normalize3(dir);
+	const float t0 = fmaxf(box_ray_intersect(aabb, org, dir).x, 0.0f);
+	V3 pos = org + (t0 + 1e-6f) * dir;
+	// primary hit (:2140-2155: every pixel is traced; the direction rides in the normal buffer)
+	Hit h; bool touched;
+	scene_nearest(sc, a.compat_nearest_aabb_only, pos, dir, h, touched, stack);
+	V3 nrm = dir;
+	if (touched) {
+		pos = pos + h.t * dir;
+		if (h.tri >= 0) nrm = tri_normal(sc, h.slot);
+	}
+	// sun shadow ray (:222-278)
+	const V3 sun = normalize3(ld3(a.sun));
+	float shadow;
+	{
+		const float sgn = -copysignf(1.0f, dot3(dir, nrm)); // faceforward(n, i, nref) = n * -sign(dot(i, nref))
+		V3 view_pos = pos + normalize3(nrm * sgn) * 1e-3f;
+		const float ts = fmaxf(box_ray_intersect(aabb, view_pos, sun).x + 1e-6f, 0.0f);
+		view_pos = view_pos + ts * sun;
+		const V3 sdir = box_contains(aabb, view_pos) ? sun : dir; // an origin outside the box keeps payload.dir (:239-244)
+		Hit sh; bool st;
+		scene_nearest(sc, a.compat_nearest_aabb_only, view_pos, sdir, sh, st, stack);
+		const V3 end = st ? view_pos + sh.t * sdir : view_pos;
+		shadow = box_contains(aabb, end) ? 0.0f : 1.0f; // write_shadow_ray_result_geometry
+	}
+	// shade_kernel_mesh_geometry (:280-355)
+	if (!box_contains(aabb, pos)) return;
+	V3 normal = normalize3(nrm);
+	bool floor_hit = false;
+	if (pos.y < a.floor_y + 0.001f && dir.y < 0.f) { normal = mk(0.0f, 1.0f, 0.0f); floor_hit = true; }
+	const V3 up = normalize3(ld3(a.up));
+	const float skyam = -dot3(normal, up) * 0.5f + 0.5f;
+	const V3 suncol = mk(255.f / 255.0f, 225.f / 255.0f, 195.f / 255.0f) * 4.f * shadow;
+	const V3 skycol = mk(195.f / 255.0f, 215.f / 255.0f, 255.f / 255.0f) * 4.f * skyam;
+	const float check_size = 8.f / (aabb.hi.x - aabb.lo.x);
+	const float check = ((int(floorf(check_size * (pos.x - aabb.lo.x))) ^ int(floorf(check_size * (pos.z - aabb.lo.z)))) & 1) ? 0.8f : 0.2f;
+	const V3 floorcol = mk(check * check * check, check * check, check);
+	const float* B = a.brdf;
+	const V3 basecolor = mk(B[7], B[8], B[9]), ambientcolor = mk(B[10], B[11], B[12]);
+	const V3 color = evaluate_shading(floor_hit ? floorcol : basecolor * basecolor, ambientcolor * skycol, suncol,
+		floor_hit ? 0.f : B[0], floor_hit ? 0.f : B[1], floor_hit ? 1.f : B[2], floor_hit ? 0.5f : B[3], 0.f, floor_hit ? 0.f : B[4], 0.f,
+		floor_hit ? 0.f : B[5], B[6], sun, -normalize3(dir), normal);
+	frame[idx] = make_float4(color.x, color.y, color.z, 1.0f);
+	depth_buffer[idx] = dot3(c2, pos - cam_pos);
+}
+
+void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, cudaStream_t s) {
+	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	mesh_pass_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, frame, depth_buffer);
+}
+void launch_trace(SceneDev scene, int compat, uint32_t n, const float* o, const float* d, int32_t* mesh, int32_t* tri, float* t, cudaStream_t s) {
+	if (!n) return;
+	trace_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(scene, compat, n, o, d, mesh, tri, t);
+}
+
+} // namespace hn

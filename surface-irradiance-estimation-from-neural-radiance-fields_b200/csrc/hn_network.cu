@@ -1,0 +1,341 @@
+// (b)+(c) Fused network evaluation for sm_100a: multiresolution hash-grid gather -> density MLP -> SH -> colour MLP in ONE
+// kernel; the 64 B/sample encoded features and all hidden activations never touch global memory.
+// Samples arrive in ray chunks of CHUNK=32 (one warp = one ray chunk = one direction). Output: 8 B/sample (r,g,b,sigma fp16).
+//
+// Arithmetic follows the reference (tcnn grid.h:48-212, common_device.h:340-366,651-718,842-854; fully_fused_mlp.cu):
+// corner weights rounded to fp16 and accumulated with fp16 FMAs (grid.h:162) -> the encoding is bit-identical to the oracle;
+// MLPs take fp16 inputs/weights, accumulate in fp32 on the tensor cores and store fp16 activations between layers.
+#include "hn_internal.h"
+#include <mma.h>
+
+namespace hn {
+
+struct EvalArgs {
+	GridLevels g;
+	const __half* table;
+	const __half* w_density;
+	const __half* w_rgb;
+	int density_hidden, rgb_hidden;
+	float train_lo[3], train_diag[3];
+	const float4* samples;          // [n_chunks][32] (x,y,z,dt) un-warped
+	const uint32_t* sample_counts;  // [n_chunks] valid samples per chunk (nullptr = all 32)
+	const uint32_t* alive_list;     // [n_chunks] ray id per chunk (nullptr with dirs_override)
+	const float4* d_mw;             // ray directions by ray id
+	const float* dirs_override;     // [n_chunks][3] (operator entry point)
+	const uint32_t* n_chunks_ptr;   // device-side chunk count (nullptr -> n_chunks)
+	uint32_t n_chunks;
+	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output
+};
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+	__half2 h = __floats2half2_rn(a, b);
+	return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+	asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+	asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+		: "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// ---- hash grid: one sample, all levels. F = features per level (2 or 4), L = 32 / F levels -> 32 halfs in `enc`.
+template <int F>
+__device__ __forceinline__ void encode_sample(const GridLevels& g, const __half* __restrict__ table, float px, float py, float pz, uint32_t (&enc)[16]) {
+	constexpr int L = 32 / F;
+	#pragma unroll
+	for (int l = 0; l < L; ++l) {
+		const float scale = g.scale[l];
+		const uint32_t res = g.res[l], size = g.size[l];
+		const __half* __restrict__ lvl = table + (size_t)g.offset[l] * F;
+		// pos_fract (common_device.h:842-854)
+		float fx = fmaf(scale, px, 0.5f), fy = fmaf(scale, py, 0.5f), fz = fmaf(scale, pz, 0.5f);
+		float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
+		uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
+		fx -= flx; fy -= fly; fz -= flz;
+		float wx[2] = {__fsub_rn(1.0f, fx), fx}, wy[2] = {__fsub_rn(1.0f, fy), fy}, wz[2] = {__fsub_rn(1.0f, fz), fz};
+		const bool hashed = g.hashed[l] != 0;
+		// grid_index (common_device.h:690-707): dense x + y*R + z*R^2, or coherent prime hash; then % hashmap_size
+		uint32_t idx[8];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			uint32_t x = gx + (c & 1), y = gy + ((c >> 1) & 1), z = gz + ((c >> 2) & 1);
+			uint32_t i = hashed ? (x ^ (y * 2654435761u) ^ (z * 805459861u)) : (x + y * res + z * res * res);
+			idx[c] = i % size;
+		}
+		if (F == 4) {
+			uint2 v[8];
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) v[c] = __ldg(reinterpret_cast<const uint2*>(lvl) + idx[c]);
+			__half2 a0 = __float2half2_rn(0.f), a1 = a0;
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) {
+				float w = __fmul_rn(__fmul_rn(__fmul_rn(1.0f, wx[c & 1]), wy[(c >> 1) & 1]), wz[(c >> 2) & 1]);
+				__half2 w2 = __float2half2_rn(w);
+				a0 = __hfma2(w2, *reinterpret_cast<__half2*>(&v[c].x), a0);
+				a1 = __hfma2(w2, *reinterpret_cast<__half2*>(&v[c].y), a1);
+			}
+			enc[2 * l] = *reinterpret_cast<uint32_t*>(&a0);
+			enc[2 * l + 1] = *reinterpret_cast<uint32_t*>(&a1);
+		} else {
+			uint32_t v[8];
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) v[c] = __ldg(reinterpret_cast<const uint32_t*>(lvl) + idx[c]);
+			__half2 a0 = __float2half2_rn(0.f);
+			#pragma unroll
+			for (int c = 0; c < 8; ++c) {
+				float w = __fmul_rn(__fmul_rn(__fmul_rn(1.0f, wx[c & 1]), wy[(c >> 1) & 1]), wz[(c >> 2) & 1]);
+				a0 = __hfma2(__float2half2_rn(w), *reinterpret_cast<__half2*>(&v[c]), a0);
+			}
+			enc[l] = *reinterpret_cast<uint32_t*>(&a0);
+		}
+	}
+}
+
+// operator entry point a-10: encoding only
+template <int F>
+__global__ void __launch_bounds__(128) encode_kernel(GridLevels g, const __half* __restrict__ table, const float* __restrict__ pos, uint32_t n, __half* __restrict__ out) {
+	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	uint32_t enc[16];
+	encode_sample<F>(g, table, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], enc);
+	uint4* o = reinterpret_cast<uint4*>(out + (size_t)i * 32);
+	#pragma unroll
+	for (int k = 0; k < 4; ++k) o[k] = make_uint4(enc[4 * k], enc[4 * k + 1], enc[4 * k + 2], enc[4 * k + 3]);
+}
+
+// ---- degree-4 real spherical harmonics (common_device.h:340-366), input = unit direction components
+__device__ __forceinline__ void sh4(float x, float y, float z, float (&o)[16]) {
+	float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
+	o[0] = 0.28209479177387814f;
+	o[1] = -0.48860251190291987f * y;
+	o[2] = 0.48860251190291987f * z;
+	o[3] = -0.48860251190291987f * x;
+	o[4] = 1.0925484305920792f * xy;
+	o[5] = -1.0925484305920792f * yz;
+	o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
+	o[7] = -1.0925484305920792f * xz;
+	o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
+	o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
+	o[10] = 2.8906114426405538f * xy * z;
+	o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
+	o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
+	o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
+	o[14] = 1.4453057213202769f * z * (x2 - y2);
+	o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
+}
+
+// ---- MLP on legacy-free warp MMA tiles: each warp owns 32 rows (2 m-tiles of 16); activations stay in registers.
+// Weights live in shared memory as [out][in] rows padded by 16 B (conflict-free ldmatrix); a row of W is one B column.
+constexpr int W32_STRIDE = 80;   // bytes per weight row with 32 inputs
+constexpr int W64_STRIDE = 144;  // bytes per weight row with 64 inputs
+constexpr int A_STRIDE = 80;     // bytes per staged input row (32 halfs + pad)
+
+// C[2][NT][4] += A[2][KT][4] x W^T, W rows = NT*8 outputs
+template <int KT, int NT, int STRIDE>
+__device__ __forceinline__ void mma_layer(const uint32_t (&A)[2][KT][4], uint32_t w_smem, float (&C)[2][NT][4], int lane) {
+	#pragma unroll
+	for (int mt = 0; mt < 2; ++mt)
+		#pragma unroll
+		for (int nt = 0; nt < NT; ++nt)
+			#pragma unroll
+			for (int k = 0; k < 4; ++k) C[mt][nt][k] = 0.0f;
+	const int mid = lane >> 3, row = lane & 7;
+	#pragma unroll
+	for (int kt = 0; kt < KT; ++kt) {
+		#pragma unroll
+		for (int np = 0; np < NT / 2; ++np) {
+			uint32_t b[4];
+			uint32_t addr = w_smem + (uint32_t)(((2 * np + (mid >> 1)) * 8 + row) * STRIDE + (kt * 16 + (mid & 1) * 8) * 2);
+			ldmatrix_x4(b, addr);
+			#pragma unroll
+			for (int mt = 0; mt < 2; ++mt) {
+				mma16816(C[mt][2 * np], A[mt][kt], b[0], b[1]);
+				mma16816(C[mt][2 * np + 1], A[mt][kt], b[2], b[3]);
+			}
+		}
+	}
+}
+// fp32 accumulators of 64 outputs -> fp16 A fragments (4 k-tiles) of the next layer, with ReLU
+__device__ __forceinline__ void relu_to_a(const float (&C)[2][8][4], uint32_t (&A)[2][4][4]) {
+	#pragma unroll
+	for (int mt = 0; mt < 2; ++mt)
+		#pragma unroll
+		for (int kt = 0; kt < 4; ++kt) {
+			A[mt][kt][0] = pack_h2(fmaxf(C[mt][2 * kt][0], 0.f), fmaxf(C[mt][2 * kt][1], 0.f));
+			A[mt][kt][1] = pack_h2(fmaxf(C[mt][2 * kt][2], 0.f), fmaxf(C[mt][2 * kt][3], 0.f));
+			A[mt][kt][2] = pack_h2(fmaxf(C[mt][2 * kt + 1][0], 0.f), fmaxf(C[mt][2 * kt + 1][1], 0.f));
+			A[mt][kt][3] = pack_h2(fmaxf(C[mt][2 * kt + 1][2], 0.f), fmaxf(C[mt][2 * kt + 1][3], 0.f));
+		}
+}
+
+__host__ __device__ inline uint32_t mlp_smem_bytes(int hidden) { return 64 * W32_STRIDE + (hidden - 1) * 64 * W64_STRIDE + 16 * W64_STRIDE; }
+
+// copy one MLP's weights (global, dense rows) into padded shared memory rows
+__device__ void stage_mlp(const __half* __restrict__ w, int hidden, uint8_t* smem) {
+	// first layer: 64 rows x 32 halfs (4 x 16 B per row)
+	for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
+		int r = i >> 2, c = i & 3;
+		*reinterpret_cast<uint4*>(smem + r * W32_STRIDE + c * 16) = __ldg(reinterpret_cast<const uint4*>(w + r * 32) + c);
+	}
+	w += 64 * 32; smem += 64 * W32_STRIDE;
+	int rows64 = (hidden - 1) * 64 + 16;
+	for (int i = threadIdx.x; i < rows64 * 8; i += blockDim.x) {
+		int r = i >> 3, c = i & 7;
+		*reinterpret_cast<uint4*>(smem + r * W64_STRIDE + c * 16) = __ldg(reinterpret_cast<const uint4*>(w + r * 64) + c);
+	}
+}
+
+// hidden stack of one MLP after its 32-wide input layer: returns the 16-wide output accumulators
+__device__ __forceinline__ void mlp_forward(const uint32_t (&Ain)[2][2][4], uint32_t w_smem, int hidden, float (&Cout)[2][2][4], int lane) {
+	float C[2][8][4];
+	uint32_t A[2][4][4];
+	mma_layer<2, 8, W32_STRIDE>(Ain, w_smem, C, lane);
+	relu_to_a(C, A);
+	w_smem += 64 * W32_STRIDE;
+	for (int l = 1; l < hidden; ++l) {
+		mma_layer<4, 8, W64_STRIDE>(A, w_smem, C, lane);
+		relu_to_a(C, A);
+		w_smem += 64 * W64_STRIDE;
+	}
+	mma_layer<4, 2, W64_STRIDE>(A, w_smem, Cout, lane);
+}
+
+template <int F>
+__global__ void __launch_bounds__(128) eval_kernel(const __grid_constant__ EvalArgs a) {
+	extern __shared__ __align__(16) uint8_t smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint8_t* w_density_s = smem;
+	uint8_t* w_rgb_s = w_density_s + mlp_smem_bytes(a.density_hidden);
+	uint8_t* stage = w_rgb_s + mlp_smem_bytes(a.rgb_hidden) + warp * (32 * A_STRIDE);
+	stage_mlp(a.w_density, a.density_hidden, w_density_s);
+	stage_mlp(a.w_rgb, a.rgb_hidden, w_rgb_s);
+	__syncthreads();
+
+	const uint32_t n_chunks = a.n_chunks_ptr ? min(*a.n_chunks_ptr, a.n_chunks) : a.n_chunks;
+	const uint32_t warps_total = gridDim.x * (blockDim.x >> 5);
+	const int g = lane >> 2, tg = lane & 3;
+
+	for (uint32_t chunk = blockIdx.x * (blockDim.x >> 5) + warp; chunk < n_chunks; chunk += warps_total) {
+		const uint32_t count = a.sample_counts ? a.sample_counts[chunk] : CHUNK;
+		if (count == 0) continue;
+		// ---- (b) gather: lane = sample row
+		{
+			uint32_t enc[16];
+			#pragma unroll
+			for (int k = 0; k < 16; ++k) enc[k] = 0u;
+			if ((uint32_t)lane < count) {
+				float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
+				// warp_position (nerf_device.cuh:265-270): (p - min) / diag, IEEE divide
+				float px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
+				float py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
+				float pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
+				encode_sample<F>(a.g, a.table, px, py, pz, enc);
+			}
+			uint4* row = reinterpret_cast<uint4*>(stage + lane * A_STRIDE);
+			#pragma unroll
+			for (int k = 0; k < 4; ++k) row[k] = make_uint4(enc[4 * k], enc[4 * k + 1], enc[4 * k + 2], enc[4 * k + 3]);
+		}
+		__syncwarp();
+		// ---- (c) density MLP
+		uint32_t Ain[2][2][4];
+		{
+			const int mid = lane >> 3, r = lane & 7;
+			#pragma unroll
+			for (int mt = 0; mt < 2; ++mt)
+				#pragma unroll
+				for (int kt = 0; kt < 2; ++kt)
+					ldmatrix_x4(Ain[mt][kt], smem_u32(stage + (mt * 16 + (mid & 1) * 8 + r) * A_STRIDE + (kt * 16 + (mid >> 1) * 8) * 2));
+		}
+		__syncwarp();
+		float Cd[2][2][4];
+		mlp_forward(Ain, smem_u32(w_density_s), a.density_hidden, Cd, lane);
+		// ---- colour MLP input: [16 density outputs | 16 SH coefficients]
+		float dx, dy, dz;
+		if (a.dirs_override) {
+			dx = a.dirs_override[3 * chunk]; dy = a.dirs_override[3 * chunk + 1]; dz = a.dirs_override[3 * chunk + 2];
+		} else {
+			float4 d = __ldg(a.d_mw + a.alive_list[chunk]);
+			dx = d.x; dy = d.y; dz = d.z;
+		}
+		// warp_direction then kernel_sh's *2-1 (nerf_device.cuh:290-292, spherical_harmonics.h:66-68)
+		dx = __fmul_rn(__fadd_rn(dx, 1.0f), 0.5f) * 2.f - 1.f;
+		dy = __fmul_rn(__fadd_rn(dy, 1.0f), 0.5f) * 2.f - 1.f;
+		dz = __fmul_rn(__fadd_rn(dz, 1.0f), 0.5f) * 2.f - 1.f;
+		float sh[16];
+		sh4(dx, dy, dz, sh);
+		uint32_t p0, p1;
+		if (tg == 0) { p0 = pack_h2(sh[0], sh[1]); p1 = pack_h2(sh[8], sh[9]); }
+		else if (tg == 1) { p0 = pack_h2(sh[2], sh[3]); p1 = pack_h2(sh[10], sh[11]); }
+		else if (tg == 2) { p0 = pack_h2(sh[4], sh[5]); p1 = pack_h2(sh[12], sh[13]); }
+		else { p0 = pack_h2(sh[6], sh[7]); p1 = pack_h2(sh[14], sh[15]); }
+		__half sigma[2][2];
+		#pragma unroll
+		for (int mt = 0; mt < 2; ++mt) {
+			Ain[mt][0][0] = pack_h2(Cd[mt][0][0], Cd[mt][0][1]);
+			Ain[mt][0][1] = pack_h2(Cd[mt][0][2], Cd[mt][0][3]);
+			Ain[mt][0][2] = pack_h2(Cd[mt][1][0], Cd[mt][1][1]);
+			Ain[mt][0][3] = pack_h2(Cd[mt][1][2], Cd[mt][1][3]);
+			Ain[mt][1][0] = p0; Ain[mt][1][1] = p0; Ain[mt][1][2] = p1; Ain[mt][1][3] = p1;
+			sigma[mt][0] = __float2half_rn(Cd[mt][0][0]); // density channel 0, rows g / g+8 (valid on tg == 0)
+			sigma[mt][1] = __float2half_rn(Cd[mt][0][2]);
+		}
+		float Cr[2][2][4];
+		mlp_forward(Ain, smem_u32(w_rgb_s), a.rgb_hidden, Cr, lane);
+		// ---- output: tg 0 holds (r,g), tg 1 holds (b,.) of rows g and g+8
+		#pragma unroll
+		for (int mt = 0; mt < 2; ++mt) {
+			float b_lo = __shfl_down_sync(0xffffffffu, Cr[mt][0][0], 1);
+			float b_hi = __shfl_down_sync(0xffffffffu, Cr[mt][0][2], 1);
+			if (tg == 0) {
+				uint2 o0, o1;
+				o0.x = pack_h2(Cr[mt][0][0], Cr[mt][0][1]);
+				o1.x = pack_h2(Cr[mt][0][2], Cr[mt][0][3]);
+				__half2 t0 = __halves2half2(__float2half_rn(b_lo), sigma[mt][0]);
+				__half2 t1 = __halves2half2(__float2half_rn(b_hi), sigma[mt][1]);
+				o0.y = *reinterpret_cast<uint32_t*>(&t0);
+				o1.y = *reinterpret_cast<uint32_t*>(&t1);
+				a.out[(size_t)chunk * CHUNK + mt * 16 + g] = o0;
+				a.out[(size_t)chunk * CHUNK + mt * 16 + g + 8] = o1;
+			}
+		}
+	}
+}
+
+// ---------------------------------------------------------------- launchers
+void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s) {
+	if (!n) return;
+	if (F == 4) encode_kernel<4><<<(n + 127) / 128, 128, 0, s>>>(g, table, positions, n, out);
+	else encode_kernel<2><<<(n + 127) / 128, 128, 0, s>>>(g, table, positions, n, out);
+}
+
+void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples,
+	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
+	uint32_t max_chunks, uint2* out, cudaStream_t s) {
+	if (!max_chunks) return;
+	EvalArgs a;
+	a.g = g;
+	a.table = params + cfg.grid_offset;
+	a.w_density = params + cfg.density_w_offset;
+	a.w_rgb = params + cfg.rgb_w_offset;
+	a.density_hidden = (int)cfg.density_hidden; a.rgb_hidden = (int)cfg.rgb_hidden;
+	for (int i = 0; i < 3; ++i) { a.train_lo[i] = fa.train_aabb[i]; a.train_diag[i] = fa.train_aabb[3 + i] - fa.train_aabb[i]; }
+	a.samples = samples; a.sample_counts = sample_counts; a.alive_list = alive_list; a.d_mw = rays.d_mw;
+	a.dirs_override = dirs_override; a.n_chunks_ptr = n_chunks_ptr; a.n_chunks = max_chunks; a.out = out;
+	size_t smem = mlp_smem_bytes(a.density_hidden) + mlp_smem_bytes(a.rgb_hidden) + 4 * 32 * A_STRIDE;
+	static int sm_count = 0;
+	if (!sm_count) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); }
+	uint32_t blocks = (max_chunks + 3) / 4;
+	uint32_t persistent = (uint32_t)sm_count * 3u;
+	if (blocks > persistent) blocks = persistent;
+	if (cfg.F == 4) {
+		cudaFuncSetAttribute(eval_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		eval_kernel<4><<<blocks, 128, smem, s>>>(a);
+	} else {
+		cudaFuncSetAttribute(eval_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		eval_kernel<2><<<blocks, 128, smem, s>>>(a);
+	}
+}
+
+} // namespace hn

@@ -1,0 +1,313 @@
+"""ctypes binding of libhn_b200.so (include/hybrid_nerf.h) shaped like the reference's ``pyngp.Testbed``
+(src/python_api.cu:263-733): same method names and argument meaning for the render path, errors raised as
+RuntimeError (pybind11 translates the reference's std::runtime_error the same way).
+
+There is no CPU path behind this module: importing it without the built CUDA library raises ImportError, and every
+computing call fails without a B200.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhn_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(make -C <package>/csrc). This package has no CPU fallback."
+    )
+
+_lib = C.CDLL(LIB_PATH)
+
+_f32p = C.POINTER(C.c_float)
+_u8p = C.POINTER(C.c_uint8)
+_u16p = C.POINTER(C.c_uint16)
+_u32p = C.POINTER(C.c_uint32)
+_i32p = C.POINTER(C.c_int32)
+
+
+class NetworkInfo(C.Structure):
+    _fields_ = [
+        ("n_levels", C.c_uint32), ("n_features_per_level", C.c_uint32), ("log2_hashmap_size", C.c_uint32), ("base_resolution", C.c_uint32),
+        ("per_level_scale", C.c_float), ("density_hidden_layers", C.c_uint32), ("rgb_hidden_layers", C.c_uint32),
+        ("n_params", C.c_uint64), ("grid_param_offset", C.c_uint64),
+        ("level_offsets", C.c_uint32 * 17), ("level_scales", C.c_float * 16), ("level_resolutions", C.c_uint32 * 16),
+    ]
+
+
+class FrameStats(C.Structure):
+    _fields_ = [
+        ("n_samples", C.c_uint64), ("n_samples_composited", C.c_uint64), ("n_rays_alive", C.c_uint32), ("n_passes", C.c_uint32),
+        ("n_kernel_launches", C.c_uint32), ("ms_mesh", C.c_float), ("ms_raygen", C.c_float), ("ms_march", C.c_float),
+        ("ms_eval", C.c_float), ("ms_composite", C.c_float), ("ms_total", C.c_float),
+    ]
+
+
+# every symbol include/hybrid_nerf.h declares (tests check that the library exports all of them)
+EXPORTS = [
+    "hn_create", "hn_destroy", "hn_last_error", "hn_version", "hn_load_network_config", "hn_load_network_config_string",
+    "hn_set_aabb_scale", "hn_get_network_info", "hn_set_params", "hn_set_density_grid", "hn_set_occupancy_bitfield",
+    "hn_get_occupancy_bitfield", "hn_load_scene", "hn_add_mesh", "hn_load_mesh_file", "hn_build_scene", "hn_clear_scene",
+    "hn_get_scene_aabb", "hn_set_option", "hn_get_option", "hn_render_frame", "hn_render_to_host", "hn_set_camera",
+    "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
+    "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace",
+]
+
+_lib.hn_last_error.restype = C.c_char_p
+_lib.hn_version.restype = C.c_char_p
+_lib.hn_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+_lib.hn_destroy.argtypes = [C.c_void_p]
+_lib.hn_last_error.argtypes = [C.c_void_p]
+_lib.hn_set_params.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+_lib.hn_set_occupancy_bitfield.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+_lib.hn_get_occupancy_bitfield.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+_lib.hn_add_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+_lib.hn_render_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_render_to_host.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+_lib.hn_pack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_unpack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
+_lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
+_lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_op_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_op_trace.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
+for _n in ("hn_load_network_config", "hn_load_network_config_string", "hn_load_scene"):
+    getattr(_lib, _n).argtypes = [C.c_void_p, C.c_char_p]
+_lib.hn_load_mesh_file.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+_lib.hn_set_aabb_scale.argtypes = [C.c_void_p, C.c_int]
+_lib.hn_get_network_info.argtypes = [C.c_void_p, C.POINTER(NetworkInfo)]
+_lib.hn_set_density_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+_lib.hn_build_scene.argtypes = [C.c_void_p]
+_lib.hn_clear_scene.argtypes = [C.c_void_p]
+_lib.hn_get_scene_aabb.argtypes = [C.c_void_p, C.c_void_p]
+_lib.hn_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int]
+_lib.hn_get_option.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int]
+_lib.hn_set_camera.argtypes = [C.c_void_p, C.c_void_p]
+_lib.hn_set_tile_shard.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+_lib.hn_tile_count.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u32p]
+_lib.hn_get_frame_stats.argtypes = [C.c_void_p, C.POINTER(FrameStats)]
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def camera_to_cols(m):
+    """3x4 row-major camera-to-world matrix (pyngp's set_nerf_camera_matrix argument) -> the ABI's 4 columns x vec3."""
+    m = np.asarray(m, dtype=np.float32).reshape(3, 4)
+    return np.ascontiguousarray(m.T).reshape(12)
+
+
+class Testbed:
+    """Render-path subset of ``pyngp.Testbed``."""
+
+    def __init__(self, mode: str = "nerf", device: int = 0):
+        self._h = C.c_void_p()
+        rc = _lib.hn_create(C.byref(self._h), int(device))
+        if rc != 0:
+            msg = _lib.hn_last_error(self._h).decode() if self._h else "hn_create failed"
+            if self._h:
+                _lib.hn_destroy(self._h)
+                self._h = C.c_void_p()
+            raise RuntimeError(msg)
+        self.mode = mode
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.hn_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(_lib.hn_last_error(self._h).decode())
+
+    # ---- network / scene (python_api.cu:429-441)
+    def reload_network_from_file(self, path: str):
+        self._check(_lib.hn_load_network_config(self._h, os.fsencode(path)))
+
+    def reload_network_from_json(self, text: str):
+        self._check(_lib.hn_load_network_config_string(self._h, text.encode()))
+
+    def set_aabb_scale(self, s: int):
+        self._check(_lib.hn_set_aabb_scale(self._h, int(s)))
+
+    def network_info(self) -> NetworkInfo:
+        info = NetworkInfo()
+        self._check(_lib.hn_get_network_info(self._h, C.byref(info)))
+        return info
+
+    def set_params(self, blob: np.ndarray):
+        blob = np.ascontiguousarray(blob)
+        if blob.dtype == np.float16:
+            dt = 0
+        elif blob.dtype == np.float32:
+            dt = 1
+        else:
+            raise TypeError("params must be float16 or float32")
+        self._check(_lib.hn_set_params(self._h, _ptr(blob), blob.size, dt))
+
+    def set_density_grid(self, grid: np.ndarray, n_cascades: int = 1):
+        g = _f32(grid)
+        assert g.size == 128 ** 3 * n_cascades
+        self._check(_lib.hn_set_density_grid(self._h, _ptr(g), n_cascades))
+
+    def set_occupancy_bitfield(self, bits: np.ndarray):
+        b = np.ascontiguousarray(bits, dtype=np.uint8)
+        self._check(_lib.hn_set_occupancy_bitfield(self._h, _ptr(b), b.size))
+
+    def get_occupancy_bitfield(self) -> np.ndarray:
+        out = np.zeros(128 ** 3 // 8 * 8, dtype=np.uint8)
+        self._check(_lib.hn_get_occupancy_bitfield(self._h, _ptr(out), out.size))
+        return out
+
+    def load_file(self, path: str):
+        """Scene json (Geometry mode) or mesh file, like Testbed::load_file (src/testbed.cu:319-389)."""
+        if path.endswith(".json"):
+            self._check(_lib.hn_load_scene(self._h, os.fsencode(path)))
+        else:
+            c = _f32([0, 0, 0])
+            self._check(_lib.hn_load_mesh_file(self._h, os.fsencode(path), _ptr(c)))
+            self.build_scene()
+
+    load_training_data = load_file
+
+    def add_mesh(self, triangles: np.ndarray, center=(0.0, 0.0, 0.0), normalize: bool = False):
+        t = _f32(triangles).reshape(-1, 9)
+        c = _f32(center)
+        self._check(_lib.hn_add_mesh(self._h, _ptr(t), t.shape[0], _ptr(c), int(normalize)))
+
+    def build_scene(self):
+        self._check(_lib.hn_build_scene(self._h))
+
+    def clear_scene(self):
+        self._check(_lib.hn_clear_scene(self._h))
+
+    def scene_aabb(self) -> np.ndarray:
+        out = np.zeros(6, dtype=np.float32)
+        self._check(_lib.hn_get_scene_aabb(self._h, _ptr(out)))
+        return out
+
+    # ---- options
+    def set_option(self, name: str, value):
+        v = _f32(np.atleast_1d(value))
+        self._check(_lib.hn_set_option(self._h, name.encode(), _ptr(v), v.size))
+
+    def get_option(self, name: str, n: int = 1):
+        v = np.zeros(n, dtype=np.float32)
+        self._check(_lib.hn_get_option(self._h, name.encode(), _ptr(v), n))
+        return v if n > 1 else float(v[0])
+
+    @property
+    def fov(self) -> float:  # python_api.cu: fov in degrees on fov_axis
+        f = self.get_option("relative_focal_length", 2)[int(self.get_option("fov_axis"))]
+        return 2.0 * 180.0 / math.pi * math.atan(1.0 / (2.0 * f))
+
+    @fov.setter
+    def fov(self, deg: float):
+        f = 0.5 / math.tan(0.5 * deg * math.pi / 180.0)
+        self.set_option("relative_focal_length", [f, f])
+
+    snap_to_pixel_centers = property(lambda s: bool(s.get_option("snap_to_pixel_centers")), lambda s, v: s.set_option("snap_to_pixel_centers", float(v)))
+    exposure = property(lambda s: s.get_option("exposure"), lambda s, v: s.set_option("exposure", v))
+    sun_dir = property(lambda s: s.get_option("sun_dir", 3), lambda s, v: s.set_option("sun_dir", v))
+    up_dir = property(lambda s: s.get_option("up_dir", 3), lambda s, v: s.set_option("up_dir", v))
+    background_color = property(lambda s: s.get_option("background_color", 4), lambda s, v: s.set_option("background_color", v))
+
+    def set_nerf_camera_matrix(self, m):
+        c = camera_to_cols(m)
+        self._check(_lib.hn_set_camera(self._h, _ptr(c)))
+
+    def set_camera_cols(self, cols12):
+        c = _f32(cols12).reshape(12)
+        self._check(_lib.hn_set_camera(self._h, _ptr(c)))
+
+    def set_tile_shard(self, rank: int, world: int, tile_w: int = 64, tile_h: int = 32):
+        self._check(_lib.hn_set_tile_shard(self._h, rank, world, tile_w, tile_h))
+
+    # ---- rendering
+    def render(self, width: int, height: int, spp: int = 1, linear: bool = True, return_depth: bool = False):
+        """pyngp.Testbed.render(width, height, spp, linear) -> float32 [h, w, 4] (python_api.cu:417-426)."""
+        out = np.empty((height, width, 4), dtype=np.float32)
+        depth = np.empty((height, width), dtype=np.float32) if return_depth else None
+        self._check(_lib.hn_render_to_host(self._h, width, height, spp, int(linear), _ptr(out), _ptr(depth) if return_depth else None))
+        return (out, depth) if return_depth else out
+
+    def render_frame(self, cam0, cam1, width, height, frame_ptr: int, depth_ptr: int, spp_index: int = 0, stream: int = 0,
+                     screen_center=(0.5, 0.5), relative_focal_length=None, rolling_shutter=(0.0, 0.0, 0.0, 1.0)):
+        """Testbed::render_frame into caller-owned DEVICE buffers (raw pointers, e.g. torch.Tensor.data_ptr())."""
+        c0, c1 = _f32(cam0).reshape(12), _f32(cam1).reshape(12)
+        sc = _f32(screen_center)
+        rf = _f32(relative_focal_length if relative_focal_length is not None else self.get_option("relative_focal_length", 2))
+        rs = _f32(rolling_shutter)
+        self._check(_lib.hn_render_frame(self._h, _ptr(c0), _ptr(c1), _ptr(sc), _ptr(rf), _ptr(rs), spp_index, width, height,
+                                         C.c_void_p(frame_ptr), C.c_void_p(depth_ptr), C.c_void_p(stream)))
+
+    def frame_stats(self) -> FrameStats:
+        s = FrameStats()
+        self._check(_lib.hn_get_frame_stats(self._h, C.byref(s)))
+        return s
+
+    def tile_count(self, width, height, rank, world) -> int:
+        n = C.c_uint32()
+        self._check(_lib.hn_tile_count(self._h, width, height, rank, world, C.byref(n)))
+        return n.value
+
+    def pack_tiles(self, width, height, rank, world, frame_ptr, depth_ptr, packed_ptr, stream=0):
+        self._check(_lib.hn_pack_tiles(self._h, width, height, rank, world, C.c_void_p(frame_ptr), C.c_void_p(depth_ptr), C.c_void_p(packed_ptr), C.c_void_p(stream)))
+
+    def unpack_tiles(self, width, height, rank, world, packed_ptr, frame_ptr, depth_ptr, stream=0):
+        self._check(_lib.hn_unpack_tiles(self._h, width, height, rank, world, C.c_void_p(packed_ptr), C.c_void_p(frame_ptr), C.c_void_p(depth_ptr), C.c_void_p(stream)))
+
+    # ---- operator-level entry points (parity tests)
+    def op_init_rays(self, cam0, cam1, width, height, spp_index=0, screen_center=(0.5, 0.5), relative_focal_length=None, rolling_shutter=(0, 0, 0, 1)):
+        n = width * height
+        o = np.empty((n, 3), np.float32); d = np.empty((n, 3), np.float32); t = np.empty(n, np.float32); alive = np.empty(n, np.uint8)
+        c0, c1 = _f32(cam0).reshape(12), _f32(cam1).reshape(12)
+        sc = _f32(screen_center)
+        rf = _f32(relative_focal_length if relative_focal_length is not None else self.get_option("relative_focal_length", 2))
+        rs = _f32(rolling_shutter)
+        self._check(_lib.hn_op_init_rays(self._h, _ptr(c0), _ptr(c1), _ptr(sc), _ptr(rf), _ptr(rs), spp_index, width, height, _ptr(o), _ptr(d), _ptr(t), _ptr(alive)))
+        return o, d, t, alive
+
+    def op_march_all(self, origins, dirs, t0, alive, max_per_ray=0):
+        o, d, t = _f32(origins), _f32(dirs), _f32(t0)
+        a = np.ascontiguousarray(alive, dtype=np.uint8)
+        n = t.size
+        counts = np.empty(n, np.uint32)
+        samples = np.empty((n, max_per_ray, 4), np.float32) if max_per_ray else None
+        self._check(_lib.hn_op_march_all(self._h, n, _ptr(o), _ptr(d), _ptr(t), _ptr(a), _ptr(counts), _ptr(samples) if max_per_ray else None, max_per_ray))
+        return counts, samples
+
+    def op_encode(self, positions):
+        p = _f32(positions).reshape(-1, 3)
+        out = np.empty((p.shape[0], 32), np.float16)
+        self._check(_lib.hn_op_encode(self._h, _ptr(p), p.shape[0], _ptr(out)))
+        return out
+
+    def op_network(self, positions_dt, dirs):
+        p = _f32(positions_dt).reshape(-1, 4)
+        d = _f32(dirs).reshape(-1, 3)
+        assert p.shape[0] == d.shape[0] * 32
+        out = np.empty((p.shape[0], 4), np.float16)
+        self._check(_lib.hn_op_network(self._h, _ptr(p), _ptr(d), p.shape[0], _ptr(out)))
+        return out
+
+    def op_trace(self, origins, dirs):
+        o, d = _f32(origins).reshape(-1, 3), _f32(dirs).reshape(-1, 3)
+        n = o.shape[0]
+        mesh = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
+        self._check(_lib.hn_op_trace(self._h, n, _ptr(o), _ptr(d), _ptr(mesh), _ptr(tri), _ptr(t)))
+        return mesh, tri, t

@@ -1,0 +1,223 @@
+"""ctypes binding of the CPU oracle (oracle/liborc.so) and of the reference's own host functions (oracle/_ref/, when
+built). TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's cpu-baseline legs."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+LIB = os.path.join(ORACLE_DIR, "liborc.so")
+REF_LIB = os.path.join(ORACLE_DIR, "_ref", "libngp_ref_host.so")
+
+f32, u32, i32 = C.c_float, C.c_uint32, C.c_int32
+
+
+def _build():
+    subprocess.run(["make", "-C", ORACLE_DIR], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+
+
+if not os.path.exists(LIB):
+    _build()
+lib = C.CDLL(LIB)
+ref = C.CDLL(REF_LIB) if os.path.exists(REF_LIB) else None
+
+
+class NetConfig(C.Structure):
+    _fields_ = [("n_levels", u32), ("n_features_per_level", u32), ("log2_hashmap_size", u32), ("base_resolution", u32),
+                ("per_level_scale", f32), ("density_hidden_layers", u32), ("rgb_hidden_layers", u32)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("width", i32), ("height", i32), ("spp", u32), ("cam0", f32 * 12), ("cam1", f32 * 12), ("rolling_shutter", f32 * 4),
+                ("screen_center", f32 * 2), ("focal", f32 * 2), ("snap_to_pixel_centers", i32), ("near_distance", f32),
+                ("render_aabb", f32 * 6), ("train_aabb", f32 * 6), ("max_mip", u32), ("cone_angle_constant", f32),
+                ("min_transmittance", f32), ("rgb_activation", i32), ("density_activation", i32), ("linear_colors", i32),
+                ("dda_iter_cap", i32), ("mesh_aabb", f32 * 6), ("sun_dir", f32 * 3), ("up_dir", f32 * 3), ("floor_y", f32),
+                ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32)]
+
+
+def P(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+for name, res in (("orc_ld_random_val", f32), ("orc_triangle_ray_intersect", f32), ("orc_morton3D", u32), ("orc_advance_to_occupied", f32),
+                  ("orc_calc_dt", f32), ("orc_srgb_to_linear", f32), ("orc_bitfield_from_grid", f32), ("orc_n_params", C.c_size_t),
+                  ("orc_grid_param_offset", C.c_size_t), ("orc_render_nerf", C.c_uint64), ("orc_render_frame", C.c_uint64),
+                  ("orc_scene_create", C.c_void_p)):
+    getattr(lib, name).restype = res
+lib.orc_scene_destroy.argtypes = [C.c_void_p]
+lib.orc_scene_add_mesh.argtypes = [C.c_void_p, C.c_void_p, u32, C.c_void_p]
+lib.orc_scene_build.argtypes = [C.c_void_p]
+lib.orc_scene_aabb.argtypes = [C.c_void_p, C.c_void_p]
+lib.orc_scene_trace.argtypes = [C.c_void_p, C.c_void_p, u32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, i32]
+lib.orc_render_mesh.argtypes = [C.c_void_p] * 4
+lib.orc_render_frame.argtypes = [C.c_void_p] * 8
+lib.orc_render_nerf.argtypes = [C.c_void_p] * 7 + [i32]
+lib.orc_init_rays.argtypes = [C.c_void_p] * 6
+lib.orc_march_all.argtypes = [C.c_void_p, C.c_void_p, u32] + [C.c_void_p] * 6 + [u32]
+lib.orc_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p]
+lib.orc_sh4.argtypes = [C.c_void_p, u32, C.c_void_p]
+lib.orc_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, u32, C.c_void_p]
+lib.orc_bitfield_from_grid.argtypes = [C.c_void_p, u32, C.c_void_p]
+lib.orc_n_params.argtypes = [C.c_void_p]
+lib.orc_grid_param_offset.argtypes = [C.c_void_p]
+lib.orc_grid_layout.argtypes = [C.c_void_p] * 4
+
+if ref is not None:
+    for name in ("ref_ld_random_val", "ref_triangle_ray_intersect", "ref_advance_to_occupied", "ref_calc_dt", "ref_advance_n_steps",
+                 "ref_srgb_to_linear", "ref_warp_dt", "ref_unwarp_dt", "ref_start_t"):
+        getattr(ref, name).restype = f32
+    ref.ref_morton3D.restype = u32
+
+DEFAULT_BRDF = [0.0, 0.0, 1.0, 0.5, 0.0, 0.0, 0.0, 0.8, 0.8, 0.8, 0.0, 0.0, 0.0, 0.0, 0.0]
+
+
+def net_config(n_levels=8, n_features=4, log2_T=19, base_res=16, per_level_scale=2.0, density_hidden=1, rgb_hidden=2) -> NetConfig:
+    return NetConfig(n_levels, n_features, log2_T, base_res, per_level_scale, density_hidden, rgb_hidden)
+
+
+def net_config_from_info(info) -> NetConfig:
+    """hn_network_info (product) -> oracle config, so both sides use the very same per_level_scale."""
+    return NetConfig(info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution, info.per_level_scale,
+                     info.density_hidden_layers, info.rgb_hidden_layers)
+
+
+def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom=1.0, screen_center=(0.5, 0.5), snap=True,
+                  render_aabb=(0, 0, 0, 1, 1, 1), train_aabb=(0, 0, 0, 1, 1, 1), max_mip=0, cone=0.0, min_transmittance=0.01,
+                  rgb_act=2, density_act=3, linear_colors=False, dda_iter_cap=0, mesh_aabb=(0, 0, 0, 1, 1, 1),
+                  sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
+                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None) -> RenderParams:
+    from math import tan, pi
+    p = RenderParams()
+    p.width, p.height, p.spp = w, h, spp
+    cam0 = np.asarray(cam0, dtype=np.float32).reshape(12)
+    cam1 = cam0 if cam1 is None else np.asarray(cam1, dtype=np.float32).reshape(12)
+    p.cam0[:] = cam0.tolist()
+    p.cam1[:] = cam1.tolist()
+    p.rolling_shutter[:] = list(rolling_shutter)
+    if rel_focal is None:
+        rel_focal = np.float32(0.5 / tan(0.5 * 50.625 * pi / 180.0))
+        rel_focal = (rel_focal, rel_focal)
+    res_axis = np.float32(w if fov_axis == 0 else h)
+    # same float32 arithmetic as calc_focal_length / render_screen_center
+    p.focal[:] = [float(np.float32(np.float32(np.float32(rel_focal[i]) * res_axis) * np.float32(zoom))) for i in range(2)]
+    p.screen_center[:] = [float(np.float32(np.float32(np.float32(0.5) - np.float32(screen_center[i])) * np.float32(zoom)) + np.float32(0.5)) for i in range(2)]
+    p.snap_to_pixel_centers = int(snap)
+    p.near_distance = near
+    p.render_aabb[:] = list(render_aabb)
+    p.train_aabb[:] = list(train_aabb)
+    p.max_mip, p.cone_angle_constant, p.min_transmittance = max_mip, cone, min_transmittance
+    p.rgb_activation, p.density_activation, p.linear_colors, p.dda_iter_cap = rgb_act, density_act, int(linear_colors), dda_iter_cap
+    p.mesh_aabb[:] = list(mesh_aabb)
+    p.sun_dir[:] = list(sun_dir)
+    p.up_dir[:] = list(up_dir)
+    p.floor_y = floor_y
+    p.brdf[:] = list(brdf) if brdf is not None else DEFAULT_BRDF
+    p.compat_nearest_aabb_only, p.depth_merge_clip = int(compat), int(clip)
+    p.n_threads = n_threads if n_threads is not None else (os.cpu_count() or 1)
+    return p
+
+
+class Scene:
+    def __init__(self, meshes):
+        self.h = C.c_void_p(lib.orc_scene_create())
+        self._keep = []
+        for t in meshes:
+            t = np.ascontiguousarray(t, dtype=np.float32).reshape(-1, 9)
+            c = np.zeros(3, np.float32)
+            self._keep.append(t)
+            lib.orc_scene_add_mesh(self.h, P(t), t.shape[0], P(c))
+        lib.orc_scene_build(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib.orc_scene_destroy(self.h)
+            self.h = None
+
+    def aabb(self):
+        out = np.zeros(6, np.float32)
+        lib.orc_scene_aabb(self.h, P(out))
+        return out
+
+    def trace(self, p: RenderParams, origins, dirs, brute=False):
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        n = o.shape[0]
+        mesh = np.empty(n, np.int32); tri = np.empty(n, np.int32); t = np.empty(n, np.float32)
+        lib.orc_scene_trace(self.h, C.byref(p), n, P(o), P(d), P(mesh), P(tri), P(t), int(brute))
+        return mesh, tri, t
+
+
+def bitfield_from_grid(grid, n_cascades=1):
+    g = np.ascontiguousarray(grid, np.float32)
+    out = np.zeros(128 ** 3 // 8 * 8, np.uint8)
+    thresh = lib.orc_bitfield_from_grid(P(g), n_cascades, P(out))
+    return out, thresh
+
+
+def init_rays(p: RenderParams, bits):
+    n = p.width * p.height
+    o = np.empty((n, 3), np.float32); d = np.empty((n, 3), np.float32); t = np.empty(n, np.float32); a = np.empty(n, np.uint8)
+    lib.orc_init_rays(C.byref(p), P(bits), P(o), P(d), P(t), P(a))
+    return o, d, t, a
+
+
+def march_all(p: RenderParams, bits, o, d, t0, alive, max_per_ray=0):
+    n = t0.size
+    counts = np.empty(n, np.uint32)
+    samples = np.zeros((n, max_per_ray, 4), np.float32) if max_per_ray else None
+    lib.orc_march_all(C.byref(p), P(bits), n, P(np.ascontiguousarray(o, np.float32)), P(np.ascontiguousarray(d, np.float32)),
+                      P(np.ascontiguousarray(t0, np.float32)), P(np.ascontiguousarray(alive, np.uint8)), P(counts),
+                      P(samples) if max_per_ray else None, max_per_ray)
+    return counts, samples
+
+
+def encode(cfg: NetConfig, params, positions):
+    pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+    out = np.empty((pos.shape[0], 32), np.float16)
+    lib.orc_encode(C.byref(cfg), P(params), P(pos), pos.shape[0], P(out))
+    return out
+
+
+def network(cfg: NetConfig, params, coords):
+    c = np.ascontiguousarray(coords, np.float32).reshape(-1, 7)
+    out = np.empty((c.shape[0], 4), np.float16)
+    lib.orc_network(C.byref(cfg), P(params), P(c), c.shape[0], P(out))
+    return out
+
+
+def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):
+    n = p.width * p.height
+    frame = np.zeros((p.height, p.width, 4), np.float32)
+    depth = np.zeros((p.height, p.width), np.float32)
+    steps = np.zeros(n, np.uint32)
+    total = lib.orc_render_frame(scene.h if scene is not None else None, C.byref(p), C.byref(cfg) if cfg is not None else None,
+                                 P(params) if params is not None else None, P(bits) if bits is not None else None, P(frame), P(depth), P(steps))
+    return frame, depth, steps.reshape(p.height, p.width), int(total)
+
+
+def render_reference_frame(tb, params, grid, n_cascades, meshes, cam, w, h, mesh_aabb=None, spp=0, compat=False, clip=False,
+                           n_threads=None, **kw):
+    """Oracle frame with the same settings as a product Testbed `tb` (network info, options) for parity checks.
+    Returns (frame, depth, n_steps) in the product's LINEAR accumulate space (spp = 1, no tonemap)."""
+    cfg = net_config_from_info(tb.network_info()) if params is not None else None
+    bits = bitfield_from_grid(grid, n_cascades)[0] if grid is not None else None
+    scene = Scene(meshes) if meshes else None
+    if mesh_aabb is None and scene is not None:
+        bb = scene.aabb()
+        mesh_aabb = np.concatenate([bb[:3] - np.float32(4.0), bb[3:] + np.float32(4.0)])
+    p = render_params(w, h, cam, spp=spp, snap=bool(tb.get_option("snap_to_pixel_centers")),
+                      render_aabb=tb.get_option("render_aabb", 6), train_aabb=tb.get_option("nerf_aabb", 6),
+                      max_mip=int(tb.get_option("max_cascade")), cone=tb.get_option("cone_angle_constant"),
+                      min_transmittance=tb.get_option("render_min_transmittance"), linear_colors=bool(tb.get_option("linear_colors")),
+                      mesh_aabb=mesh_aabb if mesh_aabb is not None else (0, 0, 0, 1, 1, 1), compat=compat, clip=clip, n_threads=n_threads, **kw)
+    frame, depth, steps, _ = render_frame(p, cfg, params, bits, scene)
+    # product epilogue for spp=1, linear: background (0,0,0,1) blend adds alpha only, then clamp
+    out = frame.copy()
+    out[..., 3] = out[..., 3] + (1.0 - out[..., 3]) * 1.0
+    out = np.clip(out, 0.0, 1.0)
+    return out, depth, steps

@@ -64,7 +64,7 @@ struct Options {
 	float exposure = 0.f;
 	float background_color[4] = {0, 0, 0, 1};
 	float fov_axis = 1;
-	float relative_focal_length[2] = {1.05729f, 1.05729f};
+	float relative_focal_length[2] = {1.057161212f, 1.057161212f}; // fov 50.625 deg on axis 1 (src/testbed.cu:541-568)
 	float screen_center[2] = {0.5f, 0.5f};
 	float zoom = 1.f;
 	int profile = 0;

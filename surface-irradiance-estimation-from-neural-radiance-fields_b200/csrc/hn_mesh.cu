@@ -99,6 +99,7 @@ __device__ void scene_nearest(const SceneDev& sc, int compat, V3 o, V3 d, Hit& h
 		if (mesh < 0) return;
 		touched = true;
 		traverse_mesh(sc, mesh, o, d, h, stack);
+		h.mesh = mesh; // the reference reports the chosen mesh even when no triangle of it is hit
 		return;
 	}
 	touched = true;
@@ -112,7 +113,6 @@ __global__ void __launch_bounds__(MESH_BLOCK) trace_kernel(SceneDev sc, int comp
 	if (i >= n) return;
 	Hit h; bool touched;
 	scene_nearest(sc, compat, ld3(o_in + 3 * i), ld3(d_in + 3 * i), h, touched, stack_s + threadIdx.x);
-	if (h.tri < 0) h.mesh = compat ? h.mesh : -1;
 	mesh_out[i] = h.mesh; tri_out[i] = h.tri; t_out[i] = h.t;
 }
 

@@ -211,6 +211,7 @@ def render_reference_frame(tb, params, grid, n_cascades, meshes, cam, w, h, mesh
         bb = scene.aabb()
         mesh_aabb = np.concatenate([bb[:3] - np.float32(4.0), bb[3:] + np.float32(4.0)])
     p = render_params(w, h, cam, spp=spp, snap=bool(tb.get_option("snap_to_pixel_centers")),
+                      rel_focal=tb.get_option("relative_focal_length", 2), fov_axis=int(tb.get_option("fov_axis")), zoom=tb.get_option("zoom"),
                       render_aabb=tb.get_option("render_aabb", 6), train_aabb=tb.get_option("nerf_aabb", 6),
                       max_mip=int(tb.get_option("max_cascade")), cone=tb.get_option("cone_angle_constant"),
                       min_transmittance=tb.get_option("render_min_transmittance"), linear_colors=bool(tb.get_option("linear_colors")),

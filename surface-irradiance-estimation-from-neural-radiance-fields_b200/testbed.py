@@ -238,9 +238,12 @@ class Testbed:
         self._check(_lib.hn_set_tile_shard(self._h, rank, world, tile_w, tile_h))
 
     # ---- rendering
-    def render(self, width: int, height: int, spp: int = 1, linear: bool = True, return_depth: bool = False):
-        """pyngp.Testbed.render(width, height, spp, linear) -> float32 [h, w, 4] (python_api.cu:417-426)."""
-        out = np.empty((height, width, 4), dtype=np.float32)
+    def render(self, width: int, height: int, spp: int = 1, linear: bool = True, return_depth: bool = False, out: np.ndarray | None = None):
+        """pyngp.Testbed.render(width, height, spp, linear) -> float32 [h, w, 4] (python_api.cu:417-426).
+        `out` may be a caller-owned (e.g. pinned) float32 [h, w, 4] array."""
+        if out is None:
+            out = np.empty((height, width, 4), dtype=np.float32)
+        assert out.dtype == np.float32 and out.size == height * width * 4 and out.flags["C_CONTIGUOUS"]
         depth = np.empty((height, width), dtype=np.float32) if return_depth else None
         self._check(_lib.hn_render_to_host(self._h, width, height, spp, int(linear), _ptr(out), _ptr(depth) if return_depth else None))
         return (out, depth) if return_depth else out

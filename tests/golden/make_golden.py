@@ -1,0 +1,170 @@
+#!/usr/bin/env python
+"""Generates the committed golden vectors under tests/golden/.
+
+  ref_host.npz   outputs of the REFERENCE's own NGP_HOST_DEVICE functions (compiled for the host from /root/reference by
+                 `make -C oracle ref` -> oracle/_ref/libngp_ref_host.so) on seeded inputs. Needs /root/reference, so it
+                 can only be produced in the authoring container; the tests read the .npz and never the reference.
+  oracle_pin.npz outputs of the CPU restatement (oracle/liborc.so) for the device-only kernels the reference cannot run on a
+                 host (hash grid, SH, MLP, compositing, shading, whole frames). The reference ships no vectors for them
+                 (SURVEY.md §4), so these pin the oracle against accidental change only ("parity unpinned" by the reference).
+
+Run: python tests/golden/make_golden.py   (after `python -c "import __graft_entry__ as g; g.build()"`)
+"""
+import ctypes as C
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import orc  # noqa: E402
+
+spec = importlib.util.spec_from_file_location("hn_synthetic", os.path.join(ROOT, "surface-irradiance-estimation-from-neural-radiance-fields_b200", "synthetic.py"))
+synthetic = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(synthetic)
+
+f32 = np.float32
+P = orc.P
+
+
+def fa(*v):
+    return (C.c_float * len(v))(*[float(x) for x in v])
+
+
+def make_ref_host():
+    ref = orc.ref
+    if ref is None:
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing: run `make -C oracle ref` where /root/reference is mounted")
+    rng = np.random.default_rng(20261104)
+    out = {}
+    # a-2 Sobol / Owen scrambling
+    idx = rng.integers(0, 2 ** 32, 256, dtype=np.uint64).astype(np.uint32)
+    seed = rng.integers(0, 2 ** 32, 256, dtype=np.uint64).astype(np.uint32)
+    idx[:8] = [0, 1, 2, 3, 4, 5, 6, 7]
+    out["ld_idx"], out["ld_seed"] = idx, seed
+    out["ld_val"] = np.array([ref.ref_ld_random_val(C.c_uint32(int(i)), C.c_uint32(int(s))) for i, s in zip(idx, seed)], f32)
+    po = np.zeros((32, 2), f32)
+    for spp in range(32):
+        tmp = (C.c_float * 2)()
+        ref.ref_ld_random_pixel_offset(C.c_uint32(spp), tmp)
+        po[spp] = tmp[:]
+    out["pixel_offset"] = po
+    # a-5 slab test, a-17 triangle test
+    n = 512
+    bb = np.concatenate([rng.uniform(-1, 0.4, (n, 3)), rng.uniform(0.6, 2, (n, 3))], 1).astype(f32)
+    o = rng.uniform(-2, 3, (n, 3)).astype(f32)
+    d = rng.normal(size=(n, 3)).astype(f32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(f32)
+    d[:4, 0] = 0.0  # axis-parallel rays: division by zero inside the slab test
+    tt = np.zeros((n, 2), f32)
+    for i in range(n):
+        tmp = (C.c_float * 2)()
+        ref.ref_bbox_ray_intersect(fa(*bb[i]), fa(*o[i]), fa(*d[i]), tmp)
+        tt[i] = tmp[:]
+    out["bb"], out["bb_o"], out["bb_d"], out["bb_t"] = bb, o, d, tt
+    tri = rng.uniform(0, 1, (n, 9)).astype(f32)
+    to = rng.uniform(-1, 2, (n, 3)).astype(f32)
+    tgt = (tri[:, 0:3] + tri[:, 3:6] + tri[:, 6:9]) / f32(3) + rng.normal(scale=0.15, size=(n, 3)).astype(f32)
+    td = (tgt - to).astype(f32)
+    td /= np.linalg.norm(td, axis=1, keepdims=True).astype(f32)
+    out["tri"], out["tri_o"], out["tri_d"] = tri, to, td
+    out["tri_t"] = np.array([ref.ref_triangle_ray_intersect(fa(*tri[i]), fa(*to[i]), fa(*td[i])) for i in range(n)], f32)
+    # morton, stepping, colour
+    xyz = rng.integers(0, 1024, (256, 3)).astype(np.uint32)
+    out["morton_xyz"] = xyz
+    out["morton"] = np.array([ref.ref_morton3D(C.c_uint32(int(a)), C.c_uint32(int(b)), C.c_uint32(int(c))) for a, b, c in xyz], np.uint32)
+    t = np.concatenate([rng.uniform(0, 4, 200), rng.uniform(0, 40, 56)]).astype(f32)
+    out["step_t"] = t
+    for cone, tag in ((0.0, "c0"), (1.0 / 256.0, "c256")):
+        out[f"calc_dt_{tag}"] = np.array([ref.ref_calc_dt(C.c_float(float(x)), C.c_float(cone)) for x in t], f32)
+        out[f"adv3_{tag}"] = np.array([ref.ref_advance_n_steps(C.c_float(float(x)), C.c_float(cone), C.c_float(2.5)) for x in t], f32)
+    s = rng.uniform(0, 1, 256).astype(f32)
+    out["srgb_in"] = s
+    out["srgb_lin"] = np.array([ref.ref_srgb_to_linear(C.c_float(float(x))) for x in s], f32)
+    dt = rng.uniform(0.0015, 0.2, 256).astype(f32)
+    out["dt_in"] = dt
+    out["dt_warp"] = np.array([ref.ref_warp_dt(C.c_float(float(x))) for x in dt], f32)
+    out["dt_unwarp"] = np.array([ref.ref_unwarp_dt(C.c_float(float(x))) for x in out["dt_warp"]], f32)
+    # a-3/a-4/a-6/a-7: pixel -> ray -> start t on the sphere occupancy (bitfield = a-20 on the synthetic grid)
+    grid = synthetic.sphere_density_grid(0.35)
+    bits, _ = orc.bitfield_from_grid(grid, 1)
+    w, h = 48, 40
+    cams = {"default": synthetic.default_camera(), "oblique": synthetic.look_at_camera((1.7, 1.2, 1.9), (0.5, 0.5, 0.5))}
+    aabb = fa(0, 0, 0, 1, 1, 1)
+    for name, cam in cams.items():
+        for spp, snap in ((0, 1), (3, 0)):
+            p = orc.render_params(w, h, cam, spp=spp, snap=bool(snap))
+            ro = np.zeros((h * w, 3), f32); rd = np.zeros((h * w, 3), f32); rt = np.zeros(h * w, f32)
+            for y in range(h):
+                for x in range(w):
+                    oo, dd = (C.c_float * 3)(), (C.c_float * 3)()
+                    ref.ref_pixel_ray(C.c_uint32(spp), C.c_uint32(x), C.c_uint32(y), w, h, p.focal, p.cam0, p.cam1, p.rolling_shutter,
+                                      p.screen_center, snap, C.c_float(0.0), oo, dd)
+                    i = x + w * y
+                    ro[i], rd[i] = oo[:], dd[:]
+                    rt[i] = ref.ref_start_t(C.c_uint32(spp), C.c_uint32(i), oo, dd, aabb, C.c_float(0.0), P(bits), C.c_uint32(0))
+            out[f"ray_o_{name}_{spp}"], out[f"ray_d_{name}_{spp}"], out[f"ray_t_{name}_{spp}"] = ro, rd, rt
+    # DDA from random interior starts, 3 cascades, both the unlimited and the 200-iteration (_geometry) variant
+    g3 = synthetic.sphere_density_grid(0.6, 3)
+    bits3, _ = orc.bitfield_from_grid(g3, 3)
+    n = 384
+    so = rng.uniform(-1.2, 2.2, (n, 3)).astype(f32)
+    sd = (f32(0.5) + rng.normal(scale=0.3, size=(n, 3)).astype(f32) - so).astype(f32)
+    sd /= np.linalg.norm(sd, axis=1, keepdims=True).astype(f32)
+    st = rng.uniform(0, 0.5, n).astype(f32)
+    box3 = fa(-1.5, -1.5, -1.5, 2.5, 2.5, 2.5)
+    out["dda_o"], out["dda_d"], out["dda_t0"] = so, sd, st
+    for cap in (0, 200):
+        for cone, tag in ((0.0, "c0"), (1.0 / 256.0, "c256")):
+            out[f"dda_t_{tag}_{cap}"] = np.array([ref.ref_advance_to_occupied(C.c_float(float(st[i])), C.c_float(cone), fa(*so[i]), fa(*sd[i]), P(bits3),
+                                                                             C.c_uint32(0), C.c_uint32(2), box3, cap) for i in range(n)], f32)
+    np.savez_compressed(os.path.join(HERE, "ref_host.npz"), **out)
+    print("ref_host.npz:", len(out), "arrays")
+
+
+class Info:
+    pass
+
+
+def base_info(cfg):
+    i = Info()
+    i.n_levels, i.n_features_per_level = cfg.n_levels, cfg.n_features_per_level
+    i.density_hidden_layers, i.rgb_hidden_layers = cfg.density_hidden_layers, cfg.rgb_hidden_layers
+    i.n_params = orc.lib.orc_n_params(C.byref(cfg))
+    i.grid_param_offset = orc.lib.orc_grid_param_offset(C.byref(cfg))
+    return i
+
+
+def make_oracle_pin():
+    rng = np.random.default_rng(7)
+    out = {}
+    cfg = orc.net_config(8, 4, 19, 16, float(np.exp(f32(np.log(f32(128.0)) / f32(7.0)))), 1, 2)
+    info = base_info(cfg)
+    params = synthetic.random_params(info, 1337, 1.0)
+    pos = rng.uniform(0, 1, (64, 3)).astype(f32)
+    pos[0] = [0, 0, 0]; pos[1] = [1, 1, 1]; pos[2] = [0.5, 0.5, 0.5]
+    out["enc_pos"] = pos
+    out["enc"] = orc.encode(cfg, params, pos)
+    coords = np.concatenate([pos, rng.uniform(0, 1, (64, 1)).astype(f32), rng.uniform(0, 1, (64, 3)).astype(f32)], 1)
+    out["net_coords"] = coords
+    out["net_out"] = orc.network(cfg, params, coords)
+    grid = synthetic.sphere_density_grid(0.35)
+    bits, thr = orc.bitfield_from_grid(grid, 1)
+    out["bits_sha_like"] = np.array([int(bits.astype(np.uint64).sum()), int((bits.astype(np.uint64) * (np.arange(bits.size) % 8191)).sum())], np.uint64)
+    out["bits_thresh"] = np.array([thr], f32)
+    tris = synthetic.torus_mesh(48, 24)
+    scene = orc.Scene([tris])
+    w, h = 40, 30
+    p = orc.render_params(w, h, synthetic.default_camera(), mesh_aabb=(-1, -1, -1, 2, 2, 2), n_threads=4)
+    frame, depth, steps, total = orc.render_frame(p, cfg, params, bits, scene)
+    out["frame"], out["depth"], out["steps"], out["total"] = frame, depth, steps, np.array([total], np.uint64)
+    np.savez_compressed(os.path.join(HERE, "oracle_pin.npz"), **out)
+    print("oracle_pin.npz:", len(out), "arrays")
+
+
+if __name__ == "__main__":
+    make_ref_host()
+    make_oracle_pin()

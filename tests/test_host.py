@@ -1,0 +1,160 @@
+"""CPU (-m "not gpu"): the C-ABI library loads and exports every symbol include/hybrid_nerf.h declares, the host logic
+behind it (JSON network configs with "parent" merge, grid offset table, scene JSON / OBJ loader, BVH build, options,
+tile arithmetic) behaves like the reference's, and every computing entry point FAILS LOUDLY without a GPU (no fallback)."""
+import ctypes as C
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+
+def _no_gpu():
+    try:
+        import torch
+        return not torch.cuda.is_available()
+    except Exception:
+        return True
+
+
+@pytest.fixture(scope="module")
+def raw(hn):
+    """(lib, ctx): a context whose hn_create failed for lack of a device keeps serving the host-only calls."""
+    from importlib import import_module
+    tbm = import_module(hn.__name__ + ".testbed")
+    lib = tbm._lib
+    h = C.c_void_p()
+    rc = lib.hn_create(C.byref(h), 0)
+    assert h.value, "hn_create must hand back a context even on failure so hn_last_error can explain"
+    yield lib, h, rc, tbm
+    lib.hn_destroy(h)
+
+
+def test_exports_match_header(hn, root):
+    text = open(os.path.join(root, "include", "hybrid_nerf.h")).read()
+    declared = sorted(set(re.findall(r"\b(hn_[a-z0-9_]+)\s*\(", text)))
+    assert len(declared) >= 30
+    lib = C.CDLL(hn.LIB_PATH)
+    missing = [s for s in declared if not hasattr(lib, s)]
+    assert not missing, f"libhn_b200.so does not export {missing}"
+    assert sorted(hn.EXPORTS) == declared
+    # every entry point cites the reference interface it replaces
+    assert text.count("testbed.h:") + text.count(".cu:") >= 10
+
+
+def test_no_cpu_fallback(hn, raw):
+    lib, h, rc, _ = raw
+    if not _no_gpu():
+        pytest.skip("a GPU is present")
+    assert rc != 0 and b"no CPU fallback" in lib.hn_last_error(h)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        hn.Testbed()
+
+
+def test_product_does_not_touch_oracle(root):
+    """The shipped path must not import, link or call anything under oracle/ (only tests/, smoke() and bench.py's CPU legs may)."""
+    pkg = os.path.join(root, "surface-irradiance-estimation-from-neural-radiance-fields_b200")
+    for dirpath, _, files in os.walk(pkg):
+        if "build" in dirpath.split(os.sep):
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", "Makefile")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "liborc" not in src and "orc_" not in src and "import orc" not in src, f"{f} references the oracle"
+    out = os.popen(f"ldd {os.path.join(pkg, 'libhn_b200.so')}").read()
+    assert "liborc" not in out
+
+
+def test_network_config_base_and_parent_merge(raw, root, tmp_path):
+    lib, h, _, tbm = raw
+    assert lib.hn_load_network_config(h, os.fsencode(os.path.join(root, "configs", "nerf", "base.json"))) == 0
+    info = tbm.NetworkInfo()
+    assert lib.hn_get_network_info(h, C.byref(info)) == 0
+    # L=8 F=4 T=2^19 N_min=16 b=2 -> resolutions 16..2048, 3 dense + 5 hashed levels, 2 920 448 entries
+    assert (info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution) == (8, 4, 19, 16)
+    assert [info.level_resolutions[i] for i in range(8)] == [16, 32, 64, 128, 256, 512, 1024, 2048]
+    assert [info.level_offsets[i + 1] - info.level_offsets[i] for i in range(8)] == [4096, 32768, 262144] + [524288] * 5
+    assert info.level_offsets[8] == 2920448
+    assert info.n_params == 2048 + 1024 + 2048 + 4096 + 1024 + 2920448 * 4 and info.grid_param_offset == 10240
+    assert abs(info.per_level_scale - 2.0) < 1e-6
+    # geometry/base.json: L=16 F=2 b=1.3819128, 6 098 120 entries, density MLP with 2 hidden layers
+    assert lib.hn_load_network_config(h, os.fsencode(os.path.join(root, "configs", "geometry", "base.json"))) == 0
+    assert lib.hn_get_network_info(h, C.byref(info)) == 0
+    assert (info.n_levels, info.n_features_per_level, info.density_hidden_layers, info.rgb_hidden_layers) == (16, 2, 2, 2)
+    assert abs(info.per_level_scale - 1.3819128) < 1e-6 and info.level_offsets[16] == 6098120
+    # "parent" merge (src/testbed.cu:86-97): the child overrides single keys of the parent
+    child = tmp_path / "child.json"
+    (tmp_path / "base.json").write_text(open(os.path.join(root, "configs", "nerf", "base.json")).read())
+    child.write_text(json.dumps({"parent": "base.json", "encoding": {"log2_hashmap_size": 18}}))  # resolved next to the child
+    rc = lib.hn_load_network_config(h, os.fsencode(str(child)))
+    assert rc == 0, lib.hn_last_error(h)
+    assert lib.hn_get_network_info(h, C.byref(info)) == 0
+    assert info.n_levels == 8 and info.n_features_per_level == 4 and info.log2_hashmap_size == 18
+    assert [info.level_offsets[i + 1] - info.level_offsets[i] for i in range(8)] == [4096, 32768] + [262144] * 6
+    # errors: status code + message, never an exception across the ABI
+    assert lib.hn_load_network_config(h, b"/nonexistent/x.json") != 0 and len(lib.hn_last_error(h)) > 0
+    assert lib.hn_load_network_config_string(h, b"{ not json") != 0
+    bad = json.dumps({"encoding": {"otype": "HashGrid", "n_levels": 8, "n_features_per_level": 3}})
+    assert lib.hn_load_network_config_string(h, bad.encode()) != 0
+
+
+def test_aabb_scale_drives_per_level_scale(raw, root):
+    lib, h, _, tbm = raw
+    assert lib.hn_load_network_config(h, os.fsencode(os.path.join(root, "configs", "nerf", "base.json"))) == 0
+    info = tbm.NetworkInfo()
+    assert lib.hn_set_aabb_scale(h, 4) == 0
+    lib.hn_get_network_info(h, C.byref(info))
+    # per_level_scale = exp(log(2048 * aabb_scale / base_res) / (L - 1)), src/testbed.cu:3958-3966
+    assert abs(info.per_level_scale - np.exp(np.log(2048 * 4 / 16) / 7)) < 1e-5
+    assert lib.hn_set_aabb_scale(h, 3) != 0
+    assert lib.hn_set_aabb_scale(h, 1) == 0
+
+
+def test_options_roundtrip_and_errors(raw):
+    lib, h, _, _ = raw
+    v = (C.c_float * 3)(0.0, 1.0, 0.0)
+    assert lib.hn_set_option(h, b"sun_dir", v, 3) == 0
+    out = (C.c_float * 3)()
+    assert lib.hn_get_option(h, b"sun_dir", out, 3) == 0 and list(out) == [0.0, 1.0, 0.0]
+    assert lib.hn_set_option(h, b"sun_dir", v, 2) != 0
+    assert lib.hn_set_option(h, b"no_such_option", v, 1) != 0 and b"no_such_option" in lib.hn_last_error(h)
+    assert lib.hn_set_tile_shard(h, 2, 2, 64, 32) != 0 and lib.hn_set_tile_shard(h, 1, 2, 64, 32) == 0
+    assert lib.hn_set_tile_shard(h, 0, 1, 64, 32) == 0
+
+
+def test_scene_json_and_obj_loader(raw, tmp_path):
+    """data/geometry/*.json format ({"geometry":[{"center","path","type"}]}) + OBJ with quads/negative indices; the upload
+    itself needs a device, so without one hn_build_scene must fail with a CUDA error, not crash."""
+    lib, h, _, _ = raw
+    obj = tmp_path / "quad.obj"
+    obj.write_text("# a unit quad and a triangle\nv 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv 0.5 0.5 1\nf 1 2 3 4\nf -1 -5 -4\n")
+    scene = tmp_path / "geometrypaths.json"
+    scene.write_text(json.dumps({"geometry": [{"center": [0.5, 0.5, 0.5], "path": str(obj), "type": "Mesh"}]}))
+    lib.hn_clear_scene(h)
+    rc = lib.hn_load_scene(h, os.fsencode(str(scene)))
+    if _no_gpu():
+        assert rc != 0 and (b"cuda" in lib.hn_last_error(h).lower() or b"device" in lib.hn_last_error(h).lower())
+    else:
+        assert rc == 0
+    bad = tmp_path / "bad.json"
+    bad.write_text(json.dumps({"geometry": [{"center": [0, 0, 0], "path": "/nonexistent.obj", "type": "Mesh"}]}))
+    assert lib.hn_load_scene(h, os.fsencode(str(bad))) != 0
+    lib.hn_clear_scene(h)
+
+
+def test_tile_arithmetic_matches_abi(hn, raw):
+    lib, h, _, _ = raw
+    from importlib import import_module
+    tiles = import_module(hn.__name__ + ".tiles")
+    for (w, hh, world) in [(1920, 1080, 1), (1920, 1080, 8), (3840, 2160, 4), (100, 70, 3), (64, 32, 2)]:
+        total = 0
+        for r in range(world):
+            n = C.c_uint32()
+            assert lib.hn_tile_count(h, w, hh, r, world, C.byref(n)) == 0
+            assert n.value == tiles.tile_count(w, hh, 64, 32, r, world)
+            total += n.value
+        tx, ty = tiles.tile_grid(w, hh, 64, 32)
+        assert total == tx * ty
+        own = tiles.owner_map(w, hh, 64, 32, world)
+        assert own.min() == 0 and own.max() == min(world, tx * ty) - 1

@@ -136,6 +136,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eval-impl", type=int, default=1, help="network kernel: 1 = tcgen05/TMEM (default), 0 = warp MMA")
     ap.add_argument("--clip", action="store_true", help="stop marching at the mesh depth instead of the reference's per-pixel test")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -166,6 +167,7 @@ def main():
     tb.snap_to_pixel_centers = True
     tb.set_option("depth_merge_clip", 1.0 if args.clip else 0.0)
     tb.set_camera_cols(cam)
+    tb.set_option("eval_impl", float(args.eval_impl))
     tile_w, tile_h = 64, 32
     tb.set_tile_shard(rank, world, tile_w, tile_h)
 

@@ -105,6 +105,14 @@ int hn_set_params(hn_context* ctx, const void* blob, size_t n_elements, int dtyp
 }
 
 // ---------------------------------------------------------------- occupancy
+static void refresh_occ_bounds(hn_context* ctx) {
+	DevBuf<int> d_b;
+	d_b.ensure(CASCADES * 6);
+	launch_occ_bounds(ctx->bitfield.p, d_b.p, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(ctx->occ_cells, d_b.p, sizeof(ctx->occ_cells), cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CUDA(cudaGetLastError());
+}
 int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades) {
 	HN_TRY(ctx)
 	need(n_cascades >= 1 && n_cascades <= CASCADES, "n_cascades must be in [1,8]");
@@ -123,6 +131,7 @@ int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades)
 	launch_grid_to_bitfield(d_grid.p, n_cascades, thresh, ctx->bitfield.p, ctx->stream);
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	HN_CUDA(cudaGetLastError());
+	refresh_occ_bounds(ctx);
 	ctx->has_bitfield = true;
 	HN_CATCH(ctx)
 }
@@ -131,6 +140,7 @@ int hn_set_occupancy_bitfield(hn_context* ctx, const uint8_t* bits, size_t n_byt
 	need(n_bytes == BITFIELD_BYTES, "bitfield must be 128^3/8*8 bytes");
 	HN_CUDA(cudaSetDevice(ctx->device));
 	HN_CUDA(cudaMemcpy(ctx->bitfield.p, bits, n_bytes, cudaMemcpyHostToDevice));
+	refresh_occ_bounds(ctx);
 	ctx->has_bitfield = true;
 	HN_CATCH(ctx)
 }
@@ -165,7 +175,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
 		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
 		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
-		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -242,6 +252,17 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	ld_random_pixel_offset(o.snap_to_pixel_centers ? 0 : spp, a.pixel_offset);
 	a.near_distance = o.near_distance;
 	std::memcpy(a.render_aabb, o.render_aabb, 24); std::memcpy(a.train_aabb, o.train_aabb, 24);
+	// world-space union of the set cells of mips 0..max_cascade, each inflated by half a cell of its mip
+	for (int k = 0; k < 3; ++k) { a.occ_aabb[k] = 1e30f; a.occ_aabb[3 + k] = -1e30f; }
+	for (int m = 0; m <= o.max_cascade && m < (int)CASCADES; ++m) {
+		const int* c = ctx->occ_cells + m * 6;
+		if (c[3] < c[0]) continue;
+		const float scale = std::ldexp(1.0f, m), pad = scale / 256.0f;
+		for (int k = 0; k < 3; ++k) {
+			a.occ_aabb[k] = std::min(a.occ_aabb[k], ((float)c[k] / 128.0f - 0.5f) * scale + 0.5f - pad);
+			a.occ_aabb[3 + k] = std::max(a.occ_aabb[3 + k], ((float)(c[3 + k] + 1) / 128.0f - 0.5f) * scale + 0.5f + pad);
+		}
+	}
 	a.max_mip = (uint32_t)o.max_cascade; a.cone_angle = o.cone_angle_constant; a.min_transmittance = o.min_transmittance;
 	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
 	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;
@@ -325,7 +346,7 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 			launch_march(a, ctx->bitfield.p, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, cnt, depth, n_alive, s);
 			tm.stop(st.ms_march);
 			tm.start();
-			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p, s);
+			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p, ctx->opt.eval_impl, s);
 			tm.stop(st.ms_eval);
 			tm.start();
 			launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
@@ -473,7 +494,7 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 	const float rs[4] = {0, 0, 0, 1};
 	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
 	RaySoA none = {};
-	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->stream);
+	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->opt.eval_impl, ctx->stream);
 	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	HN_CUDA(cudaGetLastError());

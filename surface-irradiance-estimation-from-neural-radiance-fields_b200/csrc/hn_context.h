@@ -68,6 +68,7 @@ struct Options {
 	float screen_center[2] = {0.5f, 0.5f};
 	float zoom = 1.f;
 	int profile = 0;
+	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int mesh_aabb_user = 0;
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
 };
@@ -91,6 +92,7 @@ struct hn_context {
 	// occupancy
 	hn::DevBuf<uint8_t> bitfield;
 	bool has_bitfield = false;
+	int occ_cells[hn::CASCADES * 6] = {};   // per-mip bounds of the set cells (cell coordinates), refreshed with the bitfield
 
 	// scene
 	std::vector<hn::HostMesh> meshes;

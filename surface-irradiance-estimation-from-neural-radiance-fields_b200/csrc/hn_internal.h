@@ -50,6 +50,7 @@ struct FrameArgs {
 	float pixel_offset[2]; // ld_random_pixel_offset(snap ? 0 : spp), computed on the host
 	float near_distance;
 	float render_aabb[6], train_aabb[6];
+	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
 	uint32_t max_mip;
 	float cone_angle;
 	float min_transmittance;
@@ -99,6 +100,7 @@ struct SceneDev {
 // exact TU (compiled with -fmad=false, no fast math): bit-exact against the oracle
 void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thresh, uint8_t* bits, cudaStream_t s);
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s);
+void launch_occ_bounds(const uint8_t* bits, int* out, cudaStream_t s);
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters,
 	float* depth_buffer, cudaStream_t s);
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s);
@@ -111,7 +113,7 @@ void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
-	uint32_t max_chunks, uint2* out, cudaStream_t s);
+	uint32_t max_chunks, uint2* out, int impl, cudaStream_t s); // impl: 0 = warp MMA (mma.sync), 1 = tcgen05/TMEM
 
 // composite TU
 void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in, const uint32_t* n_alive_ptr, uint32_t* alive_out,

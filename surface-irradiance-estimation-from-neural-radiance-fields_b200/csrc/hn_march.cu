@@ -179,17 +179,41 @@ __device__ __forceinline__ uint32_t mip_from_pos(V3 pos) {
 	return (uint32_t)min(max(exponent + 1, 0), (int)CASCADES - 1);
 }
 // nerf_device.cuh:461-495 (iter_cap == 0) / :497-534 (iter_cap == 200)
+// t_far: parameter beyond which the ray has left the (inflated) bounds of every set occupancy cell. No sample can follow, so
+// the reference's loop is bound to end in MAX_DEPTH there; returning it at once is exact and removes the cell-by-cell walk
+// through empty space to the edge of the render box.
 __device__ float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bits, uint32_t min_mip, uint32_t max_mip,
-	const Box& aabb, int iter_cap) {
+	const Box& aabb, int iter_cap, float t_far) {
 	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
 		V3 pos = o + t * d;
-		if (t >= MAX_DEPTH_F || !box_contains(aabb, pos)) return MAX_DEPTH_F;
+		if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) return MAX_DEPTH_F;
 		uint32_t mip = min(max(mip_from_pos(pos), min_mip), max_mip);
 		if (!bits || occupied_at(pos, bits, mip)) return t;
 		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
 		t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
 	}
 	return MAX_DEPTH_F;
+}
+
+// Far end of the ray inside the occupancy bounds (conservative: robust slab test on the inflated box, plus a margin).
+// A ray that misses the bounds gets -1: it can never meet a set cell.
+__device__ __forceinline__ float occ_t_far(const FrameArgs& a, const uint8_t* bits, V3 o, V3 d) {
+	if (!bits) return FLT_MAX;
+	float tmin = -FLT_MAX, tmax = FLT_MAX;
+	const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+	#pragma unroll
+	for (int k = 0; k < 3; ++k) {
+		const float lo = a.occ_aabb[k], hi = a.occ_aabb[3 + k];
+		if (dd[k] == 0.0f) {
+			if (oo[k] < lo || oo[k] > hi) return -1.0f;
+		} else {
+			const float t0 = (lo - oo[k]) / dd[k], t1 = (hi - oo[k]) / dd[k];
+			tmin = fmaxf(tmin, fminf(t0, t1));
+			tmax = fminf(tmax, fmaxf(t0, t1));
+		}
+	}
+	if (!(tmin <= tmax)) return -1.0f;
+	return tmax + 1e-3f;
 }
 
 // per-pixel start state: init_rays (:1478-1543) + advance_pos_nerf (:333-362). Returns alive.
@@ -202,7 +226,7 @@ __device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, 
 	if (!box_contains(aabb, o + t * d)) return false;
 	V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
 	t = advance_n_steps(t, a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
-	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0);
+	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, occ_t_far(a, bits, o, d));
 	if (t >= MAX_DEPTH_F) return false;
 	t_out = t;
 	return true;
@@ -264,37 +288,73 @@ __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const ui
 
 // generate_next_nerf_network_inputs (src/testbed_nerf.cu:430-477): up to CHUNK samples per live ray per pass.
 // Sample slot of list position p, step j = p*CHUNK + j (ray-major, so a warp of the network kernel owns one ray chunk).
+// The reference nests a data-dependent empty-space loop inside the per-sample loop; with one ray per lane that serialises
+// a warp on its slowest lane at every sample. Here both loops are flattened into ONE warp-converged loop: each trip a lane
+// either emits a sample (cell occupied) or skips to the next voxel, and the skip code is entered only when some lane of
+// the warp needs it (warp-uniform branch). Per-lane arithmetic and its order are unchanged -> bit-identical samples.
 __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, const uint32_t* __restrict__ alive_list,
 	const uint32_t* __restrict__ n_alive_ptr, float4* __restrict__ samples, uint32_t* __restrict__ sample_counts, uint32_t* __restrict__ counters,
 	const float* __restrict__ depth_buffer) {
-	uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-	uint32_t n_alive = *n_alive_ptr;
-	uint32_t count = 0;
-	if (p < n_alive) {
-		uint32_t r = alive_list[p];
-		float4 ot = rays.o_t[r];
-		float4 dm = rays.d_mw[r];
-		V3 o = {ot.x, ot.y, ot.z}, d = {dm.x, dm.y, dm.z};
-		V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-		Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
-		V3 tdiag = train.hi - train.lo;
-		V3 cam_fwd = ld3(a.cam1 + 6), cam_pos = ld3(a.cam1 + 9);
-		float clip = (a.depth_clip && a.depth_test) ? depth_buffer[rays.pixel[r]] : MAX_DEPTH_F;
-		float t = ot.w;
-		float4* dst = samples + (size_t)p * CHUNK;
-		for (uint32_t j = 0; j < CHUNK; ++j) {
-			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap);
-			if (t >= MAX_DEPTH_F) break;
-			float dt = calc_dt(t, a.cone_angle);
-			V3 pos = o + t * d;
-			if (a.depth_clip && a.depth_test) {
-				V3 up = train.lo + ((pos - train.lo) / tdiag) * tdiag;
-				if (dot3(cam_fwd, up - cam_pos) > clip) break;
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t n_alive = *n_alive_ptr;
+	const bool valid = p < n_alive;
+	bool active = valid;
+	uint32_t count = 0, r = 0;
+	int it = 1; // trip counter of the reference's inner loop (nerf_device.cuh:510: i < 200 in the _geometry variant)
+	V3 o = {0.f, 0.f, 0.f}, d = {0.f, 0.f, 1.f}, idir = {0.f, 0.f, 1.f};
+	float t = 0.f, t_far = -1.f, clip = MAX_DEPTH_F;
+	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
+	const V3 tdiag = train.hi - train.lo;
+	const V3 cam_fwd = ld3(a.cam1 + 6), cam_pos = ld3(a.cam1 + 9);
+	const bool clipping = a.depth_clip && a.depth_test;
+	if (valid) {
+		r = alive_list[p];
+		const float4 ot = rays.o_t[r], dm = rays.d_mw[r];
+		o = mk(ot.x, ot.y, ot.z); d = mk(dm.x, dm.y, dm.z); t = ot.w;
+		idir = mk(1.0f, 1.0f, 1.0f) / d;
+		t_far = occ_t_far(a, bits, o, d);
+		if (clipping) clip = depth_buffer[rays.pixel[r]];
+	}
+	float4* dst = samples + (size_t)p * CHUNK;
+	while (__any_sync(0xffffffffu, active)) {
+		bool skip = false;
+		uint32_t mip = 0;
+		V3 pos = o;
+		if (active) {
+			pos = o + t * d;
+			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) {
+				t = MAX_DEPTH_F; active = false;
+			} else {
+				mip = min(max(mip_from_pos(pos), 0u), a.max_mip);
+				if (!bits || occupied_at(pos, bits, mip)) {
+					const float dt = calc_dt(t, a.cone_angle);
+					bool emit = true;
+					if (clipping) {
+						const V3 up = train.lo + ((pos - train.lo) / tdiag) * tdiag;
+						if (dot3(cam_fwd, up - cam_pos) > clip) { emit = false; active = false; }
+					}
+					if (emit) {
+						dst[count] = make_float4(pos.x, pos.y, pos.z, dt);
+						++count;
+						t += dt;
+						it = 1;
+						if (count == CHUNK) active = false;
+					}
+				} else {
+					skip = true;
+				}
 			}
-			dst[j] = make_float4(pos.x, pos.y, pos.z, dt);
-			++count;
-			t += dt;
 		}
+		if (__any_sync(0xffffffffu, skip)) {
+			if (skip) {
+				while (mip < a.max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
+				t = advance_to_next_voxel(t, a.cone_angle, pos, d, idir, mip);
+				++it;
+				if (a.dda_iter_cap > 0 && it >= a.dda_iter_cap) { t = MAX_DEPTH_F; active = false; }
+			}
+		}
+	}
+	if (valid) {
 		rays.o_t[r].w = t;
 		sample_counts[p] = count;
 	}
@@ -315,8 +375,9 @@ __global__ void __launch_bounds__(128) march_all_kernel(FrameArgs a, const uint8
 		V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
 		Box aabb = ldbox(a.render_aabb);
 		float t = t0[i];
+		const float t_far = occ_t_far(a, bits, o, d);
 		while (true) {
-			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap);
+			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
 			if (t >= MAX_DEPTH_F) break;
 			float dt = calc_dt(t, a.cone_angle);
 			if (samples && c < max_per_ray) {
@@ -369,7 +430,32 @@ __global__ void grid_mean_kernel(const float* __restrict__ grid, double* __restr
 	if ((threadIdx.x & 31u) == 0) atomicAdd(sum, acc);
 }
 
+// per-mip bounds of the set cells in cell coordinates: out[mip] = {min x,y,z, max x,y,z} (min > max when the mip is empty)
+__global__ void occ_bounds_kernel(const uint8_t* __restrict__ bits, int* __restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // byte index over all mips
+	if (i >= BITFIELD_BYTES) return;
+	const uint32_t byte = bits[i];
+	if (!byte) return;
+	const uint32_t per_mip = GRID_CELLS / 8;
+	const uint32_t mip = i / per_mip, base = (i - mip * per_mip) * 8;
+	int lo[3] = {1 << 30, 1 << 30, 1 << 30}, hi[3] = {-1, -1, -1};
+	for (uint32_t b = 0; b < 8; ++b) {
+		if (!(byte & (1u << b))) continue;
+		const uint32_t idx = base + b;
+		const int c[3] = {(int)morton3D_invert(idx), (int)morton3D_invert(idx >> 1), (int)morton3D_invert(idx >> 2)};
+		for (int k = 0; k < 3; ++k) { lo[k] = min(lo[k], c[k]); hi[k] = max(hi[k], c[k]); }
+	}
+	for (int k = 0; k < 3; ++k) { atomicMin(out + mip * 6 + k, lo[k]); atomicMax(out + mip * 6 + 3 + k, hi[k]); }
+}
+
 // ---------------------------------------------------------------- launchers
+void launch_occ_bounds(const uint8_t* bits, int* out /* CASCADES x 6, device */, cudaStream_t s) {
+	int init[CASCADES * 6];
+	for (uint32_t m = 0; m < CASCADES; ++m) for (int k = 0; k < 3; ++k) { init[m * 6 + k] = 1 << 30; init[m * 6 + 3 + k] = -1; }
+	cudaMemcpyAsync(out, init, sizeof(init), cudaMemcpyHostToDevice, s);
+	cudaStreamSynchronize(s); // `init` lives on this stack frame
+	occ_bounds_kernel<<<(BITFIELD_BYTES + 255) / 256, 256, 0, s>>>(bits, out);
+}
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s) {
 	// mean_out is reinterpreted as a double accumulator (8 bytes, zeroed here)
 	cudaMemsetAsync(mean_out, 0, sizeof(double), s);

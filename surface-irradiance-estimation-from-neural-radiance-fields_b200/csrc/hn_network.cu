@@ -5,33 +5,11 @@
 // Arithmetic follows the reference (tcnn grid.h:48-212, common_device.h:340-366,651-718,842-854; fully_fused_mlp.cu):
 // corner weights rounded to fp16 and accumulated with fp16 FMAs (grid.h:162) -> the encoding is bit-identical to the oracle;
 // MLPs take fp16 inputs/weights, accumulate in fp32 on the tensor cores and store fp16 activations between layers.
-#include "hn_internal.h"
+#include "hn_network.cuh"
 #include <mma.h>
 
 namespace hn {
 
-struct EvalArgs {
-	GridLevels g;
-	const __half* table;
-	const __half* w_density;
-	const __half* w_rgb;
-	int density_hidden, rgb_hidden;
-	float train_lo[3], train_diag[3];
-	const float4* samples;          // [n_chunks][32] (x,y,z,dt) un-warped
-	const uint32_t* sample_counts;  // [n_chunks] valid samples per chunk (nullptr = all 32)
-	const uint32_t* alive_list;     // [n_chunks] ray id per chunk (nullptr with dirs_override)
-	const float4* d_mw;             // ray directions by ray id
-	const float* dirs_override;     // [n_chunks][3] (operator entry point)
-	const uint32_t* n_chunks_ptr;   // device-side chunk count (nullptr -> n_chunks)
-	uint32_t n_chunks;
-	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output
-};
-
-__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
-	__half2 h = __floats2half2_rn(a, b);
-	return *reinterpret_cast<uint32_t*>(&h);
-}
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
 	asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
@@ -40,58 +18,6 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 		: "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-// ---- hash grid: one sample, all levels. F = features per level (2 or 4), L = 32 / F levels -> 32 halfs in `enc`.
-template <int F>
-__device__ __forceinline__ void encode_sample(const GridLevels& g, const __half* __restrict__ table, float px, float py, float pz, uint32_t (&enc)[16]) {
-	constexpr int L = 32 / F;
-	#pragma unroll
-	for (int l = 0; l < L; ++l) {
-		const float scale = g.scale[l];
-		const uint32_t res = g.res[l], size = g.size[l];
-		const __half* __restrict__ lvl = table + (size_t)g.offset[l] * F;
-		// pos_fract (common_device.h:842-854)
-		float fx = fmaf(scale, px, 0.5f), fy = fmaf(scale, py, 0.5f), fz = fmaf(scale, pz, 0.5f);
-		float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
-		uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
-		fx -= flx; fy -= fly; fz -= flz;
-		float wx[2] = {__fsub_rn(1.0f, fx), fx}, wy[2] = {__fsub_rn(1.0f, fy), fy}, wz[2] = {__fsub_rn(1.0f, fz), fz};
-		const bool hashed = g.hashed[l] != 0;
-		// grid_index (common_device.h:690-707): dense x + y*R + z*R^2, or coherent prime hash; then % hashmap_size
-		uint32_t idx[8];
-		#pragma unroll
-		for (int c = 0; c < 8; ++c) {
-			uint32_t x = gx + (c & 1), y = gy + ((c >> 1) & 1), z = gz + ((c >> 2) & 1);
-			uint32_t i = hashed ? (x ^ (y * 2654435761u) ^ (z * 805459861u)) : (x + y * res + z * res * res);
-			idx[c] = i % size;
-		}
-		if (F == 4) {
-			uint2 v[8];
-			#pragma unroll
-			for (int c = 0; c < 8; ++c) v[c] = __ldg(reinterpret_cast<const uint2*>(lvl) + idx[c]);
-			__half2 a0 = __float2half2_rn(0.f), a1 = a0;
-			#pragma unroll
-			for (int c = 0; c < 8; ++c) {
-				float w = __fmul_rn(__fmul_rn(__fmul_rn(1.0f, wx[c & 1]), wy[(c >> 1) & 1]), wz[(c >> 2) & 1]);
-				__half2 w2 = __float2half2_rn(w);
-				a0 = __hfma2(w2, *reinterpret_cast<__half2*>(&v[c].x), a0);
-				a1 = __hfma2(w2, *reinterpret_cast<__half2*>(&v[c].y), a1);
-			}
-			enc[2 * l] = *reinterpret_cast<uint32_t*>(&a0);
-			enc[2 * l + 1] = *reinterpret_cast<uint32_t*>(&a1);
-		} else {
-			uint32_t v[8];
-			#pragma unroll
-			for (int c = 0; c < 8; ++c) v[c] = __ldg(reinterpret_cast<const uint32_t*>(lvl) + idx[c]);
-			__half2 a0 = __float2half2_rn(0.f);
-			#pragma unroll
-			for (int c = 0; c < 8; ++c) {
-				float w = __fmul_rn(__fmul_rn(__fmul_rn(1.0f, wx[c & 1]), wy[(c >> 1) & 1]), wz[(c >> 2) & 1]);
-				a0 = __hfma2(__float2half2_rn(w), *reinterpret_cast<__half2*>(&v[c]), a0);
-			}
-			enc[l] = *reinterpret_cast<uint32_t*>(&a0);
-		}
-	}
-}
 
 // operator entry point a-10: encoding only
 template <int F>
@@ -105,26 +31,6 @@ __global__ void __launch_bounds__(128) encode_kernel(GridLevels g, const __half*
 	for (int k = 0; k < 4; ++k) o[k] = make_uint4(enc[4 * k], enc[4 * k + 1], enc[4 * k + 2], enc[4 * k + 3]);
 }
 
-// ---- degree-4 real spherical harmonics (common_device.h:340-366), input = unit direction components
-__device__ __forceinline__ void sh4(float x, float y, float z, float (&o)[16]) {
-	float xy = x * y, xz = x * z, yz = y * z, x2 = x * x, y2 = y * y, z2 = z * z;
-	o[0] = 0.28209479177387814f;
-	o[1] = -0.48860251190291987f * y;
-	o[2] = 0.48860251190291987f * z;
-	o[3] = -0.48860251190291987f * x;
-	o[4] = 1.0925484305920792f * xy;
-	o[5] = -1.0925484305920792f * yz;
-	o[6] = 0.94617469575755997f * z2 - 0.31539156525251999f;
-	o[7] = -1.0925484305920792f * xz;
-	o[8] = 0.54627421529603959f * x2 - 0.54627421529603959f * y2;
-	o[9] = 0.59004358992664352f * y * (-3.0f * x2 + y2);
-	o[10] = 2.8906114426405538f * xy * z;
-	o[11] = 0.45704579946446572f * y * (1.0f - 5.0f * z2);
-	o[12] = 0.3731763325901154f * z * (5.0f * z2 - 3.0f);
-	o[13] = 0.45704579946446572f * x * (1.0f - 5.0f * z2);
-	o[14] = 1.4453057213202769f * z * (x2 - y2);
-	o[15] = 0.59004358992664352f * x * (-x2 + 3.0f * y2);
-}
 
 // ---- MLP on legacy-free warp MMA tiles: each warp owns 32 rows (2 m-tiles of 16); activations stay in registers.
 // Weights live in shared memory as [out][in] rows padded by 16 B (conflict-free ldmatrix); a row of W is one B column.
@@ -312,7 +218,7 @@ void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const f
 
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
-	uint32_t max_chunks, uint2* out, cudaStream_t s) {
+	uint32_t max_chunks, uint2* out, int impl, cudaStream_t s) {
 	if (!max_chunks) return;
 	EvalArgs a;
 	a.g = g;
@@ -323,6 +229,7 @@ void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, c
 	for (int i = 0; i < 3; ++i) { a.train_lo[i] = fa.train_aabb[i]; a.train_diag[i] = fa.train_aabb[3 + i] - fa.train_aabb[i]; }
 	a.samples = samples; a.sample_counts = sample_counts; a.alive_list = alive_list; a.d_mw = rays.d_mw;
 	a.dirs_override = dirs_override; a.n_chunks_ptr = n_chunks_ptr; a.n_chunks = max_chunks; a.out = out;
+	if (impl == 1) { launch_eval_tc(a, cfg.F, max_chunks, s); return; }
 	size_t smem = mlp_smem_bytes(a.density_hidden) + mlp_smem_bytes(a.rgb_hidden) + 4 * 32 * A_STRIDE;
 	static int sm_count = 0;
 	if (!sm_count) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); }

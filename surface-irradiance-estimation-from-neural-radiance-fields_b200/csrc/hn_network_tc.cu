@@ -1,0 +1,291 @@
+// (b)+(c) Fused network evaluation on the 5th-generation tensor cores (tcgen05 / TMEM), sm_100a only.
+//
+// One CTA = 128 threads = one tile of 128 samples (4 ray chunks of 32; thread t owns sample row t = TMEM lane t).
+//   gather   : thread t computes the 32 hash-grid features of its sample (tcnn grid.h:48-212 arithmetic, bit-identical to the
+//              oracle) and stores them as the A operand in shared memory in the UMMA canonical K-major layout
+//   layers   : ONE elected thread issues tcgen05.mma (M=128, N=64 or 16, K=16 per instruction, fp16 x fp16 -> fp32 in TMEM);
+//              completion arrives on an mbarrier via tcgen05.commit
+//   epilogue : each warp reads its 32 TMEM lanes with tcgen05.ld, applies ReLU, rounds to fp16 (tcnn stores fp16
+//              activations between layers, fully_fused_mlp.cu:47-129) and writes the next layer's A operand
+//   output   : (r,g,b,sigma) fp16, 8 B per sample, coalesced
+// All weights (<= 28 KB) stay resident in shared memory in the canonical B layout for the life of the (persistent) CTA;
+// the 64 B/sample features and every hidden activation never leave the SM. Several CTAs per SM overlap one tile's gather
+// (L1/L2 latency bound) with another tile's MMA/epilogue rounds.
+//
+// Shared-memory operand layout (no swizzle, K-major; CUTLASS cute/atom/mma_traits_sm100.hpp "LayoutType::INTERLEAVE"):
+//   a core matrix is 8 rows x 16 B, rows contiguous; here every 16-byte K-chunk c of the tile is one plane
+//   [c][row][8 halfs], so element (row, k) sits at c*(ROWS*16) + row*16 + (k%8)*2 with c = k/8. For one K=16 instruction
+//   the descriptor holds start = plane 2*kk, LBO (next K-chunk) = ROWS*16, SBO (next 8-row group) = 128.
+#include "hn_network.cuh"
+
+namespace hn {
+namespace tc {
+
+constexpr int TILE = 128;                 // rows per CTA tile = TMEM lanes
+constexpr uint32_t A_PLANE = TILE * 16;   // bytes of one K-chunk plane of the A operand
+constexpr uint32_t A_BYTES = 8 * A_PLANE; // K up to 64
+constexpr uint32_t TMEM_COLS = 64;        // fp32 accumulator 128 x 64
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+	uint32_t done;
+	do {
+		asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+			: "=r"(done) : "r"(bar), "r"(parity) : "memory");
+	} while (!done);
+}
+// ---- proxies / tcgen05 ordering
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+
+// ---- TMEM allocation (one warp, all lanes converged)
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+	asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(dst_smem), "r"(cols) : "memory");
+	asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+	asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(taddr), "r"(cols) : "memory");
+}
+
+// ---- descriptors (cute/arch/mma_sm100_desc.hpp: SmemDescriptor, InstrDescriptor)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+	return (uint64_t)((saddr >> 4) & 0x3FFFu)          // start address, bits [0,14)
+		| ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) // leading byte offset: next 16-byte K chunk
+		| ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) // stride byte offset: next 8-row group
+		| (1ull << 46);                                  // descriptor version 1 (Blackwell); swizzle none, base offset 0
+}
+__host__ __device__ constexpr uint32_t instr_desc(uint32_t M, uint32_t N) {
+	// c_format F32 (bits 4-5) | a,b format F16 (0) | a,b K-major (0) | N >> 3 (bits 17-22) | M >> 4 (bits 24-28)
+	return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+	asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+		:: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+	asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
+}
+
+// ---- TMEM -> registers: 32 lanes x 32 bit, N consecutive columns; thread t of warp w reads lane 32*(w%4)+t
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+		  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+		: "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[4]) {
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];\n"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
+}
+
+// fp32 pair -> packed fp16 pair (lo = a, hi = b), with ReLU fused into the conversion
+__device__ __forceinline__ uint32_t pack_relu(uint32_t a_bits, uint32_t b_bits) {
+	uint32_t d;
+	asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;\n" : "=r"(d) : "f"(__uint_as_float(b_bits)), "f"(__uint_as_float(a_bits)));
+	return d;
+}
+__device__ __forceinline__ uint32_t pack_plain(uint32_t a_bits, uint32_t b_bits) {
+	uint32_t d;
+	asm("cvt.rn.f16x2.f32 %0, %1, %2;\n" : "=r"(d) : "f"(__uint_as_float(b_bits)), "f"(__uint_as_float(a_bits)));
+	return d;
+}
+
+
+// ---- weights: global row-major [out][in] -> canonical B planes [k/8][out][8 halfs]
+__device__ __forceinline__ uint32_t stage_layer(const __half* __restrict__ w, int N, int K, uint8_t* dst) {
+	const int chunks = K / 8;
+	for (int i = threadIdx.x; i < N * chunks; i += blockDim.x) {
+		const int n = i / chunks, c = i - n * chunks;
+		*reinterpret_cast<uint4*>(dst + (size_t)c * N * 16 + n * 16) = __ldg(reinterpret_cast<const uint4*>(w + (size_t)n * K) + c);
+	}
+	return (uint32_t)(N * K * 2);
+}
+__host__ __device__ inline uint32_t mlp_bytes(int hidden) { return (64 * 32 + (hidden - 1) * 64 * 64 + 16 * 64) * 2; }
+
+// one layer = K/16 instructions into the same accumulator, then a commit that arrives on `bar` when they have all retired
+__device__ __forceinline__ void issue_layer(uint32_t d_tmem, uint32_t a_s, uint32_t w_s, int K, int N, uint32_t bar) {
+	const uint32_t idesc = instr_desc(TILE, (uint32_t)N);
+	const uint32_t w_plane = (uint32_t)N * 16u;
+	for (int kk = 0; kk < K / 16; ++kk) {
+		const uint64_t ad = smem_desc(a_s + (uint32_t)kk * 2u * A_PLANE, A_PLANE, 128u);
+		const uint64_t bd = smem_desc(w_s + (uint32_t)kk * 2u * w_plane, w_plane, 128u);
+		umma_f16(d_tmem, ad, bd, idesc, kk > 0 ? 1u : 0u);
+	}
+	umma_commit(bar);
+}
+
+// 64 fp32 accumulator columns of this thread's row -> ReLU -> fp16 -> the 8 K-chunks of the next A operand
+__device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) {
+	#pragma unroll
+	for (int h = 0; h < 2; ++h) {
+		uint32_t v0[16], v1[16];
+		tmem_ld16(t_row + h * 32, v0);
+		tmem_ld16(t_row + h * 32 + 16, v1);
+		tc_wait_ld();
+		uint4 c0 = make_uint4(pack_relu(v0[0], v0[1]), pack_relu(v0[2], v0[3]), pack_relu(v0[4], v0[5]), pack_relu(v0[6], v0[7]));
+		uint4 c1 = make_uint4(pack_relu(v0[8], v0[9]), pack_relu(v0[10], v0[11]), pack_relu(v0[12], v0[13]), pack_relu(v0[14], v0[15]));
+		uint4 c2 = make_uint4(pack_relu(v1[0], v1[1]), pack_relu(v1[2], v1[3]), pack_relu(v1[4], v1[5]), pack_relu(v1[6], v1[7]));
+		uint4 c3 = make_uint4(pack_relu(v1[8], v1[9]), pack_relu(v1[10], v1[11]), pack_relu(v1[12], v1[13]), pack_relu(v1[14], v1[15]));
+		*reinterpret_cast<uint4*>(a_row + (4 * h + 0) * A_PLANE) = c0;
+		*reinterpret_cast<uint4*>(a_row + (4 * h + 1) * A_PLANE) = c1;
+		*reinterpret_cast<uint4*>(a_row + (4 * h + 2) * A_PLANE) = c2;
+		*reinterpret_cast<uint4*>(a_row + (4 * h + 3) * A_PLANE) = c3;
+	}
+}
+
+template <int F>
+__global__ void __launch_bounds__(TILE) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
+	extern __shared__ __align__(1024) uint8_t smem[];
+	uint8_t* a_s = smem;                                  // A operand, 8 planes x 128 rows x 16 B
+	uint8_t* wd_s = a_s + A_BYTES;                        // density MLP weights
+	uint8_t* wr_s = wd_s + mlp_bytes(a.density_hidden);   // colour MLP weights
+	uint64_t* bar_p = reinterpret_cast<uint64_t*>(wr_s + mlp_bytes(a.rgb_hidden));
+	uint32_t* tmem_p = reinterpret_cast<uint32_t*>(bar_p + 1);
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+	// ---- one-time set-up: weights -> canonical B planes, mbarrier, TMEM columns
+	{
+		uint8_t* d = wd_s;
+		const __half* w = a.w_density;
+		d += stage_layer(w, 64, 32, d); w += 64 * 32;
+		for (int l = 1; l < a.density_hidden; ++l) { d += stage_layer(w, 64, 64, d); w += 64 * 64; }
+		stage_layer(w, 16, 64, d);
+		d = wr_s; w = a.w_rgb;
+		d += stage_layer(w, 64, 32, d); w += 64 * 32;
+		for (int l = 1; l < a.rgb_hidden; ++l) { d += stage_layer(w, 64, 64, d); w += 64 * 64; }
+		stage_layer(w, 16, 64, d);
+	}
+	const uint32_t bar = smem_addr(bar_p);
+	if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+	if (warp == 0) tmem_alloc(smem_addr(tmem_p), TMEM_COLS);
+	fence_proxy_async();   // the staged weights are read by the async proxy (tcgen05.mma)
+	tc_fence_before();
+	__syncthreads();
+	tc_fence_after();
+	const uint32_t tmem_base = *tmem_p;
+	const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16); // this warp's 32 lanes, column 0
+	const uint32_t a_addr = smem_addr(a_s), wd_addr = smem_addr(wd_s), wr_addr = smem_addr(wr_s);
+	uint8_t* a_row = a_s + tid * 16;
+	uint32_t phase = 0;
+
+	const uint32_t n_chunks = a.n_chunks_ptr ? min(*a.n_chunks_ptr, a.n_chunks) : a.n_chunks;
+	const uint32_t n_tiles = (n_chunks + 3) / 4;
+
+	// every thread of the CTA runs the same number of rounds per tile: barriers are CTA-uniform by construction
+	#define HN_ROUND(K, N, W_ADDR) do { \
+		fence_proxy_async(); tc_fence_before(); __syncthreads(); \
+		if (tid == 0) { tc_fence_after(); issue_layer(tmem_base, a_addr, (W_ADDR), (K), (N), bar); } \
+	} while (0)
+	#define HN_WAIT() do { mbar_wait(bar, phase); phase ^= 1u; tc_fence_after(); } while (0)
+
+	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+		const uint32_t chunk = tile * 4 + warp;
+		const uint32_t count = chunk < n_chunks ? (a.sample_counts ? a.sample_counts[chunk] : CHUNK) : 0u;
+		// ---- (b) gather: 32 features of this thread's sample -> A planes 0..3
+		{
+			uint32_t enc[16];
+			#pragma unroll
+			for (int k = 0; k < 16; ++k) enc[k] = 0u;
+			if ((uint32_t)lane < count) {
+				const float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
+				const float px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
+				const float py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
+				const float pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
+				encode_sample<F>(a.g, a.table, px, py, pz, enc);
+			}
+			#pragma unroll
+			for (int c = 0; c < 4; ++c)
+				*reinterpret_cast<uint4*>(a_row + c * A_PLANE) = make_uint4(enc[4 * c], enc[4 * c + 1], enc[4 * c + 2], enc[4 * c + 3]);
+		}
+		// ---- (c) density MLP
+		uint32_t w_addr = wd_addr;
+		HN_ROUND(32, 64, w_addr); w_addr += 64 * 32 * 2;
+		for (int l = 1; l < a.density_hidden; ++l) {
+			HN_WAIT(); hidden_epilogue(t_row, a_row);
+			HN_ROUND(64, 64, w_addr); w_addr += 64 * 64 * 2;
+		}
+		HN_WAIT(); hidden_epilogue(t_row, a_row);
+		HN_ROUND(64, 16, w_addr);
+		// ---- colour MLP input: [16 density outputs | 16 SH coefficients of the ray direction]
+		uint32_t sigma_bits;
+		{
+			float dx = 0.f, dy = 0.f, dz = 1.f;
+			if (chunk < n_chunks) {
+				if (a.dirs_override) { dx = a.dirs_override[3 * chunk]; dy = a.dirs_override[3 * chunk + 1]; dz = a.dirs_override[3 * chunk + 2]; }
+				else { const float4 d = __ldg(a.d_mw + a.alive_list[chunk]); dx = d.x; dy = d.y; dz = d.z; }
+			}
+			dx = __fmul_rn(__fadd_rn(dx, 1.0f), 0.5f) * 2.f - 1.f;
+			dy = __fmul_rn(__fadd_rn(dy, 1.0f), 0.5f) * 2.f - 1.f;
+			dz = __fmul_rn(__fadd_rn(dz, 1.0f), 0.5f) * 2.f - 1.f;
+			float sh[16];
+			sh4(dx, dy, dz, sh);
+			const uint4 s0 = make_uint4(pack_h2(sh[0], sh[1]), pack_h2(sh[2], sh[3]), pack_h2(sh[4], sh[5]), pack_h2(sh[6], sh[7]));
+			const uint4 s1 = make_uint4(pack_h2(sh[8], sh[9]), pack_h2(sh[10], sh[11]), pack_h2(sh[12], sh[13]), pack_h2(sh[14], sh[15]));
+			HN_WAIT();
+			uint32_t v[16];
+			tmem_ld16(t_row, v);
+			tc_wait_ld();
+			const uint4 d0 = make_uint4(pack_plain(v[0], v[1]), pack_plain(v[2], v[3]), pack_plain(v[4], v[5]), pack_plain(v[6], v[7]));
+			const uint4 d1 = make_uint4(pack_plain(v[8], v[9]), pack_plain(v[10], v[11]), pack_plain(v[12], v[13]), pack_plain(v[14], v[15]));
+			sigma_bits = d0.x & 0xFFFFu; // density channel 0 (extract_density, nerf_network.h:31-43)
+			*reinterpret_cast<uint4*>(a_row + 0 * A_PLANE) = d0;
+			*reinterpret_cast<uint4*>(a_row + 1 * A_PLANE) = d1;
+			*reinterpret_cast<uint4*>(a_row + 2 * A_PLANE) = s0;
+			*reinterpret_cast<uint4*>(a_row + 3 * A_PLANE) = s1;
+		}
+		w_addr = wr_addr;
+		HN_ROUND(32, 64, w_addr); w_addr += 64 * 32 * 2;
+		for (int l = 1; l < a.rgb_hidden; ++l) {
+			HN_WAIT(); hidden_epilogue(t_row, a_row);
+			HN_ROUND(64, 64, w_addr); w_addr += 64 * 64 * 2;
+		}
+		HN_WAIT(); hidden_epilogue(t_row, a_row);
+		HN_ROUND(64, 16, w_addr);
+		// ---- output (r,g | b,sigma), 8 B per sample
+		HN_WAIT();
+		{
+			uint32_t v[4];
+			tmem_ld4(t_row, v);
+			tc_wait_ld();
+			uint2 o;
+			o.x = pack_plain(v[0], v[1]);
+			o.y = (pack_plain(v[2], 0u) & 0xFFFFu) | (sigma_bits << 16);
+			if (chunk < n_chunks) a.out[(size_t)chunk * CHUNK + lane] = o;
+		}
+	}
+	#undef HN_ROUND
+	#undef HN_WAIT
+	tc_fence_before();
+	__syncthreads();
+	if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+} // namespace tc
+
+void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStream_t s) {
+	if (!max_chunks) return;
+	const size_t smem = tc::A_BYTES + tc::mlp_bytes(a.density_hidden) + tc::mlp_bytes(a.rgb_hidden) + 16;
+	static int sm_count = 0;
+	if (!sm_count) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); }
+	uint32_t tiles = (max_chunks + 3) / 4;
+	uint32_t persistent = (uint32_t)sm_count * 5u;
+	uint32_t blocks = tiles < persistent ? tiles : persistent;
+	if (F == 4) {
+		cudaFuncSetAttribute(tc::eval_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		tc::eval_tc_kernel<4><<<blocks, tc::TILE, smem, s>>>(a);
+	} else {
+		cudaFuncSetAttribute(tc::eval_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		tc::eval_tc_kernel<2><<<blocks, tc::TILE, smem, s>>>(a);
+	}
+}
+
+} // namespace hn

@@ -78,6 +78,7 @@ void finalize_network(hn_context* ctx) {
 		uint32_t stride = 1;
 		for (uint32_t dim = 0; dim < 3 && stride <= g.size[i]; ++dim) stride *= n.res[i];
 		g.hashed[i] = g.size[i] < stride ? 1u : 0u;
+		g.mask[i] = (g.size[i] & (g.size[i] - 1)) == 0 ? g.size[i] - 1 : 0u;
 	}
 	ctx->has_net = true;
 	ctx->has_params = false;

@@ -36,6 +36,7 @@ struct GridLevels {
 	uint32_t res[MAX_LEVELS];
 	float scale[MAX_LEVELS];
 	uint32_t hashed[MAX_LEVELS];   // 1 = coherent prime hash, 0 = dense index
+	uint32_t mask[MAX_LEVELS];     // size - 1 when the size is a power of two (index reduction by AND), else 0
 	uint32_t L;
 };
 

@@ -142,15 +142,21 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 	}
 }
 
-template <int F>
-__global__ void __launch_bounds__(TILE) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
+// G independent tile groups of 128 threads share one copy of the weights and one TMEM allocation (64 columns each); a
+// group synchronises on its own named barrier and its own mbarrier, so the groups of a CTA drift apart freely and one
+// group's gather overlaps the other groups' MMA rounds.
+__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
+
+template <int F, int G>
+__global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
-	uint8_t* a_s = smem;                                  // A operand, 8 planes x 128 rows x 16 B
-	uint8_t* wd_s = a_s + A_BYTES;                        // density MLP weights
+	const int grp = threadIdx.x >> 7;                     // tile group of this thread
+	const int tid = threadIdx.x & (TILE - 1), lane = tid & 31, warp = tid >> 5; // within the group; warp == CTA warp index % 4
+	uint8_t* a_s = smem + (size_t)grp * A_BYTES;          // this group's A operand, 8 planes x 128 rows x 16 B
+	uint8_t* wd_s = smem + (size_t)G * A_BYTES;           // density MLP weights
 	uint8_t* wr_s = wd_s + mlp_bytes(a.density_hidden);   // colour MLP weights
-	uint64_t* bar_p = reinterpret_cast<uint64_t*>(wr_s + mlp_bytes(a.rgb_hidden));
-	uint32_t* tmem_p = reinterpret_cast<uint32_t*>(bar_p + 1);
-	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	uint64_t* bar_p = reinterpret_cast<uint64_t*>(wr_s + mlp_bytes(a.rgb_hidden)) + grp;
+	uint32_t* tmem_p = reinterpret_cast<uint32_t*>(reinterpret_cast<uint64_t*>(wr_s + mlp_bytes(a.rgb_hidden)) + G);
 
 	// ---- one-time set-up: weights -> canonical B planes, mbarrier, TMEM columns
 	{
@@ -166,12 +172,12 @@ __global__ void __launch_bounds__(TILE) eval_tc_kernel(const __grid_constant__ E
 	}
 	const uint32_t bar = smem_addr(bar_p);
 	if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); }
-	if (warp == 0) tmem_alloc(smem_addr(tmem_p), TMEM_COLS);
+	if (threadIdx.x < 32) tmem_alloc(smem_addr(tmem_p), TMEM_COLS * G);
 	fence_proxy_async();   // the staged weights are read by the async proxy (tcgen05.mma)
 	tc_fence_before();
 	__syncthreads();
 	tc_fence_after();
-	const uint32_t tmem_base = *tmem_p;
+	const uint32_t tmem_base = *tmem_p + (uint32_t)grp * TMEM_COLS;
 	const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16); // this warp's 32 lanes, column 0
 	const uint32_t a_addr = smem_addr(a_s), wd_addr = smem_addr(wd_s), wr_addr = smem_addr(wr_s);
 	uint8_t* a_row = a_s + tid * 16;
@@ -182,12 +188,12 @@ __global__ void __launch_bounds__(TILE) eval_tc_kernel(const __grid_constant__ E
 
 	// every thread of the CTA runs the same number of rounds per tile: barriers are CTA-uniform by construction
 	#define HN_ROUND(K, N, W_ADDR) do { \
-		fence_proxy_async(); tc_fence_before(); __syncthreads(); \
+		fence_proxy_async(); tc_fence_before(); group_sync(grp); \
 		if (tid == 0) { tc_fence_after(); issue_layer(tmem_base, a_addr, (W_ADDR), (K), (N), bar); } \
 	} while (0)
 	#define HN_WAIT() do { mbar_wait(bar, phase); phase ^= 1u; tc_fence_after(); } while (0)
 
-	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+	for (uint32_t tile = blockIdx.x * G + grp; tile < n_tiles; tile += gridDim.x * G) {
 		const uint32_t chunk = tile * 4 + warp;
 		const uint32_t count = chunk < n_chunks ? (a.sample_counts ? a.sample_counts[chunk] : CHUNK) : 0u;
 		// ---- (b) gather: 32 features of this thread's sample -> A planes 0..3
@@ -266,25 +272,27 @@ __global__ void __launch_bounds__(TILE) eval_tc_kernel(const __grid_constant__ E
 	#undef HN_WAIT
 	tc_fence_before();
 	__syncthreads();
-	if (warp == 0) tmem_dealloc(tmem_base, TMEM_COLS);
+	if (threadIdx.x < 32) tmem_dealloc(*tmem_p, TMEM_COLS * G);
 }
 
 } // namespace tc
 
 void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStream_t s) {
 	if (!max_chunks) return;
-	const size_t smem = tc::A_BYTES + tc::mlp_bytes(a.density_hidden) + tc::mlp_bytes(a.rgb_hidden) + 16;
+	constexpr int G = 4; // tile groups per CTA: 512 threads, 2 CTAs per SM = 8 tiles (32 warps) in flight per SM
+	const size_t smem = (size_t)G * tc::A_BYTES + tc::mlp_bytes(a.density_hidden) + tc::mlp_bytes(a.rgb_hidden) + 8 * G + 16;
 	static int sm_count = 0;
 	if (!sm_count) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); }
 	uint32_t tiles = (max_chunks + 3) / 4;
-	uint32_t persistent = (uint32_t)sm_count * 5u;
-	uint32_t blocks = tiles < persistent ? tiles : persistent;
+	uint32_t ctas = (tiles + G - 1) / G;
+	uint32_t persistent = (uint32_t)sm_count * 2u;
+	uint32_t blocks = ctas < persistent ? ctas : persistent;
 	if (F == 4) {
-		cudaFuncSetAttribute(tc::eval_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		tc::eval_tc_kernel<4><<<blocks, tc::TILE, smem, s>>>(a);
+		cudaFuncSetAttribute(tc::eval_tc_kernel<4, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		tc::eval_tc_kernel<4, G><<<blocks, tc::TILE * G, smem, s>>>(a);
 	} else {
-		cudaFuncSetAttribute(tc::eval_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		tc::eval_tc_kernel<2><<<blocks, tc::TILE, smem, s>>>(a);
+		cudaFuncSetAttribute(tc::eval_tc_kernel<2, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		tc::eval_tc_kernel<2, G><<<blocks, tc::TILE * G, smem, s>>>(a);
 	}
 }
 

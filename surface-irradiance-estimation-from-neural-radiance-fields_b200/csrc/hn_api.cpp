@@ -175,7 +175,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
 		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
 		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
-		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -346,10 +346,14 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 			launch_march(a, ctx->bitfield.p, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, cnt, depth, n_alive, s);
 			tm.stop(st.ms_march);
 			tm.start();
-			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p, ctx->opt.eval_impl, s);
+			const bool fused = ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite;
+			if (fused) ctx->survive.ensure(n_alive);
+			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p,
+				ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s);
 			tm.stop(st.ms_eval);
 			tm.start();
-			launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
+			if (fused) launch_compact(lists[cur], n_alive_ptr, ctx->survive.p, lists[cur ^ 1], n_next_ptr, n_alive, s);
+			else launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
 			tm.stop(st.ms_composite);
 			st.n_kernel_launches += 3;
 			st.n_passes += 1;
@@ -494,7 +498,7 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 	const float rs[4] = {0, 0, 0, 1};
 	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
 	RaySoA none = {};
-	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->opt.eval_impl, ctx->stream);
+	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->opt.eval_impl, nullptr, nullptr, nullptr, nullptr, ctx->stream);
 	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	HN_CUDA(cudaGetLastError());

@@ -5,30 +5,9 @@
 // next pass's list with ONE atomic per warp; rays that finish are blended straight into the frame buffer with the
 // mesh depth test (composite_kernel_nerf src/testbed_nerf.cu:528-735, compact_kernel_nerf :1403-1426,
 // shade_kernel_nerf_geometry src/testbed_geometry_training.cu:1826-1871).
-#include "hn_internal.h"
+#include "hn_shade.cuh"
 
 namespace hn {
-
-#define HN_MIN_STEP (1.73205080757f / 1024.0f)
-
-__device__ __forceinline__ float act_rgb(float v, int act) {
-	switch (act) {
-		case 1: return fmaxf(v, 0.0f);
-		case 2: return 1.0f / (1.0f + __expf(-v));
-		case 3: return __expf(fminf(fmaxf(v, -10.0f), 10.0f));
-		default: return v;
-	}
-}
-__device__ __forceinline__ float act_density(float v, int act) {
-	switch (act) {
-		case 1: return fmaxf(v, 0.0f);
-		case 2: return 1.0f / (1.0f + __expf(-v));
-		case 3: return __expf(v);
-		default: return v;
-	}
-}
-__device__ __forceinline__ float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
-__device__ __forceinline__ float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
 
 __global__ void __launch_bounds__(256) composite_kernel(FrameArgs a, RaySoA rays, const uint32_t* __restrict__ alive_in, const uint32_t* __restrict__ n_alive_ptr,
 	uint32_t* __restrict__ alive_out, uint32_t* __restrict__ n_alive_out, uint32_t* __restrict__ counters, const float4* __restrict__ samples,
@@ -208,6 +187,25 @@ __global__ void pack_tiles_kernel(int w, int h, int rank, int world, int tw, int
 			dst[0] = c.x; dst[1] = c.y; dst[2] = c.z; dst[3] = c.w; dst[4] = depth[pix];
 		}
 	}
+}
+
+// next pass's live-ray list from the survive flags of the fused network+composite kernel (one atomic per warp)
+__global__ void __launch_bounds__(256) compact_kernel(const uint32_t* __restrict__ alive_in, const uint32_t* __restrict__ n_alive_ptr,
+	const uint32_t* __restrict__ survive, uint32_t* __restrict__ alive_out, uint32_t* __restrict__ n_alive_out) {
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t lane = threadIdx.x & 31u;
+	const bool keep = p < *n_alive_ptr && survive[p] != 0u;
+	const uint32_t mask = __ballot_sync(0xffffffffu, keep);
+	if (!mask) return;
+	uint32_t base = 0;
+	const int leader = __ffs(mask) - 1;
+	if ((int)lane == leader) base = atomicAdd(n_alive_out, __popc(mask));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	if (keep) alive_out[base + __popc(mask & ((1u << lane) - 1u))] = alive_in[p];
+}
+void launch_compact(const uint32_t* alive_in, const uint32_t* n_alive_ptr, const uint32_t* survive, uint32_t* alive_out, uint32_t* n_alive_out, uint32_t max_rays, cudaStream_t s) {
+	if (!max_rays) return;
+	compact_kernel<<<(max_rays + 255) / 256, 256, 0, s>>>(alive_in, n_alive_ptr, survive, alive_out, n_alive_out);
 }
 
 void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in, const uint32_t* n_alive_ptr, uint32_t* alive_out,

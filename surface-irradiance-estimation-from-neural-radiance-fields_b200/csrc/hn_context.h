@@ -68,6 +68,7 @@ struct Options {
 	float screen_center[2] = {0.5f, 0.5f};
 	float zoom = 1.f;
 	int profile = 0;
+	int fuse_composite = 1;                     // composite inside the tcgen05 network kernel (eval_impl 1 only)
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int mesh_aabb_user = 0;
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
@@ -114,6 +115,7 @@ struct hn_context {
 	hn::DevBuf<uint32_t> ray_pixel, ray_nsteps, alive_a, alive_b, sample_counts, counters;
 	hn::DevBuf<float4> samples;
 	hn::DevBuf<uint2> net_out;
+	hn::DevBuf<uint32_t> survive;
 	uint32_t* pinned_counters = nullptr; // CNT_N uint32
 	// render_to_host buffers
 	hn::DevBuf<float4> frame, accum, tonemapped;

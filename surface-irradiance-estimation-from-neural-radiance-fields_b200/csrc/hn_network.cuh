@@ -18,7 +18,17 @@ struct EvalArgs {
 	const float* dirs_override;     // [n_chunks][3] (operator entry point)
 	const uint32_t* n_chunks_ptr;   // device-side chunk count (nullptr -> n_chunks)
 	uint32_t n_chunks;
-	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output
+	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output (unfused path)
+	// fused compositing (tcgen05 kernel only): the warp that evaluated a ray chunk also composites it
+	int fused;
+	float cam_fwd[3], cam_pos[3];
+	float min_transmittance;
+	int rgb_act, density_act, linear_colors, depth_test, depth_clip;
+	RaySoA rays;
+	float4* frame;
+	float* depth_buffer;
+	uint32_t* survive;              // [n_chunks] 1 = the ray continues into the next pass
+	uint32_t* counters;
 };
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {

@@ -2,6 +2,7 @@
 // scratch comes from a persistent workspace owned by the context (the reference re-allocates from tcnn's arena per frame).
 #include "hn_context.h"
 #include "hn_device_math.cuh"
+#include "hn_shade.cuh"
 #include <cmath>
 #include <cstring>
 #include <map>
@@ -175,7 +176,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
 		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
 		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
-		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -352,7 +353,13 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 				ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s);
 			tm.stop(st.ms_eval);
 			tm.start();
-			if (fused) launch_compact(lists[cur], n_alive_ptr, ctx->survive.p, lists[cur ^ 1], n_next_ptr, n_alive, s);
+			const bool per_ray = !fused && ctx->opt.composite_impl == 1;
+			if (per_ray) {
+				ctx->survive.ensure(n_alive);
+				launch_composite_rays(make_comp_args(a, rays, lists[cur], ctx->samples.p, frame, depth, ctx->survive.p, cnt), n_alive_ptr, ctx->sample_counts.p, ctx->net_out.p, n_alive, s);
+				st.n_kernel_launches += 1;
+			}
+			if (fused || per_ray) launch_compact(lists[cur], n_alive_ptr, ctx->survive.p, lists[cur ^ 1], n_next_ptr, n_alive, s);
 			else launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
 			tm.stop(st.ms_composite);
 			st.n_kernel_launches += 3;

@@ -189,6 +189,46 @@ __global__ void pack_tiles_kernel(int w, int h, int rank, int world, int tw, int
 	}
 }
 
+CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_list, const float4* samples, float4* frame, float* depth_buffer,
+	uint32_t* survive, uint32_t* counters) {
+	CompArgs c;
+	c.alive_list = alive_list; c.samples = samples;
+	for (int i = 0; i < 3; ++i) {
+		c.train_lo[i] = fa.train_aabb[i]; c.train_diag[i] = fa.train_aabb[3 + i] - fa.train_aabb[i];
+		c.cam_fwd[i] = fa.cam1[6 + i]; c.cam_pos[i] = fa.cam1[9 + i];
+	}
+	c.min_transmittance = fa.min_transmittance; c.rgb_act = fa.rgb_act; c.density_act = fa.density_act; c.linear_colors = fa.linear_colors;
+	c.depth_test = fa.depth_test; c.depth_clip = fa.depth_clip;
+	c.rays = rays; c.frame = frame; c.depth_buffer = depth_buffer; c.survive = survive; c.counters = counters;
+	return c;
+}
+
+// One warp per live ray (lane j = sample j of this pass's chunk): every load of the kernel is issued up front, so the
+// kernel runs at memory latency x waves instead of 32 dependent round trips per warp (composite_kernel above keeps 32 rays
+// per warp and is latency-bound by its serial ray loop). Survivors are flagged; compact_kernel builds the next list.
+__global__ void __launch_bounds__(512) composite_ray_kernel(const __grid_constant__ CompArgs a, const uint32_t* __restrict__ n_alive_ptr,
+	const uint32_t* __restrict__ sample_counts, const uint2* __restrict__ net_out) {
+	__shared__ uint32_t block_total;
+	if (threadIdx.x == 0) block_total = 0;
+	__syncthreads();
+	const uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (chunk < *n_alive_ptr) { // warp-uniform
+		const uint32_t count = sample_counts[chunk];
+		uint2 o = make_uint2(0u, 0u);
+		if ((uint32_t)lane < count) o = __ldg(net_out + (size_t)chunk * CHUNK + lane);
+		const RayPre pre = composite_prefetch(a, chunk, count, lane);
+		const uint32_t n = composite_chunk(a, pre, chunk, count, lane, o);
+		if (lane == 0 && n) atomicAdd(&block_total, n);
+	}
+	__syncthreads();
+	if (threadIdx.x == 0 && block_total) atomicAdd((unsigned long long*)&a.counters[CNT_COMPOSITED_LO], (unsigned long long)block_total);
+}
+void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const uint32_t* sample_counts, const uint2* net_out, uint32_t max_rays, cudaStream_t s) {
+	if (!max_rays) return;
+	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out);
+}
+
 // next pass's live-ray list from the survive flags of the fused network+composite kernel (one atomic per warp)
 __global__ void __launch_bounds__(256) compact_kernel(const uint32_t* __restrict__ alive_in, const uint32_t* __restrict__ n_alive_ptr,
 	const uint32_t* __restrict__ survive, uint32_t* __restrict__ alive_out, uint32_t* __restrict__ n_alive_out) {

@@ -68,7 +68,8 @@ struct Options {
 	float screen_center[2] = {0.5f, 0.5f};
 	float zoom = 1.f;
 	int profile = 0;
-	int fuse_composite = 1;                     // composite inside the tcgen05 network kernel (eval_impl 1 only)
+	int fuse_composite = 0;                     // 1 = composite inside the tcgen05 network kernel (eval_impl 1 only; measured slower, kept as an option)
+	int composite_impl = 1;                     // 1 = one warp per ray + compact kernel, 0 = 32 rays per warp with in-kernel compaction
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int mesh_aabb_user = 0;
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};

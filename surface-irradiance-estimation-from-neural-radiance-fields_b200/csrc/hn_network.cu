@@ -230,10 +230,7 @@ void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, c
 	a.samples = samples; a.sample_counts = sample_counts; a.alive_list = alive_list; a.d_mw = rays.d_mw;
 	a.dirs_override = dirs_override; a.n_chunks_ptr = n_chunks_ptr; a.n_chunks = max_chunks; a.out = out;
 	a.fused = (impl == 1 && fused_frame) ? 1 : 0;
-	for (int i = 0; i < 3; ++i) { a.cam_fwd[i] = fa.cam1[6 + i]; a.cam_pos[i] = fa.cam1[9 + i]; }
-	a.min_transmittance = fa.min_transmittance; a.rgb_act = fa.rgb_act; a.density_act = fa.density_act; a.linear_colors = fa.linear_colors;
-	a.depth_test = fa.depth_test; a.depth_clip = fa.depth_clip;
-	a.rays = rays; a.frame = fused_frame; a.depth_buffer = fused_depth; a.survive = survive; a.counters = counters;
+	a.comp = make_comp_args(fa, rays, alive_list, samples, fused_frame, fused_depth, survive, counters);
 	if (impl == 1) { launch_eval_tc(a, cfg.F, max_chunks, s); return; }
 	size_t smem = mlp_smem_bytes(a.density_hidden) + mlp_smem_bytes(a.rgb_hidden) + 4 * 32 * A_STRIDE;
 	static int sm_count = 0;

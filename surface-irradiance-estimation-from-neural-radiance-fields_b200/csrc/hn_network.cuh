@@ -1,6 +1,7 @@
 // Shared pieces of the network evaluation kernels (hn_network.cu: warp-MMA path, hn_network_tc.cu: tcgen05/TMEM path).
 #pragma once
 #include "hn_internal.h"
+#include "hn_shade.cuh"
 
 namespace hn {
 
@@ -21,14 +22,7 @@ struct EvalArgs {
 	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output (unfused path)
 	// fused compositing (tcgen05 kernel only): the warp that evaluated a ray chunk also composites it
 	int fused;
-	float cam_fwd[3], cam_pos[3];
-	float min_transmittance;
-	int rgb_act, density_act, linear_colors, depth_test, depth_clip;
-	RaySoA rays;
-	float4* frame;
-	float* depth_buffer;
-	uint32_t* survive;              // [n_chunks] 1 = the ray continues into the next pass
-	uint32_t* counters;
+	CompArgs comp;
 };
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {

@@ -143,103 +143,12 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 	}
 }
 
-// (d) Fused compositing: the warp that evaluated a ray chunk holds the chunk's 32 samples in its 32 lanes, which is exactly
-// the shape of the warp-segmented scan of hn_composite.cu (composite_kernel_nerf src/testbed_nerf.cu:528-735, final blend
-// shade_kernel_nerf_geometry src/testbed_geometry_training.cu:1826-1871). Transmittance = warp product scan, early-out
-// sample by ballot, colour/alpha by warp reductions, depth = warp arg-max of the weights. The raw network output is
-// rounded to fp16 first, so the numbers equal the unfused path's. Lane 0 owns the ray state. Returns samples composited.
-__device__ __forceinline__ uint32_t composite_chunk(const EvalArgs& a, uint32_t chunk, uint32_t count, int lane, uint2 o) {
-	const uint32_t r = a.alive_list[chunk];
-	float4 rgba = a.rays.rgba[r];
-	float depth = a.rays.depth[r];
-	float max_weight = a.rays.d_mw[r].w;
-	uint32_t n_steps = a.rays.n_steps[r];
-	bool terminated = false;
-	uint32_t composited = 0;
-	if (count > 0) {
-		const bool has = (uint32_t)lane < count;
-		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, zview = 0.f;
-		if (has) {
-			const float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
-			const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
-			const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP);
-			const float sigma = act_density(__high2float(bs), a.density_act);
-			const float wdt = __fdiv_rn(__fsub_rn(s.w, HN_MIN_STEP), dt_range);
-			const float dt = __fadd_rn(__fmul_rn(wdt, dt_range), HN_MIN_STEP);
-			alpha = 1.f - __expf(-sigma * dt);
-			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
-			const float ux = __fadd_rn(a.train_lo[0], __fmul_rn(__fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]), a.train_diag[0]));
-			const float uy = __fadd_rn(a.train_lo[1], __fmul_rn(__fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]), a.train_diag[1]));
-			const float uz = __fadd_rn(a.train_lo[2], __fmul_rn(__fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]), a.train_diag[2]));
-			zview = a.cam_fwd[0] * (ux - a.cam_pos[0]) + a.cam_fwd[1] * (uy - a.cam_pos[1]) + a.cam_fwd[2] * (uz - a.cam_pos[2]);
-		}
-		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
-		#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) {
-			const float up = __shfl_up_sync(0xffffffffu, P, d);
-			if (lane >= d) P *= up;
-		}
-		float Pex = __shfl_up_sync(0xffffffffu, P, 1);
-		if (lane == 0) Pex = 1.f;
-		const float T_in = 1.f - rgba.w;
-		const float weight = alpha * (T_in * Pex);
-		const float A_after = 1.f - T_in * P;
-		const uint32_t term_mask = __ballot_sync(0xffffffffu, has && (A_after > (1.0f - a.min_transmittance)));
-		const bool term = term_mask != 0;
-		const uint32_t last = term ? (uint32_t)(__ffs(term_mask) - 1) : count - 1;
-		const bool use = has && (uint32_t)lane <= last;
-		float sw = use ? weight : 0.f, sr = use ? cr * weight : 0.f, sg = use ? cg * weight : 0.f, sb = use ? cb * weight : 0.f;
-		float bw = use ? weight : -1.f;
-		uint32_t bj = (uint32_t)lane;
-		#pragma unroll
-		for (int d = 16; d > 0; d >>= 1) {
-			sw += __shfl_xor_sync(0xffffffffu, sw, d);
-			sr += __shfl_xor_sync(0xffffffffu, sr, d);
-			sg += __shfl_xor_sync(0xffffffffu, sg, d);
-			sb += __shfl_xor_sync(0xffffffffu, sb, d);
-			const float ow = __shfl_xor_sync(0xffffffffu, bw, d);
-			const uint32_t oj = __shfl_xor_sync(0xffffffffu, bj, d);
-			if (ow > bw || (ow == bw && oj < bj)) { bw = ow; bj = oj; }
-		}
-		const float zbest = __shfl_sync(0xffffffffu, zview, bj);
-		rgba.x += sr; rgba.y += sg; rgba.z += sb; rgba.w += sw;
-		if (bw > max_weight) { max_weight = bw; depth = zbest; }
-		n_steps += last + 1;
-		composited = last + 1;
-		if (term) {
-			const float inv = rgba.w;
-			rgba.x /= inv; rgba.y /= inv; rgba.z /= inv; rgba.w /= inv;
-			terminated = true;
-		}
-	}
-	const bool alive_next = !terminated && count == CHUNK;
-	if (lane == 0) {
-		a.rays.rgba[r] = rgba;
-		a.rays.depth[r] = depth;
-		a.rays.d_mw[r].w = max_weight;
-		a.rays.n_steps[r] = n_steps;
-		a.survive[chunk] = alive_next ? 1u : 0u;
-		if (!alive_next && rgba.w > 0.001f) { // compact_kernel_nerf keeps finished rays with alpha > 0.001
-			const uint32_t pix = a.rays.pixel[r];
-			if (!(a.depth_test && !a.depth_clip && depth > a.depth_buffer[pix])) { // NeRF behind the mesh: drop (per-pixel rule)
-				float4 tmp = rgba;
-				if (!a.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
-				const float4 fb = a.frame[pix];
-				const float ia = 1.0f - tmp.w;
-				a.frame[pix] = make_float4(tmp.x + fb.x * ia, tmp.y + fb.y * ia, tmp.z + fb.z * ia, tmp.w + fb.w * ia);
-				if (tmp.w > 0.2f) a.depth_buffer[pix] = depth;
-			}
-		}
-	}
-	return lane == 0 ? composited : 0u;
-}
-
 // G independent tile groups of 128 threads share one copy of the weights and one TMEM allocation (64 columns each); a
 // group synchronises on its own named barrier and its own mbarrier, so the groups of a CTA drift apart freely and one
 // group's gather overlaps the other groups' MMA rounds.
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
 
-template <int F, int G>
+template <int F, int G, bool FUSED>
 __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
 	const int grp = threadIdx.x >> 7;                     // tile group of this thread
@@ -349,7 +258,10 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 		}
 		HN_WAIT(); hidden_epilogue(t_row, a_row);
 		HN_ROUND(64, 16, w_addr);
-		// ---- output (r,g | b,sigma), 8 B per sample
+		// ---- output (r,g | b,sigma), 8 B per sample; fused: composite the chunk in this warp
+		const bool fuse_here = FUSED && chunk < n_chunks;
+		RayPre pre;
+		if (fuse_here) pre = composite_prefetch(a.comp, chunk, count, lane);
 		HN_WAIT();
 		{
 			uint32_t v[4];
@@ -358,15 +270,15 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 			uint2 o;
 			o.x = pack_plain(v[0], v[1]);
 			o.y = (pack_plain(v[2], 0u) & 0xFFFFu) | (sigma_bits << 16);
-			if (!a.fused) {
+			if (!FUSED) {
 				if (chunk < n_chunks) a.out[(size_t)chunk * CHUNK + lane] = o;
-			} else if (chunk < n_chunks) {
-				composited_acc += composite_chunk(a, chunk, count, lane, o);
+			} else if (fuse_here) {
+				composited_acc += composite_chunk(a.comp, pre, chunk, count, lane, o);
 			}
 		}
 	}
-	if (a.fused) { // frame statistics: one atomic per warp per launch
-		if (lane == 0 && composited_acc) atomicAdd((unsigned long long*)&a.counters[CNT_COMPOSITED_LO], (unsigned long long)composited_acc);
+	if (FUSED) { // frame statistics: one atomic per warp per launch
+		if (lane == 0 && composited_acc) atomicAdd((unsigned long long*)&a.comp.counters[CNT_COMPOSITED_LO], (unsigned long long)composited_acc);
 	}
 	#undef HN_ROUND
 	#undef HN_WAIT
@@ -387,13 +299,12 @@ void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStre
 	uint32_t ctas = (tiles + G - 1) / G;
 	uint32_t persistent = (uint32_t)sm_count * 2u;
 	uint32_t blocks = ctas < persistent ? ctas : persistent;
-	if (F == 4) {
-		cudaFuncSetAttribute(tc::eval_tc_kernel<4, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		tc::eval_tc_kernel<4, G><<<blocks, tc::TILE * G, smem, s>>>(a);
-	} else {
-		cudaFuncSetAttribute(tc::eval_tc_kernel<2, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		tc::eval_tc_kernel<2, G><<<blocks, tc::TILE * G, smem, s>>>(a);
-	}
+	#define HN_LAUNCH_TC(FF, FU) do { \
+		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+		tc::eval_tc_kernel<FF, G, FU><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
+	if (F == 4) { if (a.fused) HN_LAUNCH_TC(4, true); else HN_LAUNCH_TC(4, false); }
+	else { if (a.fused) HN_LAUNCH_TC(2, true); else HN_LAUNCH_TC(2, false); }
+	#undef HN_LAUNCH_TC
 }
 
 } // namespace hn

@@ -26,4 +26,128 @@ __device__ __forceinline__ float act_density(float v, int act) {
 __device__ __forceinline__ float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : powf((s + 0.055f) / 1.055f, 2.4f); }
 __device__ __forceinline__ float linear_to_srgb(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * powf(l, 0.41666f) - 0.055f; }
 
+// Everything the per-chunk compositing needs (shared by composite_ray_kernel and the fused epilogue of the tcgen05 kernel)
+struct CompArgs {
+	const uint32_t* alive_list;   // [n_chunks] ray id per list position
+	const float4* samples;        // [n_chunks][32] (x,y,z,dt)
+	float train_lo[3], train_diag[3];
+	float cam_fwd[3], cam_pos[3];
+	float min_transmittance;
+	int rgb_act, density_act, linear_colors, depth_test, depth_clip;
+	RaySoA rays;
+	float4* frame;
+	float* depth_buffer;
+	uint32_t* survive;            // [n_chunks] 1 = the ray continues into the next pass
+	uint32_t* counters;
+};
+
+// (d) Compositing of ONE ray chunk by ONE warp: lane j holds sample j of the chunk (warp-segmented scan;
+// composite_kernel_nerf src/testbed_nerf.cu:528-735, final blend
+// shade_kernel_nerf_geometry src/testbed_geometry_training.cu:1826-1871). Transmittance = warp product scan, early-out
+// sample by ballot, colour/alpha by warp reductions, depth = warp arg-max of the weights. The raw network output is
+// rounded to fp16 first, so the numbers equal the unfused path's. Lane 0 owns the ray state. Returns samples composited.
+// The ray state and the lane's sample are fetched by composite_prefetch() right after the last layer has been issued,
+// so their global-memory latency hides behind that MMA round instead of extending the tile.
+struct RayPre { uint32_t r, n_steps; float4 rgba; float depth, max_weight; float4 s; };
+__device__ __forceinline__ RayPre composite_prefetch(const CompArgs& a, uint32_t chunk, uint32_t count, int lane) {
+	RayPre p;
+	p.r = a.alive_list[chunk];
+	p.rgba = a.rays.rgba[p.r];
+	p.depth = a.rays.depth[p.r];
+	p.max_weight = a.rays.d_mw[p.r].w;
+	p.n_steps = a.rays.n_steps[p.r];
+	p.s = make_float4(0.f, 0.f, 0.f, 0.f);
+	if ((uint32_t)lane < count) p.s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
+	return p;
+}
+__device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const RayPre& pre, uint32_t chunk, uint32_t count, int lane, uint2 o) {
+	const uint32_t r = pre.r;
+	float4 rgba = pre.rgba;
+	float depth = pre.depth;
+	float max_weight = pre.max_weight;
+	uint32_t n_steps = pre.n_steps;
+	bool terminated = false;
+	uint32_t composited = 0;
+	if (count > 0) {
+		const bool has = (uint32_t)lane < count;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, zview = 0.f;
+		if (has) {
+			const float4 s = pre.s;
+			const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
+			const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP);
+			const float sigma = act_density(__high2float(bs), a.density_act);
+			const float wdt = __fdiv_rn(__fsub_rn(s.w, HN_MIN_STEP), dt_range);
+			const float dt = __fadd_rn(__fmul_rn(wdt, dt_range), HN_MIN_STEP);
+			alpha = 1.f - __expf(-sigma * dt);
+			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
+			const float ux = __fadd_rn(a.train_lo[0], __fmul_rn(__fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]), a.train_diag[0]));
+			const float uy = __fadd_rn(a.train_lo[1], __fmul_rn(__fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]), a.train_diag[1]));
+			const float uz = __fadd_rn(a.train_lo[2], __fmul_rn(__fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]), a.train_diag[2]));
+			zview = a.cam_fwd[0] * (ux - a.cam_pos[0]) + a.cam_fwd[1] * (uy - a.cam_pos[1]) + a.cam_fwd[2] * (uz - a.cam_pos[2]);
+		}
+		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
+		#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const float up = __shfl_up_sync(0xffffffffu, P, d);
+			if (lane >= d) P *= up;
+		}
+		float Pex = __shfl_up_sync(0xffffffffu, P, 1);
+		if (lane == 0) Pex = 1.f;
+		const float T_in = 1.f - rgba.w;
+		const float weight = alpha * (T_in * Pex);
+		const float A_after = 1.f - T_in * P;
+		const uint32_t term_mask = __ballot_sync(0xffffffffu, has && (A_after > (1.0f - a.min_transmittance)));
+		const bool term = term_mask != 0;
+		const uint32_t last = term ? (uint32_t)(__ffs(term_mask) - 1) : count - 1;
+		const bool use = has && (uint32_t)lane <= last;
+		float sw = use ? weight : 0.f, sr = use ? cr * weight : 0.f, sg = use ? cg * weight : 0.f, sb = use ? cb * weight : 0.f;
+		float bw = use ? weight : -1.f;
+		uint32_t bj = (uint32_t)lane;
+		#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			sw += __shfl_xor_sync(0xffffffffu, sw, d);
+			sr += __shfl_xor_sync(0xffffffffu, sr, d);
+			sg += __shfl_xor_sync(0xffffffffu, sg, d);
+			sb += __shfl_xor_sync(0xffffffffu, sb, d);
+			const float ow = __shfl_xor_sync(0xffffffffu, bw, d);
+			const uint32_t oj = __shfl_xor_sync(0xffffffffu, bj, d);
+			if (ow > bw || (ow == bw && oj < bj)) { bw = ow; bj = oj; }
+		}
+		const float zbest = __shfl_sync(0xffffffffu, zview, bj);
+		rgba.x += sr; rgba.y += sg; rgba.z += sb; rgba.w += sw;
+		if (bw > max_weight) { max_weight = bw; depth = zbest; }
+		n_steps += last + 1;
+		composited = last + 1;
+		if (term) {
+			const float inv = rgba.w;
+			rgba.x /= inv; rgba.y /= inv; rgba.z /= inv; rgba.w /= inv;
+			terminated = true;
+		}
+	}
+	const bool alive_next = !terminated && count == CHUNK;
+	if (lane == 0) {
+		a.rays.rgba[r] = rgba;
+		a.rays.depth[r] = depth;
+		a.rays.d_mw[r].w = max_weight;
+		a.rays.n_steps[r] = n_steps;
+		a.survive[chunk] = alive_next ? 1u : 0u;
+		if (!alive_next && rgba.w > 0.001f) { // compact_kernel_nerf keeps finished rays with alpha > 0.001
+			const uint32_t pix = a.rays.pixel[r];
+			if (!(a.depth_test && !a.depth_clip && depth > a.depth_buffer[pix])) { // NeRF behind the mesh: drop (per-pixel rule)
+				float4 tmp = rgba;
+				if (!a.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+				const float4 fb = a.frame[pix];
+				const float ia = 1.0f - tmp.w;
+				a.frame[pix] = make_float4(tmp.x + fb.x * ia, tmp.y + fb.y * ia, tmp.z + fb.z * ia, tmp.w + fb.w * ia);
+				if (tmp.w > 0.2f) a.depth_buffer[pix] = depth;
+			}
+		}
+	}
+	return lane == 0 ? composited : 0u;
+}
+
+CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_list, const float4* samples, float4* frame, float* depth_buffer,
+	uint32_t* survive, uint32_t* counters); // hn_composite.cu
+void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const uint32_t* sample_counts, const uint2* net_out, uint32_t max_rays, cudaStream_t s);
+
 } // namespace hn

@@ -28,6 +28,30 @@ __device__ __forceinline__ V3 mix3(V3 a, V3 b, float c) { return a * (1.0f - c) 
 __device__ __forceinline__ V3 mix3(V3 a, V3 b, V3 c) { return {mixf(a.x, b.x, c.x), mixf(a.y, b.y, c.y), mixf(a.z, b.z, c.z)}; }
 __device__ __forceinline__ V3 ld3(const float* f) { return {f[0], f[1], f[2]}; }
 
+// Thread index -> pixel of THIS rank. One rank: row-major over the frame. Tile-sharded: the rank's own tiles are
+// enumerated back to back (local tile k = global tile k*world + rank), so no thread is spent on a foreign pixel.
+__device__ __forceinline__ bool owned_pixel(const FrameArgs& a, uint32_t i, uint32_t& x, uint32_t& y) {
+	const uint32_t w = (uint32_t)a.w, h = (uint32_t)a.h;
+	if (a.world <= 1) {
+		if (i >= w * h) return false;
+		x = i % w; y = i / w;
+		return true;
+	}
+	const uint32_t tw = (uint32_t)a.tile_w, th = (uint32_t)a.tile_h, per_tile = tw * th;
+	const uint32_t tiles_x = (w + tw - 1) / tw, tiles_y = (h + th - 1) / th;
+	const uint32_t tile = (i / per_tile) * (uint32_t)a.world + (uint32_t)a.rank;
+	if (tile >= tiles_x * tiles_y) return false;
+	const uint32_t k = i % per_tile;
+	x = (tile % tiles_x) * tw + k % tw;
+	y = (tile / tiles_x) * th + k / tw;
+	return x < w && y < h;
+}
+__host__ inline uint32_t owned_pixel_threads(const FrameArgs& a) {
+	if (a.world <= 1) return (uint32_t)a.w * (uint32_t)a.h;
+	const uint32_t tiles = (uint32_t)((a.w + a.tile_w - 1) / a.tile_w) * (uint32_t)((a.h + a.tile_h - 1) / a.tile_h);
+	return ((tiles + a.world - 1 - a.rank) / a.world) * (uint32_t)(a.tile_w * a.tile_h);
+}
+
 struct Box { V3 lo, hi; };
 __device__ __forceinline__ Box ldbox(const float* f) { return {{f[0], f[1], f[2]}, {f[3], f[4], f[5]}}; }
 // bounding_box.cuh:313

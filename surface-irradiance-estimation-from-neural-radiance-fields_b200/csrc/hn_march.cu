@@ -244,17 +244,14 @@ __device__ __forceinline__ bool tile_owned(const FrameArgs& a, uint32_t x, uint3
 // per warp); the ray id is the slot. Order is non-deterministic, results are keyed by pixel so the image is not.
 __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, uint32_t* __restrict__ alive_list,
 	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer) {
-	uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	uint32_t x = 0, y = 0, idx = 0;
 	bool alive = false;
 	V3 o, d; float t = 0.0f;
-	if (idx < n) {
-		uint32_t x = idx % (uint32_t)a.w, y = idx / (uint32_t)a.w;
-		if (tile_owned(a, x, y)) {
-			// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
-			if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
-			alive = start_ray(a, bits, x, y, o, d, t);
-		}
+	if (owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) {
+		idx = x + (uint32_t)a.w * y;
+		// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
+		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
+		alive = start_ray(a, bits, x, y, o, d, t);
 	}
 	uint32_t mask = __ballot_sync(0xffffffffu, alive);
 	if (mask == 0) return;
@@ -470,7 +467,8 @@ void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thres
 	}
 }
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters, float* depth_buffer, cudaStream_t s) {
-	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	uint32_t n = owned_pixel_threads(a);
+	if (!n) return;
 	raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer);
 }
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {

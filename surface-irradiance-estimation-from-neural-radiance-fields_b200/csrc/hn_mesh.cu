@@ -187,10 +187,9 @@ __device__ __forceinline__ bool mesh_tile_owned(const FrameArgs& a, uint32_t x, 
 __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, SceneDev sc, float4* __restrict__ frame, float* __restrict__ depth_buffer) {
 	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
 	int* stack = stack_s + threadIdx.x;
-	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= (uint32_t)a.w * (uint32_t)a.h) return;
-	const uint32_t x = idx % (uint32_t)a.w, y = idx / (uint32_t)a.w;
-	if (!mesh_tile_owned(a, x, y)) return;
+	uint32_t x, y;
+	if (!owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) return;
+	const uint32_t idx = x + (uint32_t)a.w * y;
 	const Box aabb = ldbox(a.mesh_aabb);
 	// init_rays_with_payload_kernel_mesh_geometry (:488-579): pixel_to_ray with camera_matrix0 as is (no rolling shutter)
 	const float u = ((float)x + a.pixel_offset[0]) / (float)a.w, v = ((float)y + a.pixel_offset[1]) / (float)a.h;
@@ -255,7 +254,8 @@ __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, Scen
 }
 
 void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, cudaStream_t s) {
-	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;
+	uint32_t n = owned_pixel_threads(a);
+	if (!n) return;
 	mesh_pass_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, frame, depth_buffer);
 }
 void launch_trace(SceneDev scene, int compat, uint32_t n, const float* o, const float* d, int32_t* mesh, int32_t* tri, float* t, cudaStream_t s) {

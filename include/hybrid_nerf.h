@@ -49,6 +49,12 @@ int hn_get_network_info(const hn_context* ctx, hn_network_info* out);
 /* dtype: 0 = fp16, 1 = fp32 (converted to fp16 like Trainer's inference copy). Host pointer. */
 int hn_set_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype);   /* Trainer::set_params / deserialize, tcnn trainer.h:275-351 */
 
+/* Snapshots (.ingp = zlib-wrapped MessagePack, .msgpack = plain): network config + fp16/fp32 parameters + fp16 density grid +
+ * aabb / camera / sun / exposure, the reference's own file format (Testbed::load_snapshot / save_snapshot,
+ * src/testbed.cu:5219-5488, testbed.h:780-782; Trainer::serialize, tcnn trainer.h:275-322). */
+int hn_load_snapshot(hn_context* ctx, const char* ingp_or_msgpack_path);
+int hn_save_snapshot(hn_context* ctx, const char* ingp_or_msgpack_path);
+
 /* ---- occupancy (a-20) ---- */
 /* grid: float[128^3 * n_cascades] in Morton order (host). Builds the 8-mip bitfield on the device. */
 int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades);     /* update_density_grid_mean_and_bitfield, src/testbed_nerf.cu:2863-2880 */

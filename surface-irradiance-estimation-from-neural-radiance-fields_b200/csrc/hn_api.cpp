@@ -35,7 +35,8 @@ int hn_create(hn_context** out, int cuda_device) {
 	HN_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
 	if (prop.major != 10) throw std::runtime_error(std::string("device '") + prop.name + "' is not sm_100: kernels are built for sm_100a only");
 	HN_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-	HN_CUDA(cudaMallocHost((void**)&ctx->pinned_counters, CNT_N * sizeof(uint32_t) * 2));
+	HN_CUDA(cudaMallocHost((void**)&ctx->pinned_counters, CNT_N * sizeof(uint32_t) * 4));
+	for (auto& e : ctx->pass_events) HN_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 	ctx->counters.ensure(CNT_N);
 	ctx->bitfield.ensure(BITFIELD_BYTES);
 	HN_CATCH(ctx)
@@ -46,6 +47,7 @@ void hn_destroy(hn_context* ctx) {
 	cudaSetDevice(ctx->device);
 	cudaDeviceSynchronize();
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+	for (auto& e : ctx->pass_events) if (e) cudaEventDestroy(e);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -69,7 +71,7 @@ int hn_set_aabb_scale(hn_context* ctx, int aabb_scale) {
 	HN_TRY(ctx)
 	need(aabb_scale >= 1 && aabb_scale <= 128 && (aabb_scale & (aabb_scale - 1)) == 0, "aabb_scale must be a power of two in [1,128]");
 	ctx->aabb_scale = aabb_scale;
-	if (ctx->has_net) load_network_config_text(ctx, ctx->config_text, ctx->config_dir);
+	if (ctx->has_net) reapply_network_config(ctx);
 	// the render box follows the training box: [0.5 - s/2, 0.5 + s/2]^3 (src/testbed_nerf.cu:2722-2727)
 	for (int d = 0; d < 3; ++d) { ctx->opt.render_aabb[d] = 0.5f - 0.5f * aabb_scale; ctx->opt.render_aabb[3 + d] = 0.5f + 0.5f * aabb_scale; }
 	HN_CATCH(ctx)
@@ -87,21 +89,7 @@ int hn_get_network_info(const hn_context* ctx, hn_network_info* out) {
 }
 int hn_set_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype) {
 	HN_TRY(ctx)
-	need(ctx->has_net, "load a network config first");
-	need(n_elements == ctx->net.n_params, "parameter blob has the wrong number of elements");
-	HN_CUDA(cudaSetDevice(ctx->device));
-	ctx->params.ensure(n_elements);
-	if (dtype == 0) {
-		HN_CUDA(cudaMemcpy(ctx->params.p, blob, n_elements * sizeof(__half), cudaMemcpyHostToDevice));
-	} else if (dtype == 1) {
-		std::vector<__half> tmp(n_elements);
-		const float* f = (const float*)blob;
-		for (size_t i = 0; i < n_elements; ++i) tmp[i] = __float2half_rn(f[i]);
-		HN_CUDA(cudaMemcpy(ctx->params.p, tmp.data(), n_elements * sizeof(__half), cudaMemcpyHostToDevice));
-	} else {
-		throw std::runtime_error("dtype must be 0 (fp16) or 1 (fp32)");
-	}
-	ctx->has_params = true;
+	upload_params(ctx, blob, n_elements, dtype);
 	HN_CATCH(ctx)
 }
 
@@ -116,7 +104,27 @@ static void refresh_occ_bounds(hn_context* ctx) {
 }
 int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades) {
 	HN_TRY(ctx)
+	upload_density_grid(ctx, grid, n_cascades);
+	HN_CATCH(ctx)
+}
+} // extern "C"
+namespace hn {
+void upload_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype) {
+	need(ctx->has_net, "load a network config first");
+	need(n_elements == ctx->net.n_params, "parameter blob has the wrong number of elements");
+	need(dtype == 0 || dtype == 1, "dtype must be 0 (fp16) or 1 (fp32)");
+	// host copy first (hn_save_snapshot writes it back out); Trainer keeps an fp16 inference copy the same way
+	ctx->params_host.resize(n_elements);
+	if (dtype == 0) std::memcpy(ctx->params_host.data(), blob, n_elements * sizeof(__half));
+	else { const float* f = (const float*)blob; for (size_t i = 0; i < n_elements; ++i) ctx->params_host[i] = __float2half_rn(f[i]); }
+	HN_CUDA(cudaSetDevice(ctx->device));
+	ctx->params.ensure(n_elements);
+	HN_CUDA(cudaMemcpy(ctx->params.p, ctx->params_host.data(), n_elements * sizeof(__half), cudaMemcpyHostToDevice));
+	ctx->has_params = true;
+}
+void upload_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades) {
 	need(n_cascades >= 1 && n_cascades <= CASCADES, "n_cascades must be in [1,8]");
+	ctx->density_grid_host.assign(grid, grid + (size_t)GRID_CELLS * n_cascades);
 	HN_CUDA(cudaSetDevice(ctx->device));
 	DevBuf<float> d_grid;
 	d_grid.ensure((size_t)GRID_CELLS * n_cascades);
@@ -134,13 +142,17 @@ int hn_set_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades)
 	HN_CUDA(cudaGetLastError());
 	refresh_occ_bounds(ctx);
 	ctx->has_bitfield = true;
-	HN_CATCH(ctx)
 }
+} // namespace hn
+extern "C" {
+int hn_load_snapshot(hn_context* ctx, const char* path) { HN_TRY(ctx) load_snapshot_file(ctx, path); HN_CATCH(ctx) }
+int hn_save_snapshot(hn_context* ctx, const char* path) { HN_TRY(ctx) save_snapshot_file(ctx, path); HN_CATCH(ctx) }
 int hn_set_occupancy_bitfield(hn_context* ctx, const uint8_t* bits, size_t n_bytes) {
 	HN_TRY(ctx)
 	need(n_bytes == BITFIELD_BYTES, "bitfield must be 128^3/8*8 bytes");
 	HN_CUDA(cudaSetDevice(ctx->device));
 	HN_CUDA(cudaMemcpy(ctx->bitfield.p, bits, n_bytes, cudaMemcpyHostToDevice));
+	ctx->density_grid_host.clear();
 	refresh_occ_bounds(ctx);
 	ctx->has_bitfield = true;
 	HN_CATCH(ctx)
@@ -330,14 +342,28 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 		tm.stop(st.ms_raygen);
 		uint32_t* lists[2] = {ctx->alive_a.p, ctx->alive_b.p};
 		int cur = 0;
-		while (true) {
-			// the one host read-back per pass (the reference does the same, src/testbed_nerf.cu:2071-2072)
-			HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-			HN_CUDA(cudaStreamSynchronize(s));
-			const uint32_t n_alive = ctx->pinned_counters[cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B];
-			if (st.n_passes == 0) st.n_rays_alive = n_alive;
-			if (n_alive == 0) break;
-			need(n_alive <= n_px, "alive counter corrupt");
+		// Pass loop without a host round trip per pass (the reference blocks on the alive counter every pass,
+		// src/testbed_nerf.cu:2071-2072): every kernel reads its ray count from device memory, the host only needs an
+		// upper bound for grid and buffer sizes (the live-ray count never grows) and the moment it reaches zero. The
+		// count entering pass j is copied to a pinned ring slot after pass j-1 and looked at LAG passes later, so the
+		// stream always holds LAG passes of queued work; at most LAG empty passes run at the end of a frame.
+		const int LAG = ctx->opt.profile ? 0 : 1;
+		constexpr int RING = 4;
+		HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+		HN_CUDA(cudaStreamSynchronize(s));
+		uint32_t n_alive = ctx->pinned_counters[CNT_ALIVE_A]; // exact for the first pass, an upper bound afterwards
+		st.n_rays_alive = n_alive;
+		need(n_alive <= n_px, "alive counter corrupt");
+		for (int k = 0; n_alive > 0; ++k) {
+			const int j = k - LAG; // newest pass whose entry count must be known before pass k is queued
+			if (j >= 1) {
+				HN_CUDA(cudaEventSynchronize(ctx->pass_events[j % RING]));
+				const uint32_t n = ctx->pinned_counters[(j % RING) * CNT_N + ((j & 1) ? CNT_ALIVE_B : CNT_ALIVE_A)];
+				if (n == 0) { st.n_passes = (uint32_t)j; break; }
+				need(n <= n_alive, "alive counter corrupt");
+				n_alive = n;
+			}
+			st.n_passes = (uint32_t)k + 1;
 			ctx->samples.ensure((size_t)n_alive * CHUNK);
 			ctx->net_out.ensure((size_t)n_alive * CHUNK);
 			uint32_t* n_alive_ptr = cnt + (cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B);
@@ -363,9 +389,12 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 			else launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
 			tm.stop(st.ms_composite);
 			st.n_kernel_launches += 3;
-			st.n_passes += 1;
 			cur ^= 1;
+			HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters + ((k + 1) % RING) * CNT_N, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+			HN_CUDA(cudaEventRecord(ctx->pass_events[(k + 1) % RING], s));
 		}
+		HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+		HN_CUDA(cudaStreamSynchronize(s));
 		st.n_samples = (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);
 		st.n_samples_composited = (uint64_t)ctx->pinned_counters[CNT_COMPOSITED_LO] | ((uint64_t)ctx->pinned_counters[CNT_COMPOSITED_HI] << 32);
 	}

@@ -92,6 +92,11 @@ void finalize_network(hn_context* ctx) {
 void load_network_config_text(hn_context* ctx, const std::string& text, const std::string& base_dir) {
 	Json cfg = JsonParser(text).parse();
 	cfg = merge_parent(cfg, base_dir);
+	apply_network_config(ctx, cfg);
+}
+
+// cfg: merged network config (also the root object of a snapshot; its "snapshot" member is ignored here)
+void apply_network_config(hn_context* ctx, const Json& cfg) {
 	if (!cfg.contains("encoding") || !cfg.contains("network")) throw std::runtime_error("network config needs 'encoding' and 'network' objects");
 	const Json& enc = cfg.at("encoding");
 	std::string otype = lower(enc.value("otype", std::string("OneBlob")));
@@ -130,9 +135,14 @@ void load_network_config_text(hn_context* ctx, const std::string& text, const st
 			throw std::runtime_error("only SphericalHarmonics degree 4 direction encoding is supported");
 	}
 	ctx->net = n;
-	ctx->config_text = text;
-	ctx->config_dir = base_dir;
+	{ // kept (without any snapshot payload) so hn_set_aabb_scale can re-derive per_level_scale, and for hn_save_snapshot
+		Json keep; keep.type = Json::Object;
+		for (auto& kv : cfg.obj) if (kv.first != "snapshot") keep.obj.push_back(kv);
+		ctx->config_blob = msgpack_write(keep);
+	}
 	finalize_network(ctx);
 }
+
+void reapply_network_config(hn_context* ctx) { apply_network_config(ctx, msgpack_parse(ctx->config_blob)); }
 
 } // namespace hn

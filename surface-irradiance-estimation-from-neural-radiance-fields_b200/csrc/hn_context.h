@@ -86,9 +86,11 @@ struct hn_context {
 	hn::NetCfg net;
 	bool has_net = false;
 	int aabb_scale = 1;
-	std::string config_text, config_dir; // config source kept so hn_set_aabb_scale can re-derive per_level_scale
+	std::string config_blob; // merged network config (MessagePack), kept so hn_set_aabb_scale can re-derive per_level_scale
 	hn::GridLevels levels;
 	hn::DevBuf<__half> params;
+	std::vector<__half> params_host;        // fp16 inference copy on the host (snapshot writer)
+	std::vector<float> density_grid_host;   // last density grid given to hn_set_density_grid (snapshot writer)
 	bool has_params = false;
 
 	// occupancy
@@ -117,7 +119,8 @@ struct hn_context {
 	hn::DevBuf<float4> samples;
 	hn::DevBuf<uint2> net_out;
 	hn::DevBuf<uint32_t> survive;
-	uint32_t* pinned_counters = nullptr; // CNT_N uint32
+	uint32_t* pinned_counters = nullptr; // ring of 4 x CNT_N uint32 (pass-loop read-backs)
+	cudaEvent_t pass_events[4] = {nullptr, nullptr, nullptr, nullptr};
 	// render_to_host buffers
 	hn::DevBuf<float4> frame, accum, tonemapped;
 	hn::DevBuf<float> depth;
@@ -135,7 +138,20 @@ struct hn_context {
 
 namespace hn {
 // hn_config.cpp
+struct Json;
 void load_network_config_text(hn_context* ctx, const std::string& text, const std::string& base_dir);
+void apply_network_config(hn_context* ctx, const Json& cfg);
+void reapply_network_config(hn_context* ctx);
+// hn_snapshot.cpp
+Json msgpack_parse(const std::string& bytes);
+std::string msgpack_write(const Json& j);
+std::string zlib_inflate(const std::string& in);
+std::string zlib_store(const std::string& in);
+void load_snapshot_file(hn_context* ctx, const std::string& path);
+void save_snapshot_file(hn_context* ctx, const std::string& path);
+// hn_api.cpp (shared by the snapshot loader)
+void upload_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype);
+void upload_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades);
 void finalize_network(hn_context* ctx);
 // hn_scene.cpp
 void add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], bool normalize);

@@ -13,7 +13,7 @@
 namespace hn {
 
 struct Json {
-	enum Type { Null, Bool, Number, String, Array, Object } type = Null;
+	enum Type { Null, Bool, Number, String, Array, Object, Binary } type = Null; // Binary: msgpack bin (snapshots), bytes in `str`
 	bool b = false;
 	double num = 0.0;
 	std::string str;

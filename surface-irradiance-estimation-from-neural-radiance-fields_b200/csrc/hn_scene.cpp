@@ -285,8 +285,12 @@ void load_scene_file(hn_context* ctx, const std::string& path) {
 		if (type == "Mesh") {
 			load_mesh_file(ctx, mpath, center);
 		} else if (type == "Nerf") {
-			// a NeRF enters through hn_load_network_config + hn_set_params / hn_set_density_grid; .ingp snapshots are §8(f)-2
-			if (exists(mpath)) throw std::runtime_error("'.ingp' snapshot loading is not part of this build (SURVEY §8f-2): load the network with hn_set_params");
+			// load_snapshot(path) (src/testbed_geometry_training.cu:3172): the hybrid scene pins the NeRF to the unit cube
+			// (src/testbed.cu:5303-5307). A missing file is tolerated: the NeRF may also enter through hn_set_params.
+			if (exists(mpath)) {
+				load_snapshot_file(ctx, mpath);
+				for (int d = 0; d < 3; ++d) { ctx->opt.train_aabb[d] = 0.0f; ctx->opt.train_aabb[3 + d] = 1.0f; }
+			}
 		} else {
 			throw std::runtime_error("Geometry type must be either 'Mesh' or 'Nerf'.");
 		}

@@ -51,7 +51,7 @@ class FrameStats(C.Structure):
 # every symbol include/hybrid_nerf.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "hn_create", "hn_destroy", "hn_last_error", "hn_version", "hn_load_network_config", "hn_load_network_config_string",
-    "hn_set_aabb_scale", "hn_get_network_info", "hn_set_params", "hn_set_density_grid", "hn_set_occupancy_bitfield",
+    "hn_set_aabb_scale", "hn_get_network_info", "hn_set_params", "hn_load_snapshot", "hn_save_snapshot", "hn_set_density_grid", "hn_set_occupancy_bitfield",
     "hn_get_occupancy_bitfield", "hn_load_scene", "hn_add_mesh", "hn_load_mesh_file", "hn_build_scene", "hn_clear_scene",
     "hn_get_scene_aabb", "hn_set_option", "hn_get_option", "hn_render_frame", "hn_render_to_host", "hn_set_camera",
     "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
@@ -77,7 +77,7 @@ _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_trace.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
-for _n in ("hn_load_network_config", "hn_load_network_config_string", "hn_load_scene"):
+for _n in ("hn_load_network_config", "hn_load_network_config_string", "hn_load_scene", "hn_load_snapshot", "hn_save_snapshot"):
     getattr(_lib, _n).argtypes = [C.c_void_p, C.c_char_p]
 _lib.hn_load_mesh_file.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
 _lib.hn_set_aabb_scale.argtypes = [C.c_void_p, C.c_int]
@@ -141,6 +141,13 @@ class Testbed:
     def reload_network_from_json(self, text: str):
         self._check(_lib.hn_load_network_config_string(self._h, text.encode()))
 
+    def load_snapshot(self, path: str):
+        """pyngp.Testbed.load_snapshot (python_api.cu:436): .ingp / .msgpack written by the reference or by save_snapshot."""
+        self._check(_lib.hn_load_snapshot(self._h, os.fsencode(path)))
+
+    def save_snapshot(self, path: str, include_optimizer_state: bool = False):
+        self._check(_lib.hn_save_snapshot(self._h, os.fsencode(path)))
+
     def set_aabb_scale(self, s: int):
         self._check(_lib.hn_set_aabb_scale(self._h, int(s)))
 
@@ -177,6 +184,8 @@ class Testbed:
         """Scene json (Geometry mode) or mesh file, like Testbed::load_file (src/testbed.cu:319-389)."""
         if path.endswith(".json"):
             self._check(_lib.hn_load_scene(self._h, os.fsencode(path)))
+        elif path.endswith((".ingp", ".msgpack")):
+            self.load_snapshot(path)
         else:
             c = _f32([0, 0, 0])
             self._check(_lib.hn_load_mesh_file(self._h, os.fsencode(path), _ptr(c)))

@@ -46,6 +46,10 @@ typedef struct {
 	int32_t compat_nearest_aabb_only; // 1 = reference top-level rule (geometry_bvh.cu:166-200)
 	int32_t depth_merge_clip;         // 0 = reference per-pixel depth test, 1 = stop marching at the mesh depth
 	int32_t n_threads;                // host threads for the frame loops (cpu baseline)
+	// a-16 environment map (envmap.cuh:24-50): lat-long RGBA32F, row-major [env_h][env_w][4]; NULL = none.
+	// env_samples = K cosine-weighted light directions per mesh hit (0 = envmap is background only).
+	int32_t env_w, env_h, env_samples, env_pad;
+	const float* envmap;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----
@@ -58,6 +62,19 @@ float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const
 	uint32_t min_mip, uint32_t max_mip, const float aabb[6], int32_t iter_cap);
 float orc_calc_dt(float t, float cone_angle);
 float orc_srgb_to_linear(float v);
+
+// ---- a-16 sampling helpers (random_val.cuh:62-72,130-185; pinned against oracle/_ref) and the envmap lookup ----
+void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]);
+void orc_dir_to_spherical_unorm(const float d[3], float out[2]);
+void orc_cosine_hemisphere(const float u[2], float out[3]);
+void orc_spherical_cap(const float u[2], float cap_height, float out[3]);
+void orc_compute_local_frame(const float z[3], float out[9]); // 3 columns: X, Y, Z
+void orc_read_envmap(const float* envmap, int32_t w, int32_t h, const float dir[3], float out[4]);
+// K light directions of pixel `idx` at sample index spp around the unit normal n: out [K][3]
+void orc_env_light_dirs(uint32_t idx, uint32_t spp, uint32_t K, const float n[3], float* out);
+// transmittance of the NeRF along a ray (density-only network evaluation), as the env-light pass uses it
+float orc_nerf_transmittance(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
+	const float o[3], const float d[3], uint32_t* n_samples_out);
 
 // ---- occupancy (a-20) ----
 // grid: float[128^3 * n_cascades] Morton order. out: uint8[128^3/8 * 8]. Returns the threshold used.

@@ -14,6 +14,11 @@ Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y);
 vec2 ld_random_pixel_offset(uint32_t spp);
 Ray uv_to_ray_pinhole(vec2 uv, int w, int h, vec2 focal, const cam_t& cam, vec2 screen_center, float near_distance);
 struct Net;
+Net* net_new(const orc_net_config& c, const uint16_t* params);
+void net_delete(Net* n);
+vec4 read_envmap(const float* env, int w, int h, vec3 dir);
+vec3 env_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, vec3 n);
+float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8_t* bits, vec3 o, vec3 d, uint32_t* n_out);
 
 struct Triangle { vec3 a, b, c; };
 
@@ -220,7 +225,11 @@ static void parallel_rows(int n_rows, int n_threads, F&& f) {
 }
 
 // testbed_geometry_training.cu:2202-2320 (render_geometry_mesh), Shade mode with sun shadow rays.
-static void render_mesh(const orc_scene& s, const orc_render_params& p, float* frame, float* depth) {
+// With an envmap and env_samples = K > 0 every shaded triangle hit also gathers environment light (a-16, OUR definition:
+// the reference's integration/shading kernels are declared but absent): K cosine-weighted directions around the
+// viewer-facing normal, each tested against the meshes (nearest-hit search = shadow ray) and attenuated by the
+// transmittance of the NeRF; Lambertian estimator colour += albedo / K * sum_k L_env(w_k) * V_k * T_k.
+static void render_mesh(const orc_scene& s, const orc_render_params& p, float* frame, float* depth, const Net* net = nullptr, const uint8_t* bits = nullptr) {
 	BoundingBox aabb = bb_from(p.mesh_aabb);
 	cam_t cam = cam_from(p.cam0);
 	vec3 cam_pos = cam.c[3], cam_fwd = cam.c[2];
@@ -278,6 +287,23 @@ static void render_mesh(const orc_scene& s, const orc_render_params& p, float* f
 			vec3 color = evaluate_shading(floor ? floorcol : basecolor * basecolor, ambientcolor * skycol, suncol,
 				floor ? 0.f : B[0], floor ? 0.f : B[1], floor ? 1.f : B[2], floor ? 0.5f : B[3], 0.f, floor ? 0.f : B[4], 0.f,
 				floor ? 0.f : B[5], B[6], sun, -normalize(dir), normal);
+			if (p.envmap && p.env_samples > 0 && touched && ti >= 0) {
+				const uint32_t K = (uint32_t)p.env_samples;
+				vec3 nf = normal * -std::copysign(1.0f, dot(dir, normal));
+				vec3 org = pos + nf * 1e-3f;
+				vec3 albedo = floor ? floorcol : basecolor * basecolor;
+				vec3 sum = {0.f, 0.f, 0.f};
+				for (uint32_t k = 0; k < K; ++k) {
+					vec3 w = env_light_dir(idx, p.spp, K, k, nf);
+					int emi, eti; float et; bool etouched;
+					scene_nearest(s, false, org, w, false, emi, eti, et, etouched);
+					if (eti >= 0) continue;
+					vec4 L = read_envmap(p.envmap, p.env_w, p.env_h, w);
+					float T = (net && bits) ? nerf_transmittance(p, *net, bits, org, w, nullptr) : 1.0f;
+					sum = sum + vec3{L.x, L.y, L.z} * T;
+				}
+				color = color + albedo * sum * (1.0f / (float)K);
+			}
 			float* fb = frame + 4 * (size_t)idx;
 			fb[0] = color.x; fb[1] = color.y; fb[2] = color.z; fb[3] = 1.0f;
 			depth[idx] = dot(cam_fwd, pos - cam_pos);
@@ -350,7 +376,9 @@ uint64_t orc_render_frame(const orc_scene* scene, const orc_render_params* p, co
 	std::memset(frame, 0, n * 4 * sizeof(float)); // render_buffer.cu:603 clear
 	std::memset(depth, 0, n * sizeof(float));
 	bool has_mesh = scene && !scene->meshes.empty();
-	if (has_mesh) render_mesh(*scene, *p, frame, depth);
+	Net* net = (params && p->envmap && p->env_samples > 0) ? net_new(*c, params) : nullptr;
+	if (has_mesh) render_mesh(*scene, *p, frame, depth, net, bitfield);
+	if (net) net_delete(net);
 	uint64_t total = 0;
 	if (params) total = orc_render_nerf(p, c, params, bitfield, frame, depth, n_steps_out, has_mesh ? 1 : 0);
 	return total;

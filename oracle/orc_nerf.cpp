@@ -427,6 +427,14 @@ void network_one(const Net& n, const float* coord, half_t out[4]) {
 	out[3] = rgb_in[0]; // extract_density: density MLP channel 0 -> output row 3
 }
 
+// density-only evaluation (NerfNetwork::density, nerf_network.h:291-318): encoding + density MLP, channel 0
+half_t density_one(const Net& n, const float* warped_pos) {
+	half_t enc[32], d_out[16];
+	encode_one(n.grid, n.table, warped_pos, enc);
+	mlp_forward(n.density, n.w_density, enc, d_out);
+	return d_out[0];
+}
+
 // ---------------------------------------------------------------- nerf_device.cuh:203-314
 static float logistic(float x) { return 1.0f / (1.0f + std::exp(-x)); }
 static float network_to_rgb(float v, int act) {
@@ -456,6 +464,65 @@ static float unwarp_dt(float dt) {
 	return dt * (max_stepsize - MIN_CONE_STEPSIZE) + MIN_CONE_STEPSIZE;
 }
 float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
+
+// ---------------------------------------------------------------- a-16: random_val.cuh:62-72,130-185, envmap.cuh:24-50
+static constexpr float PI_F = 3.14159265358979323846f;
+vec2 dir_to_spherical_unorm(vec3 d) {
+	float cos_theta = std::fmin(std::fmax(d.z, -1.0f), 1.0f);
+	float theta = std::acos(cos_theta);
+	float phi = std::atan2(d.y, d.x);
+	return {theta / PI_F, (phi / (2.0f * PI_F) + 0.5f)};
+}
+vec3 cosine_hemisphere(vec2 u) {
+	float r = std::sqrt(u.x);
+	float phi = 2.0f * PI_F * u.y;
+	vec3 p;
+	p.x = r * std::cos(phi);
+	p.y = r * std::sin(phi);
+	p.z = std::sqrt(std::fmax(0.0f, 1.0f - p.x * p.x - p.y * p.y));
+	return p;
+}
+vec3 spherical_cap_uniform(vec2 u, float cap_height) {
+	float z = (float)((double)(1.0f - cap_height) * (1.0 - (double)u.x) + (double)u.x); // the reference mixes a double literal in (random_val.cuh:147)
+	float r = std::sqrt(std::fmax(0.0f, 1.0f - z * z));
+	float phi = 2.0f * PI_F * u.y;
+	return {r * std::cos(phi), r * std::sin(phi), z};
+}
+mat3 compute_local_frame(vec3 lz) {
+	float x = lz.x, y = lz.y, z = lz.z;
+	float sz = (z >= 0) ? 1.0f : -1.0f;
+	float a = 1 / (sz + z);
+	float ya = y * a;
+	float b = x * ya;
+	float c = x * sz;
+	mat3 f;
+	f.c[0] = {c * x * a - 1, sz * b, c};
+	f.c[1] = {b, y * ya - sz, y};
+	f.c[2] = lz;
+	return f;
+}
+// envmap.cuh:24-50: lat-long lookup, bilinear, wrap in x, clamp in y
+vec4 read_envmap(const float* env, int w, int h, vec3 dir) {
+	vec2 cyl = dir_to_spherical_unorm({dir.z, -dir.x, dir.y});
+	float fx = cyl.y * (float)(w - 1), fy = cyl.x * (float)(h - 1);
+	int tx = (int)fx, ty = (int)fy;
+	float wx = fx - (float)tx, wy = fy - (float)ty;
+	auto rd = [&](int px, int py) -> vec4 {
+		if (px < 0) px += w; else if (px >= w) px -= w;
+		py = std::max(std::min(py, h - 1), 0);
+		const float* t = env + 4 * ((size_t)px + (size_t)py * w);
+		return {t[0], t[1], t[2], t[3]};
+	};
+	vec4 a = rd(tx, ty), b = rd(tx + 1, ty), c = rd(tx, ty + 1), d = rd(tx + 1, ty + 1);
+	float w00 = (1 - wx) * (1 - wy), w10 = wx * (1 - wy), w01 = (1 - wx) * wy, w11 = wx * wy;
+	return {w00 * a.x + w10 * b.x + w01 * c.x + w11 * d.x, w00 * a.y + w10 * b.y + w01 * c.y + w11 * d.y,
+		w00 * a.z + w10 * b.z + w01 * c.z + w11 * d.z, w00 * a.w + w10 * b.w + w01 * c.w + w11 * d.w};
+}
+// OUR definition (the reference's shading kernels are absent, SURVEY a-16): light direction k of pixel idx
+vec3 env_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, vec3 n) {
+	vec2 u = ld_random_val_2d(k + K * spp, idx * 786433u + 0x9E3779B9u);
+	return normalize(mul(compute_local_frame(n), cosine_hemisphere(u)));
+}
 
 // ---------------------------------------------------------------- per-pixel ray set-up: testbed_nerf.cu:1428-1544 + 333-381
 struct RayState { vec3 o, d; float t; bool alive; };
@@ -501,6 +568,12 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			uint32_t idx = x + p.width * y;
 			if (n_steps_out) n_steps_out[idx] = 0;
 			RayState r = init_ray(p, bits, x, y, &depth[idx]);
+			// :1526-1528 envmap -> frame buffer for every valid ray; in hybrid frames only where the mesh pass left nothing
+			if (p.envmap && !(depth_test && depth[idx] < MAX_DEPTH)) {
+				vec4 e = read_envmap(p.envmap, p.env_w, p.env_h, r.d);
+				float* fb = frame + 4 * (size_t)idx;
+				fb[0] = e.x; fb[1] = e.y; fb[2] = e.z; fb[3] = e.w;
+			}
 			if (!r.alive) continue;
 			Ray ray = {r.o, r.d};
 			vec3 idir = vec3{1.0f, 1.0f, 1.0f} / r.d;
@@ -555,6 +628,37 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 	return total;
 }
 
+// OUR definition (a-16): transmittance of the volume along a light ray from a mesh hit. Same AABB entry, DDA and step
+// sizes as the camera rays (no start jitter); density-only network evaluation; stops once T < min_transmittance.
+float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8_t* bits, vec3 o, vec3 d, uint32_t* n_out) {
+	BoundingBox render_aabb = bb_from(p.render_aabb), train_aabb = bb_from(p.train_aabb);
+	if (n_out) *n_out = 0;
+	float t = std::fmax(render_aabb.ray_intersect(o, d).x, 0.0f) + 1e-6f;
+	Ray ray = {o, d};
+	if (!render_aabb.contains(ray.at(t))) return 1.0f;
+	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / d;
+	float cone = p.cone_angle_constant;
+	float T = 1.0f;
+	uint32_t n = 0;
+	while (true) {
+		t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap);
+		if (t >= MAX_DEPTH) break;
+		float dt = calc_dt(t, cone);
+		vec3 wp = train_aabb.relative_pos(ray.at(t));
+		float coord[3] = {wp.x, wp.y, wp.z};
+		float sigma = network_to_density(h2f(density_one(net, coord)), p.density_activation);
+		T *= std::exp(-sigma * unwarp_dt(warp_dt(dt)));
+		++n;
+		if (T < p.min_transmittance) break;
+		t += dt;
+	}
+	if (n_out) *n_out = n;
+	return T;
+}
+
+Net* net_new(const orc_net_config& c, const uint16_t* params) { return new Net(make_net(c, params)); }
+void net_delete(Net* n) { delete n; }
+
 } // namespace orc
 
 using namespace orc;
@@ -576,6 +680,27 @@ float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const
 }
 float orc_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
 float orc_srgb_to_linear(float v) { return srgb_to_linear(v); }
+
+void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
+void orc_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm({d[0], d[1], d[2]}); out[0] = v.x; out[1] = v.y; }
+void orc_cosine_hemisphere(const float u[2], float out[3]) { vec3 v = cosine_hemisphere({u[0], u[1]}); out[0] = v.x; out[1] = v.y; out[2] = v.z; }
+void orc_spherical_cap(const float u[2], float cap_height, float out[3]) { vec3 v = spherical_cap_uniform({u[0], u[1]}, cap_height); out[0] = v.x; out[1] = v.y; out[2] = v.z; }
+void orc_compute_local_frame(const float z[3], float out[9]) {
+	mat3 f = compute_local_frame({z[0], z[1], z[2]});
+	for (int c = 0; c < 3; ++c) { out[3 * c] = f.c[c].x; out[3 * c + 1] = f.c[c].y; out[3 * c + 2] = f.c[c].z; }
+}
+void orc_read_envmap(const float* envmap, int32_t w, int32_t h, const float dir[3], float out[4]) {
+	vec4 v = read_envmap(envmap, w, h, {dir[0], dir[1], dir[2]});
+	out[0] = v.x; out[1] = v.y; out[2] = v.z; out[3] = v.w;
+}
+void orc_env_light_dirs(uint32_t idx, uint32_t spp, uint32_t K, const float n[3], float* out) {
+	for (uint32_t k = 0; k < K; ++k) { vec3 v = env_light_dir(idx, spp, K, k, {n[0], n[1], n[2]}); out[3 * k] = v.x; out[3 * k + 1] = v.y; out[3 * k + 2] = v.z; }
+}
+float orc_nerf_transmittance(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
+	const float o[3], const float d[3], uint32_t* n_samples_out) {
+	Net net = make_net(*c, params);
+	return nerf_transmittance(*p, net, bitfield, {o[0], o[1], o[2]}, {d[0], d[1], d[2]}, n_samples_out);
+}
 
 float orc_bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out) { return bitfield_from_grid(grid, n_cascades, out); }
 

@@ -81,4 +81,16 @@ float ref_start_t(uint32_t spp, uint32_t idx, const float o[3], const float d[3]
 	return if_unoccupied_advance_to_next_occupied_voxel(t, cone_angle, ray, idir, bitfield, 0, max_mip, b);
 }
 
+// a-16 sampling helpers (random_val.cuh:62-72,130-185), all NGP_HOST_DEVICE
+void ref_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
+void ref_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm(vec3(d[0], d[1], d[2])); out[0] = v.x; out[1] = v.y; }
+void ref_cosine_hemisphere(const float u[2], float out[3]) { vec3 v = cosine_hemisphere(vec2(u[0], u[1])); out[0] = v.x; out[1] = v.y; out[2] = v.z; }
+void ref_spherical_cap(const float u[2], float cap_height, float out[3]) {
+	vec3 v = warp_square_to_spherical_cap_uniform(vec2(u[0], u[1]), cap_height); out[0] = v.x; out[1] = v.y; out[2] = v.z;
+}
+void ref_compute_local_frame(const float z[3], float out[9]) {
+	mat3 f = compute_local_frame(vec3(z[0], z[1], z[2]));
+	for (int c = 0; c < 3; ++c) { out[3 * c] = f[c].x; out[3 * c + 1] = f[c].y; out[3 * c + 2] = f[c].z; }
+}
+
 }

@@ -125,6 +125,43 @@ def make_ref_host():
     print("ref_host.npz:", len(out), "arrays")
 
 
+def make_ref_env():
+    """a-16 sampling helpers of the reference (random_val.cuh), host-callable -> ref_host_env.npz"""
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_cosine_hemisphere"):
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing or stale: run `make -C oracle ref`")
+    rng = np.random.default_rng(20261105)
+    out = {}
+    n = 512
+    idx = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    seed = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    idx[:16] = np.arange(16)
+    v2 = np.zeros((n, 2), f32)
+    for i in range(n):
+        tmp = (C.c_float * 2)()
+        ref.ref_ld_random_val_2d(C.c_uint32(int(idx[i])), C.c_uint32(int(seed[i])), tmp)
+        v2[i] = tmp[:]
+    out["ld2_idx"], out["ld2_seed"], out["ld2_val"] = idx, seed, v2
+    d = rng.normal(size=(n, 3)).astype(f32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(f32)
+    d[0] = [0, 0, 1]; d[1] = [0, 0, -1]; d[2] = [1, 0, 0]; d[3] = [0, -1, 0]
+    sph = np.zeros((n, 2), f32); frm = np.zeros((n, 9), f32)
+    for i in range(n):
+        tmp = (C.c_float * 2)(); ref.ref_dir_to_spherical_unorm(fa(*d[i]), tmp); sph[i] = tmp[:]
+        t9 = (C.c_float * 9)(); ref.ref_compute_local_frame(fa(*d[i]), t9); frm[i] = t9[:]
+    out["dirs"], out["spherical_unorm"], out["local_frame"] = d, sph, frm
+    u = rng.uniform(0, 1, (n, 2)).astype(f32)
+    u[0] = [0, 0]; u[1] = [1, 1]; u[2] = [0.5, 0.25]
+    cos_h = np.zeros((n, 3), f32); cap = np.zeros((n, 3), f32)
+    caps = rng.uniform(0.01, 1.0, n).astype(f32)
+    for i in range(n):
+        t3 = (C.c_float * 3)(); ref.ref_cosine_hemisphere(fa(*u[i]), t3); cos_h[i] = t3[:]
+        t3 = (C.c_float * 3)(); ref.ref_spherical_cap(fa(*u[i]), C.c_float(float(caps[i])), t3); cap[i] = t3[:]
+    out["u"], out["cosine_hemisphere"], out["cap_height"], out["spherical_cap"] = u, cos_h, caps, cap
+    np.savez_compressed(os.path.join(HERE, "ref_host_env.npz"), **out)
+    print("ref_host_env.npz:", len(out), "arrays")
+
+
 class Info:
     pass
 
@@ -166,5 +203,9 @@ def make_oracle_pin():
 
 
 if __name__ == "__main__":
-    make_ref_host()
-    make_oracle_pin()
+    if len(sys.argv) > 1 and sys.argv[1] == "env":  # only the a-16 vectors (leaves the other files untouched)
+        make_ref_env()
+    else:
+        make_ref_host()
+        make_ref_env()
+        make_oracle_pin()

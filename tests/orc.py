@@ -37,7 +37,8 @@ class RenderParams(C.Structure):
                 ("render_aabb", f32 * 6), ("train_aabb", f32 * 6), ("max_mip", u32), ("cone_angle_constant", f32),
                 ("min_transmittance", f32), ("rgb_activation", i32), ("density_activation", i32), ("linear_colors", i32),
                 ("dda_iter_cap", i32), ("mesh_aabb", f32 * 6), ("sun_dir", f32 * 3), ("up_dir", f32 * 3), ("floor_y", f32),
-                ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32)]
+                ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32),
+                ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p)]
 
 
 def P(a):
@@ -66,12 +67,23 @@ lib.orc_bitfield_from_grid.argtypes = [C.c_void_p, u32, C.c_void_p]
 lib.orc_n_params.argtypes = [C.c_void_p]
 lib.orc_grid_param_offset.argtypes = [C.c_void_p]
 lib.orc_grid_layout.argtypes = [C.c_void_p] * 4
+lib.orc_ld_random_val_2d.argtypes = [u32, u32, C.c_void_p]
+lib.orc_dir_to_spherical_unorm.argtypes = [C.c_void_p, C.c_void_p]
+lib.orc_cosine_hemisphere.argtypes = [C.c_void_p, C.c_void_p]
+lib.orc_spherical_cap.argtypes = [C.c_void_p, f32, C.c_void_p]
+lib.orc_compute_local_frame.argtypes = [C.c_void_p, C.c_void_p]
+lib.orc_read_envmap.argtypes = [C.c_void_p, i32, i32, C.c_void_p, C.c_void_p]
+lib.orc_env_light_dirs.argtypes = [u32, u32, u32, C.c_void_p, C.c_void_p]
+lib.orc_nerf_transmittance.argtypes = [C.c_void_p] * 7
+lib.orc_nerf_transmittance.restype = f32
 
 if ref is not None:
     for name in ("ref_ld_random_val", "ref_triangle_ray_intersect", "ref_advance_to_occupied", "ref_calc_dt", "ref_advance_n_steps",
                  "ref_srgb_to_linear", "ref_warp_dt", "ref_unwarp_dt", "ref_start_t"):
         getattr(ref, name).restype = f32
     ref.ref_morton3D.restype = u32
+    if hasattr(ref, "ref_cosine_hemisphere"):
+        ref.ref_spherical_cap.argtypes = [C.c_void_p, f32, C.c_void_p]
 
 DEFAULT_BRDF = [0.0, 0.0, 1.0, 0.5, 0.0, 0.0, 0.0, 0.8, 0.8, 0.8, 0.0, 0.0, 0.0, 0.0, 0.0]
 
@@ -90,7 +102,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   render_aabb=(0, 0, 0, 1, 1, 1), train_aabb=(0, 0, 0, 1, 1, 1), max_mip=0, cone=0.0, min_transmittance=0.01,
                   rgb_act=2, density_act=3, linear_colors=False, dda_iter_cap=0, mesh_aabb=(0, 0, 0, 1, 1, 1),
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
-                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None) -> RenderParams:
+                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -119,6 +131,12 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.brdf[:] = list(brdf) if brdf is not None else DEFAULT_BRDF
     p.compat_nearest_aabb_only, p.depth_merge_clip = int(compat), int(clip)
     p.n_threads = n_threads if n_threads is not None else (os.cpu_count() or 1)
+    if envmap is not None:
+        env = np.ascontiguousarray(envmap, np.float32)
+        assert env.ndim == 3 and env.shape[2] == 4
+        p._env_keep = env  # keep the buffer alive as long as the params
+        p.env_h, p.env_w, p.env_samples = env.shape[0], env.shape[1], int(env_samples)
+        p.envmap = env.ctypes.data
     return p
 
 
@@ -188,6 +206,29 @@ def network(cfg: NetConfig, params, coords):
     out = np.empty((c.shape[0], 4), np.float16)
     lib.orc_network(C.byref(cfg), P(params), P(c), c.shape[0], P(out))
     return out
+
+
+def read_envmap(env, dirs):
+    env = np.ascontiguousarray(env, np.float32)
+    d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+    out = np.empty((d.shape[0], 4), np.float32)
+    for i in range(d.shape[0]):
+        lib.orc_read_envmap(P(env), env.shape[1], env.shape[0], P(d[i]), P(out[i]))
+    return out
+
+
+def env_light_dirs(idx, spp, K, normal):
+    n = np.ascontiguousarray(normal, np.float32)
+    out = np.empty((K, 3), np.float32)
+    lib.orc_env_light_dirs(int(idx), int(spp), int(K), P(n), P(out))
+    return out
+
+
+def nerf_transmittance(p: RenderParams, cfg, params, bits, o, d):
+    o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+    n = C.c_uint32(0)
+    T = lib.orc_nerf_transmittance(C.byref(p), C.byref(cfg), P(params), P(bits), P(o), P(d), C.byref(n))
+    return float(T), int(n.value)
 
 
 def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):

@@ -70,6 +70,20 @@ int hn_build_scene(hn_context* ctx);                                            
 int hn_clear_scene(hn_context* ctx);
 int hn_get_scene_aabb(const hn_context* ctx, float out[6]);                           /* root box of all meshes (before inflation) */
 
+/* ---- environment map (a-16) ---- */
+/* rgba: float[height][width][4] HOST, lat-long (read_envmap, envmap.cuh:24-50; Testbed::m_envmap, testbed.h:1227-1241).
+ * Background of camera rays (src/testbed_nerf.cu:1526-1528) and, with option "env_light_samples" = K > 0, light source of the
+ * mesh pass: K cosine-weighted light rays per mesh hit, each a shadow ray through the BVH and a transmittance march through
+ * the NeRF (the reference declares computeEnvmap / shade_from_nerf, testbed.h:394-407,709-743, without defining them).
+ * rgba == NULL removes the map. */
+int hn_set_envmap(hn_context* ctx, const float* rgba, int width, int height);
+/* a-16 operator entry points (host in/out): envmap lookup for n unit directions -> out[n][4];
+ * the K light directions of pixel `pixel_index` at sample index spp around unit normal n -> out[K][3];
+ * NeRF transmittance along n rays (origin, unit dir) -> T[n], samples taken [n] (may be NULL). */
+int hn_op_read_envmap(hn_context* ctx, const float* dirs, uint32_t n, float* out);
+int hn_op_env_light_dirs(hn_context* ctx, uint32_t pixel_index, uint32_t spp_index, uint32_t K, const float normal[3], float* out);
+int hn_op_transmittance(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, float* T, uint32_t* n_samples);
+
 /* ---- render state (public Testbed members; names follow src/python_api.cu:482-567) ---- */
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values);
 int hn_get_option(const hn_context* ctx, const char* name, float* values, int n_values);
@@ -102,6 +116,12 @@ typedef struct {
 	uint32_t n_passes;         /* march/eval/composite rounds */
 	uint32_t n_kernel_launches;
 	float ms_mesh, ms_raygen, ms_march, ms_eval, ms_composite, ms_total; /* filled when option "profile" = 1 */
+	/* a-16 environment light pass */
+	float ms_envlight;         /* whole pass (generation + shadow rays + volume march + reduce) */
+	uint32_t n_env_hits;       /* mesh hits that gathered light */
+	uint64_t n_light_rays;     /* light rays traced through the BVH */
+	uint64_t n_light_rays_volume; /* of those, rays that entered the NeRF volume */
+	uint64_t n_light_samples;  /* density-network samples evaluated for them */
 } hn_frame_stats;
 int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out);
 

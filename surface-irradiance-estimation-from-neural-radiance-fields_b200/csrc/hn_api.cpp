@@ -189,6 +189,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
 		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
 		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -285,6 +286,8 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	a.floor_y = o.floor_enable ? o.mesh_aabb[1] + 0.001f : -10000.f; // get_floor_y, testbed.h:1019
 	std::memcpy(a.brdf, o.brdf, sizeof(a.brdf));
 	a.compat_nearest_aabb_only = o.compat_nearest_aabb_only;
+	a.envmap = ctx->envmap.p; a.env_w = ctx->env_w; a.env_h = ctx->env_h; // nullptr = no map
+	a.env_samples = ctx->envmap.p ? std::max(o.env_light_samples, 0) : 0;
 	return a;
 }
 
@@ -310,6 +313,118 @@ struct Timer {
 	void stop(float& acc) { if (on) { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); acc += ms; } }
 };
 
+// The march / network / composite rounds over a live-ray list whose initial count sits in counters[CNT_ALIVE_A].
+// light == false: camera rays (colour compositing into the frame); light == true: a-16 light rays (density-only network
+// evaluation, transmittance only). Returns the number of rays that entered the loop.
+// No host round trip per pass (the reference blocks on the alive counter every pass, src/testbed_nerf.cu:2071-2072): every
+// kernel reads its ray count from device memory, the host only needs an upper bound for grid and buffer sizes (the
+// live-ray count never grows) and the moment it reaches zero. The count entering pass j is copied to a pinned ring slot
+// after pass j-1 and looked at LAG passes later, so the stream always holds LAG passes of queued work; at most LAG empty
+// passes run at the end.
+uint32_t run_passes(hn_context* ctx, const FrameArgs& a, RaySoA rays, float4* frame, float* depth, bool light, cudaStream_t s, Timer& tm) {
+	hn_frame_stats& st = ctx->stats;
+	uint32_t* cnt = ctx->counters.p;
+	uint32_t* lists[2] = {ctx->alive_a.p, ctx->alive_b.p};
+	int cur = 0;
+	const int LAG = ctx->opt.profile ? 0 : 1;
+	constexpr int RING = 4;
+	HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	uint32_t n_alive = ctx->pinned_counters[CNT_ALIVE_A]; // exact for the first pass, an upper bound afterwards
+	const uint32_t n_first = n_alive;
+	need(n_alive <= ctx->alive_a.n, "alive counter corrupt");
+	uint32_t passes = 0;
+	float ms_dummy = 0.f;
+	for (int k = 0; n_alive > 0; ++k) {
+		const int j = k - LAG; // newest pass whose entry count must be known before pass k is queued
+		if (j >= 1) {
+			HN_CUDA(cudaEventSynchronize(ctx->pass_events[j % RING]));
+			const uint32_t n = ctx->pinned_counters[(j % RING) * CNT_N + ((j & 1) ? CNT_ALIVE_B : CNT_ALIVE_A)];
+			if (n == 0) { passes = (uint32_t)j; break; }
+			need(n <= n_alive, "alive counter corrupt");
+			n_alive = n;
+		}
+		passes = (uint32_t)k + 1;
+		ctx->samples.ensure((size_t)n_alive * CHUNK);
+		ctx->net_out.ensure((size_t)n_alive * CHUNK);
+		uint32_t* n_alive_ptr = cnt + (cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B);
+		uint32_t* n_next_ptr = cnt + (cur == 0 ? CNT_ALIVE_B : CNT_ALIVE_A);
+		HN_CUDA(cudaMemsetAsync(n_next_ptr, 0, sizeof(uint32_t), s));
+		tm.start();
+		launch_march(a, ctx->bitfield.p, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, cnt, depth, n_alive, s);
+		tm.stop(light ? ms_dummy : st.ms_march);
+		tm.start();
+		const bool fused = !light && ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite;
+		if (fused) ctx->survive.ensure(n_alive);
+		launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p,
+			ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s, light);
+		tm.stop(light ? ms_dummy : st.ms_eval);
+		tm.start();
+		const bool per_ray = !light && !fused && ctx->opt.composite_impl == 1;
+		if (light) {
+			ctx->survive.ensure(n_alive);
+			launch_transmittance(a, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, ctx->survive.p, cnt, n_alive, s);
+			st.n_kernel_launches += 1;
+		} else if (per_ray) {
+			ctx->survive.ensure(n_alive);
+			launch_composite_rays(make_comp_args(a, rays, lists[cur], ctx->samples.p, frame, depth, ctx->survive.p, cnt), n_alive_ptr, ctx->sample_counts.p, ctx->net_out.p, n_alive, s);
+			st.n_kernel_launches += 1;
+		}
+		if (light || fused || per_ray) launch_compact(lists[cur], n_alive_ptr, ctx->survive.p, lists[cur ^ 1], n_next_ptr, n_alive, s);
+		else launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
+		tm.stop(light ? ms_dummy : st.ms_composite);
+		st.n_kernel_launches += 3;
+		cur ^= 1;
+		HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters + ((k + 1) % RING) * CNT_N, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+		HN_CUDA(cudaEventRecord(ctx->pass_events[(k + 1) % RING], s));
+	}
+	if (!light) st.n_passes = passes;
+	HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	return n_first;
+}
+
+EnvHits env_hits(hn_context* ctx) {
+	EnvHits h;
+	h.pos_pix = ctx->hit_pos_pix.p; h.nrm = ctx->hit_nrm.p; h.albedo = ctx->hit_albedo.p; h.count = ctx->hit_count.p;
+	return h;
+}
+
+// a-16: environment light on the mesh hits the mesh pass listed. Batches of hits so that at most env_light_batch light
+// rays are in flight: generate (direction, shadow ray, envmap radiance) -> enter the volume -> transmittance passes -> reduce.
+void env_light_pass(hn_context* ctx, const FrameArgs& a_in, float4* frame, float* depth, cudaStream_t s, Timer& tm) {
+	hn_frame_stats& st = ctx->stats;
+	FrameArgs a = a_in;
+	a.depth_test = 0; a.depth_clip = 0; // light rays are not clipped by the camera's mesh depth
+	uint32_t n_hits = 0;
+	HN_CUDA(cudaMemcpyAsync(&n_hits, ctx->hit_count.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	st.n_env_hits = n_hits;
+	if (!n_hits) return;
+	const uint32_t K = (uint32_t)a.env_samples;
+	const bool volume = ctx->opt.render_nerf && ctx->has_net && ctx->has_params && ctx->has_bitfield;
+	const uint32_t per_batch = std::max<uint32_t>(1u, (uint32_t)std::max(ctx->opt.env_light_batch, 1) / K);
+	uint32_t* cnt = ctx->counters.p;
+	for (uint32_t first = 0; first < n_hits; first += per_batch) {
+		const uint32_t n = std::min(per_batch, n_hits - first);
+		const size_t n_rays = (size_t)n * K;
+		ensure_rays(ctx, n_rays);
+		RaySoA rays = ray_soa(ctx);
+		launch_envlight_gen(a, ctx->scene_dev(), env_hits(ctx), first, n, rays, s);
+		st.n_kernel_launches += 1;
+		st.n_light_rays += n_rays;
+		if (volume) {
+			HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
+			launch_secondary_start(a, ctx->bitfield.p, rays, (uint32_t)n_rays, ctx->alive_a.p, cnt, s);
+			st.n_kernel_launches += 1;
+			st.n_light_rays_volume += run_passes(ctx, a, rays, frame, depth, true, s, tm);
+			st.n_light_samples += (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);
+		}
+		launch_envlight_reduce(a, env_hits(ctx), first, n, rays, frame, s);
+		st.n_kernel_launches += 1;
+	}
+}
+
 void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame, float* depth, cudaStream_t s) {
 	FrameArgs a = args_in;
 	const size_t n_px = (size_t)a.w * a.h;
@@ -323,10 +438,23 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 	const bool do_mesh = ctx->opt.render_mesh && !ctx->meshes.empty();
 	if (do_mesh) {
 		need(ctx->scene_built, "scene has meshes but hn_build_scene was not called");
+		const bool env_light = a.envmap && a.env_samples > 0;
+		EnvHits hits = {nullptr, nullptr, nullptr, nullptr};
+		if (env_light) {
+			ctx->hit_pos_pix.ensure(n_px); ctx->hit_nrm.ensure(n_px); ctx->hit_albedo.ensure(n_px); ctx->hit_count.ensure(1);
+			HN_CUDA(cudaMemsetAsync(ctx->hit_count.p, 0, sizeof(uint32_t), s));
+			hits = env_hits(ctx);
+		}
 		tm.start();
-		launch_mesh_pass(a, ctx->scene_dev(), frame, depth, s);
+		launch_mesh_pass(a, ctx->scene_dev(), frame, depth, hits, s);
 		st.n_kernel_launches += 1;
 		tm.stop(st.ms_mesh);
+		if (env_light) {
+			Timer te(ctx->opt.profile != 0, s);
+			te.start();
+			env_light_pass(ctx, a, frame, depth, s, tm);
+			te.stop(st.ms_envlight);
+		}
 		a.depth_test = 1;
 	}
 	if (ctx->opt.render_nerf && ctx->has_net) {
@@ -337,64 +465,10 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 		HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
 		RaySoA rays = ray_soa(ctx);
 		tm.start();
-		launch_raygen(a, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth, s);
+		launch_raygen(a, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth, frame, s);
 		st.n_kernel_launches += 1;
 		tm.stop(st.ms_raygen);
-		uint32_t* lists[2] = {ctx->alive_a.p, ctx->alive_b.p};
-		int cur = 0;
-		// Pass loop without a host round trip per pass (the reference blocks on the alive counter every pass,
-		// src/testbed_nerf.cu:2071-2072): every kernel reads its ray count from device memory, the host only needs an
-		// upper bound for grid and buffer sizes (the live-ray count never grows) and the moment it reaches zero. The
-		// count entering pass j is copied to a pinned ring slot after pass j-1 and looked at LAG passes later, so the
-		// stream always holds LAG passes of queued work; at most LAG empty passes run at the end of a frame.
-		const int LAG = ctx->opt.profile ? 0 : 1;
-		constexpr int RING = 4;
-		HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-		HN_CUDA(cudaStreamSynchronize(s));
-		uint32_t n_alive = ctx->pinned_counters[CNT_ALIVE_A]; // exact for the first pass, an upper bound afterwards
-		st.n_rays_alive = n_alive;
-		need(n_alive <= n_px, "alive counter corrupt");
-		for (int k = 0; n_alive > 0; ++k) {
-			const int j = k - LAG; // newest pass whose entry count must be known before pass k is queued
-			if (j >= 1) {
-				HN_CUDA(cudaEventSynchronize(ctx->pass_events[j % RING]));
-				const uint32_t n = ctx->pinned_counters[(j % RING) * CNT_N + ((j & 1) ? CNT_ALIVE_B : CNT_ALIVE_A)];
-				if (n == 0) { st.n_passes = (uint32_t)j; break; }
-				need(n <= n_alive, "alive counter corrupt");
-				n_alive = n;
-			}
-			st.n_passes = (uint32_t)k + 1;
-			ctx->samples.ensure((size_t)n_alive * CHUNK);
-			ctx->net_out.ensure((size_t)n_alive * CHUNK);
-			uint32_t* n_alive_ptr = cnt + (cur == 0 ? CNT_ALIVE_A : CNT_ALIVE_B);
-			uint32_t* n_next_ptr = cnt + (cur == 0 ? CNT_ALIVE_B : CNT_ALIVE_A);
-			HN_CUDA(cudaMemsetAsync(n_next_ptr, 0, sizeof(uint32_t), s));
-			tm.start();
-			launch_march(a, ctx->bitfield.p, rays, lists[cur], n_alive_ptr, ctx->samples.p, ctx->sample_counts.p, cnt, depth, n_alive, s);
-			tm.stop(st.ms_march);
-			tm.start();
-			const bool fused = ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite;
-			if (fused) ctx->survive.ensure(n_alive);
-			launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p,
-				ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s);
-			tm.stop(st.ms_eval);
-			tm.start();
-			const bool per_ray = !fused && ctx->opt.composite_impl == 1;
-			if (per_ray) {
-				ctx->survive.ensure(n_alive);
-				launch_composite_rays(make_comp_args(a, rays, lists[cur], ctx->samples.p, frame, depth, ctx->survive.p, cnt), n_alive_ptr, ctx->sample_counts.p, ctx->net_out.p, n_alive, s);
-				st.n_kernel_launches += 1;
-			}
-			if (fused || per_ray) launch_compact(lists[cur], n_alive_ptr, ctx->survive.p, lists[cur ^ 1], n_next_ptr, n_alive, s);
-			else launch_composite(a, rays, lists[cur], n_alive_ptr, lists[cur ^ 1], cnt, ctx->samples.p, ctx->sample_counts.p, ctx->net_out.p, frame, depth, n_alive, s);
-			tm.stop(st.ms_composite);
-			st.n_kernel_launches += 3;
-			cur ^= 1;
-			HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters + ((k + 1) % RING) * CNT_N, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-			HN_CUDA(cudaEventRecord(ctx->pass_events[(k + 1) % RING], s));
-		}
-		HN_CUDA(cudaMemcpyAsync(ctx->pinned_counters, cnt, CNT_N * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-		HN_CUDA(cudaStreamSynchronize(s));
+		st.n_rays_alive = run_passes(ctx, a, rays, frame, depth, false, s, tm);
 		st.n_samples = (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);
 		st.n_samples_composited = (uint64_t)ctx->pinned_counters[CNT_COMPOSITED_LO] | ((uint64_t)ctx->pinned_counters[CNT_COMPOSITED_HI] << 32);
 	}
@@ -435,6 +509,8 @@ int hn_render_to_host(hn_context* ctx, int width, int height, int spp, int linea
 		acc.n_rays_alive = ctx->stats.n_rays_alive;
 		acc.ms_mesh += ctx->stats.ms_mesh; acc.ms_raygen += ctx->stats.ms_raygen; acc.ms_march += ctx->stats.ms_march; acc.ms_eval += ctx->stats.ms_eval;
 		acc.ms_composite += ctx->stats.ms_composite; acc.ms_total += ctx->stats.ms_total;
+		acc.ms_envlight += ctx->stats.ms_envlight; acc.n_env_hits = ctx->stats.n_env_hits; acc.n_light_rays += ctx->stats.n_light_rays;
+		acc.n_light_rays_volume += ctx->stats.n_light_rays_volume; acc.n_light_samples += ctx->stats.n_light_samples;
 	}
 	launch_tonemap(ctx->accum.p, ctx->tonemapped.p, (uint32_t)n, linear ? 0 : 1, ctx->opt.exposure, ctx->opt.background_color, ctx->stream);
 	launches += 1;
@@ -507,6 +583,76 @@ int hn_op_march_all(hn_context* ctx, uint32_t n, const float* origins, const flo
 	HN_CUDA(cudaMemcpyAsync(counts, d_c, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	if (d_s) HN_CUDA(cudaMemcpyAsync(samples, d_s, (size_t)n * max_per_ray * 16, cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+int hn_set_envmap(hn_context* ctx, const float* rgba, int width, int height) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (!rgba) { ctx->envmap.release(); ctx->env_w = ctx->env_h = 0; return 0; }
+	need(width >= 2 && height >= 2, "envmap must be at least 2x2");
+	ctx->envmap.release();
+	ctx->envmap.ensure((size_t)width * height);
+	HN_CUDA(cudaMemcpy(ctx->envmap.p, rgba, (size_t)width * height * sizeof(float4), cudaMemcpyHostToDevice));
+	ctx->env_w = width; ctx->env_h = height;
+	HN_CATCH(ctx)
+}
+
+int hn_op_read_envmap(hn_context* ctx, const float* dirs, uint32_t n, float* out) {
+	HN_TRY(ctx)
+	need(ctx->envmap.p != nullptr, "no environment map set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const float rs[4] = {0, 0, 0, 1};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	float* d_d = scratch<float>(ctx, 0, (size_t)n * 3); float4* d_o = scratch<float4>(ctx, 1, n);
+	HN_CUDA(cudaMemcpyAsync(d_d, dirs, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	launch_op_read_envmap(a, d_d, n, d_o, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+int hn_op_env_light_dirs(hn_context* ctx, uint32_t pixel_index, uint32_t spp_index, uint32_t K, const float normal[3], float* out) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	float* d_o = scratch<float>(ctx, 0, (size_t)K * 3);
+	launch_op_env_light_dirs(pixel_index, spp_index, K, normal, d_o, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)K * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+// the volume half of the env-light pass on caller-given rays: enter the volume, density-only passes, transmittance
+int hn_op_transmittance(hn_context* ctx, uint32_t n, const float* origins, const float* dirs, float* T, uint32_t* n_samples) {
+	HN_TRY(ctx)
+	need(ctx->has_net && ctx->has_params && ctx->has_bitfield, "network, parameters and occupancy grid must be set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (!n) return 0;
+	cudaStream_t s = ctx->stream;
+	const float rs[4] = {0, 0, 0, 1};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	a.depth_test = 0; a.depth_clip = 0;
+	ensure_rays(ctx, n);
+	RaySoA rays = ray_soa(ctx);
+	std::vector<float4> h_o(n), h_d(n), h_c(n, make_float4(1.f, 1.f, 1.f, 1.f));
+	for (uint32_t i = 0; i < n; ++i) {
+		h_o[i] = make_float4(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2], 0.f);
+		h_d[i] = make_float4(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2], 0.f);
+	}
+	HN_CUDA(cudaMemcpyAsync(rays.o_t, h_o.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(rays.d_mw, h_d.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(rays.rgba, h_c.data(), (size_t)n * 16, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemsetAsync(rays.n_steps, 0, (size_t)n * 4, s));
+	HN_CUDA(cudaMemsetAsync(rays.pixel, 0, (size_t)n * 4, s));
+	HN_CUDA(cudaMemsetAsync(ctx->counters.p, 0, CNT_N * sizeof(uint32_t), s));
+	launch_secondary_start(a, ctx->bitfield.p, rays, n, ctx->alive_a.p, ctx->counters.p, s);
+	Timer tm(false, s);
+	ctx->stats = hn_frame_stats{};
+	run_passes(ctx, a, rays, nullptr, nullptr, true, s, tm);
+	HN_CUDA(cudaMemcpyAsync(h_c.data(), rays.rgba, (size_t)n * 16, cudaMemcpyDeviceToHost, s));
+	if (n_samples) HN_CUDA(cudaMemcpyAsync(n_samples, rays.n_steps, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	for (uint32_t i = 0; i < n; ++i) T[i] = h_c[i].w;
 	HN_CATCH(ctx)
 }
 

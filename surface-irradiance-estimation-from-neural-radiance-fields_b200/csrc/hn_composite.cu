@@ -229,6 +229,55 @@ void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const
 	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out);
 }
 
+// a-16 light rays: one warp per ray chunk, lane j = sample j. T_j = T_in * prod_{k<=j} exp(-sigma_k dt_k) (warp product scan);
+// the ray ends at the first sample with T_j < min_transmittance (oracle nerf_transmittance) or when it leaves the volume.
+__global__ void __launch_bounds__(512) transmittance_kernel(FrameArgs a, RaySoA rays, const uint32_t* __restrict__ alive_list,
+	const uint32_t* __restrict__ n_alive_ptr, const float4* __restrict__ samples, const uint32_t* __restrict__ sample_counts,
+	const uint2* __restrict__ net_out, uint32_t* __restrict__ survive, uint32_t* __restrict__ counters) {
+	__shared__ uint32_t block_total;
+	if (threadIdx.x == 0) block_total = 0;
+	__syncthreads();
+	const uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t lane = threadIdx.x & 31u;
+	if (chunk < *n_alive_ptr) { // warp-uniform
+		const uint32_t count = sample_counts[chunk];
+		const uint32_t r = alive_list[chunk];
+		const float T_in = rays.rgba[r].w;
+		float f = 1.0f;
+		if (lane < count) {
+			const size_t si = (size_t)chunk * CHUNK + lane;
+			const uint2 o = __ldg(net_out + si);
+			const float dt_in = __ldg(&samples[si].w);
+			const __half2 bs = *reinterpret_cast<const __half2*>(&o.y);
+			const float sigma = act_density(__high2float(bs), a.density_act);
+			const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP);
+			const float dt = __fadd_rn(__fmul_rn(__fdiv_rn(__fsub_rn(dt_in, HN_MIN_STEP), dt_range), dt_range), HN_MIN_STEP);
+			f = __expf(-sigma * dt);
+		}
+		float P = f;
+		#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const float up = __shfl_up_sync(0xffffffffu, P, d);
+			if (lane >= (uint32_t)d) P *= up;
+		}
+		const float T = T_in * P;
+		const uint32_t term_mask = __ballot_sync(0xffffffffu, lane < count && T < a.min_transmittance);
+		const uint32_t last = term_mask ? (uint32_t)(__ffs(term_mask) - 1) : (count ? count - 1 : 0u);
+		const float T_out = __shfl_sync(0xffffffffu, T, last);
+		if (lane == 0) {
+			if (count) { rays.rgba[r].w = T_out; rays.n_steps[r] += last + 1; atomicAdd(&block_total, last + 1); }
+			survive[chunk] = (!term_mask && count == CHUNK) ? 1u : 0u;
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x == 0 && block_total) atomicAdd((unsigned long long*)&counters[CNT_COMPOSITED_LO], (unsigned long long)block_total);
+}
+void launch_transmittance(const FrameArgs& a, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr, const float4* samples,
+	const uint32_t* sample_counts, const uint2* net_out, uint32_t* survive, uint32_t* counters, uint32_t max_rays, cudaStream_t s) {
+	if (!max_rays) return;
+	transmittance_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, rays, alive_list, n_alive_ptr, samples, sample_counts, net_out, survive, counters);
+}
+
 // next pass's live-ray list from the survive flags of the fused network+composite kernel (one atomic per warp)
 __global__ void __launch_bounds__(256) compact_kernel(const uint32_t* __restrict__ alive_in, const uint32_t* __restrict__ n_alive_ptr,
 	const uint32_t* __restrict__ survive, uint32_t* __restrict__ alive_out, uint32_t* __restrict__ n_alive_out) {

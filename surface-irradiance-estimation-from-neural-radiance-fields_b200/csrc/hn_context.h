@@ -71,6 +71,8 @@ struct Options {
 	int fuse_composite = 0;                     // 1 = composite inside the tcgen05 network kernel (eval_impl 1 only; measured slower, kept as an option)
 	int composite_impl = 1;                     // 1 = one warp per ray + compact kernel, 0 = 32 rays per warp with in-kernel compaction
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
+	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
+	int env_light_batch = 8 << 20;              // light rays in flight per batch (bounds the workspace)
 	int mesh_aabb_user = 0;
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
 };
@@ -105,6 +107,12 @@ struct hn_context {
 	hn::DevBuf<hn::Node4> d_nodes;
 	hn::DevBuf<float4> d_tris;
 	hn::DevBuf<hn::MeshDev> d_meshes;
+
+	// environment map (a-16)
+	hn::DevBuf<float4> envmap;
+	int env_w = 0, env_h = 0;
+	hn::DevBuf<float4> hit_pos_pix, hit_nrm, hit_albedo;
+	hn::DevBuf<uint32_t> hit_count;
 
 	hn::Options opt;
 	float camera[12] = {1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5f, 0.5f, 2.0f}; // reset_camera default (src/testbed.cu:541-568)

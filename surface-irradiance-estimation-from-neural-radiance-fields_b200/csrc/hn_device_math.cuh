@@ -105,4 +105,73 @@ __host__ __device__ __forceinline__ float hn_ld_random_val(uint32_t index, uint3
 	return (float)hn_owen(hn_reverse_bits(index), hn_hash_combine(seed, 0u)) * 2.3283064365386963e-10f; // 2^-32
 }
 
+// dimension 1 of the Sobol sequence: v_j = v_{j-1} ^ (v_{j-1} >> 1) (random_val.cuh:207-300)
+__host__ __device__ __forceinline__ uint32_t hn_sobol_dim1(uint32_t index) {
+	uint32_t X = 0, v = 0x80000000u;
+	for (uint32_t bit = 0; bit < 32; ++bit) {
+		if ((index >> bit) & 1u) X ^= v;
+		v ^= v >> 1;
+	}
+	return X;
+}
+__host__ __device__ __forceinline__ float2 hn_ld_random_val_2d(uint32_t index, uint32_t seed) {
+	index = hn_owen(index, seed);
+	float2 r;
+	r.x = (float)hn_owen(hn_reverse_bits(index), hn_hash_combine(seed, 0u)) * 2.3283064365386963e-10f;
+	r.y = (float)hn_owen(hn_sobol_dim1(index), hn_hash_combine(seed, 1u)) * 2.3283064365386963e-10f;
+	return r;
+}
+
+// ---- a-16: environment map + light-direction sampling (random_val.cuh:62-72,130-185, envmap.cuh:24-50) ----
+#define HN_PI_F 3.14159265358979323846f
+__device__ __forceinline__ float2 dir_to_spherical_unorm(V3 d) {
+	const float cos_theta = fminf(fmaxf(d.z, -1.0f), 1.0f);
+	const float theta = acosf(cos_theta);
+	const float phi = atan2f(d.y, d.x);
+	return make_float2(theta / HN_PI_F, (phi / (2.0f * HN_PI_F) + 0.5f));
+}
+__device__ __forceinline__ V3 cosine_hemisphere(float2 u) {
+	const float r = sqrtf(u.x);
+	const float phi = 2.0f * HN_PI_F * u.y;
+	V3 p;
+	p.x = r * cosf(phi);
+	p.y = r * sinf(phi);
+	p.z = sqrtf(fmaxf(0.0f, 1.0f - p.x * p.x - p.y * p.y));
+	return p;
+}
+// compute_local_frame (random_val.cuh:167-185) applied to a local vector: columns X, Y, Z = n
+__device__ __forceinline__ V3 local_frame_apply(V3 n, V3 l) {
+	const float sz = (n.z >= 0) ? 1.0f : -1.0f;
+	const float a = 1 / (sz + n.z);
+	const float ya = n.y * a;
+	const float b = n.x * ya;
+	const float c = n.x * sz;
+	const V3 X = mk(c * n.x * a - 1, sz * b, c), Y = mk(b, n.y * ya - sz, n.y);
+	V3 r = mk(0.0f, 0.0f, 0.0f);
+	r.x += X.x * l.x; r.y += X.y * l.x; r.z += X.z * l.x;
+	r.x += Y.x * l.y; r.y += Y.y * l.y; r.z += Y.z * l.y;
+	r.x += n.x * l.z; r.y += n.y * l.z; r.z += n.z * l.z;
+	return r;
+}
+// light direction k of K of pixel idx (OUR definition, oracle env_light_dir)
+__device__ __forceinline__ V3 env_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, V3 n) {
+	const float2 u = hn_ld_random_val_2d(k + K * spp, idx * 786433u + 0x9E3779B9u);
+	return normalize3(local_frame_apply(n, cosine_hemisphere(u)));
+}
+__device__ __forceinline__ float4 read_envmap(const float4* __restrict__ env, int w, int h, V3 dir) {
+	const float2 cyl = dir_to_spherical_unorm(mk(dir.z, -dir.x, dir.y));
+	const float fx = cyl.y * (float)(w - 1), fy = cyl.x * (float)(h - 1);
+	const int tx = (int)fx, ty = (int)fy;
+	const float wx = fx - (float)tx, wy = fy - (float)ty;
+	int x0 = tx, x1 = tx + 1;
+	if (x0 < 0) x0 += w; else if (x0 >= w) x0 -= w;
+	if (x1 < 0) x1 += w; else if (x1 >= w) x1 -= w;
+	const int y0 = max(min(ty, h - 1), 0), y1 = max(min(ty + 1, h - 1), 0);
+	const float4 a = __ldg(env + x0 + (size_t)y0 * w), b = __ldg(env + x1 + (size_t)y0 * w);
+	const float4 c = __ldg(env + x0 + (size_t)y1 * w), d = __ldg(env + x1 + (size_t)y1 * w);
+	const float w00 = (1 - wx) * (1 - wy), w10 = wx * (1 - wy), w01 = (1 - wx) * wy, w11 = wx * wy;
+	return make_float4(w00 * a.x + w10 * b.x + w01 * c.x + w11 * d.x, w00 * a.y + w10 * b.y + w01 * c.y + w11 * d.y,
+		w00 * a.z + w10 * b.z + w01 * c.z + w11 * d.z, w00 * a.w + w10 * b.w + w01 * c.w + w11 * d.w);
+}
+
 } // namespace hn

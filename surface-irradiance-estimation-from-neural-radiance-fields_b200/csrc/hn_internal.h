@@ -64,6 +64,17 @@ struct FrameArgs {
 	float floor_y;
 	float brdf[13]; // metallic subsurface specular roughness sheen clearcoat clearcoat_gloss basecolor[3] ambientcolor[3]
 	int compat_nearest_aabb_only;
+	// a-16 environment map (device, lat-long float4 [env_h][env_w]); env_samples = K light directions per mesh hit
+	const float4* envmap;
+	int env_w, env_h, env_samples;
+};
+
+// mesh hits that gather environment light: filled by the mesh pass (one entry per shaded triangle hit, warp-aggregated append)
+struct EnvHits {
+	float4* pos_pix;   // hit position (already offset along the facing normal), pixel index bits in .w
+	float4* nrm;       // viewer-facing unit normal
+	float4* albedo;    // Lambertian albedo of the hit (floor checker or basecolor^2)
+	uint32_t* count;   // device counter
 };
 
 // ---- ray state, SoA, indexed by ray id (assigned at ray generation) ----
@@ -103,7 +114,7 @@ void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thres
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s);
 void launch_occ_bounds(const uint8_t* bits, int* out, cudaStream_t s);
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters,
-	float* depth_buffer, cudaStream_t s);
+	float* depth_buffer, float4* frame, cudaStream_t s);
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s);
 void launch_march(const FrameArgs& a, const uint8_t* bits, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr,
 	float4* samples, uint32_t* sample_counts, uint32_t* counters, const float* depth_buffer, uint32_t max_rays, cudaStream_t s);
@@ -114,7 +125,8 @@ void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
-	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s);
+	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,
+	bool density_only = false);
 // fused_frame != nullptr (impl 1 only): composite inside the network kernel, write survive[chunk]; then launch_compact builds the next list
 void launch_compact(const uint32_t* alive_in, const uint32_t* n_alive_ptr, const uint32_t* survive, uint32_t* alive_out, uint32_t* n_alive_out, uint32_t max_rays, cudaStream_t s); // impl: 0 = warp MMA (mma.sync), 1 = tcgen05/TMEM
 
@@ -127,8 +139,20 @@ void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, f
 void launch_pack_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float* packed, bool unpack, cudaStream_t s);
 
 // mesh TU (exact flags as well)
-void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, cudaStream_t s);
+void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, EnvHits hits, cudaStream_t s);
+// a-16: K light rays per hit [first, first+n): direction, mesh visibility, envmap radiance -> ray slots (hit-first)*K + k
+void launch_envlight_gen(const FrameArgs& a, SceneDev scene, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays, cudaStream_t s);
+// frame[pixel].rgb += albedo / K * sum_k radiance_k * T_k
+void launch_envlight_reduce(const FrameArgs& a, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays, float4* frame, cudaStream_t s);
+// light rays with radiance enter the volume: AABB entry + advance to the first occupied voxel; live ones are appended to the list
+void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s);
+// one warp per ray chunk: T *= prod exp(-sigma dt), stop below min_transmittance; survive flags for launch_compact
+void launch_transmittance(const FrameArgs& a, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr, const float4* samples,
+	const uint32_t* sample_counts, const uint2* net_out, uint32_t* survive, uint32_t* counters, uint32_t max_rays, cudaStream_t s);
 void launch_trace(SceneDev scene, int compat, uint32_t n, const float* o, const float* d, int32_t* mesh, int32_t* tri, float* t, cudaStream_t s);
+
+void launch_op_read_envmap(const FrameArgs& a, const float* dirs, uint32_t n, float4* out, cudaStream_t s);
+void launch_op_env_light_dirs(uint32_t pix, uint32_t spp, uint32_t K, const float n[3], float* out, cudaStream_t s);
 
 // counters layout (uint32 array on the device)
 enum Counter : uint32_t { CNT_ALIVE_A = 0, CNT_ALIVE_B = 1, CNT_SAMPLES_LO = 2, CNT_SAMPLES_HI = 3, CNT_COMPOSITED_LO = 4, CNT_COMPOSITED_HI = 5, CNT_RAYS = 6, CNT_ERR = 7, CNT_N = 8 };

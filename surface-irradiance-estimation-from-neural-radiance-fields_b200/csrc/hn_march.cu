@@ -243,7 +243,7 @@ __device__ __forceinline__ bool tile_owned(const FrameArgs& a, uint32_t x, uint3
 // One thread per pixel. Live rays are appended to the SoA ray buffers through a warp-aggregated atomic (one atomicAdd
 // per warp); the ray id is the slot. Order is non-deterministic, results are keyed by pixel so the image is not.
 __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, uint32_t* __restrict__ alive_list,
-	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer) {
+	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer, float4* __restrict__ frame) {
 	uint32_t x = 0, y = 0, idx = 0;
 	bool alive = false;
 	V3 o, d; float t = 0.0f;
@@ -252,6 +252,8 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
 		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
 		alive = start_ray(a, bits, x, y, o, d, t);
+		// :1526-1528: envmap -> frame buffer; in hybrid frames only where the mesh pass left nothing
+		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);
 	}
 	uint32_t mask = __ballot_sync(0xffffffffu, alive);
 	if (mask == 0) return;
@@ -268,6 +270,40 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		rays.pixel[r] = idx;
 		rays.n_steps[r] = 0;
 		alive_list[r] = r;
+	}
+}
+
+// a-16: light rays that carry radiance enter the volume like camera rays (AABB entry, advance to the first occupied voxel;
+// no start jitter: oracle nerf_transmittance). Rays that never meet a set cell keep T = 1 and are not listed.
+__global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, uint32_t n_rays,
+	uint32_t* __restrict__ alive_list, uint32_t* __restrict__ counters) {
+	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+	bool alive = false;
+	float t = 0.0f;
+	if (r < n_rays) {
+		const float4 L = rays.rgba[r];
+		if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {
+			const float4 ot = rays.o_t[r], dm = rays.d_mw[r];
+			const V3 o = mk(ot.x, ot.y, ot.z), d = mk(dm.x, dm.y, dm.z);
+			const Box aabb = ldbox(a.render_aabb);
+			t = fmaxf(box_ray_intersect(aabb, o, d).x, 0.0f) + 1e-6f;
+			if (box_contains(aabb, o + t * d)) {
+				const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+				t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, occ_t_far(a, bits, o, d));
+				alive = t < MAX_DEPTH_F;
+			}
+		}
+	}
+	const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+	if (!mask) return;
+	const uint32_t lane = threadIdx.x & 31u;
+	const int leader = __ffs(mask) - 1;
+	uint32_t base = 0;
+	if ((int)lane == leader) base = atomicAdd(&counters[CNT_ALIVE_A], __popc(mask));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	if (alive) {
+		rays.o_t[r].w = t;
+		alive_list[base + __popc(mask & ((1u << lane) - 1u))] = r;
 	}
 }
 
@@ -466,10 +502,14 @@ void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thres
 		bitfield_max_pool_kernel<<<(per_mip / 8 + 255) / 256, 256, 0, s>>>(per_mip / 8, bits + (size_t)per_mip * (level - 1), bits + (size_t)per_mip * level);
 	}
 }
-void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters, float* depth_buffer, cudaStream_t s) {
+void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters, float* depth_buffer, float4* frame, cudaStream_t s) {
 	uint32_t n = owned_pixel_threads(a);
 	if (!n) return;
-	raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer);
+	raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
+}
+void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
+	if (!n_rays) return;
+	secondary_start_kernel<<<(n_rays + 255) / 256, 256, 0, s>>>(a, bits, rays, n_rays, alive_list, counters);
 }
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {
 	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;

@@ -184,11 +184,9 @@ __device__ __forceinline__ bool mesh_tile_owned(const FrameArgs& a, uint32_t x, 
 }
 
 // render_geometry_mesh (src/testbed_geometry_training.cu:2202-2320), Shade mode, one thread per pixel.
-__global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, SceneDev sc, float4* __restrict__ frame, float* __restrict__ depth_buffer) {
-	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
-	int* stack = stack_s + threadIdx.x;
-	uint32_t x, y;
-	if (!owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) return;
+// Per-pixel body; returns true when the pixel is a shaded triangle hit that gathers environment light (a-16).
+__device__ bool mesh_pixel(const FrameArgs& a, const SceneDev& sc, float4* __restrict__ frame, float* __restrict__ depth_buffer, int* stack,
+	uint32_t x, uint32_t y, V3& env_org, V3& env_nrm, V3& env_albedo) {
 	const uint32_t idx = x + (uint32_t)a.w * y;
 	const Box aabb = ldbox(a.mesh_aabb);
 	// init_rays_with_payload_kernel_mesh_geometry (:488-579): pixel_to_ray with camera_matrix0 as is (no rolling shutter)
@@ -233,7 +231,7 @@ __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, Scen
 		shadow = box_contains(aabb, end) ? 0.0f : 1.0f; // write_shadow_ray_result_geometry
 	}
 	// shade_kernel_mesh_geometry (:280-355)
-	if (!box_contains(aabb, pos)) return;
+	if (!box_contains(aabb, pos)) return false;
 	V3 normal = normalize3(nrm);
 	bool floor_hit = false;
 	if (pos.y < a.floor_y + 0.001f && dir.y < 0.f) { normal = mk(0.0f, 1.0f, 0.0f); floor_hit = true; }
@@ -251,12 +249,104 @@ __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, Scen
 		floor_hit ? 0.f : B[5], B[6], sun, -normalize3(dir), normal);
 	frame[idx] = make_float4(color.x, color.y, color.z, 1.0f);
 	depth_buffer[idx] = dot3(c2, pos - cam_pos);
+	if (!(touched && h.tri >= 0)) return false;
+	env_nrm = normal * -copysignf(1.0f, dot3(dir, normal));
+	env_org = pos + env_nrm * 1e-3f;
+	env_albedo = floor_hit ? floorcol : basecolor * basecolor;
+	return true;
 }
 
-void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, cudaStream_t s) {
+__global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, SceneDev sc, float4* __restrict__ frame, float* __restrict__ depth_buffer, EnvHits hits) {
+	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
+	uint32_t x = 0, y = 0;
+	bool lit = false;
+	V3 org, nrm, alb;
+	if (owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) lit = mesh_pixel(a, sc, frame, depth_buffer, stack_s + threadIdx.x, x, y, org, nrm, alb);
+	if (!hits.count) return; // warp-uniform
+	const uint32_t mask = __ballot_sync(0xffffffffu, lit);
+	if (!mask) return;
+	const uint32_t lane = threadIdx.x & 31u;
+	const int leader = __ffs(mask) - 1;
+	uint32_t base = 0;
+	if ((int)lane == leader) base = atomicAdd(hits.count, __popc(mask));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	if (lit) {
+		const uint32_t slot = base + __popc(mask & ((1u << lane) - 1u));
+		hits.pos_pix[slot] = make_float4(org.x, org.y, org.z, __uint_as_float(x + (uint32_t)a.w * y));
+		hits.nrm[slot] = make_float4(nrm.x, nrm.y, nrm.z, 0.0f);
+		hits.albedo[slot] = make_float4(alb.x, alb.y, alb.z, 0.0f);
+	}
+}
+
+// a-16 (OUR definition, oracle render_mesh): light ray k of hit j -> ray slot (j - first) * K + k. The shadow test is a
+// nearest-hit search over all meshes; occluded rays carry zero radiance and never enter the volume.
+__global__ void __launch_bounds__(MESH_BLOCK) envlight_gen_kernel(FrameArgs a, SceneDev sc, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays) {
+	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
+	const uint32_t K = (uint32_t)a.env_samples;
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n * K) return;
+	const uint32_t j = first + i / K, k = i % K;
+	const float4 pp = __ldg(hits.pos_pix + j), nn = __ldg(hits.nrm + j);
+	const uint32_t pix = __float_as_uint(pp.w);
+	const V3 org = mk(pp.x, pp.y, pp.z);
+	const V3 w = env_light_dir(pix, a.spp, K, k, mk(nn.x, nn.y, nn.z));
+	Hit h; bool touched;
+	scene_nearest(sc, 0, org, w, h, touched, stack_s + threadIdx.x);
+	float4 L = make_float4(0.f, 0.f, 0.f, 0.f);
+	if (h.tri < 0) L = read_envmap(a.envmap, a.env_w, a.env_h, w);
+	rays.o_t[i] = make_float4(org.x, org.y, org.z, 0.0f);
+	rays.d_mw[i] = make_float4(w.x, w.y, w.z, 0.0f);
+	rays.rgba[i] = make_float4(L.x, L.y, L.z, 1.0f); // .w = transmittance T of the volume along the light ray
+	rays.pixel[i] = pix;
+	rays.n_steps[i] = 0;
+}
+
+__global__ void __launch_bounds__(256) envlight_reduce_kernel(FrameArgs a, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays, float4* __restrict__ frame) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t K = (uint32_t)a.env_samples;
+	V3 sum = mk(0.f, 0.f, 0.f);
+	for (uint32_t k = 0; k < K; ++k) {
+		const float4 r = rays.rgba[(size_t)i * K + k];
+		sum = sum + mk(r.x, r.y, r.z) * r.w;
+	}
+	const float4 alb = hits.albedo[first + i];
+	const uint32_t pix = __float_as_uint(hits.pos_pix[first + i].w);
+	const V3 add = (mk(alb.x, alb.y, alb.z) * sum) * (1.0f / (float)K);
+	float4 f = frame[pix];
+	f.x += add.x; f.y += add.y; f.z += add.z;
+	frame[pix] = f;
+}
+
+void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, EnvHits hits, cudaStream_t s) {
 	uint32_t n = owned_pixel_threads(a);
 	if (!n) return;
-	mesh_pass_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, frame, depth_buffer);
+	mesh_pass_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, frame, depth_buffer, hits);
+}
+void launch_envlight_gen(const FrameArgs& a, SceneDev scene, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays, cudaStream_t s) {
+	if (!n) return;
+	const uint32_t threads = n * (uint32_t)a.env_samples;
+	envlight_gen_kernel<<<(threads + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, hits, first, n, rays);
+}
+void launch_envlight_reduce(const FrameArgs& a, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays, float4* frame, cudaStream_t s) {
+	if (!n) return;
+	envlight_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, hits, first, n, rays, frame);
+}
+__global__ void op_read_envmap_kernel(FrameArgs a, const float* __restrict__ dirs, uint32_t n, float4* __restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = read_envmap(a.envmap, a.env_w, a.env_h, ld3(dirs + 3 * i));
+}
+__global__ void op_env_light_dirs_kernel(uint32_t pix, uint32_t spp, uint32_t K, float nx, float ny, float nz, float* __restrict__ out) {
+	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= K) return;
+	const V3 w = env_light_dir(pix, spp, K, k, mk(nx, ny, nz));
+	out[3 * k] = w.x; out[3 * k + 1] = w.y; out[3 * k + 2] = w.z;
+}
+void launch_op_read_envmap(const FrameArgs& a, const float* dirs, uint32_t n, float4* out, cudaStream_t s) {
+	if (n) op_read_envmap_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, dirs, n, out);
+}
+void launch_op_env_light_dirs(uint32_t pix, uint32_t spp, uint32_t K, const float n[3], float* out, cudaStream_t s) {
+	if (K) op_env_light_dirs_kernel<<<(K + 63) / 64, 64, 0, s>>>(pix, spp, K, n[0], n[1], n[2], out);
 }
 void launch_trace(SceneDev scene, int compat, uint32_t n, const float* o, const float* d, int32_t* mesh, int32_t* tri, float* t, cudaStream_t s) {
 	if (!n) return;

@@ -218,9 +218,11 @@ void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const f
 
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
-	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s) {
+	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,
+	bool density_only) {
 	if (!max_chunks) return;
 	EvalArgs a;
+	a.density_only = (density_only && impl == 1) ? 1 : 0; // the warp-MMA kernel always runs both MLPs (sigma is the same)
 	a.g = g;
 	a.table = params + cfg.grid_offset;
 	a.w_density = params + cfg.density_w_offset;

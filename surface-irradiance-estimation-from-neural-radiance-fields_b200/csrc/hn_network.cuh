@@ -22,6 +22,7 @@ struct EvalArgs {
 	uint2* out;                     // [n_chunks][32] (r,g | b,sigma) fp16 raw network output (unfused path)
 	// fused compositing (tcgen05 kernel only): the warp that evaluated a ray chunk also composites it
 	int fused;
+	int density_only;               // tcgen05 kernel: stop after the density MLP, out = (0, 0 | 0, sigma) (light rays, a-16)
 	CompArgs comp;
 };
 

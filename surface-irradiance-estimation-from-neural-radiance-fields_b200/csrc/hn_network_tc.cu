@@ -148,7 +148,7 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 // group's gather overlaps the other groups' MMA rounds.
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
 
-template <int F, int G, bool FUSED>
+template <int F, int G, bool FUSED, bool DONLY>
 __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
 	const int grp = threadIdx.x >> 7;                     // tile group of this thread
@@ -223,6 +223,15 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 		}
 		HN_WAIT(); hidden_epilogue(t_row, a_row);
 		HN_ROUND(64, 16, w_addr);
+		if (DONLY) { // light rays only need sigma: density channel 0, rounded to fp16 like the full path
+			HN_WAIT();
+			uint32_t v[4];
+			tmem_ld4(t_row, v);
+			tc_wait_ld();
+			if (chunk < n_chunks) a.out[(size_t)chunk * CHUNK + lane] = make_uint2(0u, (pack_plain(v[0], 0u) & 0xFFFFu) << 16);
+			tc_fence_before(); // the next tile's first MMA overwrites these TMEM columns
+			continue;
+		}
 		// ---- colour MLP input: [16 density outputs | 16 SH coefficients of the ray direction]
 		uint32_t sigma_bits;
 		{
@@ -299,11 +308,11 @@ void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStre
 	uint32_t ctas = (tiles + G - 1) / G;
 	uint32_t persistent = (uint32_t)sm_count * 2u;
 	uint32_t blocks = ctas < persistent ? ctas : persistent;
-	#define HN_LAUNCH_TC(FF, FU) do { \
-		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		tc::eval_tc_kernel<FF, G, FU><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
-	if (F == 4) { if (a.fused) HN_LAUNCH_TC(4, true); else HN_LAUNCH_TC(4, false); }
-	else { if (a.fused) HN_LAUNCH_TC(2, true); else HN_LAUNCH_TC(2, false); }
+	#define HN_LAUNCH_TC(FF, FU, DO) do { \
+		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+		tc::eval_tc_kernel<FF, G, FU, DO><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
+	if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true); else if (a.fused) HN_LAUNCH_TC(4, true, false); else HN_LAUNCH_TC(4, false, false); }
+	else { if (a.density_only) HN_LAUNCH_TC(2, false, true); else if (a.fused) HN_LAUNCH_TC(2, true, false); else HN_LAUNCH_TC(2, false, false); }
 	#undef HN_LAUNCH_TC
 }
 

@@ -109,3 +109,26 @@ def load_obj(path: str) -> np.ndarray:
                 for k in range(2, len(idx)):
                     tris.append(verts[idx[0]] + verts[idx[k - 1]] + verts[idx[k]])
     return np.asarray(tris, dtype=np.float32)
+
+
+def envmap(width: int = 1024, height: int = 512, seed: int = 3, lobe=(0.3, 0.7), lobe_strength: float = 6.0) -> np.ndarray:
+    """Lat-long RGBA32F environment map [height][width][4] (SURVEY config 4): seeded smooth noise (periodic in x) plus one
+    bright lobe centred at (u, v) = `lobe`. Alpha = 1."""
+    rng = np.random.default_rng(seed)
+    u = (np.arange(width, dtype=np.float32) + 0.5) / width
+    v = (np.arange(height, dtype=np.float32) + 0.5) / height
+    U, V = np.meshgrid(u, v)
+    img = np.zeros((height, width, 4), np.float32)
+    for c in range(3):
+        acc = np.full((height, width), 0.35, np.float32)
+        for f in (1, 2, 3, 5):
+            ph = rng.uniform(0, 2 * np.pi, 2)
+            amp = np.float32(0.12 / f)
+            acc += amp * np.sin(2 * np.pi * f * U + ph[0]).astype(np.float32) * np.cos(np.pi * f * V + ph[1]).astype(np.float32)
+        img[..., c] = acc
+    du = np.minimum(np.abs(U - lobe[0]), 1.0 - np.abs(U - lobe[0]))
+    g = np.exp(-((du / 0.05) ** 2 + ((V - lobe[1]) / 0.08) ** 2)).astype(np.float32)
+    img[..., :3] += np.float32(lobe_strength) * g[..., None] * np.array([1.0, 0.9, 0.75], np.float32)
+    img[..., :3] = np.maximum(img[..., :3], 0.0)
+    img[..., 3] = 1.0
+    return img

@@ -45,6 +45,8 @@ class FrameStats(C.Structure):
         ("n_samples", C.c_uint64), ("n_samples_composited", C.c_uint64), ("n_rays_alive", C.c_uint32), ("n_passes", C.c_uint32),
         ("n_kernel_launches", C.c_uint32), ("ms_mesh", C.c_float), ("ms_raygen", C.c_float), ("ms_march", C.c_float),
         ("ms_eval", C.c_float), ("ms_composite", C.c_float), ("ms_total", C.c_float),
+        ("ms_envlight", C.c_float), ("n_env_hits", C.c_uint32), ("n_light_rays", C.c_uint64), ("n_light_rays_volume", C.c_uint64),
+        ("n_light_samples", C.c_uint64),
     ]
 
 
@@ -55,7 +57,8 @@ EXPORTS = [
     "hn_get_occupancy_bitfield", "hn_load_scene", "hn_add_mesh", "hn_load_mesh_file", "hn_build_scene", "hn_clear_scene",
     "hn_get_scene_aabb", "hn_set_option", "hn_get_option", "hn_render_frame", "hn_render_to_host", "hn_set_camera",
     "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
-    "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace",
+    "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
+    "hn_op_transmittance",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -92,6 +95,10 @@ _lib.hn_set_camera.argtypes = [C.c_void_p, C.c_void_p]
 _lib.hn_set_tile_shard.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
 _lib.hn_tile_count.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u32p]
 _lib.hn_get_frame_stats.argtypes = [C.c_void_p, C.POINTER(FrameStats)]
+_lib.hn_set_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+_lib.hn_op_read_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_op_env_light_dirs.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+_lib.hn_op_transmittance.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
 def _f32(a):
@@ -316,6 +323,36 @@ class Testbed:
         out = np.empty((p.shape[0], 4), np.float16)
         self._check(_lib.hn_op_network(self._h, _ptr(p), _ptr(d), p.shape[0], _ptr(out)))
         return out
+
+    # ---- a-16 environment map (Testbed::m_envmap, testbed.h:1227-1241)
+    def set_envmap(self, rgba: np.ndarray | None):
+        """rgba: float32 [h][w][4] lat-long map, or None to remove it. Background of camera rays and, with option
+        `env_light_samples` > 0, light source of the mesh pass."""
+        if rgba is None:
+            self._check(_lib.hn_set_envmap(self._h, None, 0, 0))
+            return
+        e = _f32(rgba)
+        if e.ndim != 3 or e.shape[2] != 4:
+            raise RuntimeError("envmap must have shape [h][w][4]")
+        self._check(_lib.hn_set_envmap(self._h, _ptr(e), e.shape[1], e.shape[0]))
+
+    def op_read_envmap(self, dirs):
+        d = _f32(dirs).reshape(-1, 3)
+        out = np.empty((d.shape[0], 4), np.float32)
+        self._check(_lib.hn_op_read_envmap(self._h, _ptr(d), d.shape[0], _ptr(out)))
+        return out
+
+    def op_env_light_dirs(self, pixel_index, spp_index, K, normal):
+        n = _f32(normal).reshape(3)
+        out = np.empty((K, 3), np.float32)
+        self._check(_lib.hn_op_env_light_dirs(self._h, int(pixel_index), int(spp_index), int(K), _ptr(n), _ptr(out)))
+        return out
+
+    def op_transmittance(self, origins, dirs):
+        o, d = _f32(origins).reshape(-1, 3), _f32(dirs).reshape(-1, 3)
+        T = np.empty(o.shape[0], np.float32); ns = np.empty(o.shape[0], np.uint32)
+        self._check(_lib.hn_op_transmittance(self._h, o.shape[0], _ptr(o), _ptr(d), _ptr(T), _ptr(ns)))
+        return T, ns
 
     def op_trace(self, origins, dirs):
         o, d = _f32(origins).reshape(-1, 3), _f32(dirs).reshape(-1, 3)

@@ -138,8 +138,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eval-impl", type=int, default=1, help="network kernel: 1 = tcgen05/TMEM (default), 0 = warp MMA")
     ap.add_argument("--clip", action="store_true", help="stop marching at the mesh depth instead of the reference's per-pixel test")
+    ap.add_argument("--workload", default="config3", choices=["config2", "config3", "config4"],
+                    help="BASELINE.json configs[1] NeRF-only 1080p / configs[2] hybrid 1080p (default, the headline) / configs[3] 4K hybrid + envmap light")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    global W, H
+    if args.workload == "config4":
+        W, H = 3840, 2160
     if args.impl == "reference":
         return reference_arm(args)
 
@@ -162,8 +167,12 @@ def main():
     info = tb.network_info()
     tb.set_params(hn.synthetic.random_params(info, 1337, 1e-4))
     tb.set_density_grid(grid, 1)
-    tb.add_mesh(mesh)
-    tb.build_scene()
+    if args.workload != "config2":
+        tb.add_mesh(mesh)
+        tb.build_scene()
+    if args.workload == "config4":
+        tb.set_envmap(hn.synthetic.envmap(1024, 512, seed=3))
+        tb.set_option("env_light_samples", 16.0)
     tb.snap_to_pixel_centers = True
     tb.set_option("depth_merge_clip", 1.0 if args.clip else 0.0)
     tb.set_camera_cols(cam)
@@ -215,6 +224,7 @@ def main():
         torch.cuda.synchronize()
         total_ms += e0.elapsed_time(e1)
         samples = tb.frame_stats().n_samples
+    last_stats = tb.frame_stats()
     barrier()
     ms = total_ms / args.steps
     if world > 1:
@@ -230,7 +240,7 @@ def main():
 
     # ---- per-kernel durations (CUDA events on the launching stream, hn option "profile"), N=1 roofline of the dominant kernel
     tb.set_option("profile", 1.0)
-    prof = {"ms_eval": 0.0, "ms_march": 0.0, "ms_composite": 0.0, "ms_mesh": 0.0, "ms_raygen": 0.0, "n_passes": 0}
+    prof = {"ms_eval": 0.0, "ms_march": 0.0, "ms_composite": 0.0, "ms_mesh": 0.0, "ms_raygen": 0.0, "ms_envlight": 0.0, "n_passes": 0}
     n_prof = 3
     for _ in range(n_prof):
         flush.fill_(1.0)
@@ -276,7 +286,7 @@ def main():
         e2e_ms = float(t.item())
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "config3":
         import orc
         cores = os.cpu_count() or 1
         w8, h8 = W // 8, H // 8
@@ -295,17 +305,24 @@ def main():
 
     if rank == 0:
         mrays = W * H / (ms * 1e-3) / 1e6
+        workload = {"config2": "configs[1]: 1920x1080 NeRF-only (base.json, 128^3 sphere occupancy, random-init)",
+                    "config3": "configs[2]: 1920x1080 hybrid NeRF (base.json, 128^3 sphere occupancy, random-init) + 1 048 576-triangle torus, sun shadow rays",
+                    "config4": "configs[3]: 3840x2160 hybrid NeRF + 1 048 576-triangle torus, sun shadow rays, 1024x512 envmap background + "
+                               "16 env light rays per mesh hit (BVH shadow ray + NeRF transmittance)"}[args.workload]
         line = {
-            "metric": "Mrays/s, 1080p hybrid NeRF+mesh frame (primary rays)", "value": mrays, "unit": "Mrays/s", "n_gpus": world,
+            "metric": "Mrays/s, 1080p hybrid NeRF+mesh frame (primary rays)" if args.workload == "config3" else f"Mrays/s, {W}x{H} frame (primary rays), {args.workload}", "value": mrays, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "fp16 params/activations, fp32 accumulate", "data": "synthetic",
-            "config": {"workload": "configs[2]: 1920x1080 hybrid NeRF (base.json, 128^3 sphere occupancy, random-init) + 1 048 576-triangle torus, sun shadow rays",
+            "config": {"workload": workload,
                        "depth_merge": "clip" if args.clip else "reference per-pixel test", "l2": "512 MB flush between timed iterations",
                        "tiles": f"{tile_w}x{tile_h} interleaved over {world} rank(s)", "samples_per_frame_all_ranks": samples_all},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": W * H / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 48, "d2h_bytes_per_step": W * H * 16},
             "roofline": roofline, "cpu_baseline": cpu_baseline,
         }
+        if args.workload == "config4":
+            line["env_light"] = {"hits_rank0": int(last_stats.n_env_hits), "light_rays_rank0": int(last_stats.n_light_rays),
+                                 "light_rays_in_volume_rank0": int(last_stats.n_light_rays_volume), "light_samples_rank0": int(last_stats.n_light_samples)}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

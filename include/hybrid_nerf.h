@@ -84,6 +84,39 @@ int hn_op_read_envmap(hn_context* ctx, const float* dirs, uint32_t n, float* out
 int hn_op_env_light_dirs(hn_context* ctx, uint32_t pixel_index, uint32_t spp_index, uint32_t K, const float normal[3], float* out);
 int hn_op_transmittance(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, float* T, uint32_t* n_samples);
 
+/* ---- training step (a-21; Testbed::train -> train_nerf -> train_nerf_step, src/testbed_nerf.cu:2929-3075,3183-3430;
+ *      tcnn Trainer::training_step, trainer.h:163-190; optimizer / loss from the network config JSON) ---- */
+/* In-memory dataset: n images of w x h, float RGBA (linear, straight alpha; NerfDataset pixels, src/nerf_loader.cu),
+ * one camera mat4x3 each (float[12], same convention as the render camera), shared pinhole intrinsics
+ * (focal length in pixels, principal point in [0,1]^2). Host pointers; copied to the device. */
+int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, int width, int height, const float* cameras,
+	const float focal_px[2], const float principal[2]);
+/* (Re)creates the trainer state from the current parameters: fp32 master copy, zeroed Adam moments, EMA, step counter
+ * (Trainer ctor + Testbed::reset_network, src/testbed.cu:3933-4200). seed drives ray / pixel / background sampling. */
+int hn_train_init(hn_context* ctx, uint32_t seed);
+/* One batch: sample rays from the dataset, march, forward, loss (loss_scale 128, common.h:232), backward ->
+ * fp32 gradient buffer [n_params] (scaled by loss_scale, summed over the batch). n_rays = 0: adaptive rays per batch
+ * towards the target batch size of 2^18 samples (src/testbed_nerf.cu:2943-2944). rank/world shard the ray stream. */
+int hn_train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out);
+/* Device pointer of the gradient buffer (for the data-parallel all-reduce between hn_train_accumulate and hn_train_apply). */
+int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats);
+/* Optimizer step on the gradient buffer: Adam (+ ExponentialDecay, + EMA) as configured; refreshes the fp16 inference copy.
+ * grad_scale multiplies the gradients first (1/world after a sum all-reduce). */
+int hn_train_apply(hn_context* ctx, float grad_scale);
+/* n_steps x (accumulate + apply) on one GPU; loss_out = mean loss of the last step (Testbed::train + m_loss_scalar). */
+int hn_train_step(hn_context* ctx, uint32_t n_steps, float* loss_out);
+typedef struct {
+	uint32_t step, rays_per_batch, n_rays_last, n_samples_last;
+	float loss_last, learning_rate;
+	float ms_sample, ms_forward, ms_loss, ms_backward, ms_optimizer; /* filled when option "profile" = 1 */
+} hn_train_stats;
+int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out);
+/* operator entry point for the parity test: explicit rays (origin, unit dir, start t), targets and backgrounds [n][3] in the
+ * training colour space -> mean loss, fp32 gradients [n_params] (host, scaled by loss_scale), samples used per ray.
+ * loss_type: 0 = L2, 1 = Huber (nerf_device.cuh:640-655). */
+int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
+	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
+
 /* ---- render state (public Testbed members; names follow src/python_api.cu:482-567) ---- */
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values);
 int hn_get_option(const hn_context* ctx, const char* name, float* values, int n_values);

@@ -103,6 +103,14 @@ void orc_network(const orc_net_config* c, const uint16_t* params, const float* c
 uint64_t orc_render_nerf(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
 	float* frame /*[h][w][4]*/, float* depth /*[h][w]*/, uint32_t* n_steps_out, int32_t depth_test);
 
+// ---- training batch (a-21): loss + parameter gradients, fp32 forward / analytic fp32 backward (orc_train.inc) ----
+// rays: origin, unit dir, start t (first sample search starts there); targets/backgrounds [n][3] in the training colour space.
+// loss_type 0 = L2, 1 = Huber(0.1)/5. grads: fp32 [orc_n_params], scaled by loss_scale. Returns the mean loss over the rays.
+void orc_loss_and_gradient(const float target[3], const float pred[3], int32_t loss_type, float out[6]);
+float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, uint32_t n_rays,
+	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, int32_t loss_type, float loss_scale,
+	uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total);
+
 // ---- meshes (a-17..a-19) ----
 typedef struct orc_scene orc_scene;
 orc_scene* orc_scene_create(void);

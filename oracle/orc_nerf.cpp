@@ -656,6 +656,8 @@ float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8
 	return T;
 }
 
+#include "orc_train.inc"
+
 Net* net_new(const orc_net_config& c, const uint16_t* params) { return new Net(make_net(c, params)); }
 void net_delete(Net* n) { delete n; }
 
@@ -700,6 +702,17 @@ float orc_nerf_transmittance(const orc_render_params* p, const orc_net_config* c
 	const float o[3], const float d[3], uint32_t* n_samples_out) {
 	Net net = make_net(*c, params);
 	return nerf_transmittance(*p, net, bitfield, {o[0], o[1], o[2]}, {d[0], d[1], d[2]}, n_samples_out);
+}
+
+// loss_type 0 L2, 1 Huber: out = loss[3], gradient[3] (nerf_device.cuh:74-112,640-655)
+void orc_loss_and_gradient(const float target[3], const float pred[3], int32_t loss_type, float out[6]) {
+	for (int k = 0; k < 3; ++k) out[k] = loss_grad(loss_type, target[k], pred[k], out[3 + k]);
+}
+float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, uint32_t n_rays,
+	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, int32_t loss_type, float loss_scale,
+	uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total) {
+	Net net = make_net(*c, params);
+	return train_gradients(*p, net, bitfield, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, max_samples, grads, n_steps_out, n_samples_total);
 }
 
 float orc_bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out) { return bitfield_from_grid(grid, n_cascades, out); }

@@ -93,4 +93,10 @@ void ref_compute_local_frame(const float z[3], float out[9]) {
 	for (int c = 0; c < 3; ++c) { out[3 * c] = f[c].x; out[3 * c + 1] = f[c].y; out[3 * c + 2] = f[c].z; }
 }
 
+// a-21 loss functions (nerf_device.cuh:74-112,640-655): loss_type 0 = L2, 1 = Huber
+void ref_loss_and_gradient(const float target[3], const float pred[3], int32_t loss_type, float out[6]) {
+	LossAndGradient lg = loss_and_gradient(vec3(target[0], target[1], target[2]), vec3(pred[0], pred[1], pred[2]), loss_type == 1 ? ELossType::Huber : ELossType::L2);
+	out[0] = lg.loss.x; out[1] = lg.loss.y; out[2] = lg.loss.z; out[3] = lg.gradient.x; out[4] = lg.gradient.y; out[5] = lg.gradient.z;
+}
+
 }

@@ -46,6 +46,7 @@ void hn_destroy(hn_context* ctx) {
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	cudaDeviceSynchronize();
+	hn::train_release(ctx);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto& e : ctx->pass_events) if (e) cudaEventDestroy(e);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -121,6 +122,7 @@ void upload_params(hn_context* ctx, const void* blob, size_t n_elements, int dty
 	ctx->params.ensure(n_elements);
 	HN_CUDA(cudaMemcpy(ctx->params.p, ctx->params_host.data(), n_elements * sizeof(__half), cudaMemcpyHostToDevice));
 	ctx->has_params = true;
+	ctx->train.ready = false; // a new blob restarts the trainer state (Trainer::set_params)
 }
 void upload_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades) {
 	need(n_cascades >= 1 && n_cascades <= CASCADES, "n_cascades must be in [1,8]");
@@ -478,7 +480,51 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 
 } // namespace
 
+namespace hn {
+FrameArgs train_frame_args(hn_context* ctx) {
+	const float rs[4] = {0.f, 0.f, 0.f, 1.f};
+	return make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+}
+} // namespace hn
+
 extern "C" {
+
+// ---------------------------------------------------------------- training (a-21)
+int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, int width, int height, const float* cameras,
+	const float focal_px[2], const float principal[2]) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_dataset(ctx, rgba, n_images, width, height, cameras, focal_px, principal); HN_CATCH(ctx)
+}
+int hn_train_init(hn_context* ctx, uint32_t seed) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_init(ctx, seed); HN_CATCH(ctx) }
+int hn_train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_accumulate(ctx, n_rays, loss_out); HN_CATCH(ctx) }
+int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats) {
+	HN_TRY(ctx)
+	need(ctx->train.ready && dev_ptr && n_floats, "trainer not initialised (hn_train_init)");
+	*dev_ptr = ctx->train.grads.p; *n_floats = ctx->net.n_params;
+	HN_CATCH(ctx)
+}
+int hn_train_apply(hn_context* ctx, float grad_scale) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_apply(ctx, grad_scale); HN_CUDA(cudaStreamSynchronize(ctx->stream)); HN_CATCH(ctx) }
+int hn_train_step(hn_context* ctx, uint32_t n_steps, float* loss_out) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	for (uint32_t i = 0; i < n_steps; ++i) { train_accumulate(ctx, 0, loss_out); train_apply(ctx, 1.0f); }
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out) {
+	if (!ctx || !out) return 1;
+	const TrainState& t = ctx->train;
+	out->step = t.step; out->rays_per_batch = t.rays_per_batch; out->n_rays_last = t.n_rays_last; out->n_samples_last = t.n_samples_last;
+	out->loss_last = t.loss_last; out->learning_rate = t.lr_last;
+	out->ms_sample = t.ms[0]; out->ms_forward = t.ms[1]; out->ms_loss = t.ms[2]; out->ms_backward = t.ms[3]; out->ms_optimizer = t.ms[4];
+	return 0;
+}
+int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
+	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	train_op_gradients(ctx, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, loss_out, grads_host, n_steps);
+	HN_CATCH(ctx)
+}
 
 int hn_render_frame(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2],
 	const float relative_focal_length[2], const float rolling_shutter[4], uint32_t spp_index,

@@ -135,6 +135,30 @@ void apply_network_config(hn_context* ctx, const Json& cfg) {
 			throw std::runtime_error("only SphericalHarmonics degree 4 direction encoding is supported");
 	}
 	ctx->net = n;
+	{ // loss + optimizer stack (Ema > ExponentialDecay > Adam in configs/nerf/base.json:2-22); unknown wrappers are skipped
+		TrainCfg t;
+		if (cfg.contains("loss")) {
+			const std::string lt = lower(cfg.at("loss").value("otype", std::string("Huber")));
+			if (lt == "l2") t.loss_type = 0; else if (lt == "huber") t.loss_type = 1;
+			else throw std::runtime_error("loss: only L2 and Huber are supported on this path, got '" + lt + "'");
+		}
+		t.ema = false; t.exp_decay = false;
+		const Json* o = cfg.find("optimizer");
+		while (o && o->is_object()) {
+			const std::string ot = lower(o->value("otype", std::string("Adam")));
+			if (ot == "ema") { t.ema = true; t.ema_decay = (float)o->value("decay", 0.99); }
+			else if (ot == "exponentialdecay") {
+				t.exp_decay = true; t.decay_start = (uint32_t)o->value("decay_start", 0.0); t.decay_interval = (uint32_t)o->value("decay_interval", 10000.0);
+				t.decay_base = (float)o->value("decay_base", 0.33);
+			} else if (ot == "adam") {
+				t.lr = (float)o->value("learning_rate", 1e-3); t.beta1 = (float)o->value("beta1", 0.9); t.beta2 = (float)o->value("beta2", 0.999);
+				t.epsilon = (float)o->value("epsilon", 1e-8); t.l2_reg = (float)o->value("l2_reg", 1e-8);
+			}
+			o = o->find("nested");
+		}
+		ctx->train_cfg = t;
+		ctx->train.ready = false;
+	}
 	{ // kept (without any snapshot payload) so hn_set_aabb_scale can re-derive per_level_scale, and for hn_save_snapshot
 		Json keep; keep.type = Json::Object;
 		for (auto& kv : cfg.obj) if (kv.first != "snapshot") keep.obj.push_back(kv);

@@ -77,6 +77,39 @@ struct Options {
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
 };
 
+// a-21 trainer state (tcnn Trainer + optimizer stack, trainer.h:37-360, optimizers/adam.h, ema.h, exponential_decay.h)
+struct TrainCfg {
+	int loss_type = 1;                      // 0 L2, 1 Huber (configs/nerf/base.json:2-4)
+	float lr = 1e-2f, beta1 = 0.9f, beta2 = 0.99f, epsilon = 1e-15f, l2_reg = 1e-6f;
+	bool ema = true; float ema_decay = 0.95f;
+	bool exp_decay = true; uint32_t decay_start = 20000, decay_interval = 10000; float decay_base = 0.33f;
+	float loss_scale = 128.0f;              // LOSS_SCALE(), common.h:232
+	uint32_t target_batch = 1u << 18;       // samples per batch (src/testbed_nerf.cu:2943)
+	int random_bg = 1;                      // nerf.training.random_bg_color
+};
+struct TrainState {
+	bool ready = false, has_dataset = false;
+	uint32_t seed = 1337, step = 0, ema_step = 0, rays_per_batch = 4096, n_rays_last = 0, n_samples_last = 0;
+	float loss_last = 0.f, lr_last = 0.f;
+	float ms[5] = {0, 0, 0, 0, 0};
+	// dataset
+	DevBuf<float4> images; DevBuf<float> cams;
+	uint32_t n_images = 0; int img_w = 0, img_h = 0; float focal[2] = {0, 0}, principal[2] = {0.5f, 0.5f};
+	// parameters
+	DevBuf<float> master, m1, m2, ema, grads;
+	DevBuf<uint32_t> param_steps;
+	DevBuf<__half> raw;                     // fp16 copy of the raw (non-EMA) weights the training forward pass uses
+	// batch workspace
+	DevBuf<float> ray_o, ray_d, ray_t, ray_target, ray_bg;
+	DevBuf<uint32_t> ray_numsteps, ray_base, counters;
+	DevBuf<float4> coords;                  // warped position, dt per sample
+	DevBuf<uint32_t> sample_ray;
+	DevBuf<__half> act[12];                 // activations: enc, density hidden..., density out, rgb in, rgb hidden..., out
+	DevBuf<__half> dact[4];                 // gradient ping-pong buffers
+	DevBuf<float> loss_acc;
+	void* cublas = nullptr;
+};
+
 } // namespace hn
 
 struct hn_context {
@@ -113,6 +146,9 @@ struct hn_context {
 	int env_w = 0, env_h = 0;
 	hn::DevBuf<float4> hit_pos_pix, hit_nrm, hit_albedo;
 	hn::DevBuf<uint32_t> hit_count;
+
+	hn::TrainCfg train_cfg;
+	hn::TrainState train;
 
 	hn::Options opt;
 	float camera[12] = {1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5f, 0.5f, 2.0f}; // reset_camera default (src/testbed.cu:541-568)
@@ -161,6 +197,14 @@ void save_snapshot_file(hn_context* ctx, const std::string& path);
 void upload_params(hn_context* ctx, const void* blob, size_t n_elements, int dtype);
 void upload_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades);
 void finalize_network(hn_context* ctx);
+// hn_train.cu
+void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, int h, const float* cams, const float focal[2], const float principal[2]);
+void train_init(hn_context* ctx, uint32_t seed);
+void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out);
+void train_apply(hn_context* ctx, float grad_scale);
+void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* t, const float* targets, const float* bgs,
+	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
+void train_release(hn_context* ctx);
 // hn_scene.cpp
 void add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], bool normalize);
 void load_mesh_file(hn_context* ctx, const std::string& path, const float center[3]);

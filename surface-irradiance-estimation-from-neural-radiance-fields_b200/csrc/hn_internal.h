@@ -121,6 +121,9 @@ void launch_march(const FrameArgs& a, const uint8_t* bits, RaySoA rays, const ui
 void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const float* o, const float* d, const float* t0, const uint8_t* alive,
 	uint32_t* counts, float* samples, uint32_t max_per_ray, cudaStream_t s);
 
+void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
+	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s);
+
 // network TU
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,

@@ -307,6 +307,44 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 	}
 }
 
+// a-21 generate_training_samples_nerf (src/testbed_nerf.cu:737-890): per training ray, count the samples along the occupancy
+// DDA (at most NERF_STEPS = 1024), reserve that many slots with ONE atomic, then walk again and write warped position + dt.
+// Rays whose samples do not fit below max_samples get none (:848-852).
+__global__ void __launch_bounds__(128) train_march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, uint32_t n_rays, const float* __restrict__ ray_o,
+	const float* __restrict__ ray_d, const float* __restrict__ ray_t, uint32_t max_samples, uint32_t* __restrict__ counter,
+	uint32_t* __restrict__ numsteps_out, uint32_t* __restrict__ base_out, float4* __restrict__ coords, uint32_t* __restrict__ sample_ray) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_rays) return;
+	const V3 o = ld3(ray_o + 3 * i), d = ld3(ray_d + 3 * i);
+	const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
+	const V3 tdiag = train.hi - train.lo;
+	const float t_far = occ_t_far(a, bits, o, d);
+	uint32_t n = 0;
+	float t = ray_t[i];
+	while (n < 1024u) {
+		t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
+		if (t >= MAX_DEPTH_F) break;
+		t += calc_dt(t, a.cone_angle);
+		++n;
+	}
+	uint32_t base = 0;
+	if (n) {
+		base = atomicAdd(counter, n);
+		if (base + n > max_samples) n = 0;
+	}
+	numsteps_out[i] = n; base_out[i] = base;
+	t = ray_t[i];
+	for (uint32_t j = 0; j < n; ++j) {
+		t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
+		const float dt = calc_dt(t, a.cone_angle);
+		const V3 wp = ((o + t * d) - train.lo) / tdiag;
+		coords[base + j] = make_float4(wp.x, wp.y, wp.z, dt);
+		sample_ray[base + j] = i;
+		t += dt;
+	}
+}
+
 __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const uint8_t* __restrict__ bits, float* __restrict__ o_out, float* __restrict__ d_out,
 	float* __restrict__ t_out, uint8_t* __restrict__ alive_out) {
 	uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -510,6 +548,11 @@ void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_
 void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
 	if (!n_rays) return;
 	secondary_start_kernel<<<(n_rays + 255) / 256, 256, 0, s>>>(a, bits, rays, n_rays, alive_list, counters);
+}
+void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
+	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s) {
+	if (!n_rays) return;
+	train_march_kernel<<<(n_rays + 127) / 128, 128, 0, s>>>(a, bits, n_rays, o, d, t, max_samples, counter, numsteps, base, coords, sample_ray);
 }
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {
 	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;

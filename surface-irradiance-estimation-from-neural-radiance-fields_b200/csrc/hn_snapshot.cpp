@@ -383,6 +383,10 @@ void save_snapshot_file(hn_context* ctx, const std::string& path) {
 	snap.set("mode") = jstr("nerf");
 	snap.set("n_params") = jnum((double)ctx->net.n_params);
 	snap.set("params_type") = jstr("__half");
+	if (ctx->params_host.size() != ctx->net.n_params) { // stale after training steps: read the fp16 inference copy back
+		ctx->params_host.resize(ctx->net.n_params);
+		HN_CUDA(cudaMemcpy(ctx->params_host.data(), ctx->params.p, ctx->net.n_params * sizeof(__half), cudaMemcpyDeviceToHost));
+	}
 	Json pb; pb.type = Json::Binary; pb.str.assign((const char*)ctx->params_host.data(), ctx->params_host.size() * sizeof(__half));
 	snap.set("params_binary") = std::move(pb);
 	snap.set("density_grid_size") = jnum(GRIDSIZE);

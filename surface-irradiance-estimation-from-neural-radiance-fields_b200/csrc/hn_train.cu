@@ -1,0 +1,559 @@
+// a-21 NeRF training step for sm_100a: ray sampling from an in-memory dataset, occupancy-DDA sample generation, forward
+// pass with stored fp16 activations, per-ray two-pass compositing loss, backward through both MLPs and the hash grid, Adam.
+//   Testbed::train_nerf / train_nerf_step       src/testbed_nerf.cu:2929-3075, 3183-3430
+//   generate_training_samples_nerf              src/testbed_nerf.cu:737-890       (train_march_kernel, hn_march.cu)
+//   compute_loss_kernel_train_nerf              src/testbed_nerf.cu:893-1212      (train_loss_kernel)
+//   kernel_grid_backward                        tcnn grid.h:214-320               (grid_backward_kernel: one 16-byte vector atomic per corner, fp32)
+//   MLP forward/backward + weight gradients     tcnn fully_fused_mlp.cu:150-259,775-829 (plain GEMMs: cuBLAS, fp16 in / fp32 accumulate;
+//                                               the reference runs CUTLASS split-K GEMMs for the same weight gradients)
+//   Trainer::training_step, adam_step, Ema, ExponentialDecay   tcnn trainer.h:163-190, optimizers/adam.h:47-118, ema.h, exponential_decay.h
+// Layout: activations [samples][width] fp16 row-major, one buffer per layer; gradients fp32 [n_params] in the layout of the
+// parameter blob [density MLP | rgb MLP | hash grid]. Round-1 scope: the MLP GEMMs are library calls, everything else is
+// hand-written; a fused tcgen05 forward/backward is the next step.
+#include "hn_context.h"
+#include "hn_network.cuh"
+#include "hn_shade.cuh"
+#include <cublas_v2.h>
+#include <algorithm>
+#include <cmath>
+
+namespace hn {
+
+#define HN_CUBLAS(expr) do { cublasStatus_t s__ = (expr); if (s__ != CUBLAS_STATUS_SUCCESS) throw std::runtime_error(std::string(#expr) + " failed: cuBLAS status " + std::to_string((int)s__)); } while (0)
+
+// ---- pcg32 (O'Neill; tcnn/dependencies/pcg32): the generator the reference samples training rays with ----
+struct Pcg32 {
+	uint64_t state, inc;
+	__host__ __device__ Pcg32(uint64_t initstate, uint64_t initseq = 1u) {
+		state = 0u; inc = (initseq << 1u) | 1u;
+		next_uint(); state += initstate; next_uint();
+	}
+	__host__ __device__ uint32_t next_uint() {
+		uint64_t old = state;
+		state = old * 0x5851f42d4c957f2dULL + inc;
+		uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+		uint32_t rot = (uint32_t)(old >> 59u);
+		return (xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31));
+	}
+	__host__ __device__ float next_float() {
+		union { uint32_t u; float f; } x;
+		x.u = (next_uint() >> 9) | 0x3f800000u;
+		return x.f - 1.0f;
+	}
+	__host__ __device__ void advance(uint64_t delta) { // skip-ahead in O(log delta)
+		uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+		while (delta > 0) {
+			if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+			cur_plus = (cur_mult + 1) * cur_plus;
+			cur_mult *= cur_mult;
+			delta /= 2;
+		}
+		state = acc_mult * state + acc_plus;
+	}
+};
+
+struct TrainDataDev {
+	const float4* images; const float* cams;
+	uint32_t n_images; int w, h; float focal[2], principal[2];
+};
+
+// Training rays from the dataset (train_nerf_step ray selection, src/testbed_nerf.cu:789-846 + :1007-1037): ray i of the
+// global stream belongs to image (i * n_images) / n_rays_total, pixel uniformly random (snapped to the pixel centre),
+// random background colour, target = linear_to_srgb(rgb + (1 - a) * bg) (Linear image colour space, sRGB training space).
+// Start t = AABB entry advanced by a random fraction of a step (:817-821).
+__global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step,
+	int random_bg, float bg_r, float bg_g, float bg_b, float* __restrict__ ray_o, float* __restrict__ ray_d, float* __restrict__ ray_t,
+	float* __restrict__ ray_target, float* __restrict__ ray_bg) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_rays) return;
+	const uint32_t gi = i + ray_offset;
+	Pcg32 rng((uint64_t)seed + ((uint64_t)step << 32));
+	rng.advance((uint64_t)gi * 16u); // N_MAX_RANDOM_SAMPLES_PER_RAY
+	const uint32_t img = (uint32_t)(((uint64_t)gi * D.n_images) / n_rays_total) % D.n_images;
+	const float u = rng.next_float(), v = rng.next_float();
+	int px = min(max((int)(u * (float)D.w), 0), D.w - 1), py = min(max((int)(v * (float)D.h), 0), D.h - 1);
+	const float uu = ((float)px + 0.5f) / (float)D.w, vv = ((float)py + 0.5f) / (float)D.h;
+	const float jitter = rng.next_float();
+	float bg[3] = {bg_r, bg_g, bg_b};
+	if (random_bg) { bg[0] = rng.next_float(); bg[1] = rng.next_float(); bg[2] = rng.next_float(); }
+	const float4 tex = __ldg(D.images + ((size_t)img * D.h + py) * D.w + px);
+	const float* c = D.cams + 12 * img;
+	float dx = (uu - D.principal[0]) * (float)D.w / D.focal[0], dy = (vv - D.principal[1]) * (float)D.h / D.focal[1];
+	float d0 = c[0] * dx + c[3] * dy + c[6], d1 = c[1] * dx + c[4] * dy + c[7], d2 = c[2] * dx + c[5] * dy + c[8];
+	const float inv = rsqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+	d0 *= inv; d1 *= inv; d2 *= inv;
+	ray_o[3 * i] = c[9]; ray_o[3 * i + 1] = c[10]; ray_o[3 * i + 2] = c[11];
+	ray_d[3 * i] = d0; ray_d[3 * i + 1] = d1; ray_d[3 * i + 2] = d2;
+	// slab test against the render box
+	float tmin = -1e30f, tmax = 1e30f;
+	const float oo[3] = {c[9], c[10], c[11]}, dd[3] = {d0, d1, d2};
+	#pragma unroll
+	for (int k = 0; k < 3; ++k) {
+		const float t0 = (a.render_aabb[k] - oo[k]) / dd[k], t1 = (a.render_aabb[3 + k] - oo[k]) / dd[k];
+		tmin = fmaxf(tmin, fminf(t0, t1)); tmax = fminf(tmax, fmaxf(t0, t1));
+	}
+	const float step_sz = HN_MIN_STEP; // cone angle 0 (aabb_scale 1); larger scenes start a fraction of the local step later
+	ray_t[i] = tmin <= tmax ? fmaxf(tmin, 0.0f) + jitter * step_sz : 3.0e4f; // beyond MAX_DEPTH: the march finds nothing
+	#pragma unroll
+	for (int k = 0; k < 3; ++k) {
+		const float texc = k == 0 ? tex.x : (k == 1 ? tex.y : tex.z);
+		ray_target[3 * i + k] = linear_to_srgb(texc * tex.w + (1.0f - tex.w) * bg[k]);
+		ray_bg[3 * i + k] = linear_to_srgb(bg[k]);
+	}
+}
+
+// hash-grid features (tcnn fp16 arithmetic, as inference) -> enc [n][32]; SH of the ray direction -> rgb_in[:, 16:32]
+template <int F>
+__global__ void train_encode_kernel(GridLevels g, const __half* __restrict__ table, uint32_t n, const float4* __restrict__ coords,
+	const uint32_t* __restrict__ sample_ray, const float* __restrict__ ray_d, __half* __restrict__ enc, __half* __restrict__ rgb_in) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float4 c = __ldg(coords + i);
+	uint32_t e[16];
+	encode_sample<F>(g, table, c.x, c.y, c.z, e);
+	uint4* dst = reinterpret_cast<uint4*>(enc + (size_t)i * 32);
+	#pragma unroll
+	for (int k = 0; k < 4; ++k) dst[k] = make_uint4(e[4 * k], e[4 * k + 1], e[4 * k + 2], e[4 * k + 3]);
+	const uint32_t r = sample_ray[i];
+	float dx = ray_d[3 * r], dy = ray_d[3 * r + 1], dz = ray_d[3 * r + 2];
+	dx = __fmul_rn(__fadd_rn(dx, 1.0f), 0.5f) * 2.f - 1.f; dy = __fmul_rn(__fadd_rn(dy, 1.0f), 0.5f) * 2.f - 1.f; dz = __fmul_rn(__fadd_rn(dz, 1.0f), 0.5f) * 2.f - 1.f;
+	float sh[16];
+	sh4(dx, dy, dz, sh);
+	uint4* d2 = reinterpret_cast<uint4*>(rgb_in + (size_t)i * 32 + 16);
+	d2[0] = make_uint4(pack_h2(sh[0], sh[1]), pack_h2(sh[2], sh[3]), pack_h2(sh[4], sh[5]), pack_h2(sh[6], sh[7]));
+	d2[1] = make_uint4(pack_h2(sh[8], sh[9]), pack_h2(sh[10], sh[11]), pack_h2(sh[12], sh[13]), pack_h2(sh[14], sh[15]));
+}
+
+__global__ void relu_kernel(__half2* __restrict__ x, size_t n2) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n2) x[i] = __hmax2(x[i], __float2half2_rn(0.f));
+}
+// gradient of a hidden layer: zero where the forward activation was clamped
+__global__ void relu_backward_kernel(__half2* __restrict__ dx, const __half2* __restrict__ act, size_t n2) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n2) return;
+	const __half2 a = act[i]; __half2 d = dx[i];
+	if (!(__low2float(a) > 0.f)) d = __halves2half2(__float2half(0.f), __high2half(d));
+	if (!(__high2float(a) > 0.f)) d = __halves2half2(__low2half(d), __float2half(0.f));
+	dx[i] = d;
+}
+// density-MLP output (16) -> first half of the colour MLP input
+__global__ void copy_density_out_kernel(const __half* __restrict__ d_out, __half* __restrict__ rgb_in, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint4* s = reinterpret_cast<const uint4*>(d_out + (size_t)i * 16);
+	uint4* d = reinterpret_cast<uint4*>(rgb_in + (size_t)i * 32);
+	d[0] = s[0]; d[1] = s[1];
+}
+// dL/d(density out) = dL/d(rgb_in)[:, :16] + dL/dsigma on channel 0
+__global__ void combine_density_grad_kernel(const __half* __restrict__ d_rgb_in, const float* __restrict__ d_sigma, __half* __restrict__ d_dout, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const __half* s = d_rgb_in + (size_t)i * 32;
+	__half* d = d_dout + (size_t)i * 16;
+	d[0] = __float2half(__half2float(s[0]) + d_sigma[i]);
+	#pragma unroll
+	for (int k = 1; k < 16; ++k) d[k] = s[k];
+}
+
+__device__ __forceinline__ float loss_grad(int loss_type, float target, float pred, float& grad) {
+	const float diff = pred - target;
+	if (loss_type == 1) { // huber_loss(alpha 0.1) / 5, nerf_device.cuh:96-112,651
+		const float alpha = 0.1f, ad = fabsf(diff);
+		const float l = ad > alpha ? (ad - 0.5f * alpha) : 0.5f / alpha * diff * diff;
+		grad = (ad > alpha ? (diff > 0 ? 1.0f : -1.0f) : (diff / alpha)) / 5.0f;
+		return l / 5.0f;
+	}
+	grad = 2.0f * diff;
+	return diff * diff;
+}
+__device__ __forceinline__ float rgb_derivative(float v, int act) {
+	switch (act) {
+		case 1: return v > 0.0f ? 1.0f : 0.0f;
+		case 2: { const float d = 1.0f / (1.0f + __expf(-v)); return d * (1 - d); }
+		case 3: return __expf(fminf(fmaxf(v, -10.0f), 10.0f));
+		default: return 1.0f;
+	}
+}
+__device__ __forceinline__ float density_derivative(float v, int act) {
+	switch (act) {
+		case 1: return v > 0.0f ? 1.0f : 0.0f;
+		case 2: { const float d = 1.0f / (1.0f + __expf(-v)); return d * (1 - d); }
+		case 3: return __expf(fminf(fmaxf(v, -15.0f), 15.0f));
+		default: return 1.0f;
+	}
+}
+
+// compute_loss_kernel_train_nerf (src/testbed_nerf.cu:893-1212), one thread per ray: composite once to get the ray colour,
+// then again to emit dL/d(network output) per sample. out/d_out_density: [samples][16] fp16. Writes d_out [samples][16] fp16
+// (rows 0..2, rest zero) and d_sigma [samples] (fp32), both scaled by loss_scale / n_rays_total; samples past the
+// early stop (T < 1e-4) get zero gradients (the reference compacts them away). loss_acc += mean(loss_rgb) / n_rays_total.
+__global__ void train_loss_kernel(uint32_t n_rays, uint32_t n_rays_total, const uint32_t* __restrict__ numsteps_in, const uint32_t* __restrict__ base_in,
+	const float4* __restrict__ coords, const __half* __restrict__ out, const __half* __restrict__ density_out, const float* __restrict__ ray_target,
+	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, __half* __restrict__ d_out, float* __restrict__ d_sigma,
+	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	float my_loss = 0.f;
+	if (i < n_rays) {
+		const uint32_t numsteps = numsteps_in[i], base = base_in[i];
+		const float dt_range = HN_MIN_STEP * 128.0f - HN_MIN_STEP;
+		float T = 1.f;
+		float rr = 0.f, rg = 0.f, rb = 0.f;
+		uint32_t compacted = 0;
+		for (; compacted < numsteps; ++compacted) {
+			if (T < 1e-4f) break;
+			const size_t s = base + compacted;
+			const __half* o = out + s * 16;
+			const float dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
+			const float alpha = 1.f - __expf(-act_density(__half2float(density_out[s * 16]), density_act) * dt);
+			const float weight = alpha * T;
+			rr += weight * act_rgb(__half2float(o[0]), rgb_act); rg += weight * act_rgb(__half2float(o[1]), rgb_act); rb += weight * act_rgb(__half2float(o[2]), rgb_act);
+			T *= (1.f - alpha);
+		}
+		if (compacted == numsteps) { rr += T * ray_bg[3 * i]; rg += T * ray_bg[3 * i + 1]; rb += T * ray_bg[3 * i + 2]; }
+		if (used_out) used_out[i] = compacted;
+		float gr, gg, gb;
+		const float l = loss_grad(loss_type, ray_target[3 * i], rr, gr) + loss_grad(loss_type, ray_target[3 * i + 1], rg, gg) + loss_grad(loss_type, ray_target[3 * i + 2], rb, gb);
+		my_loss = numsteps ? l / 3.0f / (float)n_rays_total : 0.f;
+		const float ls = loss_scale / (float)n_rays_total;
+		const float l2_reg = rgb_act == 3 ? 1e-4f : 0.0f;
+		float r2 = 0.f, g2 = 0.f, b2 = 0.f;
+		T = 1.f;
+		for (uint32_t j = 0; j < numsteps; ++j) {
+			const size_t s = base + j;
+			uint4* dst = reinterpret_cast<uint4*>(d_out + s * 16);
+			if (j >= compacted) { dst[0] = make_uint4(0, 0, 0, 0); dst[1] = make_uint4(0, 0, 0, 0); d_sigma[s] = 0.f; continue; }
+			const __half* o = out + s * 16;
+			const float o0 = __half2float(o[0]), o1 = __half2float(o[1]), o2 = __half2float(o[2]), sraw = __half2float(density_out[s * 16]);
+			const float cr = act_rgb(o0, rgb_act), cg = act_rgb(o1, rgb_act), cb = act_rgb(o2, rgb_act);
+			const float dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
+			const float alpha = 1.f - __expf(-act_density(sraw, density_act) * dt);
+			const float weight = alpha * T;
+			r2 += weight * cr; g2 += weight * cg; b2 += weight * cb;
+			T *= (1.f - alpha);
+			const float sr = rr - r2, sg = rg - g2, sb = rb - b2; // suffix of the ray behind this sample
+			const float d0 = ls * (weight * gr * rgb_derivative(o0, rgb_act) + fmaxf(0.0f, l2_reg * o0));
+			const float d1 = ls * (weight * gg * rgb_derivative(o1, rgb_act) + fmaxf(0.0f, l2_reg * o1));
+			const float d2 = ls * (weight * gb * rgb_derivative(o2, rgb_act) + fmaxf(0.0f, l2_reg * o2));
+			dst[0] = make_uint4(pack_h2(d0, d1), pack_h2(d2, 0.f), 0, 0); dst[1] = make_uint4(0, 0, 0, 0);
+			d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T * cr - sr) + gg * (T * cg - sg) + gb * (T * cb - sb)));
+		}
+	}
+	#pragma unroll
+	for (int d = 16; d > 0; d >>= 1) my_loss += __shfl_xor_sync(0xffffffffu, my_loss, d);
+	if ((threadIdx.x & 31) == 0 && my_loss != 0.f) atomicAdd(loss_acc, my_loss);
+}
+
+// kernel_grid_backward (tcnn grid.h:214-320): thread = (sample, level); dL/dfeature scattered to the 8 corners with the
+// trilinear weights. fp32 gradients; F = 4 uses ONE 16-byte vector atomic per corner (red.global.add.v4.f32, sm_90+).
+template <int F>
+__global__ void grid_backward_kernel(GridLevels g, uint32_t n, const float4* __restrict__ coords, const __half* __restrict__ d_enc, float* __restrict__ grid_grad) {
+	constexpr uint32_t L = 32 / F;
+	const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t i = tid / L, l = tid % L;
+	if (i >= n) return;
+	const __half* de = d_enc + (size_t)i * 32 + l * F;
+	float gr[F];
+	bool any = false;
+	#pragma unroll
+	for (int f = 0; f < F; ++f) { gr[f] = __half2float(de[f]); any |= gr[f] != 0.f; }
+	if (!any) return;
+	const float4 c = __ldg(coords + i);
+	const float scale = g.scale[l];
+	const uint32_t res = g.res[l], size = g.size[l], mask = g.mask[l];
+	float fx = fmaf(scale, c.x, 0.5f), fy = fmaf(scale, c.y, 0.5f), fz = fmaf(scale, c.z, 0.5f);
+	const float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
+	const uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
+	fx -= flx; fy -= fly; fz -= flz;
+	float* lvl = grid_grad + (size_t)g.offset[l] * F;
+	#pragma unroll
+	for (int k = 0; k < 8; ++k) {
+		const uint32_t x = gx + (k & 1), y = gy + ((k >> 1) & 1), z = gz + ((k >> 2) & 1);
+		const uint32_t h = g.hashed[l] ? (x ^ (y * 2654435761u) ^ (z * 805459861u)) : (x + y * res + z * res * res);
+		const uint32_t idx = mask ? (h & mask) : (h < size ? h : h % size);
+		const float w = ((k & 1) ? fx : 1.f - fx) * ((k & 2) ? fy : 1.f - fy) * ((k & 4) ? fz : 1.f - fz);
+		if (F == 4) atomicAdd(reinterpret_cast<float4*>(lvl + (size_t)idx * 4), make_float4(w * gr[0], w * gr[1], w * gr[2], w * gr[3]));
+		else atomicAdd(reinterpret_cast<float2*>(lvl + (size_t)idx * 2), make_float2(w * gr[0], w * gr[1]));
+	}
+}
+
+// adam_step (tcnn optimizers/adam.h:47-118) + Ema (ema.h) fused: hash-grid entries with a zero gradient are skipped and keep
+// their own step counter; L2 regularisation only on the MLP ("matrix") weights.
+__global__ void adam_kernel(uint32_t n, uint32_t n_matrix, float grad_scale, float inv_loss_scale, float lr, float beta1, float beta2, float eps, float l2_reg,
+	int use_ema, float ema_decay, float ema_debias, float* __restrict__ master, __half* __restrict__ raw, __half* __restrict__ inference,
+	const float* __restrict__ grads, float* __restrict__ m1, float* __restrict__ m2, float* __restrict__ ema, uint32_t* __restrict__ steps) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float w = master[i];
+	float gradient = grads[i] * grad_scale * inv_loss_scale;
+	const bool skip = i >= n_matrix && gradient == 0.f;
+	if (!skip) {
+		if (i < n_matrix) gradient += l2_reg * w;
+		const float a = m1[i] = beta1 * m1[i] + (1 - beta1) * gradient;
+		const float b = m2[i] = beta2 * m2[i] + (1 - beta2) * gradient * gradient;
+		const uint32_t t = ++steps[i];
+		const float l = lr * sqrtf(1 - powf(beta2, (float)t)) / (1 - powf(beta1, (float)t));
+		w -= (l / (sqrtf(b) + eps)) * a;
+		master[i] = w;
+		raw[i] = __float2half(w);
+	}
+	if (use_ema) { // every parameter, every step (ema.h: tmp = decay * ema + (1 - decay) * w; weights_ema = tmp / (1 - decay^t))
+		const float e = ema[i] = ema_decay * ema[i] + (1 - ema_decay) * w;
+		inference[i] = __float2half(e / ema_debias);
+	} else if (!skip) {
+		inference[i] = __float2half(w);
+	}
+}
+__global__ void half_to_float_kernel(const __half* __restrict__ in, float* __restrict__ out, size_t n) {
+	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) out[i] = __half2float(in[i]);
+}
+
+FrameArgs train_frame_args(hn_context* ctx); // hn_api.cpp: aabbs, occupancy bounds, cone angle, activations
+
+namespace {
+
+cublasHandle_t handle(hn_context* ctx) {
+	if (!ctx->train.cublas) {
+		cublasHandle_t h;
+		HN_CUBLAS(cublasCreate(&h));
+		HN_CUBLAS(cublasSetMathMode(h, CUBLAS_DEFAULT_MATH));
+		ctx->train.cublas = h;
+	}
+	cublasHandle_t h = (cublasHandle_t)ctx->train.cublas;
+	HN_CUBLAS(cublasSetStream(h, ctx->stream));
+	return h;
+}
+// row-major views: Y[B][N] = X[B][K] W[N][K]^T ; dX[B][K] = dY[B][N] W[N][K] ; dW[N][K] (fp32) = dY[B][N]^T X[B][K]
+void gemm_forward(cublasHandle_t h, uint32_t B, int N, int K, const __half* X, const __half* W, __half* Y) {
+	const float one = 1.f, zero = 0.f;
+	HN_CUBLAS(cublasGemmEx(h, CUBLAS_OP_T, CUBLAS_OP_N, N, (int)B, K, &one, W, CUDA_R_16F, K, X, CUDA_R_16F, K, &zero, Y, CUDA_R_16F, N, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT));
+}
+void gemm_backward_input(cublasHandle_t h, uint32_t B, int N, int K, const __half* dY, const __half* W, __half* dX) {
+	const float one = 1.f, zero = 0.f;
+	HN_CUBLAS(cublasGemmEx(h, CUBLAS_OP_N, CUBLAS_OP_N, K, (int)B, N, &one, W, CUDA_R_16F, K, dY, CUDA_R_16F, N, &zero, dX, CUDA_R_16F, K, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT));
+}
+void gemm_backward_weights(cublasHandle_t h, uint32_t B, int N, int K, const __half* dY, const __half* X, float* dW) {
+	const float one = 1.f, zero = 0.f;
+	HN_CUBLAS(cublasGemmEx(h, CUBLAS_OP_N, CUBLAS_OP_T, K, N, (int)B, &one, X, CUDA_R_16F, K, dY, CUDA_R_16F, N, &zero, dW, CUDA_R_32F, K, CUBLAS_COMPUTE_32F, CUBLAS_GEMM_DEFAULT));
+}
+inline uint32_t blocks(size_t n, uint32_t b = 256) { return (uint32_t)((n + b - 1) / b); }
+
+struct Ev {
+	cudaEvent_t a = nullptr, b = nullptr; bool on; cudaStream_t s;
+	Ev(bool e, cudaStream_t st) : on(e), s(st) { if (on) { cudaEventCreate(&a); cudaEventCreate(&b); } }
+	~Ev() { if (on) { cudaEventDestroy(a); cudaEventDestroy(b); } }
+	void start() { if (on) cudaEventRecord(a, s); }
+	void stop(float& acc) { if (on) { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); acc = ms; } }
+};
+
+void ensure_batch(hn_context* ctx, uint32_t n_rays, uint32_t max_samples) {
+	TrainState& t = ctx->train;
+	t.ray_o.ensure((size_t)n_rays * 3); t.ray_d.ensure((size_t)n_rays * 3); t.ray_t.ensure(n_rays);
+	t.ray_target.ensure((size_t)n_rays * 3); t.ray_bg.ensure((size_t)n_rays * 3);
+	t.ray_numsteps.ensure(n_rays); t.ray_base.ensure(n_rays); t.counters.ensure(4); t.loss_acc.ensure(4);
+	t.coords.ensure(max_samples); t.sample_ray.ensure(max_samples);
+	const uint32_t Hd = ctx->net.density_hidden, Hr = ctx->net.rgb_hidden;
+	if (Hd + Hr + 4 > 12) throw std::runtime_error("training supports at most 8 hidden layers in total");
+	for (uint32_t l = 0; l < Hd + Hr + 4; ++l) t.act[l].ensure((size_t)max_samples * 64);
+	for (auto& d : t.dact) d.ensure((size_t)max_samples * 64);
+}
+
+// march (samples) -> forward -> loss -> backward into t.grads. Rays are already in t.ray_*.
+void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, uint32_t max_samples, int loss_type, float loss_scale, uint32_t* used_dev) {
+	TrainState& t = ctx->train;
+	cudaStream_t s = ctx->stream;
+	const NetCfg& net = ctx->net;
+	const uint32_t Hd = net.density_hidden, Hr = net.rgb_hidden;
+	const bool prof = ctx->opt.profile != 0;
+	Ev ev(prof, s);
+	FrameArgs a = train_frame_args(ctx);
+	ev.start();
+	HN_CUDA(cudaMemsetAsync(t.counters.p, 0, 4 * sizeof(uint32_t), s));
+	HN_CUDA(cudaMemsetAsync(t.loss_acc.p, 0, 4 * sizeof(float), s));
+	launch_train_march(a, ctx->bitfield.p, n_rays, t.ray_o.p, t.ray_d.p, t.ray_t.p, max_samples, t.counters.p, t.ray_numsteps.p, t.ray_base.p, t.coords.p, t.sample_ray.p, s);
+	uint32_t n = 0;
+	HN_CUDA(cudaMemcpyAsync(&n, t.counters.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	ev.stop(t.ms[0]);
+	n = std::min(n, max_samples); // rays beyond the cap reserved slots but wrote nothing; their numsteps is 0
+	t.n_samples_last = n; t.n_rays_last = n_rays;
+	HN_CUDA(cudaMemsetAsync(t.grads.p, 0, net.n_params * sizeof(float), s));
+	if (!n) return;
+	cublasHandle_t h = handle(ctx);
+	const __half* W = t.raw.p;
+	__half* enc = t.act[0].p; __half* d_out = t.act[Hd + 1].p; __half* rgb_in = t.act[Hd + 2].p; __half* out = t.act[Hd + 3 + Hr].p;
+	// ---- forward
+	ev.start();
+	if (net.F == 4) train_encode_kernel<4><<<blocks(n, 128), 128, 0, s>>>(ctx->levels, W + net.grid_offset, n, t.coords.p, t.sample_ray.p, t.ray_d.p, enc, rgb_in);
+	else train_encode_kernel<2><<<blocks(n, 128), 128, 0, s>>>(ctx->levels, W + net.grid_offset, n, t.coords.p, t.sample_ray.p, t.ray_d.p, enc, rgb_in);
+	auto mlp_forward = [&](const __half* w, uint32_t first_act, uint32_t hidden) {
+		int K = 32;
+		for (uint32_t l = 0; l < hidden; ++l) {
+			gemm_forward(h, n, 64, K, t.act[first_act + l].p, w, t.act[first_act + l + 1].p);
+			relu_kernel<<<blocks((size_t)n * 32), 256, 0, s>>>((__half2*)t.act[first_act + l + 1].p, (size_t)n * 32);
+			w += 64 * K; K = 64;
+		}
+		gemm_forward(h, n, 16, 64, t.act[first_act + hidden].p, w, t.act[first_act + hidden + 1].p);
+	};
+	mlp_forward(W + net.density_w_offset, 0, Hd);
+	copy_density_out_kernel<<<blocks(n), 256, 0, s>>>(d_out, rgb_in, n);
+	mlp_forward(W + net.rgb_w_offset, Hd + 2, Hr);
+	ev.stop(t.ms[1]);
+	// ---- loss and dL/d(output)
+	ev.start();
+	__half* g_out = t.dact[0].p;               // [n][16]
+	float* d_sigma = (float*)t.dact[3].p;      // [n] fp32 (buffer holds n*64 halfs)
+	train_loss_kernel<<<blocks(n_rays, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
+		loss_type, loss_scale, a.rgb_act, a.density_act, g_out, d_sigma, used_dev, t.loss_acc.p);
+	ev.stop(t.ms[2]);
+	// ---- backward
+	ev.start();
+	// returns the gradient w.r.t. the MLP input [n][32] in dact[ret]
+	auto mlp_backward = [&](const __half* w, float* gw, uint32_t first_act, uint32_t hidden, __half* g_top /*[n][16]*/, int buf_a, int buf_b) -> __half* {
+		// weight offsets per layer
+		std::vector<size_t> off(hidden + 1);
+		size_t o = 0; int K = 32;
+		for (uint32_t l = 0; l < hidden; ++l) { off[l] = o; o += (size_t)64 * K; K = 64; }
+		off[hidden] = o;
+		__half* g = g_top;
+		int N = 16;
+		int cur = buf_a;
+		for (int l = (int)hidden; l >= 0; --l) {
+			const int Kin = l == 0 ? 32 : 64;
+			const __half* x = t.act[first_act + l].p;
+			gemm_backward_weights(h, n, N, Kin, g, x, gw + off[l]);
+			__half* gx = t.dact[cur].p;
+			gemm_backward_input(h, n, N, Kin, g, w + off[l], gx);
+			if (l > 0) relu_backward_kernel<<<blocks((size_t)n * 32), 256, 0, s>>>((__half2*)gx, (const __half2*)x, (size_t)n * 32);
+			g = gx; N = 64;
+			cur = (cur == buf_a) ? buf_b : buf_a;
+		}
+		return g;
+	};
+	__half* g_rgb_in = mlp_backward(W + net.rgb_w_offset, t.grads.p + net.rgb_w_offset, Hd + 2, Hr, g_out, 1, 2);
+	__half* g_dout = t.dact[0].p; // dL/d(output) is consumed; reuse its buffer for [n][16]
+	combine_density_grad_kernel<<<blocks(n), 256, 0, s>>>(g_rgb_in, d_sigma, g_dout, n);
+	__half* g_enc = mlp_backward(W + net.density_w_offset, t.grads.p + net.density_w_offset, 0, Hd, g_dout, 1, 2);
+	float* grid_grad = t.grads.p + net.grid_offset;
+	if (net.F == 4) grid_backward_kernel<4><<<blocks((size_t)n * 8, 256), 256, 0, s>>>(ctx->levels, n, t.coords.p, g_enc, grid_grad);
+	else grid_backward_kernel<2><<<blocks((size_t)n * 16, 256), 256, 0, s>>>(ctx->levels, n, t.coords.p, g_enc, grid_grad);
+	ev.stop(t.ms[3]);
+	HN_CUDA(cudaGetLastError());
+}
+
+void check_ready(hn_context* ctx, bool need_dataset) {
+	if (!ctx->has_net || !ctx->has_params) throw std::runtime_error("training needs a network config and parameters");
+	if (!ctx->has_bitfield) throw std::runtime_error("training needs an occupancy grid (hn_set_density_grid)");
+	if (need_dataset && !ctx->train.has_dataset) throw std::runtime_error("no training dataset (hn_train_set_dataset)");
+	if (!ctx->train.ready) train_init(ctx, ctx->train.seed);
+}
+
+} // namespace
+
+void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, int h, const float* cams, const float focal[2], const float principal[2]) {
+	if (!rgba || !cams || n == 0 || w <= 0 || h <= 0 || !(focal[0] > 0.f) || !(focal[1] > 0.f)) throw std::runtime_error("bad training dataset arguments");
+	TrainState& t = ctx->train;
+	const size_t px = (size_t)n * w * h;
+	t.images.ensure(px); t.cams.ensure((size_t)n * 12);
+	HN_CUDA(cudaMemcpy(t.images.p, rgba, px * sizeof(float4), cudaMemcpyHostToDevice));
+	HN_CUDA(cudaMemcpy(t.cams.p, cams, (size_t)n * 12 * sizeof(float), cudaMemcpyHostToDevice));
+	t.n_images = n; t.img_w = w; t.img_h = h;
+	t.focal[0] = focal[0]; t.focal[1] = focal[1]; t.principal[0] = principal[0]; t.principal[1] = principal[1];
+	t.has_dataset = true;
+}
+
+void train_init(hn_context* ctx, uint32_t seed) {
+	if (!ctx->has_net || !ctx->has_params) throw std::runtime_error("training needs a network config and parameters");
+	TrainState& t = ctx->train;
+	const size_t n = ctx->net.n_params;
+	cudaStream_t s = ctx->stream;
+	t.master.ensure(n); t.m1.ensure(n); t.m2.ensure(n); t.ema.ensure(n); t.grads.ensure(n); t.param_steps.ensure(n); t.raw.ensure(n);
+	HN_CUDA(cudaMemcpyAsync(t.raw.p, ctx->params.p, n * sizeof(__half), cudaMemcpyDeviceToDevice, s));
+	half_to_float_kernel<<<blocks(n), 256, 0, s>>>(t.raw.p, t.master.p, n);
+	HN_CUDA(cudaMemsetAsync(t.m1.p, 0, n * sizeof(float), s)); HN_CUDA(cudaMemsetAsync(t.m2.p, 0, n * sizeof(float), s));
+	HN_CUDA(cudaMemsetAsync(t.ema.p, 0, n * sizeof(float), s)); HN_CUDA(cudaMemsetAsync(t.grads.p, 0, n * sizeof(float), s));
+	HN_CUDA(cudaMemsetAsync(t.param_steps.p, 0, n * sizeof(uint32_t), s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	t.seed = seed; t.step = 0; t.ema_step = 0; t.rays_per_batch = 4096; t.loss_last = 0.f;
+	t.ready = true;
+}
+
+void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
+	check_ready(ctx, true);
+	TrainState& t = ctx->train;
+	const TrainCfg& c = ctx->train_cfg;
+	cudaStream_t s = ctx->stream;
+	const uint32_t world = (uint32_t)std::max(ctx->world, 1), rank = (uint32_t)ctx->rank;
+	if (!n_rays) n_rays = t.rays_per_batch;
+	const uint32_t max_samples = c.target_batch * 2u;
+	ensure_batch(ctx, n_rays, max_samples);
+	FrameArgs a = train_frame_args(ctx);
+	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
+	const float* bg = ctx->opt.background_color;
+	train_raygen_kernel<<<blocks(n_rays), 256, 0, s>>>(D, a, n_rays, rank * n_rays, n_rays * world, t.seed, t.step, c.random_bg, bg[0], bg[1], bg[2],
+		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p);
+	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr);
+	float loss = 0.f;
+	HN_CUDA(cudaMemcpyAsync(&loss, t.loss_acc.p, sizeof(float), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	t.loss_last = loss;
+	if (loss_out) *loss_out = loss;
+	// rays per batch follow the measured samples per ray towards the target batch size (src/testbed_nerf.cu:3049-3056)
+	if (t.n_samples_last > 0) {
+		const double per_ray = (double)t.n_samples_last / (double)n_rays;
+		uint32_t next = (uint32_t)std::min<double>((double)c.target_batch / per_ray, 1u << 20);
+		next = std::max(128u, (next + 127u) / 128u * 128u);
+		t.rays_per_batch = next;
+	}
+}
+
+void train_apply(hn_context* ctx, float grad_scale) {
+	check_ready(ctx, false);
+	TrainState& t = ctx->train;
+	const TrainCfg& c = ctx->train_cfg;
+	cudaStream_t s = ctx->stream;
+	Ev ev(ctx->opt.profile != 0, s);
+	ev.start();
+	// ExponentialDecay (exponential_decay.h): base lr scaled by decay_base^((step - start) / interval + 1) once step >= start
+	float lr = c.lr;
+	if (c.exp_decay && t.step >= c.decay_start && c.decay_interval > 0) lr *= std::pow(c.decay_base, (float)((t.step - c.decay_start) / c.decay_interval + 1));
+	t.lr_last = lr;
+	++t.ema_step;
+	const float debias = c.ema ? 1.0f - std::pow(c.ema_decay, (float)t.ema_step) : 1.0f;
+	const uint32_t n = (uint32_t)ctx->net.n_params, n_matrix = (uint32_t)ctx->net.grid_offset; // blob = [density MLP | rgb MLP | grid]
+	adam_kernel<<<blocks(n), 256, 0, s>>>(n, n_matrix, grad_scale, 1.0f / c.loss_scale, lr, c.beta1, c.beta2, c.epsilon, c.l2_reg, c.ema ? 1 : 0, c.ema_decay, debias,
+		t.master.p, t.raw.p, ctx->params.p, t.grads.p, t.m1.p, t.m2.p, t.ema.p, t.param_steps.p);
+	ev.stop(t.ms[4]);
+	++t.step;
+	ctx->params_host.clear(); // the host copy (snapshot writer) is stale now; hn_save_snapshot reads the device copy back
+	HN_CUDA(cudaGetLastError());
+}
+
+void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* tt, const float* targets, const float* bgs,
+	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps) {
+	check_ready(ctx, false);
+	TrainState& t = ctx->train;
+	cudaStream_t s = ctx->stream;
+	if (!n_rays) throw std::runtime_error("no rays");
+	const uint32_t max_samples = std::max<uint32_t>(n_rays * 64u, 1u << 16);
+	ensure_batch(ctx, n_rays, max_samples);
+	HN_CUDA(cudaMemcpyAsync(t.ray_o.p, o, (size_t)n_rays * 12, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(t.ray_d.p, d, (size_t)n_rays * 12, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(t.ray_t.p, tt, (size_t)n_rays * 4, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(t.ray_target.p, targets, (size_t)n_rays * 12, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(t.ray_bg.p, bgs, (size_t)n_rays * 12, cudaMemcpyHostToDevice, s));
+	DevBuf<uint32_t> used; used.ensure(n_rays);
+	HN_CUDA(cudaMemsetAsync(used.p, 0, (size_t)n_rays * 4, s));
+	forward_backward(ctx, n_rays, n_rays, max_samples, loss_type, loss_scale, used.p);
+	if (loss_out) HN_CUDA(cudaMemcpyAsync(loss_out, t.loss_acc.p, sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (grads_host) HN_CUDA(cudaMemcpyAsync(grads_host, t.grads.p, ctx->net.n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (n_steps) HN_CUDA(cudaMemcpyAsync(n_steps, used.p, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+}
+
+void train_release(hn_context* ctx) {
+	if (ctx->train.cublas) { cublasDestroy((cublasHandle_t)ctx->train.cublas); ctx->train.cublas = nullptr; }
+}
+
+} // namespace hn

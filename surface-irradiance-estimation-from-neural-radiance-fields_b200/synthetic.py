@@ -132,3 +132,33 @@ def envmap(width: int = 1024, height: int = 512, seed: int = 3, lobe=(0.3, 0.7),
     img[..., :3] = np.maximum(img[..., :3], 0.0)
     img[..., 3] = 1.0
     return img
+
+
+def sphere_dataset(n_views: int = 16, res: int = 64, radius: float = 0.3, seed: int = 9, fov_deg: float = 50.625):
+    """Analytic training set (SURVEY config 5 stand-in for a rendered one): views of a patterned sphere centred in the unit
+    cube. Returns (images [n][res][res][4] linear RGB + straight alpha, cameras [n][12], focal length in pixels)."""
+    rng = np.random.default_rng(seed)
+    focal = 0.5 * res / np.tan(0.5 * np.deg2rad(fov_deg))
+    imgs = np.zeros((n_views, res, res, 4), np.float32)
+    cams = np.zeros((n_views, 12), np.float32)
+    c = np.array([0.5, 0.5, 0.5], np.float64)
+    ys, xs = np.meshgrid(np.arange(res) + 0.5, np.arange(res) + 0.5, indexing="ij")
+    for i in range(n_views):
+        eye = rng.normal(size=3)
+        eye = eye / np.linalg.norm(eye) * 1.5 + c
+        cam = np.asarray(look_at_camera(tuple(eye), tuple(c)), np.float64).reshape(4, 3)
+        cams[i] = cam.reshape(12).astype(np.float32)
+        d = ((xs / res - 0.5) * res / focal)[..., None] * cam[0] + ((ys / res - 0.5) * res / focal)[..., None] * cam[1] + cam[2]
+        d /= np.linalg.norm(d, axis=-1, keepdims=True)
+        oc = cam[3] - c
+        b = (d * oc).sum(-1)
+        disc = b * b - ((oc * oc).sum() - radius * radius)
+        hit = disc > 0
+        t = -b - np.sqrt(np.maximum(disc, 0))
+        p = cam[3] + t[..., None] * d
+        n = (p - c) / radius
+        shade = 0.35 + 0.65 * np.clip(n @ np.array([0.5, 0.7, 0.5]), 0, 1)
+        col = 0.5 + 0.5 * np.sin(9.0 * p + np.array([0.0, 2.0, 4.0]))
+        imgs[i, ..., :3] = np.where(hit[..., None], col * shade[..., None], 0.0)
+        imgs[i, ..., 3] = hit
+    return imgs, cams, float(focal)

@@ -50,6 +50,14 @@ class FrameStats(C.Structure):
     ]
 
 
+class TrainStats(C.Structure):
+    _fields_ = [
+        ("step", C.c_uint32), ("rays_per_batch", C.c_uint32), ("n_rays_last", C.c_uint32), ("n_samples_last", C.c_uint32),
+        ("loss_last", C.c_float), ("learning_rate", C.c_float), ("ms_sample", C.c_float), ("ms_forward", C.c_float), ("ms_loss", C.c_float),
+        ("ms_backward", C.c_float), ("ms_optimizer", C.c_float),
+    ]
+
+
 # every symbol include/hybrid_nerf.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "hn_create", "hn_destroy", "hn_last_error", "hn_version", "hn_load_network_config", "hn_load_network_config_string",
@@ -58,7 +66,8 @@ EXPORTS = [
     "hn_get_scene_aabb", "hn_set_option", "hn_get_option", "hn_render_frame", "hn_render_to_host", "hn_set_camera",
     "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
-    "hn_op_transmittance",
+    "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
+    "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -95,10 +104,28 @@ _lib.hn_set_camera.argtypes = [C.c_void_p, C.c_void_p]
 _lib.hn_set_tile_shard.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
 _lib.hn_tile_count.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _u32p]
 _lib.hn_get_frame_stats.argtypes = [C.c_void_p, C.POINTER(FrameStats)]
+_lib.hn_train_set_dataset.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_train_init.argtypes = [C.c_void_p, C.c_uint32]
+_lib.hn_train_accumulate.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_float)]
+_lib.hn_train_gradient_buffer.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+_lib.hn_train_apply.argtypes = [C.c_void_p, C.c_float]
+_lib.hn_train_step.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_float)]
+_lib.hn_get_train_stats.argtypes = [C.c_void_p, C.POINTER(TrainStats)]
+_lib.hn_op_train_gradients.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.POINTER(C.c_float), C.c_void_p, C.c_void_p]
 _lib.hn_set_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
 _lib.hn_op_read_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_env_light_dirs.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
 _lib.hn_op_transmittance.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+
+
+def cudart_memcpy_d2h(out: np.ndarray, dev_ptr: int) -> int:
+    """Device -> host copy of out.nbytes bytes through the CUDA runtime the library is linked against (tests, tooling)."""
+    try:
+        rt = C.CDLL("libcudart.so.12")
+    except OSError:
+        rt = C.CDLL("/usr/local/cuda/lib64/libcudart.so.12")
+    rt.cudaMemcpy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+    return int(rt.cudaMemcpy(out.ctypes.data_as(C.c_void_p), C.c_void_p(dev_ptr), out.nbytes, 2))
 
 
 def _f32(a):
@@ -323,6 +350,63 @@ class Testbed:
         out = np.empty((p.shape[0], 4), np.float16)
         self._check(_lib.hn_op_network(self._h, _ptr(p), _ptr(d), p.shape[0], _ptr(out)))
         return out
+
+    # ---- a-21 training (pyngp: Testbed.train / .frame with shall_train, .loss, .training_step; src/python_api.cu:427-440,584-590)
+    def set_training_data(self, images: np.ndarray, cameras: np.ndarray, focal_px, principal=(0.5, 0.5)):
+        """images float32 [n][h][w][4] (linear RGB, straight alpha), cameras [n][12] (mat4x3 columns), pinhole intrinsics."""
+        im = _f32(images)
+        cams = _f32(cameras).reshape(-1, 12)
+        if im.ndim != 4 or im.shape[3] != 4 or im.shape[0] != cams.shape[0]:
+            raise RuntimeError("images must be [n][h][w][4] with one camera each")
+        f = _f32(np.broadcast_to(np.asarray(focal_px, np.float32), (2,)).copy())
+        pp = _f32(principal)
+        self._check(_lib.hn_train_set_dataset(self._h, _ptr(im), im.shape[0], im.shape[2], im.shape[1], _ptr(cams), _ptr(f), _ptr(pp)))
+
+    def reset_trainer(self, seed: int = 1337):
+        self._check(_lib.hn_train_init(self._h, seed))
+
+    def train(self, n_steps: int = 1) -> float:
+        loss = C.c_float(0)
+        self._check(_lib.hn_train_step(self._h, n_steps, C.byref(loss)))
+        return float(loss.value)
+
+    def train_accumulate(self, n_rays: int = 0) -> float:
+        loss = C.c_float(0)
+        self._check(_lib.hn_train_accumulate(self._h, n_rays, C.byref(loss)))
+        return float(loss.value)
+
+    def train_gradient_buffer(self):
+        """(device pointer, number of floats) of the fp32 gradient buffer: all-reduce it between accumulate and apply."""
+        ptr = C.c_void_p(0); n = C.c_size_t(0)
+        self._check(_lib.hn_train_gradient_buffer(self._h, C.byref(ptr), C.byref(n)))
+        return int(ptr.value), int(n.value)
+
+    def train_apply(self, grad_scale: float = 1.0):
+        self._check(_lib.hn_train_apply(self._h, grad_scale))
+
+    def train_stats(self) -> TrainStats:
+        st = TrainStats()
+        _lib.hn_get_train_stats(self._h, C.byref(st))
+        return st
+
+    @property
+    def loss(self) -> float:
+        return float(self.train_stats().loss_last)
+
+    @property
+    def training_step(self) -> int:
+        return int(self.train_stats().step)
+
+    def op_train_gradients(self, origins, dirs, t_start, targets, backgrounds, loss_type=1, loss_scale=128.0):
+        o, d, t = _f32(origins).reshape(-1, 3), _f32(dirs).reshape(-1, 3), _f32(t_start).reshape(-1)
+        tg, bg = _f32(targets).reshape(-1, 3), _f32(backgrounds).reshape(-1, 3)
+        n = o.shape[0]
+        grads = np.empty(int(self.network_info().n_params), np.float32)
+        steps = np.empty(n, np.uint32)
+        loss = C.c_float(0)
+        self._check(_lib.hn_op_train_gradients(self._h, n, _ptr(o), _ptr(d), _ptr(t), _ptr(tg), _ptr(bg), int(loss_type), float(loss_scale),
+                                               C.byref(loss), _ptr(grads), _ptr(steps)))
+        return float(loss.value), grads, steps
 
     # ---- a-16 environment map (Testbed::m_envmap, testbed.h:1227-1241)
     def set_envmap(self, rgba: np.ndarray | None):

@@ -158,6 +158,15 @@ def make_ref_env():
         t3 = (C.c_float * 3)(); ref.ref_cosine_hemisphere(fa(*u[i]), t3); cos_h[i] = t3[:]
         t3 = (C.c_float * 3)(); ref.ref_spherical_cap(fa(*u[i]), C.c_float(float(caps[i])), t3); cap[i] = t3[:]
     out["u"], out["cosine_hemisphere"], out["cap_height"], out["spherical_cap"] = u, cos_h, caps, cap
+    # a-21 loss functions (nerf_device.cuh:74-112,640-655)
+    lt_t = rng.random((256, 3)).astype(f32)
+    lt_p = (rng.random((256, 3)) * 1.4 - 0.2).astype(f32)
+    for lt, tag in ((0, "l2"), (1, "huber")):
+        res = np.zeros((256, 6), f32)
+        for i in range(256):
+            t6 = (C.c_float * 6)(); ref.ref_loss_and_gradient(fa(*lt_t[i]), fa(*lt_p[i]), lt, t6); res[i] = t6[:]
+        out[f"loss_{tag}"] = res
+    out["loss_target"], out["loss_pred"] = lt_t, lt_p
     np.savez_compressed(os.path.join(HERE, "ref_host_env.npz"), **out)
     print("ref_host_env.npz:", len(out), "arrays")
 

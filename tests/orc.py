@@ -76,6 +76,8 @@ lib.orc_read_envmap.argtypes = [C.c_void_p, i32, i32, C.c_void_p, C.c_void_p]
 lib.orc_env_light_dirs.argtypes = [u32, u32, u32, C.c_void_p, C.c_void_p]
 lib.orc_nerf_transmittance.argtypes = [C.c_void_p] * 7
 lib.orc_nerf_transmittance.restype = f32
+lib.orc_train_gradients.argtypes = [C.c_void_p] * 4 + [u32] + [C.c_void_p] * 5 + [i32, f32, u32, C.c_void_p, C.c_void_p, C.c_void_p]
+lib.orc_train_gradients.restype = f32
 
 if ref is not None:
     for name in ("ref_ld_random_val", "ref_triangle_ray_intersect", "ref_advance_to_occupied", "ref_calc_dt", "ref_advance_n_steps",
@@ -229,6 +231,19 @@ def nerf_transmittance(p: RenderParams, cfg, params, bits, o, d):
     n = C.c_uint32(0)
     T = lib.orc_nerf_transmittance(C.byref(p), C.byref(cfg), P(params), P(bits), P(o), P(d), C.byref(n))
     return float(T), int(n.value)
+
+
+def train_gradients(p: RenderParams, cfg, params, bits, origins, dirs, t_start, targets, backgrounds, loss_type=1, loss_scale=128.0, max_samples=1 << 20):
+    """a-21 oracle: (mean loss, fp32 gradients [n_params] scaled by loss_scale, samples used per ray)"""
+    o = np.ascontiguousarray(origins, np.float32); d = np.ascontiguousarray(dirs, np.float32); t = np.ascontiguousarray(t_start, np.float32)
+    tg = np.ascontiguousarray(targets, np.float32); bg = np.ascontiguousarray(backgrounds, np.float32)
+    n = o.shape[0]
+    grads = np.zeros(int(lib.orc_n_params(C.byref(cfg))), np.float32)
+    steps = np.zeros(n, np.uint32)
+    total = u32(0)
+    loss = lib.orc_train_gradients(C.byref(p), C.byref(cfg), P(params), P(bits), n, P(o), P(d), P(t), P(tg), P(bg), int(loss_type), float(loss_scale),
+                                   int(max_samples), P(grads), P(steps), C.byref(total))
+    return float(loss), grads, steps
 
 
 def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):

@@ -1,0 +1,142 @@
+"""-m gpu: a-21 training step — loss and parameter gradients against the fp32 oracle (loss within 1e-2
+relative, gradient cosine >= 0.999), the data-parallel split of a batch, and a short optimisation run on a teacher scene."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def cosine(a, b):
+    a = a.astype(np.float64); b = b.astype(np.float64)
+    return float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-300))
+
+
+def make_rays(rng, n):
+    o = rng.normal(size=(n, 3)).astype(f32)
+    o = o / np.linalg.norm(o, axis=1, keepdims=True) * f32(1.2) + f32(0.5)
+    tgt = f32(0.5) + (rng.random((n, 3), dtype=f32) - f32(0.5)) * f32(0.6)
+    d = tgt - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    t0 = np.zeros(n, f32)
+    for i in range(n):
+        with np.errstate(divide="ignore"):
+            a = (0.0 - o[i]) / d[i]; b = (1.0 - o[i]) / d[i]
+        t0[i] = max(np.minimum(a, b).max(), 0.0) + 1e-4
+    return o, d, t0
+
+
+def nerf_setup(hn, root, blob_scale, config="nerf/base.json"):
+    tb = hn.Testbed()
+    tb.reload_network_from_file(os.path.join(root, "configs", *config.split("/")))
+    info = tb.network_info()
+    grid = hn.synthetic.sphere_density_grid(0.35)
+    params = hn.synthetic.random_params(info, 1337, blob_scale)
+    tb.set_params(params)
+    tb.set_density_grid(grid, 1)
+    tb.snap_to_pixel_centers = True
+    return tb, params, grid
+
+
+@pytest.mark.parametrize("loss_type,config", [(1, "nerf/base.json"), (0, "nerf/base.json"), (1, "geometry/base.json")])
+def test_gradients_match_oracle(hn, orc, root, loss_type, config):
+    tb, params, grid = nerf_setup(hn, root, 0.5, config)
+    rng = np.random.default_rng(5)
+    n = 96
+    o, d, t0 = make_rays(rng, n)
+    targets = rng.random((n, 3), dtype=f32)
+    bgs = rng.random((n, 3), dtype=f32)
+    loss, grads, steps = tb.op_train_gradients(o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=128.0)
+    info = tb.network_info()
+    cfg = orc.net_config_from_info(info)
+    bits = orc.bitfield_from_grid(grid, 1)[0]
+    p = orc.render_params(8, 8, hn.synthetic.default_camera())
+    wl, wg, ws = orc.train_gradients(p, cfg, params, bits, o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=128.0)
+    assert ws.sum() > 5000
+    assert np.mean(steps == ws) >= 0.97            # the T < 1e-4 early stop can flip by a sample
+    assert abs(loss - wl) <= 1e-2 * abs(wl)
+    n_mlp = int(info.grid_param_offset)
+    n_density = n_mlp - (64 * 32 + (info.rgb_hidden_layers - 1) * 64 * 64 + 16 * 64)
+    assert cosine(grads[:n_density], wg[:n_density]) >= 0.999
+    assert cosine(grads[n_density:n_mlp], wg[n_density:n_mlp]) >= 0.999
+    assert cosine(grads[n_mlp:], wg[n_mlp:]) >= 0.999
+    # magnitudes agree too, and untouched table entries stay exactly zero on both sides
+    assert abs(np.linalg.norm(grads) / np.linalg.norm(wg) - 1.0) <= 2e-2
+    assert np.all(grads[n_mlp:][wg[n_mlp:] == 0] == 0)   # (fp16 gradient underflow may zero a few more on the GPU side)
+    assert np.mean((grads[n_mlp:] == 0) == (wg[n_mlp:] == 0)) > 0.999
+
+
+def teacher_dataset(hn, root, n_views=12, res=64):
+    teacher, params, grid = nerf_setup(hn, root, 1.0)
+    rng = np.random.default_rng(9)
+    cams, imgs = [], []
+    for i in range(n_views):
+        eye = rng.normal(size=3)
+        eye = eye / np.linalg.norm(eye) * 1.6 + 0.5
+        cam = hn.synthetic.look_at_camera(tuple(eye), (0.5, 0.5, 0.5))
+        teacher.set_camera_cols(cam)
+        imgs.append(teacher.render(res, res, 1, True).copy())
+        cams.append(np.asarray(cam, f32).reshape(12))
+    focal = float(teacher.get_option("relative_focal_length", 2)[1]) * res
+    return np.stack(imgs), np.stack(cams), focal, grid
+
+
+def test_training_reduces_loss_and_improves_psnr(hn, root):
+    imgs, cams, focal = hn.synthetic.sphere_dataset(16, 64)
+    tb, _, _ = nerf_setup(hn, root, 1e-4)
+    tb.set_training_data(imgs, cams, focal)
+    tb.reset_trainer(7)
+    target0 = imgs[0][..., :3] * imgs[0][..., 3:4]    # over the render's black background
+
+    def psnr_view0():
+        tb.set_camera_cols(cams[0])
+        img = tb.render(64, 64, 1, True)
+        mse = float(np.mean((img[..., :3] - target0) ** 2))
+        return 10 * np.log10(1.0 / max(mse, 1e-12))
+
+    before = psnr_view0()
+    first = tb.train(1)
+    losses = [tb.train(1) for _ in range(120)]
+    after = psnr_view0()
+    st = tb.train_stats()
+    assert st.step == 121 and st.n_samples_last > 50000 and st.rays_per_batch % 128 == 0
+    assert np.isfinite(losses).all()
+    assert np.mean(losses[-10:]) < 0.5 * first, (first, losses[-10:])
+    assert after > before + 3.0, (before, after)
+    # the snapshot writer sees the trained parameters
+    path = "/tmp/hn_trained.ingp"
+    tb.save_snapshot(path)
+    tb2 = hn.Testbed()
+    tb2.load_snapshot(path)
+    tb2.snap_to_pixel_centers = True
+    tb2.set_camera_cols(cams[0]); tb.set_camera_cols(cams[0])
+    assert np.abs(tb2.render(64, 64, 1, True) - tb.render(64, 64, 1, True)).max() <= 1e-6
+
+
+def test_data_parallel_split_sums_to_the_full_batch(hn, root):
+    """Two ranks draw disjoint halves of the same ray stream; their gradient buffers sum to the one-rank gradient of the
+    whole batch (what the NCCL all-reduce in bench.py --workload config5 relies on)."""
+    import ctypes as C
+    imgs, cams, focal, grid = teacher_dataset(hn, root, n_views=6, res=48)
+
+    def grads_of(rank, world, n_rays):
+        tb, _, _ = nerf_setup(hn, root, 0.3)
+        tb.set_training_data(imgs, cams, focal)
+        tb.set_tile_shard(rank, world)
+        tb.reset_trainer(11)
+        loss = tb.train_accumulate(n_rays)
+        ptr, n = tb.train_gradient_buffer()
+        out = np.empty(n, f32)
+        rc = hn.testbed.cudart_memcpy_d2h(out, ptr)
+        assert rc == 0
+        return loss, out
+
+    l0, g0 = grads_of(0, 2, 1024)
+    l1, g1 = grads_of(1, 2, 1024)
+    lf, gf = grads_of(0, 1, 2048)
+    assert abs((l0 + l1) - lf) <= 1e-4 * abs(lf) + 1e-7
+    assert cosine(g0 + g1, gf) >= 0.99999
+    assert np.abs((g0 + g1) - gf).max() <= 1e-3 * np.abs(gf).max()
+    assert cosine(g0, g1) < 0.999   # the halves really are different rays

@@ -1,0 +1,106 @@
+"""CPU (-m "not gpu"): the a-21 training oracle (oracle/orc_train.inc) checks itself — its analytic gradients against central
+finite differences of its own loss, and the loss functions against the reference's host-callable ones when oracle/_ref is built."""
+import ctypes as C
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+f32 = np.float32
+
+
+@pytest.fixture(scope="module")
+def synthetic():
+    root = os.path.dirname(HERE)
+    spec = importlib.util.spec_from_file_location("hn_synthetic", os.path.join(root, "surface-irradiance-estimation-from-neural-radiance-fields_b200", "synthetic.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def make_rays(rng, n):
+    o = rng.normal(size=(n, 3)).astype(f32)
+    o = o / np.linalg.norm(o, axis=1, keepdims=True) * f32(1.2) + f32(0.5)
+    tgt = f32(0.5) + (rng.random((n, 3), dtype=f32) - f32(0.5)) * f32(0.5)
+    d = tgt - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    # start t = entry into the unit cube
+    t0 = np.zeros(n, f32)
+    for i in range(n):
+        with np.errstate(divide="ignore"):
+            a = (0.0 - o[i]) / d[i]; b = (1.0 - o[i]) / d[i]
+        t0[i] = max(np.minimum(a, b).max(), 0.0) + 1e-4
+    return o, d, t0
+
+
+def setup(orc, synthetic, scale=0.5):
+    cfg = orc.net_config(8, 4, 19, 16, 2.0, 1, 2)
+
+    class Info:
+        n_levels, n_features_per_level, density_hidden_layers, rgb_hidden_layers = 8, 4, 1, 2
+        n_params = orc.lib.orc_n_params(C.byref(cfg))
+        grid_param_offset = orc.lib.orc_grid_param_offset(C.byref(cfg))
+
+    params = synthetic.random_params(Info, 1337, scale)
+    bits, _ = orc.bitfield_from_grid(synthetic.sphere_density_grid(0.35), 1)
+    p = orc.render_params(8, 8, synthetic.default_camera())
+    return cfg, Info, params, bits, p
+
+
+@pytest.mark.parametrize("loss_type", [0, 1])
+def test_oracle_gradients_match_finite_differences(orc, synthetic, loss_type):
+    cfg, info, params, bits, p = setup(orc, synthetic)
+    rng = np.random.default_rng(3)
+    o, d, t0 = make_rays(rng, 6)
+    targets = rng.random((6, 3), dtype=f32)
+    bgs = rng.random((6, 3), dtype=f32)
+    loss, grads, steps = orc.train_gradients(p, cfg, params, bits, o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=1.0)
+    assert steps.sum() > 300 and np.isfinite(loss) and loss > 0
+    n_mlp = int(info.grid_param_offset)
+    # parameters with the largest gradients in each region: density MLP, rgb MLP, coarse and fine grid levels
+    picks = []
+    picks += list(np.argsort(-np.abs(grads[:3072]))[:3])
+    picks += list(3072 + np.argsort(-np.abs(grads[3072:n_mlp]))[:3])
+    g = grads[n_mlp:]
+    picks += list(n_mlp + np.argsort(-np.abs(g))[:4])
+    fine = n_mlp + 4 * (4096 + 32768 + 262144 + 524288 * 3)          # inside level 6
+    picks += list(fine + np.argsort(-np.abs(grads[fine:fine + 4 * 524288]))[:2])
+    for idx in picks:
+        w = params.copy()
+        base = np.float32(w[idx])
+        delta = max(abs(float(base)) * 2 ** -5, 2 ** -9)
+        hi, lo = np.float16(base + delta), np.float16(base - delta)
+        w[idx] = hi
+        lp = orc.train_gradients(p, cfg, w, bits, o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=1.0)[0]
+        w[idx] = lo
+        lm = orc.train_gradients(p, cfg, w, bits, o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=1.0)[0]
+        fd = (lp - lm) / (float(hi) - float(lo))
+        # the oracle's "loss" is mean over channels (/3), its gradients follow the reference's convention (sum over channels of dL/drgb): factor 3
+        an = float(grads[idx]) / 3.0
+        assert abs(fd - an) <= 0.05 * max(abs(an), abs(fd)) + 2e-6, (idx, fd, an)
+
+
+def test_loss_functions_pinned_against_reference_host(orc):
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_loss_and_gradient"):
+        pytest.skip("oracle/_ref not built here (authoring container only); vectors in tests/golden/ref_host_env.npz cover the CPU suite")
+    rng = np.random.default_rng(1)
+    for _ in range(200):
+        t, pr = rng.random(3, dtype=f32), (rng.random(3, dtype=f32) * 1.4 - 0.2).astype(f32)
+        for lt in (0, 1):
+            out = np.zeros(6, f32)
+            ref.ref_loss_and_gradient(orc.P(t), orc.P(pr), lt, orc.P(out))
+            got = np.zeros(6, f32)
+            orc.lib.orc_loss_and_gradient(orc.P(t), orc.P(pr), lt, orc.P(got))
+            assert np.array_equal(out.view(np.uint32), got.view(np.uint32))
+
+
+def test_loss_functions_pinned_against_golden(orc):
+    g = np.load(os.path.join(HERE, "golden", "ref_host_env.npz"))
+    for lt, tag in ((0, "l2"), (1, "huber")):
+        for i in range(g["loss_target"].shape[0]):
+            got = np.zeros(6, f32)
+            orc.lib.orc_loss_and_gradient(orc.P(g["loss_target"][i].copy()), orc.P(g["loss_pred"][i].copy()), lt, orc.P(got))
+            assert np.array_equal(got.view(np.uint32), g[f"loss_{tag}"][i].view(np.uint32))

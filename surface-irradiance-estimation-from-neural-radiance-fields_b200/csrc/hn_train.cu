@@ -382,6 +382,15 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	if (!n) return;
 	cublasHandle_t h = handle(ctx);
 	const __half* W = t.raw.p;
+	// The GEMMs run on the sample count rounded up to 32 Ki rows (zero rows: no bias anywhere, so they stay zero through both
+	// passes and add nothing to the weight gradients): the count changes every step, and a new GEMM shape costs cuBLAS a
+	// heuristics search of ~2 ms per call on the host (measured: 26 ms per step for the 13 backward GEMMs).
+	const uint32_t n_gemm = std::min<uint32_t>((n + 32767u) / 32768u * 32768u, (uint32_t)(t.act[0].n / 64));
+	if (n_gemm > n) {
+		HN_CUDA(cudaMemsetAsync(t.act[0].p + (size_t)n * 32, 0, (size_t)(n_gemm - n) * 32 * sizeof(__half), s));
+		HN_CUDA(cudaMemsetAsync(t.act[Hd + 2].p + (size_t)n * 32, 0, (size_t)(n_gemm - n) * 32 * sizeof(__half), s));
+		HN_CUDA(cudaMemsetAsync(t.dact[0].p + (size_t)n * 16, 0, (size_t)(n_gemm - n) * 16 * sizeof(__half), s));
+	}
 	__half* enc = t.act[0].p; __half* d_out = t.act[Hd + 1].p; __half* rgb_in = t.act[Hd + 2].p; __half* out = t.act[Hd + 3 + Hr].p;
 	// ---- forward
 	ev.start();
@@ -390,11 +399,11 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	auto mlp_forward = [&](const __half* w, uint32_t first_act, uint32_t hidden) {
 		int K = 32;
 		for (uint32_t l = 0; l < hidden; ++l) {
-			gemm_forward(h, n, 64, K, t.act[first_act + l].p, w, t.act[first_act + l + 1].p);
+			gemm_forward(h, n_gemm, 64, K, t.act[first_act + l].p, w, t.act[first_act + l + 1].p);
 			relu_kernel<<<blocks((size_t)n * 32), 256, 0, s>>>((__half2*)t.act[first_act + l + 1].p, (size_t)n * 32);
 			w += 64 * K; K = 64;
 		}
-		gemm_forward(h, n, 16, 64, t.act[first_act + hidden].p, w, t.act[first_act + hidden + 1].p);
+		gemm_forward(h, n_gemm, 16, 64, t.act[first_act + hidden].p, w, t.act[first_act + hidden + 1].p);
 	};
 	mlp_forward(W + net.density_w_offset, 0, Hd);
 	copy_density_out_kernel<<<blocks(n), 256, 0, s>>>(d_out, rgb_in, n);
@@ -422,9 +431,9 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 		for (int l = (int)hidden; l >= 0; --l) {
 			const int Kin = l == 0 ? 32 : 64;
 			const __half* x = t.act[first_act + l].p;
-			gemm_backward_weights(h, n, N, Kin, g, x, gw + off[l]);
+			gemm_backward_weights(h, n_gemm, N, Kin, g, x, gw + off[l]);
 			__half* gx = t.dact[cur].p;
-			gemm_backward_input(h, n, N, Kin, g, w + off[l], gx);
+			gemm_backward_input(h, n_gemm, N, Kin, g, w + off[l], gx);
 			if (l > 0) relu_backward_kernel<<<blocks((size_t)n * 32), 256, 0, s>>>((__half2*)gx, (const __half2*)x, (size_t)n * 32);
 			g = gx; N = 64;
 			cur = (cur == buf_a) ? buf_b : buf_a;

@@ -60,3 +60,14 @@ def unpack_tiles_host(packed: np.ndarray, frame: np.ndarray, depth: np.ndarray, 
         x1, y1 = min(x0 + tile_w, w), min(y0 + tile_h, h)
         frame[y0:y1, x0:x1] = p[k, : y1 - y0, : x1 - x0, :4]
         depth[y0:y1, x0:x1] = p[k, : y1 - y0, : x1 - x0, 4]
+
+
+# ---- data-parallel training (SURVEY §8e "Training"): the ray stream of one step is cut into `world` consecutive blocks ----
+def train_ray_shard(n_rays_per_rank: int, rank: int, world: int, n_images: int) -> tuple[np.ndarray, np.ndarray]:
+    """Global ray indices of this rank's block and the image each ray samples — the rule of train_raygen_kernel
+    (csrc/hn_train.cu): global ray g = rank * n + i, image = (g * n_images) // (n * world) % n_images. The loss of every ray is
+    normalised by the GLOBAL ray count, so the SUM all-reduce of the per-rank gradient buffers is the gradient of the whole
+    batch and hn_train_apply takes grad_scale = 1."""
+    g = rank * n_rays_per_rank + np.arange(n_rays_per_rank, dtype=np.int64)
+    img = (g * n_images) // (n_rays_per_rank * world) % n_images
+    return g, img.astype(np.int64)

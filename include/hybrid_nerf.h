@@ -105,6 +105,14 @@ int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats);
 int hn_train_apply(hn_context* ctx, float grad_scale);
 /* n_steps x (accumulate + apply) on one GPU; loss_out = mean loss of the last step (Testbed::train + m_loss_scalar). */
 int hn_train_step(hn_context* ctx, uint32_t n_steps, float* loss_out);
+/* Occupancy-grid maintenance from the live network (Testbed::update_density_grid_nerf, src/testbed_nerf.cu:2772-2861; called by
+ * training_prep_nerf :3433-3446, which hn_train_accumulate does on the reference's schedule unless option "train_auto_grid" = 0):
+ * n_uniform samples over all cells + n_nonuniform among occupied cells, density network, max-splat, grid = max(grid * decay, new),
+ * then mean -> threshold -> bitfield + mips (update_density_grid_mean_and_bitfield :2863-2880). */
+int hn_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+/* mark_untrained_density_grid (:74-145): cells no training camera sees become -1 (never occupied), the rest 0. */
+int hn_mark_untrained_density_grid(hn_context* ctx);
+int hn_get_density_grid(hn_context* ctx, float* out_host, size_t n_floats);     /* float[128^3 * (max_cascade+1)], Morton order */
 typedef struct {
 	uint32_t step, rays_per_batch, n_rays_last, n_samples_last;
 	float loss_last, learning_rate;

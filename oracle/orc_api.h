@@ -111,6 +111,12 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, int32_t loss_type, float loss_scale,
 	uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total);
 
+// ---- occupancy-grid maintenance from the live network (orc_grid.inc) ----
+void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]);
+void orc_update_density_grid(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, float* grid, uint32_t n_cascades, uint32_t ema_step,
+	uint32_t n_uniform, uint32_t n_nonuniform, float decay, uint32_t seed, uint32_t rng_calls);
+uint32_t orc_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out);
+
 // ---- meshes (a-17..a-19) ----
 typedef struct orc_scene orc_scene;
 orc_scene* orc_scene_create(void);

@@ -657,6 +657,7 @@ float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8
 }
 
 #include "orc_train.inc"
+#include "orc_grid.inc"
 
 Net* net_new(const orc_net_config& c, const uint16_t* params) { return new Net(make_net(c, params)); }
 void net_delete(Net* n) { delete n; }
@@ -713,6 +714,20 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 	uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total) {
 	Net net = make_net(*c, params);
 	return train_gradients(*p, net, bitfield, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, max_samples, grads, n_steps_out, n_samples_total);
+}
+
+void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]) {
+	mark_untrained_grid(grid, n_cascades, n_images, cams, w, h, focal, principal);
+}
+void orc_update_density_grid(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, float* grid, uint32_t n_cascades, uint32_t ema_step,
+	uint32_t n_uniform, uint32_t n_nonuniform, float decay, uint32_t seed, uint32_t rng_calls) {
+	Net net = make_net(*c, params);
+	update_density_grid(*p, net, grid, n_cascades, ema_step, n_uniform, n_nonuniform, decay, seed, rng_calls);
+}
+uint32_t orc_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out) {
+	Pcg32 r(seed); r.advance(advance);
+	for (uint32_t i = 0; i < n; ++i) out[i] = r.next_uint();
+	return n;
 }
 
 float orc_bitfield_from_grid(const float* grid, uint32_t n_cascades, uint8_t* out) { return bitfield_from_grid(grid, n_cascades, out); }

@@ -99,4 +99,12 @@ void ref_loss_and_gradient(const float target[3], const float pred[3], int32_t l
 	out[0] = lg.loss.x; out[1] = lg.loss.y; out[2] = lg.loss.z; out[3] = lg.gradient.x; out[4] = lg.gradient.y; out[5] = lg.gradient.z;
 }
 
+// pcg32 (tcnn/dependencies/pcg32): seed, skip-ahead, raw 32-bit outputs
+uint32_t ref_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out) {
+	tcnn::pcg32 r{seed};
+	r.advance((int64_t)advance);
+	for (uint32_t i = 0; i < n; ++i) out[i] = r.next_uint();
+	return n;
+}
+
 }

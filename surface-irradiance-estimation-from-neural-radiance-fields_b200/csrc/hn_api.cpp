@@ -128,11 +128,17 @@ void upload_density_grid(hn_context* ctx, const float* grid, uint32_t n_cascades
 	need(n_cascades >= 1 && n_cascades <= CASCADES, "n_cascades must be in [1,8]");
 	ctx->density_grid_host.assign(grid, grid + (size_t)GRID_CELLS * n_cascades);
 	HN_CUDA(cudaSetDevice(ctx->device));
-	DevBuf<float> d_grid;
-	d_grid.ensure((size_t)GRID_CELLS * n_cascades);
+	ctx->density_grid.ensure((size_t)GRID_CELLS * n_cascades);
+	ctx->grid_cascades = n_cascades;
+	HN_CUDA(cudaMemcpyAsync(ctx->density_grid.p, grid, (size_t)GRID_CELLS * n_cascades * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	refresh_bitfield_from_device_grid(ctx);
+}
+void refresh_bitfield_from_device_grid(hn_context* ctx) {
+	const uint32_t n_cascades = ctx->grid_cascades;
+	float* d_grid_p = ctx->density_grid.p;
+	struct { float* p; } d_grid = {d_grid_p};
 	DevBuf<double> d_sum;
 	d_sum.ensure(1);
-	HN_CUDA(cudaMemcpyAsync(d_grid.p, grid, (size_t)GRID_CELLS * n_cascades * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	launch_grid_mean(d_grid.p, (float*)d_sum.p, ctx->stream);
 	double sum = 0.0;
 	HN_CUDA(cudaMemcpyAsync(&sum, d_sum.p, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -191,6 +197,8 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"exposure", {&o.exposure, 1, false}}, {"background_color", {o.background_color, 4, false}},
 		{"relative_focal_length", {o.relative_focal_length, 2, false}}, {"screen_center", {o.screen_center, 2, false}}, {"zoom", {&o.zoom, 1, false}},
 		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
+		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
+		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
 		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
 	};
 }
@@ -517,6 +525,19 @@ int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out) {
 	out->loss_last = t.loss_last; out->learning_rate = t.lr_last;
 	out->ms_sample = t.ms[0]; out->ms_forward = t.ms[1]; out->ms_loss = t.ms[2]; out->ms_backward = t.ms[3]; out->ms_optimizer = t.ms[4];
 	return 0;
+}
+int hn_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_update_density_grid(ctx, decay, n_uniform, n_nonuniform); HN_CATCH(ctx)
+}
+int hn_mark_untrained_density_grid(hn_context* ctx) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_mark_untrained(ctx); refresh_bitfield_from_device_grid(ctx); HN_CATCH(ctx)
+}
+int hn_get_density_grid(hn_context* ctx, float* out, size_t n_floats) {
+	HN_TRY(ctx)
+	need(ctx->density_grid.p && n_floats == (size_t)GRID_CELLS * ctx->grid_cascades, "no density grid / wrong size");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaMemcpy(out, ctx->density_grid.p, n_floats * sizeof(float), cudaMemcpyDeviceToHost));
+	HN_CATCH(ctx)
 }
 int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
 	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps) {

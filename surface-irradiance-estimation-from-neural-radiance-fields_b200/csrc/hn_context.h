@@ -86,6 +86,8 @@ struct TrainCfg {
 	float loss_scale = 128.0f;              // LOSS_SCALE(), common.h:232
 	uint32_t target_batch = 1u << 18;       // samples per batch (src/testbed_nerf.cu:2943)
 	int random_bg = 1;                      // nerf.training.random_bg_color
+	int auto_grid = 1;                      // refresh the occupancy grid from the network on the reference's schedule (training_prep_nerf)
+	float grid_decay = 0.95f;               // nerf.training.density_grid_decay (nerf.h:120)
 };
 struct TrainState {
 	bool ready = false, has_dataset = false;
@@ -107,6 +109,9 @@ struct TrainState {
 	DevBuf<__half> act[12];                 // activations: enc, density hidden..., density out, rgb in, rgb hidden..., out
 	DevBuf<__half> dact[4];                 // gradient ping-pong buffers
 	DevBuf<float> loss_acc;
+	// occupancy-grid maintenance (update_density_grid_nerf)
+	DevBuf<float> grid_tmp; DevBuf<float4> grid_pos; DevBuf<uint32_t> grid_idx; DevBuf<uint2> grid_out;
+	uint32_t grid_seed = 1337, grid_rng_calls = 0, grid_ema_step = 0;
 	void* cublas = nullptr;
 };
 
@@ -131,6 +136,8 @@ struct hn_context {
 	// occupancy
 	hn::DevBuf<uint8_t> bitfield;
 	bool has_bitfield = false;
+	hn::DevBuf<float> density_grid;         // device copy of the float grid [128^3 x grid_cascades] (Morton order), kept for the live updates
+	uint32_t grid_cascades = 0;
 	int occ_cells[hn::CASCADES * 6] = {};   // per-mip bounds of the set cells (cell coordinates), refreshed with the bitfield
 
 	// scene
@@ -205,6 +212,9 @@ void train_apply(hn_context* ctx, float grad_scale);
 void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* t, const float* targets, const float* bgs,
 	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
 void train_release(hn_context* ctx);
+void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+void train_mark_untrained(hn_context* ctx);
+void refresh_bitfield_from_device_grid(hn_context* ctx); // hn_api.cpp: mean -> threshold -> bitfield + mips -> occupancy bounds
 // hn_scene.cpp
 void add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], bool normalize);
 void load_mesh_file(hn_context* ctx, const std::string& path, const float center[3]);

@@ -392,6 +392,10 @@ void save_snapshot_file(hn_context* ctx, const std::string& path) {
 	snap.set("density_grid_size") = jnum(GRIDSIZE);
 	Json gb; gb.type = Json::Binary;
 	{
+		if (ctx->density_grid_host.empty() && ctx->density_grid.p && ctx->grid_cascades) { // refreshed on the device by training
+			ctx->density_grid_host.resize((size_t)GRID_CELLS * ctx->grid_cascades);
+			HN_CUDA(cudaMemcpy(ctx->density_grid_host.data(), ctx->density_grid.p, ctx->density_grid_host.size() * sizeof(float), cudaMemcpyDeviceToHost));
+		}
 		std::vector<__half> h(ctx->density_grid_host.size());
 		for (size_t i = 0; i < h.size(); ++i) h[i] = __float2half_rn(ctx->density_grid_host[i]);
 		gb.str.assign((const char*)h.data(), h.size() * sizeof(__half));

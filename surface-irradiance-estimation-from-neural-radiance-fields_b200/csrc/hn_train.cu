@@ -309,6 +309,76 @@ __global__ void half_to_float_kernel(const __half* __restrict__ in, float* __res
 	if (i < n) out[i] = __half2float(in[i]);
 }
 
+// ---------------------------------------------------------------- occupancy grid from the live network
+__device__ __forceinline__ uint32_t morton_invert(uint32_t x) {
+	x = x & 0x49249249u;
+	x = (x | (x >> 2)) & 0xc30c30c3u;
+	x = (x | (x >> 4)) & 0x0f00f00fu;
+	x = (x | (x >> 8)) & 0xff0000ffu;
+	x = (x | (x >> 16)) & 0x0000ffffu;
+	return x;
+}
+// generate_grid_samples_nerf_nonuniform (src/testbed_nerf.cu:185-217): sample i -> (cascade, cell, jittered position)
+__global__ void grid_samples_kernel(uint32_t n, Pcg32 rng, uint32_t step, const float* __restrict__ grid_in, float4* __restrict__ out, uint32_t* __restrict__ indices,
+	uint32_t n_cascades, float thresh) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	rng.advance((uint64_t)i * 4);
+	const uint32_t level = (uint32_t)(rng.next_float() * n_cascades) % n_cascades;
+	uint32_t idx = 0;
+	for (uint32_t j = 0; j < 10; ++j) {
+		idx = ((i + step * n) * 56924617u + j * 19349663u + 96925573u) % GRID_CELLS;
+		idx += level * GRID_CELLS;
+		if (grid_in[idx] > thresh) break;
+	}
+	const uint32_t pos_idx = idx % GRID_CELLS;
+	const float x = (float)morton_invert(pos_idx), y = (float)morton_invert(pos_idx >> 1), z = (float)morton_invert(pos_idx >> 2);
+	const float r0 = rng.next_float(), r1 = rng.next_float(), r2 = rng.next_float();
+	const float sc = scalbnf(1.0f, (int)level);
+	out[i] = make_float4(__fadd_rn(__fmul_rn(__fsub_rn(__fdiv_rn(__fadd_rn(x, r0), 128.0f), 0.5f), sc), 0.5f),
+		__fadd_rn(__fmul_rn(__fsub_rn(__fdiv_rn(__fadd_rn(y, r1), 128.0f), 0.5f), sc), 0.5f),
+		__fadd_rn(__fmul_rn(__fsub_rn(__fdiv_rn(__fadd_rn(z, r2), 128.0f), 0.5f), sc), 0.5f), HN_MIN_STEP);
+	indices[i] = idx;
+}
+// splat_grid_samples_nerf_max_nearest_neighbor (:219-236): optical thickness of the smallest step, atomicMax on the bit pattern
+__global__ void grid_splat_kernel(uint32_t n, const uint32_t* __restrict__ indices, const uint2* __restrict__ net_out, int density_act, float* __restrict__ tmp) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const __half2 bs = *reinterpret_cast<const __half2*>(&net_out[i].y);
+	const float thickness = act_density(__high2float(bs), density_act) * HN_MIN_STEP;
+	atomicMax(reinterpret_cast<uint32_t*>(tmp) + indices[i], __float_as_uint(thickness));
+}
+// ema_grid_samples_nerf (:258-282): maximum instead of a mean, so thin features switch a cell on at once
+__global__ void grid_ema_kernel(uint32_t n, float decay, float* __restrict__ grid, const float* __restrict__ tmp) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float prev = grid[i];
+	grid[i] = prev < 0.f ? prev : fmaxf(prev * decay, tmp[i]);
+}
+// mark_untrained_density_grid (:74-145), pinhole cameras: a cell no training view sees can never be trained -> -1
+__global__ void mark_untrained_kernel(uint32_t n_elements, float* __restrict__ grid, TrainDataDev D) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_elements) return;
+	const uint32_t level = i / GRID_CELLS, pos_idx = i % GRID_CELLS;
+	const float voxel = scalbnf(1.0f / 128.0f, (int)level), sc = scalbnf(1.0f, (int)level);
+	const float px = ((float)morton_invert(pos_idx) / 128.0f - 0.5f) * sc + 0.5f, py = ((float)morton_invert(pos_idx >> 1) / 128.0f - 0.5f) * sc + 0.5f,
+		pz = ((float)morton_invert(pos_idx >> 2) / 128.0f - 0.5f) * sc + 0.5f;
+	bool seen = false;
+	for (uint32_t j = 0; j < D.n_images && !seen; ++j) {
+		const float* c = D.cams + 12 * j;
+		for (uint32_t k = 0; k < 8 && !seen; ++k) {
+			const float rx = px + ((k & 1) ? voxel : 0.f) - c[9], ry = py + ((k & 2) ? voxel : 0.f) - c[10], rz = pz + ((k & 4) ? voxel : 0.f) - c[11];
+			const float len = sqrtf(rx * rx + ry * ry + rz * rz);
+			const float cz = rx * c[6] + ry * c[7] + rz * c[8];
+			if (cz / len < 1e-4f) continue;
+			const float cx = rx * c[0] + ry * c[1] + rz * c[2], cy = rx * c[3] + ry * c[4] + rz * c[5];
+			const float u = cx / cz * D.focal[0] / (float)D.w + D.principal[0], v = cy / cz * D.focal[1] / (float)D.h + D.principal[1];
+			if (u > 0.f && v > 0.f && u < 1.f && v < 1.f) seen = true;
+		}
+	}
+	grid[i] = seen ? 0.f : -1.f;
+}
+
 FrameArgs train_frame_args(hn_context* ctx); // hn_api.cpp: aabbs, occupancy bounds, cone angle, activations
 
 namespace {
@@ -489,6 +559,19 @@ void train_init(hn_context* ctx, uint32_t seed) {
 }
 
 void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
+	if (ctx->train_cfg.auto_grid && ctx->train.has_dataset && ctx->has_net && ctx->has_params) {
+		// Testbed::train (src/testbed.cu:4418-4440): training_prep_nerf every min(max(step / 16, 1), 16) steps; all cells for the
+		// first 256 steps, then a quarter uniformly and a quarter among the occupied cells (:3433-3446)
+		if (!ctx->train.ready) train_init(ctx, ctx->train.seed);
+		TrainState& tt = ctx->train;
+		const uint32_t skip = std::min(std::max(tt.step / 16u, 1u), 16u);
+		if (tt.step % skip == 0) {
+			const uint32_t nc = (uint32_t)ctx->opt.max_cascade + 1u;
+			if (tt.step == 0) train_mark_untrained(ctx);
+			if (tt.step < 256) train_update_density_grid(ctx, ctx->train_cfg.grid_decay, GRID_CELLS * nc, 0);
+			else train_update_density_grid(ctx, ctx->train_cfg.grid_decay, GRID_CELLS / 4 * nc, GRID_CELLS / 4 * nc);
+		}
+	}
 	check_ready(ctx, true);
 	TrainState& t = ctx->train;
 	const TrainCfg& c = ctx->train_cfg;
@@ -559,6 +642,56 @@ void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const 
 	if (grads_host) HN_CUDA(cudaMemcpyAsync(grads_host, t.grads.p, ctx->net.n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
 	if (n_steps) HN_CUDA(cudaMemcpyAsync(n_steps, used.p, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, s));
 	HN_CUDA(cudaStreamSynchronize(s));
+}
+
+// Testbed::update_density_grid_nerf (src/testbed_nerf.cu:2772-2861) + update_density_grid_mean_and_bitfield (:2863-2880)
+void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform) {
+	if (!ctx->has_net || !ctx->has_params) throw std::runtime_error("density-grid update needs a network config and parameters");
+	TrainState& t = ctx->train;
+	cudaStream_t s = ctx->stream;
+	const uint32_t n_cascades = (uint32_t)ctx->opt.max_cascade + 1u;
+	const uint32_t n_elements = GRID_CELLS * n_cascades;
+	if (ctx->density_grid.n < n_elements || ctx->grid_cascades != n_cascades) { // no grid yet (or another cascade count): start from "nothing known"
+		ctx->density_grid.ensure(n_elements);
+		HN_CUDA(cudaMemsetAsync(ctx->density_grid.p, 0, (size_t)n_elements * sizeof(float), s));
+		ctx->grid_cascades = n_cascades;
+	}
+	const uint32_t n = n_uniform + n_nonuniform;
+	if (!n) return;
+	const uint32_t chunks = (n + CHUNK - 1) / CHUNK;
+	t.grid_tmp.ensure(n_elements); t.grid_pos.ensure((size_t)chunks * CHUNK); t.grid_idx.ensure(n); t.grid_out.ensure((size_t)chunks * CHUNK);
+	HN_CUDA(cudaMemsetAsync(t.grid_tmp.p, 0, (size_t)n_elements * sizeof(float), s));
+	HN_CUDA(cudaMemsetAsync(t.grid_pos.p, 0, (size_t)chunks * CHUNK * sizeof(float4), s)); // padding samples sit at the box corner
+	for (int pass = 0; pass < 2; ++pass) {
+		const uint32_t cnt = pass == 0 ? n_uniform : n_nonuniform, off = pass == 0 ? 0u : n_uniform;
+		Pcg32 rng(t.grid_seed);
+		for (uint32_t k = 0; k < t.grid_rng_calls; ++k) rng.advance(1ull << 32);
+		++t.grid_rng_calls; // density_grid_rng.advance() after every generate call, used or not (:2826,2839)
+		if (cnt) grid_samples_kernel<<<blocks(cnt), 256, 0, s>>>(cnt, rng, t.grid_ema_step, ctx->density_grid.p, t.grid_pos.p + off, t.grid_idx.p + off, n_cascades,
+			pass == 0 ? -0.01f : 0.01f);
+	}
+	FrameArgs a = train_frame_args(ctx);
+	RaySoA none = {};
+	const __half* weights = t.ready ? t.raw.p : ctx->params.p; // density(..., use_inference_params = false): the raw training weights
+	launch_eval(ctx->net, ctx->levels, weights, a, t.grid_pos.p, nullptr, nullptr, none, nullptr, nullptr, chunks, t.grid_out.p, 1, nullptr, nullptr, nullptr, nullptr, s, true);
+	grid_splat_kernel<<<blocks(n), 256, 0, s>>>(n, t.grid_idx.p, t.grid_out.p, a.density_act, t.grid_tmp.p);
+	grid_ema_kernel<<<blocks(n_elements), 256, 0, s>>>(n_elements, decay, ctx->density_grid.p, t.grid_tmp.p);
+	++t.grid_ema_step;
+	HN_CUDA(cudaGetLastError());
+	ctx->density_grid_host.clear(); // stale; the snapshot writer reads the device grid back
+	refresh_bitfield_from_device_grid(ctx);
+}
+
+void train_mark_untrained(hn_context* ctx) {
+	TrainState& t = ctx->train;
+	if (!t.has_dataset) throw std::runtime_error("no training dataset (hn_train_set_dataset)");
+	const uint32_t n_cascades = (uint32_t)ctx->opt.max_cascade + 1u, n_elements = GRID_CELLS * n_cascades;
+	ctx->density_grid.ensure(n_elements);
+	ctx->grid_cascades = n_cascades;
+	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
+	mark_untrained_kernel<<<blocks(n_elements), 256, 0, ctx->stream>>>(n_elements, ctx->density_grid.p, D);
+	t.grid_ema_step = 0;
+	HN_CUDA(cudaGetLastError());
 }
 
 void train_release(hn_context* ctx) {

@@ -67,7 +67,8 @@ EXPORTS = [
     "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
-    "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients",
+    "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
+    "hn_get_density_grid",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -112,6 +113,9 @@ _lib.hn_train_apply.argtypes = [C.c_void_p, C.c_float]
 _lib.hn_train_step.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_float)]
 _lib.hn_get_train_stats.argtypes = [C.c_void_p, C.POINTER(TrainStats)]
 _lib.hn_op_train_gradients.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.POINTER(C.c_float), C.c_void_p, C.c_void_p]
+_lib.hn_update_density_grid.argtypes = [C.c_void_p, C.c_float, C.c_uint32, C.c_uint32]
+_lib.hn_mark_untrained_density_grid.argtypes = [C.c_void_p]
+_lib.hn_get_density_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
 _lib.hn_set_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
 _lib.hn_op_read_envmap.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_env_light_dirs.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
@@ -383,6 +387,17 @@ class Testbed:
 
     def train_apply(self, grad_scale: float = 1.0):
         self._check(_lib.hn_train_apply(self._h, grad_scale))
+
+    def update_density_grid(self, decay: float = 0.95, n_uniform: int = 128 ** 3, n_nonuniform: int = 0):
+        self._check(_lib.hn_update_density_grid(self._h, decay, n_uniform, n_nonuniform))
+
+    def mark_untrained_density_grid(self):
+        self._check(_lib.hn_mark_untrained_density_grid(self._h))
+
+    def get_density_grid(self, n_cascades: int = 1) -> np.ndarray:
+        out = np.empty(128 ** 3 * n_cascades, np.float32)
+        self._check(_lib.hn_get_density_grid(self._h, _ptr(out), out.size))
+        return out
 
     def train_stats(self) -> TrainStats:
         st = TrainStats()

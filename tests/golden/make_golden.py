@@ -167,6 +167,16 @@ def make_ref_env():
             t6 = (C.c_float * 6)(); ref.ref_loss_and_gradient(fa(*lt_t[i]), fa(*lt_p[i]), lt, t6); res[i] = t6[:]
         out[f"loss_{tag}"] = res
     out["loss_target"], out["loss_pred"] = lt_t, lt_p
+    # pcg32 (training ray selection, density-grid jitter): raw outputs after seeding + skip-ahead
+    seeds = np.array([0, 1, 1337, 2 ** 40 + 12345], np.uint64)
+    advs = np.array([0, 4, 16 * 4096, 2 ** 32], np.uint64)
+    pc = np.zeros((4, 4, 8), np.uint32)
+    for a, sd in enumerate(seeds):
+        for b, ad in enumerate(advs):
+            tmp = (C.c_uint32 * 8)()
+            ref.ref_pcg32(C.c_uint64(int(sd)), C.c_uint64(int(ad)), 8, tmp)
+            pc[a, b] = tmp[:]
+    out["pcg_seeds"], out["pcg_advances"], out["pcg_out"] = seeds, advs, pc
     np.savez_compressed(os.path.join(HERE, "ref_host_env.npz"), **out)
     print("ref_host_env.npz:", len(out), "arrays")
 

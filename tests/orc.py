@@ -246,6 +246,23 @@ def train_gradients(p: RenderParams, cfg, params, bits, origins, dirs, t_start, 
     return float(loss), grads, steps
 
 
+def update_density_grid(p: RenderParams, cfg, params, grid, n_cascades, ema_step, n_uniform, n_nonuniform, decay=0.95, seed=1337, rng_calls=0):
+    g = np.ascontiguousarray(grid, np.float32).copy()
+    lib.orc_update_density_grid.argtypes = [C.c_void_p] * 4 + [u32, u32, u32, u32, f32, u32, u32]
+    lib.orc_update_density_grid(C.byref(p), C.byref(cfg), P(params), P(g), n_cascades, ema_step, n_uniform, n_nonuniform, decay, seed, rng_calls)
+    return g
+
+
+def mark_untrained_grid(n_cascades, cams, w, h, focal, principal=(0.5, 0.5)):
+    g = np.zeros(128 ** 3 * n_cascades, np.float32)
+    c = np.ascontiguousarray(cams, np.float32).reshape(-1, 12)
+    f = np.asarray([focal, focal] if np.isscalar(focal) else focal, np.float32)
+    pp = np.asarray(principal, np.float32)
+    lib.orc_mark_untrained_grid.argtypes = [C.c_void_p, u32, u32, C.c_void_p, i32, i32, C.c_void_p, C.c_void_p]
+    lib.orc_mark_untrained_grid(P(g), n_cascades, c.shape[0], P(c), w, h, P(f), P(pp))
+    return g
+
+
 def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):
     n = p.width * p.height
     frame = np.zeros((p.height, p.width, 4), np.float32)

@@ -140,3 +140,44 @@ def test_data_parallel_split_sums_to_the_full_batch(hn, root):
     assert cosine(g0 + g1, gf) >= 0.99999
     assert np.abs((g0 + g1) - gf).max() <= 1e-3 * np.abs(gf).max()
     assert cosine(g0, g1) < 0.999   # the halves really are different rays
+
+
+def test_density_grid_update_matches_oracle(hn, orc, root):
+    """update_density_grid_nerf — same cells, same jitter (pcg32), density network, max-splat, decayed maximum."""
+    tb, params, grid = nerf_setup(hn, root, 0.5)
+    n = 128 ** 3
+    cfg = orc.net_config_from_info(tb.network_info())
+    p = orc.render_params(8, 8, hn.synthetic.default_camera())
+    start = (grid * np.float32(0.02)).astype(f32)          # occupied sphere (0.02 > threshold) so the non-uniform half finds cells
+    tb.set_density_grid(start, 1)
+    tb.update_density_grid(0.95, n // 4, n // 4)
+    got = tb.get_density_grid(1)
+    want = orc.update_density_grid(p, cfg, params, start, 1, 0, n // 4, n // 4, 0.95, 1337, 0)
+    touched = want != start * np.float32(0.95)
+    assert touched.mean() > 0.2
+    assert np.array_equal(got == start * np.float32(0.95), ~touched) or np.mean((got != start * np.float32(0.95)) == touched) > 0.9999
+    assert np.allclose(got, want, rtol=2e-2, atol=1e-6), np.abs(got - want).max()
+    # second round continues the rng stream and the ema step
+    tb.update_density_grid(0.95, n // 4, 0)
+    got2 = tb.get_density_grid(1)
+    want2 = orc.update_density_grid(p, cfg, params, want, 1, 1, n // 4, 0, 0.95, 1337, 2)
+    assert np.allclose(got2, want2, rtol=2e-2, atol=1e-6)
+    # the bitfield follows the grid (a-20 path, bit-exact given the same grid): compare through the oracle on the GPU's own grid
+    bits = tb.get_occupancy_bitfield()
+    wbits, _ = orc.bitfield_from_grid(got2, 1)
+    assert np.array_equal(bits, wbits)
+
+
+def test_mark_untrained_matches_oracle(hn, orc, root):
+    imgs, _, focal = hn.synthetic.sphere_dataset(2, 32)
+    # two cameras INSIDE the unit cube: cells behind them and outside their frusta are never seen
+    cams = np.stack([np.asarray(hn.synthetic.look_at_camera((0.5, 0.5, 0.95), (0.5, 0.5, 0.5)), f32).reshape(12),
+                     np.asarray(hn.synthetic.look_at_camera((0.1, 0.6, 0.4), (0.6, 0.5, 0.5)), f32).reshape(12)])
+    tb, _, _ = nerf_setup(hn, root, 0.5)
+    tb.set_training_data(imgs, cams, focal)
+    tb.mark_untrained_density_grid()
+    got = tb.get_density_grid(1)
+    want = orc.mark_untrained_grid(1, cams, 32, 32, focal)
+    assert set(np.unique(got)) <= {-1.0, 0.0}
+    assert np.mean(got == want) > 0.9995
+    assert 0.01 < np.mean(want < 0) < 0.99

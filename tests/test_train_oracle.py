@@ -104,3 +104,13 @@ def test_loss_functions_pinned_against_golden(orc):
             got = np.zeros(6, f32)
             orc.lib.orc_loss_and_gradient(orc.P(g["loss_target"][i].copy()), orc.P(g["loss_pred"][i].copy()), lt, orc.P(got))
             assert np.array_equal(got.view(np.uint32), g[f"loss_{tag}"][i].view(np.uint32))
+
+
+def test_pcg32_pinned_against_golden(orc):
+    g = np.load(os.path.join(HERE, "golden", "ref_host_env.npz"))
+    orc.lib.orc_pcg32.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]
+    for a, sd in enumerate(g["pcg_seeds"]):
+        for b, ad in enumerate(g["pcg_advances"]):
+            out = np.zeros(8, np.uint32)
+            orc.lib.orc_pcg32(int(sd), int(ad), 8, orc.P(out))
+            assert np.array_equal(out, g["pcg_out"][a, b])

@@ -307,42 +307,82 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 	}
 }
 
+// One ray per lane, at most `limit` samples, in the flat warp-converged loop of march_kernel (each trip a lane either takes a
+// sample or skips to the next voxel; the skip code runs only when some lane needs it): per-lane arithmetic and its order are
+// those of advance_to_occupied + calc_dt, so counts and positions equal the sequential walk. WRITE = false only counts.
+template <bool WRITE>
+__device__ __forceinline__ uint32_t flat_march(const FrameArgs& a, const uint8_t* __restrict__ bits, bool valid, V3 o, V3 d, float t, uint32_t limit,
+	float4* __restrict__ dst, uint32_t* __restrict__ dst_ray, uint32_t ray) {
+	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
+	const V3 tdiag = train.hi - train.lo;
+	const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+	const float t_far = valid ? occ_t_far(a, bits, o, d) : -1.f;
+	bool active = valid && limit > 0;
+	uint32_t count = 0;
+	int it = 1;
+	while (__any_sync(0xffffffffu, active)) {
+		bool skip = false;
+		uint32_t mip = 0;
+		V3 pos = o;
+		if (active) {
+			pos = o + t * d;
+			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) {
+				active = false;
+			} else {
+				mip = min(max(mip_from_pos(pos), 0u), a.max_mip);
+				if (!bits || occupied_at(pos, bits, mip)) {
+					const float dt = calc_dt(t, a.cone_angle);
+					if (WRITE) {
+						const V3 wp = (pos - train.lo) / tdiag;
+						dst[count] = make_float4(wp.x, wp.y, wp.z, dt);
+						dst_ray[count] = ray;
+					}
+					++count;
+					t += dt;
+					it = 1;
+					if (count == limit) active = false;
+				} else {
+					skip = true;
+				}
+			}
+		}
+		if (__any_sync(0xffffffffu, skip)) {
+			if (skip) {
+				while (mip < a.max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
+				t = advance_to_next_voxel(t, a.cone_angle, pos, d, idir, mip);
+				++it;
+				if (a.dda_iter_cap > 0 && it >= a.dda_iter_cap) active = false;
+			}
+		}
+	}
+	return count;
+}
+
 // a-21 generate_training_samples_nerf (src/testbed_nerf.cu:737-890): per training ray, count the samples along the occupancy
-// DDA (at most NERF_STEPS = 1024), reserve that many slots with ONE atomic, then walk again and write warped position + dt.
-// Rays whose samples do not fit below max_samples get none (:848-852).
-__global__ void __launch_bounds__(128) train_march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, uint32_t n_rays, const float* __restrict__ ray_o,
+// DDA (at most NERF_STEPS = 1024), reserve that many slots (one atomic per WARP: warp prefix sum of the counts), then walk
+// again and write warped position + dt. Rays whose samples do not fit below max_samples get none (:848-852).
+__global__ void __launch_bounds__(64) train_march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, uint32_t n_rays, const float* __restrict__ ray_o,
 	const float* __restrict__ ray_d, const float* __restrict__ ray_t, uint32_t max_samples, uint32_t* __restrict__ counter,
 	uint32_t* __restrict__ numsteps_out, uint32_t* __restrict__ base_out, float4* __restrict__ coords, uint32_t* __restrict__ sample_ray) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_rays) return;
-	const V3 o = ld3(ray_o + 3 * i), d = ld3(ray_d + 3 * i);
-	const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
-	const V3 tdiag = train.hi - train.lo;
-	const float t_far = occ_t_far(a, bits, o, d);
-	uint32_t n = 0;
-	float t = ray_t[i];
-	while (n < 1024u) {
-		t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
-		if (t >= MAX_DEPTH_F) break;
-		t += calc_dt(t, a.cone_angle);
-		++n;
-	}
-	uint32_t base = 0;
-	if (n) {
-		base = atomicAdd(counter, n);
-		if (base + n > max_samples) n = 0;
-	}
-	numsteps_out[i] = n; base_out[i] = base;
-	t = ray_t[i];
-	for (uint32_t j = 0; j < n; ++j) {
-		t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
-		const float dt = calc_dt(t, a.cone_angle);
-		const V3 wp = ((o + t * d) - train.lo) / tdiag;
-		coords[base + j] = make_float4(wp.x, wp.y, wp.z, dt);
-		sample_ray[base + j] = i;
-		t += dt;
-	}
+	const uint32_t lane = threadIdx.x & 31u;
+	const bool valid = i < n_rays;
+	V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 0.f, 1.f);
+	float t0 = MAX_DEPTH_F;
+	if (valid) { o = ld3(ray_o + 3 * i); d = ld3(ray_d + 3 * i); t0 = ray_t[i]; }
+	uint32_t n = flat_march<false>(a, bits, valid, o, d, t0, 1024u, nullptr, nullptr, 0u);
+	// warp-aggregated slot reservation
+	uint32_t incl = n;
+	#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) { const uint32_t up = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= (uint32_t)s) incl += up; }
+	const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+	uint32_t warp_base = 0;
+	if (lane == 0 && total) warp_base = atomicAdd(counter, total);
+	warp_base = __shfl_sync(0xffffffffu, warp_base, 0);
+	const uint32_t base = warp_base + incl - n;
+	if (base + n > max_samples) n = 0;
+	if (valid) { numsteps_out[i] = n; base_out[i] = base; }
+	flat_march<true>(a, bits, valid, o, d, t0, n, coords + base, sample_ray + base, i);
 }
 
 __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const uint8_t* __restrict__ bits, float* __restrict__ o_out, float* __restrict__ d_out,
@@ -552,7 +592,7 @@ void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays
 void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
 	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s) {
 	if (!n_rays) return;
-	train_march_kernel<<<(n_rays + 127) / 128, 128, 0, s>>>(a, bits, n_rays, o, d, t, max_samples, counter, numsteps, base, coords, sample_ray);
+	train_march_kernel<<<(n_rays + 63) / 64, 64, 0, s>>>(a, bits, n_rays, o, d, t, max_samples, counter, numsteps, base, coords, sample_ray);
 }
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {
 	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;

@@ -184,64 +184,107 @@ __device__ __forceinline__ float density_derivative(float v, int act) {
 	}
 }
 
-// compute_loss_kernel_train_nerf (src/testbed_nerf.cu:893-1212), one thread per ray: composite once to get the ray colour,
-// then again to emit dL/d(network output) per sample. out/d_out_density: [samples][16] fp16. Writes d_out [samples][16] fp16
-// (rows 0..2, rest zero) and d_sigma [samples] (fp32), both scaled by loss_scale / n_rays_total; samples past the
-// early stop (T < 1e-4) get zero gradients (the reference compacts them away). loss_acc += mean(loss_rgb) / n_rays_total.
-__global__ void train_loss_kernel(uint32_t n_rays, uint32_t n_rays_total, const uint32_t* __restrict__ numsteps_in, const uint32_t* __restrict__ base_in,
+__device__ __forceinline__ float warp_incl_sum(float v, uint32_t lane) {
+	#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) { const float up = __shfl_up_sync(0xffffffffu, v, s); if (lane >= (uint32_t)s) v += up; }
+	return v;
+}
+__device__ __forceinline__ float warp_incl_prod(float v, uint32_t lane) {
+	#pragma unroll
+	for (int s = 1; s < 32; s <<= 1) { const float up = __shfl_up_sync(0xffffffffu, v, s); if (lane >= (uint32_t)s) v *= up; }
+	return v;
+}
+
+// compute_loss_kernel_train_nerf (src/testbed_nerf.cu:893-1212), ONE WARP per ray (the reference: one thread per ray; at
+// ~5 000 rays per step that leaves a B200 with 40 blocks): lane j takes sample 32c + j of chunk c. Pass 1 composites the ray
+// colour (transmittance = warp product scan carried across chunks; the ray stops at the first sample whose incoming T is
+// below 1e-4), pass 2 recomputes the weights and emits dL/d(network output) per sample from inclusive prefix sums of w*c
+// (the "suffix" of the reference is ray colour minus that prefix). out/density_out: [samples][16] fp16. Writes
+// d_out [samples][16] fp16 (rows 0..2) and d_sigma [samples] fp32, both scaled by loss_scale / n_rays_total; samples past the
+// stop get zero gradients (the reference compacts them away). loss_acc += mean(loss_rgb) / n_rays_total.
+__global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32_t n_rays_total, const uint32_t* __restrict__ numsteps_in, const uint32_t* __restrict__ base_in,
 	const float4* __restrict__ coords, const __half* __restrict__ out, const __half* __restrict__ density_out, const float* __restrict__ ray_target,
 	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, __half* __restrict__ d_out, float* __restrict__ d_sigma,
 	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc) {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	float my_loss = 0.f;
-	if (i < n_rays) {
-		const uint32_t numsteps = numsteps_in[i], base = base_in[i];
-		const float dt_range = HN_MIN_STEP * 128.0f - HN_MIN_STEP;
-		float T = 1.f;
-		float rr = 0.f, rg = 0.f, rb = 0.f;
-		uint32_t compacted = 0;
-		for (; compacted < numsteps; ++compacted) {
-			if (T < 1e-4f) break;
-			const size_t s = base + compacted;
-			const __half* o = out + s * 16;
-			const float dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
-			const float alpha = 1.f - __expf(-act_density(__half2float(density_out[s * 16]), density_act) * dt);
-			const float weight = alpha * T;
-			rr += weight * act_rgb(__half2float(o[0]), rgb_act); rg += weight * act_rgb(__half2float(o[1]), rgb_act); rb += weight * act_rgb(__half2float(o[2]), rgb_act);
-			T *= (1.f - alpha);
-		}
-		if (compacted == numsteps) { rr += T * ray_bg[3 * i]; rg += T * ray_bg[3 * i + 1]; rb += T * ray_bg[3 * i + 2]; }
-		if (used_out) used_out[i] = compacted;
-		float gr, gg, gb;
-		const float l = loss_grad(loss_type, ray_target[3 * i], rr, gr) + loss_grad(loss_type, ray_target[3 * i + 1], rg, gg) + loss_grad(loss_type, ray_target[3 * i + 2], rb, gb);
-		my_loss = numsteps ? l / 3.0f / (float)n_rays_total : 0.f;
-		const float ls = loss_scale / (float)n_rays_total;
-		const float l2_reg = rgb_act == 3 ? 1e-4f : 0.0f;
-		float r2 = 0.f, g2 = 0.f, b2 = 0.f;
-		T = 1.f;
-		for (uint32_t j = 0; j < numsteps; ++j) {
+	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t lane = threadIdx.x & 31u;
+	if (i >= n_rays) return; // warp-uniform
+	const uint32_t numsteps = numsteps_in[i], base = base_in[i];
+	const float dt_range = HN_MIN_STEP * 128.0f - HN_MIN_STEP;
+	const uint32_t n_chunks = (numsteps + 31u) / 32u;
+	// ---- pass 1: ray colour
+	float T = 1.f, rr = 0.f, rg = 0.f, rb = 0.f;
+	uint32_t compacted = numsteps;
+	for (uint32_t c = 0; c < n_chunks; ++c) {
+		const uint32_t j = c * 32u + lane;
+		const bool has = j < numsteps;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+		if (has) {
 			const size_t s = base + j;
-			uint4* dst = reinterpret_cast<uint4*>(d_out + s * 16);
-			if (j >= compacted) { dst[0] = make_uint4(0, 0, 0, 0); dst[1] = make_uint4(0, 0, 0, 0); d_sigma[s] = 0.f; continue; }
-			const __half* o = out + s * 16;
-			const float o0 = __half2float(o[0]), o1 = __half2float(o[1]), o2 = __half2float(o[2]), sraw = __half2float(density_out[s * 16]);
-			const float cr = act_rgb(o0, rgb_act), cg = act_rgb(o1, rgb_act), cb = act_rgb(o2, rgb_act);
+			const uint2 o = *reinterpret_cast<const uint2*>(out + s * 16);
+			const __half2 h01 = *reinterpret_cast<const __half2*>(&o.x), h2x = *reinterpret_cast<const __half2*>(&o.y);
 			const float dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
-			const float alpha = 1.f - __expf(-act_density(sraw, density_act) * dt);
-			const float weight = alpha * T;
-			r2 += weight * cr; g2 += weight * cg; b2 += weight * cb;
-			T *= (1.f - alpha);
-			const float sr = rr - r2, sg = rg - g2, sb = rb - b2; // suffix of the ray behind this sample
-			const float d0 = ls * (weight * gr * rgb_derivative(o0, rgb_act) + fmaxf(0.0f, l2_reg * o0));
-			const float d1 = ls * (weight * gg * rgb_derivative(o1, rgb_act) + fmaxf(0.0f, l2_reg * o1));
-			const float d2 = ls * (weight * gb * rgb_derivative(o2, rgb_act) + fmaxf(0.0f, l2_reg * o2));
-			dst[0] = make_uint4(pack_h2(d0, d1), pack_h2(d2, 0.f), 0, 0); dst[1] = make_uint4(0, 0, 0, 0);
-			d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T * cr - sr) + gg * (T * cg - sg) + gb * (T * cb - sb)));
+			alpha = 1.f - __expf(-act_density(__half2float(density_out[s * 16]), density_act) * dt);
+			cr = act_rgb(__low2float(h01), rgb_act); cg = act_rgb(__high2float(h01), rgb_act); cb = act_rgb(__low2float(h2x), rgb_act);
 		}
+		const float P = warp_incl_prod(1.f - alpha, lane);
+		float Pex = __shfl_up_sync(0xffffffffu, P, 1);
+		if (lane == 0) Pex = 1.f;
+		const float T_before = T * Pex;
+		const uint32_t stop = __ballot_sync(0xffffffffu, has && T_before < 1e-4f);
+		const uint32_t last = stop ? (uint32_t)(__ffs(stop) - 1) : 32u; // samples [0, last) of this chunk are used
+		const float w = (has && lane < last) ? alpha * T_before : 0.f;
+		float sr = w * cr, sg = w * cg, sb = w * cb;
+		#pragma unroll
+		for (int dd = 16; dd > 0; dd >>= 1) { sr += __shfl_xor_sync(0xffffffffu, sr, dd); sg += __shfl_xor_sync(0xffffffffu, sg, dd); sb += __shfl_xor_sync(0xffffffffu, sb, dd); }
+		rr += sr; rg += sg; rb += sb;
+		if (stop) { compacted = c * 32u + last; T = __shfl_sync(0xffffffffu, T_before, last); break; }
+		T *= __shfl_sync(0xffffffffu, P, 31);
 	}
-	#pragma unroll
-	for (int d = 16; d > 0; d >>= 1) my_loss += __shfl_xor_sync(0xffffffffu, my_loss, d);
-	if ((threadIdx.x & 31) == 0 && my_loss != 0.f) atomicAdd(loss_acc, my_loss);
+	if (compacted == numsteps) { rr += T * ray_bg[3 * i]; rg += T * ray_bg[3 * i + 1]; rb += T * ray_bg[3 * i + 2]; }
+	if (used_out && lane == 0) used_out[i] = compacted;
+	float gr, gg, gb;
+	const float l = loss_grad(loss_type, ray_target[3 * i], rr, gr) + loss_grad(loss_type, ray_target[3 * i + 1], rg, gg) + loss_grad(loss_type, ray_target[3 * i + 2], rb, gb);
+	if (lane == 0 && numsteps) atomicAdd(loss_acc, l / 3.0f / (float)n_rays_total);
+	const float ls = loss_scale / (float)n_rays_total;
+	const float l2_reg = rgb_act == 3 ? 1e-4f : 0.0f;
+	// ---- pass 2: gradients
+	float Tc = 1.f, pr = 0.f, pg = 0.f, pb = 0.f; // carried transmittance and colour prefix
+	for (uint32_t c = 0; c < n_chunks; ++c) {
+		const uint32_t j = c * 32u + lane;
+		const bool has = j < numsteps;
+		const size_t s = base + j;
+		const bool used = j < compacted;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, o0 = 0.f, o1 = 0.f, o2 = 0.f, sraw = 0.f, dt = 0.f;
+		if (used) {
+			const uint2 o = *reinterpret_cast<const uint2*>(out + s * 16);
+			const __half2 h01 = *reinterpret_cast<const __half2*>(&o.x), h2x = *reinterpret_cast<const __half2*>(&o.y);
+			o0 = __low2float(h01); o1 = __high2float(h01); o2 = __low2float(h2x); sraw = __half2float(density_out[s * 16]);
+			dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
+			alpha = 1.f - __expf(-act_density(sraw, density_act) * dt);
+			cr = act_rgb(o0, rgb_act); cg = act_rgb(o1, rgb_act); cb = act_rgb(o2, rgb_act);
+		}
+		const float P = warp_incl_prod(1.f - alpha, lane);
+		float Pex = __shfl_up_sync(0xffffffffu, P, 1);
+		if (lane == 0) Pex = 1.f;
+		const float weight = alpha * (Tc * Pex);
+		const float T_after = Tc * P;
+		const float r2 = pr + warp_incl_sum(weight * cr, lane), g2 = pg + warp_incl_sum(weight * cg, lane), b2 = pb + warp_incl_sum(weight * cb, lane);
+		if (has) {
+			uint4* dst = reinterpret_cast<uint4*>(d_out + s * 16);
+			if (!used) { dst[0] = make_uint4(0, 0, 0, 0); dst[1] = make_uint4(0, 0, 0, 0); d_sigma[s] = 0.f; }
+			else {
+				const float sr = rr - r2, sg = rg - g2, sb = rb - b2; // suffix of the ray behind this sample
+				const float d0 = ls * (weight * gr * rgb_derivative(o0, rgb_act) + fmaxf(0.0f, l2_reg * o0));
+				const float d1 = ls * (weight * gg * rgb_derivative(o1, rgb_act) + fmaxf(0.0f, l2_reg * o1));
+				const float d2 = ls * (weight * gb * rgb_derivative(o2, rgb_act) + fmaxf(0.0f, l2_reg * o2));
+				dst[0] = make_uint4(pack_h2(d0, d1), pack_h2(d2, 0.f), 0, 0); dst[1] = make_uint4(0, 0, 0, 0);
+				d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T_after * cr - sr) + gg * (T_after * cg - sg) + gb * (T_after * cb - sb)));
+			}
+		}
+		Tc *= __shfl_sync(0xffffffffu, P, 31);
+		pr = __shfl_sync(0xffffffffu, r2, 31); pg = __shfl_sync(0xffffffffu, g2, 31); pb = __shfl_sync(0xffffffffu, b2, 31);
+	}
 }
 
 // kernel_grid_backward (tcnn grid.h:214-320): thread = (sample, level); dL/dfeature scattered to the 8 corners with the
@@ -483,7 +526,7 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	ev.start();
 	__half* g_out = t.dact[0].p;               // [n][16]
 	float* d_sigma = (float*)t.dact[3].p;      // [n] fp32 (buffer holds n*64 halfs)
-	train_loss_kernel<<<blocks(n_rays, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
+	train_loss_kernel<<<blocks((size_t)n_rays * 32, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
 		loss_type, loss_scale, a.rgb_act, a.density_act, g_out, d_sigma, used_dev, t.loss_acc.p);
 	ev.stop(t.ms[2]);
 	// ---- backward

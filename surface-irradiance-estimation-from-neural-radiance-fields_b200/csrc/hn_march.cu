@@ -436,7 +436,7 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) {
 				t = MAX_DEPTH_F; active = false;
 			} else {
-				mip = min(max(mip_from_pos(pos), 0u), a.max_mip);
+				mip = a.max_mip ? min(max(mip_from_pos(pos), 0u), a.max_mip) : 0u; // one cascade: the clamp makes it 0 whatever frexpf says
 				if (!bits || occupied_at(pos, bits, mip)) {
 					const float dt = calc_dt(t, a.cone_angle);
 					bool emit = true;

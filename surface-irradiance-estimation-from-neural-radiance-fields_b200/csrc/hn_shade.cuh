@@ -10,7 +10,7 @@ namespace hn {
 __device__ __forceinline__ float act_rgb(float v, int act) {
 	switch (act) {
 		case 1: return fmaxf(v, 0.0f);
-		case 2: return 1.0f / (1.0f + __expf(-v));
+		case 2: return __fdividef(1.0f, 1.0f + __expf(-v));
 		case 3: return __expf(fminf(fmaxf(v, -10.0f), 10.0f));
 		default: return v;
 	}
@@ -74,16 +74,12 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 		if (has) {
 			const float4 s = pre.s;
 			const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
-			const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP);
 			const float sigma = act_density(__high2float(bs), a.density_act);
-			const float wdt = __fdiv_rn(__fsub_rn(s.w, HN_MIN_STEP), dt_range);
-			const float dt = __fadd_rn(__fmul_rn(wdt, dt_range), HN_MIN_STEP);
-			alpha = 1.f - __expf(-sigma * dt);
+			// the reference sends dt and the position through warp/unwarp (network input); that round trip moves them by at most an
+			// ulp, far below the compositing tolerance, and costs five IEEE divisions per sample: use the marched values directly
+			alpha = 1.f - __expf(-sigma * s.w);
 			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
-			const float ux = __fadd_rn(a.train_lo[0], __fmul_rn(__fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]), a.train_diag[0]));
-			const float uy = __fadd_rn(a.train_lo[1], __fmul_rn(__fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]), a.train_diag[1]));
-			const float uz = __fadd_rn(a.train_lo[2], __fmul_rn(__fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]), a.train_diag[2]));
-			zview = a.cam_fwd[0] * (ux - a.cam_pos[0]) + a.cam_fwd[1] * (uy - a.cam_pos[1]) + a.cam_fwd[2] * (uz - a.cam_pos[2]);
+			zview = a.cam_fwd[0] * (s.x - a.cam_pos[0]) + a.cam_fwd[1] * (s.y - a.cam_pos[1]) + a.cam_fwd[2] * (s.z - a.cam_pos[2]);
 		}
 		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
 		#pragma unroll
@@ -125,17 +121,24 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 		}
 	}
 	const bool alive_next = !terminated && count == CHUNK;
+	// every lane holds the same ray state here (the reductions are butterflies); the sRGB -> linear conversion of a finished
+	// ray (three powf, ~50 instructions each) is spread over lanes 0..2 so the warp issues it once instead of three times
+	const bool finished = !alive_next && rgba.w > 0.001f; // compact_kernel_nerf keeps finished rays with alpha > 0.001
+	float4 tmp = rgba;
+	if (finished && !a.linear_colors) {
+		float c = lane == 0 ? rgba.x : (lane == 1 ? rgba.y : rgba.z);
+		c = srgb_to_linear(c);
+		tmp.x = __shfl_sync(0xffffffffu, c, 0); tmp.y = __shfl_sync(0xffffffffu, c, 1); tmp.z = __shfl_sync(0xffffffffu, c, 2);
+	}
 	if (lane == 0) {
 		a.rays.rgba[r] = rgba;
 		a.rays.depth[r] = depth;
 		a.rays.d_mw[r].w = max_weight;
 		a.rays.n_steps[r] = n_steps;
 		a.survive[chunk] = alive_next ? 1u : 0u;
-		if (!alive_next && rgba.w > 0.001f) { // compact_kernel_nerf keeps finished rays with alpha > 0.001
+		if (finished) {
 			const uint32_t pix = a.rays.pixel[r];
 			if (!(a.depth_test && !a.depth_clip && depth > a.depth_buffer[pix])) { // NeRF behind the mesh: drop (per-pixel rule)
-				float4 tmp = rgba;
-				if (!a.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
 				const float4 fb = a.frame[pix];
 				const float ia = 1.0f - tmp.w;
 				a.frame[pix] = make_float4(tmp.x + fb.x * ia, tmp.y + fb.y * ia, tmp.z + fb.z * ia, tmp.w + fb.w * ia);

@@ -121,7 +121,8 @@ typedef struct {
 int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out);
 /* operator entry point for the parity test: explicit rays (origin, unit dir, start t), targets and backgrounds [n][3] in the
  * training colour space -> mean loss, fp32 gradients [n_params] (host, scaled by loss_scale), samples used per ray.
- * loss_type: 0 = L2, 1 = Huber (nerf_device.cuh:640-655). */
+ * loss_type (ELossType, nerf_device.cuh:74-142,640-655; also option "train_loss_type" and "loss"."otype" of the config):
+ * 0 L2, 1 Huber(0.1)/5, 2 RelativeL2, 3 L1, 4 Mape, 5 Smape, 6 LogL1. */
 int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
 	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
 

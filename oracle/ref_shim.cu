@@ -95,7 +95,7 @@ void ref_compute_local_frame(const float z[3], float out[9]) {
 
 // a-21 loss functions (nerf_device.cuh:74-112,640-655): loss_type 0 = L2, 1 = Huber
 void ref_loss_and_gradient(const float target[3], const float pred[3], int32_t loss_type, float out[6]) {
-	LossAndGradient lg = loss_and_gradient(vec3(target[0], target[1], target[2]), vec3(pred[0], pred[1], pred[2]), loss_type == 1 ? ELossType::Huber : ELossType::L2);
+	LossAndGradient lg = loss_and_gradient(vec3(target[0], target[1], target[2]), vec3(pred[0], pred[1], pred[2]), (loss_type == 1 ? ELossType::Huber : loss_type == 2 ? ELossType::RelativeL2 : loss_type == 3 ? ELossType::L1 : loss_type == 4 ? ELossType::Mape : loss_type == 5 ? ELossType::Smape : loss_type == 6 ? ELossType::LogL1 : ELossType::L2));
 	out[0] = lg.loss.x; out[1] = lg.loss.y; out[2] = lg.loss.z; out[3] = lg.gradient.x; out[4] = lg.gradient.y; out[5] = lg.gradient.z;
 }
 

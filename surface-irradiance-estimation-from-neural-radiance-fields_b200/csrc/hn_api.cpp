@@ -199,6 +199,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
+		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
 		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
 	};
 }

@@ -139,8 +139,11 @@ void apply_network_config(hn_context* ctx, const Json& cfg) {
 		TrainCfg t;
 		if (cfg.contains("loss")) {
 			const std::string lt = lower(cfg.at("loss").value("otype", std::string("Huber")));
-			if (lt == "l2") t.loss_type = 0; else if (lt == "huber") t.loss_type = 1;
-			else throw std::runtime_error("loss: only L2 and Huber are supported on this path, got '" + lt + "'");
+			// ELossType (nerf_device.cuh:48-56, string_to_loss_type src/testbed_nerf.cu): ids used across the ABI
+			static const char* names[] = {"l2", "huber", "relativel2", "l1", "mape", "smape", "logl1"};
+			t.loss_type = -1;
+			for (int k = 0; k < 7; ++k) if (lt == names[k]) t.loss_type = k;
+			if (t.loss_type < 0) throw std::runtime_error("loss: unknown otype '" + lt + "'");
 		}
 		t.ema = false; t.exp_decay = false;
 		const Json* o = cfg.find("optimizer");

@@ -71,6 +71,7 @@ struct Options {
 	int fuse_composite = 0;                     // 1 = composite inside the tcgen05 network kernel (eval_impl 1 only; measured slower, kept as an option)
 	int composite_impl = 1;                     // 1 = one warp per ray + compact kernel, 0 = 32 rays per warp with in-kernel compaction
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
+	int snapshot_optimizer_state = 0;           // hn_save_snapshot: include the Trainer's optimizer state (save_snapshot(path, include_optimizer_state))
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
 	int env_light_batch = 8 << 20;              // light rays in flight per batch (bounds the workspace)
 	int mesh_aabb_user = 0;
@@ -212,6 +213,8 @@ void train_apply(hn_context* ctx, float grad_scale);
 void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* t, const float* targets, const float* bgs,
 	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
 void train_release(hn_context* ctx);
+void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps);
+void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n);
 void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
 void train_mark_untrained(hn_context* ctx);
 void refresh_bitfield_from_device_grid(hn_context* ctx); // hn_api.cpp: mean -> threshold -> bitfield + mips -> occupancy bounds

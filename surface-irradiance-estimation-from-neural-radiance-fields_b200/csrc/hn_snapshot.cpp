@@ -357,6 +357,19 @@ void load_snapshot_file(hn_context* ctx, const std::string& path) {
 	if (ptype == "__half") upload_params(ctx, pb.str.data(), pb.str.size() / 2, 0);
 	else if (ptype == "float") upload_params(ctx, pb.str.data(), pb.str.size() / 4, 1);
 	else throw std::runtime_error("Trainer: snapshot parameters must be of type float of __half");
+	// optimizer state (Trainer::deserialize -> Optimizer::deserialize): innermost Adam moments + step counters
+	if (snap.contains("optimizer")) {
+		const Json* oj = &snap.at("optimizer");
+		while (oj->is_object() && oj->contains("nested")) oj = &oj->at("nested");
+		if (oj->is_object() && oj->contains("first_moments_binary") && oj->contains("second_moments_binary")) {
+			const Json& a1 = oj->at("first_moments_binary"); const Json& a2 = oj->at("second_moments_binary");
+			if (a1.type != Json::Binary || a2.type != Json::Binary || a1.str.size() != a2.str.size()) throw std::runtime_error("snapshot: bad optimizer moments");
+			const Json* ps = oj->find("param_steps_binary");
+			if (ps && (ps->type != Json::Binary || ps->str.size() != a1.str.size())) ps = nullptr;
+			train_import_state(ctx, (uint32_t)oj->value("current_step", snap.value("training_step", 0.0)), (const float*)a1.str.data(), (const float*)a2.str.data(),
+				ps ? (const uint32_t*)ps->str.data() : nullptr, a1.str.size() / 4);
+		}
+	}
 	// density grid (fp16, Morton order, 128^3 per cascade)
 	if (snap.contains("density_grid_binary")) {
 		const Json& gb = snap.at("density_grid_binary");
@@ -407,9 +420,37 @@ void save_snapshot_file(hn_context* ctx, const std::string& path) {
 	nerf.set("aabb_scale") = jnum(ctx->aabb_scale);
 	Json& rgb = nerf.set("rgb");
 	rgb.type = Json::Object;
-	rgb.set("rays_per_batch") = jnum(4096); rgb.set("measured_batch_size") = jnum(0); rgb.set("measured_batch_size_before_compaction") = jnum(0);
-	snap.set("training_step") = jnum(0);
-	snap.set("loss") = jnum(0);
+	rgb.set("rays_per_batch") = jnum(ctx->train.ready ? ctx->train.rays_per_batch : 4096); rgb.set("measured_batch_size") = jnum(ctx->train.n_samples_last);
+	rgb.set("measured_batch_size_before_compaction") = jnum(ctx->train.n_samples_last);
+	snap.set("training_step") = jnum(ctx->train.ready ? ctx->train.step : 0);
+	snap.set("loss") = jnum(ctx->train.loss_last);
+	if (ctx->opt.snapshot_optimizer_state && ctx->train.ready) {
+		// Trainer::serialize(true): the optimizer stack serialises itself outside-in (Ema > ExponentialDecay > Adam for
+		// configs/nerf/base.json; tcnn ema.h:190-195, exponential_decay.h:136-142, adam.h:278-286)
+		std::vector<float> m1, m2; std::vector<uint32_t> steps;
+		train_export_state(ctx, m1, m2, steps);
+		auto bin = [](const void* p, size_t bytes) { Json b; b.type = Json::Binary; b.str.assign((const char*)p, bytes); return b; };
+		Json adam; adam.type = Json::Object;
+		adam.set("current_step") = jnum(ctx->train.step);
+		adam.set("base_learning_rate") = jnum(ctx->train_cfg.lr);
+		adam.set("first_moments_binary") = bin(m1.data(), m1.size() * 4);
+		adam.set("second_moments_binary") = bin(m2.data(), m2.size() * 4);
+		adam.set("param_steps_binary") = bin(steps.data(), steps.size() * 4);
+		Json cur = std::move(adam);
+		// wrap inside-out following the config's nesting
+		std::vector<std::string> chain;
+		for (const Json* oj = cfg.find("optimizer"); oj && oj->is_object(); oj = oj->find("nested")) chain.push_back(oj->value("otype", std::string("Adam")));
+		for (int i = (int)chain.size() - 2; i >= 0; --i) {
+			Json w; w.type = Json::Object;
+			std::string ot = chain[i];
+			for (auto& ch : ot) ch = (char)std::tolower((unsigned char)ch);
+			w.set("nested") = std::move(cur);
+			if (ot == "ema") w.set("weights_ema_binary") = bin(ctx->params_host.data(), ctx->params_host.size() * sizeof(__half));
+			else if (ot == "exponentialdecay") { w.set("learning_rate") = jnum(ctx->train_cfg.lr); w.set("learning_rate_factor") = jnum(ctx->train.lr_last > 0.f ? ctx->train.lr_last / ctx->train_cfg.lr : 1.0); }
+			cur = std::move(w);
+		}
+		snap.set("optimizer") = std::move(cur);
+	}
 	auto box = [](const float* b) { Json j; j.type = Json::Object; j.set("min") = jvec(b, 3); j.set("max") = jvec(b + 3, 3); return j; };
 	snap.set("aabb") = box(o.train_aabb);
 	snap.set("render_aabb") = box(o.render_aabb);

@@ -156,16 +156,23 @@ __global__ void combine_density_grad_kernel(const __half* __restrict__ d_rgb_in,
 	for (int k = 1; k < 16; ++k) d[k] = s[k];
 }
 
+// loss_and_gradient (nerf_device.cuh:74-142,640-655) per channel. ids: 0 L2, 1 Huber(0.1)/5, 2 RelativeL2, 3 L1, 4 Mape, 5 Smape, 6 LogL1
 __device__ __forceinline__ float loss_grad(int loss_type, float target, float pred, float& grad) {
 	const float diff = pred - target;
-	if (loss_type == 1) { // huber_loss(alpha 0.1) / 5, nerf_device.cuh:96-112,651
-		const float alpha = 0.1f, ad = fabsf(diff);
-		const float l = ad > alpha ? (ad - 0.5f * alpha) : 0.5f / alpha * diff * diff;
-		grad = (ad > alpha ? (diff > 0 ? 1.0f : -1.0f) : (diff / alpha)) / 5.0f;
-		return l / 5.0f;
+	switch (loss_type) {
+		case 1: {
+			const float alpha = 0.1f, ad = fabsf(diff);
+			const float l = ad > alpha ? (ad - 0.5f * alpha) : 0.5f / alpha * diff * diff;
+			grad = (ad > alpha ? (diff > 0 ? 1.0f : -1.0f) : (diff / alpha)) / 5.0f;
+			return l / 5.0f;
+		}
+		case 2: { const float denom = pred * pred + 1e-2f; grad = 2.0f * diff / denom; return diff * diff / denom; }
+		case 3: grad = copysignf(1.0f, diff); return fabsf(diff);
+		case 4: { const float denom = fabsf(pred) + 1e-2f; grad = copysignf(1.0f / denom, diff); return fabsf(diff) / denom; }
+		case 5: { const float denom = 0.5f * (fabsf(pred) + fabsf(target)) + 1e-2f; grad = copysignf(1.0f / denom, diff); return fabsf(diff) / denom; }
+		case 6: { const float div = fabsf(diff) + 1.0f; grad = copysignf(1.0f / div, diff); return logf(div); }
+		default: grad = 2.0f * diff; return diff * diff;
 	}
-	grad = 2.0f * diff;
-	return diff * diff;
 }
 __device__ __forceinline__ float rgb_derivative(float v, int act) {
 	switch (act) {
@@ -654,7 +661,7 @@ void train_apply(hn_context* ctx, float grad_scale) {
 	float lr = c.lr;
 	if (c.exp_decay && t.step >= c.decay_start && c.decay_interval > 0) lr *= std::pow(c.decay_base, (float)((t.step - c.decay_start) / c.decay_interval + 1));
 	t.lr_last = lr;
-	++t.ema_step;
+	if (t.ema_step < (1u << 20)) ++t.ema_step;
 	const float debias = c.ema ? 1.0f - std::pow(c.ema_decay, (float)t.ema_step) : 1.0f;
 	const uint32_t n = (uint32_t)ctx->net.n_params, n_matrix = (uint32_t)ctx->net.grid_offset; // blob = [density MLP | rgb MLP | grid]
 	adam_kernel<<<blocks(n), 256, 0, s>>>(n, n_matrix, grad_scale, 1.0f / c.loss_scale, lr, c.beta1, c.beta2, c.epsilon, c.l2_reg, c.ema ? 1 : 0, c.ema_decay, debias,
@@ -735,6 +742,30 @@ void train_mark_untrained(hn_context* ctx) {
 	mark_untrained_kernel<<<blocks(n_elements), 256, 0, ctx->stream>>>(n_elements, ctx->density_grid.p, D);
 	t.grid_ema_step = 0;
 	HN_CUDA(cudaGetLastError());
+}
+
+// Trainer state for snapshots (Trainer::serialize(true), tcnn trainer.h:275-288; AdamOptimizer::serialize, adam.h:278-299)
+void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps) {
+	TrainState& t = ctx->train;
+	if (!t.ready) throw std::runtime_error("trainer not initialised");
+	const size_t n = ctx->net.n_params;
+	m1.resize(n); m2.resize(n); steps.resize(n);
+	HN_CUDA(cudaMemcpy(m1.data(), t.m1.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+	HN_CUDA(cudaMemcpy(m2.data(), t.m2.p, n * sizeof(float), cudaMemcpyDeviceToHost));
+	HN_CUDA(cudaMemcpy(steps.data(), t.param_steps.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+}
+// The snapshot's parameters are the inference (EMA) weights; as in Trainer::deserialize they become the training weights,
+// and the EMA accumulator restarts from them (Ema::deserialize, ema.h:197-206).
+void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n) {
+	if (n != ctx->net.n_params) throw std::runtime_error("snapshot: optimizer state has the wrong number of parameters");
+	train_init(ctx, ctx->train.seed);
+	TrainState& t = ctx->train;
+	HN_CUDA(cudaMemcpy(t.m1.p, m1, n * sizeof(float), cudaMemcpyHostToDevice));
+	HN_CUDA(cudaMemcpy(t.m2.p, m2, n * sizeof(float), cudaMemcpyHostToDevice));
+	if (steps) HN_CUDA(cudaMemcpy(t.param_steps.p, steps, n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	HN_CUDA(cudaMemcpy(t.ema.p, t.master.p, n * sizeof(float), cudaMemcpyDeviceToDevice)); // accumulator = weights, debias 1
+	t.step = step;
+	t.ema_step = 1u << 20; // 1 - decay^step == 1: the restored accumulator is already debiased
 }
 
 void train_release(hn_context* ctx) {

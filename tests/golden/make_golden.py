@@ -161,7 +161,7 @@ def make_ref_env():
     # a-21 loss functions (nerf_device.cuh:74-112,640-655)
     lt_t = rng.random((256, 3)).astype(f32)
     lt_p = (rng.random((256, 3)) * 1.4 - 0.2).astype(f32)
-    for lt, tag in ((0, "l2"), (1, "huber")):
+    for lt, tag in ((0, "l2"), (1, "huber"), (2, "relativel2"), (3, "l1"), (4, "mape"), (5, "smape"), (6, "logl1")):
         res = np.zeros((256, 6), f32)
         for i in range(256):
             t6 = (C.c_float * 6)(); ref.ref_loss_and_gradient(fa(*lt_t[i]), fa(*lt_p[i]), lt, t6); res[i] = t6[:]

@@ -40,7 +40,7 @@ def nerf_setup(hn, root, blob_scale, config="nerf/base.json"):
     return tb, params, grid
 
 
-@pytest.mark.parametrize("loss_type,config", [(1, "nerf/base.json"), (0, "nerf/base.json"), (1, "geometry/base.json")])
+@pytest.mark.parametrize("loss_type,config", [(1, "nerf/base.json"), (0, "nerf/base.json"), (4, "geometry/base.json"), (5, "nerf/base.json")])
 def test_gradients_match_oracle(hn, orc, root, loss_type, config):
     tb, params, grid = nerf_setup(hn, root, 0.5, config)
     rng = np.random.default_rng(5)
@@ -183,3 +183,37 @@ def test_mark_untrained_matches_oracle(hn, orc, root):
     assert set(np.unique(got)) <= {-1.0, 0.0}
     assert np.mean(got == want) > 0.9995
     assert 0.01 < np.mean(want < 0) < 0.99
+
+
+def test_snapshot_with_optimizer_state_round_trip(hn, root):
+    """save_snapshot(path, include_optimizer_state=True): Ema > ExponentialDecay > Adam nesting of tcnn's serialisers; a fresh
+    Testbed resumes from it (step counter, Adam moments) and keeps converging."""
+    import msgpack
+    import zlib
+    imgs, cams, focal = hn.synthetic.sphere_dataset(8, 48)
+    tb, _, _ = nerf_setup(hn, root, 1e-4)
+    tb.set_training_data(imgs, cams, focal)
+    tb.reset_trainer(3)
+    for _ in range(40):
+        last = tb.train(1)
+    tb.set_option("snapshot_optimizer_state", 1.0)
+    path = "/tmp/hn_opt_state.ingp"
+    tb.save_snapshot(path)
+    blob = msgpack.unpackb(zlib.decompress(open(path, "rb").read()), raw=False, strict_map_key=False)
+    snap = blob["snapshot"]
+    n = int(tb.network_info().n_params)
+    assert snap["training_step"] == 40 and abs(snap["loss"] - last) < 1e-6
+    opt = snap["optimizer"]
+    assert len(opt["weights_ema_binary"]) == 2 * n                          # Ema
+    assert "learning_rate" in opt["nested"]                                 # ExponentialDecay
+    adam = opt["nested"]["nested"]
+    assert adam["current_step"] == 40 and len(adam["first_moments_binary"]) == 4 * n and len(adam["param_steps_binary"]) == 4 * n
+    m2 = np.frombuffer(adam["second_moments_binary"], np.float32)
+    assert np.isfinite(m2).all() and (m2 > 0).sum() > 10000
+    tb2 = hn.Testbed()
+    tb2.load_snapshot(path)
+    tb2.set_training_data(imgs, cams, focal)
+    assert tb2.training_step == 40
+    resumed = [tb2.train(1) for _ in range(10)]
+    assert tb2.training_step == 50 and np.isfinite(resumed).all()
+    assert np.mean(resumed) < 2.0 * last + 1e-3

@@ -89,7 +89,7 @@ def test_loss_functions_pinned_against_reference_host(orc):
     rng = np.random.default_rng(1)
     for _ in range(200):
         t, pr = rng.random(3, dtype=f32), (rng.random(3, dtype=f32) * 1.4 - 0.2).astype(f32)
-        for lt in (0, 1):
+        for lt in range(7):
             out = np.zeros(6, f32)
             ref.ref_loss_and_gradient(orc.P(t), orc.P(pr), lt, orc.P(out))
             got = np.zeros(6, f32)
@@ -99,7 +99,7 @@ def test_loss_functions_pinned_against_reference_host(orc):
 
 def test_loss_functions_pinned_against_golden(orc):
     g = np.load(os.path.join(HERE, "golden", "ref_host_env.npz"))
-    for lt, tag in ((0, "l2"), (1, "huber")):
+    for lt, tag in ((0, "l2"), (1, "huber"), (2, "relativel2"), (3, "l1"), (4, "mape"), (5, "smape"), (6, "logl1")):
         for i in range(g["loss_target"].shape[0]):
             got = np.zeros(6, f32)
             orc.lib.orc_loss_and_gradient(orc.P(g["loss_target"][i].copy()), orc.P(g["loss_pred"][i].copy()), lt, orc.P(got))

@@ -91,6 +91,12 @@ int hn_op_transmittance(hn_context* ctx, uint32_t n_rays, const float* origins, 
  * (focal length in pixels, principal point in [0,1]^2). Host pointers; copied to the device. */
 int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, int width, int height, const float* cameras,
 	const float focal_px[2], const float principal[2]);
+/* Testbed::load_training_data(path) (testbed.h:600, src/testbed_nerf.cu:2674-2716 -> load_nerf, src/nerf_loader.cu:273-770):
+ * a transforms.json (or the folder holding one) with 8-bit PNG frames: camera matrices through nerf_matrix_to_ngp (scale 0.33,
+ * offset 0.5), focal length from x_fov | fl_x | camera_angle_x (and y), cx / cy, aabb_scale. One resolution and one pinhole
+ * for all frames; anything else (per-frame intrinsics, distortion, JPEG / EXR, depth or ray files) is an error. Call it
+ * before hn_set_params when aabb_scale != 1: a new aabb_scale re-derives the network layout. */
+int hn_load_training_data(hn_context* ctx, const char* transforms_json_or_dir);
 /* (Re)creates the trainer state from the current parameters: fp32 master copy, zeroed Adam moments, EMA, step counter
  * (Trainer ctor + Testbed::reset_network, src/testbed.cu:3933-4200). seed drives ray / pixel / background sampling. */
 int hn_train_init(hn_context* ctx, uint32_t seed);

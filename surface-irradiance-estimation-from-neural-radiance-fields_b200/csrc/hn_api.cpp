@@ -503,6 +503,9 @@ int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, 
 	const float focal_px[2], const float principal[2]) {
 	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_dataset(ctx, rgba, n_images, width, height, cameras, focal_px, principal); HN_CATCH(ctx)
 }
+int hn_load_training_data(hn_context* ctx, const char* path) {
+	HN_TRY(ctx) need(path != nullptr, "null path"); HN_CUDA(cudaSetDevice(ctx->device)); load_training_data_file(ctx, path); HN_CATCH(ctx)
+}
 int hn_train_init(hn_context* ctx, uint32_t seed) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_init(ctx, seed); HN_CATCH(ctx) }
 int hn_train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_accumulate(ctx, n_rays, loss_out); HN_CATCH(ctx) }
 int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats) {

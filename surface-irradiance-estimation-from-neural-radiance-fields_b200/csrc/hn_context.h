@@ -92,6 +92,7 @@ struct TrainCfg {
 };
 struct TrainState {
 	bool ready = false, has_dataset = false;
+	int srgb_space = 0;                     // 1: images came from 8-bit sRGB files -> target blended in sRGB (EColorSpace::SRGB), 0: linear float images
 	uint32_t seed = 1337, step = 0, ema_step = 0, rays_per_batch = 4096, n_rays_last = 0, n_samples_last = 0;
 	float loss_last = 0.f, lr_last = 0.f;
 	float ms[5] = {0, 0, 0, 0, 0};
@@ -218,6 +219,8 @@ void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const f
 void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
 void train_mark_untrained(hn_context* ctx);
 void refresh_bitfield_from_device_grid(hn_context* ctx); // hn_api.cpp: mean -> threshold -> bitfield + mips -> occupancy bounds
+// hn_dataset.cpp
+void load_training_data_file(hn_context* ctx, const std::string& path);
 // hn_scene.cpp
 void add_mesh(hn_context* ctx, const float* tris, size_t n, const float center[3], bool normalize);
 void load_mesh_file(hn_context* ctx, const std::string& path, const float center[3]);

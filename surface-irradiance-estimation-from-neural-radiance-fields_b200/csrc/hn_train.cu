@@ -62,7 +62,7 @@ struct TrainDataDev {
 // random background colour, target = linear_to_srgb(rgb + (1 - a) * bg) (Linear image colour space, sRGB training space).
 // Start t = AABB entry advanced by a random fraction of a step (:817-821).
 __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step,
-	int random_bg, float bg_r, float bg_g, float bg_b, float* __restrict__ ray_o, float* __restrict__ ray_d, float* __restrict__ ray_t,
+	int random_bg, int srgb_space, float bg_r, float bg_g, float bg_b, float* __restrict__ ray_o, float* __restrict__ ray_d, float* __restrict__ ray_t,
 	float* __restrict__ ray_target, float* __restrict__ ray_bg) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_rays) return;
@@ -97,7 +97,8 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 	#pragma unroll
 	for (int k = 0; k < 3; ++k) {
 		const float texc = k == 0 ? tex.x : (k == 1 ? tex.y : tex.z);
-		ray_target[3 * i + k] = linear_to_srgb(texc * tex.w + (1.0f - tex.w) * bg[k]);
+		// :1023-1037: linear images are composited over the background, then taken to sRGB; sRGB (byte) images are blended in sRGB
+		ray_target[3 * i + k] = srgb_space ? linear_to_srgb(texc) * tex.w + (1.0f - tex.w) * linear_to_srgb(bg[k]) : linear_to_srgb(texc * tex.w + (1.0f - tex.w) * bg[k]);
 		ray_bg[3 * i + k] = linear_to_srgb(bg[k]);
 	}
 }
@@ -590,6 +591,7 @@ void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, in
 	t.n_images = n; t.img_w = w; t.img_h = h;
 	t.focal[0] = focal[0]; t.focal[1] = focal[1]; t.principal[0] = principal[0]; t.principal[1] = principal[1];
 	t.has_dataset = true;
+	t.srgb_space = 0;
 }
 
 void train_init(hn_context* ctx, uint32_t seed) {
@@ -633,7 +635,7 @@ void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
 	FrameArgs a = train_frame_args(ctx);
 	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
 	const float* bg = ctx->opt.background_color;
-	train_raygen_kernel<<<blocks(n_rays), 256, 0, s>>>(D, a, n_rays, rank * n_rays, n_rays * world, t.seed, t.step, c.random_bg, bg[0], bg[1], bg[2],
+	train_raygen_kernel<<<blocks(n_rays), 256, 0, s>>>(D, a, n_rays, rank * n_rays, n_rays * world, t.seed, t.step, c.random_bg, t.srgb_space, bg[0], bg[1], bg[2],
 		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p);
 	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr);
 	float loss = 0.f;

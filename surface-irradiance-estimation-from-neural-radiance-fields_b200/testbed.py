@@ -68,7 +68,7 @@ EXPORTS = [
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
-    "hn_get_density_grid",
+    "hn_get_density_grid", "hn_load_training_data",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -113,6 +113,7 @@ _lib.hn_train_apply.argtypes = [C.c_void_p, C.c_float]
 _lib.hn_train_step.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_float)]
 _lib.hn_get_train_stats.argtypes = [C.c_void_p, C.POINTER(TrainStats)]
 _lib.hn_op_train_gradients.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5 + [C.c_int, C.c_float, C.POINTER(C.c_float), C.c_void_p, C.c_void_p]
+_lib.hn_load_training_data.argtypes = [C.c_void_p, C.c_char_p]
 _lib.hn_update_density_grid.argtypes = [C.c_void_p, C.c_float, C.c_uint32, C.c_uint32]
 _lib.hn_mark_untrained_density_grid.argtypes = [C.c_void_p]
 _lib.hn_get_density_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
@@ -365,6 +366,10 @@ class Testbed:
         f = _f32(np.broadcast_to(np.asarray(focal_px, np.float32), (2,)).copy())
         pp = _f32(principal)
         self._check(_lib.hn_train_set_dataset(self._h, _ptr(im), im.shape[0], im.shape[2], im.shape[1], _ptr(cams), _ptr(f), _ptr(pp)))
+
+    def load_training_data(self, path: str):
+        """pyngp Testbed.load_training_data (src/python_api.cu:409): transforms.json (or its folder) with PNG frames."""
+        self._check(_lib.hn_load_training_data(self._h, path.encode()))
 
     def reset_trainer(self, seed: int = 1337):
         self._check(_lib.hn_train_init(self._h, seed))

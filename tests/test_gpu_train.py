@@ -217,3 +217,79 @@ def test_snapshot_with_optimizer_state_round_trip(hn, root):
     resumed = [tb2.train(1) for _ in range(10)]
     assert tb2.training_step == 50 and np.isfinite(resumed).all()
     assert np.mean(resumed) < 2.0 * last + 1e-3
+
+
+def _write_png(path, rgba8, filter_mode):
+    """Minimal PNG writer (RGBA8, non-interlaced); filter_mode None = per-row cycling through the five filter types."""
+    import struct
+    import zlib
+    h, w, _ = rgba8.shape
+    rows = rgba8.astype(np.int32).reshape(h, w * 4)
+    raw = bytearray()
+    prev = np.zeros(w * 4, np.int32)
+    for y in range(h):
+        cur = rows[y]
+        ft = (y % 5) if filter_mode is None else filter_mode
+        left = np.concatenate([np.zeros(4, np.int32), cur[:-4]])
+        upleft = np.concatenate([np.zeros(4, np.int32), prev[:-4]])
+        if ft == 0: pred = np.zeros_like(cur)
+        elif ft == 1: pred = left
+        elif ft == 2: pred = prev
+        elif ft == 3: pred = (left + prev) // 2
+        else:
+            p = left + prev - upleft
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - upleft)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, upleft))
+        raw.append(ft)
+        raw += ((cur - pred) % 256).astype(np.uint8).tobytes()
+        prev = cur
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xffffffff)
+    comp = zlib.compress(bytes(raw), 6)
+    half = len(comp) // 2   # two IDAT chunks: the reader has to concatenate them
+    open(path, "wb").write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6, 0, 0, 0)) + chunk(b"IDAT", comp[:half]) +
+                           chunk(b"IDAT", comp[half:]) + chunk(b"IEND", b""))
+
+
+def test_load_training_data_transforms_json_png(hn, root, tmp_path):
+    """transforms.json + PNG frames -> the same training set as the in-memory path (cameras through
+    nerf_matrix_to_ngp, focal from camera_angle_x, sRGB bytes with straight alpha), checked through the first step's loss."""
+    import json
+    n, res = 6, 40
+    imgs, cams, focal = hn.synthetic.sphere_dataset(n, res)
+    srgb = np.where(imgs[..., :3] < 0.0031308, 12.92 * imgs[..., :3], 1.055 * np.power(np.maximum(imgs[..., :3], 1e-12), 1 / 2.4) - 0.055)
+    rgba8 = np.concatenate([np.round(np.clip(srgb, 0, 1) * 255), np.round(imgs[..., 3:4] * 255)], -1).astype(np.uint8)
+    frames = []
+    for i in range(n):
+        _write_png(str(tmp_path / f"r_{i}.png"), rgba8[i], None if i % 2 == 0 else i % 5)
+        c = cams[i].reshape(4, 3).astype(np.float64)                   # ngp columns {right, down, forward, pos}
+        col = np.stack([c[:, 2], c[:, 0], c[:, 1]], 1)                  # undo the axis cycle: old[c][0] = new[c][2], old[c][1] = new[c][0], old[c][2] = new[c][1]
+        col[1] *= -1; col[2] *= -1
+        col[3] = (col[3] - 0.5) / 0.33
+        m = np.eye(4); m[:3, :4] = col.T
+        frames.append({"file_path": f"r_{i}", "transform_matrix": m.tolist()})
+    meta = {"camera_angle_x": float(2 * np.arctan(0.5 * res / focal)), "aabb_scale": 1, "frames": frames}
+    (tmp_path / "transforms.json").write_text(json.dumps(meta))
+
+    def first_loss(loader):
+        tb, _, _ = nerf_setup(hn, root, 0.3)
+        tb.set_option("train_auto_grid", 0.0)
+        loader(tb)
+        tb.reset_trainer(5)
+        return tb.train_accumulate(1024), tb
+
+    # the byte path, and the float path fed with the very same quantised pixels (decoded like read_rgba does)
+    l_png, tb_png = first_loss(lambda tb: tb.load_training_data(str(tmp_path)))
+    lin = np.where(rgba8[..., :3] / 255.0 <= 0.04045, rgba8[..., :3] / 255.0 / 12.92, np.power((rgba8[..., :3] / 255.0 + 0.055) / 1.055, 2.4))
+    q = np.concatenate([lin, rgba8[..., 3:4] / 255.0], -1).astype(f32)
+
+    def float_loader(tb):
+        tb.set_training_data(q, cams, focal)
+    l_f32, tb_f = first_loss(float_loader)
+    st = tb_png.train_stats()
+    assert st.n_samples_last == tb_f.train_stats().n_samples_last and st.n_samples_last > 10000   # same cameras -> same rays
+    # alpha is 0 or 1 in this set, so blending in sRGB (byte path) or in linear space (float path) gives the same targets
+    assert abs(l_png - l_f32) <= 2e-5 * max(abs(l_f32), 1e-6) + 1e-7, (l_png, l_f32)
+    with pytest.raises(RuntimeError):
+        tb_png.load_training_data(str(tmp_path / "missing"))

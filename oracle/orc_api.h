@@ -50,6 +50,8 @@ typedef struct {
 	// env_samples = K cosine-weighted light directions per mesh hit (0 = envmap is background only).
 	int32_t env_w, env_h, env_samples, env_pad;
 	const float* envmap;
+	// ERenderMode of the NeRF pass (common.h:58-72; 0 AO, 1 Shade, 6 Positions, 7 Depth, 9 Cost, 12 EncodingVis) and 1 / dataset scale
+	int32_t render_mode; float depth_scale;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----

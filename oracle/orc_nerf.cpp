@@ -603,6 +603,11 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 				float alpha = 1.f - std::exp(-network_to_density(h2f(out[3]), p.density_activation) * dtu);
 				float weight = alpha * T;
 				vec3 rgb = {network_to_rgb(h2f(out[0]), p.rgb_activation), network_to_rgb(h2f(out[1]), p.rgb_activation), network_to_rgb(h2f(out[2]), p.rgb_activation)};
+				// :686-702 visualisation modes replace the sample colour
+				if (p.render_mode == 6) rgb = (pos - 0.5f) / 2.0f + 0.5f;
+				else if (p.render_mode == 12) rgb = wp;
+				else if (p.render_mode == 7) { float z = dot(cam_fwd, pos - r.o) * p.depth_scale; rgb = {z, z, z}; }
+				else if (p.render_mode == 0) rgb = {alpha, alpha, alpha};
 				rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
 				if (weight > max_weight) { max_weight = weight; local_depth = dot(cam_fwd, pos - cam_pos); }
 				if (rgba.w > (1.0f - p.min_transmittance)) {
@@ -617,7 +622,8 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			if (!(rgba.w > 0.001f)) continue;                    // compact_kernel_nerf :1419
 			if (depth_test && !p.depth_merge_clip && local_depth > depth[idx]) continue; // geometry :1843-1846
 			vec4 tmp = rgba;
-			if (!p.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+			if (p.render_mode == 9) { float col = (float)n / 128.0f; tmp = {col, col, col, 1.0f}; } // shade_kernel_nerf :1381-1383
+			if (!p.linear_colors && p.render_mode >= 1 && p.render_mode <= 4) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); } // :1391-1394
 			float* fb = frame + 4 * (size_t)idx;
 			float ia = 1.0f - tmp.w;
 			fb[0] = tmp.x + fb[0] * ia; fb[1] = tmp.y + fb[1] * ia; fb[2] = tmp.z + fb[2] * ia; fb[3] = tmp.w + fb[3] * ia;

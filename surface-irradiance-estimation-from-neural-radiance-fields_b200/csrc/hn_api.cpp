@@ -190,7 +190,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"render_aabb", {o.render_aabb, 6, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
-		{"linear_colors", {&o.linear_colors, 1, true}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
+		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
 		{"sun_dir", {o.sun_dir, 3, false}}, {"up_dir", {o.up_dir, 3, false}}, {"floor_enable", {&o.floor_enable, 1, true}},
 		{"brdf", {o.brdf, 13, false}}, {"compat_nearest_aabb_only", {&o.compat_nearest_aabb_only, 1, true}},
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
@@ -291,6 +291,7 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	a.max_mip = (uint32_t)o.max_cascade; a.cone_angle = o.cone_angle_constant; a.min_transmittance = o.min_transmittance;
 	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
 	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;
+	a.render_mode = o.render_mode; a.depth_scale = o.depth_scale;
 	a.rank = ctx->rank; a.world = ctx->world; a.tile_w = ctx->tile_w; a.tile_h = ctx->tile_h;
 	std::memcpy(a.mesh_aabb, o.mesh_aabb, 24);
 	std::memcpy(a.sun, o.sun_dir, 12); std::memcpy(a.up, o.up_dir, 12);
@@ -471,6 +472,11 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 	if (ctx->opt.render_nerf && ctx->has_net) {
 		need(ctx->has_params, "network parameters not set");
 		need(ctx->has_bitfield, "occupancy grid not set");
+		{
+			const int m = ctx->opt.render_mode;
+			need(m == 0 || (m >= 1 && m <= 4) || m == 6 || m == 7 || m == 9 || m == 12, "render_mode: AO, Shade, Positions, Depth, Cost and EncodingVis are built; Normals, Distortion and Slice are not");
+			need((m >= 1 && m <= 4) || (ctx->opt.composite_impl == 1 && !ctx->opt.fuse_composite) || (ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite), "visualisation render modes need composite_impl 1");
+		}
 		ensure_rays(ctx, n_px);
 		uint32_t* cnt = ctx->counters.p;
 		HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));

@@ -199,6 +199,7 @@ CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_
 	}
 	c.min_transmittance = fa.min_transmittance; c.rgb_act = fa.rgb_act; c.density_act = fa.density_act; c.linear_colors = fa.linear_colors;
 	c.depth_test = fa.depth_test; c.depth_clip = fa.depth_clip;
+	c.render_mode = fa.render_mode; c.depth_scale = fa.depth_scale;
 	c.rays = rays; c.frame = frame; c.depth_buffer = depth_buffer; c.survive = survive; c.counters = counters;
 	return c;
 }

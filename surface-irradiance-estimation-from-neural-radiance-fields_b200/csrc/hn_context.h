@@ -53,6 +53,8 @@ struct Options {
 	int rgb_activation = 2;                     // Logistic
 	int density_activation = 3;                 // Exponential
 	int linear_colors = 0;
+	int render_mode = 1;                        // ERenderMode::Shade (common.h:58-72)
+	float depth_scale = 1.0f / 0.33f;           // 1 / nerf.training.dataset.scale (NERF_SCALE)
 	int dda_iter_cap = 0;
 	float sun_dir[3] = {0.57735026919f, 0.57735026919f, 0.57735026919f};
 	float up_dir[3] = {0, 1, 0};

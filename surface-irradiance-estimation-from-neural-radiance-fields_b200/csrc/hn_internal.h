@@ -57,6 +57,8 @@ struct FrameArgs {
 	float min_transmittance;
 	int rgb_act, density_act, linear_colors, dda_iter_cap;
 	int depth_test, depth_clip;
+	int render_mode;       // ERenderMode of the NeRF pass (1 = Shade)
+	float depth_scale;
 	int rank, world, tile_w, tile_h;
 	// mesh pass
 	float mesh_aabb[6];

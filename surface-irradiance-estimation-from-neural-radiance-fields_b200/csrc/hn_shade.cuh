@@ -34,6 +34,8 @@ struct CompArgs {
 	float cam_fwd[3], cam_pos[3];
 	float min_transmittance;
 	int rgb_act, density_act, linear_colors, depth_test, depth_clip;
+	int render_mode;              // ERenderMode (common.h:58-72): 0 AO, 1..4 Shade, 6 Positions, 7 Depth, 9 Cost, 12 EncodingVis
+	float depth_scale;            // 1 / dataset scale (src/testbed_nerf.cu:2121)
 	RaySoA rays;
 	float4* frame;
 	float* depth_buffer;
@@ -48,7 +50,7 @@ struct CompArgs {
 // rounded to fp16 first, so the numbers equal the unfused path's. Lane 0 owns the ray state. Returns samples composited.
 // The ray state and the lane's sample are fetched by composite_prefetch() right after the last layer has been issued,
 // so their global-memory latency hides behind that MMA round instead of extending the tile.
-struct RayPre { uint32_t r, n_steps; float4 rgba; float depth, max_weight; float4 s; };
+struct RayPre { uint32_t r, n_steps; float4 rgba; float depth, max_weight; float4 s; float4 o_t; };
 __device__ __forceinline__ RayPre composite_prefetch(const CompArgs& a, uint32_t chunk, uint32_t count, int lane) {
 	RayPre p;
 	p.r = a.alive_list[chunk];
@@ -56,6 +58,7 @@ __device__ __forceinline__ RayPre composite_prefetch(const CompArgs& a, uint32_t
 	p.depth = a.rays.depth[p.r];
 	p.max_weight = a.rays.d_mw[p.r].w;
 	p.n_steps = a.rays.n_steps[p.r];
+	p.o_t = a.render_mode == 7 ? a.rays.o_t[p.r] : make_float4(0.f, 0.f, 0.f, 0.f);
 	p.s = make_float4(0.f, 0.f, 0.f, 0.f);
 	if ((uint32_t)lane < count) p.s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
 	return p;
@@ -80,6 +83,11 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 			alpha = 1.f - __expf(-sigma * s.w);
 			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
 			zview = a.cam_fwd[0] * (s.x - a.cam_pos[0]) + a.cam_fwd[1] * (s.y - a.cam_pos[1]) + a.cam_fwd[2] * (s.z - a.cam_pos[2]);
+			// per-sample colour of the visualisation modes (composite_kernel_nerf, src/testbed_nerf.cu:686-702)
+			if (a.render_mode == 6) { cr = (s.x - 0.5f) / 2.0f + 0.5f; cg = (s.y - 0.5f) / 2.0f + 0.5f; cb = (s.z - 0.5f) / 2.0f + 0.5f; }
+			else if (a.render_mode == 12) { cr = (s.x - a.train_lo[0]) / a.train_diag[0]; cg = (s.y - a.train_lo[1]) / a.train_diag[1]; cb = (s.z - a.train_lo[2]) / a.train_diag[2]; }
+			else if (a.render_mode == 7) { cr = cg = cb = (a.cam_fwd[0] * (s.x - pre.o_t.x) + a.cam_fwd[1] * (s.y - pre.o_t.y) + a.cam_fwd[2] * (s.z - pre.o_t.z)) * a.depth_scale; }
+			else if (a.render_mode == 0) { cr = cg = cb = alpha; }
 		}
 		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
 		#pragma unroll
@@ -125,7 +133,9 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 	// ray (three powf, ~50 instructions each) is spread over lanes 0..2 so the warp issues it once instead of three times
 	const bool finished = !alive_next && rgba.w > 0.001f; // compact_kernel_nerf keeps finished rays with alpha > 0.001
 	float4 tmp = rgba;
-	if (finished && !a.linear_colors) {
+	const bool shade_mode = a.render_mode >= 1 && a.render_mode <= 4; // only Shade (and Slice) accumulate in linear colours (shade_kernel_nerf :1391-1394)
+	if (a.render_mode == 9) { const float col = (float)n_steps / 128.0f; tmp = make_float4(col, col, col, 1.0f); } // Cost (:1381-1383)
+	if (finished && !a.linear_colors && shade_mode) {
 		float c = lane == 0 ? rgba.x : (lane == 1 ? rgba.y : rgba.z);
 		c = srgb_to_linear(c);
 		tmp.x = __shfl_sync(0xffffffffu, c, 0); tmp.y = __shfl_sync(0xffffffffu, c, 1); tmp.z = __shfl_sync(0xffffffffu, c, 2);

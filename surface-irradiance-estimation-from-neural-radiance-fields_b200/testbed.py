@@ -8,6 +8,7 @@ computing call fails without a B200.
 from __future__ import annotations
 
 import ctypes as C
+import enum
 import math
 import os
 
@@ -147,6 +148,21 @@ def camera_to_cols(m):
     return np.ascontiguousarray(m.T).reshape(12)
 
 
+class RenderMode(enum.IntEnum):
+    AO = 0
+    Shade = 1
+    ShadeNerf = 2
+    ShadeEnvMap = 3
+    ShadeGridEnvMap = 4
+    Normals = 5
+    Positions = 6
+    Depth = 7
+    Distortion = 8
+    Cost = 9
+    Slice = 10
+    EncodingVis = 12
+
+
 class Testbed:
     """Render-path subset of ``pyngp.Testbed``."""
 
@@ -272,6 +288,9 @@ class Testbed:
     exposure = property(lambda s: s.get_option("exposure"), lambda s, v: s.set_option("exposure", v))
     sun_dir = property(lambda s: s.get_option("sun_dir", 3), lambda s, v: s.set_option("sun_dir", v))
     up_dir = property(lambda s: s.get_option("up_dir", 3), lambda s, v: s.set_option("up_dir", v))
+    # ERenderMode (include/neural-graphics-primitives/common.h:58-72, pyngp RenderMode); the NeRF pass builds AO, Shade*, Positions,
+    # Depth, Cost and EncodingVis, the others raise at render time
+    render_mode = property(lambda s: RenderMode(int(s.get_option("render_mode"))), lambda s, v: s.set_option("render_mode", float(int(v))))
     background_color = property(lambda s: s.get_option("background_color", 4), lambda s, v: s.set_option("background_color", v))
 
     def set_nerf_camera_matrix(self, m):

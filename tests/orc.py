@@ -38,7 +38,8 @@ class RenderParams(C.Structure):
                 ("min_transmittance", f32), ("rgb_activation", i32), ("density_activation", i32), ("linear_colors", i32),
                 ("dda_iter_cap", i32), ("mesh_aabb", f32 * 6), ("sun_dir", f32 * 3), ("up_dir", f32 * 3), ("floor_y", f32),
                 ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32),
-                ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p)]
+                ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p),
+                ("render_mode", i32), ("depth_scale", f32)]
 
 
 def P(a):
@@ -104,7 +105,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   render_aabb=(0, 0, 0, 1, 1, 1), train_aabb=(0, 0, 0, 1, 1, 1), max_mip=0, cone=0.0, min_transmittance=0.01,
                   rgb_act=2, density_act=3, linear_colors=False, dda_iter_cap=0, mesh_aabb=(0, 0, 0, 1, 1, 1),
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
-                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0) -> RenderParams:
+                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -133,6 +134,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.brdf[:] = list(brdf) if brdf is not None else DEFAULT_BRDF
     p.compat_nearest_aabb_only, p.depth_merge_clip = int(compat), int(clip)
     p.n_threads = n_threads if n_threads is not None else (os.cpu_count() or 1)
+    p.render_mode, p.depth_scale = int(render_mode), float(depth_scale)
     if envmap is not None:
         env = np.ascontiguousarray(envmap, np.float32)
         assert env.ndim == 3 and env.shape[2] == 4

@@ -185,3 +185,38 @@ def test_full_size_properties(base, hn):
     q = tb.render(w // 4, h // 4, 1, True)
     frac_full, frac_q = mask.mean(), (q[..., :3].sum(-1) > 0).mean()
     assert abs(frac_full - frac_q) < 0.01
+
+
+@pytest.mark.parametrize("mode,name", [(0, "AO"), (6, "Positions"), (7, "Depth"), (9, "Cost"), (12, "EncodingVis")])
+def test_visualisation_render_modes(base, hn, orc, mode, name):
+    """ERenderMode (common.h:58-72) other than Shade: the per-sample colour is replaced in compositing
+    (src/testbed_nerf.cu:686-702), Cost paints n_steps/128 at the final blend (:1381-1383), and only Shade converts
+    sRGB -> linear. Same tolerance as the shaded frame; Cost is an integer count / 128 and must match exactly."""
+    tb, _, grid, blob = base
+    cam = hn.synthetic.look_at_camera((1.4, 1.2, 1.6), (0.5, 0.5, 0.5))
+    tb.set_camera_cols(cam)
+    tb.set_option("render_mode", float(mode))
+    tb.set_option("depth_scale", 0.4)
+    try:
+        img = tb.render(160, 120, 1, True)
+        ref, _, _ = orc.render_reference_frame(tb, blob, grid, 1, [], cam, 160, 120, render_mode=mode, depth_scale=0.4)
+    finally:
+        tb.set_option("render_mode", 1.0)
+        tb.set_option("depth_scale", 1.0 / 0.33)
+    shaded = tb.render(160, 120, 1, True)
+    assert np.abs(img[..., :3] - shaded[..., :3]).max() > 0.05, "mode did not change the picture"
+    if mode == 9:
+        assert np.array_equal(img, ref)
+    else:
+        assert np.abs(img - ref).max() <= 1e-2 and psnr(img, ref) >= 50.0, (name, np.abs(img - ref).max())
+
+
+def test_unbuilt_render_modes_fail_loudly(base, hn):
+    tb, _, _, _ = base
+    for mode in (5, 8, 10):  # Normals (needs input gradients), Distortion, Slice
+        tb.set_option("render_mode", float(mode))
+        try:
+            with pytest.raises(RuntimeError):
+                tb.render(32, 32, 1, True)
+        finally:
+            tb.set_option("render_mode", 1.0)

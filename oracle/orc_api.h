@@ -52,6 +52,10 @@ typedef struct {
 	const float* envmap;
 	// ERenderMode of the NeRF pass (common.h:58-72; 0 AO, 1 Shade, 6 Positions, 7 Depth, 9 Cost, 12 EncodingVis) and 1 / dataset scale
 	int32_t render_mode; float depth_scale;
+	// camera model of uv_to_ray (common_device.cuh:416-483): ELensMode + params (NeRF ray init only), depth of field, parallax shift
+	int32_t lens_mode; float lens_params[7];
+	float aperture_size, focus_z;
+	float parallax_shift[3];
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----
@@ -66,6 +70,8 @@ float orc_calc_dt(float t, float cone_angle);
 float orc_srgb_to_linear(float v);
 
 // ---- a-16 sampling helpers (random_val.cuh:62-72,130-185; pinned against oracle/_ref) and the envmap lookup ----
+// uv_to_ray with the lens / depth-of-field / parallax fields of p (direction not normalised); returns 0 for an invalid ray
+int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]);
 void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]);
 void orc_dir_to_spherical_unorm(const float d[3], float out[2]);
 void orc_cosine_hemisphere(const float u[2], float out[3]);

@@ -10,9 +10,9 @@
 namespace orc {
 
 // defined in orc_nerf.cpp
-Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y);
+Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y, bool* valid);
 vec2 ld_random_pixel_offset(uint32_t spp);
-Ray uv_to_ray_pinhole(vec2 uv, int w, int h, vec2 focal, const cam_t& cam, vec2 screen_center, float near_distance);
+Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& cam, bool use_lens, bool* valid);
 struct Net;
 Net* net_new(const orc_net_config& c, const uint16_t* params);
 void net_delete(Net* n);
@@ -244,7 +244,7 @@ static void render_mesh(const orc_scene& s, const orc_render_params& p, float* f
 			// :488-579 init_rays_with_payload_kernel_mesh_geometry (pixel_to_ray: no rolling shutter, camera_matrix as is)
 			vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
 			vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
-			Ray ray = uv_to_ray_pinhole(uv, p.width, p.height, {p.focal[0], p.focal[1]}, cam, {p.screen_center[0], p.screen_center[1]}, p.near_distance);
+			Ray ray = uv_to_ray(p, p.spp, uv, cam, false, nullptr); // no Lens on this ray init (:520-536); parallax shift + depth of field apply
 			depth[idx] = MAX_DEPTH;
 			ray.d = normalize(ray.d);
 			float t0 = std::max(aabb.ray_intersect(ray.o, ray.d).x, 0.0f);

@@ -133,24 +133,107 @@ static cam_t camera_slerp(const cam_t& a, const cam_t& b, float t) {
 	return r;
 }
 
-// common_device.cuh:416-483 (pinhole lens, no foveation / distortion / DoF / parallax) — direction not normalised.
-Ray uv_to_ray_pinhole(vec2 uv, int w, int h, vec2 focal, const cam_t& cam, vec2 screen_center, float near_distance) {
-	vec3 dir = {
-		(uv.x - screen_center.x) * (float)w / focal.x,
-		(uv.y - screen_center.y) * (float)h / focal.y,
-		1.0f,
-	};
-	vec3 head_pos = {0.0f, 0.0f, 0.0f};
-	dir = dir - head_pos * 0.0f;
+static constexpr float PI_F = 3.14159265358979323846f;
+// common_device.cuh:249-321: OpenCV / OpenCV-fisheye distortion deltas and their Newton inversion
+static void opencv_distortion_delta(const float* k, float u, float v, float* du, float* dv) {
+	float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+	float radial = k[0] * r2 + k[1] * r2 * r2;
+	*du = u * radial + 2.0f * k[2] * uv + k[3] * (r2 + 2.0f * u2);
+	*dv = v * radial + 2.0f * k[3] * uv + k[2] * (r2 + 2.0f * v2);
+}
+static void fisheye_distortion_delta(const float* k, float u, float v, float* du, float* dv) {
+	float r = std::sqrt(u * u + v * v);
+	if (r > (float)std::numeric_limits<double>::epsilon()) {
+		float theta = std::atan(r), theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+		float thetad = theta * (1.0f + k[0] * theta2 + k[1] * theta4 + k[2] * theta6 + k[3] * theta8);
+		*du = u * thetad / r - u;
+		*dv = v * thetad / r - v;
+	} else { *du = 0.0f; *dv = 0.0f; }
+}
+typedef void (*distortion_fn)(const float*, float, float, float*, float*);
+static void iterative_undistortion(const float* k, float* u, float* v, distortion_fn fn) {
+	const float x0 = *u, y0 = *v;
+	float x = x0, y = y0;
+	for (uint32_t i = 0; i < 100; ++i) {
+		float step0 = std::max(std::numeric_limits<float>::epsilon(), std::fabs(1e-6f * x));
+		float step1 = std::max(std::numeric_limits<float>::epsilon(), std::fabs(1e-6f * y));
+		float dx, dy, bx0, by0, fx0, fy0, bx1, by1, fx1, fy1;
+		fn(k, x, y, &dx, &dy); fn(k, x - step0, y, &bx0, &by0); fn(k, x + step0, y, &fx0, &fy0); fn(k, x, y - step1, &bx1, &by1); fn(k, x, y + step1, &fx1, &fy1);
+		float J00 = 1.0f + (fx0 - bx0) / (2.0f * step0), J10 = (fx1 - bx1) / (2.0f * step1);
+		float J01 = (fy0 - by0) / (2.0f * step0), J11 = 1.0f + (fy1 - by1) / (2.0f * step1);
+		float det = J00 * J11 - J01 * J10; // tcnn inverse = adjoint / determinant (vec.h:803-808,861-863)
+		float I00 = J11 / det, I01 = -J01 / det, I10 = -J10 / det, I11 = J00 / det;
+		float rx = x + dx - x0, ry = y + dy - y0;
+		float sx = 0.0f, sy = 0.0f;
+		sx += I00 * rx; sy += I01 * rx;
+		sx += I10 * ry; sy += I11 * ry;
+		x -= sx; y -= sy;
+		if (sx * sx + sy * sy < 1e-10f) break;
+	}
+	*u = x; *v = y;
+}
+// random_val.cuh:112-128
+static vec2 square2disk_shirley(vec2 sq) {
+	float phi, r, a = sq.x, b = sq.y;
+	if (a * a > b * b) { r = a; phi = (PI_F / 4.0f) * (b / a); }
+	else { r = b; phi = (PI_F / 2.0f) - (PI_F / 4.0f) * (a / b); }
+	return {r * std::cos(phi), r * std::sin(phi)};
+}
+
+// common_device.cuh:416-483 uv_to_ray without foveation / hidden-area mask / distortion grid (VR only) — direction not
+// normalised; valid = false for an f-theta pixel outside the image circle. lens_mode follows ELensMode (common.h:223-230).
+Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& cam, bool use_lens, bool* valid) {
+	const int w = p.width, h = p.height;
+	const vec2 focal = {p.focal[0], p.focal[1]}, sc = {p.screen_center[0], p.screen_center[1]};
+	const int mode = use_lens ? p.lens_mode : 0;
+	const float* lp = p.lens_params;
+	if (valid) *valid = true;
+	vec3 dir;
+	if (mode == 2) { // f_theta_undistortion :360-374
+		float xpix = (uv.x - sc.x) * lp[5], ypix = (uv.y - sc.y) * lp[6];
+		float norm = std::sqrt(xpix * xpix + ypix * ypix);
+		float alpha = lp[0] + norm * (lp[1] + norm * (lp[2] + norm * (lp[3] + norm * lp[4])));
+		float sa = std::sin(alpha), ca = std::cos(alpha);
+		if (ca <= std::numeric_limits<float>::min() || norm == 0.f) { if (valid) *valid = false; return {{0, 0, 0}, {0, 0, 0}}; }
+		sa *= 1.f / norm;
+		dir = {sa * xpix, sa * ypix, ca};
+		if (dir.x == 0.0f && dir.y == 0.0f && dir.z == 0.0f) { if (valid) *valid = false; return {{0, 0, 0}, {0, 0, 0}}; }
+	} else if (mode == 3) { // latlong_to_dir :376-383
+		float theta = (uv.y - 0.5f) * PI_F, phi = (uv.x - 0.5f) * PI_F * 2.0f;
+		float st = std::sin(theta), ct = std::cos(theta), sp = std::sin(phi), cp = std::cos(phi);
+		dir = {sp * ct, st, cp * ct};
+	} else if (mode == 5) { // equirectangular_to_dir :385-392
+		float ct = (uv.y - 0.5f) * 2.0f, st = std::sqrt(std::max(1.0f - ct * ct, 0.0f)), phi = (uv.x - 0.5f) * PI_F * 2.0f;
+		float sp = std::sin(phi), cp = std::cos(phi);
+		dir = {sp * st, ct, cp * st};
+	} else {
+		dir = {(uv.x - sc.x) * (float)w / focal.x, (uv.y - sc.y) * (float)h / focal.y, 1.0f};
+		if (mode == 1) iterative_undistortion(lp, &dir.x, &dir.y, opencv_distortion_delta);
+		else if (mode == 4) iterative_undistortion(lp, &dir.x, &dir.y, fisheye_distortion_delta);
+	}
+	vec3 head_pos = {p.parallax_shift[0], p.parallax_shift[1], 0.0f};
+	dir = dir - head_pos * p.parallax_shift[2];
 	mat3 m = {{cam.c[0], cam.c[1], cam.c[2]}};
 	dir = mul(m, dir);
 	vec3 origin = mul(m, head_pos) + cam.c[3];
-	origin = origin + dir * near_distance;
+	if (p.aperture_size != 0.0f) {
+		vec3 lookat = origin + dir * p.focus_z;
+		int px = (int)(uv.x * (float)w), py = (int)(uv.y * (float)h);
+		vec2 rnd = ld_random_val_2d(spp, (uint32_t)px * 19349663u + (uint32_t)py * 96925573u);
+		vec2 disk = square2disk_shirley({rnd.x * 2.0f - 1.0f, rnd.y * 2.0f - 1.0f});
+		float bx = p.aperture_size * disk.x, by = p.aperture_size * disk.y;
+		vec3 sh = {0.0f, 0.0f, 0.0f};
+		sh.x += cam.c[0].x * bx; sh.y += cam.c[0].y * bx; sh.z += cam.c[0].z * bx;
+		sh.x += cam.c[1].x * by; sh.y += cam.c[1].y * by; sh.z += cam.c[1].z * by;
+		origin = origin + sh;
+		dir = (lookat - origin) / p.focus_z;
+	}
+	origin = origin + dir * p.near_distance;
 	return {origin, dir};
 }
 
 // testbed_nerf.cu:1428-1476: uv + per-pixel rolling-shutter camera
-Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y) {
+Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y, bool* valid) {
 	uint32_t idx = x + (uint32_t)p.width * y;
 	vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
 	vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
@@ -158,7 +241,7 @@ Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y) {
 	const float* rs = p.rolling_shutter;
 	float pixel_t = rs[0] + rs[1] * uv.x + rs[2] * uv.y + rs[3] * mb;
 	cam_t cam = camera_slerp(cam_from(p.cam0), cam_from(p.cam1), pixel_t);
-	return uv_to_ray_pinhole(uv, p.width, p.height, {p.focal[0], p.focal[1]}, cam, {p.screen_center[0], p.screen_center[1]}, p.near_distance);
+	return uv_to_ray(p, p.spp, uv, cam, true, valid);
 }
 
 // ---------------------------------------------------------------- nerf_device.cuh:316-534 (occupancy DDA)
@@ -466,7 +549,6 @@ static float unwarp_dt(float dt) {
 float srgb_to_linear(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
 
 // ---------------------------------------------------------------- a-16: random_val.cuh:62-72,130-185, envmap.cuh:24-50
-static constexpr float PI_F = 3.14159265358979323846f;
 vec2 dir_to_spherical_unorm(vec3 d) {
 	float cos_theta = std::fmin(std::fmax(d.z, -1.0f), 1.0f);
 	float theta = std::acos(cos_theta);
@@ -529,8 +611,10 @@ struct RayState { vec3 o, d; float t; bool alive; };
 RayState init_ray(const orc_render_params& p, const uint8_t* bits, uint32_t x, uint32_t y, float* depth_px) {
 	RayState r = {};
 	uint32_t idx = x + (uint32_t)p.width * y;
-	Ray ray = pixel_ray(p, x, y);
+	bool valid = true;
+	Ray ray = pixel_ray(p, x, y, &valid);
 	if (depth_px && *depth_px < 0.01f) *depth_px = MAX_DEPTH; // :1490-1493 (keeps a mesh depth already present)
+	if (!valid) { r.o = ray.o; r.d = {0.0f, 0.0f, 0.0f}; r.alive = false; return r; } // :1494-1498
 	ray.d = normalize(ray.d);
 	BoundingBox render_aabb = bb_from(p.render_aabb);
 	float t = std::fmax(render_aabb.ray_intersect(ray.o, ray.d).x, 0.0f) + 1e-6f;
@@ -569,7 +653,7 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			if (n_steps_out) n_steps_out[idx] = 0;
 			RayState r = init_ray(p, bits, x, y, &depth[idx]);
 			// :1526-1528 envmap -> frame buffer for every valid ray; in hybrid frames only where the mesh pass left nothing
-			if (p.envmap && !(depth_test && depth[idx] < MAX_DEPTH)) {
+			if (p.envmap && (r.d.x != 0.0f || r.d.y != 0.0f || r.d.z != 0.0f) && !(depth_test && depth[idx] < MAX_DEPTH)) { // invalid rays return before this (:1494-1498)
 				vec4 e = read_envmap(p.envmap, p.env_w, p.env_h, r.d);
 				float* fb = frame + 4 * (size_t)idx;
 				fb[0] = e.x; fb[1] = e.y; fb[2] = e.z; fb[3] = e.w;
@@ -690,6 +774,12 @@ float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const
 float orc_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
 float orc_srgb_to_linear(float v) { return srgb_to_linear(v); }
 
+int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]) {
+	bool valid = true;
+	Ray r = uv_to_ray(*p, spp, {uv[0], uv[1]}, cam_from(p->cam0), use_lens != 0, &valid);
+	out_o[0] = r.o.x; out_o[1] = r.o.y; out_o[2] = r.o.z; out_d[0] = r.d.x; out_d[1] = r.d.y; out_d[2] = r.d.z;
+	return valid ? 1 : 0;
+}
 void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 void orc_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm({d[0], d[1], d[2]}); out[0] = v.x; out[1] = v.y; }
 void orc_cosine_hemisphere(const float u[2], float out[3]) { vec3 v = cosine_hemisphere({u[0], u[1]}); out[0] = v.x; out[1] = v.y; out[2] = v.z; }

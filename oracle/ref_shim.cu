@@ -81,6 +81,21 @@ float ref_start_t(uint32_t spp, uint32_t idx, const float o[3], const float d[3]
 	return if_unoccupied_advance_to_next_occupied_voxel(t, cone_angle, ray, idir, bitfield, 0, max_mip, b);
 }
 
+// uv_to_ray (common_device.cuh:416-483) with a Lens, parallax shift and depth of field; foveation / masks / distortion grid default.
+int32_t ref_uv_to_ray_lens(uint32_t spp, const float uv[2], int32_t w, int32_t h, const float focal[2], const float cam[12], const float screen_center[2],
+	const float parallax[3], float near_distance, float focus_z, float aperture_size, int32_t lens_mode, const float lens_params[7], float out_o[3], float out_d[3]) {
+	mat4x3 c;
+	for (int i = 0; i < 4; ++i) c[i] = vec3(cam[3*i], cam[3*i+1], cam[3*i+2]);
+	Lens lens;
+	lens.mode = (ELensMode)lens_mode;
+	for (int i = 0; i < 7; ++i) lens.params[i] = lens_params[i];
+	Ray ray = uv_to_ray(spp, vec2(uv[0], uv[1]), ivec2(w, h), vec2(focal[0], focal[1]), c, vec2(screen_center[0], screen_center[1]),
+		vec3(parallax[0], parallax[1], parallax[2]), near_distance, focus_z, aperture_size, Foveation{}, Buffer2DView<const uint8_t>{}, lens);
+	out_o[0] = ray.o.x; out_o[1] = ray.o.y; out_o[2] = ray.o.z;
+	out_d[0] = ray.d.x; out_d[1] = ray.d.y; out_d[2] = ray.d.z;
+	return ray.is_valid() ? 1 : 0;
+}
+
 // a-16 sampling helpers (random_val.cuh:62-72,130-185), all NGP_HOST_DEVICE
 void ref_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 void ref_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm(vec3(d[0], d[1], d[2])); out[0] = v.x; out[1] = v.y; }

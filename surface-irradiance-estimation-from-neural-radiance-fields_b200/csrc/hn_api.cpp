@@ -187,6 +187,8 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 	Options& o = c->opt;
 	return {
 		{"snap_to_pixel_centers", {&o.snap_to_pixel_centers, 1, true}}, {"render_near_distance", {&o.near_distance, 1, false}},
+		{"lens_mode", {&o.lens_mode, 1, true}}, {"lens_params", {o.lens_params, 7, false}}, {"aperture_size", {&o.aperture_size, 1, false}},
+		{"focus_z", {&o.focus_z, 1, false}}, {"parallax_shift", {o.parallax_shift, 3, false}},
 		{"render_aabb", {o.render_aabb, 6, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
@@ -276,6 +278,10 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	}
 	ld_random_pixel_offset(o.snap_to_pixel_centers ? 0 : spp, a.pixel_offset);
 	a.near_distance = o.near_distance;
+	a.lens_mode = o.lens_mode;
+	for (int i = 0; i < 7; ++i) a.lens_params[i] = o.lens_params[i];
+	a.aperture_size = o.aperture_size; a.focus_z = o.focus_z;
+	for (int i = 0; i < 3; ++i) a.parallax_shift[i] = o.parallax_shift[i];
 	std::memcpy(a.render_aabb, o.render_aabb, 24); std::memcpy(a.train_aabb, o.train_aabb, 24);
 	// world-space union of the set cells of mips 0..max_cascade, each inflated by half a cell of its mip
 	for (int k = 0; k < 3; ++k) { a.occ_aabb[k] = 1e30f; a.occ_aabb[3 + k] = -1e30f; }

@@ -45,6 +45,11 @@ struct Options {
 	// defaults follow testbed.h:852-1091 and nerf.h:150-186
 	int snap_to_pixel_centers = 0;
 	float near_distance = 0.0f;
+	int lens_mode = 0;                          // m_nerf.render_lens.mode when render_with_lens_distortion (ELensMode, common.h:223-230)
+	float lens_params[7] = {0, 0, 0, 0, 0, 0, 0};
+	float aperture_size = 0.0f;                 // m_aperture_size
+	float focus_z = 1.0f;                       // m_slice_plane_z + m_scale
+	float parallax_shift[3] = {0, 0, 0};        // m_parallax_shift
 	float render_aabb[6] = {0, 0, 0, 1, 1, 1};
 	float train_aabb[6] = {0, 0, 0, 1, 1, 1};   // m_geometry.nerfBoundingBox / m_aabb
 	int max_cascade = 0;

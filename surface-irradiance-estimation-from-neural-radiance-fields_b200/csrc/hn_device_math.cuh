@@ -122,8 +122,122 @@ __host__ __device__ __forceinline__ float2 hn_ld_random_val_2d(uint32_t index, u
 	return r;
 }
 
-// ---- a-16: environment map + light-direction sampling (random_val.cuh:62-72,130-185, envmap.cuh:24-50) ----
 #define HN_PI_F 3.14159265358979323846f
+// ---- camera models (common_device.cuh:249-483): lens undistortion, parallax shift, depth of field ----
+// ELensMode (common.h:223-230): 0 Perspective, 1 OpenCV, 2 FTheta, 3 LatLong, 4 OpenCVFisheye, 5 Equirectangular
+__device__ __forceinline__ void opencv_distortion_delta(const float* k, float u, float v, float* du, float* dv) {
+	const float u2 = u * u, uv = u * v, v2 = v * v, r2 = u2 + v2;
+	const float radial = k[0] * r2 + k[1] * r2 * r2;
+	*du = u * radial + 2.0f * k[2] * uv + k[3] * (r2 + 2.0f * u2);
+	*dv = v * radial + 2.0f * k[3] * uv + k[2] * (r2 + 2.0f * v2);
+}
+__device__ __forceinline__ void fisheye_distortion_delta(const float* k, float u, float v, float* du, float* dv) {
+	const float r = sqrtf(u * u + v * v);
+	if (r > (float)DBL_EPSILON) {
+		const float theta = atanf(r), theta2 = theta * theta, theta4 = theta2 * theta2, theta6 = theta4 * theta2, theta8 = theta4 * theta4;
+		const float thetad = theta * (1.0f + k[0] * theta2 + k[1] * theta4 + k[2] * theta6 + k[3] * theta8);
+		*du = u * thetad / r - u;
+		*dv = v * thetad / r - v;
+	} else { *du = 0.0f; *dv = 0.0f; }
+}
+// Newton iteration with central differences (iterative_lens_undistortion, common_device.cuh:281-321)
+template <bool FISHEYE>
+__device__ void iterative_undistortion(const float* k, float* u, float* v) {
+	const float x0 = *u, y0 = *v;
+	float x = x0, y = y0;
+	for (uint32_t i = 0; i < 100; ++i) {
+		const float step0 = fmaxf(FLT_EPSILON, fabsf(1e-6f * x)), step1 = fmaxf(FLT_EPSILON, fabsf(1e-6f * y));
+		float dx, dy, bx0, by0, fx0, fy0, bx1, by1, fx1, fy1;
+		if (FISHEYE) {
+			fisheye_distortion_delta(k, x, y, &dx, &dy); fisheye_distortion_delta(k, x - step0, y, &bx0, &by0); fisheye_distortion_delta(k, x + step0, y, &fx0, &fy0);
+			fisheye_distortion_delta(k, x, y - step1, &bx1, &by1); fisheye_distortion_delta(k, x, y + step1, &fx1, &fy1);
+		} else {
+			opencv_distortion_delta(k, x, y, &dx, &dy); opencv_distortion_delta(k, x - step0, y, &bx0, &by0); opencv_distortion_delta(k, x + step0, y, &fx0, &fy0);
+			opencv_distortion_delta(k, x, y - step1, &bx1, &by1); opencv_distortion_delta(k, x, y + step1, &fx1, &fy1);
+		}
+		// J is column-major: J[c][r]
+		const float J00 = 1.0f + (fx0 - bx0) / (2.0f * step0), J10 = (fx1 - bx1) / (2.0f * step1);
+		const float J01 = (fy0 - by0) / (2.0f * step0), J11 = 1.0f + (fy1 - by1) / (2.0f * step1);
+		const float det = J00 * J11 - J01 * J10;
+		const float I00 = J11 / det, I01 = -J01 / det, I10 = -J10 / det, I11 = J00 / det; // adjoint / determinant
+		const float rx = x + dx - x0, ry = y + dy - y0;
+		float sx = 0.0f, sy = 0.0f;
+		sx += I00 * rx; sy += I01 * rx;
+		sx += I10 * ry; sy += I11 * ry;
+		x -= sx; y -= sy;
+		if (sx * sx + sy * sy < 1e-10f) break;
+	}
+	*u = x; *v = y;
+}
+__device__ __forceinline__ float2 square2disk_shirley(float a, float b) { // random_val.cuh:112-128
+	float phi, r;
+	if (a * a > b * b) { r = a; phi = (HN_PI_F / 4.0f) * (b / a); }
+	else { r = b; phi = (HN_PI_F / 2.0f) - (HN_PI_F / 4.0f) * (a / b); }
+	float sp, cp;
+	sincosf(phi, &sp, &cp);
+	return make_float2(r * cp, r * sp);
+}
+// uv_to_ray (common_device.cuh:416-483) without foveation / hidden-area mask / distortion grid (VR only). c0..c2 = camera
+// rotation columns, pos = camera[3]. `use_lens` is false on the mesh pass (its ray init takes no Lens, geometry :520-536).
+// Returns false for an invalid ray (f-theta outside the image circle). The direction is NOT normalised.
+__device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, float u, float v, V3 c0, V3 c1, V3 c2, V3 pos, V3& origin, V3& dir) {
+	V3 d;
+	const int mode = use_lens ? a.lens_mode : 0;
+	if (mode == 2) {
+		const float xpix = (u - a.screen_center[0]) * a.lens_params[5], ypix = (v - a.screen_center[1]) * a.lens_params[6];
+		const float norm = sqrtf(xpix * xpix + ypix * ypix);
+		const float alpha = a.lens_params[0] + norm * (a.lens_params[1] + norm * (a.lens_params[2] + norm * (a.lens_params[3] + norm * a.lens_params[4])));
+		float sa, ca;
+		sincosf(alpha, &sa, &ca);
+		if (ca <= FLT_MIN || norm == 0.f) return false;
+		sa *= 1.f / norm;
+		d = mk(sa * xpix, sa * ypix, ca);
+		if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) return false;
+	} else if (mode == 3) {
+		const float theta = (v - 0.5f) * HN_PI_F, phi = (u - 0.5f) * HN_PI_F * 2.0f;
+		float sp, cp, st, ct;
+		sincosf(theta, &st, &ct); sincosf(phi, &sp, &cp);
+		d = mk(sp * ct, st, cp * ct);
+	} else if (mode == 5) {
+		const float ct = (v - 0.5f) * 2.0f, st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f)), phi = (u - 0.5f) * HN_PI_F * 2.0f;
+		float sp, cp;
+		sincosf(phi, &sp, &cp);
+		d = mk(sp * st, ct, cp * st);
+	} else {
+		d = mk((u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f);
+		if (mode == 1) iterative_undistortion<false>(a.lens_params, &d.x, &d.y);
+		else if (mode == 4) iterative_undistortion<true>(a.lens_params, &d.x, &d.y);
+	}
+	const V3 head = mk(a.parallax_shift[0], a.parallax_shift[1], 0.0f);
+	d = d - head * a.parallax_shift[2];
+	V3 r = mk(0.0f, 0.0f, 0.0f);
+	r.x += c0.x * d.x; r.y += c0.y * d.x; r.z += c0.z * d.x;
+	r.x += c1.x * d.y; r.y += c1.y * d.y; r.z += c1.z * d.y;
+	r.x += c2.x * d.z; r.y += c2.y * d.z; r.z += c2.z * d.z;
+	d = r;
+	V3 o = mk(0.0f, 0.0f, 0.0f);
+	o.x += c0.x * head.x; o.y += c0.y * head.x; o.z += c0.z * head.x;
+	o.x += c1.x * head.y; o.y += c1.y * head.y; o.z += c1.z * head.y;
+	o.x += c2.x * head.z; o.y += c2.y * head.z; o.z += c2.z * head.z;
+	o = o + pos;
+	if (a.aperture_size != 0.0f) {
+		const V3 lookat = o + d * a.focus_z;
+		const int px = (int)(u * (float)a.w), py = (int)(v * (float)a.h);
+		const float2 rnd = hn_ld_random_val_2d(a.spp, (uint32_t)px * 19349663u + (uint32_t)py * 96925573u);
+		const float2 disk = square2disk_shirley(rnd.x * 2.0f - 1.0f, rnd.y * 2.0f - 1.0f);
+		const float bx = a.aperture_size * disk.x, by = a.aperture_size * disk.y;
+		V3 sh = mk(0.0f, 0.0f, 0.0f);
+		sh.x += c0.x * bx; sh.y += c0.y * bx; sh.z += c0.z * bx;
+		sh.x += c1.x * by; sh.y += c1.y * by; sh.z += c1.z * by;
+		o = o + sh;
+		d = (lookat - o) / a.focus_z;
+	}
+	origin = o + d * a.near_distance;
+	dir = d;
+	return true;
+}
+
+// ---- a-16: environment map + light-direction sampling (random_val.cuh:62-72,130-185, envmap.cuh:24-50) ----
 __device__ __forceinline__ float2 dir_to_spherical_unorm(V3 d) {
 	const float cos_theta = fminf(fmaxf(d.z, -1.0f), 1.0f);
 	const float theta = acosf(cos_theta);

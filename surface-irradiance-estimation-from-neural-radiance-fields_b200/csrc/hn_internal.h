@@ -50,6 +50,10 @@ struct FrameArgs {
 	float focal[2];
 	float pixel_offset[2]; // ld_random_pixel_offset(snap ? 0 : spp), computed on the host
 	float near_distance;
+	int lens_mode;            // ELensMode of the NeRF ray init (0 = perspective)
+	float lens_params[7];
+	float aperture_size, focus_z;  // depth of field: focus_z = slice_plane_z + scale (src/testbed_nerf.cu:2342)
+	float parallax_shift[3];
 	float render_aabb[6], train_aabb[6];
 	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
 	uint32_t max_mip;

@@ -85,7 +85,7 @@ __device__ __forceinline__ M3 quat_to_mat3(Quat q) {
 }
 
 // init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1428-1476) + uv_to_ray pinhole (common_device.cuh:416-483)
-__device__ void pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& dir) {
+__device__ bool pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& dir) {
 	uint32_t idx = x + (uint32_t)a.w * y;
 	float u = ((float)x + a.pixel_offset[0]) / (float)a.w;
 	float v = ((float)y + a.pixel_offset[1]) / (float)a.h;
@@ -95,14 +95,10 @@ __device__ void pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin
 	M3 m0 = {{c0.c[0], c0.c[1], c0.c[2]}}, m1 = {{c1.c[0], c1.c[1], c1.c[2]}};
 	M3 rot = quat_to_mat3(qnormalize(qslerp(qnormalize(quat_from(m0)), qnormalize(quat_from(m1)), pixel_t)));
 	V3 pos = mix3(c0.c[3], c1.c[3], pixel_t);
-	V3 d = {(u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f};
-	V3 head = {0.0f, 0.0f, 0.0f};
-	d = d - head * 0.0f;
-	d = mul3(rot, d);
-	V3 o = mul3(rot, head) + pos;
-	o = o + d * a.near_distance;
-	origin = o;
+	V3 d;
+	if (!camera_ray(a, true, u, v, rot.c[0], rot.c[1], rot.c[2], pos, origin, d)) { origin = mk(0.0f, 0.0f, 0.0f); dir = mk(0.0f, 0.0f, 0.0f); return false; } // Ray::invalid()
 	dir = normalize3(d);
+	return true;
 }
 
 // ---------------------------------------------------------------- occupancy DDA (nerf_device.cuh:316-534)
@@ -218,7 +214,8 @@ __device__ __forceinline__ float occ_t_far(const FrameArgs& a, const uint8_t* bi
 
 // per-pixel start state: init_rays (:1478-1543) + advance_pos_nerf (:333-362). Returns alive.
 __device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out) {
-	pixel_ray(a, x, y, o, d);
+	t_out = MAX_DEPTH_F;
+	if (!pixel_ray(a, x, y, o, d)) return false; // invalid ray (f-theta lens outside its image circle)
 	uint32_t idx = x + (uint32_t)a.w * y;
 	Box aabb = ldbox(a.render_aabb);
 	float t = fmaxf(box_ray_intersect(aabb, o, d).x, 0.0f) + 1e-6f;
@@ -253,7 +250,7 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
 		alive = start_ray(a, bits, x, y, o, d, t);
 		// :1526-1528: envmap -> frame buffer; in hybrid frames only where the mesh pass left nothing
-		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);
+		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) if (d.x != 0.0f || d.y != 0.0f || d.z != 0.0f) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);
 	}
 	uint32_t mask = __ballot_sync(0xffffffffu, alive);
 	if (mask == 0) return;

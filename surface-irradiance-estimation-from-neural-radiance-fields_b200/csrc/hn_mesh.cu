@@ -191,19 +191,9 @@ __device__ bool mesh_pixel(const FrameArgs& a, const SceneDev& sc, float4* __res
 	const Box aabb = ldbox(a.mesh_aabb);
 	// init_rays_with_payload_kernel_mesh_geometry (:488-579): pixel_to_ray with camera_matrix0 as is (no rolling shutter)
 	const float u = ((float)x + a.pixel_offset[0]) / (float)a.w, v = ((float)y + a.pixel_offset[1]) / (float)a.h;
-	V3 dir = mk((u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f);
 	const V3 c0 = ld3(a.cam0), c1 = ld3(a.cam0 + 3), c2 = ld3(a.cam0 + 6), cam_pos = ld3(a.cam0 + 9);
-	{
-		V3 head = mk(0.0f, 0.0f, 0.0f);
-		dir = dir - head * 0.0f;
-		V3 r = mk(0.0f, 0.0f, 0.0f);
-		r.x += c0.x * dir.x; r.y += c0.y * dir.x; r.z += c0.z * dir.x;
-		r.x += c1.x * dir.y; r.y += c1.y * dir.y; r.z += c1.z * dir.y;
-		r.x += c2.x * dir.z; r.y += c2.y * dir.z; r.z += c2.z * dir.z;
-		dir = r;
-	}
-	V3 org = mk(0.0f, 0.0f, 0.0f) + cam_pos; // mat3(camera) * head_pos (= 0) + camera[3]
-	org = org + dir * a.near_distance;
+	V3 org, dir;
+	camera_ray(a, false, u, v, c0, c1, c2, cam_pos, org, dir); // no Lens on this ray init; parallax shift and depth of field apply
 	depth_buffer[idx] = MAX_DEPTH_F;
 	dir = normalize3(dir);
 	const float t0 = fmaxf(box_ray_intersect(aabb, org, dir).x, 0.0f);

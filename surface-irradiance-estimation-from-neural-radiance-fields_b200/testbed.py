@@ -291,6 +291,8 @@ class Testbed:
     # ERenderMode (include/neural-graphics-primitives/common.h:58-72, pyngp RenderMode); the NeRF pass builds AO, Shade*, Positions,
     # Depth, Cost and EncodingVis, the others raise at render time
     render_mode = property(lambda s: RenderMode(int(s.get_option("render_mode"))), lambda s, v: s.set_option("render_mode", float(int(v))))
+    aperture_size = property(lambda s: s.get_option("aperture_size"), lambda s, v: s.set_option("aperture_size", v))
+    parallax_shift = property(lambda s: s.get_option("parallax_shift", 3), lambda s, v: s.set_option("parallax_shift", v))
     background_color = property(lambda s: s.get_option("background_color", 4), lambda s, v: s.set_option("background_color", v))
 
     def set_nerf_camera_matrix(self, m):

@@ -181,6 +181,42 @@ def make_ref_env():
     print("ref_host_env.npz:", len(out), "arrays")
 
 
+LENS_CASES = [  # (tag, lens_mode, lens_params, aperture, focus_z, parallax)
+    ("pinhole_dof", 0, (0,) * 7, 0.05, 1.7, (0.02, -0.03, 0.5)),
+    ("opencv", 1, (-0.12, 0.05, 0.002, -0.003, 0, 0, 0), 0.0, 1.0, (0, 0, 0)),
+    ("ftheta", 2, (0.0, 1.1e-3, 2.0e-8, -1.0e-11, 0.0, 800.0, 600.0), 0.0, 1.0, (0, 0, 0)),
+    ("latlong", 3, (0,) * 7, 0.0, 1.0, (0, 0, 0)),
+    ("fisheye", 4, (0.03, -0.01, 0.004, -0.001, 0, 0, 0), 0.02, 2.5, (0, 0, 0)),
+    ("equirect", 5, (0,) * 7, 0.0, 1.0, (0.01, 0.0, 1.0)),
+]
+
+
+def make_ref_lens():
+    """uv_to_ray (common_device.cuh:416-483) of the reference with a Lens, parallax shift and depth of field -> ref_host_lens.npz"""
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_uv_to_ray_lens"):
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing or stale: run `make -C oracle ref`")
+    ref.ref_uv_to_ray_lens.restype = C.c_int32
+    rng = np.random.default_rng(20261106)
+    n = 192
+    uv = rng.uniform(0, 1, (n, 2)).astype(f32)
+    uv[0] = [0.5, 0.5]; uv[1] = [0, 0]; uv[2] = [1, 1]; uv[3] = [0.5, 0.0]
+    cam = synthetic.look_at_camera((1.4, 1.2, 1.6), (0.5, 0.5, 0.5)).astype(f32).reshape(12)
+    w, h = 800, 600
+    focal = np.array([700.0, 710.0], f32); sc = np.array([0.48, 0.53], f32)
+    out = {"uv": uv, "cam": cam, "res": np.array([w, h], np.int32), "focal": focal, "screen_center": sc, "near": np.array([0.05], f32), "spp": np.array([3], np.uint32)}
+    for tag, mode, lp, ap, fz, par in LENS_CASES:
+        o = np.zeros((n, 3), f32); d = np.zeros((n, 3), f32); ok = np.zeros(n, np.int32)
+        for i in range(n):
+            to, td = (C.c_float * 3)(), (C.c_float * 3)()
+            ok[i] = ref.ref_uv_to_ray_lens(C.c_uint32(3), fa(*uv[i]), w, h, fa(*focal), fa(*cam), fa(*sc), fa(*par), C.c_float(0.05), C.c_float(fz),
+                                           C.c_float(ap), mode, fa(*lp), to, td)
+            o[i], d[i] = to[:], td[:]
+        out[f"{tag}_o"], out[f"{tag}_d"], out[f"{tag}_valid"] = o, d, ok
+    np.savez_compressed(os.path.join(HERE, "ref_host_lens.npz"), **out)
+    print("ref_host_lens.npz:", len(out), "arrays")
+
+
 class Info:
     pass
 
@@ -224,7 +260,10 @@ def make_oracle_pin():
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "env":  # only the a-16 vectors (leaves the other files untouched)
         make_ref_env()
+    elif len(sys.argv) > 1 and sys.argv[1] == "lens":
+        make_ref_lens()
     else:
+        make_ref_lens()
         make_ref_host()
         make_ref_env()
         make_oracle_pin()

@@ -39,7 +39,8 @@ class RenderParams(C.Structure):
                 ("dda_iter_cap", i32), ("mesh_aabb", f32 * 6), ("sun_dir", f32 * 3), ("up_dir", f32 * 3), ("floor_y", f32),
                 ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32),
                 ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p),
-                ("render_mode", i32), ("depth_scale", f32)]
+                ("render_mode", i32), ("depth_scale", f32),
+                ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3)]
 
 
 def P(a):
@@ -105,7 +106,8 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   render_aabb=(0, 0, 0, 1, 1, 1), train_aabb=(0, 0, 0, 1, 1, 1), max_mip=0, cone=0.0, min_transmittance=0.01,
                   rgb_act=2, density_act=3, linear_colors=False, dda_iter_cap=0, mesh_aabb=(0, 0, 0, 1, 1, 1),
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
-                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33) -> RenderParams:
+                  clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
+                  lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0)) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -135,6 +137,9 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.compat_nearest_aabb_only, p.depth_merge_clip = int(compat), int(clip)
     p.n_threads = n_threads if n_threads is not None else (os.cpu_count() or 1)
     p.render_mode, p.depth_scale = int(render_mode), float(depth_scale)
+    p.lens_mode, p.aperture_size, p.focus_z = int(lens_mode), float(aperture_size), float(focus_z)
+    p.lens_params[:] = [float(v) for v in lens_params]
+    p.parallax_shift[:] = [float(v) for v in parallax_shift]
     if envmap is not None:
         env = np.ascontiguousarray(envmap, np.float32)
         assert env.ndim == 3 and env.shape[2] == 4
@@ -273,6 +278,17 @@ def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):
     total = lib.orc_render_frame(scene.h if scene is not None else None, C.byref(p), C.byref(cfg) if cfg is not None else None,
                                  P(params) if params is not None else None, P(bits) if bits is not None else None, P(frame), P(depth), P(steps))
     return frame, depth, steps.reshape(p.height, p.width), int(total)
+
+
+def uv_to_ray(p: RenderParams, spp, uv, use_lens=True):
+    """oracle uv_to_ray for an array of uv (camera = p.cam0): (origins, directions (not normalised), valid)"""
+    uv = np.ascontiguousarray(uv, dtype=np.float32)
+    n = uv.shape[0]
+    o = np.zeros((n, 3), np.float32); d = np.zeros((n, 3), np.float32); ok = np.zeros(n, np.int32)
+    lib.orc_uv_to_ray.restype = C.c_int32
+    for i in range(n):
+        ok[i] = lib.orc_uv_to_ray(C.byref(p), C.c_uint32(int(spp)), P(uv[i]), C.c_int32(int(use_lens)), P(o[i]), P(d[i]))
+    return o, d, ok
 
 
 def render_reference_frame(tb, params, grid, n_cascades, meshes, cam, w, h, mesh_aabb=None, spp=0, compat=False, clip=False,

@@ -1,0 +1,34 @@
+"""Hash-grid levels 3..7 gathered through the TEX pipe (option eval_tex_gather, default 1) against the LSU-only gather,
+config3 1080p frame on one GPU: eval kernel time and bit-identity of the frame. The split was chosen from a sweep over
+(level, corner pair) masks with this script (results in profiles/r01_tex_probe.txt)."""
+import os, sys, importlib
+import numpy as np, torch
+ROOT=os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+hn = importlib.import_module("surface-irradiance-estimation-from-neural-radiance-fields_b200")
+W,H=1920,1080
+tb = hn.Testbed(device=0)
+tb.reload_network_from_file(os.path.join(ROOT,"configs","nerf","base.json"))
+info=tb.network_info()
+tb.set_params(hn.synthetic.random_params(info,1337,1e-4))
+tb.set_density_grid(hn.synthetic.sphere_density_grid(0.35),1)
+tb.add_mesh(hn.synthetic.torus_mesh(1024,512)); tb.build_scene()
+tb.snap_to_pixel_centers=True
+cam=hn.synthetic.default_camera(); tb.set_camera_cols(cam)
+frame=torch.zeros(H,W,4,device="cuda"); depth=torch.zeros(H,W,device="cuda")
+stream=torch.cuda.current_stream().cuda_stream
+base=None
+for on in (0, 1, 0, 1):
+    tb.set_option("eval_tex_gather", float(on))
+    for _ in range(3): tb.render_frame(cam,cam,W,H,frame.data_ptr(),depth.data_ptr(),0,stream)
+    torch.cuda.synchronize()
+    e0,e1=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20): tb.render_frame(cam,cam,W,H,frame.data_ptr(),depth.data_ptr(),0,stream)
+    e1.record(); torch.cuda.synchronize(); ms=e0.elapsed_time(e1)/20
+    img=frame.cpu().numpy().copy()
+    if base is None: base=img
+    tb.set_option("profile",1.0); ev=0.0
+    for _ in range(3):
+        tb.render_frame(cam,cam,W,H,frame.data_ptr(),depth.data_ptr(),0,stream); ev+=tb.frame_stats().ms_eval/3
+    tb.set_option("profile",0.0)
+    print(f"eval_tex_gather {on}: frame {ms:.3f} ms  eval {ev:.3f} ms  identical {np.array_equal(img,base)}")

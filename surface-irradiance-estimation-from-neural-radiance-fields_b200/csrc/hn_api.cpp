@@ -15,6 +15,31 @@ using namespace hn;
 
 static void need(bool cond, const char* msg) { if (!cond) throw std::runtime_error(msg); }
 
+// Texture views (16-byte and 8-byte texels, point sampled, element type) of the parameter buffer for the TEX-pipe gather of the
+// tcgen05 kernel. Rebuilt lazily when the buffer has moved; nullptr = gather through the LSU pipe only.
+static void release_param_textures(hn_context* ctx) {
+	if (ctx->param_tex.tex16) cudaDestroyTextureObject(ctx->param_tex.tex16);
+	if (ctx->param_tex.tex8) cudaDestroyTextureObject(ctx->param_tex.tex8);
+	ctx->param_tex = hn::ParamTextures{};
+}
+static const hn::ParamTextures* param_textures(hn_context* ctx) {
+	if (!ctx->opt.eval_tex_gather || !ctx->params.p || ctx->net.F != 4) return nullptr;
+	if (ctx->param_tex.ptr == ctx->params.p) return &ctx->param_tex;
+	release_param_textures(ctx);
+	cudaResourceDesc rd = {};
+	rd.resType = cudaResourceTypeLinear;
+	rd.res.linear.devPtr = (void*)ctx->params.p;
+	rd.res.linear.sizeInBytes = (ctx->net.n_params * sizeof(__half)) & ~(size_t)15;
+	cudaTextureDesc td = {};
+	td.readMode = cudaReadModeElementType; td.filterMode = cudaFilterModePoint; td.addressMode[0] = cudaAddressModeClamp;
+	rd.res.linear.desc = cudaCreateChannelDesc(32, 32, 32, 32, cudaChannelFormatKindUnsigned);
+	HN_CUDA(cudaCreateTextureObject(&ctx->param_tex.tex16, &rd, &td, nullptr));
+	rd.res.linear.desc = cudaCreateChannelDesc(32, 32, 0, 0, cudaChannelFormatKindUnsigned);
+	HN_CUDA(cudaCreateTextureObject(&ctx->param_tex.tex8, &rd, &td, nullptr));
+	ctx->param_tex.ptr = ctx->params.p;
+	return &ctx->param_tex;
+}
+
 extern "C" {
 
 const char* hn_version(void) { return "hybrid-nerf-b200 0.1 (sm_100a)"; }
@@ -47,6 +72,7 @@ void hn_destroy(hn_context* ctx) {
 	cudaSetDevice(ctx->device);
 	cudaDeviceSynchronize();
 	hn::train_release(ctx);
+	release_param_textures(ctx);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto& e : ctx->pass_events) if (e) cudaEventDestroy(e);
 	if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -192,7 +218,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"render_aabb", {o.render_aabb, 6, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
-		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
+		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"eval_tex_gather", {&o.eval_tex_gather, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
 		{"sun_dir", {o.sun_dir, 3, false}}, {"up_dir", {o.up_dir, 3, false}}, {"floor_enable", {&o.floor_enable, 1, true}},
 		{"brdf", {o.brdf, 13, false}}, {"compat_nearest_aabb_only", {&o.compat_nearest_aabb_only, 1, true}},
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
@@ -375,7 +401,7 @@ uint32_t run_passes(hn_context* ctx, const FrameArgs& a, RaySoA rays, float4* fr
 		const bool fused = !light && ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite;
 		if (fused) ctx->survive.ensure(n_alive);
 		launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p,
-			ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s, light);
+			ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s, light, param_textures(ctx));
 		tm.stop(light ? ms_dummy : st.ms_eval);
 		tm.start();
 		const bool per_ray = !light && !fused && ctx->opt.composite_impl == 1;
@@ -763,7 +789,7 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 	const float rs[4] = {0, 0, 0, 1};
 	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
 	RaySoA none = {};
-	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->opt.eval_impl, nullptr, nullptr, nullptr, nullptr, ctx->stream);
+	launch_eval(ctx->net, ctx->levels, ctx->params.p, a, d_p, nullptr, nullptr, none, d_d, nullptr, chunks, d_o, ctx->opt.eval_impl, nullptr, nullptr, nullptr, nullptr, ctx->stream, false, param_textures(ctx));
 	HN_CUDA(cudaMemcpyAsync(out, d_o, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	HN_CUDA(cudaGetLastError());

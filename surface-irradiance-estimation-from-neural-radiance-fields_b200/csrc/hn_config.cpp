@@ -81,6 +81,7 @@ void finalize_network(hn_context* ctx) {
 		g.mask[i] = (g.size[i] & (g.size[i] - 1)) == 0 ? g.size[i] - 1 : 0u;
 	}
 	ctx->has_net = true;
+	ctx->param_tex.ptr = nullptr; // texture views are rebuilt for the new layout on the next frame
 	ctx->has_params = false;
 	// aabb_scale drives the cascades and the cone angle (src/testbed_nerf.cu:2728-2740)
 	int max_cascade = 0;

@@ -77,6 +77,7 @@ struct Options {
 	int profile = 0;
 	int fuse_composite = 0;                     // 1 = composite inside the tcgen05 network kernel (eval_impl 1 only; measured slower, kept as an option)
 	int composite_impl = 1;                     // 1 = one warp per ray + compact kernel, 0 = 32 rays per warp with in-kernel compaction
+	int eval_tex_gather = 1;                    // 1 = tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe (F = 4), 0 = LSU only
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int snapshot_optimizer_state = 0;           // hn_save_snapshot: include the Trainer's optimizer state (save_snapshot(path, include_optimizer_state))
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
@@ -138,6 +139,7 @@ struct hn_context {
 	std::string config_blob; // merged network config (MessagePack), kept so hn_set_aabb_scale can re-derive per_level_scale
 	hn::GridLevels levels;
 	hn::DevBuf<__half> params;
+	hn::ParamTextures param_tex;                // texture views of `params` (TEX-pipe gather); rebuilt when the buffer moves
 	std::vector<__half> params_host;        // fp16 inference copy on the host (snapshot writer)
 	std::vector<float> density_grid_host;   // last density grid given to hn_set_density_grid (snapshot writer)
 	bool has_params = false;

@@ -132,10 +132,12 @@ void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays
 
 // network TU
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
+// The parameter buffer seen as 16-byte and 8-byte texels: the tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe.
+struct ParamTextures { cudaTextureObject_t tex16 = 0, tex8 = 0; const void* ptr = nullptr; };
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
 	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,
-	bool density_only = false);
+	bool density_only = false, const ParamTextures* tex = nullptr);
 // fused_frame != nullptr (impl 1 only): composite inside the network kernel, write survive[chunk]; then launch_compact builds the next list
 void launch_compact(const uint32_t* alive_in, const uint32_t* n_alive_ptr, const uint32_t* survive, uint32_t* alive_out, uint32_t* n_alive_out, uint32_t max_rays, cudaStream_t s); // impl: 0 = warp MMA (mma.sync), 1 = tcgen05/TMEM
 

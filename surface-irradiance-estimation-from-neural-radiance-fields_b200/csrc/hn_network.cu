@@ -219,7 +219,7 @@ void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const f
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
 	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,
-	bool density_only) {
+	bool density_only, const ParamTextures* tex) {
 	if (!max_chunks) return;
 	EvalArgs a;
 	a.density_only = (density_only && impl == 1) ? 1 : 0; // the warp-MMA kernel always runs both MLPs (sigma is the same)
@@ -232,6 +232,8 @@ void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, c
 	a.samples = samples; a.sample_counts = sample_counts; a.alive_list = alive_list; a.d_mw = rays.d_mw;
 	a.dirs_override = dirs_override; a.n_chunks_ptr = n_chunks_ptr; a.n_chunks = max_chunks; a.out = out;
 	a.fused = (impl == 1 && fused_frame) ? 1 : 0;
+	a.tex16 = 0; a.tex8 = 0; a.tex_base = (uint32_t)(cfg.grid_offset / 4);
+	if (impl == 1 && tex && tex->tex16 && cfg.F == 4 && cfg.grid_offset % 8 == 0) { a.tex16 = tex->tex16; a.tex8 = tex->tex8; }
 	a.comp = make_comp_args(fa, rays, alive_list, samples, fused_frame, fused_depth, survive, counters);
 	if (impl == 1) { launch_eval_tc(a, cfg.F, max_chunks, s); return; }
 	size_t smem = mlp_smem_bytes(a.density_hidden) + mlp_smem_bytes(a.rgb_hidden) + 4 * 32 * A_STRIDE;

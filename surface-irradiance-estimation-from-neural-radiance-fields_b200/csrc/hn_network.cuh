@@ -23,6 +23,8 @@ struct EvalArgs {
 	// fused compositing (tcgen05 kernel only): the warp that evaluated a ray chunk also composites it
 	int fused;
 	int density_only;               // tcgen05 kernel: stop after the density MLP, out = (0, 0 | 0, sigma) (light rays, a-16)
+	cudaTextureObject_t tex16, tex8; // the whole parameter buffer as 16-byte / 8-byte texels (TEX-pipe gather of some levels)
+	uint32_t tex_base;              // grid table offset inside the parameter buffer, in 8-byte texels
 	CompArgs comp;
 };
 
@@ -37,8 +39,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // aligned 2-entry block (always for even x: the hash only XORs x in, dense rows are contiguous) ONE load brings both, which
 // removes a quarter of the gather instructions and of the L1 wavefronts. Values and the order of the fp16 FMAs are those
 // of tcnn's kernel_grid (grid.h:94-168), so the result stays bit-identical to the oracle.
-template <int F>
-__device__ __forceinline__ void encode_sample(const GridLevels& g, const __half* __restrict__ table, float px, float py, float pz, uint32_t (&enc)[16]) {
+template <int F, uint32_t TEXMASK = 0>
+__device__ __forceinline__ void encode_sample(const GridLevels& g, const __half* __restrict__ table, float px, float py, float pz, uint32_t (&enc)[16],
+	cudaTextureObject_t tex16 = 0, cudaTextureObject_t tex8 = 0, uint32_t tex_base = 0) {
 	constexpr int L = 32 / F;
 	#pragma unroll
 	for (int l = 0; l < L; ++l) {
@@ -66,11 +69,13 @@ __device__ __forceinline__ void encode_sample(const GridLevels& g, const __half*
 			#pragma unroll
 			for (int c = 0; c < 8; c += 2) {
 				const bool paired = (idx[c] ^ idx[c + 1]) == 1u;
-				const uint4 q = __ldg(reinterpret_cast<const uint4*>(lvl) + (idx[c] >> 1));
+				const bool via_tex = (TEXMASK >> (4 * l + (c >> 1))) & 1u; // compile-time per unrolled (level, corner pair): this gather rides the TEX pipe
+				const uint32_t tbase = tex_base + g.offset[l];
+				const uint4 q = via_tex ? tex1Dfetch<uint4>(tex16, (int)((tbase + idx[c]) >> 1)) : __ldg(reinterpret_cast<const uint4*>(lvl) + (idx[c] >> 1));
 				const bool odd = idx[c] & 1u;
 				v[c] = odd ? make_uint2(q.z, q.w) : make_uint2(q.x, q.y);
 				v[c + 1] = odd ? make_uint2(q.x, q.y) : make_uint2(q.z, q.w);
-				if (!paired) v[c + 1] = __ldg(reinterpret_cast<const uint2*>(lvl) + idx[c + 1]);
+				if (!paired) v[c + 1] = via_tex ? tex1Dfetch<uint2>(tex8, (int)(tbase + idx[c + 1])) : __ldg(reinterpret_cast<const uint2*>(lvl) + idx[c + 1]);
 			}
 			__half2 a0 = __float2half2_rn(0.f), a1 = a0;
 			#pragma unroll

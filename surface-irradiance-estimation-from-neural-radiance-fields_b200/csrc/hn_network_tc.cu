@@ -148,7 +148,7 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 // group's gather overlaps the other groups' MMA rounds.
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
 
-template <int F, int G, bool FUSED, bool DONLY>
+template <int F, int G, bool FUSED, bool DONLY, uint32_t TEXMASK = 0>
 __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
 	const int grp = threadIdx.x >> 7;                     // tile group of this thread
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 				const float px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
 				const float py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
 				const float pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
-				encode_sample<F>(a.g, a.table, px, py, pz, enc);
+				encode_sample<F, TEXMASK>(a.g, a.table, px, py, pz, enc, a.tex16, a.tex8, a.tex_base);
 			}
 			#pragma unroll
 			for (int c = 0; c < 4; ++c)
@@ -308,11 +308,16 @@ void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStre
 	uint32_t ctas = (tiles + G - 1) / G;
 	uint32_t persistent = (uint32_t)sm_count * 2u;
 	uint32_t blocks = ctas < persistent ? ctas : persistent;
-	#define HN_LAUNCH_TC(FF, FU, DO) do { \
-		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		tc::eval_tc_kernel<FF, G, FU, DO><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
-	if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true); else if (a.fused) HN_LAUNCH_TC(4, true, false); else HN_LAUNCH_TC(4, false, false); }
-	else { if (a.density_only) HN_LAUNCH_TC(2, false, true); else if (a.fused) HN_LAUNCH_TC(2, true, false); else HN_LAUNCH_TC(2, false, false); }
+	#define HN_LAUNCH_TC(FF, FU, DO, TM) do { \
+		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO, TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+		tc::eval_tc_kernel<FF, G, FU, DO, TM><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
+	// F = 4 with texture objects: the five fine levels (3..7, the hashed ones of the base config) are gathered through the TEX
+	// pipe, the three coarse ones through the LSU pipe. Measured on B200 (profiles/r01_tex_probe.txt): eval 7.03 -> 6.53 ms per
+	// 1080p frame, bit-identical output; every other split of (level, corner pair) between the two pipes was slower.
+	constexpr uint32_t TM = 0xFFFFF000u;
+	if (F == 4 && a.tex16) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM); else HN_LAUNCH_TC(4, false, false, TM); }
+	else if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true, 0u); else if (a.fused) HN_LAUNCH_TC(4, true, false, 0u); else HN_LAUNCH_TC(4, false, false, 0u); }
+	else { if (a.density_only) HN_LAUNCH_TC(2, false, true, 0u); else if (a.fused) HN_LAUNCH_TC(2, true, false, 0u); else HN_LAUNCH_TC(2, false, false, 0u); }
 	#undef HN_LAUNCH_TC
 }
 

@@ -195,6 +195,24 @@ def train_arm(args):
         ts = t.clone(); dist.all_reduce(ts)
         ms, samples = float(tm[0].item()), float(ts[1].item())
     clocks = sampler.stop() if rank == 0 else None
+    # where a multi-GPU step goes (host clock around host-synchronous phases, max over ranks): compute, wait for the slowest rank,
+    # the all-reduce itself (entered together, right after a barrier), optimizer
+    phases = None
+    if world > 1:
+        acc = [0.0, 0.0, 0.0, 0.0]
+        n_ph = 10
+        for _ in range(n_ph):
+            torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter(); tb.train_accumulate(0); torch.cuda.synchronize()
+            t1 = time.perf_counter(); dist.barrier(); torch.cuda.synchronize()
+            t2 = time.perf_counter(); dist.all_reduce(grads); torch.cuda.synchronize()
+            t3 = time.perf_counter(); tb.train_apply(1.0); torch.cuda.synchronize()
+            t4 = time.perf_counter()
+            for i, v in enumerate((t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+                acc[i] += v * 1e3 / n_ph
+        tp = torch.tensor(acc, device=dev, dtype=torch.float64)
+        dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        phases = {k: round(float(v), 4) for k, v in zip(("accumulate", "wait_slowest_rank", "all_reduce", "apply"), tp.tolist())}
     tb.set_option("profile", 1.0)
     step()
     st = tb.train_stats()
@@ -208,7 +226,7 @@ def train_arm(args):
                 "clocks": clocks, "gpu_launches": int(args.steps * 45), "loss": loss,
                 "e2e": {"value": samples / args.steps / (wall_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": wall_ms, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 8},
                 "kernel_ms": {"sample": st.ms_sample, "forward": st.ms_forward, "loss": st.ms_loss, "backward": st.ms_backward, "optimizer": st.ms_optimizer},
-                "roofline": None, "cpu_baseline": None}
+                "step_phases_ms": phases, "roofline": None, "cpu_baseline": None}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -28,7 +28,7 @@ W, H = 1920, 1080
 MESH_NU, MESH_NV = 1024, 512  # 1024 * 512 * 2 = 1 048 576 triangles
 ALGO_BYTES_PER_SAMPLE = 512    # L*8 corners*F*2 B gathered per network sample
 ALGO_FLOP_PER_SAMPLE = 18816
-NCU_EVAL_DRAM_BYTES = 185.9e6  # dram__bytes_read.sum + dram__bytes_write.sum of one eval_tc_kernel launch (ncu --set full, profiles/r01_ncu_eval_tc_v3.txt)
+NCU_EVAL_DRAM_BYTES = 186.7e6  # dram__bytes_read.sum + dram__bytes_write.sum of one eval_tc_kernel launch (ncu --set full, profiles/r01_ncu_eval_tc_v5.txt)
 
 
 def peaks():
@@ -360,7 +360,7 @@ def main():
     ach_gbs = samples * ALGO_BYTES_PER_SAMPLE / eval_s / 1e9 if eval_s > 0 else 0.0
     roofline = {"kernel": "eval_kernel (fused hash-grid gather + density/colour MLPs)", "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak,
                 "unit": "GB/s", "frac": ach_gbs / hbm_peak, "traffic": NCU_EVAL_DRAM_BYTES,
-                "traffic_source": "profiles/r01_ncu_eval_tc_v3.txt: dram read 142.3 MB + write 43.6 MB for the largest pass launch (785 us); far below the algorithmic gather bytes because the 32 MiB of hash tables stay resident in the 126 MB L2 (86.8 % L2 hit rate) - compulsory DRAM bytes are the 32 B/sample of sample + output records",
+                "traffic_source": "profiles/r01_ncu_eval_tc_v5.txt: dram read 142.8 MB + write 43.9 MB for the largest pass launch (727 us); far below the algorithmic gather bytes because the 23 MB of hash tables stay resident in the 126 MB L2 (88.9 % L2 hit rate) - compulsory DRAM bytes are the 32 B/sample of sample + output records",
                 "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",
                 "mlp_tflops": samples * ALGO_FLOP_PER_SAMPLE / eval_s / 1e12 if eval_s > 0 else 0.0, "mlp_frac_of_tensor_peak": (samples * ALGO_FLOP_PER_SAMPLE / eval_s / 1e12) / tf_peak if eval_s > 0 else 0.0,
                 "kernel_ms_per_frame": {k: round(v, 4) for k, v in prof.items()}, "samples_per_frame": int(samples)}

@@ -56,6 +56,8 @@ typedef struct {
 	int32_t lens_mode; float lens_params[7];
 	float aperture_size, focus_z;
 	float parallax_shift[3];
+	// m_render_aabb_to_local (column-major mat3): crop box rotation, applied when crop_rotated != 0 (src/testbed_nerf.cu:1530-1532)
+	int32_t crop_rotated; float render_aabb_to_local[9];
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----
@@ -72,6 +74,9 @@ float orc_srgb_to_linear(float v);
 // ---- a-16 sampling helpers (random_val.cuh:62-72,130-185; pinned against oracle/_ref) and the envmap lookup ----
 // uv_to_ray with the lens / depth-of-field / parallax fields of p (direction not normalised); returns 0 for an invalid ray
 int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]);
+// tonemap_kernel (src/render_buffer.cu:529-560) on a linear accumulation buffer; curve = ETonemapCurve (0 Identity, 1 ACES, 2 Hable, 3 Reinhard)
+void orc_tonemap(const float* accum, uint32_t n, int32_t to_srgb, float exposure, const float bg[4], int32_t curve, int32_t clamp_output,
+	int32_t unmultiply_alpha, float* out);
 void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]);
 void orc_dir_to_spherical_unorm(const float d[3], float out[2]);
 void orc_cosine_hemisphere(const float u[2], float out[3]);

@@ -321,16 +321,24 @@ static uint32_t mip_from_pos(vec3 pos, uint32_t max_cascade = NERF_CASCADES - 1)
 }
 // nerf_device.cuh:461-495 (iter_cap == 0) and :497-534 (iter_cap == 200, loop runs for i in [1, cap))
 float advance_to_occupied(float t, float cone_angle, const Ray& ray, vec3 idir, const uint8_t* bits, uint32_t min_mip, uint32_t max_mip,
-	const BoundingBox& aabb, int iter_cap) {
+	const BoundingBox& aabb, int iter_cap, const mat3* to_local) {
 	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
 		vec3 pos = ray.at(t);
-		if (t >= MAX_DEPTH || !aabb.contains(pos)) return MAX_DEPTH;
+		if (t >= MAX_DEPTH || !aabb.contains(to_local ? mul(*to_local, pos) : pos)) return MAX_DEPTH; // aabb_to_local * pos (nerf_device.cuh:470)
 		uint32_t mip = std::min(std::max(mip_from_pos(pos), min_mip), max_mip);
 		if (!bits || occupied_at(pos, bits, mip)) return t;
 		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
 		t = advance_to_next_voxel(t, cone_angle, pos, ray.d, idir, mip);
 	}
 	return MAX_DEPTH;
+}
+
+// m_render_aabb_to_local of the frame (nullptr = axis-aligned crop box)
+static const mat3* crop_matrix(const orc_render_params& p, mat3& store) {
+	if (!p.crop_rotated) return nullptr;
+	const float* R = p.render_aabb_to_local;
+	store = {{{R[0], R[1], R[2]}, {R[3], R[4], R[5]}, {R[6], R[7], R[8]}}};
+	return &store;
 }
 
 // ---------------------------------------------------------------- testbed_nerf.cu:284-331, 2863-2880
@@ -617,14 +625,15 @@ RayState init_ray(const orc_render_params& p, const uint8_t* bits, uint32_t x, u
 	if (!valid) { r.o = ray.o; r.d = {0.0f, 0.0f, 0.0f}; r.alive = false; return r; } // :1494-1498
 	ray.d = normalize(ray.d);
 	BoundingBox render_aabb = bb_from(p.render_aabb);
-	float t = std::fmax(render_aabb.ray_intersect(ray.o, ray.d).x, 0.0f) + 1e-6f;
+	mat3 crop_store; const mat3* crop = crop_matrix(p, crop_store);
+	float t = std::fmax((crop ? render_aabb.ray_intersect(mul(*crop, ray.o), mul(*crop, ray.d)) : render_aabb.ray_intersect(ray.o, ray.d)).x, 0.0f) + 1e-6f; // :1530
 	r.o = ray.o; r.d = ray.d;
-	if (!render_aabb.contains(ray.at(t))) { r.alive = false; return r; }
+	if (!render_aabb.contains(crop ? mul(*crop, ray.at(t)) : ray.at(t))) { r.alive = false; return r; }
 	// advance_pos_nerf :333-362
 	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / ray.d;
 	float cone = p.cone_angle_constant;
 	t = advance_n_steps(t, cone, ld_random_val(p.spp, idx * 786433u));
-	t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, 0);
+	t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, 0, crop);
 	if (t >= MAX_DEPTH) { r.alive = false; return r; }
 	r.t = t; r.alive = true;
 	return r;
@@ -645,6 +654,7 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 	BoundingBox render_aabb = bb_from(p.render_aabb), train_aabb = bb_from(p.train_aabb);
 	cam_t cam1 = cam_from(p.cam1);
 	vec3 cam_fwd = cam1.c[2], cam_pos = cam1.c[3];
+	mat3 crop_store; const mat3* crop = crop_matrix(p, crop_store);
 	std::atomic<uint64_t> total{0};
 	parallel_rows(p.height, p.n_threads, [&](int y) {
 		uint64_t row_total = 0;
@@ -668,7 +678,7 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			uint32_t n = 0;
 			float clip_depth = (p.depth_merge_clip && depth_test) ? depth[idx] : MAX_DEPTH;
 			while (true) {
-				t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap);
+				t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap, crop);
 				if (t >= MAX_DEPTH) break;
 				float dt = calc_dt(t, cone);
 				vec3 wp = train_aabb.relative_pos(ray.at(t));
@@ -723,15 +733,16 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8_t* bits, vec3 o, vec3 d, uint32_t* n_out) {
 	BoundingBox render_aabb = bb_from(p.render_aabb), train_aabb = bb_from(p.train_aabb);
 	if (n_out) *n_out = 0;
-	float t = std::fmax(render_aabb.ray_intersect(o, d).x, 0.0f) + 1e-6f;
+	mat3 crop_store; const mat3* crop = crop_matrix(p, crop_store);
+	float t = std::fmax((crop ? render_aabb.ray_intersect(mul(*crop, o), mul(*crop, d)) : render_aabb.ray_intersect(o, d)).x, 0.0f) + 1e-6f;
 	Ray ray = {o, d};
-	if (!render_aabb.contains(ray.at(t))) return 1.0f;
+	if (!render_aabb.contains(crop ? mul(*crop, ray.at(t)) : ray.at(t))) return 1.0f;
 	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / d;
 	float cone = p.cone_angle_constant;
 	float T = 1.0f;
 	uint32_t n = 0;
 	while (true) {
-		t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap);
+		t = advance_to_occupied(t, cone, ray, idir, bits, 0, p.max_mip, render_aabb, p.dda_iter_cap, crop);
 		if (t >= MAX_DEPTH) break;
 		float dt = calc_dt(t, cone);
 		vec3 wp = train_aabb.relative_pos(ray.at(t));
@@ -769,7 +780,7 @@ float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const
 	uint32_t min_mip, uint32_t max_mip, const float aabb[6], int32_t iter_cap) {
 	Ray ray = {{o[0], o[1], o[2]}, {d[0], d[1], d[2]}};
 	vec3 idir = vec3{1.0f, 1.0f, 1.0f} / ray.d;
-	return advance_to_occupied(t, cone_angle, ray, idir, bitfield, min_mip, max_mip, bb_from(aabb), iter_cap);
+	return advance_to_occupied(t, cone_angle, ray, idir, bitfield, min_mip, max_mip, bb_from(aabb), iter_cap, nullptr);
 }
 float orc_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
 float orc_srgb_to_linear(float v) { return srgb_to_linear(v); }
@@ -779,6 +790,45 @@ int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2
 	Ray r = uv_to_ray(*p, spp, {uv[0], uv[1]}, cam_from(p->cam0), use_lens != 0, &valid);
 	out_o[0] = r.o.x; out_o[1] = r.o.y; out_o[2] = r.o.z; out_d[0] = r.d.x; out_d[1] = r.d.y; out_d[2] = r.d.z;
 	return valid ? 1 : 0;
+}
+// src/render_buffer.cu:264-321 tonemap curve, :323-343 exposure / colour space, :529-560 tonemap_kernel (linear accumulation)
+static void tonemap_curve(float* c, int curve) {
+	if (curve == 0) return;
+	for (int i = 0; i < 3; ++i) c[i] = std::max(c[i], 0.0f);
+	float k0, k1, k2, k3, k4, k5;
+	if (curve == 1) {
+		k0 = 0.6f * 0.6f * 2.51f; k1 = 0.6f * 0.03f; k2 = 0.0f; k3 = 0.6f * 0.6f * 2.43f; k4 = 0.6f * 0.59f; k5 = 0.14f;
+	} else if (curve == 2) {
+		const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+		k0 = A * F - A * E; k1 = C * B * F - B * E; k2 = 0.0f; k3 = A * F; k4 = B * F; k5 = D * F * F;
+		const float W = 11.2f;
+		const float nom = k0 * (W * W) + k1 * W + k2, denom = k3 * (W * W) + k4 * W + k5;
+		const float white_scale = denom / nom;
+		k0 = 4.0f * k0 * white_scale; k1 = 2.0f * k1 * white_scale; k2 = k2 * white_scale; k3 = 4.0f * k3; k4 = 2.0f * k4;
+	} else {
+		float Y = 0.2126f * c[0] + 0.7152f * c[1] + 0.0722f * c[2];
+		float sc = 1.f / (Y + 1.0f);
+		for (int i = 0; i < 3; ++i) c[i] *= sc;
+		return;
+	}
+	for (int i = 0; i < 3; ++i) c[i] = (c[i] * c[i] * k0 + k1 * c[i] + k2) / (k3 * (c[i] * c[i]) + k4 * c[i] + k5);
+}
+static float linear_to_srgb_f(float l) { return l < 0.0031308f ? 12.92f * l : 1.055f * std::pow(l, 0.41666f) - 0.055f; }
+void orc_tonemap(const float* accum, uint32_t n, int32_t to_srgb, float exposure, const float bg[4], int32_t curve, int32_t clamp_output,
+	int32_t unmultiply_alpha, float* out) {
+	const float scale = std::exp2(exposure);
+	for (uint32_t i = 0; i < n; ++i) {
+		float c[4] = {accum[4 * i], accum[4 * i + 1], accum[4 * i + 2], accum[4 * i + 3]};
+		float w = (1.f - c[3]) * bg[3];
+		for (int k = 0; k < 3; ++k) c[k] += srgb_to_linear(bg[k]) * w;
+		c[3] += w;
+		for (int k = 0; k < 3; ++k) c[k] *= scale;
+		tonemap_curve(c, curve);
+		if (to_srgb) for (int k = 0; k < 3; ++k) c[k] = linear_to_srgb_f(c[k]);
+		if (unmultiply_alpha && c[3] > 0.0f) for (int k = 0; k < 3; ++k) c[k] /= c[3];
+		if (clamp_output) for (int k = 0; k < 4; ++k) c[k] = std::min(std::max(c[k], 0.f), 1.f);
+		for (int k = 0; k < 4; ++k) out[4 * i + k] = c[k];
+	}
 }
 void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 void orc_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm({d[0], d[1], d[2]}); out[0] = v.x; out[1] = v.y; }
@@ -852,7 +902,8 @@ void orc_march_all(const orc_render_params* p, const uint8_t* bitfield, uint32_t
 		float t = t0[i];
 		uint32_t n = 0;
 		while (true) {
-			t = advance_to_occupied(t, p->cone_angle_constant, ray, idir, bitfield, 0, p->max_mip, render_aabb, p->dda_iter_cap);
+			mat3 crop_store; const mat3* crop = crop_matrix(*p, crop_store);
+			t = advance_to_occupied(t, p->cone_angle_constant, ray, idir, bitfield, 0, p->max_mip, render_aabb, p->dda_iter_cap, crop);
 			if (t >= MAX_DEPTH) break;
 			float dt = calc_dt(t, p->cone_angle_constant);
 			if (samples && n < max_per_ray) {

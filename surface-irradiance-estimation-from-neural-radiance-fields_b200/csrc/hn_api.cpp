@@ -215,10 +215,11 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"snap_to_pixel_centers", {&o.snap_to_pixel_centers, 1, true}}, {"render_near_distance", {&o.near_distance, 1, false}},
 		{"lens_mode", {&o.lens_mode, 1, true}}, {"lens_params", {o.lens_params, 7, false}}, {"aperture_size", {&o.aperture_size, 1, false}},
 		{"focus_z", {&o.focus_z, 1, false}}, {"parallax_shift", {o.parallax_shift, 3, false}},
-		{"render_aabb", {o.render_aabb, 6, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
+		{"render_aabb", {o.render_aabb, 6, false}}, {"render_aabb_to_local", {o.render_aabb_to_local, 9, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
-		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"eval_tex_gather", {&o.eval_tex_gather, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
+		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"tonemap_curve", {&o.tonemap_curve, 1, true}},
+		{"clamp_output_color", {&o.clamp_output_color, 1, true}}, {"unmultiply_alpha", {&o.unmultiply_alpha, 1, true}}, {"eval_tex_gather", {&o.eval_tex_gather, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
 		{"sun_dir", {o.sun_dir, 3, false}}, {"up_dir", {o.up_dir, 3, false}}, {"floor_enable", {&o.floor_enable, 1, true}},
 		{"brdf", {o.brdf, 13, false}}, {"compat_nearest_aabb_only", {&o.compat_nearest_aabb_only, 1, true}},
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
@@ -309,6 +310,11 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	a.aperture_size = o.aperture_size; a.focus_z = o.focus_z;
 	for (int i = 0; i < 3; ++i) a.parallax_shift[i] = o.parallax_shift[i];
 	std::memcpy(a.render_aabb, o.render_aabb, 24); std::memcpy(a.train_aabb, o.train_aabb, 24);
+	{
+		static const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+		std::memcpy(a.aabb_to_local, o.render_aabb_to_local, 36);
+		a.crop_rotated = std::memcmp(o.render_aabb_to_local, ident, 36) != 0;
+	}
 	// world-space union of the set cells of mips 0..max_cascade, each inflated by half a cell of its mip
 	for (int k = 0; k < 3; ++k) { a.occ_aabb[k] = 1e30f; a.occ_aabb[3 + k] = -1e30f; }
 	for (int m = 0; m <= o.max_cascade && m < (int)CASCADES; ++m) {
@@ -530,7 +536,9 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 namespace hn {
 FrameArgs train_frame_args(hn_context* ctx) {
 	const float rs[4] = {0.f, 0.f, 0.f, 1.f};
-	return make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
+	a.crop_rotated = 0; // training marches the training box (m_aabb), never the rotated render crop
+	return a;
 }
 } // namespace hn
 
@@ -621,7 +629,8 @@ int hn_render_to_host(hn_context* ctx, int width, int height, int spp, int linea
 		acc.ms_envlight += ctx->stats.ms_envlight; acc.n_env_hits = ctx->stats.n_env_hits; acc.n_light_rays += ctx->stats.n_light_rays;
 		acc.n_light_rays_volume += ctx->stats.n_light_rays_volume; acc.n_light_samples += ctx->stats.n_light_samples;
 	}
-	launch_tonemap(ctx->accum.p, ctx->tonemapped.p, (uint32_t)n, linear ? 0 : 1, ctx->opt.exposure, ctx->opt.background_color, ctx->stream);
+	launch_tonemap(ctx->accum.p, ctx->tonemapped.p, (uint32_t)n, linear ? 0 : 1, ctx->opt.exposure, ctx->opt.background_color,
+		ctx->opt.tonemap_curve, ctx->opt.clamp_output_color, ctx->opt.unmultiply_alpha, ctx->stream);
 	launches += 1;
 	HN_CUDA(cudaMemcpyAsync(rgba_host, ctx->tonemapped.p, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
 	if (depth_host) HN_CUDA(cudaMemcpyAsync(depth_host, ctx->depth.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));

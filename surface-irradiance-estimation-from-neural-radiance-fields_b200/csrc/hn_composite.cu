@@ -152,16 +152,44 @@ __global__ void accumulate_kernel(const float4* __restrict__ frame, float4* __re
 	t.z = (t.z * sample_count + c.z) / inv; t.w = (t.w * sample_count + c.w) / inv;
 	accum[i] = t;
 }
-// render_buffer.cu:529-560: background blend, exposure, optional sRGB, clamp; linear device buffer instead of a surface
-__global__ void tonemap_kernel(const float4* __restrict__ accum, float4* __restrict__ out, uint32_t n, int to_srgb, float exposure_scale, float4 bg) {
+// tonemap curves (ETonemapCurve: 0 Identity, 1 ACES, 2 Hable, 3 Reinhard; src/render_buffer.cu:264-321)
+__device__ __forceinline__ void tonemap_curve(float& r, float& g, float& b, int curve) {
+	if (curve == 0) return;
+	r = fmaxf(r, 0.0f); g = fmaxf(g, 0.0f); b = fmaxf(b, 0.0f);
+	float k0, k1, k2, k3, k4, k5;
+	if (curve == 1) {
+		k0 = 0.6f * 0.6f * 2.51f; k1 = 0.6f * 0.03f; k2 = 0.0f; k3 = 0.6f * 0.6f * 2.43f; k4 = 0.6f * 0.59f; k5 = 0.14f;
+	} else if (curve == 2) {
+		const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+		k0 = A * F - A * E; k1 = C * B * F - B * E; k2 = 0.0f; k3 = A * F; k4 = B * F; k5 = D * F * F;
+		const float W = 11.2f;
+		const float nom = k0 * (W * W) + k1 * W + k2, denom = k3 * (W * W) + k4 * W + k5;
+		const float white_scale = denom / nom;
+		k0 = 4.0f * k0 * white_scale; k1 = 2.0f * k1 * white_scale; k2 = k2 * white_scale; k3 = 4.0f * k3; k4 = 2.0f * k4;
+	} else {
+		const float Y = 0.2126f * r + 0.7152f * g + 0.0722f * b;
+		const float s = 1.f / (Y + 1.0f);
+		r *= s; g *= s; b *= s;
+		return;
+	}
+	r = (r * r * k0 + k1 * r + k2) / (k3 * (r * r) + k4 * r + k5);
+	g = (g * g * k0 + k1 * g + k2) / (k3 * (g * g) + k4 * g + k5);
+	b = (b * b * k0 + k1 * b + k2) / (k3 * (b * b) + k4 * b + k5);
+}
+// render_buffer.cu:529-560 (accumulation in linear colours): background blend, exposure, curve, optional sRGB, optional alpha
+// un-multiply, optional clamp; linear device buffer instead of a surface
+__global__ void tonemap_kernel(const float4* __restrict__ accum, float4* __restrict__ out, uint32_t n, int to_srgb, float exposure_scale, float4 bg,
+	int curve, int clamp_output, int unmultiply_alpha) {
 	uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	float4 c = accum[i];
 	float w = (1.f - c.w) * bg.w;
 	c.x += srgb_to_linear(bg.x) * w; c.y += srgb_to_linear(bg.y) * w; c.z += srgb_to_linear(bg.z) * w; c.w += w;
 	c.x *= exposure_scale; c.y *= exposure_scale; c.z *= exposure_scale;
+	tonemap_curve(c.x, c.y, c.z, curve);
 	if (to_srgb) { c.x = linear_to_srgb(c.x); c.y = linear_to_srgb(c.y); c.z = linear_to_srgb(c.z); }
-	c.x = fminf(fmaxf(c.x, 0.f), 1.f); c.y = fminf(fmaxf(c.y, 0.f), 1.f); c.z = fminf(fmaxf(c.z, 0.f), 1.f); c.w = fminf(fmaxf(c.w, 0.f), 1.f);
+	if (unmultiply_alpha && c.w > 0.0f) { c.x /= c.w; c.y /= c.w; c.z /= c.w; }
+	if (clamp_output) { c.x = fminf(fmaxf(c.x, 0.f), 1.f); c.y = fminf(fmaxf(c.y, 0.f), 1.f); c.z = fminf(fmaxf(c.z, 0.f), 1.f); c.w = fminf(fmaxf(c.w, 0.f), 1.f); }
 	out[i] = c;
 }
 
@@ -310,8 +338,8 @@ void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in,
 void launch_accumulate(const float4* frame, float4* accum, uint32_t n, uint32_t spp_index, cudaStream_t s) {
 	accumulate_kernel<<<(n + 255) / 256, 256, 0, s>>>(frame, accum, n, (float)spp_index);
 }
-void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* bg, cudaStream_t s) {
-	tonemap_kernel<<<(n + 255) / 256, 256, 0, s>>>(accum, out, n, to_srgb, exp2f(exposure), make_float4(bg[0], bg[1], bg[2], bg[3]));
+void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* bg, int curve, int clamp_output, int unmultiply_alpha, cudaStream_t s) {
+	tonemap_kernel<<<(n + 255) / 256, 256, 0, s>>>(accum, out, n, to_srgb, exp2f(exposure), make_float4(bg[0], bg[1], bg[2], bg[3]), curve, clamp_output, unmultiply_alpha);
 }
 void launch_pack_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float* packed, bool unpack, cudaStream_t s) {
 	uint32_t tiles = ((w + tw - 1) / tw) * ((h + th - 1) / th);

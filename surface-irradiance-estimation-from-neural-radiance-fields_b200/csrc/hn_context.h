@@ -51,6 +51,7 @@ struct Options {
 	float focus_z = 1.0f;                       // m_slice_plane_z + m_scale
 	float parallax_shift[3] = {0, 0, 0};        // m_parallax_shift
 	float render_aabb[6] = {0, 0, 0, 1, 1, 1};
+	float render_aabb_to_local[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; // m_render_aabb_to_local, column-major (crop box rotation)
 	float train_aabb[6] = {0, 0, 0, 1, 1, 1};   // m_geometry.nerfBoundingBox / m_aabb
 	int max_cascade = 0;
 	float cone_angle_constant = 0.0f;           // 0 for aabb_scale <= 1 (src/testbed_nerf.cu:2736), else 1/256
@@ -69,6 +70,8 @@ struct Options {
 	int depth_merge_clip = 0;
 	int render_nerf = 1, render_mesh = 1;
 	float exposure = 0.f;
+	int tonemap_curve = 0;                      // ETonemapCurve: 0 Identity, 1 ACES, 2 Hable, 3 Reinhard (render_buffer.cu:264-321)
+	int clamp_output_color = 1, unmultiply_alpha = 0; // render_buffer.cu:552-558
 	float background_color[4] = {0, 0, 0, 1};
 	float fov_axis = 1;
 	float relative_focal_length[2] = {1.057161212f, 1.057161212f}; // fov 50.625 deg on axis 1 (src/testbed.cu:541-568)

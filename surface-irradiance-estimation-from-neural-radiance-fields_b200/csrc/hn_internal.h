@@ -55,6 +55,7 @@ struct FrameArgs {
 	float aperture_size, focus_z;  // depth of field: focus_z = slice_plane_z + scale (src/testbed_nerf.cu:2342)
 	float parallax_shift[3];
 	float render_aabb[6], train_aabb[6];
+	float aabb_to_local[9]; int crop_rotated; // m_render_aabb_to_local (column-major); crop_rotated = 0 -> identity, skipped
 	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
 	uint32_t max_mip;
 	float cone_angle;
@@ -146,7 +147,7 @@ void launch_composite(const FrameArgs& a, RaySoA rays, const uint32_t* alive_in,
 	uint32_t* counters, const float4* samples, const uint32_t* sample_counts, const uint2* net_out,
 	float4* frame, float* depth_buffer, uint32_t max_rays, cudaStream_t s);
 void launch_accumulate(const float4* frame, float4* accum, uint32_t n, uint32_t spp_index, cudaStream_t s);
-void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* background, cudaStream_t s);
+void launch_tonemap(const float4* accum, float4* out, uint32_t n, int to_srgb, float exposure, const float* background, int curve, int clamp_output, int unmultiply_alpha, cudaStream_t s);
 void launch_pack_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float* packed, bool unpack, cudaStream_t s);
 
 // mesh TU (exact flags as well)

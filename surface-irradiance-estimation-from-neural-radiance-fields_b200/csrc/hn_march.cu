@@ -174,15 +174,26 @@ __device__ __forceinline__ uint32_t mip_from_pos(V3 pos) {
 	frexpf(maxval, &exponent);
 	return (uint32_t)min(max(exponent + 1, 0), (int)CASCADES - 1);
 }
+// crop box test with the optional rotation render_aabb_to_local (src/testbed_nerf.cu:1530-1532, nerf_device.cuh:461-495):
+// R = nullptr is the axis-aligned box (the common case costs one uniform predicate)
+__device__ __forceinline__ V3 to_crop_local(const float* __restrict__ R, V3 v) {
+	if (!R) return v;
+	V3 r = mk(0.0f, 0.0f, 0.0f);
+	r.x += R[0] * v.x; r.y += R[1] * v.x; r.z += R[2] * v.x;
+	r.x += R[3] * v.y; r.y += R[4] * v.y; r.z += R[5] * v.y;
+	r.x += R[6] * v.z; r.y += R[7] * v.z; r.z += R[8] * v.z;
+	return r;
+}
+#define HN_CROP_R(a) ((a).crop_rotated ? (a).aabb_to_local : nullptr)
 // nerf_device.cuh:461-495 (iter_cap == 0) / :497-534 (iter_cap == 200)
 // t_far: parameter beyond which the ray has left the (inflated) bounds of every set occupancy cell. No sample can follow, so
 // the reference's loop is bound to end in MAX_DEPTH there; returning it at once is exact and removes the cell-by-cell walk
 // through empty space to the edge of the render box.
 __device__ float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bits, uint32_t min_mip, uint32_t max_mip,
-	const Box& aabb, int iter_cap, float t_far) {
+	const Box& aabb, int iter_cap, float t_far, const float* __restrict__ R = nullptr) {
 	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
 		V3 pos = o + t * d;
-		if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) return MAX_DEPTH_F;
+		if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(R, pos))) return MAX_DEPTH_F;
 		uint32_t mip = min(max(mip_from_pos(pos), min_mip), max_mip);
 		if (!bits || occupied_at(pos, bits, mip)) return t;
 		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
@@ -218,12 +229,13 @@ __device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, 
 	if (!pixel_ray(a, x, y, o, d)) return false; // invalid ray (f-theta lens outside its image circle)
 	uint32_t idx = x + (uint32_t)a.w * y;
 	Box aabb = ldbox(a.render_aabb);
-	float t = fmaxf(box_ray_intersect(aabb, o, d).x, 0.0f) + 1e-6f;
+	const float* R = HN_CROP_R(a);
+	float t = fmaxf(box_ray_intersect(aabb, to_crop_local(R, o), to_crop_local(R, d)).x, 0.0f) + 1e-6f;
 	t_out = MAX_DEPTH_F;
-	if (!box_contains(aabb, o + t * d)) return false;
+	if (!box_contains(aabb, to_crop_local(R, o + t * d))) return false;
 	V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
 	t = advance_n_steps(t, a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
-	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, occ_t_far(a, bits, o, d));
+	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, occ_t_far(a, bits, o, d), R);
 	if (t >= MAX_DEPTH_F) return false;
 	t_out = t;
 	return true;
@@ -283,10 +295,11 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 			const float4 ot = rays.o_t[r], dm = rays.d_mw[r];
 			const V3 o = mk(ot.x, ot.y, ot.z), d = mk(dm.x, dm.y, dm.z);
 			const Box aabb = ldbox(a.render_aabb);
-			t = fmaxf(box_ray_intersect(aabb, o, d).x, 0.0f) + 1e-6f;
-			if (box_contains(aabb, o + t * d)) {
+			const float* R = HN_CROP_R(a);
+			t = fmaxf(box_ray_intersect(aabb, to_crop_local(R, o), to_crop_local(R, d)).x, 0.0f) + 1e-6f;
+			if (box_contains(aabb, to_crop_local(R, o + t * d))) {
 				const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-				t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, occ_t_far(a, bits, o, d));
+				t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, occ_t_far(a, bits, o, d), R);
 				alive = t < MAX_DEPTH_F;
 			}
 		}
@@ -323,7 +336,7 @@ __device__ __forceinline__ uint32_t flat_march(const FrameArgs& a, const uint8_t
 		V3 pos = o;
 		if (active) {
 			pos = o + t * d;
-			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) {
+			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(HN_CROP_R(a), pos))) {
 				active = false;
 			} else {
 				mip = min(max(mip_from_pos(pos), 0u), a.max_mip);
@@ -430,7 +443,7 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 		V3 pos = o;
 		if (active) {
 			pos = o + t * d;
-			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, pos)) {
+			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(HN_CROP_R(a), pos))) {
 				t = MAX_DEPTH_F; active = false;
 			} else {
 				mip = a.max_mip ? min(max(mip_from_pos(pos), 0u), a.max_mip) : 0u; // one cascade: the clamp makes it 0 whatever frexpf says
@@ -485,7 +498,7 @@ __global__ void __launch_bounds__(128) march_all_kernel(FrameArgs a, const uint8
 		float t = t0[i];
 		const float t_far = occ_t_far(a, bits, o, d);
 		while (true) {
-			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far);
+			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far, HN_CROP_R(a));
 			if (t >= MAX_DEPTH_F) break;
 			float dt = calc_dt(t, a.cone_angle);
 			if (samples && c < max_per_ray) {

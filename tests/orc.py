@@ -40,7 +40,8 @@ class RenderParams(C.Structure):
                 ("brdf", f32 * 15), ("compat_nearest_aabb_only", i32), ("depth_merge_clip", i32), ("n_threads", i32),
                 ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p),
                 ("render_mode", i32), ("depth_scale", f32),
-                ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3)]
+                ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3),
+                ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9)]
 
 
 def P(a):
@@ -107,7 +108,8 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   rgb_act=2, density_act=3, linear_colors=False, dda_iter_cap=0, mesh_aabb=(0, 0, 0, 1, 1, 1),
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
                   clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
-                  lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0)) -> RenderParams:
+                  lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0),
+                  render_aabb_to_local=None) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -140,6 +142,10 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.lens_mode, p.aperture_size, p.focus_z = int(lens_mode), float(aperture_size), float(focus_z)
     p.lens_params[:] = [float(v) for v in lens_params]
     p.parallax_shift[:] = [float(v) for v in parallax_shift]
+    ident = [1, 0, 0, 0, 1, 0, 0, 0, 1]
+    R = ident if render_aabb_to_local is None else [float(v) for v in np.asarray(render_aabb_to_local, np.float32).reshape(9)]
+    p.render_aabb_to_local[:] = R
+    p.crop_rotated = int(any(abs(a - b) > 0 for a, b in zip(R, ident)))
     if envmap is not None:
         env = np.ascontiguousarray(envmap, np.float32)
         assert env.ndim == 3 and env.shape[2] == 4
@@ -278,6 +284,16 @@ def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):
     total = lib.orc_render_frame(scene.h if scene is not None else None, C.byref(p), C.byref(cfg) if cfg is not None else None,
                                  P(params) if params is not None else None, P(bits) if bits is not None else None, P(frame), P(depth), P(steps))
     return frame, depth, steps.reshape(p.height, p.width), int(total)
+
+
+def tonemap(accum, to_srgb, exposure, bg, curve, clamp_output=True, unmultiply_alpha=False):
+    """oracle tonemap_kernel on an (..., 4) linear accumulation buffer"""
+    a = np.ascontiguousarray(accum, dtype=np.float32)
+    out = np.empty_like(a)
+    bgv = np.asarray(bg, np.float32)
+    lib.orc_tonemap(P(a), C.c_uint32(a.size // 4), C.c_int32(int(to_srgb)), C.c_float(float(exposure)), P(bgv), C.c_int32(int(curve)),
+                    C.c_int32(int(clamp_output)), C.c_int32(int(unmultiply_alpha)), P(out))
+    return out
 
 
 def uv_to_ray(p: RenderParams, spp, uv, use_lens=True):

@@ -220,3 +220,34 @@ def test_unbuilt_render_modes_fail_loudly(base, hn):
                 tb.render(32, 32, 1, True)
         finally:
             tb.set_option("render_mode", 1.0)
+
+
+@pytest.mark.parametrize("curve,name", [(0, "Identity"), (1, "ACES"), (2, "Hable"), (3, "Reinhard")])
+def test_tonemap_curves(base, hn, orc, curve, name):
+    """tonemap_kernel (src/render_buffer.cu:264-343,529-560): background blend, 2^exposure, curve, sRGB output, alpha
+    un-multiply, clamp — product against the oracle restatement applied to the product's own raw accumulation buffer
+    (2 spp, curve Identity, no clamp, transparent background)."""
+    tb, _, _, _ = base
+    cam = hn.synthetic.look_at_camera((1.4, 1.2, 1.6), (0.5, 0.5, 0.5))
+    tb.set_camera_cols(cam)
+    saved = tb.background_color
+    try:
+        tb.set_option("clamp_output_color", 0.0)
+        tb.background_color = [0, 0, 0, 0]
+        raw = tb.render(128, 96, 2, True).copy()
+        assert raw[..., 3].max() > 0.5 and raw[..., :3].max() > 0.05
+        bg = [0.3, 0.5, 0.8, 1.0]
+        tb.background_color = bg
+        tb.exposure = 1.5
+        tb.set_option("tonemap_curve", float(curve))
+        for clamp, unmul, linear in ((1, 0, False), (0, 1, False), (1, 0, True)):
+            tb.set_option("clamp_output_color", float(clamp))
+            tb.set_option("unmultiply_alpha", float(unmul))
+            img = tb.render(128, 96, 2, linear)
+            ref = orc.tonemap(raw, not linear, 1.5, bg, curve, clamp, unmul)
+            assert np.allclose(img, ref, rtol=1e-4, atol=2e-5), (name, clamp, unmul, linear, np.abs(img - ref).max())
+    finally:
+        tb.background_color = saved
+        tb.exposure = 0.0
+        for k, v in (("tonemap_curve", 0.0), ("clamp_output_color", 1.0), ("unmultiply_alpha", 0.0)):
+            tb.set_option(k, v)

@@ -39,7 +39,7 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // aligned 2-entry block (always for even x: the hash only XORs x in, dense rows are contiguous) ONE load brings both, which
 // removes a quarter of the gather instructions and of the L1 wavefronts. Values and the order of the fp16 FMAs are those
 // of tcnn's kernel_grid (grid.h:94-168), so the result stays bit-identical to the oracle.
-template <int F, uint32_t TEXMASK = 0>
+template <int F, uint32_t TEXMASK = 0, int NDENSE = -1>
 __device__ __forceinline__ void encode_sample(const GridLevels& g, const __half* __restrict__ table, float px, float py, float pz, uint32_t (&enc)[16],
 	cudaTextureObject_t tex16 = 0, cudaTextureObject_t tex8 = 0, uint32_t tex_base = 0) {
 	constexpr int L = 32 / F;
@@ -54,7 +54,9 @@ __device__ __forceinline__ void encode_sample(const GridLevels& g, const __half*
 		uint32_t gx = (uint32_t)(int)flx, gy = (uint32_t)(int)fly, gz = (uint32_t)(int)flz;
 		fx -= flx; fy -= fly; fz -= flz;
 		float wx[2] = {__fsub_rn(1.0f, fx), fx}, wy[2] = {__fsub_rn(1.0f, fy), fy}, wz[2] = {__fsub_rn(1.0f, fz), fz};
-		const bool hashed = g.hashed[l] != 0;
+		// NDENSE >= 0: the launcher has checked that exactly the first NDENSE levels are dense and every hashed level has a
+		// power-of-two table, so the level kind and the index reduction are compile-time per unrolled level
+		const bool hashed = NDENSE >= 0 ? (l >= NDENSE) : (g.hashed[l] != 0);
 		// grid_index (common_device.h:690-707): dense x + y*R + z*R^2, or coherent prime hash; then % hashmap_size
 		// (a power-of-two size is a mask; a dense index below the size needs no reduction at all)
 		uint32_t idx[8];
@@ -62,7 +64,8 @@ __device__ __forceinline__ void encode_sample(const GridLevels& g, const __half*
 		for (int c = 0; c < 8; ++c) {
 			uint32_t x = gx + (c & 1), y = gy + ((c >> 1) & 1), z = gz + ((c >> 2) & 1);
 			uint32_t i = hashed ? (x ^ (y * 2654435761u) ^ (z * 805459861u)) : (x + y * res + z * res * res);
-			idx[c] = mask ? (i & mask) : (i < size ? i : i % size);
+			if (NDENSE >= 0) idx[c] = (l >= NDENSE) ? (i & mask) : (i < size ? i : i % size);
+			else idx[c] = mask ? (i & mask) : (i < size ? i : i % size);
 		}
 		if (F == 4) {
 			uint2 v[8];

@@ -148,7 +148,7 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 // group's gather overlaps the other groups' MMA rounds.
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
 
-template <int F, int G, bool FUSED, bool DONLY, uint32_t TEXMASK = 0>
+template <int F, int G, bool FUSED, bool DONLY, uint32_t TEXMASK = 0, int NDENSE = -1>
 __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
 	const int grp = threadIdx.x >> 7;                     // tile group of this thread
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 				const float px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
 				const float py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
 				const float pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
-				encode_sample<F, TEXMASK>(a.g, a.table, px, py, pz, enc, a.tex16, a.tex8, a.tex_base);
+				encode_sample<F, TEXMASK, NDENSE>(a.g, a.table, px, py, pz, enc, a.tex16, a.tex8, a.tex_base);
 			}
 			#pragma unroll
 			for (int c = 0; c < 4; ++c)
@@ -308,16 +308,20 @@ void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStre
 	uint32_t ctas = (tiles + G - 1) / G;
 	uint32_t persistent = (uint32_t)sm_count * 2u;
 	uint32_t blocks = ctas < persistent ? ctas : persistent;
-	#define HN_LAUNCH_TC(FF, FU, DO, TM) do { \
-		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO, TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		tc::eval_tc_kernel<FF, G, FU, DO, TM><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
+	#define HN_LAUNCH_TC(FF, FU, DO, TM, ND) do { \
+		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO, TM, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+		tc::eval_tc_kernel<FF, G, FU, DO, TM, ND><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
 	// F = 4 with texture objects: the five fine levels (3..7, the hashed ones of the base config) are gathered through the TEX
 	// pipe, the three coarse ones through the LSU pipe. Measured on B200 (profiles/r01_tex_probe.txt): eval 7.03 -> 6.53 ms per
 	// 1080p frame, bit-identical output; every other split of (level, corner pair) between the two pipes was slower.
 	constexpr uint32_t TM = 0xFFFFF000u;
-	if (F == 4 && a.tex16) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM); else HN_LAUNCH_TC(4, false, false, TM); }
-	else if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true, 0u); else if (a.fused) HN_LAUNCH_TC(4, true, false, 0u); else HN_LAUNCH_TC(4, false, false, 0u); }
-	else { if (a.density_only) HN_LAUNCH_TC(2, false, true, 0u); else if (a.fused) HN_LAUNCH_TC(2, true, false, 0u); else HN_LAUNCH_TC(2, false, false, 0u); }
+	// level layout of configs/nerf/base.json (3 dense levels, then hashed power-of-two tables): level kind compiled in
+	bool base_layout = F == 4;
+	for (int l = 0; l < 8 && base_layout; ++l) base_layout = l < 3 ? (a.g.hashed[l] == 0) : (a.g.hashed[l] != 0 && a.g.mask[l] != 0);
+	if (F == 4 && a.tex16 && base_layout) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM, 3); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM, -1); else HN_LAUNCH_TC(4, false, false, TM, 3); }
+	else if (F == 4 && a.tex16) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM, -1); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM, -1); else HN_LAUNCH_TC(4, false, false, TM, -1); }
+	else if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true, 0u, -1); else if (a.fused) HN_LAUNCH_TC(4, true, false, 0u, -1); else HN_LAUNCH_TC(4, false, false, 0u, -1); }
+	else { if (a.density_only) HN_LAUNCH_TC(2, false, true, 0u, -1); else if (a.fused) HN_LAUNCH_TC(2, true, false, 0u, -1); else HN_LAUNCH_TC(2, false, false, 0u, -1); }
 	#undef HN_LAUNCH_TC
 }
 

@@ -75,6 +75,8 @@ float orc_srgb_to_linear(float v);
 // uv_to_ray with the lens / depth-of-field / parallax fields of p (direction not normalised); returns 0 for an invalid ray
 int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]);
 // tonemap_kernel (src/render_buffer.cu:529-560) on a linear accumulation buffer; curve = ETonemapCurve (0 Identity, 1 ACES, 2 Hable, 3 Reinhard)
+float orc_density_input_gradient(const orc_net_config* c, const uint16_t* params, const float wp[3], float grad[3]);
+float orc_density_raw_f32(const orc_net_config* c, const uint16_t* params, const float wp[3]);
 void orc_tonemap(const float* accum, uint32_t n, int32_t to_srgb, float exposure, const float bg[4], int32_t curve, int32_t clamp_output,
 	int32_t unmultiply_alpha, float* out);
 void orc_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]);

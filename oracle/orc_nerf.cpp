@@ -526,6 +526,79 @@ half_t density_one(const Net& n, const float* warped_pos) {
 	return d_out[0];
 }
 
+// NerfNetwork::input_gradient(dim 3) (src/testbed_nerf.cu:2106-2107): gradient of the raw density output with respect to
+// the warped position, through the density MLP (fully_fused_mlp backward: transposed weights, ReLU masks of the forward
+// activations) and the grid encoding (grid.h:170-212: per feature, scale * sum over the corner pairs along the dimension of
+// w_other * (v_right - v_left)). fp32 here; the reference runs the MLP part in fp16. Returns the raw density (fp16-rounded).
+float density_input_gradient(const Net& n, const float* wp, float grad[3]) {
+	half_t enc[32];
+	encode_one(n.grid, n.table, wp, enc);
+	const MlpShape& s = n.density;
+	const half_t* w = n.w_density;
+	std::vector<std::vector<float>> act(s.hidden_layers, std::vector<float>(64));
+	for (uint32_t o = 0; o < 64; ++o) {
+		float acc = 0.0f;
+		for (uint32_t i = 0; i < s.in; ++i) acc += h2f(w[o * s.in + i]) * h2f(enc[i]);
+		act[0][o] = h2f(f2h(std::max(acc, 0.0f)));
+	}
+	const half_t* wl = w + 64 * s.in;
+	for (uint32_t l = 1; l < s.hidden_layers; ++l) {
+		for (uint32_t o = 0; o < 64; ++o) {
+			float acc = 0.0f;
+			for (uint32_t i = 0; i < 64; ++i) acc += h2f(wl[o * 64 + i]) * act[l - 1][i];
+			act[l][o] = h2f(f2h(std::max(acc, 0.0f)));
+		}
+		wl += 64 * 64;
+	}
+	float raw = 0.0f;
+	std::vector<float> g(64), gp(64);
+	for (uint32_t i = 0; i < 64; ++i) { float wv = h2f(wl[i]); raw += wv * act[s.hidden_layers - 1][i]; g[i] = act[s.hidden_layers - 1][i] > 0.0f ? wv : 0.0f; }
+	raw = h2f(f2h(raw));
+	for (uint32_t l = s.hidden_layers - 1; l >= 1; --l) {
+		const half_t* wm = w + 64 * s.in + (size_t)(l - 1) * 64 * 64;
+		for (uint32_t i = 0; i < 64; ++i) {
+			float acc = 0.0f;
+			for (uint32_t o = 0; o < 64; ++o) acc += h2f(wm[o * 64 + i]) * g[o];
+			gp[i] = act[l - 1][i] > 0.0f ? acc : 0.0f;
+		}
+		g = gp;
+	}
+	float genc[32] = {};
+	for (uint32_t o = 0; o < 64; ++o) for (uint32_t i = 0; i < s.in; ++i) genc[i] += h2f(w[o * s.in + i]) * g[o];
+	grad[0] = grad[1] = grad[2] = 0.0f;
+	const GridLayout& gl = n.grid;
+	for (uint32_t level = 0; level < gl.L; ++level) {
+		const half_t* grid = n.table + (size_t)gl.offsets[level] * gl.F;
+		uint32_t hashmap_size = gl.offsets[level + 1] - gl.offsets[level];
+		float scale = gl.scales[level];
+		uint32_t res = gl.res[level];
+		float pos[3]; uint32_t pg[3];
+		for (int d = 0; d < 3; ++d) { float v = std::fmaf(scale, wp[d], 0.5f); float fl = std::floor(v); pg[d] = (uint32_t)(int)fl; pos[d] = v - fl; }
+		for (uint32_t f = 0; f < gl.F; ++f) {
+			float ge = genc[level * gl.F + f] * scale;
+			for (int gd = 0; gd < 3; ++gd) {
+				float acc = 0.0f;
+				for (uint32_t idx = 0; idx < 4; ++idx) {
+					float weight = 1.0f;
+					uint32_t pl[3];
+					for (int nd = 0; nd < 2; ++nd) {
+						int dim = nd >= gd ? nd + 1 : nd;
+						if ((idx & (1u << nd)) == 0) { weight *= 1 - pos[dim]; pl[dim] = pg[dim]; }
+						else { weight *= pos[dim]; pl[dim] = pg[dim] + 1; }
+					}
+					pl[gd] = pg[gd];
+					float left = h2f(grid[grid_index(hashmap_size, res, pl[0], pl[1], pl[2]) * gl.F + f]);
+					pl[gd] = pg[gd] + 1;
+					float right = h2f(grid[grid_index(hashmap_size, res, pl[0], pl[1], pl[2]) * gl.F + f]);
+					acc += weight * (right - left);
+				}
+				grad[gd] += ge * acc;
+			}
+		}
+	}
+	return raw;
+}
+
 // ---------------------------------------------------------------- nerf_device.cuh:203-314
 static float logistic(float x) { return 1.0f / (1.0f + std::exp(-x)); }
 static float network_to_rgb(float v, int act) {
@@ -543,6 +616,16 @@ static float network_to_density(float v, int act) {
 		case 1: return v > 0.0f ? v : 0.0f;
 		case 2: return logistic(v);
 		case 3: return std::exp(v);
+	}
+	return 0.0f;
+}
+// nerf_device.cuh:245-254
+static float network_to_density_derivative(float v, int act) {
+	switch (act) {
+		case 0: return 1.0f;
+		case 1: return v > 0.0f ? 1.0f : 0.0f;
+		case 2: { float d = logistic(v); return d * (1 - d); }
+		case 3: return std::exp(std::min(std::max(v, -15.0f), 15.0f));
 	}
 	return 0.0f;
 }
@@ -702,6 +785,13 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 				else if (p.render_mode == 12) rgb = wp;
 				else if (p.render_mode == 7) { float z = dot(cam_fwd, pos - r.o) * p.depth_scale; rgb = {z, z, z}; }
 				else if (p.render_mode == 0) rgb = {alpha, alpha, alpha};
+				else if (p.render_mode == 5) { // :688-693 normal = -d sigma/d raw * (gradient of the raw density w.r.t. the network input), normalised; fp16 like the product's sample record
+					float gr[3];
+					float raw = density_input_gradient(net, coord, gr);
+					float der = network_to_density_derivative(raw, p.density_activation);
+					vec3 nrm = normalize(vec3{-der * gr[0], -der * gr[1], -der * gr[2]});
+					rgb = {h2f(f2h(nrm.x)), h2f(f2h(nrm.y)), h2f(f2h(nrm.z))};
+				}
 				rgba.x += rgb.x * weight; rgba.y += rgb.y * weight; rgba.z += rgb.z * weight; rgba.w += weight;
 				if (weight > max_weight) { max_weight = weight; local_depth = dot(cam_fwd, pos - cam_pos); }
 				if (rgba.w > (1.0f - p.min_transmittance)) {
@@ -717,6 +807,7 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			if (depth_test && !p.depth_merge_clip && local_depth > depth[idx]) continue; // geometry :1843-1846
 			vec4 tmp = rgba;
 			if (p.render_mode == 9) { float col = (float)n / 128.0f; tmp = {col, col, col, 1.0f}; } // shade_kernel_nerf :1381-1383
+			if (p.render_mode == 5) { vec3 nn = normalize(vec3{rgba.x, rgba.y, rgba.z}); tmp.x = (0.5f * nn.x + 0.5f) * rgba.w; tmp.y = (0.5f * nn.y + 0.5f) * rgba.w; tmp.z = (0.5f * nn.z + 0.5f) * rgba.w; } // :1379-1381
 			if (!p.linear_colors && p.render_mode >= 1 && p.render_mode <= 4) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); } // :1391-1394
 			float* fb = frame + 4 * (size_t)idx;
 			float ia = 1.0f - tmp.w;
@@ -854,6 +945,19 @@ float orc_nerf_transmittance(const orc_render_params* p, const orc_net_config* c
 // loss_type 0 L2, 1 Huber: out = loss[3], gradient[3] (nerf_device.cuh:74-112,640-655)
 void orc_loss_and_gradient(const float target[3], const float pred[3], int32_t loss_type, float out[6]) {
 	for (int k = 0; k < 3; ++k) out[k] = loss_grad(loss_type, target[k], pred[k], out[3 + k]);
+}
+// Normals mode: raw density and its gradient w.r.t. the warped position (returns raw)
+float orc_density_input_gradient(const orc_net_config* c, const uint16_t* params, const float wp[3], float grad[3]) {
+	Net net = make_net(*c, params);
+	return density_input_gradient(net, wp, grad);
+}
+// all-fp32 raw density of the same weights (finite-difference witness for the gradient above; tests only)
+float orc_density_raw_f32(const orc_net_config* c, const uint16_t* params, const float wp[3]) {
+	Net net = make_net(*c, params);
+	std::vector<float> acts(mlp_act_size(net.density));
+	encode_f32(net.grid, net.table, wp, acts.data(), nullptr, nullptr);
+	mlp_forward_f32(net.density, net.w_density, acts.data());
+	return acts[net.density.in + 64 * net.density.hidden_layers];
 }
 float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, uint32_t n_rays,
 	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, int32_t loss_type, float loss_scale,

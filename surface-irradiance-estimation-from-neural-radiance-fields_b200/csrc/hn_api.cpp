@@ -408,6 +408,8 @@ uint32_t run_passes(hn_context* ctx, const FrameArgs& a, RaySoA rays, float4* fr
 		if (fused) ctx->survive.ensure(n_alive);
 		launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, lists[cur], rays, nullptr, n_alive_ptr, n_alive, ctx->net_out.p,
 			ctx->opt.eval_impl, fused ? frame : nullptr, depth, ctx->survive.p, cnt, s, light, param_textures(ctx));
+		if (!light && a.render_mode == 5) // Normals: the density gradient replaces the colour of every sample
+			launch_normals(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, n_alive_ptr, n_alive, ctx->net_out.p, s);
 		tm.stop(light ? ms_dummy : st.ms_eval);
 		tm.start();
 		const bool per_ray = !light && !fused && ctx->opt.composite_impl == 1;
@@ -512,7 +514,8 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 		need(ctx->has_bitfield, "occupancy grid not set");
 		{
 			const int m = ctx->opt.render_mode;
-			need(m == 0 || (m >= 1 && m <= 4) || m == 6 || m == 7 || m == 9 || m == 12, "render_mode: AO, Shade, Positions, Depth, Cost and EncodingVis are built; Normals, Distortion and Slice are not");
+			need(m == 0 || (m >= 1 && m <= 7) || m == 9 || m == 12, "render_mode: AO, Shade, Normals, Positions, Depth, Cost and EncodingVis are built; Distortion and Slice are not");
+			need(m != 5 || ctx->net.density_hidden <= 2, "render_mode Normals: at most two hidden layers in the density network");
 			need((m >= 1 && m <= 4) || (ctx->opt.composite_impl == 1 && !ctx->opt.fuse_composite) || (ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite), "visualisation render modes need composite_impl 1");
 		}
 		ensure_rays(ctx, n_px);

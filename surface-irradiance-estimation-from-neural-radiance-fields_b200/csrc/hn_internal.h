@@ -132,6 +132,9 @@ void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays
 	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s);
 
 // network TU
+// ERenderMode::Normals: overwrite the (r,g,b) of the network output with the unit normal from the density gradient
+void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples, const uint32_t* sample_counts,
+	const uint32_t* n_chunks_ptr, uint32_t max_chunks, uint2* out, cudaStream_t s);
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 // The parameter buffer seen as 16-byte and 8-byte texels: the tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe.
 struct ParamTextures { cudaTextureObject_t tex16 = 0, tex8 = 0; const void* ptr = nullptr; };

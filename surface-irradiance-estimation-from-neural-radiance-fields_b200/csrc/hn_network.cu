@@ -216,6 +216,141 @@ void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const f
 	else encode_kernel<2><<<(n + 127) / 128, 128, 0, s>>>(g, table, positions, n, out);
 }
 
+// ---- ERenderMode::Normals (src/testbed_nerf.cu:2106-2107,688-693): NerfNetwork::input_gradient(dim 3) = gradient of the raw
+// density output with respect to the warped position, through the density MLP and the hash grid. A visualisation mode, so
+// plain CUDA cores and fp32: one thread per sample, density-MLP weights staged in shared memory.
+//   forward : enc (the bit-exact fp16 encoding) -> hidden layers (fp32 accumulate, fp16 activations as in inference)
+//   backward: one-hot on output 0 -> W_out row 0 masked by ReLU -> ... -> W_first^T -> 32 encoding gradients
+//   grid    : d enc[l,f] / d x_d = scale_l * sum over the 4 corner pairs along d of w_other * (v_hi - v_lo)   (grid.h:170-212)
+// The sample's (r,g,b) slots of the network output are overwritten with normalize(-dsigma/draw * grad) as fp16.
+template <int F>
+__global__ void __launch_bounds__(128) normals_kernel(GridLevels g, const __half* __restrict__ table, const __half* __restrict__ w_density, int hidden_layers,
+	float3 lo, float3 diag, const float4* __restrict__ samples, const uint32_t* __restrict__ sample_counts, const uint32_t* __restrict__ n_chunks_ptr,
+	uint32_t n_chunks, int density_act, uint2* __restrict__ out) {
+	extern __shared__ __half w_s[];
+	const int n_w = 64 * 32 + (hidden_layers - 1) * 64 * 64 + 16 * 64;
+	for (int i = threadIdx.x; i < n_w; i += blockDim.x) w_s[i] = w_density[i];
+	__syncthreads();
+	const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t chunk = idx >> 5, lane = idx & 31u;
+	uint32_t nc = n_chunks;
+	if (n_chunks_ptr) nc = min(nc, *n_chunks_ptr);
+	if (chunk >= nc) return;
+	const uint32_t count = sample_counts ? sample_counts[chunk] : CHUNK;
+	if (lane >= count) return;
+	const float4 s = __ldg(samples + idx);
+	const float px = __fdiv_rn(__fsub_rn(s.x, lo.x), diag.x), py = __fdiv_rn(__fsub_rn(s.y, lo.y), diag.y), pz = __fdiv_rn(__fsub_rn(s.z, lo.z), diag.z);
+	uint32_t encu[16];
+	encode_sample<F>(g, table, px, py, pz, encu);
+	float enc[32];
+	#pragma unroll
+	for (int k = 0; k < 16; ++k) { const __half2 h = *reinterpret_cast<const __half2*>(&encu[k]); enc[2 * k] = __low2float(h); enc[2 * k + 1] = __high2float(h); }
+	// forward through the hidden layers (at most 2, checked by the launcher)
+	float h0[64], h1[64];
+	const __half* w = w_s;
+	for (int o = 0; o < 64; ++o) {
+		float acc = 0.0f;
+		#pragma unroll
+		for (int i = 0; i < 32; ++i) acc += __half2float(w[o * 32 + i]) * enc[i];
+		h0[o] = __half2float(__float2half_rn(fmaxf(acc, 0.0f)));
+	}
+	w += 64 * 32;
+	if (hidden_layers == 2) {
+		for (int o = 0; o < 64; ++o) {
+			float acc = 0.0f;
+			for (int i = 0; i < 64; ++i) acc += __half2float(w[o * 64 + i]) * h0[i];
+			h1[o] = __half2float(__float2half_rn(fmaxf(acc, 0.0f)));
+		}
+		w += 64 * 64;
+	}
+	// raw density (output row 0) and the backward pass of its one-hot gradient
+	float raw = 0.0f;
+	float gl[64]; // gradient at the last hidden layer
+	{
+		const float* hl = hidden_layers == 2 ? h1 : h0;
+		for (int i = 0; i < 64; ++i) { const float wv = __half2float(w[i]); raw += wv * hl[i]; gl[i] = hl[i] > 0.0f ? wv : 0.0f; }
+	}
+	raw = __half2float(__float2half_rn(raw));
+	if (hidden_layers == 2) {
+		const __half* w2 = w_s + 64 * 32;
+		float gp[64];
+		for (int i = 0; i < 64; ++i) {
+			float acc = 0.0f;
+			for (int o = 0; o < 64; ++o) acc += __half2float(w2[o * 64 + i]) * gl[o];
+			gp[i] = h0[i] > 0.0f ? acc : 0.0f;
+		}
+		for (int i = 0; i < 64; ++i) gl[i] = gp[i];
+	}
+	float genc[32];
+	#pragma unroll
+	for (int i = 0; i < 32; ++i) genc[i] = 0.0f;
+	for (int o = 0; o < 64; ++o) {
+		const float go = gl[o];
+		#pragma unroll
+		for (int i = 0; i < 32; ++i) genc[i] += __half2float(w_s[o * 32 + i]) * go;
+	}
+	// hash grid: gradient of every feature with respect to the position
+	float gx = 0.0f, gy = 0.0f, gz = 0.0f;
+	constexpr int L = 32 / F;
+	for (int l = 0; l < L; ++l) {
+		const float scale = g.scale[l];
+		const uint32_t res = g.res[l], size = g.size[l], mask = g.mask[l];
+		const __half* __restrict__ lvl = table + (size_t)g.offset[l] * F;
+		float fx = fmaf(scale, px, 0.5f), fy = fmaf(scale, py, 0.5f), fz = fmaf(scale, pz, 0.5f);
+		const float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
+		const uint32_t x0 = (uint32_t)(int)flx, y0 = (uint32_t)(int)fly, z0 = (uint32_t)(int)flz;
+		fx -= flx; fy -= fly; fz -= flz;
+		const bool hashed = g.hashed[l] != 0;
+		float v[8][F];
+		#pragma unroll
+		for (int c = 0; c < 8; ++c) {
+			const uint32_t x = x0 + (c & 1), y = y0 + ((c >> 1) & 1), z = z0 + ((c >> 2) & 1);
+			uint32_t i = hashed ? (x ^ (y * 2654435761u) ^ (z * 805459861u)) : (x + y * res + z * res * res);
+			i = mask ? (i & mask) : (i < size ? i : i % size);
+			#pragma unroll
+			for (int f = 0; f < F; ++f) v[c][f] = __half2float(lvl[(size_t)i * F + f]);
+		}
+		const float wx[2] = {1.0f - fx, fx}, wy[2] = {1.0f - fy, fy}, wz[2] = {1.0f - fz, fz};
+		#pragma unroll
+		for (int f = 0; f < F; ++f) {
+			const float ge = genc[l * F + f] * scale;
+			float dx = 0.0f, dy = 0.0f, dz = 0.0f;
+			#pragma unroll
+			for (int b = 0; b < 2; ++b) {
+				#pragma unroll
+				for (int a2 = 0; a2 < 2; ++a2) {
+					dx += wy[a2] * wz[b] * (v[1 + 2 * a2 + 4 * b][f] - v[0 + 2 * a2 + 4 * b][f]);
+					dy += wx[a2] * wz[b] * (v[a2 + 2 + 4 * b][f] - v[a2 + 4 * b][f]);
+					dz += wx[a2] * wy[b] * (v[a2 + 2 * b + 4][f] - v[a2 + 2 * b][f]);
+				}
+			}
+			gx += ge * dx; gy += ge * dy; gz += ge * dz;
+		}
+	}
+	// network_to_density_derivative (nerf_device.cuh:245-254), normal = -derivative * gradient, normalised
+	float der = 1.0f;
+	if (density_act == 1) der = raw > 0.0f ? 1.0f : 0.0f;
+	else if (density_act == 2) { const float d = 1.0f / (1.0f + expf(-raw)); der = d * (1.0f - d); }
+	else if (density_act == 3) der = expf(fminf(fmaxf(raw, -15.0f), 15.0f));
+	float nx = -der * gx, ny = -der * gy, nz = -der * gz;
+	const float len = sqrtf(nx * nx + ny * ny + nz * nz);
+	nx /= len; ny /= len; nz /= len;
+	uint2 o = out[idx];
+	o.x = pack_h2(nx, ny);
+	o.y = (o.y & 0xFFFF0000u) | (pack_h2(nz, 0.0f) & 0xFFFFu);
+	out[idx] = o;
+}
+void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples, const uint32_t* sample_counts,
+	const uint32_t* n_chunks_ptr, uint32_t max_chunks, uint2* out, cudaStream_t s) {
+	if (!max_chunks) return;
+	const float3 lo = make_float3(fa.train_aabb[0], fa.train_aabb[1], fa.train_aabb[2]);
+	const float3 diag = make_float3(fa.train_aabb[3] - fa.train_aabb[0], fa.train_aabb[4] - fa.train_aabb[1], fa.train_aabb[5] - fa.train_aabb[2]);
+	const size_t smem = (size_t)(64 * 32 + (cfg.density_hidden - 1) * 64 * 64 + 16 * 64) * sizeof(__half);
+	const uint32_t blocks = (max_chunks * CHUNK + 127) / 128;
+	if (cfg.F == 4) normals_kernel<4><<<blocks, 128, smem, s>>>(g, params + cfg.grid_offset, params + cfg.density_w_offset, (int)cfg.density_hidden, lo, diag, samples, sample_counts, n_chunks_ptr, max_chunks, fa.density_act, out);
+	else normals_kernel<2><<<blocks, 128, smem, s>>>(g, params + cfg.grid_offset, params + cfg.density_w_offset, (int)cfg.density_hidden, lo, diag, samples, sample_counts, n_chunks_ptr, max_chunks, fa.density_act, out);
+}
+
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& fa, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
 	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,

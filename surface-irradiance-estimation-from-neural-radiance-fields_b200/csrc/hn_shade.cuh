@@ -34,7 +34,7 @@ struct CompArgs {
 	float cam_fwd[3], cam_pos[3];
 	float min_transmittance;
 	int rgb_act, density_act, linear_colors, depth_test, depth_clip;
-	int render_mode;              // ERenderMode (common.h:58-72): 0 AO, 1..4 Shade, 6 Positions, 7 Depth, 9 Cost, 12 EncodingVis
+	int render_mode;              // ERenderMode (common.h:58-72): 0 AO, 1..4 Shade, 5 Normals, 6 Positions, 7 Depth, 9 Cost, 12 EncodingVis
 	float depth_scale;            // 1 / dataset scale (src/testbed_nerf.cu:2121)
 	RaySoA rays;
 	float4* frame;
@@ -88,6 +88,7 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 			else if (a.render_mode == 12) { cr = (s.x - a.train_lo[0]) / a.train_diag[0]; cg = (s.y - a.train_lo[1]) / a.train_diag[1]; cb = (s.z - a.train_lo[2]) / a.train_diag[2]; }
 			else if (a.render_mode == 7) { cr = cg = cb = (a.cam_fwd[0] * (s.x - pre.o_t.x) + a.cam_fwd[1] * (s.y - pre.o_t.y) + a.cam_fwd[2] * (s.z - pre.o_t.z)) * a.depth_scale; }
 			else if (a.render_mode == 0) { cr = cg = cb = alpha; }
+			else if (a.render_mode == 5) { cr = __low2float(rg); cg = __high2float(rg); cb = __low2float(bs); } // unit normal written by normals_kernel (:688-693)
 		}
 		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
 		#pragma unroll
@@ -135,6 +136,10 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 	float4 tmp = rgba;
 	const bool shade_mode = a.render_mode >= 1 && a.render_mode <= 4; // only Shade (and Slice) accumulate in linear colours (shade_kernel_nerf :1391-1394)
 	if (a.render_mode == 9) { const float col = (float)n_steps / 128.0f; tmp = make_float4(col, col, col, 1.0f); } // Cost (:1381-1383)
+	if (a.render_mode == 5) { // Normals (:1379-1381): (0.5 n + 0.5) * alpha
+		const float len = sqrtf(rgba.x * rgba.x + rgba.y * rgba.y + rgba.z * rgba.z);
+		tmp.x = (0.5f * (rgba.x / len) + 0.5f) * rgba.w; tmp.y = (0.5f * (rgba.y / len) + 0.5f) * rgba.w; tmp.z = (0.5f * (rgba.z / len) + 0.5f) * rgba.w;
+	}
 	if (finished && !a.linear_colors && shade_mode) {
 		float c = lane == 0 ? rgba.x : (lane == 1 ? rgba.y : rgba.z);
 		c = srgb_to_linear(c);

@@ -187,7 +187,7 @@ def test_full_size_properties(base, hn):
     assert abs(frac_full - frac_q) < 0.01
 
 
-@pytest.mark.parametrize("mode,name", [(0, "AO"), (6, "Positions"), (7, "Depth"), (9, "Cost"), (12, "EncodingVis")])
+@pytest.mark.parametrize("mode,name", [(0, "AO"), (5, "Normals"), (6, "Positions"), (7, "Depth"), (9, "Cost"), (12, "EncodingVis")])
 def test_visualisation_render_modes(base, hn, orc, mode, name):
     """ERenderMode (common.h:58-72) other than Shade: the per-sample colour is replaced in compositing
     (src/testbed_nerf.cu:686-702), Cost paints n_steps/128 at the final blend (:1381-1383), and only Shade converts
@@ -207,13 +207,19 @@ def test_visualisation_render_modes(base, hn, orc, mode, name):
     assert np.abs(img[..., :3] - shaded[..., :3]).max() > 0.05, "mode did not change the picture"
     if mode == 9:
         assert np.array_equal(img, ref)
+    elif mode == 5:
+        # Normals: per-sample unit normal from the density gradient through MLP + hash grid (fp32 on both sides, summed in a
+        # different order), stored as fp16; where the density gradient nearly vanishes the direction is ill-conditioned
+        bad = np.abs(img - ref).max(axis=2) > 1e-2
+        assert bad.mean() <= 5e-3, (bad.sum(), np.abs(img - ref).max())
+        assert psnr(np.where(bad[..., None], ref, img), ref) >= 50.0
     else:
         assert np.abs(img - ref).max() <= 1e-2 and psnr(img, ref) >= 50.0, (name, np.abs(img - ref).max())
 
 
 def test_unbuilt_render_modes_fail_loudly(base, hn):
     tb, _, _, _ = base
-    for mode in (5, 8, 10):  # Normals (needs input gradients), Distortion, Slice
+    for mode in (8, 10):  # Distortion, Slice
         tb.set_option("render_mode", float(mode))
         try:
             with pytest.raises(RuntimeError):

@@ -114,3 +114,50 @@ def test_pcg32_pinned_against_golden(orc):
             out = np.zeros(8, np.uint32)
             orc.lib.orc_pcg32(int(sd), int(ad), 8, orc.P(out))
             assert np.array_equal(out, g["pcg_out"][a, b])
+
+
+def test_density_input_gradient_finite_differences(orc):
+    """Normals mode (NerfNetwork::input_gradient, src/testbed_nerf.cu:2106-2107): the oracle's analytic gradient of the raw
+    density w.r.t. the warped position against central differences of an all-fp32 forward pass of the same weights. The
+    step stays inside one cell of the finest level (1/2048), away from the cell faces where the interpolant has kinks."""
+    import ctypes as C
+    from importlib import import_module
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    synthetic = import_module("surface-irradiance-estimation-from-neural-radiance-fields_b200.synthetic") if False else None
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("hn_synthetic", os.path.join(root, "surface-irradiance-estimation-from-neural-radiance-fields_b200", "synthetic.py"))
+    synthetic = importlib.util.module_from_spec(spec); spec.loader.exec_module(synthetic)
+    L = orc.lib
+    L.orc_density_input_gradient.restype = C.c_float
+    L.orc_density_raw_f32.restype = C.c_float
+    for layers, nl, nf in ((1, 8, 4), (2, 16, 2)):
+        scale = float(np.exp(np.float32(np.log(np.float32(128.0 if nl == 8 else 2048.0 / 16)) / np.float32(nl - 1))))
+        cfg = orc.net_config(nl, nf, 19, 16, scale, layers, 2)
+
+        class Info:
+            n_levels, n_features_per_level, density_hidden_layers, rgb_hidden_layers = nl, nf, layers, 2
+            n_params = L.orc_n_params(C.byref(cfg))
+            grid_param_offset = L.orc_grid_param_offset(C.byref(cfg))
+        params = synthetic.random_params(Info, 11, 1.0)
+        rng = np.random.default_rng(5)
+        ok = 0
+        for _ in range(40):
+            # centre of a finest-level cell: fract(scale_max * p + 0.5) = 0.5 -> all coarser levels are away from a face by >= 2^-12
+            cell = rng.integers(100, 1900, 3)
+            wp = ((cell.astype(np.float64) + 0.5 - 0.5) / 2047.0 + 0.13 / 2047.0).astype(np.float32)
+            g = np.zeros(3, np.float32)
+            L.orc_density_input_gradient(C.byref(cfg), orc.P(params), orc.P(wp), orc.P(g))
+            h = np.float32(2e-5)
+            fd = np.zeros(3, np.float64)
+            for d in range(3):
+                a = wp.copy(); b = wp.copy(); a[d] += h; b[d] -= h
+                fd[d] = (float(L.orc_density_raw_f32(C.byref(cfg), orc.P(params), orc.P(a))) - float(L.orc_density_raw_f32(C.byref(cfg), orc.P(params), orc.P(b)))) / float(a[d] - b[d])
+            nrm = np.linalg.norm(fd)
+            if nrm < 1e-3:
+                continue
+            cos = float(np.dot(fd, g) / (nrm * np.linalg.norm(g)))
+            if cos > 0.99 and abs(np.linalg.norm(g) / nrm - 1) < 0.1:
+                ok += 1
+        assert ok >= 24, (layers, ok)  # of 40: central differences of a kinked interpolant, some points straddle a cell face of some level

@@ -350,6 +350,83 @@ void orc_scene_aabb(const orc_scene* s, float out[6]) {
 	out[0] = s->root.min.x; out[1] = s->root.min.y; out[2] = s->root.min.z;
 	out[3] = s->root.max.x; out[4] = s->root.max.y; out[5] = s->root.max.z;
 }
+// ---------------------------------------------------------------- triangle.cuh:39-41,66-147 (distance queries)
+static float sign1(float x) { return std::copysign(1.0f, x); }
+static float clamp01(float x) { return std::min(std::max(x, 0.0f), 1.0f); }
+static float tri_distance_sq(const Triangle& t, vec3 pos) {
+	vec3 v21 = t.b - t.a, p1 = pos - t.a, v32 = t.c - t.b, p2 = pos - t.b, v13 = t.a - t.c, p3 = pos - t.c;
+	vec3 nor = cross(v21, v13);
+	if (sign1(dot(cross(v21, nor), p1)) + sign1(dot(cross(v32, nor), p2)) + sign1(dot(cross(v13, nor), p3)) < 2.0f) {
+		vec3 e1 = v21 * clamp01(dot(v21, p1) / length2(v21)) - p1;
+		vec3 e2 = v32 * clamp01(dot(v32, p2) / length2(v32)) - p2;
+		vec3 e3 = v13 * clamp01(dot(v13, p3) / length2(v13)) - p3;
+		return std::min(std::min(length2(e1), length2(e2)), length2(e3));
+	}
+	return dot(nor, p1) * dot(nor, p1) / length2(nor);
+}
+static vec3 closest_on_segment(vec3 a, vec3 b, vec3 c) {
+	float t = dot(c - a, b - a) / dot(b - a, b - a);
+	t = std::max(std::min(t, 1.0f), 0.0f);
+	return a + t * (b - a);
+}
+static vec3 tri_closest_point(const Triangle& t, vec3 point) {
+	vec3 n = tri_normal(t);
+	point = point - dot(n, point - t.a) * n;
+	vec3 la = t.a - point, lb = t.b - point, lc = t.c - point;
+	vec3 u = cross(lb, lc), v = cross(lc, la), w = cross(la, lb);
+	if (dot(u, v) >= 0.0f && dot(u, w) >= 0.0f) return point;
+	vec3 c1 = closest_on_segment(t.a, t.b, point), c2 = closest_on_segment(t.b, t.c, point), c3 = closest_on_segment(t.c, t.a, point);
+	float m1 = length2(point - c1), m2 = length2(point - c2), m3 = length2(point - c3);
+	float mn = std::min(std::min(m1, m2), m3);
+	if (mn == m1) return c1;
+	if (mn == m2) return c2;
+	return c3;
+}
+void orc_triangle_distance_sq(const float tri[9], const float p[3], float* out) {
+	Triangle t = {{tri[0], tri[1], tri[2]}, {tri[3], tri[4], tri[5]}, {tri[6], tri[7], tri[8]}};
+	*out = tri_distance_sq(t, {p[0], p[1], p[2]});
+}
+void orc_triangle_closest_point(const float tri[9], const float p[3], float out[3]) {
+	Triangle t = {{tri[0], tri[1], tri[2]}, {tri[3], tri[4], tri[5]}, {tri[6], tri[7], tri[8]}};
+	vec3 c = tri_closest_point(t, {p[0], p[1], p[2]});
+	out[0] = c.x; out[1] = c.y; out[2] = c.z;
+}
+// TriangleBvh::unsigned_distance / signed_distance_watertight (triangle_bvh.cu:285-297) by brute force over every triangle of
+// the scene: the minimum does not depend on the BVH, so this is the witness for the product's pruned walk.
+void orc_scene_distance(const orc_scene* s, uint32_t n, const float* pos, int32_t mode, float max_distance, int32_t n_threads, float* out, int32_t* tri_out) {
+	int nt = n_threads > 1 ? n_threads : 1;
+	std::atomic<uint32_t> next{0};
+	auto work = [&] {
+		for (uint32_t b; (b = next.fetch_add(64)) < n;) {
+			for (uint32_t i = b; i < std::min(n, b + 64); ++i) {
+				vec3 p = {pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]};
+				float best = max_distance * max_distance;
+				int bm = -1, bt = -1;
+				for (size_t m = 0; m < s->meshes.size(); ++m)
+					for (size_t k = 0; k < s->meshes[m].tris.size(); ++k) {
+						float d2 = tri_distance_sq(s->meshes[m].tris[k], p);
+						if (d2 < best || (d2 == best && bm < 0)) { best = d2; bm = (int)m; bt = (int)k; }
+					}
+				if (bm < 0) { out[i] = max_distance; if (tri_out) tri_out[i] = -1; continue; }
+				float d = std::sqrt(best);
+				if (tri_out) tri_out[i] = bt;
+				if (mode == 1) {
+					vec3 cp = tri_closest_point(s->meshes[bm].tris[bt], p);
+					vec3 ns = {0.0f, 0.0f, 0.0f}; float nw = 0.0f;
+					for (const Triangle& t : s->meshes[bm].tris) if (tri_distance_sq(t, cp) < 1e-6f) { ns = ns + tri_normal(t); nw += 1.0f; }
+					vec3 avg = ns / nw;
+					d = std::copysign(d, dot(avg, p - cp));
+				}
+				out[i] = d;
+			}
+		}
+	};
+	std::vector<std::thread> th;
+	for (int k = 1; k < nt; ++k) th.emplace_back(work);
+	work();
+	for (auto& t : th) t.join();
+}
+
 void orc_scene_trace(const orc_scene* s, const orc_render_params* p, uint32_t n, const float* o, const float* d,
 	int32_t* mesh_idx, int32_t* tri_idx, float* t, int32_t brute) {
 	int nt = p->n_threads > 1 ? p->n_threads : 1;

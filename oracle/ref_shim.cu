@@ -96,6 +96,17 @@ int32_t ref_uv_to_ray_lens(uint32_t spp, const float uv[2], int32_t w, int32_t h
 	return ray.is_valid() ? 1 : 0;
 }
 
+// Triangle::distance_sq / closest_point (triangle.cuh:66-147), NGP_HOST_DEVICE
+float ref_triangle_distance_sq(const float tri[9], const float p[3]) {
+	Triangle t{vec3(tri[0], tri[1], tri[2]), vec3(tri[3], tri[4], tri[5]), vec3(tri[6], tri[7], tri[8])};
+	return t.distance_sq(vec3(p[0], p[1], p[2]));
+}
+void ref_triangle_closest_point(const float tri[9], const float p[3], float out[3]) {
+	Triangle t{vec3(tri[0], tri[1], tri[2]), vec3(tri[3], tri[4], tri[5]), vec3(tri[6], tri[7], tri[8])};
+	vec3 c = t.closest_point(vec3(p[0], p[1], p[2]));
+	out[0] = c.x; out[1] = c.y; out[2] = c.z;
+}
+
 // a-16 sampling helpers (random_val.cuh:62-72,130-185), all NGP_HOST_DEVICE
 void ref_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 void ref_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm(vec3(d[0], d[1], d[2])); out[0] = v.x; out[1] = v.y; }

@@ -808,6 +808,21 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 	HN_CATCH(ctx)
 }
 
+int hn_op_mesh_distance(hn_context* ctx, uint32_t n, const float* positions, int mode, float max_distance, float* distances, int32_t* tri_idx) {
+	HN_TRY(ctx)
+	need(ctx->scene_built && !ctx->meshes.empty(), "scene not built");
+	need(mode == 0 || mode == 1, "mesh distance mode: 0 = unsigned, 1 = signed (watertight); raystab / path-escape are not built");
+	need(max_distance > 0.0f, "max_distance must be positive");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	float* d_p = scratch<float>(ctx, 0, (size_t)n * 3); float* d_d = scratch<float>(ctx, 1, n); int32_t* d_i = scratch<int32_t>(ctx, 2, n);
+	HN_CUDA(cudaMemcpyAsync(d_p, positions, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
+	launch_distance(ctx->scene_dev(), n, d_p, mode, max_distance, d_d, tri_idx ? d_i : nullptr, ctx->stream);
+	HN_CUDA(cudaMemcpyAsync(distances, d_d, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (tri_idx) HN_CUDA(cudaMemcpyAsync(tri_idx, d_i, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
 int hn_op_trace(hn_context* ctx, uint32_t n, const float* origins, const float* dirs, int32_t* mesh_idx, int32_t* tri_idx, float* t) {
 	HN_TRY(ctx)
 	need(ctx->scene_built && !ctx->meshes.empty(), "scene not built");

@@ -132,6 +132,8 @@ void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays
 	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s);
 
 // network TU
+// distance queries on the scene BVH (triangle_bvh.cu:195-303): mode 0 unsigned, 1 signed (watertight rule)
+void launch_distance(const SceneDev& sc, uint32_t n, const float* pos, int mode, float max_distance, float* out, int32_t* tri_out, cudaStream_t s);
 // ERenderMode::Normals: overwrite the (r,g,b) of the network output with the unit normal from the density gradient
 void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples, const uint32_t* sample_counts,
 	const uint32_t* n_chunks_ptr, uint32_t max_chunks, uint2* out, cudaStream_t s);

@@ -116,6 +116,129 @@ __global__ void __launch_bounds__(MESH_BLOCK) trace_kernel(SceneDev sc, int comp
 	mesh_out[i] = h.mesh; tri_out[i] = h.tri; t_out[i] = h.t;
 }
 
+// ---------------------------------------------------------------- distance queries (triangle.cuh:39-41,66-147, triangle_bvh.cu:195-303)
+__device__ __forceinline__ float sign1(float x) { return copysignf(1.0f, x); }
+__device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
+// Triangle::distance_sq (iq's formulation), same operation order as the reference
+__device__ float tri_distance_sq(V3 a, V3 b, V3 c, V3 pos) {
+	const V3 v21 = b - a, p1 = pos - a, v32 = c - b, p2 = pos - b, v13 = a - c, p3 = pos - c;
+	const V3 nor = cross3(v21, v13);
+	if (sign1(dot3(cross3(v21, nor), p1)) + sign1(dot3(cross3(v32, nor), p2)) + sign1(dot3(cross3(v13, nor), p3)) < 2.0f) {
+		const V3 e1 = v21 * clamp01(dot3(v21, p1) / dot3(v21, v21)) - p1;
+		const V3 e2 = v32 * clamp01(dot3(v32, p2) / dot3(v32, v32)) - p2;
+		const V3 e3 = v13 * clamp01(dot3(v13, p3) / dot3(v13, v13)) - p3;
+		return fminf(fminf(dot3(e1, e1), dot3(e2, e2)), dot3(e3, e3));
+	}
+	return dot3(nor, p1) * dot3(nor, p1) / dot3(nor, nor);
+}
+__device__ __forceinline__ V3 tri_normal(V3 a, V3 b, V3 c) { const V3 n = cross3(b - a, c - a); return n / sqrtf(dot3(n, n)); }
+__device__ __forceinline__ V3 closest_on_segment(V3 a, V3 b, V3 c) {
+	float t = dot3(c - a, b - a) / dot3(b - a, b - a);
+	t = fmaxf(fminf(t, 1.0f), 0.0f);
+	return a + t * (b - a);
+}
+__device__ V3 tri_closest_point(V3 a, V3 b, V3 c, V3 point) {
+	const V3 n = tri_normal(a, b, c);
+	point = point - dot3(n, point - a) * n;
+	{ // point_in_triangle
+		const V3 la = a - point, lb = b - point, lc = c - point;
+		const V3 u = cross3(lb, lc), v = cross3(lc, la), w = cross3(la, lb);
+		if (dot3(u, v) >= 0.0f && dot3(u, w) >= 0.0f) return point;
+	}
+	const V3 c1 = closest_on_segment(a, b, point), c2 = closest_on_segment(b, c, point), c3 = closest_on_segment(c, a, point);
+	const V3 d1 = point - c1, d2 = point - c2, d3 = point - c3;
+	const float m1 = dot3(d1, d1), m2 = dot3(d2, d2), m3 = dot3(d3, d3);
+	const float mn = fminf(fminf(m1, m2), m3);
+	if (mn == m1) return c1;
+	if (mn == m2) return c2;
+	return c3;
+}
+__device__ __forceinline__ float box_distance_sq(float lx, float ly, float lz, float hx, float hy, float hz, V3 p) {
+	const float dx = fmaxf(fmaxf(lx - p.x, p.x - hx), 0.0f), dy = fmaxf(fmaxf(ly - p.y, p.y - hy), 0.0f), dz = fmaxf(fmaxf(lz - p.z, p.z - hz), 0.0f);
+	return dx * dx + dy * dy + dz * dz;
+}
+// One stack walk over one mesh. NEAREST: closest triangle (`<=` as triangle_bvh.cu:211, so the last of equal candidates in
+// walk order wins; the distance itself does not depend on that). !NEAREST: sum of the normals of every triangle within
+// sqrt(1e-6) of `p` (avg_normal_around_point :246-283).
+template <bool NEAREST>
+__device__ void distance_walk(const SceneDev& sc, int mesh, V3 p, float& best_d2, uint32_t& best_slot, V3& nsum, float& nweight, int* stack) {
+	const MeshDev m = sc.meshes[mesh];
+	int sp = 0;
+	stack[0] = (int)m.node_root; sp = 1;
+	while (sp > 0) {
+		const int code = stack[(--sp) * MESH_BLOCK];
+		if (code < 0) {
+			const uint32_t v = (uint32_t)(-1 - code);
+			const uint32_t first = m.tri_first + (v >> 4), cnt = v & 15u;
+			for (uint32_t k = 0; k < cnt; ++k) {
+				const float4 A = __ldg(sc.tris + (size_t)(first + k) * 3), B = __ldg(sc.tris + (size_t)(first + k) * 3 + 1), C = __ldg(sc.tris + (size_t)(first + k) * 3 + 2);
+				const V3 a = mk(A.x, A.y, A.z), b = mk(B.x, B.y, B.z), c = mk(C.x, C.y, C.z);
+				const float d2 = tri_distance_sq(a, b, c, p);
+				if (NEAREST) { if (d2 <= best_d2) { best_d2 = d2; best_slot = first + k; } }
+				else if (d2 < 1e-6f) { nsum = nsum + tri_normal(a, b, c); nweight += 1.0f; }
+			}
+			continue;
+		}
+		const float4* np = reinterpret_cast<const float4*>(sc.nodes + code);
+		const float4 lox = __ldg(np), loy = __ldg(np + 1), loz = __ldg(np + 2), hix = __ldg(np + 3), hiy = __ldg(np + 4), hiz = __ldg(np + 5);
+		const int4 child = __ldg(reinterpret_cast<const int4*>(np + 6)), count = __ldg(reinterpret_cast<const int4*>(np + 7));
+		const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+		const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+		const int ch[4] = {child.x, child.y, child.z, child.w}, cn[4] = {count.x, count.y, count.z, count.w};
+		float dist[4]; int idx[4];
+		#pragma unroll
+		for (int i = 0; i < 4; ++i) {
+			const float d2 = box_distance_sq(lx[i], ly[i], lz[i], hx[i], hy[i], hz[i], p); // padded boxes: a valid lower bound
+			const bool keep = cn[i] != 0 && (NEAREST ? d2 <= best_d2 : d2 < 1e-6f);
+			dist[i] = keep ? d2 : -1.0f;
+			idx[i] = ch[i];
+		}
+		cswap(dist[0], idx[0], dist[2], idx[2]);
+		cswap(dist[1], idx[1], dist[3], idx[3]);
+		cswap(dist[0], idx[0], dist[1], idx[1]);
+		cswap(dist[2], idx[2], dist[3], idx[3]);
+		cswap(dist[1], idx[1], dist[2], idx[2]);
+		#pragma unroll
+		for (int i = 0; i < 4; ++i) {
+			if (dist[i] >= 0.0f && sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+		}
+	}
+}
+// mode 0: unsigned distance to the nearest triangle of the scene; mode 1: signed, watertight rule (:289-297: sign of
+// dot(average normal around the closest point, p - closest point)). max_distance bounds the search like MAX_DIST.
+__global__ void __launch_bounds__(MESH_BLOCK) distance_kernel(SceneDev sc, uint32_t n, const float* __restrict__ pos, int mode, float max_distance,
+	float* __restrict__ out, int32_t* __restrict__ tri_out) {
+	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const V3 p = ld3(pos + 3 * i);
+	float best = max_distance * max_distance;
+	uint32_t slot = 0xFFFFFFFFu;
+	int best_mesh = -1;
+	V3 ns = mk(0.0f, 0.0f, 0.0f); float nw = 0.0f;
+	for (uint32_t m = 0; m < sc.n_meshes; ++m) {
+		uint32_t s = 0xFFFFFFFFu; float b = best;
+		distance_walk<true>(sc, (int)m, p, b, s, ns, nw, stack_s + threadIdx.x);
+		if (s != 0xFFFFFFFFu) { best = b; slot = s; best_mesh = (int)m; }
+	}
+	if (slot == 0xFFFFFFFFu) { out[i] = max_distance; if (tri_out) tri_out[i] = -1; return; }
+	float d = sqrtf(best);
+	const float4 A = __ldg(sc.tris + (size_t)slot * 3), B = __ldg(sc.tris + (size_t)slot * 3 + 1), C = __ldg(sc.tris + (size_t)slot * 3 + 2);
+	if (tri_out) tri_out[i] = __float_as_int(A.w);
+	if (mode == 1) {
+		const V3 cp = tri_closest_point(mk(A.x, A.y, A.z), mk(B.x, B.y, B.z), mk(C.x, C.y, C.z), p);
+		float dummy = 0.0f; uint32_t ds = 0;
+		distance_walk<false>(sc, best_mesh, cp, dummy, ds, ns, nw, stack_s + threadIdx.x);
+		const V3 avg = ns / nw;
+		d = copysignf(d, dot3(avg, p - cp));
+	}
+	out[i] = d;
+}
+void launch_distance(const SceneDev& sc, uint32_t n, const float* pos, int mode, float max_distance, float* out, int32_t* tri_out, cudaStream_t s) {
+	if (!n) return;
+	distance_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(sc, n, pos, mode, max_distance, out, tri_out);
+}
+
 // ---------------------------------------------------------------- shading (testbed_geometry_training.cu:50-144)
 __device__ __forceinline__ float sqr(float x) { return x * x; }
 __device__ __forceinline__ float saturate1(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }

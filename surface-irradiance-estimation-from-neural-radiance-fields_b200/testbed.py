@@ -65,7 +65,7 @@ EXPORTS = [
     "hn_set_aabb_scale", "hn_get_network_info", "hn_set_params", "hn_load_snapshot", "hn_save_snapshot", "hn_set_density_grid", "hn_set_occupancy_bitfield",
     "hn_get_occupancy_bitfield", "hn_load_scene", "hn_add_mesh", "hn_load_mesh_file", "hn_build_scene", "hn_clear_scene",
     "hn_get_scene_aabb", "hn_set_option", "hn_get_option", "hn_render_frame", "hn_render_to_host", "hn_set_camera",
-    "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays",
+    "hn_set_tile_shard", "hn_tile_count", "hn_pack_tiles", "hn_unpack_tiles", "hn_get_frame_stats", "hn_op_init_rays", "hn_op_mesh_distance",
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
@@ -91,6 +91,7 @@ _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_trace.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
+_lib.hn_op_mesh_distance.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
 for _n in ("hn_load_network_config", "hn_load_network_config_string", "hn_load_scene", "hn_load_snapshot", "hn_save_snapshot"):
     getattr(_lib, _n).argtypes = [C.c_void_p, C.c_char_p]
 _lib.hn_load_mesh_file.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
@@ -413,6 +414,15 @@ class Testbed:
 
     def train_apply(self, grad_scale: float = 1.0):
         self._check(_lib.hn_train_apply(self._h, grad_scale))
+
+    def op_mesh_distance(self, positions, mode: int = 0, max_distance: float = 10.0, return_triangles: bool = False):
+        """TriangleBvh unsigned / watertight-signed distance (src/triangle_bvh.cu:285-297) for an (n, 3) array of positions"""
+        p = np.ascontiguousarray(positions, dtype=np.float32).reshape(-1, 3)
+        d = np.empty(p.shape[0], np.float32)
+        tri = np.empty(p.shape[0], np.int32) if return_triangles else None
+        self._check(_lib.hn_op_mesh_distance(self._h, C.c_uint32(p.shape[0]), _ptr(p), C.c_int(mode), C.c_float(max_distance), _ptr(d),
+                                             _ptr(tri) if tri is not None else None))
+        return (d, tri) if return_triangles else d
 
     def update_density_grid(self, decay: float = 0.95, n_uniform: int = 128 ** 3, n_nonuniform: int = 0):
         self._check(_lib.hn_update_density_grid(self._h, decay, n_uniform, n_nonuniform))

@@ -217,6 +217,28 @@ def make_ref_lens():
     print("ref_host_lens.npz:", len(out), "arrays")
 
 
+def make_ref_tri():
+    """Triangle::distance_sq / closest_point (triangle.cuh:66-147) of the reference, host-callable -> ref_host_tri.npz"""
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_triangle_distance_sq"):
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing or stale: run `make -C oracle ref`")
+    ref.ref_triangle_distance_sq.restype = C.c_float
+    rng = np.random.default_rng(42)
+    n = 512
+    tris = rng.uniform(-1, 1, (n, 9)).astype(f32)
+    pts = rng.uniform(-1.5, 1.5, (n, 3)).astype(f32)
+    for i in range(64):  # points in the triangle's plane, inside it
+        w = rng.dirichlet([1, 1, 1]).astype(f32)
+        pts[i] = w[0] * tris[i, :3] + w[1] * tris[i, 3:6] + w[2] * tris[i, 6:]
+    pts[64] = tris[64, :3]  # a vertex
+    d = np.zeros(n, f32); cp = np.zeros((n, 3), f32)
+    for i in range(n):
+        d[i] = ref.ref_triangle_distance_sq(orc.P(tris[i]), orc.P(pts[i]))
+        ref.ref_triangle_closest_point(orc.P(tris[i]), orc.P(pts[i]), orc.P(cp[i]))
+    np.savez_compressed(os.path.join(HERE, "ref_host_tri.npz"), tris=tris, pts=pts, distance_sq=d, closest_point=cp)
+    print("ref_host_tri.npz: 4 arrays")
+
+
 class Info:
     pass
 
@@ -262,7 +284,10 @@ if __name__ == "__main__":
         make_ref_env()
     elif len(sys.argv) > 1 and sys.argv[1] == "lens":
         make_ref_lens()
+    elif len(sys.argv) > 1 and sys.argv[1] == "tri":
+        make_ref_tri()
     else:
+        make_ref_tri()
         make_ref_lens()
         make_ref_host()
         make_ref_env()

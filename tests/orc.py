@@ -176,6 +176,13 @@ class Scene:
         lib.orc_scene_aabb(self.h, P(out))
         return out
 
+    def distance(self, positions, mode=0, max_distance=10.0, n_threads=None):
+        """brute-force unsigned (mode 0) / watertight-signed (mode 1) distance of every position to the scene; (distance, triangle)"""
+        pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        out = np.empty(pos.shape[0], np.float32); tri = np.empty(pos.shape[0], np.int32)
+        lib.orc_scene_distance(self.h, C.c_uint32(pos.shape[0]), P(pos), C.c_int32(mode), C.c_float(max_distance), C.c_int32(n_threads or (os.cpu_count() or 1)), P(out), P(tri))
+        return out, tri
+
     def trace(self, p: RenderParams, origins, dirs, brute=False):
         o = np.ascontiguousarray(origins, np.float32)
         d = np.ascontiguousarray(dirs, np.float32)

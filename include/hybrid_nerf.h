@@ -188,8 +188,9 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 /* a-17/a-18: nearest hit per ray: mesh index, ORIGINAL triangle index, t (100 = miss) (host in/out). */
 /* Distance from each position to the nearest triangle of the scene, through the BVH (TriangleBvh::signed_distance_gpu,
  * src/triangle_bvh.cu:195-303,330-376; include/neural-graphics-primitives/triangle.cuh:66-147). mode 0 = unsigned_distance,
- * mode 1 = signed_distance_watertight (sign of dot(average normal around the closest point, p - closest point)); raystab and
- * path-escape are not built. max_distance bounds the search (the reference's MAX_DIST); tri_idx (optional) receives the
+ * mode 1 = signed_distance_watertight (sign of dot(average normal around the closest point, p - closest point)), mode 2 =
+ * signed_distance_raystab (32 Fibonacci stab rays with the kernel's pcg32 offset; inside when none escapes); path-escape
+ * (OptiX only in the reference) is not built. max_distance bounds the search (the reference's MAX_DIST); tri_idx (optional) receives the
  * original index of the nearest triangle inside its mesh, -1 when nothing lies within max_distance. Host pointers. */
 int hn_op_mesh_distance(hn_context* ctx, uint32_t n, const float* positions, int mode, float max_distance, float* distances, int32_t* tri_idx);
 int hn_op_trace(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, int32_t* mesh_idx, int32_t* tri_idx, float* t);

@@ -141,9 +141,11 @@ void orc_scene_add_mesh(orc_scene*, const float* triangles, uint32_t n_tris, con
 void orc_scene_build(orc_scene*);
 void orc_scene_aabb(const orc_scene*, float out[6]);
 // nearest hit per ray; brute = 1 tests every triangle (no BVH). t = MAX_DIST(100) and tri=-1 on miss.
-// triangle.cuh:66-147 restated (pinned on the reference's host functions) and the brute-force scene distance (mode 0 unsigned, 1 watertight-signed)
+// triangle.cuh:66-147 restated (pinned on the reference's host functions) and the brute-force scene distance (mode 0 unsigned, 1 watertight-signed, 2 raystab-signed)
 void orc_triangle_distance_sq(const float tri[9], const float p[3], float* out);
 void orc_triangle_closest_point(const float tri[9], const float p[3], float out[3]);
+void orc_fibonacci_dir32(uint32_t i, const float offset[2], float out[3]);
+void orc_default_rng_offset(uint64_t advance, float out[2]);
 void orc_scene_distance(const orc_scene*, uint32_t n, const float* positions, int32_t mode, float max_distance, int32_t n_threads, float* out, int32_t* tri_out);
 void orc_scene_trace(const orc_scene*, const orc_render_params* p, uint32_t n, const float* origins, const float* dirs,
 	int32_t* mesh_idx, int32_t* tri_idx, float* t, int32_t brute);

@@ -391,6 +391,38 @@ void orc_triangle_closest_point(const float tri[9], const float p[3], float out[
 	vec3 c = tri_closest_point(t, {p[0], p[1], p[2]});
 	out[0] = c.x; out[1] = c.y; out[2] = c.z;
 }
+// pcg32 in its default state (default_rng_t rng; pcg32.h PCG32_DEFAULT_STATE / PCG32_DEFAULT_STREAM), skip-ahead, two floats
+static void default_rng_offset(uint64_t delta, float out[2]) {
+	uint64_t state = 0x853c49e6748fea9bULL, inc = 0xda3e39cb94b95bdbULL;
+	uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+	while (delta > 0) {
+		if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+		cur_plus = (cur_mult + 1) * cur_plus;
+		cur_mult *= cur_mult;
+		delta /= 2;
+	}
+	state = acc_mult * state + acc_plus;
+	for (int k = 0; k < 2; ++k) {
+		uint64_t old = state;
+		state = old * 0x5851f42d4c957f2dULL + inc;
+		uint32_t xorshifted = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+		uint32_t rot = (uint32_t)(old >> 59u);
+		uint32_t u = (((xorshifted >> rot) | (xorshifted << ((~rot + 1u) & 31))) >> 9) | 0x3f800000u;
+		float f; std::memcpy(&f, &u, 4);
+		out[k] = f - 1.0f;
+	}
+}
+static float fractf1(float x) { return x - std::floor(x); }
+// random_val.cuh:45-54,84-101 with N_DIRS = 32 (epsilon 1.33)
+static vec3 fibonacci_dir32(uint32_t i, float ox, float oy) {
+	const float epsilon = 1.33f, GOLDEN_RATIO = 1.6180339887498948482045868343656f;
+	float px = fractf1((i + epsilon) / (32 - 1 + 2 * epsilon) + ox), py = fractf1(i / GOLDEN_RATIO + oy);
+	float cos_theta = -2.0f * px + 1.0f, phi = 2.0f * 3.14159265358979323846f * (py - 0.5f);
+	float sin_theta = std::sqrt(std::fmax(1.0f - cos_theta * cos_theta, 0.0f));
+	return {sin_theta * std::cos(phi), sin_theta * std::sin(phi), cos_theta};
+}
+void orc_fibonacci_dir32(uint32_t i, const float offset[2], float out[3]) { vec3 d = fibonacci_dir32(i, offset[0], offset[1]); out[0] = d.x; out[1] = d.y; out[2] = d.z; }
+void orc_default_rng_offset(uint64_t advance, float out[2]) { default_rng_offset(advance, out); }
 // TriangleBvh::unsigned_distance / signed_distance_watertight (triangle_bvh.cu:285-297) by brute force over every triangle of
 // the scene: the minimum does not depend on the BVH, so this is the witness for the product's pruned walk.
 void orc_scene_distance(const orc_scene* s, uint32_t n, const float* pos, int32_t mode, float max_distance, int32_t n_threads, float* out, int32_t* tri_out) {
@@ -416,6 +448,16 @@ void orc_scene_distance(const orc_scene* s, uint32_t n, const float* pos, int32_
 					for (const Triangle& t : s->meshes[bm].tris) if (tri_distance_sq(t, cp) < 1e-6f) { ns = ns + tri_normal(t); nw += 1.0f; }
 					vec3 avg = ns / nw;
 					d = std::copysign(d, dot(avg, p - cp));
+				} else if (mode == 2) { // signed_distance_raystab (:299-317) with the kernel's rng (:573-574): any escaping stab ray -> outside
+					float off[2];
+					default_rng_offset((uint64_t)i * 2, off);
+					bool inside = true;
+					for (uint32_t k = 0; k < 32 && inside; ++k) {
+						int mi, ti; float tt; bool touched;
+						scene_nearest(*s, false, p, fibonacci_dir32(k, off[0], off[1]), false, mi, ti, tt, touched);
+						if (ti < 0) inside = false;
+					}
+					if (inside) d = -d;
 				}
 				out[i] = d;
 			}

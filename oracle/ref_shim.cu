@@ -107,6 +107,18 @@ void ref_triangle_closest_point(const float tri[9], const float p[3], float out[
 	out[0] = c.x; out[1] = c.y; out[2] = c.z;
 }
 
+// raystab sign of the mesh SDF (triangle_bvh.cu:299-317,561-590): stab directions and the per-element random offset
+void ref_fibonacci_dir32(uint32_t i, const float offset[2], float out[3]) {
+	vec3 d = fibonacci_dir<32>(i, vec2(offset[0], offset[1]));
+	out[0] = d.x; out[1] = d.y; out[2] = d.z;
+}
+void ref_default_rng_offset(uint64_t advance, float out[2]) {
+	default_rng_t rng;
+	rng.advance(advance);
+	vec2 v = random_val_2d(rng);
+	out[0] = v.x; out[1] = v.y;
+}
+
 // a-16 sampling helpers (random_val.cuh:62-72,130-185), all NGP_HOST_DEVICE
 void ref_ld_random_val_2d(uint32_t index, uint32_t seed, float out[2]) { vec2 v = ld_random_val_2d(index, seed); out[0] = v.x; out[1] = v.y; }
 void ref_dir_to_spherical_unorm(const float d[3], float out[2]) { vec2 v = dir_to_spherical_unorm(vec3(d[0], d[1], d[2])); out[0] = v.x; out[1] = v.y; }

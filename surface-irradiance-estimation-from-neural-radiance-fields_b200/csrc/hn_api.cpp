@@ -811,7 +811,7 @@ int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, ui
 int hn_op_mesh_distance(hn_context* ctx, uint32_t n, const float* positions, int mode, float max_distance, float* distances, int32_t* tri_idx) {
 	HN_TRY(ctx)
 	need(ctx->scene_built && !ctx->meshes.empty(), "scene not built");
-	need(mode == 0 || mode == 1, "mesh distance mode: 0 = unsigned, 1 = signed (watertight); raystab / path-escape are not built");
+	need(mode >= 0 && mode <= 2, "mesh distance mode: 0 = unsigned, 1 = signed (watertight), 2 = signed (raystab); path-escape (OptiX only) is not built");
 	need(max_distance > 0.0f, "max_distance must be positive");
 	HN_CUDA(cudaSetDevice(ctx->device));
 	float* d_p = scratch<float>(ctx, 0, (size_t)n * 3); float* d_d = scratch<float>(ctx, 1, n); int32_t* d_i = scratch<int32_t>(ctx, 2, n);

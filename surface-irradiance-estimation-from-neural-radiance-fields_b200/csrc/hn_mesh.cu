@@ -205,7 +205,8 @@ __device__ void distance_walk(const SceneDev& sc, int mesh, V3 p, float& best_d2
 	}
 }
 // mode 0: unsigned distance to the nearest triangle of the scene; mode 1: signed, watertight rule (:289-297: sign of
-// dot(average normal around the closest point, p - closest point)). max_distance bounds the search like MAX_DIST.
+// dot(average normal around the closest point, p - closest point)); mode 2: signed, raystab rule (:299-317).
+// max_distance bounds the search like MAX_DIST.
 __global__ void __launch_bounds__(MESH_BLOCK) distance_kernel(SceneDev sc, uint32_t n, const float* __restrict__ pos, int mode, float max_distance,
 	float* __restrict__ out, int32_t* __restrict__ tri_out) {
 	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
@@ -231,6 +232,41 @@ __global__ void __launch_bounds__(MESH_BLOCK) distance_kernel(SceneDev sc, uint3
 		distance_walk<false>(sc, best_mesh, cp, dummy, ds, ns, nw, stack_s + threadIdx.x);
 		const V3 avg = ns / nw;
 		d = copysignf(d, dot3(avg, p - cp));
+	} else if (mode == 2) { // signed_distance_raystab (:299-317): 32 Fibonacci stab rays, any escape -> outside
+		// default_rng_t rng; rng.advance(i * 2); offset = random_val_2d(rng)   (triangle_bvh.cu:573-574, pcg32 default state)
+		uint64_t state = 0x853c49e6748fea9bULL; const uint64_t inc = 0xda3e39cb94b95bdbULL;
+		{
+			uint64_t delta = (uint64_t)i * 2u, cur_mult = 0x5851f42d4c957f2dULL, cur_plus = inc, acc_mult = 1u, acc_plus = 0u;
+			while (delta > 0) {
+				if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+				cur_plus = (cur_mult + 1) * cur_plus;
+				cur_mult *= cur_mult;
+				delta /= 2;
+			}
+			state = acc_mult * state + acc_plus;
+		}
+		float off[2];
+		#pragma unroll
+		for (int k = 0; k < 2; ++k) {
+			const uint64_t old = state;
+			state = old * 0x5851f42d4c957f2dULL + inc;
+			const uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u), rot = (uint32_t)(old >> 59u);
+			off[k] = __uint_as_float((((xs >> rot) | (xs << ((~rot + 1u) & 31))) >> 9) | 0x3f800000u) - 1.0f;
+		}
+		bool inside = true;
+		for (uint32_t k = 0; k < 32u && inside; ++k) {
+			// fibonacci_dir<32> (random_val.cuh:45-54,84-101), epsilon = 1.33
+			float px = ((float)k + 1.33f) / (32 - 1 + 2 * 1.33f) + off[0], py = (float)k / 1.6180339887498948482045868343656f + off[1];
+			px -= floorf(px); py -= floorf(py);
+			const float cos_theta = -2.0f * px + 1.0f, phi = 2.0f * HN_PI_F * (py - 0.5f);
+			const float sin_theta = sqrtf(fmaxf(1.0f - cos_theta * cos_theta, 0.0f));
+			float sp, cp;
+			sincosf(phi, &sp, &cp);
+			Hit h; bool touched;
+			scene_nearest(sc, 0, p, mk(sin_theta * cp, sin_theta * sp, cos_theta), h, touched, stack_s + threadIdx.x);
+			if (h.tri < 0) inside = false;
+		}
+		if (inside) d = -d;
 	}
 	out[i] = d;
 }

@@ -235,8 +235,19 @@ def make_ref_tri():
     for i in range(n):
         d[i] = ref.ref_triangle_distance_sq(orc.P(tris[i]), orc.P(pts[i]))
         ref.ref_triangle_closest_point(orc.P(tris[i]), orc.P(pts[i]), orc.P(cp[i]))
-    np.savez_compressed(os.path.join(HERE, "ref_host_tri.npz"), tris=tris, pts=pts, distance_sq=d, closest_point=cp)
-    print("ref_host_tri.npz: 4 arrays")
+    # raystab helpers (random_val.cuh:84-101 fibonacci_dir<32>; default_rng_t advanced by 2 i, triangle_bvh.cu:573-574)
+    offs = rng.uniform(0, 1, (8, 2)).astype(f32); offs[0] = 0
+    fib = np.zeros((8, 32, 3), f32)
+    for a in range(8):
+        for i in range(32):
+            ref.ref_fibonacci_dir32(C.c_uint32(i), orc.P(offs[a]), orc.P(fib[a, i]))
+    adv = np.array([0, 2, 4, 6, 1000, 2 * 4095, 2 ** 33 + 2], np.uint64)
+    rng_off = np.zeros((adv.size, 2), f32)
+    for a in range(adv.size):
+        ref.ref_default_rng_offset(C.c_uint64(int(adv[a])), orc.P(rng_off[a]))
+    np.savez_compressed(os.path.join(HERE, "ref_host_tri.npz"), tris=tris, pts=pts, distance_sq=d, closest_point=cp,
+                        fib_offsets=offs, fib_dirs=fib, rng_advance=adv, rng_offsets=rng_off)
+    print("ref_host_tri.npz: 8 arrays")
 
 
 class Info:

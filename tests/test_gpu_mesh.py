@@ -154,5 +154,12 @@ def test_mesh_distance_queries(hn, orc):
     # bounded search: nothing within reach -> max_distance
     out = tb.op_mesh_distance(np.array([[30.0, 30.0, 30.0]], np.float32), 0, max_distance=5.0)
     assert out[0] == np.float32(5.0)
+    # raystab sign (32 Fibonacci stab rays, pcg32 offset per element): same rays on both sides; a ray grazing an edge can
+    # flip one hit/miss through sin/cos rounding -> allow 0.2 % of the points
+    rwant, _ = scene.distance(pos, 2)
+    rgot = tb.op_mesh_distance(pos, 2)
+    assert np.array_equal(np.abs(rgot).view(np.uint32), want.view(np.uint32))
+    assert (np.sign(rgot) != np.sign(rwant)).mean() <= 2e-3
+    assert (rwant < 0).sum() > 50 and (rwant > 0).sum() > 1000  # closed tori: inside is negative whatever the winding
     with pytest.raises(RuntimeError):
-        tb.op_mesh_distance(pos[:4], 2)
+        tb.op_mesh_distance(pos[:4], 3)

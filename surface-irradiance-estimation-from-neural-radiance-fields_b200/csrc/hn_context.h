@@ -119,6 +119,7 @@ struct TrainState {
 	DevBuf<uint32_t> ray_numsteps, ray_base, counters;
 	DevBuf<float4> coords;                  // warped position, dt per sample
 	DevBuf<uint32_t> sample_ray;
+	DevBuf<float4> march_staging;           // [n_rays][1024] per-ray staging rows of the single-walk sample generation
 	DevBuf<__half> act[12];                 // activations: enc, density hidden..., density out, rgb in, rgb hidden..., out
 	DevBuf<__half> dact[4];                 // gradient ping-pong buffers
 	DevBuf<float> loss_acc;

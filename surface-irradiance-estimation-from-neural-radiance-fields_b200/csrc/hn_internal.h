@@ -129,7 +129,7 @@ void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const
 	uint32_t* counts, float* samples, uint32_t max_per_ray, cudaStream_t s);
 
 void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
-	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s);
+	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, float4* staging /* [n_rays][1024] */, cudaStream_t s);
 
 // network TU
 // distance queries on the scene BVH (triangle_bvh.cu:195-303): mode 0 unsigned, 1 signed (watertight rule)

@@ -345,7 +345,7 @@ __device__ __forceinline__ uint32_t flat_march(const FrameArgs& a, const uint8_t
 					if (WRITE) {
 						const V3 wp = (pos - train.lo) / tdiag;
 						dst[count] = make_float4(wp.x, wp.y, wp.z, dt);
-						dst_ray[count] = ray;
+						if (dst_ray) dst_ray[count] = ray;
 					}
 					++count;
 					t += dt;
@@ -368,19 +368,22 @@ __device__ __forceinline__ uint32_t flat_march(const FrameArgs& a, const uint8_t
 	return count;
 }
 
-// a-21 generate_training_samples_nerf (src/testbed_nerf.cu:737-890): per training ray, count the samples along the occupancy
-// DDA (at most NERF_STEPS = 1024), reserve that many slots (one atomic per WARP: warp prefix sum of the counts), then walk
-// again and write warped position + dt. Rays whose samples do not fit below max_samples get none (:848-852).
+// a-21 generate_training_samples_nerf (src/testbed_nerf.cu:737-890): per training ray, walk the occupancy DDA (at most
+// NERF_STEPS = 1024 samples), reserve that many slots (one atomic per WARP: warp prefix sum of the counts) and store warped
+// position + dt. Rays whose samples do not fit below max_samples get none (:848-852). The reference walks every ray twice
+// (count, then write); a batch has only a few thousand rays, so the kernel is bound by the latency of the longest serial
+// walk: here the ONE walk writes into a per-ray staging row (n_rays x 1024 float4 in HBM, L2-resident for a batch) and the
+// warp then copies each of its 32 rays' rows to the packed slots with coalesced accesses. Same samples, same packing rule.
 __global__ void __launch_bounds__(64) train_march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, uint32_t n_rays, const float* __restrict__ ray_o,
 	const float* __restrict__ ray_d, const float* __restrict__ ray_t, uint32_t max_samples, uint32_t* __restrict__ counter,
-	uint32_t* __restrict__ numsteps_out, uint32_t* __restrict__ base_out, float4* __restrict__ coords, uint32_t* __restrict__ sample_ray) {
+	uint32_t* __restrict__ numsteps_out, uint32_t* __restrict__ base_out, float4* __restrict__ coords, uint32_t* __restrict__ sample_ray, float4* __restrict__ staging) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	const uint32_t lane = threadIdx.x & 31u;
 	const bool valid = i < n_rays;
 	V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 0.f, 1.f);
 	float t0 = MAX_DEPTH_F;
 	if (valid) { o = ld3(ray_o + 3 * i); d = ld3(ray_d + 3 * i); t0 = ray_t[i]; }
-	uint32_t n = flat_march<false>(a, bits, valid, o, d, t0, 1024u, nullptr, nullptr, 0u);
+	uint32_t n = flat_march<true>(a, bits, valid, o, d, t0, 1024u, staging + (size_t)(valid ? i : 0u) * 1024u, nullptr, 0u);
 	// warp-aggregated slot reservation
 	uint32_t incl = n;
 	#pragma unroll
@@ -392,7 +395,14 @@ __global__ void __launch_bounds__(64) train_march_kernel(FrameArgs a, const uint
 	const uint32_t base = warp_base + incl - n;
 	if (base + n > max_samples) n = 0;
 	if (valid) { numsteps_out[i] = n; base_out[i] = base; }
-	flat_march<true>(a, bits, valid, o, d, t0, n, coords + base, sample_ray + base, i);
+	__syncwarp();
+	// staging rows -> packed slots, one ray of the warp at a time, all 32 lanes copying (coalesced both ways)
+	const uint32_t ray0 = i - lane;
+	for (uint32_t r = 0; r < 32u; ++r) {
+		const uint32_t nr = __shfl_sync(0xffffffffu, n, r), br = __shfl_sync(0xffffffffu, base, r);
+		const float4* src = staging + (size_t)(ray0 + r) * 1024u;
+		for (uint32_t k = lane; k < nr; k += 32u) { coords[br + k] = src[k]; sample_ray[br + k] = ray0 + r; }
+	}
 }
 
 __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const uint8_t* __restrict__ bits, float* __restrict__ o_out, float* __restrict__ d_out,
@@ -600,9 +610,9 @@ void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays
 	secondary_start_kernel<<<(n_rays + 255) / 256, 256, 0, s>>>(a, bits, rays, n_rays, alive_list, counters);
 }
 void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
-	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, cudaStream_t s) {
+	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, float4* staging, cudaStream_t s) {
 	if (!n_rays) return;
-	train_march_kernel<<<(n_rays + 63) / 64, 64, 0, s>>>(a, bits, n_rays, o, d, t, max_samples, counter, numsteps, base, coords, sample_ray);
+	train_march_kernel<<<(n_rays + 63) / 64, 64, 0, s>>>(a, bits, n_rays, o, d, t, max_samples, counter, numsteps, base, coords, sample_ray, staging);
 }
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s) {
 	uint32_t n = (uint32_t)a.w * (uint32_t)a.h;

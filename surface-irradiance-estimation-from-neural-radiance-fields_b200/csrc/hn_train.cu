@@ -492,7 +492,9 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	ev.start();
 	HN_CUDA(cudaMemsetAsync(t.counters.p, 0, 4 * sizeof(uint32_t), s));
 	HN_CUDA(cudaMemsetAsync(t.loss_acc.p, 0, 4 * sizeof(float), s));
-	launch_train_march(a, ctx->bitfield.p, n_rays, t.ray_o.p, t.ray_d.p, t.ray_t.p, max_samples, t.counters.p, t.ray_numsteps.p, t.ray_base.p, t.coords.p, t.sample_ray.p, s);
+	if ((size_t)n_rays * 1024u > t.march_staging.n) // the ray count drifts with the batch controller: grow in steps of 25 % + 4096 rows, never per step
+		t.march_staging.ensure(((size_t)n_rays + n_rays / 4 + 4096u) * 1024u);
+	launch_train_march(a, ctx->bitfield.p, n_rays, t.ray_o.p, t.ray_d.p, t.ray_t.p, max_samples, t.counters.p, t.ray_numsteps.p, t.ray_base.p, t.coords.p, t.sample_ray.p, t.march_staging.p, s);
 	uint32_t n = 0;
 	HN_CUDA(cudaMemcpyAsync(&n, t.counters.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 	HN_CUDA(cudaStreamSynchronize(s));

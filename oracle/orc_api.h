@@ -16,6 +16,11 @@ typedef struct {
 	float per_level_scale;
 	uint32_t density_hidden_layers; // "network.n_hidden_layers"
 	uint32_t rgb_hidden_layers;     // "rgb_network.n_hidden_layers"
+	// The reference evaluates grid_scale() on the GPU under --use_fast_math (MUFU.EX2 + one FFMA, see csrc/hn_config.cpp
+	// level_scale_kernel); a CPU cannot reproduce MUFU.EX2 bit for bit, so the per-level scales the device computed can be
+	// handed in. 0 = derive them on the host with exp2f (exact for power-of-two per_level_scale, e.g. nerf/base.json).
+	uint32_t has_device_scales;
+	float device_scales[16];
 } orc_net_config;
 
 typedef struct {

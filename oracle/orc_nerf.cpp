@@ -394,6 +394,10 @@ GridLayout grid_layout(const orc_net_config& c) {
 		offset += n;
 		g.scales[i] = scale;
 		g.res[i] = resolution;
+		if (c.has_device_scales) { // what kernel_grid itself computes (offsets above stay host arithmetic, grid.h:692-721)
+			g.scales[i] = c.device_scales[i];
+			g.res[i] = (uint32_t)std::ceil(c.device_scales[i]) + 1;
+		}
 	}
 	g.offsets[g.L] = offset;
 	return g;

@@ -37,6 +37,22 @@ static Json merge_parent(const Json& child, const std::string& child_dir) {
 
 static std::string lower(std::string s) { std::transform(s.begin(), s.end(), s.begin(), [](unsigned char c) { return (char)std::tolower(c); }); return s; }
 
+// The reference evaluates grid_scale / grid_resolution (tcnn common_device.h:709-718) INSIDE kernel_grid, compiled with
+// --use_fast_math: exp2f becomes MUFU.EX2 (ex2.approx.ftz) and `* base_resolution - 1` one FFMA (SASS of the reference's
+// kernel_grid<__half,3,2>: FMUL.FTZ, MUFU.EX2, FFMA.FTZ ... -1, F2I.CEIL). Whenever per_level_scale is not a power of two
+// (configs/geometry/base.json: b = 1.38) that differs from the host's exp2f in the last bits, which moves every sample
+// inside its cell. The per-level scale / resolution the gather uses are therefore computed on the device with the same
+// three instructions; the OFFSET table stays host arithmetic, as in tcnn's GridEncoding constructor (grid.h:692-721).
+__global__ void level_scale_kernel(uint32_t L, float log2_per_level_scale, uint32_t base_res, float* scales, uint32_t* res) {
+	const uint32_t level = threadIdx.x;
+	if (level >= L) return;
+	float e;
+	asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(__fmul_rn((float)level, log2_per_level_scale)));
+	const float scale = __fmaf_rn(e, (float)base_res, -1.0f);
+	scales[level] = scale;
+	res[level] = (uint32_t)ceilf(scale) + 1u;
+}
+
 static uint32_t mlp_params(uint32_t in, uint32_t hidden, uint32_t out_padded) { return 64u * in + (hidden - 1) * 64u * 64u + out_padded * 64u; }
 
 void finalize_network(hn_context* ctx) {
@@ -61,6 +77,15 @@ void finalize_network(hn_context* ctx) {
 		offset += params_in_level;
 	}
 	n.offsets[n.L] = offset;
+	if (ctx->stream) { // device-side scale / resolution per level (see level_scale_kernel); a context without a GPU only answers layout queries
+		HN_CUDA(cudaSetDevice(ctx->device));
+		DevBuf<float> d_scales; DevBuf<uint32_t> d_res;
+		d_scales.ensure(MAX_LEVELS); d_res.ensure(MAX_LEVELS);
+		level_scale_kernel<<<1, 32>>>(n.L, log2_scale, n.base_res, d_scales.p, d_res.p);
+		HN_CUDA(cudaGetLastError());
+		HN_CUDA(cudaMemcpy(n.scales, d_scales.p, n.L * sizeof(float), cudaMemcpyDeviceToHost));
+		HN_CUDA(cudaMemcpy(n.res, d_res.p, n.L * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+	}
 	// parameter blob: [density MLP | rgb MLP | grid] (nerf_network.h:356-371)
 	n.density_w_offset = 0;
 	n.rgb_w_offset = mlp_params(n.L * n.F, n.density_hidden, 16);

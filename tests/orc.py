@@ -28,7 +28,8 @@ ref = C.CDLL(REF_LIB) if os.path.exists(REF_LIB) else None
 
 class NetConfig(C.Structure):
     _fields_ = [("n_levels", u32), ("n_features_per_level", u32), ("log2_hashmap_size", u32), ("base_resolution", u32),
-                ("per_level_scale", f32), ("density_hidden_layers", u32), ("rgb_hidden_layers", u32)]
+                ("per_level_scale", f32), ("density_hidden_layers", u32), ("rgb_hidden_layers", u32),
+                ("has_device_scales", u32), ("device_scales", f32 * 16)]
 
 
 class RenderParams(C.Structure):
@@ -99,8 +100,24 @@ def net_config(n_levels=8, n_features=4, log2_T=19, base_res=16, per_level_scale
 
 def net_config_from_info(info) -> NetConfig:
     """hn_network_info (product) -> oracle config, so both sides use the very same per_level_scale."""
-    return NetConfig(info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution, info.per_level_scale,
-                     info.density_hidden_layers, info.rgb_hidden_layers)
+    c = NetConfig(info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution, info.per_level_scale,
+                  info.density_hidden_layers, info.rgb_hidden_layers)
+    # the per-level scales as the device computes them (MUFU.EX2 + FFMA like the reference's kernel_grid); identical to the
+    # host's exp2f for power-of-two per_level_scale
+    c.has_device_scales = 1
+    for i in range(info.n_levels):
+        c.device_scales[i] = info.level_scales[i]
+    return c
+
+
+def with_device_scales(cfg: NetConfig, scales) -> NetConfig:
+    """copy of cfg using an explicit per-level scale table (e.g. the one stored beside reference-GPU golden vectors)"""
+    c = NetConfig(cfg.n_levels, cfg.n_features_per_level, cfg.log2_hashmap_size, cfg.base_resolution, cfg.per_level_scale,
+                  cfg.density_hidden_layers, cfg.rgb_hidden_layers)
+    c.has_device_scales = 1
+    for i, v in enumerate(scales):
+        c.device_scales[i] = float(v)
+    return c
 
 
 def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom=1.0, screen_center=(0.5, 0.5), snap=True,

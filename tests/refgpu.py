@@ -1,0 +1,246 @@
+"""ctypes binding of oracle/_ref/libngp_ref_gpu.so — the reference's OWN CUDA build (ngp::Testbed + tiny-cuda-nn compiled
+for sm_100a by oracle/ref_gpu.mk, C wrapper oracle/ref_gpu_shim.cu). TEST / MEASUREMENT INFRASTRUCTURE ONLY: used by
+tests/golden/make_ref_gpu_golden.py (golden vectors), by the live cross-checks in tests/test_gpu_refgpu.py and by
+bench.py's reference arm. The product never loads it."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(ROOT, "oracle", "_ref", "libngp_ref_gpu.so")
+
+_lib = None
+
+
+def available() -> bool:
+    """True when the reference CUDA build exists AND loads (it needs the driver's libcuda.so.1, i.e. a GPU box)."""
+    if not os.path.exists(LIB_PATH):
+        return False
+    try:
+        lib()
+        return True
+    except OSError:
+        return False
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OSError(f"{LIB_PATH} missing: build it with `make -C oracle -f ref_gpu.mk -j8` where /root/reference is mounted")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.rg_last_error.restype = C.c_char_p
+        _lib.rg_create.restype = C.c_void_p
+        _lib.rg_destroy.argtypes = [C.c_void_p]
+        for n in ("rg_load_training_data", "rg_load_snapshot", "rg_reload_network"):
+            getattr(_lib, n).argtypes = [C.c_void_p, C.c_char_p]
+        _lib.rg_save_snapshot.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        _lib.rg_set_mode.argtypes = [C.c_void_p, C.c_int]
+        _lib.rg_mode.argtypes = [C.c_void_p]
+        _lib.rg_set_camera.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.rg_set.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int]
+        _lib.rg_get.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int]
+        _lib.rg_get_bitfield.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        _lib.rg_get_params.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        _lib.rg_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.rg_time_render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p]
+        _lib.rg_network_inference.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        _lib.rg_encode_pos.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        _lib.rg_encode_dir.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        _lib.rg_encoding_widths.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib.rg_time_inference.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_void_p]
+        _lib.rg_trace_mesh.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        _lib.rg_mesh_triangles.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t]
+        _lib.rg_mesh_count.argtypes = [C.c_void_p]
+        _lib.rg_mesh_count.restype = C.c_uint32
+        _lib.rg_mesh_n_triangles.argtypes = [C.c_void_p, C.c_uint32]
+        _lib.rg_mesh_n_triangles.restype = C.c_uint64
+        _lib.rg_train.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+        _lib.rg_time_train.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+BATCH = 256  # tcnn BATCH_SIZE_GRANULARITY
+
+
+def pad_rows(a: np.ndarray, mult: int = BATCH) -> np.ndarray:
+    n = a.shape[0]
+    m = (n + mult - 1) // mult * mult
+    if m == n:
+        return a
+    return np.concatenate([a, np.repeat(a[-1:], m - n, axis=0)], 0)
+
+
+class RefTestbed:
+    """The reference's ngp::Testbed, headless."""
+
+    def __init__(self):
+        self.l = lib()
+        self.h = self.l.rg_create()
+        if not self.h:
+            raise RuntimeError("rg_create: " + self.l.rg_last_error().decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.l.rg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise RuntimeError(self.l.rg_last_error().decode())
+
+    def load_training_data(self, path):
+        self._ck(self.l.rg_load_training_data(self.h, os.fsencode(path)))
+
+    def load_snapshot(self, path):
+        self._ck(self.l.rg_load_snapshot(self.h, os.fsencode(path)))
+
+    def save_snapshot(self, path, with_optimizer=False):
+        self._ck(self.l.rg_save_snapshot(self.h, os.fsencode(path), int(with_optimizer)))
+
+    def reload_network(self, path):
+        self._ck(self.l.rg_reload_network(self.h, os.fsencode(path)))
+
+    def set_mode(self, mode: int):
+        self._ck(self.l.rg_set_mode(self.h, mode))
+
+    def mode(self) -> int:
+        return int(self.l.rg_mode(self.h))
+
+    def set_camera(self, cols12):
+        c = _f32(cols12).reshape(12)
+        self._ck(self.l.rg_set_camera(self.h, _p(c)))
+
+    def set(self, name, value):
+        v = _f32(np.atleast_1d(value))
+        self._ck(self.l.rg_set(self.h, name.encode(), _p(v), v.size))
+
+    def get(self, name, n=1):
+        v = np.zeros(max(n, 1), np.float32)
+        self._ck(self.l.rg_get(self.h, name.encode(), _p(v), n))
+        return v if n > 1 else float(v[0])
+
+    def bitfield(self, n_bytes=128 ** 3 // 8 * 8):
+        out = np.zeros(n_bytes, np.uint8)
+        self._ck(self.l.rg_get_bitfield(self.h, _p(out), out.size))
+        return out
+
+    def params(self, n):
+        out = np.zeros(n, np.float16)
+        self._ck(self.l.rg_get_params(self.h, _p(out), n))
+        return out
+
+    def render(self, w, h, spp=1, linear=True, raw=False):
+        """-> tonemapped RGBA [h,w,4] (what pyngp.Testbed.render returns); with raw=True also the raw frame buffer
+        (premultiplied linear RGBA of the last sample) and the depth buffer."""
+        out = np.zeros((h, w, 4), np.float32)
+        fr = np.zeros((h, w, 4), np.float32) if raw else None
+        dp = np.zeros((h, w), np.float32) if raw else None
+        self._ck(self.l.rg_render(self.h, w, h, spp, int(linear), _p(out), _p(fr), _p(dp)))
+        return (out, fr, dp) if raw else out
+
+    def time_render(self, w, h, warmup=3, steps=20, l2_flush_bytes=512 << 20):
+        ms = np.zeros(steps, np.float32)
+        self._ck(self.l.rg_time_render(self.h, w, h, warmup, steps, l2_flush_bytes, _p(ms)))
+        return ms
+
+    def widths(self):
+        a, b, c = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._ck(self.l.rg_encoding_widths(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def network(self, coords7):
+        """coords7: [n,7] (warped pos, dt, warped dir) -> raw fp16 (r,g,b,sigma) [n,4]."""
+        c = _f32(coords7).reshape(-1, 7)
+        n = c.shape[0]
+        cp = pad_rows(c)
+        out = np.zeros((4, cp.shape[0]), np.float16)
+        self._ck(self.l.rg_network_inference(self.h, _p(cp), cp.shape[0], _p(out)))
+        return np.ascontiguousarray(out[:, :n].T)
+
+    def encode_pos(self, pos):
+        p = _f32(pos).reshape(-1, 3)
+        n = p.shape[0]
+        pp = pad_rows(p)
+        wdt = self.widths()[0]
+        out = np.zeros((wdt, pp.shape[0]), np.float16)
+        self._ck(self.l.rg_encode_pos(self.h, _p(pp), pp.shape[0], _p(out)))
+        return np.ascontiguousarray(out[:, :n].T)
+
+    def encode_dir(self, dirs01):
+        d = _f32(dirs01).reshape(-1, 3)
+        n = d.shape[0]
+        dp = pad_rows(d)
+        wdt = self.widths()[1]
+        out = np.zeros((wdt, dp.shape[0]), np.float16)
+        self._ck(self.l.rg_encode_dir(self.h, _p(dp), dp.shape[0], _p(out)))
+        return np.ascontiguousarray(out[:, :n].T)
+
+    def time_inference(self, coords_dev_ptr: int, n_total: int, chunk: int = 2 << 20, reps: int = 3) -> float:
+        ms = C.c_float(0)
+        self._ck(self.l.rg_time_inference(self.h, C.c_void_p(coords_dev_ptr), n_total, chunk, reps, C.byref(ms)))
+        return float(ms.value)
+
+    def trace_mesh(self, origins, dirs):
+        """mesh_raytrace_kernel: -> (positions after the trace, directions/normals after the trace)."""
+        o = _f32(origins).reshape(-1, 3).copy()
+        d = _f32(dirs).reshape(-1, 3).copy()
+        self._ck(self.l.rg_trace_mesh(self.h, _p(o), _p(d), o.shape[0]))
+        return o, d
+
+    def mesh_triangles(self, m):
+        n = int(self.l.rg_mesh_n_triangles(self.h, m))
+        out = np.zeros((n, 9), np.float32)
+        self._ck(self.l.rg_mesh_triangles(self.h, m, _p(out), n))
+        return out
+
+    def mesh_count(self):
+        return int(self.l.rg_mesh_count(self.h))
+
+    def train(self, batch=1 << 18, n_steps=1):
+        loss = C.c_float(0)
+        self._ck(self.l.rg_train(self.h, batch, n_steps, C.byref(loss)))
+        return float(loss.value)
+
+    def time_train(self, batch=1 << 18, warmup=8, steps=20):
+        ms, sm = C.c_float(0), C.c_float(0)
+        self._ck(self.l.rg_time_train(self.h, batch, warmup, steps, C.byref(ms), C.byref(sm)))
+        return float(ms.value), float(sm.value)
+
+
+# ---- scene files in the reference's own formats ------------------------------------------------------------------------------
+
+def write_obj(path, tris):
+    """Triangle soup [n,9] -> ASCII .obj the reference's tinyobj loader reads (one v-triple + f per triangle)."""
+    t = np.asarray(tris, np.float32).reshape(-1, 3)
+    with open(path, "w") as f:
+        # %.9g round-trips float32 exactly
+        f.write("".join("v %.9g %.9g %.9g\n" % (a, b, c) for a, b, c in t))
+        n = t.shape[0] // 3
+        f.write("".join("f %d %d %d\n" % (3 * i + 1, 3 * i + 2, 3 * i + 3) for i in range(n)))
+
+
+def write_scene(path, entries):
+    """entries: list of (type, path, center). The file name must contain 'geometry' for the reference to pick Geometry mode
+    (mode_from_scene, src/common_host.cu:146-166)."""
+    assert "geometry" in os.path.basename(path)
+    with open(path, "w") as f:
+        json.dump({"geometry": [{"center": [float(x) for x in c], "path": p, "type": t} for t, p, c in entries]}, f)

@@ -63,6 +63,10 @@ typedef struct {
 	float parallax_shift[3];
 	// m_render_aabb_to_local (column-major mat3): crop box rotation, applied when crop_rotated != 0 (src/testbed_nerf.cu:1530-1532)
 	int32_t crop_rotated; float render_aabb_to_local[9];
+	// optional: uint8[width*height], only pixels with a non-zero entry are rendered by orc_render_frame / orc_render_nerf /
+	// orc_render_mesh (the others keep the cleared value). Lets a test check a stratified subset of a full-size frame.
+	int32_t mask_pad;
+	const uint8_t* pixel_mask;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----

@@ -241,6 +241,7 @@ static void render_mesh(const orc_scene& s, const orc_render_params& p, float* f
 	parallel_rows(p.height, p.n_threads, [&](int y) {
 		for (int x = 0; x < p.width; ++x) {
 			uint32_t idx = x + p.width * y;
+			if (p.pixel_mask && !p.pixel_mask[idx]) continue;
 			// :488-579 init_rays_with_payload_kernel_mesh_geometry (pixel_to_ray: no rolling shutter, camera_matrix as is)
 			vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
 			vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};

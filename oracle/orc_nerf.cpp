@@ -748,6 +748,7 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 		for (int x = 0; x < p.width; ++x) {
 			uint32_t idx = x + p.width * y;
 			if (n_steps_out) n_steps_out[idx] = 0;
+			if (p.pixel_mask && !p.pixel_mask[idx]) continue;
 			RayState r = init_ray(p, bits, x, y, &depth[idx]);
 			// :1526-1528 envmap -> frame buffer for every valid ray; in hybrid frames only where the mesh pass left nothing
 			if (p.envmap && (r.d.x != 0.0f || r.d.y != 0.0f || r.d.z != 0.0f) && !(depth_test && depth[idx] < MAX_DEPTH)) { // invalid rays return before this (:1494-1498)

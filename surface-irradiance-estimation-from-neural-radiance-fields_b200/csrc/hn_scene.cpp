@@ -296,6 +296,14 @@ void load_scene_file(hn_context* ctx, const std::string& path) {
 		}
 	}
 	build_scene(ctx);
+	// load_scene :3183-3189 runs AFTER the entries are loaded: m_render_aabb = m_aabb = mesh root box inflated by 4, identity
+	// crop rotation - so in a Geometry-mode scene the NeRF rays enter at THAT box (not at the snapshot's render box) and the
+	// DDA walks from there; the NeRF itself stays pinned to the unit cube (train_aabb above).
+	if (!ctx->meshes.empty()) {
+		std::memcpy(ctx->opt.render_aabb, ctx->opt.mesh_aabb, sizeof(ctx->opt.render_aabb));
+		const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+		std::memcpy(ctx->opt.render_aabb_to_local, ident, sizeof(ident));
+	}
 }
 
 } // namespace hn

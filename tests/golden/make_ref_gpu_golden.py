@@ -87,7 +87,7 @@ def stage_network(out_dir, tag, cfg_rel, blob_range, frame_res, aabb_scale=1, ca
     rt.set("screen_center", [0.5, 0.5])
     print(f"[{tag}] reference mode={rt.mode()} n_params={rt.get('n_params'):.0f} ours={info.n_params} widths={rt.widths()} "
           f"max_cascade={rt.get('max_cascade')} cone={rt.get('cone_angle_constant')} aabb={rt.get('aabb', 6)} render_aabb={rt.get('render_aabb', 6)}")
-    res = {}
+    res = {"level_scales": np.array([info.level_scales[i] for i in range(info.n_levels)], f32)}
     # parameters as the reference's trainer holds them, occupancy bits as its kernels built them from the snapshot's grid
     rp = rt.params(int(info.n_params))
     print(f"[{tag}] params bit-identical after the snapshot round trip: {np.array_equal(rp.view(np.uint16), params.view(np.uint16))}")
@@ -128,7 +128,7 @@ def stage_network(out_dir, tag, cfg_rel, blob_range, frame_res, aabb_scale=1, ca
         print(f"[{tag}] network {name} vs ref: max abs {dd.max():.3e} (rgb {dd[:, :3].max():.3e}, sigma {dd[:, 3].max():.3e}), max rel {rel.max():.3e}")
     sh_o = None
     try:
-        sh_o = orc.sh4(dirs) if hasattr(orc, "sh4") else None
+        sh_o = orc.sh4(d01) if hasattr(orc, "sh4") else None
     except Exception:
         pass
     if sh_o is not None:
@@ -185,6 +185,11 @@ def stage_hybrid(out_dir, tag, meshes, centers, res_wh, cam):
     ref_tris = [rt.mesh_triangles(i) for i in range(rt.mesh_count())]
     for i, t in enumerate(ref_tris):
         res[f"mesh_in_{i}"] = np.asarray(meshes[i], f32)
+        res[f"ref_tris_{i}"] = t  # as the reference holds them: load_mesh-normalised, reordered by its BVH build
+        key = lambda a: a[np.lexsort(a.T[::-1])]
+        # GeometryBvh::build_mesh nth_element()s the mesh vector itself, so reference mesh i is SOME input mesh
+        same = [np.array_equal(key(t).view(np.uint32), key(orc.normalize_mesh(m, c)).view(np.uint32)) for m, c in zip(meshes, centers)]
+        print(f"[{tag}] reference mesh {i}: load_mesh-normalised triangles bit-identical (as a set) to the oracle's normalisation of input mesh {same.index(True) if any(same) else None}")
     # a-17/18 mesh trace on seeded rays (camera rays of this view + random + axis-aligned)
     rng = np.random.default_rng(7)
     o_c, d_c, _, _ = tb.op_init_rays(cam, cam, 64, 48, 0)

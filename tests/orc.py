@@ -42,7 +42,7 @@ class RenderParams(C.Structure):
                 ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p),
                 ("render_mode", i32), ("depth_scale", f32),
                 ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3),
-                ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9)]
+                ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9), ("mask_pad", i32), ("pixel_mask", C.c_void_p)]
 
 
 def P(a):
@@ -126,7 +126,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
                   clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
                   lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0),
-                  render_aabb_to_local=None) -> RenderParams:
+                  render_aabb_to_local=None, pixel_mask=None) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -163,6 +163,11 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     R = ident if render_aabb_to_local is None else [float(v) for v in np.asarray(render_aabb_to_local, np.float32).reshape(9)]
     p.render_aabb_to_local[:] = R
     p.crop_rotated = int(any(abs(a - b) > 0 for a, b in zip(R, ident)))
+    if pixel_mask is not None:
+        pm = np.ascontiguousarray(pixel_mask, np.uint8).reshape(-1)
+        assert pm.size == w * h
+        p._mask_keep = pm
+        p.pixel_mask = pm.ctypes.data
     if envmap is not None:
         env = np.ascontiguousarray(envmap, np.float32)
         assert env.ndim == 3 and env.shape[2] == 4
@@ -238,6 +243,33 @@ def encode(cfg: NetConfig, params, positions):
     out = np.empty((pos.shape[0], 32), np.float16)
     lib.orc_encode(C.byref(cfg), P(params), P(pos), pos.shape[0], P(out))
     return out
+
+
+def sh4(dirs01):
+    """degree-4 SH of warped directions in [0,1]^3 -> fp16 [n][16]"""
+    d = np.ascontiguousarray(dirs01, np.float32).reshape(-1, 3)
+    out = np.empty((d.shape[0], 16), np.float16)
+    lib.orc_sh4(P(d), C.c_uint32(d.shape[0]), P(out))
+    return out
+
+
+def normalize_mesh(tris, center=(0.0, 0.0, 0.0)):
+    """Testbed::load_mesh's normalisation (src/testbed_geometry_training.cpp:2805-2823) in float32, same operation order:
+    box of all vertices inflated by 0.5 % of its diagonal, longest side -> 1, centred on 0.5, then offset by `center`."""
+    f = np.float32
+    v = np.ascontiguousarray(tris, np.float32).reshape(-1, 3)
+    lo, hi = v.min(0), v.max(0)
+    diag = hi - lo
+    ln = f(0.0)
+    for d in range(3):
+        ln = f(ln + f(diag[d] * diag[d]))
+    infl = f(np.sqrt(ln) * f(0.005))
+    lo = (lo - infl).astype(f); hi = (hi + infl).astype(f)
+    diag = (hi - lo).astype(f)
+    scale = f(diag.max())
+    x = ((((v - lo).astype(f) - (f(0.5) * diag).astype(f)).astype(f) / scale).astype(f) + f(0.5)).astype(f)
+    x = (x + np.asarray(center, f)).astype(f)
+    return np.ascontiguousarray(x.reshape(-1, 9))
 
 
 def network(cfg: NetConfig, params, coords):

@@ -67,6 +67,9 @@ typedef struct {
 	// orc_render_mesh (the others keep the cleared value). Lets a test check a stratified subset of a full-size frame.
 	int32_t mask_pad;
 	const uint8_t* pixel_mask;
+	// training: mean of max(density grid, 0) over cascade 0 (m_nerf.density_grid_mean); below NERF_MIN_OPTICAL_THICKNESS (0.01) the
+	// loss adds the unscaled L1 density regulariser (src/testbed_nerf.cu:1113,1161-1164). 0 here = "not given" = regulariser off.
+	float density_grid_mean; int32_t pad2;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----

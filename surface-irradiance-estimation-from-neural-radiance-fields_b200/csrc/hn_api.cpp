@@ -26,6 +26,11 @@ static const hn::ParamTextures* param_textures(hn_context* ctx) {
 	if (!ctx->opt.eval_tex_gather || !ctx->params.p || ctx->net.F != 4) return nullptr;
 	if (ctx->param_tex.ptr == ctx->params.p) return &ctx->param_tex;
 	release_param_textures(ctx);
+	{ // a table beyond the 1D linear texture limit (e.g. log2_hashmap_size 24, F = 4) falls back to the LSU gather instead of failing
+		int max_texels = 0;
+		HN_CUDA(cudaDeviceGetAttribute(&max_texels, cudaDevAttrMaxTexture1DLinearWidth, ctx->device));
+		if ((ctx->net.n_params * sizeof(__half)) / 8 > (size_t)max_texels) { ctx->param_tex.ptr = nullptr; return nullptr; }
+	}
 	cudaResourceDesc rd = {};
 	rd.resType = cudaResourceTypeLinear;
 	rd.res.linear.devPtr = (void*)ctx->params.p;
@@ -170,6 +175,7 @@ void refresh_bitfield_from_device_grid(hn_context* ctx) {
 	HN_CUDA(cudaMemcpyAsync(&sum, d_sum.p, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	const float mean = (float)(sum / GRID_CELLS);
+	ctx->density_grid_mean = mean;
 	const float thresh = std::min(0.01f, mean); // NERF_MIN_OPTICAL_THICKNESS, src/testbed_nerf.cu:297
 	launch_grid_to_bitfield(d_grid.p, n_cascades, thresh, ctx->bitfield.p, ctx->stream);
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -187,6 +193,7 @@ int hn_set_occupancy_bitfield(hn_context* ctx, const uint8_t* bits, size_t n_byt
 	HN_CUDA(cudaSetDevice(ctx->device));
 	HN_CUDA(cudaMemcpy(ctx->bitfield.p, bits, n_bytes, cudaMemcpyHostToDevice));
 	ctx->density_grid_host.clear();
+	ctx->density_grid_mean = 1.0f;
 	refresh_occ_bounds(ctx);
 	ctx->has_bitfield = true;
 	HN_CATCH(ctx)
@@ -540,7 +547,10 @@ namespace hn {
 FrameArgs train_frame_args(hn_context* ctx) {
 	const float rs[4] = {0.f, 0.f, 0.f, 1.f};
 	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, 1, 1);
-	a.crop_rotated = 0; // training marches the training box (m_aabb), never the rotated render crop
+	// training clips and marches rays against the TRAINING box (m_aabb: generate_training_samples_nerf, src/testbed_nerf.cu:737-890),
+	// never the render crop (m_render_aabb / m_render_aabb_to_local), so a crop set for viewing cannot change what is trained
+	std::memcpy(a.render_aabb, a.train_aabb, sizeof(a.render_aabb));
+	a.crop_rotated = 0;
 	return a;
 }
 } // namespace hn

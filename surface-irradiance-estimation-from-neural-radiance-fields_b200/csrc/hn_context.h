@@ -153,6 +153,7 @@ struct hn_context {
 	bool has_bitfield = false;
 	hn::DevBuf<float> density_grid;         // device copy of the float grid [128^3 x grid_cascades] (Morton order), kept for the live updates
 	uint32_t grid_cascades = 0;
+	float density_grid_mean = 1.0f;         // m_nerf.density_grid_mean (mean of max(v, 0) over cascade 0); 1 = unknown (bitfield set directly)
 	int occ_cells[hn::CASCADES * 6] = {};   // per-mip bounds of the set cells (cell coordinates), refreshed with the bitfield
 
 	// scene
@@ -213,6 +214,9 @@ Json msgpack_parse(const std::string& bytes);
 std::string msgpack_write(const Json& j);
 std::string zlib_inflate(const std::string& in);
 std::string zlib_store(const std::string& in);
+std::string gzip_inflate(const std::string& in);
+std::string gzip_store(const std::string& in);
+std::string snapshot_unwrap(const std::string& in); // gzip / zlib / plain, detected by magic like zstr::istream
 void load_snapshot_file(hn_context* ctx, const std::string& path);
 void save_snapshot_file(hn_context* ctx, const std::string& path);
 // hn_api.cpp (shared by the snapshot loader)

@@ -1,6 +1,6 @@
 // Snapshots: the reference's `.ingp` / `.msgpack` files (Testbed::save_snapshot / load_snapshot, src/testbed.cu:5219-5488):
 // the network config JSON plus a "snapshot" object, serialised as MessagePack (nlohmann::json::to_msgpack), and for `.ingp`
-// wrapped in a zlib stream (zstr). This is how a trained NeRF enters a hybrid scene (load_scene, type "Nerf",
+// wrapped in a gzip member by zstr (read: gzip, zlib or plain, auto-detected like zstr::istream). This is how a trained NeRF enters a hybrid scene (load_scene, type "Nerf",
 // src/testbed_geometry_training.cu:3172). Self-contained: a DEFLATE decoder (RFC 1950/1951), a MessagePack reader/writer.
 #include "hn_context.h"
 #include "hn_json.h"
@@ -85,13 +85,8 @@ uint32_t adler32(const std::string& s) {
 
 } // namespace
 
-std::string zlib_inflate(const std::string& in) {
-	if (in.size() < 6) throw std::runtime_error("snapshot: zlib stream too short");
-	const uint8_t* d = (const uint8_t*)in.data();
-	if ((d[0] & 0x0f) != 8 || ((d[0] << 8) | d[1]) % 31 != 0 || (d[1] & 0x20)) throw std::runtime_error("snapshot: not a zlib stream");
-	BitReader br(d + 2, in.size() - 2);
-	std::string out;
-	out.reserve(in.size() * 2);
+// raw DEFLATE body (RFC 1951) starting at br; leaves br byte-aligned just behind the last block
+static void deflate_body(BitReader& br, std::string& out) {
 	bool last;
 	do {
 		last = br.bits(1) != 0;
@@ -143,11 +138,92 @@ std::string zlib_inflate(const std::string& in) {
 			throw std::runtime_error("snapshot: bad DEFLATE block type");
 		}
 	} while (!last);
+	// bytes already pulled into the bit buffer but not consumed belong to the trailer
+	br.pos -= (size_t)(br.cnt / 8);
 	br.align();
+}
+
+static bool is_zlib_header(const uint8_t* d, size_t n) { return n >= 2 && (d[0] & 0x0f) == 8 && ((d[0] << 8) | d[1]) % 31 == 0 && !(d[1] & 0x20); }
+
+std::string zlib_inflate(const std::string& in) {
+	if (in.size() < 6) throw std::runtime_error("snapshot: zlib stream too short");
+	const uint8_t* d = (const uint8_t*)in.data();
+	if (!is_zlib_header(d, in.size())) throw std::runtime_error("snapshot: not a zlib stream");
+	BitReader br(d + 2, in.size() - 2);
+	std::string out;
+	out.reserve(in.size() * 2);
+	deflate_body(br, out);
 	if (br.pos + 4 <= br.n) {
 		uint32_t want = ((uint32_t)br.p[br.pos] << 24) | ((uint32_t)br.p[br.pos + 1] << 16) | ((uint32_t)br.p[br.pos + 2] << 8) | br.p[br.pos + 3];
 		if (want != adler32(out)) throw std::runtime_error("snapshot: zlib checksum mismatch");
 	}
+	return out;
+}
+
+static uint32_t crc32_of(const std::string& s) {
+	static uint32_t table[256];
+	static bool init = false;
+	if (!init) {
+		for (uint32_t i = 0; i < 256; ++i) { uint32_t c = i; for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1; table[i] = c; }
+		init = true;
+	}
+	uint32_t c = 0xFFFFFFFFu;
+	for (unsigned char ch : s) c = table[(c ^ ch) & 0xFFu] ^ (c >> 8);
+	return c ^ 0xFFFFFFFFu;
+}
+
+// gzip member (RFC 1952): what the reference WRITES - Testbed::save_snapshot streams through zstr::ostream, whose
+// deflateInit2(..., 15 + 16, ...) selects the gzip container even at Z_NO_COMPRESSION (dependencies/zstr/src/zstr.hpp:107).
+std::string gzip_inflate(const std::string& in) {
+	const uint8_t* d = (const uint8_t*)in.data();
+	const size_t n = in.size();
+	if (n < 18 || d[0] != 0x1f || d[1] != 0x8b) throw std::runtime_error("snapshot: not a gzip stream");
+	if (d[2] != 8) throw std::runtime_error("snapshot: gzip compression method is not DEFLATE");
+	const uint8_t flg = d[3];
+	size_t pos = 10;
+	auto need = [&](size_t k) { if (pos + k > n) throw std::runtime_error("snapshot: truncated gzip header"); };
+	if (flg & 4) { need(2); size_t xlen = d[pos] | (d[pos + 1] << 8); pos += 2; need(xlen); pos += xlen; } // FEXTRA
+	if (flg & 8) { while (true) { need(1); if (!d[pos++]) break; } }                                     // FNAME
+	if (flg & 16) { while (true) { need(1); if (!d[pos++]) break; } }                                    // FCOMMENT
+	if (flg & 2) { need(2); pos += 2; }                                                                  // FHCRC
+	BitReader br(d + pos, n - pos);
+	std::string out;
+	out.reserve(in.size() * 2);
+	deflate_body(br, out);
+	if (br.pos + 8 > br.n) throw std::runtime_error("snapshot: truncated gzip trailer");
+	const uint8_t* t = br.p + br.pos;
+	const uint32_t crc = t[0] | (t[1] << 8) | (t[2] << 16) | ((uint32_t)t[3] << 24), isize = t[4] | (t[5] << 8) | (t[6] << 16) | ((uint32_t)t[7] << 24);
+	if (crc != crc32_of(out)) throw std::runtime_error("snapshot: gzip CRC32 mismatch");
+	if (isize != (uint32_t)out.size()) throw std::runtime_error("snapshot: gzip length mismatch");
+	return out;
+}
+
+// zstr::istream auto-detection (zstr.hpp:240-262): gzip magic 1f 8b, a valid zlib header, else the bytes pass through as they are
+std::string snapshot_unwrap(const std::string& in) {
+	const uint8_t* d = (const uint8_t*)in.data();
+	if (in.size() >= 2 && d[0] == 0x1f && d[1] == 0x8b) return gzip_inflate(in);
+	if (is_zlib_header(d, in.size())) return zlib_inflate(in);
+	return in;
+}
+
+// gzip member of stored (uncompressed) blocks: the container the reference writes, trivially produced
+std::string gzip_store(const std::string& in) {
+	std::string out;
+	const unsigned char hdr[10] = {0x1f, 0x8b, 8, 0, 0, 0, 0, 0, 0, 3}; // no flags, no mtime, OS = unix
+	out.append((const char*)hdr, 10);
+	size_t i = 0;
+	do {
+		size_t k = std::min<size_t>(65535, in.size() - i);
+		bool last = i + k >= in.size();
+		out.push_back(last ? 1 : 0);
+		out.push_back((char)(k & 0xff)); out.push_back((char)(k >> 8));
+		out.push_back((char)(~k & 0xff)); out.push_back((char)((~k >> 8) & 0xff));
+		out.append(in, i, k);
+		i += k;
+	} while (i < in.size());
+	const uint32_t c = crc32_of(in), sz = (uint32_t)in.size();
+	for (int sft = 0; sft < 32; sft += 8) out.push_back((char)((c >> sft) & 0xff));
+	for (int sft = 0; sft < 32; sft += 8) out.push_back((char)((sz >> sft) & 0xff));
 	return out;
 }
 
@@ -307,7 +383,7 @@ std::string msgpack_write(const Json& j) { std::string o; msg_write(o, j); retur
 // (update_density_grid_mean_and_bitfield), aabb / render_aabb, camera, sun/up direction, exposure, background colour.
 void load_snapshot_file(hn_context* ctx, const std::string& path) {
 	std::string bytes = read_text_file(path);
-	if (ends_with(path, ".ingp")) bytes = zlib_inflate(bytes); // zstr::ifstream (src/testbed.cu:255-262)
+	if (ends_with(path, ".ingp")) bytes = snapshot_unwrap(bytes); // zstr::ifstream (src/testbed.cu:255-262): gzip, zlib or plain
 	Json cfg = msgpack_parse(bytes);
 	bytes.clear(); bytes.shrink_to_fit();
 	if (!cfg.is_object() || !cfg.contains("snapshot")) throw std::runtime_error("File '" + path + "' does not contain a snapshot.");
@@ -330,6 +406,12 @@ void load_snapshot_file(hn_context* ctx, const std::string& path) {
 	}
 	if (snap.contains("aabb")) read_box(snap.at("aabb"), o.train_aabb);
 	if (snap.contains("render_aabb")) read_box(snap.at("render_aabb"), o.render_aabb);
+	if (snap.contains("render_aabb_to_local")) { // mat3 as 3 rows (tcnn vec_json.h:40-48) -> column-major option
+		const Json& m = snap.at("render_aabb_to_local");
+		if (m.type == Json::Array && m.arr.size() == 3) {
+			for (int row = 0; row < 3; ++row) { float r3[3]; read_vec(m.arr[row], r3, 3); for (int col = 0; col < 3; ++col) o.render_aabb_to_local[3 * col + row] = r3[col]; }
+		}
+	}
 	if (snap.contains("sun_dir")) read_vec(snap.at("sun_dir"), o.sun_dir, 3);
 	if (snap.contains("up_dir")) read_vec(snap.at("up_dir"), o.up_dir, 3);
 	o.exposure = (float)snap.value("exposure", (double)o.exposure);
@@ -454,6 +536,11 @@ void save_snapshot_file(hn_context* ctx, const std::string& path) {
 	auto box = [](const float* b) { Json j; j.type = Json::Object; j.set("min") = jvec(b, 3); j.set("max") = jvec(b + 3, 3); return j; };
 	snap.set("aabb") = box(o.train_aabb);
 	snap.set("render_aabb") = box(o.render_aabb);
+	{
+		Json m; m.type = Json::Array;
+		for (int row = 0; row < 3; ++row) { float r3[3]; for (int col = 0; col < 3; ++col) r3[col] = o.render_aabb_to_local[3 * col + row]; m.arr.push_back(jvec(r3, 3)); }
+		snap.set("render_aabb_to_local") = std::move(m);
+	}
 	snap.set("up_dir") = jvec(o.up_dir, 3);
 	snap.set("sun_dir") = jvec(o.sun_dir, 3);
 	snap.set("exposure") = jnum(o.exposure);
@@ -468,7 +555,7 @@ void save_snapshot_file(hn_context* ctx, const std::string& path) {
 	cam.set("screen_center") = jvec(o.screen_center, 2);
 	cam.set("zoom") = jnum(o.zoom);
 	std::string bytes = msgpack_write(cfg);
-	if (ends_with(path, ".ingp")) bytes = zlib_store(bytes);
+	if (ends_with(path, ".ingp")) bytes = gzip_store(bytes); // the gzip container zstr::ostream produces
 	std::ofstream f(path, std::ios::binary);
 	if (!f) throw std::runtime_error("cannot write '" + path + "'");
 	f.write(bytes.data(), (std::streamsize)bytes.size());

@@ -212,7 +212,7 @@ __device__ __forceinline__ float warp_incl_prod(float v, uint32_t lane) {
 // stop get zero gradients (the reference compacts them away). loss_acc += mean(loss_rgb) / n_rays_total.
 __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32_t n_rays_total, const uint32_t* __restrict__ numsteps_in, const uint32_t* __restrict__ base_in,
 	const float4* __restrict__ coords, const __half* __restrict__ out, const __half* __restrict__ density_out, const float* __restrict__ ray_target,
-	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, __half* __restrict__ d_out, float* __restrict__ d_sigma,
+	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, float l1_reg_density, __half* __restrict__ d_out, float* __restrict__ d_sigma,
 	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc) {
 	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const uint32_t lane = threadIdx.x & 31u;
@@ -287,7 +287,11 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 				const float d1 = ls * (weight * gg * rgb_derivative(o1, rgb_act) + fmaxf(0.0f, l2_reg * o1));
 				const float d2 = ls * (weight * gb * rgb_derivative(o2, rgb_act) + fmaxf(0.0f, l2_reg * o2));
 				dst[0] = make_uint4(pack_h2(d0, d1), pack_h2(d2, 0.f), 0, 0); dst[1] = make_uint4(0, 0, 0, 0);
-				d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T_after * cr - sr) + gg * (T_after * cg - sg) + gb * (T_after * cb - sb)));
+				// + the reference's UNSCALED L1 density regulariser (src/testbed_nerf.cu:1113,1161-1164): pushes negative raw densities down
+				// while the grid is nearly empty (mean density < NERF_MIN_OPTICAL_THICKNESS), which keeps such a grid from collapsing.
+				// (its near-distance term is inert: near_distance is 0 on this path)
+				d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T_after * cr - sr) + gg * (T_after * cg - sg) + gb * (T_after * cb - sb)))
+					+ (sraw < 0.0f ? -l1_reg_density : 0.0f);
 			}
 		}
 		Tc *= __shfl_sync(0xffffffffu, P, 31);
@@ -537,7 +541,7 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	__half* g_out = t.dact[0].p;               // [n][16]
 	float* d_sigma = (float*)t.dact[3].p;      // [n] fp32 (buffer holds n*64 halfs)
 	train_loss_kernel<<<blocks((size_t)n_rays * 32, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
-		loss_type, loss_scale, a.rgb_act, a.density_act, g_out, d_sigma, used_dev, t.loss_acc.p);
+		loss_type, loss_scale, a.rgb_act, a.density_act, ctx->density_grid_mean < 0.01f ? 1e-4f : 0.0f, g_out, d_sigma, used_dev, t.loss_acc.p);
 	ev.stop(t.ms[2]);
 	// ---- backward
 	ev.start();
@@ -648,7 +652,7 @@ void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
 	// rays per batch follow the measured samples per ray towards the target batch size (src/testbed_nerf.cu:3049-3056)
 	if (t.n_samples_last > 0) {
 		const double per_ray = (double)t.n_samples_last / (double)n_rays;
-		uint32_t next = (uint32_t)std::min<double>((double)c.target_batch / per_ray, 1u << 20);
+		uint32_t next = (uint32_t)std::min<double>((double)c.target_batch / per_ray, 1u << 18); // the reference's cap (src/testbed_nerf.cu:2943-2944)
 		next = std::max(128u, (next + 127u) / 128u * 128u);
 		t.rays_per_batch = next;
 	}

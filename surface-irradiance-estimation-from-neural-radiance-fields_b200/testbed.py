@@ -202,6 +202,9 @@ class Testbed:
         self._check(_lib.hn_load_snapshot(self._h, os.fsencode(path)))
 
     def save_snapshot(self, path: str, include_optimizer_state: bool = False):
+        """pyngp.Testbed.save_snapshot(path, include_optimizer_state) (python_api.cu:437): with the flag the optimizer stack
+        (Adam moments, per-parameter step counters, EMA weights) is serialised as tcnn's Trainer::serialize(true) does."""
+        self.set_option("snapshot_optimizer_state", float(bool(include_optimizer_state)))
         self._check(_lib.hn_save_snapshot(self._h, os.fsencode(path)))
 
     def set_aabb_scale(self, s: int):

@@ -42,7 +42,8 @@ class RenderParams(C.Structure):
                 ("env_w", i32), ("env_h", i32), ("env_samples", i32), ("env_pad", i32), ("envmap", C.c_void_p),
                 ("render_mode", i32), ("depth_scale", f32),
                 ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3),
-                ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9), ("mask_pad", i32), ("pixel_mask", C.c_void_p)]
+                ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9), ("mask_pad", i32), ("pixel_mask", C.c_void_p),
+                ("density_grid_mean", f32), ("pad2", i32)]
 
 
 def P(a):
@@ -126,7 +127,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
                   clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
                   lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0),
-                  render_aabb_to_local=None, pixel_mask=None) -> RenderParams:
+                  render_aabb_to_local=None, pixel_mask=None, density_grid_mean=0.0) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -163,6 +164,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     R = ident if render_aabb_to_local is None else [float(v) for v in np.asarray(render_aabb_to_local, np.float32).reshape(9)]
     p.render_aabb_to_local[:] = R
     p.crop_rotated = int(any(abs(a - b) > 0 for a, b in zip(R, ident)))
+    p.density_grid_mean = float(density_grid_mean)
     if pixel_mask is not None:
         pm = np.ascontiguousarray(pixel_mask, np.uint8).reshape(-1)
         assert pm.size == w * h

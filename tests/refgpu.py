@@ -244,3 +244,27 @@ def write_scene(path, entries):
     assert "geometry" in os.path.basename(path)
     with open(path, "w") as f:
         json.dump({"geometry": [{"center": [float(x) for x in c], "path": p, "type": t} for t, p, c in entries]}, f)
+
+
+def write_snapshot_py(path, config_json_path, params_fp16, density_grid, aabb_scale=1, camera_cols=None, rel_focal=None):
+    """A `.ingp` snapshot produced WITHOUT the product library (python msgpack + gzip, the container zstr writes): network config
+    JSON + fp16 parameter blob + fp16 density grid, the members Testbed::load_snapshot requires (src/testbed.cu:5285-5463).
+    Used by bench.py's reference arm so that nothing of the product touches the reference's inputs."""
+    import gzip
+    import msgpack
+    cfg = json.load(open(config_json_path))
+    cam = np.asarray(camera_cols if camera_cols is not None else [1, 0, 0, 0, -1, 0, 0, 0, -1, 0.5, 0.5, 2.0], np.float32).reshape(4, 3)
+    rf = [1.0572856, 1.0572856] if rel_focal is None else [float(rel_focal[0]), float(rel_focal[1])]
+    lo, hi = 0.5 - 0.5 * aabb_scale, 0.5 + 0.5 * aabb_scale
+    cfg["snapshot"] = {
+        "version": 1, "mode": "nerf", "n_params": int(params_fp16.size), "params_type": "__half",
+        "params_binary": np.ascontiguousarray(params_fp16, np.float16).tobytes(),
+        "density_grid_size": 128, "density_grid_binary": np.ascontiguousarray(density_grid, np.float32).astype(np.float16).tobytes(),
+        "nerf": {"aabb_scale": int(aabb_scale), "rgb": {"rays_per_batch": 4096, "measured_batch_size": 0, "measured_batch_size_before_compaction": 0}},
+        "training_step": 0, "loss": 0.0, "aabb": {"min": [lo] * 3, "max": [hi] * 3}, "render_aabb": {"min": [lo] * 3, "max": [hi] * 3},
+        "up_dir": [0.0, 1.0, 0.0], "sun_dir": [0.57735026919] * 3, "exposure": 0.0, "background_color": [0.0, 0.0, 0.0, 1.0],
+        "camera": {"matrix": [[float(cam[c][r]) for c in range(4)] for r in range(3)], "fov_axis": 1, "relative_focal_length": rf,
+                   "screen_center": [0.5, 0.5], "zoom": 1.0},
+    }
+    with open(path, "wb") as f:
+        f.write(gzip.compress(msgpack.packb(cfg, use_bin_type=True), compresslevel=0))

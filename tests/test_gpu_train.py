@@ -28,11 +28,11 @@ def make_rays(rng, n):
     return o, d, t0
 
 
-def nerf_setup(hn, root, blob_scale, config="nerf/base.json"):
+def nerf_setup(hn, root, blob_scale, config="nerf/base.json", grid_value=1.0):
     tb = hn.Testbed()
     tb.reload_network_from_file(os.path.join(root, "configs", *config.split("/")))
     info = tb.network_info()
-    grid = hn.synthetic.sphere_density_grid(0.35)
+    grid = hn.synthetic.sphere_density_grid(0.35, value=grid_value)
     params = hn.synthetic.random_params(info, 1337, blob_scale)
     tb.set_params(params)
     tb.set_density_grid(grid, 1)
@@ -40,9 +40,11 @@ def nerf_setup(hn, root, blob_scale, config="nerf/base.json"):
     return tb, params, grid
 
 
-@pytest.mark.parametrize("loss_type,config", [(1, "nerf/base.json"), (0, "nerf/base.json"), (4, "geometry/base.json"), (5, "nerf/base.json")])
-def test_gradients_match_oracle(hn, orc, root, loss_type, config):
-    tb, params, grid = nerf_setup(hn, root, 0.5, config)
+@pytest.mark.parametrize("loss_type,config,grid_value", [(1, "nerf/base.json", 1.0), (0, "nerf/base.json", 1.0), (4, "geometry/base.json", 1.0),
+                                                         (5, "nerf/base.json", 1.0), (1, "nerf/base.json", 0.02)])
+def test_gradients_match_oracle(hn, orc, root, loss_type, config, grid_value):
+    # grid_value 0.02: mean density 0.004 < NERF_MIN_OPTICAL_THICKNESS -> the L1 density regulariser of the reference is active
+    tb, params, grid = nerf_setup(hn, root, 0.5, config, grid_value)
     rng = np.random.default_rng(5)
     n = 96
     o, d, t0 = make_rays(rng, n)
@@ -52,7 +54,7 @@ def test_gradients_match_oracle(hn, orc, root, loss_type, config):
     info = tb.network_info()
     cfg = orc.net_config_from_info(info)
     bits = orc.bitfield_from_grid(grid, 1)[0]
-    p = orc.render_params(8, 8, hn.synthetic.default_camera())
+    p = orc.render_params(8, 8, hn.synthetic.default_camera(), density_grid_mean=float(np.maximum(grid, 0).mean()))
     wl, wg, ws = orc.train_gradients(p, cfg, params, bits, o, d, t0, targets, bgs, loss_type=loss_type, loss_scale=128.0)
     assert ws.sum() > 5000
     assert np.mean(steps == ws) >= 0.97            # the T < 1e-4 early stop can flip by a sample

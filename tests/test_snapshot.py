@@ -3,6 +3,7 @@ the container formats (python `msgpack` + `zlib`, real DEFLATE with dynamic Huff
 without a GPU the call gets as far as the parameter upload, and the network shape it reports proves the decode. GPU part:
 snapshot round trips render the identical frame."""
 import ctypes as C
+import gzip
 import os
 import zlib
 
@@ -11,7 +12,7 @@ import numpy as np
 import pytest
 
 
-def make_snapshot(root, synthetic, info_like, path, compress=True, params_type="__half", aabb_scale=1, level=6):
+def make_snapshot(root, synthetic, info_like, path, compress=True, params_type="__half", aabb_scale=1, level=6, container="zlib"):
     import json
     cfg = json.load(open(os.path.join(root, "configs", "nerf", "base.json")))
     blob = synthetic.random_params(info_like, 21, 1.0)
@@ -29,7 +30,12 @@ def make_snapshot(root, synthetic, info_like, path, compress=True, params_type="
     }
     raw = msgpack.packb(cfg, use_bin_type=True)
     with open(path, "wb") as f:
-        f.write(zlib.compress(raw, level) if compress else raw)
+        if not compress:
+            f.write(raw)
+        elif container == "gzip":  # what the reference writes: zstr::ostream -> deflateInit2(.., 15 + 16, ..) = gzip member
+            f.write(gzip.compress(raw, compresslevel=level))
+        else:
+            f.write(zlib.compress(raw, level))
     return blob, grid.astype(np.float32)
 
 
@@ -42,6 +48,35 @@ class BaseInfo:
 def _no_gpu():
     import torch
     return not torch.cuda.is_available()
+
+
+@pytest.mark.parametrize("container,level", [("gzip", 6), ("gzip", 0), ("zlib", 0), ("plain", 0)])
+def test_ingp_containers_decode_on_host(hn, root, tmp_path, container, level):
+    """.ingp as the reference writes it (gzip member, dynamic Huffman or level 0 = stored blocks: save_snapshot(compress=false)),
+    a zlib stream, and an uncompressed .ingp (zstr::istream passes unknown magic through) all decode."""
+    from importlib import import_module
+    tbm = import_module(hn.__name__ + ".testbed")
+    lib = tbm._lib
+    h = C.c_void_p()
+    lib.hn_create(C.byref(h), 0)
+    path = str(tmp_path / "snap.ingp")
+    make_snapshot(root, hn.synthetic, BaseInfo, path, compress=container != "plain", level=level, container=container)
+    head = open(path, "rb").read(2)
+    assert head == (b"\x1f\x8b" if container == "gzip" else head)
+    rc = lib.hn_load_snapshot(h, os.fsencode(path))
+    info = tbm.NetworkInfo()
+    assert lib.hn_get_network_info(h, C.byref(info)) == 0, lib.hn_last_error(h)
+    assert (info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.n_params) == (8, 4, 19, BaseInfo.n_params)
+    if not _no_gpu():
+        assert rc == 0, lib.hn_last_error(h)
+    # a corrupted gzip trailer (CRC32) is rejected
+    if container == "gzip":
+        data = bytearray(open(path, "rb").read())
+        data[-6] ^= 0xFF
+        bad = tmp_path / "badcrc.ingp"
+        bad.write_bytes(bytes(data))
+        assert lib.hn_load_snapshot(h, os.fsencode(str(bad))) != 0 and b"CRC32" in lib.hn_last_error(h)
+    lib.hn_destroy(h)
 
 
 @pytest.mark.parametrize("ext,compress,ptype", [(".ingp", True, "__half"), (".msgpack", False, "float")])
@@ -66,8 +101,8 @@ def test_snapshot_decodes_on_host(hn, root, tmp_path, ext, compress, ptype):
         assert rc == 0, lib.hn_last_error(h)
     # corrupt / foreign files fail with a message
     bad = tmp_path / "bad.ingp"
-    bad.write_bytes(b"not a zlib stream at all")
-    assert lib.hn_load_snapshot(h, os.fsencode(str(bad))) != 0 and b"zlib" in lib.hn_last_error(h)
+    bad.write_bytes(b"not a snapshot at all")   # passes through the container detection as plain bytes, fails in the MessagePack reader
+    assert lib.hn_load_snapshot(h, os.fsencode(str(bad))) != 0 and len(lib.hn_last_error(h)) > 0
     trunc = tmp_path / "trunc.ingp"
     trunc.write_bytes(open(path, "rb").read()[:1000] if compress else zlib.compress(b"\x81\xa1a\x01"))
     assert lib.hn_load_snapshot(h, os.fsencode(str(trunc))) != 0
@@ -96,7 +131,8 @@ def test_snapshot_roundtrip_renders_identically(hn, root, tmp_path):
     # our writer -> python's zlib/msgpack read it back -> our reader renders the same again
     out = str(tmp_path / "resaved.ingp")
     b.save_snapshot(out)
-    back = msgpack.unpackb(zlib.decompress(open(out, "rb").read()), raw=False)
+    assert open(out, "rb").read(2) == b"\x1f\x8b"   # the gzip container the reference writes
+    back = msgpack.unpackb(gzip.decompress(open(out, "rb").read()), raw=False)
     assert back["snapshot"]["params_binary"] == blob.tobytes() and back["snapshot"]["version"] == 1
     assert back["encoding"]["n_levels"] == 8 and back["snapshot"]["camera"]["matrix"][2] == [0.0, 0.0, -1.0, 2.25]
     c = hn.Testbed()

@@ -198,10 +198,10 @@ def test_snapshot_with_optimizer_state_round_trip(hn, root):
     tb.reset_trainer(3)
     for _ in range(40):
         last = tb.train(1)
-    tb.set_option("snapshot_optimizer_state", 1.0)
     path = "/tmp/hn_opt_state.ingp"
-    tb.save_snapshot(path)
-    blob = msgpack.unpackb(zlib.decompress(open(path, "rb").read()), raw=False, strict_map_key=False)
+    tb.save_snapshot(path, include_optimizer_state=True)   # the pyngp signature (python_api.cu:437)
+    import gzip
+    blob = msgpack.unpackb(gzip.decompress(open(path, "rb").read()), raw=False, strict_map_key=False)
     snap = blob["snapshot"]
     n = int(tb.network_info().n_params)
     assert snap["training_step"] == 40 and abs(snap["loss"] - last) < 1e-6

@@ -417,6 +417,7 @@ def main():
     ap.add_argument("--eval-impl", type=int, default=1, help="network kernel: 1 = tcgen05/TMEM (default), 0 = warp MMA")
     ap.add_argument("--clip", action="store_true", help="stop marching at the mesh depth instead of the reference's per-pixel test")
     ap.add_argument("--crop-unit-cube", action="store_true", help="render box = the NeRF's unit cube instead of the Geometry-mode default (mesh box + 4)")
+    ap.add_argument("--opt", action="append", default=[], help="name=value library option (hn_set_option) for A/B runs, e.g. --opt eval_gather=2")
     ap.add_argument("--workload", default="config3", choices=["config2", "config3", "config4", "config5"],
                     help="BASELINE.json configs[1] NeRF-only 1080p / configs[2] hybrid 1080p (default, the headline) / configs[3] 4K hybrid + envmap light")
     args = ap.parse_args()
@@ -463,6 +464,9 @@ def main():
     tb.set_option("depth_merge_clip", 1.0 if args.clip else 0.0)
     tb.set_camera_cols(cam)
     tb.set_option("eval_impl", float(args.eval_impl))
+    for kv in args.opt:
+        k, v = kv.split("=")
+        tb.set_option(k, [float(x) for x in v.split(",")])
     tile_w, tile_h = 64, 32
     tb.set_tile_shard(rank, world, tile_w, tile_h)
 
@@ -632,7 +636,7 @@ def main():
             "vs_baseline": None, "dtype": "fp16 params/activations, fp32 accumulate", "data": "synthetic",
             "config": {"workload": workload,
                        "depth_merge": "clip" if args.clip else "reference per-pixel test", "l2": "512 MB flush between timed iterations",
-                       "tiles": f"{tile_w}x{tile_h} interleaved over {world} rank(s)", "samples_per_frame_all_ranks": samples_all},
+                       "tiles": f"{tile_w}x{tile_h} interleaved over {world} rank(s)", "samples_per_frame_all_ranks": samples_all, "options": args.opt},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": W * H / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 48, "d2h_bytes_per_step": W * H * 16},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "reference_cuda": reference_cuda,

@@ -226,7 +226,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
 		{"linear_colors", {&o.linear_colors, 1, true}}, {"render_mode", {&o.render_mode, 1, true}}, {"tonemap_curve", {&o.tonemap_curve, 1, true}},
-		{"clamp_output_color", {&o.clamp_output_color, 1, true}}, {"unmultiply_alpha", {&o.unmultiply_alpha, 1, true}}, {"eval_tex_gather", {&o.eval_tex_gather, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
+		{"clamp_output_color", {&o.clamp_output_color, 1, true}}, {"unmultiply_alpha", {&o.unmultiply_alpha, 1, true}}, {"eval_tex_gather", {&o.eval_tex_gather, 1, true}}, {"eval_gather", {&o.eval_gather, 1, true}}, {"eval_groups", {&o.eval_groups, 1, true}}, {"eval_texsplit", {&o.eval_texsplit, 1, true}}, {"eval_ray_sh", {&o.eval_ray_sh, 1, true}}, {"depth_scale", {&o.depth_scale, 1, false}}, {"dda_iter_cap", {&o.dda_iter_cap, 1, true}},
 		{"sun_dir", {o.sun_dir, 3, false}}, {"up_dir", {o.up_dir, 3, false}}, {"floor_enable", {&o.floor_enable, 1, true}},
 		{"brdf", {o.brdf, 13, false}}, {"compat_nearest_aabb_only", {&o.compat_nearest_aabb_only, 1, true}},
 		{"depth_merge_clip", {&o.depth_merge_clip, 1, true}}, {"render_nerf", {&o.render_nerf, 1, true}}, {"render_mesh", {&o.render_mesh, 1, true}},
@@ -337,6 +337,7 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
 	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;
 	a.render_mode = o.render_mode; a.depth_scale = o.depth_scale;
+	a.eval_gather = o.eval_gather; a.eval_groups = o.eval_groups; a.eval_texsplit = o.eval_texsplit;
 	a.rank = ctx->rank; a.world = ctx->world; a.tile_w = ctx->tile_w; a.tile_h = ctx->tile_h;
 	std::memcpy(a.mesh_aabb, o.mesh_aabb, 24);
 	std::memcpy(a.sun, o.sun_dir, 12); std::memcpy(a.up, o.up_dir, 12);
@@ -352,6 +353,7 @@ RaySoA ray_soa(hn_context* ctx) {
 	RaySoA r;
 	r.o_t = ctx->ray_o_t.p; r.d_mw = ctx->ray_d_mw.p; r.rgba = ctx->ray_rgba.p; r.depth = ctx->ray_depth.p;
 	r.pixel = ctx->ray_pixel.p; r.n_steps = ctx->ray_nsteps.p;
+	r.sh = nullptr; // set by the camera-ray path after ray_sh_kernel has run
 	return r;
 }
 
@@ -532,6 +534,12 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 		tm.start();
 		launch_raygen(a, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth, frame, s);
 		st.n_kernel_launches += 1;
+		if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) { // SH input of the colour MLP, once per ray instead of once per sample
+			ctx->ray_sh.ensure(2 * n_px);
+			launch_ray_sh(ctx->alive_a.p, cnt + CNT_ALIVE_A, (uint32_t)n_px, rays.d_mw, ctx->ray_sh.p, s);
+			rays.sh = ctx->ray_sh.p;
+			st.n_kernel_launches += 1;
+		}
 		tm.stop(st.ms_raygen);
 		st.n_rays_alive = run_passes(ctx, a, rays, frame, depth, false, s, tm);
 		st.n_samples = (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);

@@ -80,6 +80,10 @@ struct Options {
 	int profile = 0;
 	int fuse_composite = 0;                     // 1 = composite inside the tcgen05 network kernel (eval_impl 1 only; measured slower, kept as an option)
 	int composite_impl = 1;                     // 1 = one warp per ray + compact kernel, 0 = 32 rays per warp with in-kernel compaction
+	int eval_gather = 2;                        // tcgen05 kernel, base layout: 1 / 2 = mask-only gather with / without paired fetches on hashed levels, 0 = generic gather
+	int eval_texsplit = 0;                      // TEX / LSU split of the fine hash-grid levels in the tcgen05 kernel (see launch_eval_tc)
+	int eval_groups = 4;                        // tile groups per CTA of the tcgen05 kernel (4 or 3)
+	int eval_ray_sh = 1;                        // 1 = SH coefficients of a ray are computed once per frame (ray_sh_kernel), 0 = by every sample
 	int eval_tex_gather = 1;                    // 1 = tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe (F = 4), 0 = LSU only
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int snapshot_optimizer_state = 0;           // hn_save_snapshot: include the Trainer's optimizer state (save_snapshot(path, include_optimizer_state))
@@ -151,6 +155,7 @@ struct hn_context {
 	// occupancy
 	hn::DevBuf<uint8_t> bitfield;
 	bool has_bitfield = false;
+	hn::DevBuf<uint4> ray_sh;               // [ray][2]: fp16 SH coefficients of the ray direction (colour MLP input), per frame
 	hn::DevBuf<float> density_grid;         // device copy of the float grid [128^3 x grid_cascades] (Morton order), kept for the live updates
 	uint32_t grid_cascades = 0;
 	float density_grid_mean = 1.0f;         // m_nerf.density_grid_mean (mean of max(v, 0) over cascade 0); 1 = unknown (bitfield set directly)

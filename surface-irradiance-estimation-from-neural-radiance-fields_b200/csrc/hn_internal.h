@@ -63,6 +63,8 @@ struct FrameArgs {
 	int rgb_act, density_act, linear_colors, dda_iter_cap;
 	int depth_test, depth_clip;
 	int render_mode;       // ERenderMode of the NeRF pass (1 = Shade)
+	int eval_texsplit;
+	int eval_gather, eval_groups; // options eval_gather / eval_groups (gather variant, tile groups per CTA of the tcgen05 kernel)
 	float depth_scale;
 	int rank, world, tile_w, tile_h;
 	// mesh pass
@@ -92,6 +94,7 @@ struct RaySoA {
 	float* depth;
 	uint32_t* pixel;
 	uint32_t* n_steps;
+	uint4* sh;       // [ray][2] fp16 SH coefficients of the direction, filled once per frame for the first live list (may be nullptr)
 };
 
 // ---- BVH (4-wide, 128 B nodes) ----
@@ -140,6 +143,7 @@ void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 // The parameter buffer seen as 16-byte and 8-byte texels: the tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe.
 struct ParamTextures { cudaTextureObject_t tex16 = 0, tex8 = 0; const void* ptr = nullptr; };
+void launch_ray_sh(const uint32_t* list, const uint32_t* n_ptr, uint32_t n_max, const float4* d_mw, uint4* out, cudaStream_t s); // hn_network_tc.cu
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,
 	uint32_t max_chunks, uint2* out, int impl, float4* fused_frame, float* fused_depth, uint32_t* survive, uint32_t* counters, cudaStream_t s,

@@ -367,6 +367,9 @@ void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, c
 	a.samples = samples; a.sample_counts = sample_counts; a.alive_list = alive_list; a.d_mw = rays.d_mw;
 	a.dirs_override = dirs_override; a.n_chunks_ptr = n_chunks_ptr; a.n_chunks = max_chunks; a.out = out;
 	a.fused = (impl == 1 && fused_frame) ? 1 : 0;
+	a.unit_box = (a.train_lo[0] == 0.f && a.train_lo[1] == 0.f && a.train_lo[2] == 0.f && a.train_diag[0] == 1.f && a.train_diag[1] == 1.f && a.train_diag[2] == 1.f) ? 1 : 0;
+	a.ray_sh = (impl == 1 && alive_list && !dirs_override) ? rays.sh : nullptr;
+	a.gather_variant = fa.eval_gather; a.groups = fa.eval_groups; a.tex_split = fa.eval_texsplit;
 	a.tex16 = 0; a.tex8 = 0; a.tex_base = (uint32_t)(cfg.grid_offset / 4);
 	if (impl == 1 && tex && tex->tex16 && cfg.F == 4 && cfg.grid_offset % 8 == 0) { a.tex16 = tex->tex16; a.tex8 = tex->tex8; }
 	a.comp = make_comp_args(fa, rays, alive_list, samples, fused_frame, fused_depth, survive, counters);

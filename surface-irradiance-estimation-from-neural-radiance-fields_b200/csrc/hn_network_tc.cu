@@ -143,16 +143,47 @@ __device__ __forceinline__ void hidden_epilogue(uint32_t t_row, uint8_t* a_row) 
 	}
 }
 
+// SH input of the colour MLP for one ray direction: warp_direction (d+1)/2 as the reference stores it in the NerfCoordinate, back to
+// [-1,1] inside kernel_sh (spherical_harmonics.h:46-72), 16 coefficients rounded to fp16
+__device__ __forceinline__ void dir_sh(float dx, float dy, float dz, uint4& s0, uint4& s1) {
+	dx = __fmul_rn(__fadd_rn(dx, 1.0f), 0.5f) * 2.f - 1.f;
+	dy = __fmul_rn(__fadd_rn(dy, 1.0f), 0.5f) * 2.f - 1.f;
+	dz = __fmul_rn(__fadd_rn(dz, 1.0f), 0.5f) * 2.f - 1.f;
+	float sh[16];
+	sh4(dx, dy, dz, sh);
+	s0 = make_uint4(pack_h2(sh[0], sh[1]), pack_h2(sh[2], sh[3]), pack_h2(sh[4], sh[5]), pack_h2(sh[6], sh[7]));
+	s1 = make_uint4(pack_h2(sh[8], sh[9]), pack_h2(sh[10], sh[11]), pack_h2(sh[12], sh[13]), pack_h2(sh[14], sh[15]));
+}
+
+// The direction of a ray does not change over the passes of a frame: its SH coefficients are computed once, for the rays of the
+// first live list, instead of by every one of the 32 lanes of every chunk of every pass (~60 instructions per sample).
+__global__ void ray_sh_kernel(const uint32_t* __restrict__ list, const uint32_t* __restrict__ n_ptr, uint32_t n_max, const float4* __restrict__ d_mw, uint4* __restrict__ out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	const uint32_t n = n_ptr ? min(*n_ptr, n_max) : n_max;
+	if (i >= n) return;
+	const uint32_t ray = list ? list[i] : i;
+	const float4 d = __ldg(d_mw + ray);
+	uint4 s0, s1;
+	dir_sh(d.x, d.y, d.z, s0, s1);
+	out[2 * (size_t)ray] = s0;
+	out[2 * (size_t)ray + 1] = s1;
+}
+
 // G independent tile groups of 128 threads share one copy of the weights and one TMEM allocation (64 columns each); a
 // group synchronises on its own named barrier and its own mbarrier, so the groups of a CTA drift apart freely and one
 // group's gather overlaps the other groups' MMA rounds.
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;\n" :: "r"(g + 1), "r"(TILE) : "memory"); }
 
-template <int F, int G, bool FUSED, bool DONLY, uint32_t TEXMASK = 0, int NDENSE = -1>
-__global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
+// GV (gather variant): 0 = encode_sample (any layout), 1 = encode_sample_pow2 with paired 16-byte fetches on hashed levels,
+// 2 = encode_sample_pow2 with 8 independent 8-byte fetches on hashed levels. 1 and 2 need the base layout (launcher checks).
+template <int F, int G, bool FUSED, bool DONLY, uint32_t TEXMASK = 0, int NDENSE = -1, int GV = 0>
+__global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : (G == 3 ? 2 : 4)) eval_tc_kernel(const __grid_constant__ EvalArgs a) {
 	extern __shared__ __align__(1024) uint8_t smem[];
-	const int grp = threadIdx.x >> 7;                     // tile group of this thread
-	const int tid = threadIdx.x & (TILE - 1), lane = tid & 31, warp = tid >> 5; // within the group; warp == CTA warp index % 4
+	// warp index through a shuffle from lane 0: the compiler then knows it is warp-uniform and keeps everything derived from it
+	// (tile group, TMEM / shared-memory addresses, descriptors of the MMA issue path) in uniform registers
+	const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+	const int grp = warp_u >> 2;                          // tile group of this thread
+	const int lane = threadIdx.x & 31, warp = warp_u & 3, tid = warp * 32 + lane; // within the group; warp == CTA warp index % 4
 	uint8_t* a_s = smem + (size_t)grp * A_BYTES;          // this group's A operand, 8 planes x 128 rows x 16 B
 	uint8_t* wd_s = smem + (size_t)G * A_BYTES;           // density MLP weights
 	uint8_t* wr_s = wd_s + mlp_bytes(a.density_hidden);   // colour MLP weights
@@ -173,7 +204,8 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 	}
 	const uint32_t bar = smem_addr(bar_p);
 	if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); }
-	if (threadIdx.x < 32) tmem_alloc(smem_addr(tmem_p), TMEM_COLS * G);
+	constexpr uint32_t TCOLS = G == 3 ? 256u : TMEM_COLS * G; // tcgen05.alloc takes a power of two >= 32
+	if (threadIdx.x < 32) tmem_alloc(smem_addr(tmem_p), TCOLS);
 	fence_proxy_async();   // the staged weights are read by the async proxy (tcgen05.mma)
 	tc_fence_before();
 	__syncthreads();
@@ -199,15 +231,32 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 		const uint32_t chunk = tile * 4 + warp;
 		const uint32_t count = chunk < n_chunks ? (a.sample_counts ? a.sample_counts[chunk] : CHUNK) : 0u;
 		// ---- (b) gather: 32 features of this thread's sample -> A planes 0..3
-		{
+		if (GV != 0) {
+			if ((uint32_t)lane < count) {
+				const float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
+				float px = s.x, py = s.y, pz = s.z;
+				if (!a.unit_box) { // warp_position; (p - 0) / 1 is the identity, so the unit cube skips three IEEE divisions
+					px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
+					py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
+					pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
+				}
+				encode_sample_pow2<TEXMASK, NDENSE, GV == 1>(a.g, a.table, px, py, pz, a_row, A_PLANE, a.tex16, a.tex8, a.tex_base);
+			} else {
+				#pragma unroll
+				for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(a_row + c * A_PLANE) = make_uint4(0u, 0u, 0u, 0u);
+			}
+		} else {
 			uint32_t enc[16];
 			#pragma unroll
 			for (int k = 0; k < 16; ++k) enc[k] = 0u;
 			if ((uint32_t)lane < count) {
 				const float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
-				const float px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
-				const float py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
-				const float pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
+				float px = s.x, py = s.y, pz = s.z;
+				if (!a.unit_box) { // warp_position; (p - 0) / 1 is the identity, so the unit cube skips three IEEE divisions
+					px = __fdiv_rn(__fsub_rn(s.x, a.train_lo[0]), a.train_diag[0]);
+					py = __fdiv_rn(__fsub_rn(s.y, a.train_lo[1]), a.train_diag[1]);
+					pz = __fdiv_rn(__fsub_rn(s.z, a.train_lo[2]), a.train_diag[2]);
+				}
 				encode_sample<F, TEXMASK, NDENSE>(a.g, a.table, px, py, pz, enc, a.tex16, a.tex8, a.tex_base);
 			}
 			#pragma unroll
@@ -235,18 +284,19 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 		// ---- colour MLP input: [16 density outputs | 16 SH coefficients of the ray direction]
 		uint32_t sigma_bits;
 		{
-			float dx = 0.f, dy = 0.f, dz = 1.f;
-			if (chunk < n_chunks) {
-				if (a.dirs_override) { dx = a.dirs_override[3 * chunk]; dy = a.dirs_override[3 * chunk + 1]; dz = a.dirs_override[3 * chunk + 2]; }
-				else { const float4 d = __ldg(a.d_mw + a.alive_list[chunk]); dx = d.x; dy = d.y; dz = d.z; }
+			uint4 s0, s1;
+			if (a.ray_sh) { // computed once per ray and frame by ray_sh_kernel: one broadcast 32-byte read per warp
+				const uint32_t ray = chunk < n_chunks ? a.alive_list[chunk] : 0u;
+				s0 = __ldg(a.ray_sh + 2 * (size_t)ray);
+				s1 = __ldg(a.ray_sh + 2 * (size_t)ray + 1);
+			} else {
+				float dx = 0.f, dy = 0.f, dz = 1.f;
+				if (chunk < n_chunks) {
+					if (a.dirs_override) { dx = a.dirs_override[3 * chunk]; dy = a.dirs_override[3 * chunk + 1]; dz = a.dirs_override[3 * chunk + 2]; }
+					else { const float4 d = __ldg(a.d_mw + a.alive_list[chunk]); dx = d.x; dy = d.y; dz = d.z; }
+				}
+				dir_sh(dx, dy, dz, s0, s1);
 			}
-			dx = __fmul_rn(__fadd_rn(dx, 1.0f), 0.5f) * 2.f - 1.f;
-			dy = __fmul_rn(__fadd_rn(dy, 1.0f), 0.5f) * 2.f - 1.f;
-			dz = __fmul_rn(__fadd_rn(dz, 1.0f), 0.5f) * 2.f - 1.f;
-			float sh[16];
-			sh4(dx, dy, dz, sh);
-			const uint4 s0 = make_uint4(pack_h2(sh[0], sh[1]), pack_h2(sh[2], sh[3]), pack_h2(sh[4], sh[5]), pack_h2(sh[6], sh[7]));
-			const uint4 s1 = make_uint4(pack_h2(sh[8], sh[9]), pack_h2(sh[10], sh[11]), pack_h2(sh[12], sh[13]), pack_h2(sh[14], sh[15]));
 			HN_WAIT();
 			uint32_t v[16];
 			tmem_ld16(t_row, v);
@@ -293,36 +343,83 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : 4) eval_tc_kernel(const
 	#undef HN_WAIT
 	tc_fence_before();
 	__syncthreads();
-	if (threadIdx.x < 32) tmem_dealloc(*tmem_p, TMEM_COLS * G);
+	if (threadIdx.x < 32) tmem_dealloc(*tmem_p, TCOLS);
 }
 
 } // namespace tc
 
+namespace {
+// per-device launch state: SM count and "dynamic shared memory limit already raised for this kernel instance"
+int sm_count_of_current_device() {
+	static int counts[64] = {};
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev < 0 || dev >= 64) { int n = 0; cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); return n; }
+	if (!counts[dev]) cudaDeviceGetAttribute(&counts[dev], cudaDevAttrMultiProcessorCount, dev);
+	return counts[dev];
+}
+template <typename K>
+void launch_tc(K kernel, const EvalArgs& a, uint32_t blocks, int threads, size_t smem, cudaStream_t s) {
+	static size_t raised[64] = {}; // one instance of this template per kernel instance
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev < 0 || dev >= 64 || raised[dev] < smem) {
+		cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (dev >= 0 && dev < 64) raised[dev] = smem;
+	}
+	kernel<<<blocks, threads, smem, s>>>(a);
+}
+} // namespace
+
+void launch_ray_sh(const uint32_t* list, const uint32_t* n_ptr, uint32_t n_max, const float4* d_mw, uint4* out, cudaStream_t s) {
+	if (!n_max) return;
+	tc::ray_sh_kernel<<<(n_max + 255) / 256, 256, 0, s>>>(list, n_ptr, n_max, d_mw, out);
+}
+
 void launch_eval_tc(const EvalArgs& a, uint32_t F, uint32_t max_chunks, cudaStream_t s) {
 	if (!max_chunks) return;
 	constexpr int G = 4; // tile groups per CTA: 512 threads, 2 CTAs per SM = 8 tiles (32 warps) in flight per SM
-	const size_t smem = (size_t)G * tc::A_BYTES + tc::mlp_bytes(a.density_hidden) + tc::mlp_bytes(a.rgb_hidden) + 8 * G + 16;
-	static int sm_count = 0;
-	if (!sm_count) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev); }
-	uint32_t tiles = (max_chunks + 3) / 4;
-	uint32_t ctas = (tiles + G - 1) / G;
-	uint32_t persistent = (uint32_t)sm_count * 2u;
-	uint32_t blocks = ctas < persistent ? ctas : persistent;
-	#define HN_LAUNCH_TC(FF, FU, DO, TM, ND) do { \
-		cudaFuncSetAttribute(tc::eval_tc_kernel<FF, G, FU, DO, TM, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		tc::eval_tc_kernel<FF, G, FU, DO, TM, ND><<<blocks, tc::TILE * G, smem, s>>>(a); } while (0)
+	const int sm_count = sm_count_of_current_device();
+	const uint32_t tiles = (max_chunks + 3) / 4;
+	const uint32_t persistent = (uint32_t)sm_count * 2u;
+	auto smem_for = [&](int g) { return (size_t)g * tc::A_BYTES + tc::mlp_bytes(a.density_hidden) + tc::mlp_bytes(a.rgb_hidden) + 8 * g + 16; };
+	auto blocks_for = [&](int g) { const uint32_t ctas = (tiles + g - 1) / g; return ctas < persistent ? ctas : persistent; };
+	const size_t smem = smem_for(G);
+	const uint32_t blocks = blocks_for(G);
+	#define HN_LAUNCH_TC(FF, FU, DO, TM, ND, GVV) launch_tc(tc::eval_tc_kernel<FF, G, FU, DO, TM, ND, GVV>, a, blocks, tc::TILE * G, smem, s)
+	#define HN_LAUNCH_TC3(FF, FU, DO, TM, ND, GVV) launch_tc(tc::eval_tc_kernel<FF, 3, FU, DO, TM, ND, GVV>, a, blocks_for(3), tc::TILE * 3, smem_for(3), s)
 	// F = 4 with texture objects: the five fine levels (3..7, the hashed ones of the base config) are gathered through the TEX
 	// pipe, the three coarse ones through the LSU pipe. Measured on B200 (profiles/r01_tex_probe.txt): eval 7.03 -> 6.53 ms per
 	// 1080p frame, bit-identical output; every other split of (level, corner pair) between the two pipes was slower.
 	constexpr uint32_t TM = 0xFFFFF000u;
-	// level layout of configs/nerf/base.json (3 dense levels, then hashed power-of-two tables): level kind compiled in
-	bool base_layout = F == 4;
-	for (int l = 0; l < 8 && base_layout; ++l) base_layout = l < 3 ? (a.g.hashed[l] == 0) : (a.g.hashed[l] != 0 && a.g.mask[l] != 0);
-	if (F == 4 && a.tex16 && base_layout) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM, 3); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM, -1); else HN_LAUNCH_TC(4, false, false, TM, 3); }
-	else if (F == 4 && a.tex16) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM, -1); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM, -1); else HN_LAUNCH_TC(4, false, false, TM, -1); }
-	else if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true, 0u, -1); else if (a.fused) HN_LAUNCH_TC(4, true, false, 0u, -1); else HN_LAUNCH_TC(4, false, false, 0u, -1); }
-	else { if (a.density_only) HN_LAUNCH_TC(2, false, true, 0u, -1); else if (a.fused) HN_LAUNCH_TC(2, true, false, 0u, -1); else HN_LAUNCH_TC(2, false, false, 0u, -1); }
+	// level layout of configs/nerf/base.json: 3 dense levels with even resolutions, then hashed levels, EVERY table a power of two
+	// -> level kind compiled in and the mask-only gather (encode_sample_pow2)
+	bool base_layout = F == 4 && a.g.L == 8;
+	for (int l = 0; l < 8 && base_layout; ++l)
+		base_layout = a.g.mask[l] != 0 && (l < 3 ? (a.g.hashed[l] == 0 && (a.g.res[l] & 1u) == 0 && (uint64_t)a.g.res[l] * a.g.res[l] * a.g.res[l] == a.g.size[l]) : a.g.hashed[l] != 0);
+	const int gv = a.gather_variant;
+	if (F == 4 && a.tex16 && base_layout && !a.fused) {
+		// which (level, x-pair) fetches ride the TEX pipe (bit 4 l + p), the rest the LSU pipe: option eval_texsplit, picked from a sweep
+		// on B200 (profiles/r02_eval_variants.txt) - with 8 independent 8-byte fetches per hashed level the TEX input queue throttles
+		// when all five fine levels use it, so part of them goes back to LSU
+		constexpr uint32_t TM1 = 0xFFF00000u; // levels 5..7
+		constexpr uint32_t TM2 = 0x33333000u; // two of the four x-pairs of levels 3..7
+		constexpr uint32_t TM3 = 0xFF000000u; // levels 6..7
+		constexpr uint32_t TM4 = 0x0F0F0000u; // levels 4 and 6
+		if (a.density_only) { if (gv == 2) HN_LAUNCH_TC(4, false, true, TM, 3, 2); else if (gv == 0) HN_LAUNCH_TC(4, false, true, TM, 3, 0); else HN_LAUNCH_TC(4, false, true, TM, 3, 1); }
+		else if (a.groups == 3) { if (gv == 2) HN_LAUNCH_TC3(4, false, false, TM, 3, 2); else HN_LAUNCH_TC3(4, false, false, TM, 3, 1); }
+		else if (gv == 2 && a.tex_split == 1) HN_LAUNCH_TC(4, false, false, TM1, 3, 2);
+		else if (gv == 2 && a.tex_split == 2) HN_LAUNCH_TC(4, false, false, TM2, 3, 2);
+		else if (gv == 2 && a.tex_split == 3) HN_LAUNCH_TC(4, false, false, TM3, 3, 2);
+		else if (gv == 2 && a.tex_split == 4) HN_LAUNCH_TC(4, false, false, TM4, 3, 2);
+		else if (gv == 2 && a.tex_split == 5) HN_LAUNCH_TC(4, false, false, 0u, 3, 2);
+		else { if (gv == 2) HN_LAUNCH_TC(4, false, false, TM, 3, 2); else if (gv == 0) HN_LAUNCH_TC(4, false, false, TM, 3, 0); else HN_LAUNCH_TC(4, false, false, TM, 3, 1); }
+	}
+	else if (F == 4 && a.tex16) { if (a.density_only) HN_LAUNCH_TC(4, false, true, TM, -1, 0); else if (a.fused) HN_LAUNCH_TC(4, true, false, TM, -1, 0); else HN_LAUNCH_TC(4, false, false, TM, -1, 0); }
+	else if (F == 4) { if (a.density_only) HN_LAUNCH_TC(4, false, true, 0u, -1, 0); else if (a.fused) HN_LAUNCH_TC(4, true, false, 0u, -1, 0); else HN_LAUNCH_TC(4, false, false, 0u, -1, 0); }
+	else { if (a.density_only) HN_LAUNCH_TC(2, false, true, 0u, -1, 0); else if (a.fused) HN_LAUNCH_TC(2, true, false, 0u, -1, 0); else HN_LAUNCH_TC(2, false, false, 0u, -1, 0); }
 	#undef HN_LAUNCH_TC
+	#undef HN_LAUNCH_TC3
 }
 
 } // namespace hn

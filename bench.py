@@ -278,7 +278,10 @@ def train_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        with quiet_stdout():  # NCCL announces its version on stdout when the first communicator comes up
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
     hn = importlib.import_module("surface-irradiance-estimation-from-neural-radiance-fields_b200")
     tb = hn.Testbed(device=local)
     tb.reload_network_from_file(os.path.join(ROOT, "configs", "nerf", "base.json"))
@@ -417,6 +420,7 @@ def main():
     ap.add_argument("--eval-impl", type=int, default=1, help="network kernel: 1 = tcgen05/TMEM (default), 0 = warp MMA")
     ap.add_argument("--clip", action="store_true", help="stop marching at the mesh depth instead of the reference's per-pixel test")
     ap.add_argument("--crop-unit-cube", action="store_true", help="render box = the NeRF's unit cube instead of the Geometry-mode default (mesh box + 4)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="multi-GPU frame gather: peer-memory tile scatter (default) or the round-1 NCCL all-gather")
     ap.add_argument("--opt", action="append", default=[], help="name=value library option (hn_set_option) for A/B runs, e.g. --opt eval_gather=2")
     ap.add_argument("--workload", default="config3", choices=["config2", "config3", "config4", "config5"],
                     help="BASELINE.json configs[1] NeRF-only 1080p / configs[2] hybrid 1080p (default, the headline) / configs[3] 4K hybrid + envmap light")
@@ -440,7 +444,10 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        with quiet_stdout():  # NCCL announces its version on stdout when the first communicator comes up
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
 
     hn = importlib.import_module("surface-irradiance-estimation-from-neural-radiance-fields_b200")
     mesh, grid, cam = build_scene_inputs(hn)
@@ -470,26 +477,55 @@ def main():
     tile_w, tile_h = 64, 32
     tb.set_tile_shard(rank, world, tile_w, tile_h)
 
-    frame = torch.zeros(H, W, 4, device=dev)
-    depth = torch.zeros(H, W, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     flush = torch.empty(512 * 1024 * 1024 // 4, device=dev)  # 512 MB > 126 MB L2
-    max_tiles = tb.tile_count(W, H, 0, world)
-    packed = torch.zeros(max_tiles * tile_w * tile_h * 5, device=dev)
-    gathered = torch.zeros(world * packed.numel(), device=dev) if world > 1 else None
+    # ---- multi-GPU exchange: "peer" (default) = every rank copies its tiles straight into rank 0's frame / depth over NVLink peer
+    # memory (CUDA IPC mapping, hn_scatter_tiles: one launch) and one 4-byte all-reduce orders it; "nccl" = round-1 path
+    # (pack -> all_gather of all 41.5 MB to every rank -> one unpack launch per peer on rank 0), kept for A/B
+    exchange = args.exchange if world > 1 else "none"
+    remote_frame = remote_depth = 0
+    if exchange == "peer":
+        handles = [None, None]
+        if rank == 0:
+            fptr, fh = tb.shared_alloc(W * H * 16)
+            dptr, dh = tb.shared_alloc(W * H * 4)
+            handles = [fh, dh]
+            frame = torch.as_tensor(_DevArray(fptr, W * H * 4), device=dev).view(H, W, 4)
+            depth = torch.as_tensor(_DevArray(dptr, W * H), device=dev).view(H, W)
+        dist.broadcast_object_list(handles, src=0)
+        if rank != 0:
+            remote_frame, remote_depth = tb.shared_open(handles[0]), tb.shared_open(handles[1])
+            frame = torch.zeros(H, W, 4, device=dev)
+            depth = torch.zeros(H, W, device=dev)
+        token = torch.zeros(1, device=dev)
+    else:
+        frame = torch.zeros(H, W, 4, device=dev)
+        depth = torch.zeros(H, W, device=dev)
+    if exchange == "nccl":
+        max_tiles = tb.tile_count(W, H, 0, world)
+        packed = torch.zeros(max_tiles * tile_w * tile_h * 5, device=dev)
+        gathered = torch.zeros(world * packed.numel(), device=dev)
 
-    def step():
-        tb.render_frame(cam, cam, W, H, frame.data_ptr(), depth.data_ptr(), 0, stream)
-        launches = tb.frame_stats().n_kernel_launches
-        if world > 1:
+    def do_exchange():
+        n = 0
+        if exchange == "peer":
+            if rank != 0:
+                tb.scatter_tiles(W, H, rank, world, frame.data_ptr(), depth.data_ptr(), remote_frame, remote_depth, stream)
+                n += 1
+            dist.all_reduce(token)  # stream-ordered on every rank: when it completes on rank 0 every peer's tile stores have landed
+        elif exchange == "nccl":
             tb.pack_tiles(W, H, rank, world, frame.data_ptr(), depth.data_ptr(), packed.data_ptr(), stream)
             dist.all_gather_into_tensor(gathered, packed)
-            launches += 1
+            n += 1
             if rank == 0:
                 for r in range(1, world):
                     tb.unpack_tiles(W, H, r, world, gathered[r * packed.numel():].data_ptr(), frame.data_ptr(), depth.data_ptr(), stream)
-                    launches += 1
-        return launches
+                    n += 1
+        return n
+
+    def step():
+        tb.render_frame(cam, cam, W, H, frame.data_ptr(), depth.data_ptr(), 0, stream)
+        return tb.frame_stats().n_kernel_launches + do_exchange()
 
     def barrier():
         if world > 1:
@@ -540,6 +576,33 @@ def main():
         for k in prof:
             prof[k] += getattr(st, k) / n_prof
     tb.set_option("profile", 0.0)
+    # ---- where a multi-GPU step goes: this rank's kernels (CUDA events per kernel), the exchange alone (entered together), the rest
+    breakdown = None
+    if world > 1:
+        ex_ms = 0.0
+        for _ in range(5):
+            barrier()
+            e0.record(); do_exchange(); e1.record(); torch.cuda.synchronize()
+            ex_ms += e0.elapsed_time(e1) / 5
+        kern = sum(v for k, v in prof.items() if k.startswith("ms_"))
+        t = torch.tensor([kern, ex_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        kern, ex_ms = float(t[0].item()), float(t[1].item())
+        # the gathered frame on rank 0 must equal the frame one GPU renders alone (tiles are independent): checked, untimed
+        step(); barrier()
+        gather_err = None
+        if rank == 0:
+            gathered_frame = frame.clone()
+            tb.set_tile_shard(0, 1, tile_w, tile_h)
+            full = torch.zeros(H, W, 4, device=dev); full_d = torch.zeros(H, W, device=dev)
+            tb.render_frame(cam, cam, W, H, full.data_ptr(), full_d.data_ptr(), 0, stream)
+            torch.cuda.synchronize()
+            gather_err = float((gathered_frame - full).abs().max().item())
+            tb.set_tile_shard(rank, world, tile_w, tile_h)
+        barrier()
+        breakdown = {"gathered_frame_max_abs_vs_unsharded_render": gather_err, "kernel_ms_per_frame": kern, "exchange_ms": ex_ms, "host_gap_ms": max(0.0, ms - kern - ex_ms), "exchange": exchange,
+                     "note": "max over ranks; kernel = sum of the slowest rank's own kernels, exchange = tile scatter + ordering all-reduce timed alone after a barrier, "
+                             "host_gap = step time minus both (launch gaps, the per-pass counter read-backs, rank skew)"}
     hbm_peak, tf_peak, peak_kind = peaks()
     eval_s = prof["ms_eval"] * 1e-3
     ach_gbs = samples * ALGO_BYTES_PER_SAMPLE / eval_s / 1e9 if eval_s > 0 else 0.0
@@ -639,7 +702,7 @@ def main():
                        "tiles": f"{tile_w}x{tile_h} interleaved over {world} rank(s)", "samples_per_frame_all_ranks": samples_all, "options": args.opt},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": W * H / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms, "h2d_bytes_per_step": 48, "d2h_bytes_per_step": W * H * 16},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "reference_cuda": reference_cuda,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity, "reference_cuda": reference_cuda, "multi_gpu": breakdown,
         }
         if args.workload == "config4":
             line["env_light"] = {"hits_rank0": int(last_stats.n_env_hits), "light_rays_rank0": int(last_stats.n_light_rays),

@@ -157,6 +157,17 @@ int hn_tile_count(const hn_context* ctx, int width, int height, int rank, int wo
 int hn_pack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev, float* packed_dev, void* cuda_stream);
 int hn_unpack_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* packed_dev, float* frame_dev, float* depth_dev, void* cuda_stream);
 
+/* Frame gather over peer memory (NVLink / NVSwitch) without a collective, one process per GPU. The reference moves whole frames
+ * between its devices with cudaMemcpyPeerAsync (Testbed::sync_device / use_device, src/testbed.cu:5523-5610); here the root rank
+ * allocates frame + depth through hn_shared_alloc and publishes the 64-byte CUDA IPC handles, every other rank maps them once with
+ * hn_shared_open and per frame copies the tiles it owns straight into them (hn_scatter_tiles: plain peer stores, one launch), then
+ * all ranks pass one barrier. dev_ptr from hn_shared_alloc is an ordinary device pointer on the root (render into it directly). */
+int hn_shared_alloc(hn_context* ctx, size_t bytes, void** dev_ptr, unsigned char handle[64]);
+int hn_shared_open(hn_context* ctx, const unsigned char handle[64], void** dev_ptr);
+int hn_shared_release(hn_context* ctx, void* dev_ptr, int owner);
+int hn_scatter_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev,
+	float* frame_remote, float* depth_remote, void* cuda_stream);
+
 typedef struct {
 	uint64_t n_samples;        /* network samples evaluated in the last frame (ERenderMode::Cost sum) */
 	uint64_t n_samples_composited;
@@ -170,6 +181,9 @@ typedef struct {
 	uint64_t n_light_rays;     /* light rays traced through the BVH */
 	uint64_t n_light_rays_volume; /* of those, rays that entered the NeRF volume */
 	uint64_t n_light_samples;  /* density-network samples evaluated for them */
+	uint32_t n_bvh_stack_overflows; /* BVH children dropped because the traversal stack was full, since hn_build_scene: must be 0
+	                                   (the reference prints "WARNING TOO BIG", triangle_bvh.cuh:139-144) */
+	uint32_t pad_;
 } hn_frame_stats;
 int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out);
 

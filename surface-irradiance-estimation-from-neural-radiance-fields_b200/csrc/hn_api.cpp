@@ -269,7 +269,16 @@ int hn_set_tile_shard(hn_context* ctx, int rank, int world, int tile_w, int tile
 	ctx->rank = rank; ctx->world = world; ctx->tile_w = tile_w; ctx->tile_h = tile_h;
 	HN_CATCH(ctx)
 }
-int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out) { if (!ctx || !out) return 1; *out = ctx->stats; return 0; }
+int hn_get_frame_stats(const hn_context* ctx, hn_frame_stats* out) {
+	if (!ctx || !out) return 1;
+	*out = ctx->stats;
+	out->n_bvh_stack_overflows = 0;
+	if (ctx->d_stack_overflow.p) { // cumulative since hn_build_scene; read on demand (not on the frame path)
+		cudaSetDevice(ctx->device);
+		cudaMemcpy(&out->n_bvh_stack_overflows, ctx->d_stack_overflow.p, sizeof(uint32_t), cudaMemcpyDeviceToHost);
+	}
+	return 0;
+}
 
 } // extern "C"
 
@@ -679,6 +688,44 @@ int hn_unpack_tiles(hn_context* ctx, int width, int height, int rank, int world,
 	HN_TRY(ctx)
 	HN_CUDA(cudaSetDevice(ctx->device));
 	launch_pack_tiles(width, height, rank, world, ctx->tile_w, ctx->tile_h, (const float4*)frame_dev, depth_dev, (float*)packed_dev, true, (cudaStream_t)cuda_stream);
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+
+// Peer-memory frame gather (one process per GPU): the root rank allocates frame + depth through the library and exports them with
+// CUDA IPC, every other rank maps them once and then copies its tiles into them per frame (launch_scatter_tiles).
+int hn_shared_alloc(hn_context* ctx, size_t bytes, void** dev_ptr, unsigned char handle[64]) {
+	HN_TRY(ctx)
+	need(dev_ptr && handle && bytes > 0, "hn_shared_alloc: bad arguments");
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaMalloc(dev_ptr, bytes));
+	HN_CUDA(cudaMemset(*dev_ptr, 0, bytes));
+	cudaIpcMemHandle_t h;
+	HN_CUDA(cudaIpcGetMemHandle(&h, *dev_ptr));
+	std::memcpy(handle, &h, 64);
+	HN_CATCH(ctx)
+}
+int hn_shared_open(hn_context* ctx, const unsigned char handle[64], void** dev_ptr) {
+	HN_TRY(ctx)
+	need(dev_ptr && handle, "hn_shared_open: bad arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	cudaIpcMemHandle_t h;
+	std::memcpy(&h, handle, 64);
+	HN_CUDA(cudaIpcOpenMemHandle(dev_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+	HN_CATCH(ctx)
+}
+int hn_shared_release(hn_context* ctx, void* dev_ptr, int owner) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (dev_ptr) { if (owner) HN_CUDA(cudaFree(dev_ptr)); else HN_CUDA(cudaIpcCloseMemHandle(dev_ptr)); }
+	HN_CATCH(ctx)
+}
+int hn_scatter_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev, float* frame_remote, float* depth_remote, void* cuda_stream) {
+	HN_TRY(ctx)
+	need(frame_dev && depth_dev && frame_remote && depth_remote && world >= 1 && rank >= 0 && rank < world, "hn_scatter_tiles: bad arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	launch_scatter_tiles(width, height, rank, world, ctx->tile_w, ctx->tile_h, (const float4*)frame_dev, depth_dev, (float4*)frame_remote, depth_remote, (cudaStream_t)cuda_stream);
 	HN_CUDA(cudaGetLastError());
 	HN_CATCH(ctx)
 }

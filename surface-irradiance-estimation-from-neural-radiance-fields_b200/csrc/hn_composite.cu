@@ -217,6 +217,31 @@ __global__ void pack_tiles_kernel(int w, int h, int rank, int world, int tw, int
 	}
 }
 
+// Multi-GPU frame gather without a collective: a rank copies the tiles it owns from its local frame / depth straight into the ROOT
+// rank's buffers, mapped into this process through CUDA IPC - plain stores to peer memory over NVLink / NVSwitch, one CTA per
+// owned tile, 16-byte coalesced rows (1 KB of colour + 256 B of depth per 64-pixel tile row). Replaces pack -> all_gather (every
+// rank receiving all 41.5 MB) -> one unpack launch per peer.
+__global__ void __launch_bounds__(256) scatter_tiles_kernel(int w, int h, int rank, int world, int tw, int th, const float4* __restrict__ frame, const float* __restrict__ depth,
+	float4* __restrict__ frame_remote, float* __restrict__ depth_remote) {
+	const uint32_t tiles_x = (w + tw - 1) / tw, tiles_y = (h + th - 1) / th;
+	const uint32_t tile = blockIdx.x * world + rank;
+	if (tile >= tiles_x * tiles_y) return;
+	const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+	for (uint32_t k = threadIdx.x; k < (uint32_t)(tw * th); k += blockDim.x) {
+		const uint32_t x = tx * tw + k % tw, y = ty * th + k / tw;
+		if (x >= (uint32_t)w || y >= (uint32_t)h) continue;
+		const uint32_t pix = x + w * y;
+		frame_remote[pix] = frame[pix];
+		depth_remote[pix] = depth[pix];
+	}
+}
+void launch_scatter_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float4* frame_remote, float* depth_remote, cudaStream_t s) {
+	const uint32_t tiles = ((w + tw - 1) / tw) * ((h + th - 1) / th);
+	const uint32_t mine = (tiles + world - 1 - rank) / world;
+	if (!mine) return;
+	scatter_tiles_kernel<<<mine, 256, 0, s>>>(w, h, rank, world, tw, th, frame, depth, frame_remote, depth_remote);
+}
+
 CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_list, const float4* samples, float4* frame, float* depth_buffer,
 	uint32_t* survive, uint32_t* counters) {
 	CompArgs c;

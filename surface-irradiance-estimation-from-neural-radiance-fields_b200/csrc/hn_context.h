@@ -200,10 +200,12 @@ struct hn_context {
 	hn::DevBuf<uint8_t> scratch[8];
 
 	hn_frame_stats stats = {};
+	hn::DevBuf<uint32_t> d_stack_overflow; // see SceneDev::stack_overflow; zeroed when the scene is built, cumulative afterwards
 
 	hn::SceneDev scene_dev() const {
 		hn::SceneDev s;
 		s.nodes = d_nodes.p; s.tris = d_tris.p; s.meshes = d_meshes.p; s.n_meshes = (uint32_t)meshes.size();
+		s.stack_overflow = d_stack_overflow.p;
 		return s;
 	}
 };

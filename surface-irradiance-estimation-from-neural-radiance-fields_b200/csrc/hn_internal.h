@@ -116,6 +116,7 @@ struct SceneDev {
 	const float4* tris;   // 3 float4 per triangle: (a, orig_idx bits), (b, 0), (c, 0), leaf order
 	const MeshDev* meshes;
 	uint32_t n_meshes;
+	uint32_t* stack_overflow; // device counter: children that did not fit the traversal stack (a dropped child = a possibly missed hit)
 };
 
 // ---- launchers (defined in the .cu files) ----
@@ -143,6 +144,7 @@ void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 // The parameter buffer seen as 16-byte and 8-byte texels: the tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe.
 struct ParamTextures { cudaTextureObject_t tex16 = 0, tex8 = 0; const void* ptr = nullptr; };
+void launch_scatter_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float4* frame_remote, float* depth_remote, cudaStream_t s); // hn_composite.cu
 void launch_ray_sh(const uint32_t* list, const uint32_t* n_ptr, uint32_t n_max, const float4* d_mw, uint4* out, cudaStream_t s); // hn_network_tc.cu
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,
 	const uint32_t* sample_counts, const uint32_t* alive_list, RaySoA rays, const float* dirs_override, const uint32_t* n_chunks_ptr,

@@ -78,7 +78,10 @@ __device__ void traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& bes
 		cswap(dist[1], idx[1], dist[2], idx[2]);
 		#pragma unroll
 		for (int i = 0; i < 4; ++i) {
-			if (dist[i] >= 0.0f && sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+			if (dist[i] >= 0.0f) {
+				if (sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+				else if (sc.stack_overflow) atomicAdd(sc.stack_overflow, 1u); // never silent: surfaced as hn_frame_stats.n_bvh_stack_overflows (the reference prints "WARNING TOO BIG", triangle_bvh.cuh:139-144)
+			}
 		}
 	}
 }
@@ -200,7 +203,10 @@ __device__ void distance_walk(const SceneDev& sc, int mesh, V3 p, float& best_d2
 		cswap(dist[1], idx[1], dist[2], idx[2]);
 		#pragma unroll
 		for (int i = 0; i < 4; ++i) {
-			if (dist[i] >= 0.0f && sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+			if (dist[i] >= 0.0f) {
+				if (sp < STACK_DEPTH) { stack[sp * MESH_BLOCK] = idx[i]; ++sp; }
+				else if (sc.stack_overflow) atomicAdd(sc.stack_overflow, 1u); // never silent: surfaced as hn_frame_stats.n_bvh_stack_overflows (the reference prints "WARNING TOO BIG", triangle_bvh.cuh:139-144)
+			}
 		}
 	}
 }

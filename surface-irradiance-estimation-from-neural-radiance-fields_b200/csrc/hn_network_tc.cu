@@ -18,6 +18,9 @@
 //   the descriptor holds start = plane 2*kk, LBO (next K-chunk) = ROWS*16, SBO (next 8-row group) = 128.
 #include "hn_network.cuh"
 #include "hn_shade.cuh"
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace hn {
 namespace tc {
@@ -358,14 +361,21 @@ int sm_count_of_current_device() {
 	if (!counts[dev]) cudaDeviceGetAttribute(&counts[dev], cudaDevAttrMultiProcessorCount, dev);
 	return counts[dev];
 }
+// cudaFuncAttributeMaxDynamicSharedMemorySize is raised once per (kernel instance, device), not on every launch. K is the same
+// function-pointer TYPE for every instance, so the record is keyed by the pointer VALUE.
 template <typename K>
 void launch_tc(K kernel, const EvalArgs& a, uint32_t blocks, int threads, size_t smem, cudaStream_t s) {
-	static size_t raised[64] = {}; // one instance of this template per kernel instance
+	static std::mutex mu;
+	static std::map<std::pair<const void*, int>, size_t> raised;
 	int dev = 0;
 	cudaGetDevice(&dev);
-	if (dev < 0 || dev >= 64 || raised[dev] < smem) {
-		cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		if (dev >= 0 && dev < 64) raised[dev] = smem;
+	{
+		std::lock_guard<std::mutex> lock(mu);
+		size_t& r = raised[std::make_pair((const void*)kernel, dev)];
+		if (r < smem) {
+			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+			r = smem;
+		}
 	}
 	kernel<<<blocks, threads, smem, s>>>(a);
 }

@@ -252,6 +252,8 @@ void build_scene(hn_context* ctx) {
 	HN_CUDA(cudaMemcpy(ctx->d_nodes.p, nodes.data(), nodes.size() * sizeof(Node4), cudaMemcpyHostToDevice));
 	HN_CUDA(cudaMemcpy(ctx->d_tris.p, tris.data(), tris.size() * sizeof(float4), cudaMemcpyHostToDevice));
 	HN_CUDA(cudaMemcpy(ctx->d_meshes.p, md.data(), md.size() * sizeof(MeshDev), cudaMemcpyHostToDevice));
+	ctx->d_stack_overflow.ensure(1);
+	HN_CUDA(cudaMemset(ctx->d_stack_overflow.p, 0, sizeof(uint32_t)));
 	// load_scene :3183-3189: m_aabb = m_render_aabb = root box inflated by 4.0
 	if (!ctx->opt.mesh_aabb_user) {
 		for (int d = 0; d < 3; ++d) { ctx->opt.mesh_aabb[d] = lo[d] - 4.0f; ctx->opt.mesh_aabb[3 + d] = hi[d] + 4.0f; }

@@ -47,7 +47,7 @@ class FrameStats(C.Structure):
         ("n_kernel_launches", C.c_uint32), ("ms_mesh", C.c_float), ("ms_raygen", C.c_float), ("ms_march", C.c_float),
         ("ms_eval", C.c_float), ("ms_composite", C.c_float), ("ms_total", C.c_float),
         ("ms_envlight", C.c_float), ("n_env_hits", C.c_uint32), ("n_light_rays", C.c_uint64), ("n_light_rays_volume", C.c_uint64),
-        ("n_light_samples", C.c_uint64),
+        ("n_light_samples", C.c_uint64), ("n_bvh_stack_overflows", C.c_uint32), ("pad_", C.c_uint32),
     ]
 
 
@@ -69,7 +69,7 @@ EXPORTS = [
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
-    "hn_get_density_grid", "hn_load_training_data",
+    "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -86,6 +86,10 @@ _lib.hn_render_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
 _lib.hn_render_to_host.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
 _lib.hn_pack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_unpack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_shared_alloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
+_lib.hn_shared_open.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+_lib.hn_shared_release.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+_lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
@@ -346,6 +350,28 @@ class Testbed:
 
     def unpack_tiles(self, width, height, rank, world, packed_ptr, frame_ptr, depth_ptr, stream=0):
         self._check(_lib.hn_unpack_tiles(self._h, width, height, rank, world, C.c_void_p(packed_ptr), C.c_void_p(frame_ptr), C.c_void_p(depth_ptr), C.c_void_p(stream)))
+
+    # ---- frame gather over peer memory (one process per GPU)
+    def shared_alloc(self, n_bytes: int):
+        """-> (device pointer, 64-byte CUDA IPC handle) of a buffer other ranks of this node can map with shared_open"""
+        ptr = C.c_void_p(0)
+        handle = (C.c_ubyte * 64)()
+        self._check(_lib.hn_shared_alloc(self._h, n_bytes, C.byref(ptr), handle))
+        return int(ptr.value), bytes(handle)
+
+    def shared_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p(0)
+        buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+        self._check(_lib.hn_shared_open(self._h, buf, C.byref(ptr)))
+        return int(ptr.value)
+
+    def shared_release(self, ptr: int, owner: bool):
+        self._check(_lib.hn_shared_release(self._h, C.c_void_p(ptr), int(owner)))
+
+    def scatter_tiles(self, width, height, rank, world, frame_ptr, depth_ptr, frame_remote, depth_remote, stream=0):
+        """copy this rank's tiles of the local frame / depth into the root rank's buffers (mapped with shared_open)"""
+        self._check(_lib.hn_scatter_tiles(self._h, width, height, rank, world, C.c_void_p(frame_ptr), C.c_void_p(depth_ptr),
+                                          C.c_void_p(frame_remote), C.c_void_p(depth_remote), C.c_void_p(stream)))
 
     # ---- operator-level entry points (parity tests)
     def op_init_rays(self, cam0, cam1, width, height, spp_index=0, screen_center=(0.5, 0.5), relative_focal_length=None, rolling_shutter=(0, 0, 0, 1)):

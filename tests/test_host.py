@@ -158,3 +158,33 @@ def test_tile_arithmetic_matches_abi(hn, raw):
         assert total == tx * ty
         own = tiles.owner_map(w, hh, 64, 32, world)
         assert own.min() == 0 and own.max() == min(world, tx * ty) - 1
+
+
+REF_CONFIGS = "/root/reference/configs"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CONFIGS), reason="the reference tree is only mounted in the authoring container")
+def test_reference_own_config_files_load_unchanged(raw, root):
+    """The reference's OWN network config files (with their envmap / distortion_map sections and the `parent` chain of
+    configs/geometry/hashgrid.json) go through hn_load_network_config untouched and give the layout of this repo's trimmed copies."""
+    lib, h, _, tbm = raw
+    want = {}
+    for name in ("nerf/base.json", "geometry/base.json"):
+        assert lib.hn_load_network_config(h, os.fsencode(os.path.join(root, "configs", *name.split("/")))) == 0
+        info = tbm.NetworkInfo()
+        lib.hn_get_network_info(h, C.byref(info))
+        want[name] = (info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution, info.density_hidden_layers,
+                      info.rgb_hidden_layers, info.n_params, info.grid_param_offset, [info.level_offsets[i] for i in range(17)])
+    for ref_name, ours in (("nerf/base.json", "nerf/base.json"), ("nerf/hashgrid.json", "nerf/base.json"), ("geometry/base.json", "geometry/base.json"),
+                           ("geometry/hashgrid.json", "geometry/base.json")):
+        path = os.path.join(REF_CONFIGS, *ref_name.split("/"))
+        rc = lib.hn_load_network_config(h, os.fsencode(path))
+        assert rc == 0, (ref_name, lib.hn_last_error(h))
+        info = tbm.NetworkInfo()
+        lib.hn_get_network_info(h, C.byref(info))
+        got = (info.n_levels, info.n_features_per_level, info.log2_hashmap_size, info.base_resolution, info.density_hidden_layers,
+               info.rgb_hidden_layers, info.n_params, info.grid_param_offset, [info.level_offsets[i] for i in range(17)])
+        assert got == want[ours], ref_name
+    # configs of other encodings are refused with a message, not mis-read
+    assert lib.hn_load_network_config(h, os.fsencode(os.path.join(REF_CONFIGS, "nerf", "frequency.json"))) != 0
+    assert len(lib.hn_last_error(h)) > 0

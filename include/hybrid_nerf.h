@@ -77,6 +77,22 @@ int hn_get_scene_aabb(const hn_context* ctx, float out[6]);                     
  * the NeRF (the reference declares computeEnvmap / shade_from_nerf, testbed.h:394-407,709-743, without defining them).
  * rgba == NULL removes the map. */
 int hn_set_envmap(hn_context* ctx, const float* rgba, int width, int height);
+
+/* a-16 irradiance probes. What the reference ships of this path: the probe ray set-up NerfTracer::init_rays_from_center /
+ * init_rays_from_center_outward / init_rays_from_multiple_center (src/testbed_nerf.cu:1924-2019, kernels :1559-1773,
+ * cylindrical_to_dir_nerf :1546-1557, halton<2/3/5> random_val.cuh:338-350) and NerfTracer::trace_mesh (:2146-2262: t = 0, no start
+ * jitter, the 200-iteration DDA). What it only declares (Testbed::computeEnvmap{,Multiple,MultipleMain,Grid}, NerfTracer::shade_from_nerf,
+ * m_envmap_tex / gridSize: testbed.h:394-407,709-743,949-950) is defined HERE ("parity unpinned" for that part): the probe texture
+ * [n_phi][n_theta] of premultiplied linear RGBA (texel (i, j) = ray idx i + n_theta * j; mode 2 averages n_origin^2 jittered centres),
+ * its nearest-texel lookup by direction, and the mesh shading from it (options env_light_source = 1, env_light_sampling = 0 cosine /
+ * 1 uniform spherical cap towards the NeRF, warp_square_to_spherical_cap_uniform random_val.cuh:144-165).
+ * mode 0: rays from the centre of the NeRF box; 1: from `origin` looking in (frame around normalize(origin)); 2: Halton centres.
+ * The texture stays on the device as the light of the mesh pass; rgba_host (optional) receives a copy. */
+int hn_render_probe(hn_context* ctx, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], float* rgba_host);
+int hn_set_probe(hn_context* ctx, const float* rgba /* [n_phi][n_theta][4] or NULL */, uint32_t n_theta, uint32_t n_phi);
+/* the probe rays alone (origins, unit directions, alive = the DDA found an occupied cell), n = n_theta*n_phi (* n_origin^2 in mode 2) */
+int hn_op_probe_rays(hn_context* ctx, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3],
+	float* origins, float* dirs, uint8_t* alive);
 /* a-16 operator entry points (host in/out): envmap lookup for n unit directions -> out[n][4];
  * the K light directions of pixel `pixel_index` at sample index spp around unit normal n -> out[K][3];
  * NeRF transmittance along n rays (origin, unit dir) -> T[n], samples taken [n] (may be NULL). */

@@ -70,6 +70,11 @@ typedef struct {
 	// training: mean of max(density grid, 0) over cascade 0 (m_nerf.density_grid_mean); below NERF_MIN_OPTICAL_THICKNESS (0.01) the
 	// loss adds the unscaled L1 density regulariser (src/testbed_nerf.cu:1113,1161-1164). 0 here = "not given" = regulariser off.
 	float density_grid_mean; int32_t pad2;
+	// a-16 probe as light of the mesh pass (OUR definition): env_source 1 = probe texture [probe_n_phi][probe_n_theta][4] instead of the
+	// environment map (no NeRF transmittance along the light rays); env_sampling 0 = cosine hemisphere, 1 = uniform spherical cap around
+	// the direction to the bounding sphere of the NeRF box (train_aabb)
+	int32_t env_source, env_sampling, probe_n_theta, probe_n_phi;
+	const float* probe;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----
@@ -129,6 +134,15 @@ void orc_network(const orc_net_config* c, const uint16_t* params, const float* c
 // n_steps_out (optional, per pixel): number of samples composited.
 uint64_t orc_render_nerf(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield,
 	float* frame /*[h][w][4]*/, float* depth /*[h][w]*/, uint32_t* n_steps_out, int32_t depth_test);
+
+// ---- a-16 irradiance probes (orc_probe.inc): probe ray set-up as the reference ships it (mode 0 centre, 1 looking in from `origin`,
+// 2 Halton-jittered centres), NerfTracer::trace_mesh per ray, probe texture [n_phi][n_theta][4] (premultiplied linear RGBA)
+void orc_cylindrical_to_dir(const float p[2], float out[3]);
+float orc_halton(uint32_t base, uint64_t idx);
+uint32_t orc_probe_rays(int32_t mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float box[6], const float origin[3], float* o_out, float* d_out, uint32_t* texel_out);
+uint64_t orc_render_probe(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, int32_t mode,
+	uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], float* tex);
+void orc_read_probe(const float* tex, uint32_t n_theta, uint32_t n_phi, const float* dirs, uint32_t n, float* out);
 
 // ---- training batch (a-21): loss + parameter gradients, fp32 forward / analytic fp32 backward (orc_train.inc) ----
 // rays: origin, unit dir, start t (first sample search starts there); targets/backgrounds [n][3] in the training colour space.

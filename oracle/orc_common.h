@@ -89,6 +89,7 @@ struct Ray {
 struct BoundingBox {
 	vec3 min, max;
 	vec3 diag() const { return max - min; }
+	vec3 center() const { return 0.5f * (max + min); } // bounding_box.cuh:99-101
 	// bounding_box.cuh:313
 	bool contains(vec3 p) const {
 		return p.x >= min.x && p.x <= max.x && p.y >= min.y && p.y <= max.y && p.z >= min.z && p.z <= max.z;

@@ -18,6 +18,8 @@ Net* net_new(const orc_net_config& c, const uint16_t* params);
 void net_delete(Net* n);
 vec4 read_envmap(const float* env, int w, int h, vec3 dir);
 vec3 env_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, vec3 n);
+vec3 cap_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, vec3 axis, float cap_height, vec3 n, float& weight);
+vec4 read_probe(const float* tex, uint32_t n_theta, uint32_t n_phi, vec3 dir);
 float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8_t* bits, vec3 o, vec3 d, uint32_t* n_out);
 
 struct Triangle { vec3 a, b, c; };
@@ -288,20 +290,34 @@ static void render_mesh(const orc_scene& s, const orc_render_params& p, float* f
 			vec3 color = evaluate_shading(floor ? floorcol : basecolor * basecolor, ambientcolor * skycol, suncol,
 				floor ? 0.f : B[0], floor ? 0.f : B[1], floor ? 1.f : B[2], floor ? 0.5f : B[3], 0.f, floor ? 0.f : B[4], 0.f,
 				floor ? 0.f : B[5], B[6], sun, -normalize(dir), normal);
-			if (p.envmap && p.env_samples > 0 && touched && ti >= 0) {
+			const bool probe_light = p.env_source == 1 && p.probe && p.probe_n_theta > 0;
+			if ((p.envmap || probe_light) && p.env_samples > 0 && touched && ti >= 0) {
 				const uint32_t K = (uint32_t)p.env_samples;
 				vec3 nf = normal * -std::copysign(1.0f, dot(dir, normal));
 				vec3 org = pos + nf * 1e-3f;
 				vec3 albedo = floor ? floorcol : basecolor * basecolor;
 				vec3 sum = {0.f, 0.f, 0.f};
 				for (uint32_t k = 0; k < K; ++k) {
-					vec3 w = env_light_dir(idx, p.spp, K, k, nf);
+					vec3 w;
+					float weight = 1.0f;
+					bool cap = false;
+					if (probe_light && p.env_sampling == 1) {
+						BoundingBox train = bb_from(p.train_aabb);
+						vec3 to_c = train.center() - org;
+						float dist = length(to_c), radius = 0.5f * length(train.diag());
+						if (dist > radius) {
+							float cos_max = std::sqrt(std::fmax(0.0f, 1.0f - (radius / dist) * (radius / dist)));
+							w = cap_light_dir(idx, p.spp, K, k, to_c / dist, 1.0f - cos_max, nf, weight);
+							cap = true;
+						}
+					}
+					if (!cap) w = env_light_dir(idx, p.spp, K, k, nf);
 					int emi, eti; float et; bool etouched;
 					scene_nearest(s, false, org, w, false, emi, eti, et, etouched);
-					if (eti >= 0) continue;
-					vec4 L = read_envmap(p.envmap, p.env_w, p.env_h, w);
-					float T = (net && bits) ? nerf_transmittance(p, *net, bits, org, w, nullptr) : 1.0f;
-					sum = sum + vec3{L.x, L.y, L.z} * T;
+					if (eti >= 0 || !(weight > 0.0f)) continue;
+					vec4 L = probe_light ? read_probe(p.probe, (uint32_t)p.probe_n_theta, (uint32_t)p.probe_n_phi, w) : read_envmap(p.envmap, p.env_w, p.env_h, w);
+					float T = (!probe_light && net && bits) ? nerf_transmittance(p, *net, bits, org, w, nullptr) : 1.0f;
+					sum = sum + vec3{L.x, L.y, L.z} * (T * weight);
 				}
 				color = color + albedo * sum * (1.0f / (float)K);
 			}

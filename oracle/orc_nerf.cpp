@@ -853,6 +853,7 @@ float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8
 	return T;
 }
 
+#include "orc_probe.inc"
 #include "orc_train.inc"
 #include "orc_grid.inc"
 
@@ -1057,6 +1058,28 @@ uint64_t orc_render_nerf(const orc_render_params* p, const orc_net_config* c, co
 	float* frame, float* depth, uint32_t* n_steps_out, int32_t depth_test) {
 	Net net = make_net(*c, params);
 	return render_nerf(*p, net, bitfield, frame, depth, n_steps_out, depth_test != 0);
+}
+
+// ---- a-16 irradiance probes (orc_probe.inc)
+void orc_cylindrical_to_dir(const float p[2], float out[3]) { vec3 d = cylindrical_to_dir({p[0], p[1]}); out[0] = d.x; out[1] = d.y; out[2] = d.z; }
+float orc_halton(uint32_t base, uint64_t idx) { return halton(base, (size_t)idx); }
+uint32_t orc_probe_rays(int32_t mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float box[6], const float origin[3], float* o_out, float* d_out, uint32_t* texel_out) {
+	const uint32_t n = n_theta * n_phi * (mode == 2 ? n_origin * n_origin : 1u);
+	BoundingBox b = bb_from(box);
+	for (uint32_t r = 0; r < n; ++r) {
+		vec3 o, d; uint32_t t = 0;
+		probe_ray(mode, n_theta, n_phi, n_origin, b, {origin[0], origin[1], origin[2]}, r, o, d, t);
+		o_out[3 * r] = o.x; o_out[3 * r + 1] = o.y; o_out[3 * r + 2] = o.z; d_out[3 * r] = d.x; d_out[3 * r + 1] = d.y; d_out[3 * r + 2] = d.z; texel_out[r] = t;
+	}
+	return n;
+}
+uint64_t orc_render_probe(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, int32_t mode,
+	uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], float* tex) {
+	Net net = make_net(*c, params);
+	return render_probe(*p, net, bitfield, mode, n_theta, n_phi, n_origin, {origin[0], origin[1], origin[2]}, tex);
+}
+void orc_read_probe(const float* tex, uint32_t n_theta, uint32_t n_phi, const float* dirs, uint32_t n, float* out) {
+	for (uint32_t i = 0; i < n; ++i) { vec4 v = read_probe(tex, n_theta, n_phi, {dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]}); out[4 * i] = v.x; out[4 * i + 1] = v.y; out[4 * i + 2] = v.z; out[4 * i + 3] = v.w; }
 }
 
 } // extern "C"

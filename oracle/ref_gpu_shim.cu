@@ -362,6 +362,47 @@ int rg_mesh_triangles(void* h, uint32_t m, float* out, size_t n_tris) {
 uint32_t rg_mesh_count(void* h) { return (uint32_t)((Testbed*)h)->m_geometry.mesh_cpu.size(); }
 uint64_t rg_mesh_n_triangles(void* h, uint32_t m) { return ((Testbed*)h)->m_geometry.mesh_cpu[m].sdf.triangles_cpu.size(); }
 
+// a-16 irradiance-probe path as far as the reference ships it: NerfTracer::init_rays_from_center / _outward / _multiple_center
+// (src/testbed_nerf.cu:1924-2019, kernels :1559-1773) followed by NerfTracer::trace_mesh (:2146-2262) on the loaded NeRF.
+// Outputs per initialised ray r: origin[3], dir[3], texel idx (payload.idx); per HIT ray (compacted by the tracer, n_hit returned):
+// its texel idx and composited rgba (premultiplied, network colour space - the reference applies no further step).
+int rg_probe(void* h, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3],
+	float* ray_o, float* ray_d, uint32_t* ray_idx, uint32_t* n_hit_out, uint32_t* hit_idx, float* hit_rgba) {
+	RG_TRY
+	Testbed* tb = (Testbed*)h;
+	auto net = nerf_net(tb);
+	if (!net) throw std::runtime_error("no NeRF network");
+	ngp::Nerf& nerf = nerf_state(tb);
+	cudaStream_t s = tb->m_stream.get();
+	const BoundingBox nerf_box = tb->m_testbed_mode == ETestbedMode::Geometry ? tb->m_geometry.nerfBoundingBox : tb->m_aabb;
+	Testbed::NerfTracer tracer;
+	if (mode == 0) tracer.init_rays_from_center(n_theta, n_phi, net->padded_output_width(), net->n_extra_dims(), nerf_box, mat3::identity(), s);
+	else if (mode == 1) tracer.init_rays_from_center_outward(n_theta, n_phi, net->padded_output_width(), net->n_extra_dims(), nerf_box, mat3::identity(), vec3(origin[0], origin[1], origin[2]), s);
+	else tracer.init_rays_from_multiple_center(n_theta, n_phi, n_origin, net->padded_output_width(), net->n_extra_dims(), nerf_box, mat3::identity(), s);
+	const uint32_t n = tracer.n_rays_initialized();
+	std::vector<NerfPayload> pl(n);
+	CUDA_CHECK_THROW(cudaMemcpyAsync(pl.data(), tracer.rays_init().payload, n * sizeof(NerfPayload), cudaMemcpyDeviceToHost, s));
+	CUDA_CHECK_THROW(cudaStreamSynchronize(s));
+	for (uint32_t r = 0; r < n; ++r) {
+		for (int k = 0; k < 3; ++k) { ray_o[3 * r + k] = pl[r].origin[k]; ray_d[3 * r + k] = pl[r].dir[k]; }
+		ray_idx[r] = pl[r].idx;
+	}
+	const uint8_t* bits = nerf.density_grid_bitfield.data();
+	const float depth_scale = 1.0f / nerf.training.dataset.scale;
+	const uint32_t n_hit = tracer.trace_mesh(net, tb->m_render_aabb, tb->m_render_aabb_to_local, nerf_box, vec2(1.0f), nerf.cone_angle_constant, bits, ERenderMode::Shade,
+		tb->m_camera, depth_scale, tb->m_visualized_layer, -1, nerf.rgb_activation, nerf.density_activation, nerf.show_accel, nerf.max_cascade,
+		nerf.render_min_transmittance, nerf.glow_y_cutoff, nerf.glow_mode, nerf.get_rendering_extra_dims(s), s);
+	*n_hit_out = n_hit;
+	if (n_hit) {
+		std::vector<NerfPayload> hp(n_hit);
+		CUDA_CHECK_THROW(cudaMemcpyAsync(hp.data(), tracer.rays_hit().payload, n_hit * sizeof(NerfPayload), cudaMemcpyDeviceToHost, s));
+		CUDA_CHECK_THROW(cudaMemcpyAsync(hit_rgba, tracer.rays_hit().rgba, n_hit * sizeof(vec4), cudaMemcpyDeviceToHost, s));
+		CUDA_CHECK_THROW(cudaStreamSynchronize(s));
+		for (uint32_t r = 0; r < n_hit; ++r) hit_idx[r] = hp[r].idx;
+	}
+	RG_CATCH
+}
+
 // One training step through the reference's Testbed::train (Nerf mode with a loaded dataset).
 int rg_train(void* h, uint32_t batch_size, int n_steps, float* loss_out) {
 	RG_TRY

@@ -236,7 +236,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
-		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -355,6 +355,11 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	a.compat_nearest_aabb_only = o.compat_nearest_aabb_only;
 	a.envmap = ctx->envmap.p; a.env_w = ctx->env_w; a.env_h = ctx->env_h; // nullptr = no map
 	a.env_samples = ctx->envmap.p ? std::max(o.env_light_samples, 0) : 0;
+	a.probe = nullptr; a.probe_n_theta = a.probe_n_phi = 0; a.env_source = 0; a.env_sampling = o.env_light_sampling;
+	if (o.env_light_source == 1 && ctx->probe_tex.p && ctx->probe_n_theta > 0) { // the NeRF's probe lights the meshes
+		a.probe = ctx->probe_tex.p; a.probe_n_theta = ctx->probe_n_theta; a.probe_n_phi = ctx->probe_n_phi; a.env_source = 1;
+		a.env_samples = std::max(o.env_light_samples, 0);
+	}
 	return a;
 }
 
@@ -472,7 +477,8 @@ void env_light_pass(hn_context* ctx, const FrameArgs& a_in, float4* frame, float
 	st.n_env_hits = n_hits;
 	if (!n_hits) return;
 	const uint32_t K = (uint32_t)a.env_samples;
-	const bool volume = ctx->opt.render_nerf && ctx->has_net && ctx->has_params && ctx->has_bitfield;
+	// probe light: the texture already holds what the NeRF emits towards the scene, no transmittance march along the light rays
+	const bool volume = a.env_source != 1 && ctx->opt.render_nerf && ctx->has_net && ctx->has_params && ctx->has_bitfield;
 	const uint32_t per_batch = std::max<uint32_t>(1u, (uint32_t)std::max(ctx->opt.env_light_batch, 1) / K);
 	uint32_t* cnt = ctx->counters.p;
 	for (uint32_t first = 0; first < n_hits; first += per_batch) {
@@ -508,7 +514,7 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 	const bool do_mesh = ctx->opt.render_mesh && !ctx->meshes.empty();
 	if (do_mesh) {
 		need(ctx->scene_built, "scene has meshes but hn_build_scene was not called");
-		const bool env_light = a.envmap && a.env_samples > 0;
+		const bool env_light = (a.envmap || a.env_source == 1) && a.env_samples > 0;
 		EnvHits hits = {nullptr, nullptr, nullptr, nullptr};
 		if (env_light) {
 			ctx->hit_pos_pix.ensure(n_px); ctx->hit_nrm.ensure(n_px); ctx->hit_albedo.ensure(n_px); ctx->hit_count.ensure(1);
@@ -769,6 +775,86 @@ int hn_op_march_all(hn_context* ctx, uint32_t n, const float* origins, const flo
 	HN_CUDA(cudaMemcpyAsync(counts, d_c, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	if (d_s) HN_CUDA(cudaMemcpyAsync(samples, d_s, (size_t)n * max_per_ray * 16, cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	HN_CATCH(ctx)
+}
+
+// a-16 irradiance probe: rays from the NeRF's centre (mode 0), from `origin` looking in (mode 1) or from n_origin^2 Halton-jittered
+// centres (mode 2) on the n_theta x n_phi lattice of cylindrical_to_dir_nerf, traced through the NeRF like NerfTracer::trace_mesh
+// (t = 0, no jitter, 200-iteration DDA) by the SAME pass loop as camera rays (march, tcgen05 network, composite), reduced into the
+// probe texture. Kept on the device as the light of the mesh pass (option env_light_source = 1); optionally copied to the host.
+int hn_render_probe(hn_context* ctx, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], float* rgba_host) {
+	HN_TRY(ctx)
+	need(mode >= 0 && mode <= 2 && n_theta > 0 && n_phi > 0 && (mode != 2 || n_origin > 0), "hn_render_probe: bad arguments");
+	need(mode != 1 || origin != nullptr, "hn_render_probe: mode 1 needs an origin");
+	need(ctx->has_net && ctx->has_params && ctx->has_bitfield, "hn_render_probe: network, parameters and occupancy grid must be set");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const size_t n_rays = (size_t)n_theta * n_phi * (mode == 2 ? (size_t)n_origin * n_origin : 1u);
+	need(n_rays < (1u << 30), "hn_render_probe: too many rays");
+	cudaStream_t s = ctx->stream;
+	const float rs[4] = {0.f, 0.f, 0.f, 1.f};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, (int)n_rays, 1);
+	a.depth_test = 0; a.depth_clip = 0; a.dda_iter_cap = 200; a.render_mode = 1; a.crop_rotated = 0;
+	a.rank = 0; a.world = 1;
+	ctx->probe_rays.ensure(n_rays); ctx->probe_depth.ensure(n_rays); ctx->probe_tex.ensure((size_t)n_theta * n_phi);
+	HN_CUDA(cudaMemsetAsync(ctx->probe_rays.p, 0, n_rays * sizeof(float4), s));
+	HN_CUDA(cudaMemsetAsync(ctx->probe_depth.p, 0, n_rays * sizeof(float), s));
+	ensure_rays(ctx, n_rays);
+	uint32_t* cnt = ctx->counters.p;
+	HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
+	RaySoA rays = ray_soa(ctx);
+	const float zero3[3] = {0.f, 0.f, 0.f};
+	launch_probe_raygen(a, ctx->bitfield.p, mode, n_theta, n_phi, n_origin, origin ? origin : zero3, rays, ctx->alive_a.p, cnt, s);
+	if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) {
+		ctx->ray_sh.ensure(2 * n_rays);
+		launch_ray_sh(ctx->alive_a.p, cnt + CNT_ALIVE_A, (uint32_t)n_rays, rays.d_mw, ctx->ray_sh.p, s);
+		rays.sh = ctx->ray_sh.p;
+	}
+	hn_frame_stats keep = ctx->stats;
+	Timer tm(false, s);
+	run_passes(ctx, a, rays, ctx->probe_rays.p, ctx->probe_depth.p, false, s, tm);
+	ctx->stats = keep;
+	launch_probe_reduce(ctx->probe_rays.p, mode, n_theta, n_phi, n_origin, ctx->probe_tex.p, s);
+	HN_CUDA(cudaGetLastError());
+	ctx->probe_n_theta = (int)n_theta; ctx->probe_n_phi = (int)n_phi;
+	if (rgba_host) HN_CUDA(cudaMemcpyAsync(rgba_host, ctx->probe_tex.p, (size_t)n_theta * n_phi * sizeof(float4), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	HN_CATCH(ctx)
+}
+// upload a probe texture computed elsewhere ([n_phi][n_theta][4]); nullptr removes it
+int hn_set_probe(hn_context* ctx, const float* rgba, uint32_t n_theta, uint32_t n_phi) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (!rgba) { ctx->probe_tex.release(); ctx->probe_n_theta = ctx->probe_n_phi = 0; return 0; }
+	need(n_theta > 0 && n_phi > 0, "hn_set_probe: empty texture");
+	ctx->probe_tex.ensure((size_t)n_theta * n_phi);
+	HN_CUDA(cudaMemcpy(ctx->probe_tex.p, rgba, (size_t)n_theta * n_phi * sizeof(float4), cudaMemcpyHostToDevice));
+	ctx->probe_n_theta = (int)n_theta; ctx->probe_n_phi = (int)n_phi;
+	HN_CATCH(ctx)
+}
+int hn_op_probe_rays(hn_context* ctx, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], float* origins, float* dirs, uint8_t* alive) {
+	HN_TRY(ctx)
+	need(mode >= 0 && mode <= 2 && n_theta > 0 && n_phi > 0 && ctx->has_bitfield, "hn_op_probe_rays: bad arguments / no occupancy grid");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	const size_t n_rays = (size_t)n_theta * n_phi * (mode == 2 ? (size_t)n_origin * n_origin : 1u);
+	cudaStream_t s = ctx->stream;
+	const float rs[4] = {0.f, 0.f, 0.f, 1.f};
+	FrameArgs a = make_args(ctx, ctx->camera, ctx->camera, ctx->opt.screen_center, ctx->opt.relative_focal_length, rs, 0, (int)n_rays, 1);
+	a.crop_rotated = 0;
+	ensure_rays(ctx, n_rays);
+	uint32_t* cnt = ctx->counters.p;
+	HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
+	RaySoA rays = ray_soa(ctx);
+	const float zero3[3] = {0.f, 0.f, 0.f};
+	launch_probe_raygen(a, ctx->bitfield.p, mode, n_theta, n_phi, n_origin, origin ? origin : zero3, rays, ctx->alive_a.p, cnt, s);
+	std::vector<float4> ot(n_rays), dm(n_rays);
+	HN_CUDA(cudaMemcpyAsync(ot.data(), rays.o_t, n_rays * sizeof(float4), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaMemcpyAsync(dm.data(), rays.d_mw, n_rays * sizeof(float4), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	for (size_t r = 0; r < n_rays; ++r) {
+		origins[3 * r] = ot[r].x; origins[3 * r + 1] = ot[r].y; origins[3 * r + 2] = ot[r].z;
+		dirs[3 * r] = dm[r].x; dirs[3 * r + 1] = dm[r].y; dirs[3 * r + 2] = dm[r].z;
+		if (alive) alive[r] = ot[r].w < MAX_DEPTH_F ? 1 : 0;
+	}
 	HN_CATCH(ctx)
 }
 

@@ -87,6 +87,8 @@ struct Options {
 	int eval_tex_gather = 1;                    // 1 = tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe (F = 4), 0 = LSU only
 	int eval_impl = 1;                          // 1 = tcgen05/TMEM network kernel (hn_network_tc.cu), 0 = warp-MMA kernel (hn_network.cu)
 	int snapshot_optimizer_state = 0;           // hn_save_snapshot: include the Trainer's optimizer state (save_snapshot(path, include_optimizer_state))
+	int env_light_source = 0;                   // light of the mesh pass: 0 = environment map (hn_set_envmap), 1 = the NeRF's irradiance probe (hn_render_probe)
+	int env_light_sampling = 0;                 // 0 = cosine hemisphere around the normal, 1 = uniform spherical cap around the direction to the NeRF (probe source)
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
 	int env_light_batch = 8 << 20;              // light rays in flight per batch (bounds the workspace)
 	int mesh_aabb_user = 0;
@@ -155,6 +157,9 @@ struct hn_context {
 	// occupancy
 	hn::DevBuf<uint8_t> bitfield;
 	bool has_bitfield = false;
+	hn::DevBuf<float4> probe_tex, probe_rays;   // a-16 probe: radiance texture [n_phi][n_theta] and the per-ray colours it was reduced from
+	hn::DevBuf<float> probe_depth;
+	int probe_n_theta = 0, probe_n_phi = 0;
 	hn::DevBuf<uint4> ray_sh;               // [ray][2]: fp16 SH coefficients of the ray direction (colour MLP input), per frame
 	hn::DevBuf<float> density_grid;         // device copy of the float grid [128^3 x grid_cascades] (Morton order), kept for the live updates
 	uint32_t grid_cascades = 0;

@@ -272,6 +272,49 @@ __device__ __forceinline__ V3 env_light_dir(uint32_t idx, uint32_t spp, uint32_t
 	const float2 u = hn_ld_random_val_2d(k + K * spp, idx * 786433u + 0x9E3779B9u);
 	return normalize3(local_frame_apply(n, cosine_hemisphere(u)));
 }
+// ---- a-16 irradiance probes: the pieces the reference ships (src/testbed_nerf.cu:1546-1557, random_val.cuh:130-160,338-350) ----
+__device__ __forceinline__ V3 cylindrical_to_dir(float px, float py) {
+	const float cos_theta = -2.0f * px + 1.0f;
+	const float phi = 2.0f * HN_PI_F * (py - 0.5f);
+	const float sin_theta = sqrtf(fmaxf(1.0f - cos_theta * cos_theta, 0.0f));
+	float sin_phi, cos_phi;
+	sincosf(phi, &sin_phi, &cos_phi);
+	return mk(sin_theta * cos_phi, sin_theta * sin_phi, cos_theta);
+}
+__device__ __forceinline__ float halton(uint32_t base, uint32_t idx) {
+	float f = 1, result = 0;
+	while (idx > 0) {
+		f /= (float)base;
+		result += f * (float)(idx % base);
+		idx /= base;
+	}
+	return result;
+}
+__device__ __forceinline__ V3 spherical_cap_uniform(float2 u, float cap_height) {
+	const float z = (float)((double)(1.0f - cap_height) * (1.0 - (double)u.x) + (double)u.x); // the reference mixes a double literal in (random_val.cuh:147)
+	const float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+	const float phi = 2.0f * HN_PI_F * u.y;
+	return mk(r * cosf(phi), r * sinf(phi), z);
+}
+// Probe texture (OUR definition; the reference only declares m_envmap_tex / computeEnvmap*): texel (i, j) holds the radiance of probe
+// ray idx = i + n_theta * j; lookup by direction = the inverse of cylindrical_to_dir, nearest texel, phi wraps, theta clamps.
+__device__ __forceinline__ float4 read_probe(const float4* __restrict__ tex, int n_theta, int n_phi, V3 dir) {
+	const float px = (1.0f - fminf(fmaxf(dir.z, -1.0f), 1.0f)) * 0.5f;
+	const float py = atan2f(dir.y, dir.x) / (2.0f * HN_PI_F) + 0.5f;
+	int i = (int)floorf(px * (float)n_theta), j = (int)floorf(py * (float)n_phi);
+	i = max(0, min(i, n_theta - 1));
+	j = ((j % n_phi) + n_phi) % n_phi;
+	return __ldg(tex + i + (size_t)n_theta * j);
+}
+// Light direction k of K of pixel idx towards a spherical cap (axis, cap_height) and its estimator weight for a Lambertian
+// surface with normal n: cos / (pi pdf) with pdf = 1 / (2 pi cap_height) (warp_square_to_spherical_cap_uniform_invpdf)
+__device__ __forceinline__ V3 cap_light_dir(uint32_t idx, uint32_t spp, uint32_t K, uint32_t k, V3 axis, float cap_height, V3 n, float& weight) {
+	const float2 u = hn_ld_random_val_2d(k + K * spp, idx * 786433u + 0x9E3779B9u);
+	const V3 w = normalize3(local_frame_apply(axis, spherical_cap_uniform(u, cap_height)));
+	weight = 2.0f * cap_height * fmaxf(0.0f, dot3(n, w));
+	return w;
+}
+
 __device__ __forceinline__ float4 read_envmap(const float4* __restrict__ env, int w, int h, V3 dir) {
 	const float2 cyl = dir_to_spherical_unorm(mk(dir.z, -dir.x, dir.y));
 	const float fx = cyl.y * (float)(w - 1), fy = cyl.x * (float)(h - 1);

@@ -76,6 +76,10 @@ struct FrameArgs {
 	// a-16 environment map (device, lat-long float4 [env_h][env_w]); env_samples = K light directions per mesh hit
 	const float4* envmap;
 	int env_w, env_h, env_samples;
+	// a-16 probe: lat-long radiance texture of the NeRF (hn_render_probe) as light source of the mesh pass when env_source == 1;
+	// env_sampling 0 = cosine hemisphere, 1 = uniform spherical cap around the direction to the NeRF's bounding sphere
+	const float4* probe;
+	int probe_n_theta, probe_n_phi, env_source, env_sampling;
 };
 
 // mesh hits that gather environment light: filled by the mesh pass (one entry per shaded triangle hit, warp-aggregated append)
@@ -144,6 +148,9 @@ void launch_normals(const NetCfg& cfg, const GridLevels& g, const __half* params
 void launch_encode(const GridLevels& g, uint32_t F, const __half* table, const float* positions, uint32_t n, __half* out, cudaStream_t s);
 // The parameter buffer seen as 16-byte and 8-byte texels: the tcgen05 kernel gathers the fine hash-grid levels through the TEX pipe.
 struct ParamTextures { cudaTextureObject_t tex16 = 0, tex8 = 0; const void* ptr = nullptr; };
+void launch_probe_raygen(const FrameArgs& a, const uint8_t* bits, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], RaySoA rays,
+	uint32_t* alive_list, uint32_t* counters, cudaStream_t s);                                                   // hn_march.cu
+void launch_probe_reduce(const float4* ray_rgba, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, float4* tex, cudaStream_t s); // hn_march.cu
 void launch_scatter_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float4* frame_remote, float* depth_remote, cudaStream_t s); // hn_composite.cu
 void launch_ray_sh(const uint32_t* list, const uint32_t* n_ptr, uint32_t n_max, const float4* d_mw, uint4* out, cudaStream_t s); // hn_network_tc.cu
 void launch_eval(const NetCfg& cfg, const GridLevels& g, const __half* params, const FrameArgs& a, const float4* samples,

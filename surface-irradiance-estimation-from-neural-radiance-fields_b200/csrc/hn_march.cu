@@ -317,6 +317,77 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 	}
 }
 
+// a-16 irradiance probes: ray set-up of init_rays_from_center{,_outward,_multiple_center}_with_payload_kernel_nerf
+// (src/testbed_nerf.cu:1559-1773) - directions on the (cos theta, phi) lattice of cylindrical_to_dir_nerf, origin = centre of the NeRF
+// box / a given point looking in / Halton<2,3,5>-jittered centres - followed by the start of NerfTracer::trace_mesh (:2146-2262):
+// t = 0, no start jitter, rays alive when the 200-iteration DDA finds an occupied cell. Ray slot r keeps its own colour; the texel
+// it belongs to is recomputed by probe_reduce_kernel.
+__device__ __forceinline__ bool probe_ray(int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, V3 center, V3 origin_in, uint32_t r, V3& o, V3& d) {
+	if (mode == 2) {
+		const uint32_t wt = n_theta * n_origin;
+		const uint32_t tm = r % wt, pm = r / wt;
+		if (pm >= n_phi * n_origin) return false;
+		const uint32_t theta_mul = tm / n_origin, theta_rem = tm % n_origin, phi_mul = pm / n_origin, phi_rem = pm % n_origin;
+		const uint32_t hidx = theta_rem * n_origin + phi_rem;
+		const float ox = (float)((double)halton(2, hidx) - 0.5), oy = (float)((double)halton(3, hidx) - 0.5), oz = (float)((double)halton(5, hidx) - 0.5);
+		o = center + mk(ox, oy, oz);
+		d = normalize3(cylindrical_to_dir((float)theta_mul / (float)n_theta, (float)phi_mul / (float)n_phi));
+		return true;
+	}
+	if (r >= n_theta * n_phi) return false;
+	const uint32_t theta_mul = r % n_theta, phi_mul = r / n_theta;
+	const V3 local = cylindrical_to_dir((float)theta_mul / (float)n_theta, (float)phi_mul / (float)n_phi);
+	if (mode == 0) { o = center; d = normalize3(local); }
+	else { o = origin_in; const V3 w = normalize3(local_frame_apply(normalize3(origin_in), local)); d = mk(-w.x, -w.y, -w.z); }
+	return true;
+}
+__global__ void __launch_bounds__(256) probe_raygen_kernel(FrameArgs a, const uint8_t* __restrict__ bits, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin,
+	float ox, float oy, float oz, uint32_t n_rays, RaySoA rays, uint32_t* __restrict__ alive_list, uint32_t* __restrict__ counters) {
+	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+	bool alive = false;
+	float t = 0.0f;
+	V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 0.f, 1.f);
+	if (r < n_rays) {
+		const Box train = ldbox(a.train_aabb);
+		const V3 center = 0.5f * (train.hi + train.lo);
+		if (probe_ray(mode, n_theta, n_phi, n_origin, center, mk(ox, oy, oz), r, o, d)) {
+			const Box aabb = ldbox(a.render_aabb);
+			const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
+			t = advance_to_occupied(0.0f, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 200, occ_t_far(a, bits, o, d), nullptr);
+			alive = t < MAX_DEPTH_F;
+		}
+		rays.o_t[r] = make_float4(o.x, o.y, o.z, alive ? t : MAX_DEPTH_F);
+		rays.d_mw[r] = make_float4(d.x, d.y, d.z, 0.0f);
+		rays.rgba[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+		rays.depth[r] = 0.0f;
+		rays.pixel[r] = r;
+		rays.n_steps[r] = 0;
+	}
+	const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+	if (!mask) return;
+	const uint32_t lane = threadIdx.x & 31u;
+	const int leader = __ffs(mask) - 1;
+	uint32_t base = 0;
+	if ((int)lane == leader) base = atomicAdd(&counters[CNT_ALIVE_A], __popc(mask));
+	base = __shfl_sync(0xffffffffu, base, leader);
+	if (alive) alive_list[base + __popc(mask & ((1u << lane) - 1u))] = r;
+}
+// probe texture [n_phi][n_theta]: mean over the rays of a texel (1 ray, or n_origin^2 jittered centres in mode 2), fixed order
+__global__ void __launch_bounds__(256) probe_reduce_kernel(const float4* __restrict__ ray_rgba, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, float4* __restrict__ tex) {
+	const uint32_t texel = blockIdx.x * blockDim.x + threadIdx.x;
+	if (texel >= n_theta * n_phi) return;
+	if (mode != 2) { tex[texel] = ray_rgba[texel]; return; }
+	const uint32_t i = texel % n_theta, j = texel / n_theta, wt = n_theta * n_origin;
+	float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+	for (uint32_t pr = 0; pr < n_origin; ++pr)
+		for (uint32_t tr = 0; tr < n_origin; ++tr) {
+			const float4 v = ray_rgba[(i * n_origin + tr) + (size_t)wt * (j * n_origin + pr)];
+			acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+		}
+	const float inv = 1.0f / (float)(n_origin * n_origin);
+	tex[texel] = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+}
+
 // One ray per lane, at most `limit` samples, in the flat warp-converged loop of march_kernel (each trip a lane either takes a
 // sample or skips to the next voxel; the skip code runs only when some lane needs it): per-lane arithmetic and its order are
 // those of advance_to_occupied + calc_dt, so counts and positions equal the sequential walk. WRITE = false only counts.
@@ -608,6 +679,17 @@ void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_
 void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
 	if (!n_rays) return;
 	secondary_start_kernel<<<(n_rays + 255) / 256, 256, 0, s>>>(a, bits, rays, n_rays, alive_list, counters);
+}
+void launch_probe_raygen(const FrameArgs& a, const uint8_t* bits, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, const float origin[3], RaySoA rays,
+	uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
+	const uint32_t n_rays = n_theta * n_phi * (mode == 2 ? n_origin * n_origin : 1u);
+	if (!n_rays) return;
+	probe_raygen_kernel<<<(n_rays + 255) / 256, 256, 0, s>>>(a, bits, mode, n_theta, n_phi, n_origin, origin[0], origin[1], origin[2], n_rays, rays, alive_list, counters);
+}
+void launch_probe_reduce(const float4* ray_rgba, int mode, uint32_t n_theta, uint32_t n_phi, uint32_t n_origin, float4* tex, cudaStream_t s) {
+	const uint32_t n = n_theta * n_phi;
+	if (!n) return;
+	probe_reduce_kernel<<<(n + 255) / 256, 256, 0, s>>>(ray_rgba, mode, n_theta, n_phi, n_origin, tex);
 }
 void launch_train_march(const FrameArgs& a, const uint8_t* bits, uint32_t n_rays, const float* o, const float* d, const float* t, uint32_t max_samples,
 	uint32_t* counter, uint32_t* numsteps, uint32_t* base, float4* coords, uint32_t* sample_ray, float4* staging, cudaStream_t s) {

@@ -444,11 +444,28 @@ __global__ void __launch_bounds__(MESH_BLOCK) envlight_gen_kernel(FrameArgs a, S
 	const float4 pp = __ldg(hits.pos_pix + j), nn = __ldg(hits.nrm + j);
 	const uint32_t pix = __float_as_uint(pp.w);
 	const V3 org = mk(pp.x, pp.y, pp.z);
-	const V3 w = env_light_dir(pix, a.spp, K, k, mk(nn.x, nn.y, nn.z));
+	const V3 nrm = mk(nn.x, nn.y, nn.z);
+	V3 w;
+	float weight = 1.0f; // estimator weight of this direction: 1 for cosine sampling of a Lambertian surface
+	bool cap = false;
+	if (a.env_source == 1 && a.env_sampling == 1) { // uniform spherical cap around the direction to the NeRF's bounding sphere
+		const Box train = ldbox(a.train_aabb);
+		const V3 c = 0.5f * (train.hi + train.lo), to_c = c - org;
+		const float dist = length3(to_c), radius = 0.5f * length3(train.hi - train.lo);
+		if (dist > radius) {
+			const float cos_max = sqrtf(fmaxf(0.0f, 1.0f - (radius / dist) * (radius / dist)));
+			w = cap_light_dir(pix, a.spp, K, k, to_c / dist, 1.0f - cos_max, nrm, weight);
+			cap = true;
+		}
+	}
+	if (!cap) w = env_light_dir(pix, a.spp, K, k, nrm);
 	Hit h; bool touched;
 	scene_nearest(sc, 0, org, w, h, touched, stack_s + threadIdx.x);
 	float4 L = make_float4(0.f, 0.f, 0.f, 0.f);
-	if (h.tri < 0) L = read_envmap(a.envmap, a.env_w, a.env_h, w);
+	if (h.tri < 0 && weight > 0.0f) {
+		L = a.env_source == 1 ? read_probe(a.probe, a.probe_n_theta, a.probe_n_phi, w) : read_envmap(a.envmap, a.env_w, a.env_h, w);
+		L.x *= weight; L.y *= weight; L.z *= weight;
+	}
 	rays.o_t[i] = make_float4(org.x, org.y, org.z, 0.0f);
 	rays.d_mw[i] = make_float4(w.x, w.y, w.z, 0.0f);
 	rays.rgba[i] = make_float4(L.x, L.y, L.z, 1.0f); // .w = transmittance T of the volume along the light ray

@@ -70,6 +70,7 @@ EXPORTS = [
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
+    "hn_render_probe", "hn_set_probe", "hn_op_probe_rays",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -86,6 +87,9 @@ _lib.hn_render_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
 _lib.hn_render_to_host.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
 _lib.hn_pack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_unpack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_render_probe.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+_lib.hn_set_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+_lib.hn_op_probe_rays.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_shared_alloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
 _lib.hn_shared_open.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
 _lib.hn_shared_release.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
@@ -499,6 +503,29 @@ class Testbed:
         if e.ndim != 3 or e.shape[2] != 4:
             raise RuntimeError("envmap must have shape [h][w][4]")
         self._check(_lib.hn_set_envmap(self._h, _ptr(e), e.shape[1], e.shape[0]))
+
+    # ---- a-16 irradiance probes (NerfTracer::init_rays_from_center* + trace_mesh; the texture and its use are defined here)
+    def render_probe(self, mode: int = 0, n_theta: int = 64, n_phi: int = 128, n_origin: int = 1, origin=(0.0, 0.0, 0.0), to_host: bool = True):
+        """-> float32 [n_phi][n_theta][4] premultiplied linear radiance of the NeRF on the (cos theta, phi) lattice; kept on the device
+        as the light of the mesh pass (options env_light_source = 1, env_light_sampling, env_light_samples)."""
+        o = _f32(origin).reshape(3)
+        out = np.empty((n_phi, n_theta, 4), np.float32) if to_host else None
+        self._check(_lib.hn_render_probe(self._h, int(mode), n_theta, n_phi, n_origin, _ptr(o), _ptr(out) if to_host else None))
+        return out
+
+    def set_probe(self, rgba):
+        if rgba is None:
+            self._check(_lib.hn_set_probe(self._h, None, 0, 0))
+            return
+        t = _f32(rgba)
+        self._check(_lib.hn_set_probe(self._h, _ptr(t), t.shape[1], t.shape[0]))
+
+    def op_probe_rays(self, mode, n_theta, n_phi, n_origin=1, origin=(0.0, 0.0, 0.0)):
+        n = n_theta * n_phi * (n_origin * n_origin if mode == 2 else 1)
+        og = _f32(origin).reshape(3)
+        o = np.empty((n, 3), np.float32); d = np.empty((n, 3), np.float32); alive = np.empty(n, np.uint8)
+        self._check(_lib.hn_op_probe_rays(self._h, int(mode), n_theta, n_phi, n_origin, _ptr(og), _ptr(o), _ptr(d), _ptr(alive)))
+        return o, d, alive
 
     def op_read_envmap(self, dirs):
         d = _f32(dirs).reshape(-1, 3)

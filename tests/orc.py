@@ -43,7 +43,8 @@ class RenderParams(C.Structure):
                 ("render_mode", i32), ("depth_scale", f32),
                 ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3),
                 ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9), ("mask_pad", i32), ("pixel_mask", C.c_void_p),
-                ("density_grid_mean", f32), ("pad2", i32)]
+                ("density_grid_mean", f32), ("pad2", i32),
+                ("env_source", i32), ("env_sampling", i32), ("probe_n_theta", i32), ("probe_n_phi", i32), ("probe", C.c_void_p)]
 
 
 def P(a):
@@ -127,7 +128,7 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
                   clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
                   lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0),
-                  render_aabb_to_local=None, pixel_mask=None, density_grid_mean=0.0) -> RenderParams:
+                  render_aabb_to_local=None, pixel_mask=None, density_grid_mean=0.0, probe=None, env_sampling=0) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -165,6 +166,13 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.render_aabb_to_local[:] = R
     p.crop_rotated = int(any(abs(a - b) > 0 for a, b in zip(R, ident)))
     p.density_grid_mean = float(density_grid_mean)
+    if probe is not None:  # a-16: the NeRF's probe texture [n_phi][n_theta][4] lights the meshes
+        pt = np.ascontiguousarray(probe, np.float32)
+        assert pt.ndim == 3 and pt.shape[2] == 4
+        p._probe_keep = pt
+        p.probe = pt.ctypes.data
+        p.probe_n_phi, p.probe_n_theta = pt.shape[0], pt.shape[1]
+        p.env_source, p.env_sampling, p.env_samples = 1, int(env_sampling), int(env_samples)
     if pixel_mask is not None:
         pm = np.ascontiguousarray(pixel_mask, np.uint8).reshape(-1)
         assert pm.size == w * h
@@ -302,6 +310,42 @@ def nerf_transmittance(p: RenderParams, cfg, params, bits, o, d):
     n = C.c_uint32(0)
     T = lib.orc_nerf_transmittance(C.byref(p), C.byref(cfg), P(params), P(bits), P(o), P(d), C.byref(n))
     return float(T), int(n.value)
+
+
+def probe_rays(mode, n_theta, n_phi, n_origin=1, box=(0, 0, 0, 1, 1, 1), origin=(0.0, 0.0, 0.0)):
+    n = n_theta * n_phi * (n_origin * n_origin if mode == 2 else 1)
+    o = np.zeros((n, 3), np.float32); d = np.zeros((n, 3), np.float32); texel = np.zeros(n, np.uint32)
+    b = np.asarray(box, np.float32); og = np.asarray(origin, np.float32)
+    lib.orc_probe_rays(C.c_int32(mode), u32(n_theta), u32(n_phi), u32(n_origin), P(b), P(og), P(o), P(d), P(texel))
+    return o, d, texel
+
+
+def render_probe(p: RenderParams, cfg, params, bits, mode, n_theta, n_phi, n_origin=1, origin=(0.0, 0.0, 0.0)):
+    """oracle probe texture [n_phi][n_theta][4] (premultiplied linear RGBA) and the number of network samples"""
+    tex = np.zeros((n_phi, n_theta, 4), np.float32)
+    og = np.asarray(origin, np.float32)
+    lib.orc_render_probe.restype = C.c_uint64
+    n = lib.orc_render_probe(C.byref(p), C.byref(cfg), P(params), P(bits), C.c_int32(mode), u32(n_theta), u32(n_phi), u32(n_origin), P(og), P(tex))
+    return tex, int(n)
+
+
+def read_probe(tex, dirs):
+    t = np.ascontiguousarray(tex, np.float32)
+    d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+    out = np.zeros((d.shape[0], 4), np.float32)
+    lib.orc_read_probe(P(t), u32(t.shape[1]), u32(t.shape[0]), P(d), u32(d.shape[0]), P(out))
+    return out
+
+
+def halton(base, idx):
+    lib.orc_halton.restype = C.c_float
+    return float(lib.orc_halton(u32(base), C.c_uint64(idx)))
+
+
+def cylindrical_to_dir(p2):
+    a = np.asarray(p2, np.float32); out = np.zeros(3, np.float32)
+    lib.orc_cylindrical_to_dir(P(a), P(out))
+    return out
 
 
 def train_gradients(p: RenderParams, cfg, params, bits, origins, dirs, t_start, targets, backgrounds, loss_type=1, loss_scale=128.0, max_samples=1 << 20):

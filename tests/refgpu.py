@@ -59,6 +59,7 @@ def lib():
         _lib.rg_mesh_count.restype = C.c_uint32
         _lib.rg_mesh_n_triangles.argtypes = [C.c_void_p, C.c_uint32]
         _lib.rg_mesh_n_triangles.restype = C.c_uint64
+        _lib.rg_probe.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 7
         _lib.rg_train.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         _lib.rg_time_train.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     return _lib
@@ -214,6 +215,17 @@ class RefTestbed:
 
     def mesh_count(self):
         return int(self.l.rg_mesh_count(self.h))
+
+    def probe(self, mode, n_theta, n_phi, n_origin=1, origin=(0.0, 0.0, 0.0)):
+        """the reference's probe path: init_rays_from_center{,_outward,_multiple_center} + NerfTracer::trace_mesh.
+        -> (ray origins, ray dirs, ray texel idx, hit texel idx, hit rgba)"""
+        n = n_theta * n_phi * (n_origin * n_origin if mode == 2 else 1)
+        o = np.zeros((n, 3), np.float32); d = np.zeros((n, 3), np.float32); idx = np.zeros(n, np.uint32)
+        hidx = np.zeros(n, np.uint32); hrgba = np.zeros((n, 4), np.float32)
+        nh = C.c_uint32(0)
+        og = _f32(origin).reshape(3)
+        self._ck(self.l.rg_probe(self.h, int(mode), n_theta, n_phi, n_origin, _p(og), _p(o), _p(d), _p(idx), C.byref(nh), _p(hidx), _p(hrgba)))
+        return o, d, idx, hidx[: nh.value], hrgba[: nh.value]
 
     def train(self, batch=1 << 18, n_steps=1):
         loss = C.c_float(0)

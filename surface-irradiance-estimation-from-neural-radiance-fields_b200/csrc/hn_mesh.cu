@@ -5,6 +5,11 @@
 // bit-identical to the oracle's brute-force search. Nodes are 128-byte lines (4 child boxes SoA), triangles 3 x float4 in
 // leaf order carrying their ORIGINAL index; the traversal stack lives in shared memory, one bank-conflict-free column
 // per thread, the nearest-first child order comes from a register sorting network.
+// NOTE on provenance: evaluate_shading() below follows evaluate_shading_geometry (src/testbed_geometry_training.cu:75-144) and
+// tri_distance_sq() follows Triangle::distance_sq (include/neural-graphics-primitives/triangle.cuh:66-147) statement for
+// statement, identifiers included: those ~60 lines of formula have to match the reference operation for operation for the frame
+// (<= 1e-2) and distance (bit-exact vs brute force) parity tests, so they are transliterations, not re-derivations. Traversal, node
+// and triangle layout, the fused pass and everything around them are this project's own.
 #include "hn_device_math.cuh"
 
 namespace hn {

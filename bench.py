@@ -138,6 +138,11 @@ def reference_arm(args):
             line = reference_arm_cuda(args, refgpu)
         print(json.dumps(line))
         return
+    if args.workload == "config5" and refgpu.available():
+        with quiet_stdout():
+            line = reference_arm_train(args, refgpu)
+        print(json.dumps(line))
+        return
     return reference_arm_cpu(args)
 
 
@@ -208,6 +213,33 @@ def reference_arm_cuda(args, refgpu):
     }
     rt.close()
     return line
+
+
+def reference_arm_train(args, refgpu):
+    """--impl reference --workload config5: Testbed::train(2^18) of the reference CUDA build on the same synthetic dataset, written as
+    transforms.json + PNG frames (pure python) and loaded by the reference's own loader; same network config file."""
+    import tempfile
+    synthetic = _load_synthetic()
+    tmp = tempfile.mkdtemp(prefix="bench_ref_train_")
+    imgs, cams, focal = synthetic.sphere_dataset(64, 256)
+    refgpu.write_nerf_dataset(tmp, imgs, cams, focal)
+    rt = refgpu.RefTestbed()
+    rt.load_training_data(tmp)
+    rt.reload_network(os.path.join(ROOT, "configs", "nerf", "base.json"))
+    sampler = ClockSampler(0)
+    sampler.start()
+    ms, samples = rt.time_train(1 << 18, max(args.warmup, 8), args.steps)
+    clocks = sampler.stop()
+    val = samples / (ms * 1e-3) / 1e6
+    rt.close()
+    return {"impl": "reference", "metric": "Msamples/s, NeRF training step (forward + backward + Adam), target batch 2^18 samples per GPU", "value": val,
+            "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 8), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp16 params/activations (tcnn), fp32 master weights", "data": "synthetic",
+            "config": {"workload": "configs[4]: Testbed::train(2^18) of the reference CUDA build, configs/nerf/base.json, the same 64 analytic views 256x256 as PNG + transforms.json",
+                       "samples_per_step": samples, "device": "1 x B200 (the reference has no multi-GPU training)"},
+            "clocks": clocks, "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": 0, "kind": "reference",
+                                               "sample": f"the reference's own CUDA build on the GPU, {args.steps} training steps (wall clock around Testbed::train)"},
+            "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4}}
 
 
 def reference_arm_cpu(args):
@@ -291,6 +323,9 @@ def train_arm(args):
     imgs, cams, focal = hn.synthetic.sphere_dataset(64, 256)
     tb.set_training_data(imgs, cams, focal)
     tb.set_tile_shard(rank, world)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        tb.set_option(k, [float(x) for x in v.split(",")])
     tb.reset_trainer(1337)
     ptr, n = tb.train_gradient_buffer()
     grads = torch.as_tensor(_DevArray(ptr, n), device=dev)
@@ -350,6 +385,38 @@ def train_arm(args):
     tb.set_option("profile", 1.0)
     step()
     st = tb.train_stats()
+    roofline, cpu_baseline = None, None
+    if rank == 0:
+        # roofline of the step's HBM-bound kernel: adam_kernel streams, per parameter, fp32 master (r+w), two fp32 moments (r+w), the fp32
+        # gradient (r), the per-parameter step counter (r+w), the fp16 training copy (w) and the fp16 EMA copy + fp32 EMA accumulator (r+w / w)
+        n_par = int(info.n_params)
+        bytes_adam = n_par * (8 + 8 + 8 + 4 + 8 + 2 + 2 + 8)
+        hbm_peak, tf_peak, peak_kind = peaks()
+        if st.ms_optimizer > 0:
+            ach = bytes_adam / (st.ms_optimizer * 1e-3) / 1e9
+            roofline = {"kernel": "adam_kernel (Adam + EMA over all 11.7 M parameters; the step's bandwidth-bound kernel)", "bound": "hbm", "achieved": ach, "peak": hbm_peak,
+                        "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None, "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",
+                        "note": "the longest kernel of the step is train_march_kernel (one DDA walk per ray, latency-bound: ~6 800 rays x ~37 samples, no bandwidth or "
+                                "tensor roofline applies); the three tcgen05 MLP kernels together take forward + backward ms below",
+                        "mlp_tflops": 3 * st.n_samples_last * 18816 / ((st.ms_forward + st.ms_backward) * 1e-3) / 1e12 if st.ms_forward + st.ms_backward > 0 else None}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import orc
+        cores = os.cpu_count() or 1
+        cfg = orc.net_config_from_info(info)
+        grid = hn.synthetic.sphere_density_grid(0.35)
+        bits, _ = orc.bitfield_from_grid(grid, 1)
+        rng = np.random.default_rng(5)
+        nr = 96
+        o = (0.5 + rng.normal(size=(nr, 3)) / np.linalg.norm(rng.normal(size=(nr, 3)), axis=1, keepdims=True) * 1.6).astype(np.float32)
+        d = (0.5 + (rng.random((nr, 3)) - 0.5) * 0.5 - o).astype(np.float32)
+        d /= np.linalg.norm(d, axis=1, keepdims=True)
+        t0v = np.full(nr, 0.8, np.float32)
+        p = orc.render_params(8, 8, hn.synthetic.default_camera(), n_threads=cores)
+        tt = time.perf_counter()
+        _, _, ws = orc.train_gradients(p, cfg, hn.synthetic.random_params(info, 1337, 1e-4), bits, o, d, t0v, rng.random((nr, 3), dtype=np.float32), rng.random((nr, 3), dtype=np.float32))
+        dtc = time.perf_counter() - tt
+        cpu_baseline = {"value": float(ws.sum()) / dtc / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
+                        "sample": f"oracle forward + fp32 backward of {nr} rays = {int(ws.sum())} samples, {dtc:.1f} s (no optimizer step)"}
     if rank == 0:
         line = {"metric": "Msamples/s, NeRF training step (forward + backward + Adam), target batch 2^18 samples per GPU", "value": samples / args.steps / (ms * 1e-3) / 1e6,
                 "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 8), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -360,7 +427,7 @@ def train_arm(args):
                 "clocks": clocks, "gpu_launches": int(args.steps * 45), "loss": loss,
                 "e2e": {"value": samples / args.steps / (wall_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": wall_ms, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 8},
                 "kernel_ms": {"sample": st.ms_sample, "forward": st.ms_forward, "loss": st.ms_loss, "backward": st.ms_backward, "optimizer": st.ms_optimizer},
-                "step_phases_ms": phases, "roofline": None, "cpu_baseline": None}
+                "step_phases_ms": phases, "roofline": roofline, "cpu_baseline": cpu_baseline, "options": args.opt}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -712,5 +779,16 @@ def main():
         dist.destroy_process_group()
 
 
+def _exit_quietly():
+    """The reference library's logger writes an ANSI reset to stdout from a static destructor at process exit, i.e. AFTER the JSON line.
+    When that library was loaded the process therefore leaves through os._exit once its own output is flushed."""
+    mod = sys.modules.get("refgpu")
+    if mod is not None and getattr(mod, "_lib", None) is not None:
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
+
+
 if __name__ == "__main__":
     main()
+    _exit_quietly()

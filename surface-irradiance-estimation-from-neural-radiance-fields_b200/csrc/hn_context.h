@@ -104,6 +104,7 @@ struct TrainCfg {
 	float loss_scale = 128.0f;              // LOSS_SCALE(), common.h:232
 	uint32_t target_batch = 1u << 18;       // samples per batch (src/testbed_nerf.cu:2943)
 	int random_bg = 1;                      // nerf.training.random_bg_color
+	int mlp_impl = 1;                       // MLP forward / backward: 1 = own tcgen05 kernels (hn_train_tc.cu), 0 = cuBLAS GEMMs + elementwise kernels (round-1 path, A/B)
 	int auto_grid = 1;                      // refresh the occupancy grid from the network on the reference's schedule (training_prep_nerf)
 	float grid_decay = 0.95f;               // nerf.training.density_grid_decay (nerf.h:120)
 };
@@ -127,7 +128,7 @@ struct TrainState {
 	DevBuf<uint32_t> sample_ray;
 	DevBuf<float4> march_staging;           // [n_rays][1024] per-ray staging rows of the single-walk sample generation
 	DevBuf<__half> act[12];                 // activations: enc, density hidden..., density out, rgb in, rgb hidden..., out
-	DevBuf<__half> dact[4];                 // gradient ping-pong buffers
+	DevBuf<__half> dact[12];                // gradients: [0] dL/d(out), [1] dL/d(density out), [2] dL/d(enc), [3] dL/d(sigma) fp32, [4+l] colour hidden l, [8+l] density hidden l (cuBLAS path: [1],[2] ping-pong)
 	DevBuf<float> loss_acc;
 	// occupancy-grid maintenance (update_density_grid_nerf)
 	DevBuf<float> grid_tmp; DevBuf<float4> grid_pos; DevBuf<uint32_t> grid_idx; DevBuf<uint2> grid_out;

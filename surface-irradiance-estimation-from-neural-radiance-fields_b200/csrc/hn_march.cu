@@ -633,21 +633,34 @@ __global__ void grid_mean_kernel(const float* __restrict__ grid, double* __restr
 }
 
 // per-mip bounds of the set cells in cell coordinates: out[mip] = {min x,y,z, max x,y,z} (min > max when the mip is empty)
-__global__ void occ_bounds_kernel(const uint8_t* __restrict__ bits, int* __restrict__ out) {
+__global__ void __launch_bounds__(1024) occ_bounds_kernel(const uint8_t* __restrict__ bits, int* __restrict__ out) {
+	// one block = 1024 consecutive bytes of ONE mip (a mip has 262 144 bytes): warp reduction, block reduction in shared memory, six
+	// atomics per block (was six atomics per non-empty byte, all onto the same 48 words: 1.05 ms per grid refresh)
+	__shared__ int s_lo[32][3], s_hi[32][3];
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // byte index over all mips
-	if (i >= BITFIELD_BYTES) return;
-	const uint32_t byte = bits[i];
-	if (!byte) return;
 	const uint32_t per_mip = GRID_CELLS / 8;
-	const uint32_t mip = i / per_mip, base = (i - mip * per_mip) * 8;
+	const uint32_t mip = (blockIdx.x * blockDim.x) / per_mip;
 	int lo[3] = {1 << 30, 1 << 30, 1 << 30}, hi[3] = {-1, -1, -1};
-	for (uint32_t b = 0; b < 8; ++b) {
-		if (!(byte & (1u << b))) continue;
-		const uint32_t idx = base + b;
-		const int c[3] = {(int)morton3D_invert(idx), (int)morton3D_invert(idx >> 1), (int)morton3D_invert(idx >> 2)};
-		for (int k = 0; k < 3; ++k) { lo[k] = min(lo[k], c[k]); hi[k] = max(hi[k], c[k]); }
+	const uint32_t byte = i < BITFIELD_BYTES ? bits[i] : 0u;
+	if (byte) {
+		const uint32_t base = (i - mip * per_mip) * 8;
+		for (uint32_t b = 0; b < 8; ++b) {
+			if (!(byte & (1u << b))) continue;
+			const uint32_t idx = base + b;
+			const int c[3] = {(int)morton3D_invert(idx), (int)morton3D_invert(idx >> 1), (int)morton3D_invert(idx >> 2)};
+			for (int k = 0; k < 3; ++k) { lo[k] = min(lo[k], c[k]); hi[k] = max(hi[k], c[k]); }
+		}
 	}
-	for (int k = 0; k < 3; ++k) { atomicMin(out + mip * 6 + k, lo[k]); atomicMax(out + mip * 6 + 3 + k, hi[k]); }
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	for (int k = 0; k < 3; ++k) { lo[k] = __reduce_min_sync(0xffffffffu, lo[k]); hi[k] = __reduce_max_sync(0xffffffffu, hi[k]); }
+	if (lane == 0) for (int k = 0; k < 3; ++k) { s_lo[warp][k] = lo[k]; s_hi[warp][k] = hi[k]; }
+	__syncthreads();
+	if (warp == 0) {
+		for (int k = 0; k < 3; ++k) {
+			const int l = __reduce_min_sync(0xffffffffu, s_lo[lane][k]), h = __reduce_max_sync(0xffffffffu, s_hi[lane][k]);
+			if (lane == 0 && h >= 0) { atomicMin(out + mip * 6 + k, l); atomicMax(out + mip * 6 + 3 + k, h); }
+		}
+	}
 }
 
 // ---------------------------------------------------------------- launchers
@@ -656,7 +669,7 @@ void launch_occ_bounds(const uint8_t* bits, int* out /* CASCADES x 6, device */,
 	for (uint32_t m = 0; m < CASCADES; ++m) for (int k = 0; k < 3; ++k) { init[m * 6 + k] = 1 << 30; init[m * 6 + 3 + k] = -1; }
 	cudaMemcpyAsync(out, init, sizeof(init), cudaMemcpyHostToDevice, s);
 	cudaStreamSynchronize(s); // `init` lives on this stack frame
-	occ_bounds_kernel<<<(BITFIELD_BYTES + 255) / 256, 256, 0, s>>>(bits, out);
+	occ_bounds_kernel<<<(BITFIELD_BYTES + 1023) / 1024, 1024, 0, s>>>(bits, out);
 }
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s) {
 	// mean_out is reinterpreted as a double accumulator (8 bytes, zeroed here)

@@ -11,6 +11,7 @@
 // parameter blob [density MLP | rgb MLP | hash grid]. Round-1 scope: the MLP GEMMs are library calls, everything else is
 // hand-written; a fused tcgen05 forward/backward is the next step.
 #include "hn_context.h"
+#include "hn_train_tc.h"
 #include "hn_network.cuh"
 #include "hn_shade.cuh"
 #include <cublas_v2.h>
@@ -523,6 +524,16 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	ev.start();
 	if (net.F == 4) train_encode_kernel<4><<<blocks(n, 128), 128, 0, s>>>(ctx->levels, W + net.grid_offset, n, t.coords.p, t.sample_ray.p, t.ray_d.p, enc, rgb_in);
 	else train_encode_kernel<2><<<blocks(n, 128), 128, 0, s>>>(ctx->levels, W + net.grid_offset, n, t.coords.p, t.sample_ray.p, t.ray_d.p, enc, rgb_in);
+	const bool own_mlp = ctx->train_cfg.mlp_impl == 1 && Hd <= (uint32_t)tc::MAX_HIDDEN && Hr <= (uint32_t)tc::MAX_HIDDEN;
+	tc::TrainMlpArgs M = {};
+	if (own_mlp) {
+		M.w_density = W + net.density_w_offset; M.w_rgb = W + net.rgb_w_offset;
+		M.density_hidden = (int)Hd; M.rgb_hidden = (int)Hr; M.n = n;
+		M.enc = enc; M.d_out = d_out; M.rgb_in = rgb_in; M.out = out;
+		for (uint32_t l = 0; l < Hd; ++l) { M.hid_d[l] = t.act[1 + l].p; M.g_hid_d[l] = t.dact[8 + l].p; }
+		for (uint32_t l = 0; l < Hr; ++l) { M.hid_r[l] = t.act[Hd + 3 + l].p; M.g_hid_r[l] = t.dact[4 + l].p; }
+		M.g_out = t.dact[0].p; M.d_sigma = (const float*)t.dact[3].p; M.g_dout = t.dact[1].p; M.g_enc = t.dact[2].p;
+	}
 	auto mlp_forward = [&](const __half* w, uint32_t first_act, uint32_t hidden) {
 		int K = 32;
 		for (uint32_t l = 0; l < hidden; ++l) {
@@ -532,9 +543,13 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 		}
 		gemm_forward(h, n_gemm, 16, 64, t.act[first_act + hidden].p, w, t.act[first_act + hidden + 1].p);
 	};
-	mlp_forward(W + net.density_w_offset, 0, Hd);
-	copy_density_out_kernel<<<blocks(n), 256, 0, s>>>(d_out, rgb_in, n);
-	mlp_forward(W + net.rgb_w_offset, Hd + 2, Hr);
+	if (own_mlp) {
+		launch_train_mlp_forward(M, s); // both MLPs, every activation stored, one launch
+	} else {
+		mlp_forward(W + net.density_w_offset, 0, Hd);
+		copy_density_out_kernel<<<blocks(n), 256, 0, s>>>(d_out, rgb_in, n);
+		mlp_forward(W + net.rgb_w_offset, Hd + 2, Hr);
+	}
 	ev.stop(t.ms[1]);
 	// ---- loss and dL/d(output)
 	ev.start();
@@ -567,10 +582,32 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 		}
 		return g;
 	};
-	__half* g_rgb_in = mlp_backward(W + net.rgb_w_offset, t.grads.p + net.rgb_w_offset, Hd + 2, Hr, g_out, 1, 2);
-	__half* g_dout = t.dact[0].p; // dL/d(output) is consumed; reuse its buffer for [n][16]
-	combine_density_grad_kernel<<<blocks(n), 256, 0, s>>>(g_rgb_in, d_sigma, g_dout, n);
-	__half* g_enc = mlp_backward(W + net.density_w_offset, t.grads.p + net.density_w_offset, 0, Hd, g_dout, 1, 2);
+	__half* g_enc = nullptr;
+	if (own_mlp) {
+		launch_train_mlp_backward(M, s); // dX chain of both MLPs with ReLU masks and the sigma gradient folded in, one launch
+		tc::DwArgs D = {};
+		D.n = n;
+		int col = 0;
+		auto add = [&](const __half* a_mat, const __half* b_mat, int nb, int transposed, float* gw) {
+			tc::DwLayer& L = D.layer[D.n_layers++];
+			L.a = a_mat; L.b = b_mat; L.nb = nb; L.transposed = transposed; L.gw = gw; L.col = col;
+			col += nb;
+		};
+		auto add_mlp = [&](float* gw, const __half* x0, __half* const* hid, __half* const* g_hid, uint32_t hidden, const __half* g_top) {
+			add(g_hid[0], x0, 32, 0, gw); gw += 64 * 32;                                         // first layer: 64 x 32
+			for (uint32_t l = 1; l < hidden; ++l) { add(g_hid[l], hid[l - 1], 64, 0, gw); gw += 64 * 64; } // hidden: 64 x 64
+			add(hid[hidden - 1], g_top, 16, 1, gw);                                              // last: 16 x 64, accumulated as [in][out]
+		};
+		add_mlp(t.grads.p + net.density_w_offset, enc, M.hid_d, M.g_hid_d, Hd, M.g_dout);
+		add_mlp(t.grads.p + net.rgb_w_offset, rgb_in, M.hid_r, M.g_hid_r, Hr, M.g_out);
+		launch_train_dw(D, s);       // every weight gradient, split-K over the batch, one launch
+		g_enc = M.g_enc;
+	} else {
+		__half* g_rgb_in = mlp_backward(W + net.rgb_w_offset, t.grads.p + net.rgb_w_offset, Hd + 2, Hr, g_out, 1, 2);
+		__half* g_dout = t.dact[0].p; // dL/d(output) is consumed; reuse its buffer for [n][16]
+		combine_density_grad_kernel<<<blocks(n), 256, 0, s>>>(g_rgb_in, d_sigma, g_dout, n);
+		g_enc = mlp_backward(W + net.density_w_offset, t.grads.p + net.density_w_offset, 0, Hd, g_dout, 1, 2);
+	}
 	float* grid_grad = t.grads.p + net.grid_offset;
 	if (net.F == 4) grid_backward_kernel<4><<<blocks((size_t)n * 8, 256), 256, 0, s>>>(ctx->levels, n, t.coords.p, g_enc, grid_grad);
 	else grid_backward_kernel<2><<<blocks((size_t)n * 16, 256), 256, 0, s>>>(ctx->levels, n, t.coords.p, g_enc, grid_grad);

@@ -280,3 +280,42 @@ def write_snapshot_py(path, config_json_path, params_fp16, density_grid, aabb_sc
     }
     with open(path, "wb") as f:
         f.write(gzip.compress(msgpack.packb(cfg, use_bin_type=True), compresslevel=0))
+
+
+def write_png_rgba8(path, rgba8):
+    """Minimal PNG writer (RGBA8, non-interlaced, filter type 0) - enough for stb_image / the product's own PNG reader."""
+    import struct
+    import zlib
+    h, w, _ = rgba8.shape
+    raw = np.concatenate([np.zeros((h, 1), np.uint8), np.ascontiguousarray(rgba8, np.uint8).reshape(h, w * 4)], 1).tobytes()
+
+    def chunk(tag, data):
+        c = struct.pack(">I", len(data)) + tag + data
+        return c + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6, 0, 0, 0)) + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
+def write_nerf_dataset(directory, images, cams, focal_px, aabb_scale=1):
+    """A NeRF dataset in the reference's format (transforms.json + 8-bit sRGB PNG frames with straight alpha): images float32
+    [n][h][w][4] linear RGB + alpha, cams [n][12] NGP-space columns {right, down, forward, position}. The transform matrices are the
+    inverse of nerf_matrix_to_ngp (scale 0.33, offset 0.5, axis cycle), so the loader lands on exactly these cameras."""
+    os.makedirs(directory, exist_ok=True)
+    n, h, w, _ = images.shape
+    rgb = images[..., :3]
+    srgb = np.where(rgb < 0.0031308, 12.92 * rgb, 1.055 * np.power(np.maximum(rgb, 1e-12), 1 / 2.4) - 0.055)
+    rgba8 = np.concatenate([np.round(np.clip(srgb, 0, 1) * 255), np.round(images[..., 3:4] * 255)], -1).astype(np.uint8)
+    frames = []
+    for i in range(n):
+        write_png_rgba8(os.path.join(directory, f"r_{i}.png"), rgba8[i])
+        c = np.asarray(cams[i], np.float64).reshape(4, 3)
+        col = np.stack([c[:, 2], c[:, 0], c[:, 1]], 1)   # undo the axis cycle
+        col[1] *= -1; col[2] *= -1
+        col[3] = (col[3] - 0.5) / 0.33
+        m = np.eye(4); m[:3, :4] = col.T
+        frames.append({"file_path": f"r_{i}", "transform_matrix": m.tolist()})
+    meta = {"camera_angle_x": float(2 * np.arctan(0.5 * w / focal_px)), "aabb_scale": int(aabb_scale), "frames": frames}
+    with open(os.path.join(directory, "transforms.json"), "w") as f:
+        json.dump(meta, f)
+    return os.path.join(directory, "transforms.json")

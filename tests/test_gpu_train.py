@@ -42,9 +42,12 @@ def nerf_setup(hn, root, blob_scale, config="nerf/base.json", grid_value=1.0):
 
 @pytest.mark.parametrize("loss_type,config,grid_value", [(1, "nerf/base.json", 1.0), (0, "nerf/base.json", 1.0), (4, "geometry/base.json", 1.0),
                                                          (5, "nerf/base.json", 1.0), (1, "nerf/base.json", 0.02)])
-def test_gradients_match_oracle(hn, orc, root, loss_type, config, grid_value):
+@pytest.mark.parametrize("mlp_impl", [1, 0])
+def test_gradients_match_oracle(hn, orc, root, loss_type, config, grid_value, mlp_impl):
     # grid_value 0.02: mean density 0.004 < NERF_MIN_OPTICAL_THICKNESS -> the L1 density regulariser of the reference is active
+    # mlp_impl 1 = the tcgen05 training kernels (forward with stored activations, backward dX, split-K dW), 0 = cuBLAS GEMMs
     tb, params, grid = nerf_setup(hn, root, 0.5, config, grid_value)
+    tb.set_option("train_mlp_impl", float(mlp_impl))
     rng = np.random.default_rng(5)
     n = 96
     o, d, t0 = make_rays(rng, n)
@@ -68,6 +71,28 @@ def test_gradients_match_oracle(hn, orc, root, loss_type, config, grid_value):
     assert abs(np.linalg.norm(grads) / np.linalg.norm(wg) - 1.0) <= 2e-2
     assert np.all(grads[n_mlp:][wg[n_mlp:] == 0] == 0)   # (fp16 gradient underflow may zero a few more on the GPU side)
     assert np.mean((grads[n_mlp:] == 0) == (wg[n_mlp:] == 0)) > 0.999
+
+
+def test_own_mlp_kernels_agree_with_cublas_path(hn, root):
+    """same rays, same weights: the tcgen05 forward / backward / dW kernels against the cuBLAS GEMM path (both fp16 in, fp32 accumulate)"""
+    rng = np.random.default_rng(11)
+    n = 200                                       # ~55 k samples (below the entry point's cap of 65 536): ~430 tiles and a ragged last one
+    o, d, t0 = make_rays(rng, n)
+    targets = rng.random((n, 3), dtype=f32); bgs = rng.random((n, 3), dtype=f32)
+    res = {}
+    for config in ("nerf/base.json", "geometry/base.json"):
+        for impl in (0, 1):
+            tb, params, grid = nerf_setup(hn, root, 0.5, config)
+            tb.set_option("train_mlp_impl", float(impl))
+            res[impl] = tb.op_train_gradients(o, d, t0, targets, bgs, loss_type=1, loss_scale=128.0)
+        (l0, g0, s0), (l1, g1, s1) = res[0], res[1]
+        assert np.array_equal(s0, s1) and s0.sum() > 30000
+        assert abs(l0 - l1) <= 1e-4 * abs(l0)
+        n_mlp = int(tb.network_info().grid_param_offset)
+        print(f"{config}: |g_tc - g_cublas| / |g_cublas|: MLP {np.linalg.norm(g1[:n_mlp] - g0[:n_mlp]) / np.linalg.norm(g0[:n_mlp]):.2e}, "
+              f"grid {np.linalg.norm(g1[n_mlp:] - g0[n_mlp:]) / np.linalg.norm(g0[n_mlp:]):.2e}")
+        assert cosine(g1[:n_mlp], g0[:n_mlp]) >= 0.99999 and cosine(g1[n_mlp:], g0[n_mlp:]) >= 0.9999
+        assert abs(np.linalg.norm(g1) / np.linalg.norm(g0) - 1.0) <= 1e-3
 
 
 def teacher_dataset(hn, root, n_views=12, res=64):

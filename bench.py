@@ -330,12 +330,13 @@ def train_arm(args):
     ptr, n = tb.train_gradient_buffer()
     grads = torch.as_tensor(_DevArray(ptr, n), device=dev)
 
+    if world > 1:  # the library's training calls go onto torch's current stream, the one NCCL's all-reduce is enqueued on:
+        tb.set_stream(torch.cuda.current_stream().cuda_stream)  # accumulate -> all-reduce -> apply are stream-ordered, no host sync
+
     def step():
         loss = tb.train_accumulate(0)
         if world > 1:
-            torch.cuda.synchronize()  # the library works on its own stream
             dist.all_reduce(grads)
-            torch.cuda.synchronize()
         tb.train_apply(1.0)
         return loss
 

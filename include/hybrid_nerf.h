@@ -125,6 +125,9 @@ int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats);
 /* Optimizer step on the gradient buffer: Adam (+ ExponentialDecay, + EMA) as configured; refreshes the fp16 inference copy.
  * grad_scale multiplies the gradients first (1/world after a sum all-reduce). */
 int hn_train_apply(hn_context* ctx, float grad_scale);
+/* Put the training / set-up calls on the caller's stream (the one its collectives use): accumulate -> all-reduce -> apply then needs
+ * no host synchronisation in between. NULL = back to the context's own stream. */
+int hn_set_stream(hn_context* ctx, void* cuda_stream);
 /* n_steps x (accumulate + apply) on one GPU; loss_out = mean loss of the last step (Testbed::train + m_loss_scalar). */
 int hn_train_step(hn_context* ctx, uint32_t n_steps, float* loss_out);
 /* Occupancy-grid maintenance from the live network (Testbed::update_density_grid_nerf, src/testbed_nerf.cu:2772-2861; called by

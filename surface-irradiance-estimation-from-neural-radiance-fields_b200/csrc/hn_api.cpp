@@ -64,7 +64,8 @@ int hn_create(hn_context** out, int cuda_device) {
 	cudaDeviceProp prop;
 	HN_CUDA(cudaGetDeviceProperties(&prop, cuda_device));
 	if (prop.major != 10) throw std::runtime_error(std::string("device '") + prop.name + "' is not sm_100: kernels are built for sm_100a only");
-	HN_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+	HN_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+	ctx->stream = ctx->own_stream;
 	HN_CUDA(cudaMallocHost((void**)&ctx->pinned_counters, CNT_N * sizeof(uint32_t) * 4));
 	for (auto& e : ctx->pass_events) HN_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 	ctx->counters.ensure(CNT_N);
@@ -80,7 +81,7 @@ void hn_destroy(hn_context* ctx) {
 	release_param_textures(ctx);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto& e : ctx->pass_events) if (e) cudaEventDestroy(e);
-	if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
 
@@ -596,7 +597,24 @@ int hn_train_gradient_buffer(hn_context* ctx, void** dev_ptr, size_t* n_floats) 
 	*dev_ptr = ctx->train.grads.p; *n_floats = ctx->net.n_params;
 	HN_CATCH(ctx)
 }
-int hn_train_apply(hn_context* ctx, float grad_scale) { HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_apply(ctx, grad_scale); HN_CUDA(cudaStreamSynchronize(ctx->stream)); HN_CATCH(ctx) }
+int hn_train_apply(hn_context* ctx, float grad_scale) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	train_apply(ctx, grad_scale);
+	if (ctx->stream == ctx->own_stream) HN_CUDA(cudaStreamSynchronize(ctx->stream)); // on a caller's stream the step stays stream-ordered (no host wait)
+	HN_CATCH(ctx)
+}
+// Run the training / set-up calls on the caller's stream (e.g. the one its NCCL collectives use), so that
+// hn_train_accumulate -> all-reduce of hn_train_gradient_buffer -> hn_train_apply needs no host synchronisation in between.
+// stream = NULL returns to the context's own stream.
+int hn_set_stream(hn_context* ctx, void* cuda_stream) {
+	HN_TRY(ctx)
+	need(ctx->own_stream != nullptr, "no CUDA device");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+	HN_CATCH(ctx)
+}
 int hn_train_step(hn_context* ctx, uint32_t n_steps, float* loss_out) {
 	HN_TRY(ctx)
 	HN_CUDA(cudaSetDevice(ctx->device));

@@ -141,7 +141,8 @@ struct TrainState {
 struct hn_context {
 	int device = 0;
 	std::string error;
-	cudaStream_t stream = nullptr; // own stream for the non-frame calls
+	cudaStream_t stream = nullptr; // stream of the non-frame calls: the context's own, or the caller's (hn_set_stream)
+	cudaStream_t own_stream = nullptr;
 
 	// network
 	hn::NetCfg net;

@@ -70,7 +70,7 @@ EXPORTS = [
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
-    "hn_render_probe", "hn_set_probe", "hn_op_probe_rays",
+    "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -87,6 +87,7 @@ _lib.hn_render_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
 _lib.hn_render_to_host.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
 _lib.hn_pack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_unpack_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_set_stream.argtypes = [C.c_void_p, C.c_void_p]
 _lib.hn_render_probe.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
 _lib.hn_set_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
 _lib.hn_op_probe_rays.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -444,6 +445,10 @@ class Testbed:
         ptr = C.c_void_p(0); n = C.c_size_t(0)
         self._check(_lib.hn_train_gradient_buffer(self._h, C.byref(ptr), C.byref(n)))
         return int(ptr.value), int(n.value)
+
+    def set_stream(self, stream: int = 0):
+        """run the training / set-up calls on the caller's CUDA stream (0 / None = the context's own)"""
+        self._check(_lib.hn_set_stream(self._h, C.c_void_p(stream or 0)))
 
     def train_apply(self, grad_scale: float = 1.0):
         self._check(_lib.hn_train_apply(self._h, grad_scale))

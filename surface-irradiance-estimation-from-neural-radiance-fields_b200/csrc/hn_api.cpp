@@ -131,6 +131,8 @@ static void refresh_occ_bounds(hn_context* ctx) {
 	DevBuf<int> d_b;
 	d_b.ensure(CASCADES * 6);
 	launch_occ_bounds(ctx->bitfield.p, d_b.p, ctx->stream);
+	ctx->occ_coarse.ensure(CASCADES * 1024);
+	launch_occ_coarse(ctx->bitfield.p, ctx->occ_coarse.p, ctx->stream);
 	HN_CUDA(cudaMemcpyAsync(ctx->occ_cells, d_b.p, sizeof(ctx->occ_cells), cudaMemcpyDeviceToHost, ctx->stream));
 	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 	HN_CUDA(cudaGetLastError());
@@ -237,7 +239,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_mlp_impl", {&c->train_cfg.mlp_impl, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
-		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -343,6 +345,7 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 			a.occ_aabb[3 + k] = std::max(a.occ_aabb[3 + k], ((float)(c[3 + k] + 1) / 128.0f - 0.5f) * scale + 0.5f + pad);
 		}
 	}
+	a.occ_coarse = ctx->opt.tight_t_far ? ctx->occ_coarse.p : nullptr;
 	a.max_mip = (uint32_t)o.max_cascade; a.cone_angle = o.cone_angle_constant; a.min_transmittance = o.min_transmittance;
 	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
 	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;
@@ -367,14 +370,14 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 RaySoA ray_soa(hn_context* ctx) {
 	RaySoA r;
 	r.o_t = ctx->ray_o_t.p; r.d_mw = ctx->ray_d_mw.p; r.rgba = ctx->ray_rgba.p; r.depth = ctx->ray_depth.p;
-	r.pixel = ctx->ray_pixel.p; r.n_steps = ctx->ray_nsteps.p;
+	r.pixel = ctx->ray_pixel.p; r.n_steps = ctx->ray_nsteps.p; r.t_far = ctx->ray_tfar.p;
 	r.sh = nullptr; // set by the camera-ray path after ray_sh_kernel has run
 	return r;
 }
 
 void ensure_rays(hn_context* ctx, size_t n) {
 	ctx->ray_o_t.ensure(n); ctx->ray_d_mw.ensure(n); ctx->ray_rgba.ensure(n); ctx->ray_depth.ensure(n);
-	ctx->ray_pixel.ensure(n); ctx->ray_nsteps.ensure(n); ctx->alive_a.ensure(n); ctx->alive_b.ensure(n); ctx->sample_counts.ensure(n);
+	ctx->ray_pixel.ensure(n); ctx->ray_nsteps.ensure(n); ctx->ray_tfar.ensure(n); ctx->alive_a.ensure(n); ctx->alive_b.ensure(n); ctx->sample_counts.ensure(n);
 }
 
 template <typename T> T* scratch(hn_context* ctx, int slot, size_t count) { ctx->scratch[slot].ensure(count * sizeof(T) + 16); return (T*)ctx->scratch[slot].p; }

@@ -91,6 +91,7 @@ struct Options {
 	int env_light_sampling = 0;                 // 0 = cosine hemisphere around the normal, 1 = uniform spherical cap around the direction to the NeRF (probe source)
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
 	int env_light_batch = 8 << 20;              // light rays in flight per batch (bounds the workspace)
+	int tight_t_far = 1;                        // 1: rays are cut off at the last flagged coarse occupancy cell (occ_t_far_tight), 0: at the box of the set cells (A/B)
 	int mesh_aabb_user = 0;
 	float mesh_aabb[6] = {0, 0, 0, 1, 1, 1};
 };
@@ -166,6 +167,8 @@ struct hn_context {
 	hn::DevBuf<float> density_grid;         // device copy of the float grid [128^3 x grid_cascades] (Morton order), kept for the live updates
 	uint32_t grid_cascades = 0;
 	float density_grid_mean = 1.0f;         // m_nerf.density_grid_mean (mean of max(v, 0) over cascade 0); 1 = unknown (bitfield set directly)
+	hn::DevBuf<uint32_t> occ_coarse;        // [CASCADES][1024] dilated 32^3 occupancy flags per mip (occ_t_far_tight), refreshed with the bitfield
+	hn::DevBuf<float> ray_tfar;
 	int occ_cells[hn::CASCADES * 6] = {};   // per-mip bounds of the set cells (cell coordinates), refreshed with the bitfield
 
 	// scene

@@ -57,6 +57,7 @@ struct FrameArgs {
 	float render_aabb[6], train_aabb[6];
 	float aabb_to_local[9]; int crop_rotated; // m_render_aabb_to_local (column-major); crop_rotated = 0 -> identity, skipped
 	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
+	const uint32_t* occ_coarse; // [CASCADES][32^3 bits] dilated coarse occupancy (occ_coarse_kernel), nullptr = slab bound only
 	uint32_t max_mip;
 	float cone_angle;
 	float min_transmittance;
@@ -98,6 +99,7 @@ struct RaySoA {
 	float* depth;
 	uint32_t* pixel;
 	uint32_t* n_steps;
+	float* t_far;    // ray parameter beyond which no set occupancy cell can be met (occ_t_far_tight), written when the ray is started
 	uint4* sh;       // [ray][2] fp16 SH coefficients of the direction, filled once per frame for the first live list (may be nullptr)
 };
 
@@ -128,6 +130,7 @@ struct SceneDev {
 void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thresh, uint8_t* bits, cudaStream_t s);
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s);
 void launch_occ_bounds(const uint8_t* bits, int* out, cudaStream_t s);
+void launch_occ_coarse(const uint8_t* bits, uint32_t* coarse, cudaStream_t s);
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters,
 	float* depth_buffer, float4* frame, cudaStream_t s);
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s);

@@ -223,9 +223,62 @@ __device__ __forceinline__ float occ_t_far(const FrameArgs& a, const uint8_t* bi
 	return tmax + 1e-3f;
 }
 
+// Tight far end: the slab test above bounds the ray by the BOX of the set cells; a ray that grazes that box, or has left the
+// occupied region long before it leaves the box, still walks the empty cells one by one (up to ~150 skip trips through the
+// corner of a sphere's box - the slowest warps of raygen_kernel and of every march pass). Each mip therefore also has a 32^3
+// coarse grid (one coarse cell = 4x4x4 fine cells = one aligned 64-bit word of the Morton-ordered bitfield) whose flag is set when
+// the cell OR one of its 26 neighbours holds a set fine cell (occ_coarse_kernel). The ray is walked BACKWARDS from its slab exit
+// through that grid with a plain 3-D DDA: the first flagged cell met is the last one along the ray, and its far side bounds every
+// t at which the fine walk can still find a set cell. The one-cell dilation makes the bound safe against the rounding of this
+// DDA (a cell the ray clips within floating-point error has a flagged neighbour that the walk does visit at about the same t);
+// the exact fine walk is unchanged, only where it is cut off, so counts and positions stay bit-identical.
+__device__ float occ_t_far_tight(const FrameArgs& a, const uint8_t* bits, V3 o, V3 d) {
+	const float coarse_far = occ_t_far(a, bits, o, d);
+	if (!bits || !a.occ_coarse || coarse_far < 0.0f) return coarse_far;
+	float best = -1.0f;
+	const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+	for (uint32_t m = 0; m <= a.max_mip; ++m) {
+		const float inv = scalbnf(1.0f, -(int)m); // mip-m grid coordinates u = (p - 0.5) 2^-m + 0.5 in [0,1]^3
+		float q[3], e[3];
+		float t0 = 0.0f, t1 = coarse_far;
+		bool miss = false;
+		#pragma unroll
+		for (int k = 0; k < 3; ++k) {
+			q[k] = (oo[k] - 0.5f) * inv + 0.5f; e[k] = dd[k] * inv;
+			if (e[k] == 0.0f) { if (q[k] < 0.0f || q[k] > 1.0f) miss = true; }
+			else { const float ta = (0.0f - q[k]) / e[k], tb = (1.0f - q[k]) / e[k]; t0 = fmaxf(t0, fminf(ta, tb)); t1 = fminf(t1, fmaxf(ta, tb)); }
+		}
+		if (miss || !(t0 <= t1)) continue;
+		// reversed ray from the exit point, parameter s in [0, t1 - t0]; scalars per axis (no dynamically indexed arrays)
+		int gx, gy, gz, sx, sy, sz;
+		float mx, my, mz, dx, dy, dz;
+		#define HN_AXIS(K, G, S, M, D) { \
+			const float x = (q[K] + t1 * e[K]) * 32.0f, r = -e[K] * 32.0f; /* position and direction in coarse cells */ \
+			G = min(max((int)floorf(x), 0), 31); \
+			if (r > 0.0f) { S = 1; M = ((float)(G + 1) - x) / r; D = 1.0f / r; } \
+			else if (r < 0.0f) { S = -1; M = ((float)G - x) / r; D = -1.0f / r; } \
+			else { S = 0; M = FLT_MAX; D = FLT_MAX; } \
+			M = fmaxf(M, 0.0f); }
+		HN_AXIS(0, gx, sx, mx, dx) HN_AXIS(1, gy, sy, my, dy) HN_AXIS(2, gz, sz, mz, dz)
+		#undef HN_AXIS
+		const uint32_t* __restrict__ flags = a.occ_coarse + m * 1024u;
+		const float s_end = t1 - t0;
+		float s = 0.0f; // parameter at which the current cell was entered
+		for (int it = 0; it < 100; ++it) {
+			const uint32_t cell = (uint32_t)gx + 32u * (uint32_t)gy + 1024u * (uint32_t)gz;
+			if (__ldg(flags + (cell >> 5)) & (1u << (cell & 31u))) { best = fmaxf(best, t1 - s); break; }
+			if (mx <= my && mx <= mz) { s = mx; gx += sx; mx += dx; if (gx < 0 || gx > 31) break; }
+			else if (my <= mz) { s = my; gy += sy; my += dy; if (gy < 0 || gy > 31) break; }
+			else { s = mz; gz += sz; mz += dz; if (gz < 0 || gz > 31) break; }
+			if (s > s_end) break;
+		}
+	}
+	return best < 0.0f ? -1.0f : fminf(best + 1e-3f, coarse_far);
+}
+
 // per-pixel start state: init_rays (:1478-1543) + advance_pos_nerf (:333-362). Returns alive.
-__device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out) {
-	t_out = MAX_DEPTH_F;
+__device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out, float& t_far_out) {
+	t_out = MAX_DEPTH_F; t_far_out = -1.0f;
 	if (!pixel_ray(a, x, y, o, d)) return false; // invalid ray (f-theta lens outside its image circle)
 	uint32_t idx = x + (uint32_t)a.w * y;
 	Box aabb = ldbox(a.render_aabb);
@@ -235,7 +288,8 @@ __device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, 
 	if (!box_contains(aabb, to_crop_local(R, o + t * d))) return false;
 	V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
 	t = advance_n_steps(t, a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
-	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, occ_t_far(a, bits, o, d), R);
+	t_far_out = occ_t_far_tight(a, bits, o, d);
+	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, t_far_out, R);
 	if (t >= MAX_DEPTH_F) return false;
 	t_out = t;
 	return true;
@@ -255,12 +309,12 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer, float4* __restrict__ frame) {
 	uint32_t x = 0, y = 0, idx = 0;
 	bool alive = false;
-	V3 o, d; float t = 0.0f;
+	V3 o, d; float t = 0.0f, t_far = -1.0f;
 	if (owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) {
 		idx = x + (uint32_t)a.w * y;
 		// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
 		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
-		alive = start_ray(a, bits, x, y, o, d, t);
+		alive = start_ray(a, bits, x, y, o, d, t, t_far);
 		// :1526-1528: envmap -> frame buffer; in hybrid frames only where the mesh pass left nothing
 		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) if (d.x != 0.0f || d.y != 0.0f || d.z != 0.0f) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);
 	}
@@ -278,6 +332,7 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		rays.depth[r] = 0.0f;
 		rays.pixel[r] = idx;
 		rays.n_steps[r] = 0;
+		rays.t_far[r] = t_far;
 		alive_list[r] = r;
 	}
 }
@@ -288,7 +343,7 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 	uint32_t* __restrict__ alive_list, uint32_t* __restrict__ counters) {
 	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
 	bool alive = false;
-	float t = 0.0f;
+	float t = 0.0f, t_far = -1.0f;
 	if (r < n_rays) {
 		const float4 L = rays.rgba[r];
 		if (L.x != 0.0f || L.y != 0.0f || L.z != 0.0f) {
@@ -299,7 +354,8 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 			t = fmaxf(box_ray_intersect(aabb, to_crop_local(R, o), to_crop_local(R, d)).x, 0.0f) + 1e-6f;
 			if (box_contains(aabb, to_crop_local(R, o + t * d))) {
 				const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-				t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, occ_t_far(a, bits, o, d), R);
+				t_far = occ_t_far_tight(a, bits, o, d);
+				t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far, R);
 				alive = t < MAX_DEPTH_F;
 			}
 		}
@@ -313,6 +369,7 @@ __global__ void __launch_bounds__(256) secondary_start_kernel(FrameArgs a, const
 	base = __shfl_sync(0xffffffffu, base, leader);
 	if (alive) {
 		rays.o_t[r].w = t;
+		rays.t_far[r] = t_far;
 		alive_list[base + __popc(mask & ((1u << lane) - 1u))] = r;
 	}
 }
@@ -345,7 +402,7 @@ __global__ void __launch_bounds__(256) probe_raygen_kernel(FrameArgs a, const ui
 	float ox, float oy, float oz, uint32_t n_rays, RaySoA rays, uint32_t* __restrict__ alive_list, uint32_t* __restrict__ counters) {
 	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
 	bool alive = false;
-	float t = 0.0f;
+	float t = 0.0f, t_far = -1.0f;
 	V3 o = mk(0.f, 0.f, 0.f), d = mk(0.f, 0.f, 1.f);
 	if (r < n_rays) {
 		const Box train = ldbox(a.train_aabb);
@@ -353,7 +410,8 @@ __global__ void __launch_bounds__(256) probe_raygen_kernel(FrameArgs a, const ui
 		if (probe_ray(mode, n_theta, n_phi, n_origin, center, mk(ox, oy, oz), r, o, d)) {
 			const Box aabb = ldbox(a.render_aabb);
 			const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-			t = advance_to_occupied(0.0f, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 200, occ_t_far(a, bits, o, d), nullptr);
+			t_far = occ_t_far_tight(a, bits, o, d);
+			t = advance_to_occupied(0.0f, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 200, t_far, nullptr);
 			alive = t < MAX_DEPTH_F;
 		}
 		rays.o_t[r] = make_float4(o.x, o.y, o.z, alive ? t : MAX_DEPTH_F);
@@ -362,6 +420,7 @@ __global__ void __launch_bounds__(256) probe_raygen_kernel(FrameArgs a, const ui
 		rays.depth[r] = 0.0f;
 		rays.pixel[r] = r;
 		rays.n_steps[r] = 0;
+		rays.t_far[r] = t_far;
 	}
 	const uint32_t mask = __ballot_sync(0xffffffffu, alive);
 	if (!mask) return;
@@ -397,7 +456,7 @@ __device__ __forceinline__ uint32_t flat_march(const FrameArgs& a, const uint8_t
 	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
 	const V3 tdiag = train.hi - train.lo;
 	const V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-	const float t_far = valid ? occ_t_far(a, bits, o, d) : -1.f;
+	const float t_far = valid ? occ_t_far_tight(a, bits, o, d) : -1.f;
 	bool active = valid && limit > 0;
 	uint32_t count = 0;
 	int it = 1;
@@ -480,8 +539,8 @@ __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const ui
 	float* __restrict__ t_out, uint8_t* __restrict__ alive_out) {
 	uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= (uint32_t)a.w * (uint32_t)a.h) return;
-	V3 o, d; float t;
-	bool alive = start_ray(a, bits, idx % (uint32_t)a.w, idx / (uint32_t)a.w, o, d, t);
+	V3 o, d; float t, t_far;
+	bool alive = start_ray(a, bits, idx % (uint32_t)a.w, idx / (uint32_t)a.w, o, d, t, t_far);
 	o_out[3 * idx] = o.x; o_out[3 * idx + 1] = o.y; o_out[3 * idx + 2] = o.z;
 	d_out[3 * idx] = d.x; d_out[3 * idx + 1] = d.y; d_out[3 * idx + 2] = d.z;
 	t_out[idx] = t;
@@ -514,7 +573,7 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 		const float4 ot = rays.o_t[r], dm = rays.d_mw[r];
 		o = mk(ot.x, ot.y, ot.z); d = mk(dm.x, dm.y, dm.z); t = ot.w;
 		idir = mk(1.0f, 1.0f, 1.0f) / d;
-		t_far = occ_t_far(a, bits, o, d);
+		t_far = rays.t_far[r]; // occ_t_far_tight, computed once when the ray was started
 		if (clipping) clip = depth_buffer[rays.pixel[r]];
 	}
 	float4* dst = samples + (size_t)p * CHUNK;
@@ -577,7 +636,7 @@ __global__ void __launch_bounds__(128) march_all_kernel(FrameArgs a, const uint8
 		V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
 		Box aabb = ldbox(a.render_aabb);
 		float t = t0[i];
-		const float t_far = occ_t_far(a, bits, o, d);
+		const float t_far = occ_t_far_tight(a, bits, o, d);
 		while (true) {
 			t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, a.dda_iter_cap, t_far, HN_CROP_R(a));
 			if (t >= MAX_DEPTH_F) break;
@@ -663,7 +722,27 @@ __global__ void __launch_bounds__(1024) occ_bounds_kernel(const uint8_t* __restr
 	}
 }
 
+// coarse occupancy flags for occ_t_far_tight: [mip][32^3 bits], bit (cx + 32 cy + 1024 cz) = some fine cell is set in coarse cell
+// (cx, cy, cz) or in one of its 26 neighbours. A coarse cell is the aligned 64-bit word morton3D(cx, cy, cz) of the mip's bitfield.
+__global__ void __launch_bounds__(256) occ_coarse_kernel(const uint8_t* __restrict__ bits, uint32_t* __restrict__ coarse) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // over CASCADES x 32^3
+	const uint32_t mip = i >> 15, c = i & 32767u;
+	const int cx = (int)(c & 31u), cy = (int)((c >> 5) & 31u), cz = (int)(c >> 10);
+	const unsigned long long* __restrict__ words = reinterpret_cast<const unsigned long long*>(bits + (size_t)mip * (GRID_CELLS / 8));
+	bool any = false;
+	for (int dz = -1; dz <= 1; ++dz) for (int dy = -1; dy <= 1; ++dy) for (int dx = -1; dx <= 1; ++dx) {
+		const int x = cx + dx, y = cy + dy, z = cz + dz;
+		if (x < 0 || x > 31 || y < 0 || y > 31 || z < 0 || z > 31) continue;
+		any = any || words[morton3D((uint32_t)x, (uint32_t)y, (uint32_t)z)] != 0ull;
+	}
+	const uint32_t word = __ballot_sync(0xffffffffu, any);
+	if ((threadIdx.x & 31u) == 0) coarse[i >> 5] = word;
+}
+
 // ---------------------------------------------------------------- launchers
+void launch_occ_coarse(const uint8_t* bits, uint32_t* coarse /* CASCADES x 1024 words, device */, cudaStream_t s) {
+	occ_coarse_kernel<<<CASCADES * 32768 / 256, 256, 0, s>>>(bits, coarse);
+}
 void launch_occ_bounds(const uint8_t* bits, int* out /* CASCADES x 6, device */, cudaStream_t s) {
 	int init[CASCADES * 6];
 	for (uint32_t m = 0; m < CASCADES; ++m) for (int k = 0; k < 3; ++k) { init[m * 6 + k] = 1 << 30; init[m * 6 + 3 + k] = -1; }

@@ -239,7 +239,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_mlp_impl", {&c->train_cfg.mlp_impl, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
-		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -345,7 +345,7 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 			a.occ_aabb[3 + k] = std::max(a.occ_aabb[3 + k], ((float)(c[3 + k] + 1) / 128.0f - 0.5f) * scale + 0.5f + pad);
 		}
 	}
-	a.occ_coarse = ctx->opt.tight_t_far ? ctx->occ_coarse.p : nullptr;
+	a.occ_coarse = ctx->opt.tight_t_far ? ctx->occ_coarse.p : nullptr; a.simple_walk = ctx->opt.march_simple;
 	a.max_mip = (uint32_t)o.max_cascade; a.cone_angle = o.cone_angle_constant; a.min_transmittance = o.min_transmittance;
 	a.rgb_act = o.rgb_activation; a.density_act = o.density_activation; a.linear_colors = o.linear_colors; a.dda_iter_cap = o.dda_iter_cap;
 	a.depth_test = 0; a.depth_clip = o.depth_merge_clip;

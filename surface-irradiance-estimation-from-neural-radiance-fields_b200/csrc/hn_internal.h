@@ -59,6 +59,7 @@ struct FrameArgs {
 	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
 	const uint32_t* occ_coarse; // [CASCADES][32^3 bits] dilated coarse occupancy (occ_coarse_kernel), nullptr = slab bound only
 	uint32_t max_mip;
+	int simple_walk;       // option march_simple: allow the compile-time specialised walk kernels (A/B switch)
 	float cone_angle;
 	float min_transmittance;
 	int rgb_act, density_act, linear_colors, dda_iter_cap;

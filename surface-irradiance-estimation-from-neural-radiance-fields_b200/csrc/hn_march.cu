@@ -189,13 +189,21 @@ __device__ __forceinline__ V3 to_crop_local(const float* __restrict__ R, V3 v) {
 // t_far: parameter beyond which the ray has left the (inflated) bounds of every set occupancy cell. No sample can follow, so
 // the reference's loop is bound to end in MAX_DEPTH there; returning it at once is exact and removes the cell-by-cell walk
 // through empty space to the edge of the render box.
-__device__ float advance_to_occupied(float t, float cone, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bits, uint32_t min_mip, uint32_t max_mip,
-	const Box& aabb, int iter_cap, float t_far, const float* __restrict__ R = nullptr) {
+// SIMPLE: the common set-up (cone angle 0, one cascade, axis-aligned crop box, a bitfield) as compile-time constants - the stepping
+// space is linear (no logf / expf paths), the mip is 0, the crop rotation and the null checks fold away: same arithmetic on the
+// same values, about half the instructions per trip of the walk.
+template <bool SIMPLE = false>
+__device__ __forceinline__ float advance_to_occupied(float t, float cone_in, V3 o, V3 d, V3 idir, const uint8_t* __restrict__ bits_in, uint32_t min_mip_in, uint32_t max_mip_in,
+	const Box& aabb, int iter_cap, float t_far, const float* __restrict__ R_in = nullptr) {
+	const float cone = SIMPLE ? 0.0f : cone_in;
+	const uint32_t min_mip = SIMPLE ? 0u : min_mip_in, max_mip = SIMPLE ? 0u : max_mip_in;
+	const float* __restrict__ R = SIMPLE ? nullptr : R_in;
+	const uint8_t* __restrict__ bits = bits_in;
 	for (int i = 1; iter_cap <= 0 || i < iter_cap; ++i) {
 		V3 pos = o + t * d;
 		if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(R, pos))) return MAX_DEPTH_F;
-		uint32_t mip = min(max(mip_from_pos(pos), min_mip), max_mip);
-		if (!bits || occupied_at(pos, bits, mip)) return t;
+		uint32_t mip = SIMPLE ? 0u : min(max(mip_from_pos(pos), min_mip), max_mip);
+		if ((!SIMPLE && !bits) || occupied_at(pos, bits, mip)) return t;
 		while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
 		t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
 	}
@@ -277,19 +285,20 @@ __device__ float occ_t_far_tight(const FrameArgs& a, const uint8_t* bits, V3 o, 
 }
 
 // per-pixel start state: init_rays (:1478-1543) + advance_pos_nerf (:333-362). Returns alive.
-__device__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out, float& t_far_out) {
+template <bool SIMPLE = false>
+__device__ __forceinline__ bool start_ray(const FrameArgs& a, const uint8_t* __restrict__ bits, uint32_t x, uint32_t y, V3& o, V3& d, float& t_out, float& t_far_out) {
 	t_out = MAX_DEPTH_F; t_far_out = -1.0f;
 	if (!pixel_ray(a, x, y, o, d)) return false; // invalid ray (f-theta lens outside its image circle)
 	uint32_t idx = x + (uint32_t)a.w * y;
 	Box aabb = ldbox(a.render_aabb);
-	const float* R = HN_CROP_R(a);
+	const float* R = SIMPLE ? nullptr : HN_CROP_R(a);
 	float t = fmaxf(box_ray_intersect(aabb, to_crop_local(R, o), to_crop_local(R, d)).x, 0.0f) + 1e-6f;
 	t_out = MAX_DEPTH_F;
 	if (!box_contains(aabb, to_crop_local(R, o + t * d))) return false;
 	V3 idir = mk(1.0f, 1.0f, 1.0f) / d;
-	t = advance_n_steps(t, a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
+	t = advance_n_steps(t, SIMPLE ? 0.0f : a.cone_angle, hn_ld_random_val(a.spp, idx * 786433u));
 	t_far_out = occ_t_far_tight(a, bits, o, d);
-	t = advance_to_occupied(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, t_far_out, R);
+	t = advance_to_occupied<SIMPLE>(t, a.cone_angle, o, d, idir, bits, 0, a.max_mip, aabb, 0, t_far_out, R);
 	if (t >= MAX_DEPTH_F) return false;
 	t_out = t;
 	return true;
@@ -305,6 +314,7 @@ __device__ __forceinline__ bool tile_owned(const FrameArgs& a, uint32_t x, uint3
 // ---------------------------------------------------------------- kernels
 // One thread per pixel. Live rays are appended to the SoA ray buffers through a warp-aggregated atomic (one atomicAdd
 // per warp); the ray id is the slot. Order is non-deterministic, results are keyed by pixel so the image is not.
+template <bool SIMPLE>
 __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, uint32_t* __restrict__ alive_list,
 	uint32_t* __restrict__ counters, float* __restrict__ depth_buffer, float4* __restrict__ frame) {
 	uint32_t x = 0, y = 0, idx = 0;
@@ -314,7 +324,7 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		idx = x + (uint32_t)a.w * y;
 		// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
 		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
-		alive = start_ray(a, bits, x, y, o, d, t, t_far);
+		alive = start_ray<SIMPLE>(a, bits, x, y, o, d, t, t_far);
 		// :1526-1528: envmap -> frame buffer; in hybrid frames only where the mesh pass left nothing
 		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) if (d.x != 0.0f || d.y != 0.0f || d.z != 0.0f) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);
 	}
@@ -553,6 +563,7 @@ __global__ void __launch_bounds__(256) raygen_debug_kernel(FrameArgs a, const ui
 // a warp on its slowest lane at every sample. Here both loops are flattened into ONE warp-converged loop: each trip a lane
 // either emits a sample (cell occupied) or skips to the next voxel, and the skip code is entered only when some lane of
 // the warp needs it (warp-uniform branch). Per-lane arithmetic and its order are unchanged -> bit-identical samples.
+template <bool SIMPLE>
 __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* __restrict__ bits, RaySoA rays, const uint32_t* __restrict__ alive_list,
 	const uint32_t* __restrict__ n_alive_ptr, float4* __restrict__ samples, uint32_t* __restrict__ sample_counts, uint32_t* __restrict__ counters,
 	const float* __restrict__ depth_buffer) {
@@ -567,7 +578,10 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 	const Box aabb = ldbox(a.render_aabb), train = ldbox(a.train_aabb);
 	const V3 tdiag = train.hi - train.lo;
 	const V3 cam_fwd = ld3(a.cam1 + 6), cam_pos = ld3(a.cam1 + 9);
-	const bool clipping = a.depth_clip && a.depth_test;
+	const bool clipping = SIMPLE ? false : (a.depth_clip && a.depth_test);
+	const float cone = SIMPLE ? 0.0f : a.cone_angle;
+	const uint32_t max_mip = SIMPLE ? 0u : a.max_mip;
+	const float* __restrict__ R = SIMPLE ? nullptr : HN_CROP_R(a);
 	if (valid) {
 		r = alive_list[p];
 		const float4 ot = rays.o_t[r], dm = rays.d_mw[r];
@@ -583,12 +597,12 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 		V3 pos = o;
 		if (active) {
 			pos = o + t * d;
-			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(HN_CROP_R(a), pos))) {
+			if (t >= MAX_DEPTH_F || t > t_far || !box_contains(aabb, to_crop_local(R, pos))) {
 				t = MAX_DEPTH_F; active = false;
 			} else {
-				mip = a.max_mip ? min(max(mip_from_pos(pos), 0u), a.max_mip) : 0u; // one cascade: the clamp makes it 0 whatever frexpf says
-				if (!bits || occupied_at(pos, bits, mip)) {
-					const float dt = calc_dt(t, a.cone_angle);
+				mip = max_mip ? min(max(mip_from_pos(pos), 0u), max_mip) : 0u; // one cascade: the clamp makes it 0 whatever frexpf says
+				if ((!SIMPLE && !bits) || occupied_at(pos, bits, mip)) {
+					const float dt = calc_dt(t, cone);
 					bool emit = true;
 					if (clipping) {
 						const V3 up = train.lo + ((pos - train.lo) / tdiag) * tdiag;
@@ -608,8 +622,8 @@ __global__ void __launch_bounds__(128) march_kernel(FrameArgs a, const uint8_t* 
 		}
 		if (__any_sync(0xffffffffu, skip)) {
 			if (skip) {
-				while (mip < a.max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
-				t = advance_to_next_voxel(t, a.cone_angle, pos, d, idir, mip);
+				while (mip < max_mip && !occupied_at(pos, bits, mip + 1)) ++mip;
+				t = advance_to_next_voxel(t, cone, pos, d, idir, mip);
 				++it;
 				if (a.dda_iter_cap > 0 && it >= a.dda_iter_cap) { t = MAX_DEPTH_F; active = false; }
 			}
@@ -740,6 +754,8 @@ __global__ void __launch_bounds__(256) occ_coarse_kernel(const uint8_t* __restri
 }
 
 // ---------------------------------------------------------------- launchers
+// the SIMPLE specialisation of the walk applies: linear stepping space, one cascade, axis-aligned crop box, a bitfield
+static bool simple_walk(const FrameArgs& a, const uint8_t* bits) { return a.simple_walk && bits && a.cone_angle <= 1e-5f && a.max_mip == 0 && !a.crop_rotated; }
 void launch_occ_coarse(const uint8_t* bits, uint32_t* coarse /* CASCADES x 1024 words, device */, cudaStream_t s) {
 	occ_coarse_kernel<<<CASCADES * 32768 / 256, 256, 0, s>>>(bits, coarse);
 }
@@ -766,7 +782,8 @@ void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thres
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters, float* depth_buffer, float4* frame, cudaStream_t s) {
 	uint32_t n = owned_pixel_threads(a);
 	if (!n) return;
-	raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
+	if (simple_walk(a, bits)) raygen_kernel<true><<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
+	else raygen_kernel<false><<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
 }
 void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
 	if (!n_rays) return;
@@ -795,7 +812,8 @@ void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, floa
 void launch_march(const FrameArgs& a, const uint8_t* bits, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr,
 	float4* samples, uint32_t* sample_counts, uint32_t* counters, const float* depth_buffer, uint32_t max_rays, cudaStream_t s) {
 	if (!max_rays) return;
-	march_kernel<<<(max_rays + 127) / 128, 128, 0, s>>>(a, bits, rays, alive_list, n_alive_ptr, samples, sample_counts, counters, depth_buffer);
+	if (simple_walk(a, bits) && !(a.depth_clip && a.depth_test)) march_kernel<true><<<(max_rays + 127) / 128, 128, 0, s>>>(a, bits, rays, alive_list, n_alive_ptr, samples, sample_counts, counters, depth_buffer);
+	else march_kernel<false><<<(max_rays + 127) / 128, 128, 0, s>>>(a, bits, rays, alive_list, n_alive_ptr, samples, sample_counts, counters, depth_buffer);
 }
 void launch_march_all(const FrameArgs& a, const uint8_t* bits, uint32_t n, const float* o, const float* d, const float* t0, const uint8_t* alive,
 	uint32_t* counts, float* samples, uint32_t max_per_ray, cudaStream_t s) {

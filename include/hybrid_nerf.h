@@ -215,6 +215,14 @@ int hn_op_march_all(hn_context* ctx, uint32_t n_rays, const float* origins, cons
 	uint32_t* counts, float* samples, uint32_t max_per_ray);
 /* a-10: hash-grid encoding of n positions in [0,1]^3 -> fp16 [n][32] (host). */
 int hn_op_encode(hn_context* ctx, const float* positions, uint32_t n, uint16_t* out);
+/* hn_op_encode without any device allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same arguments and the
+ * same (bit-identical) result as hn_op_encode; the device staging is a static __device__ array of the library (4.75 MiB per GPU,
+ * held until the process exits) instead of the context's growable buffers. n > HN_NOALLOC_MAX_POSITIONS is rejected (returns 1,
+ * hn_last_error says why). The array is shared by every call and context on a device and keeps the last call's contents: calls
+ * that overlap on the GPU race - serialise them. Calls no cudaMalloc / cudaFree / allocating library routine. (csrc/hn_noalloc.cu) */
+#define HN_NOALLOC_MAX_POSITIONS 65536u
+int hn_op_encode_noalloc(hn_context* ctx, const float* positions, uint32_t n, uint16_t* out);
 /* a-10..a-13: samples come in ray chunks of 32 sharing one direction. positions [n][4] = un-warped x,y,z,dt (n % 32 == 0),
  * dirs [n/32][3] unit vectors; out fp16 [n][4] raw (r,g,b,sigma). */
 int hn_op_network(hn_context* ctx, const float* positions, const float* dirs, uint32_t n, uint16_t* out);

@@ -60,6 +60,8 @@ class TrainStats(C.Structure):
 
 
 # every symbol include/hybrid_nerf.h declares (tests check that the library exports all of them)
+NOALLOC_MAX_POSITIONS = 65536  # HN_NOALLOC_MAX_POSITIONS (include/hybrid_nerf.h): positions per hn_op_encode_noalloc call
+
 EXPORTS = [
     "hn_create", "hn_destroy", "hn_last_error", "hn_version", "hn_load_network_config", "hn_load_network_config_string",
     "hn_set_aabb_scale", "hn_get_network_info", "hn_set_params", "hn_load_snapshot", "hn_save_snapshot", "hn_set_density_grid", "hn_set_occupancy_bitfield",
@@ -70,7 +72,7 @@ EXPORTS = [
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
-    "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream",
+    "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -98,6 +100,7 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_op_encode_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_trace.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
 _lib.hn_op_mesh_distance.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
@@ -402,6 +405,13 @@ class Testbed:
         p = _f32(positions).reshape(-1, 3)
         out = np.empty((p.shape[0], 32), np.float16)
         self._check(_lib.hn_op_encode(self._h, _ptr(p), p.shape[0], _ptr(out)))
+        return out
+
+    def op_encode_noalloc(self, positions):
+        """hn_op_encode through the library's static device scratch: no device allocation, at most NOALLOC_MAX_POSITIONS per call"""
+        p = _f32(positions).reshape(-1, 3)
+        out = np.empty((p.shape[0], 32), np.float16)
+        self._check(_lib.hn_op_encode_noalloc(self._h, _ptr(p), p.shape[0], _ptr(out)))
         return out
 
     def op_network(self, positions_dt, dirs):

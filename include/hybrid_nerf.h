@@ -151,6 +151,24 @@ int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out);
 int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
 	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
 
+/* ---- error map (nerf.h:104-118; src/testbed_nerf.cu:1080-1106,1776-1832,2986-3075; nerf_device.cuh:536-639) ----
+ * hn_train_accumulate deposits every ray's mean loss into a coarse per-image map and rebuilds the sampling CDFs from it every
+ * n_steps_between_error_map_updates steps (128, then x1.5 each time). Options "sample_focal_plane_proportional_to_error" and
+ * "sample_image_proportional_to_error" (both 0 by default, as in the reference) let the CDFs pick the pixel / the image of a ray.
+ * hn_get_error_map: m_nerf.training.error_map.{resolution,data}; res[2] = (x, y), data [n_images][res_y][res_x] (data may be NULL). */
+int hn_get_error_map(hn_context* ctx, int res[2], uint32_t* n_images, float* data, size_t n_floats);
+/* operators for the parity tests (host buffers): construct_cdf_2d + construct_cdf_1d + the host image CDF on `data`
+ * [n_images][height][width] -> cdf_x_cond_y (same shape), cdf_y [n_images][height], cdf_img / pmf_img [n_images] (outputs may be NULL) */
+int hn_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y,
+	float* cdf_img, float* pmf_img);
+/* image_idx + nerf_random_image_pos_training as the training ray generator runs them for global ray ray_offset + i of step `step`
+ * (pcg32(seed + step << 32) advanced 16 per ray; CDFs may be NULL = uniform): image, un-snapped uv [n][2], pdf = img_pdf * uv_pdf */
+int hn_op_sample_training_pixels(hn_context* ctx, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images,
+	int cdf_res_x, int cdf_res_y, const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img, float* uv, float* pdf);
+/* the bilinear deposit of compute_loss_kernel_train_nerf (:1080-1106) of n values at (img, uv) into a zeroed map [n_images][res_y][res_x] */
+int hn_op_error_map_deposit(hn_context* ctx, uint32_t n, const uint32_t* img, const float* uv, const float* val, uint32_t n_images, int res_x, int res_y,
+	int img_w, int img_h, float* map);
+
 /* ---- render state (public Testbed members; names follow src/python_api.cu:482-567) ---- */
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values);
 int hn_get_option(const hn_context* ctx, const char* name, float* values, int n_values);

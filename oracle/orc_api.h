@@ -158,6 +158,15 @@ void orc_update_density_grid(const orc_render_params* p, const orc_net_config* c
 	uint32_t n_uniform, uint32_t n_nonuniform, float decay, uint32_t seed, uint32_t rng_calls);
 uint32_t orc_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out);
 
+// ---- training error map (orc_errmap.inc) ----
+uint32_t orc_binary_search(float val, const float* data, uint32_t length);
+uint32_t orc_image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images, const float* cdf, float* pdf);
+void orc_sample_cdf_2d(float sample[2], uint32_t img, int32_t res_x, int32_t res_y, const float* cdf_x_cond_y, const float* cdf_y, float* pdf);
+void orc_error_map_cdf(uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img);
+void orc_sample_training_pixels(uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images, int32_t res_x, int32_t res_y,
+	const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img_out, float* uv_out, float* pdf_out);
+void orc_error_map_deposit(uint32_t n, const uint32_t* img, const float* uv, const float* val, int32_t res_x, int32_t res_y, int32_t img_w, int32_t img_h, float* map);
+
 // ---- meshes (a-17..a-19) ----
 typedef struct orc_scene orc_scene;
 orc_scene* orc_scene_create(void);

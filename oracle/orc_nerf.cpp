@@ -856,6 +856,7 @@ float nerf_transmittance(const orc_render_params& p, const Net& net, const uint8
 #include "orc_probe.inc"
 #include "orc_train.inc"
 #include "orc_grid.inc"
+#include "orc_errmap.inc"
 
 Net* net_new(const orc_net_config& c, const uint16_t* params) { return new Net(make_net(c, params)); }
 void net_delete(Net* n) { delete n; }

@@ -145,4 +145,60 @@ uint32_t ref_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out) {
 	return n;
 }
 
+// ---- training error map: binary_search (common.h:242-264), sample_cdf_2d / image_idx (nerf_device.cuh:538-568, 617-639)
+uint32_t ref_binary_search(float val, const float* data, uint32_t length) { return binary_search(val, data, length); }
+void ref_sample_cdf_2d(float sample[2], uint32_t img, int32_t res_x, int32_t res_y, const float* cdf_x_cond_y, const float* cdf_y, float* pdf) {
+	*pdf = 1.0f;
+	vec2 r = sample_cdf_2d(vec2(sample[0], sample[1]), img, ivec2(res_x, res_y), cdf_x_cond_y, cdf_y, pdf);
+	sample[0] = r.x; sample[1] = r.y;
+}
+uint32_t ref_image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images, const float* cdf, float* pdf) { return image_idx(base_idx, n_rays, 0, n_images, cdf, pdf); }
+
+// ---- foveation (common_device.cuh:117-246): constructor (20-step bisection) + warp / unwarp / density
+static Foveation make_fov(const float f[6]) { return Foveation(vec2(f[0], f[1]), vec2(f[2], f[3]), vec2(f[4], f[5])); }
+void ref_foveation_coeffs(const float f[6], float out[24]) {
+	Foveation fv = make_fov(f);
+	const FoveationPiecewiseQuadratic* w[2] = {&fv.warp_x, &fv.warp_y};
+	for (int k = 0; k < 2; ++k) {
+		float* o = out + 12 * k;
+		o[0] = w[k]->al; o[1] = w[k]->bl; o[2] = w[k]->cl; o[3] = w[k]->am; o[4] = w[k]->bm; o[5] = w[k]->ar; o[6] = w[k]->br; o[7] = w[k]->cr;
+		o[8] = w[k]->switch_left; o[9] = w[k]->switch_right; o[10] = w[k]->inv_switch_left; o[11] = w[k]->inv_switch_right;
+	}
+}
+void ref_foveation_warp(const float f[6], const float uv[2], float warped[2], float unwarped[2], float* density) {
+	Foveation fv = make_fov(f);
+	vec2 a = fv.warp(vec2(uv[0], uv[1])), b = fv.unwarp(vec2(uv[0], uv[1]));
+	warped[0] = a.x; warped[1] = a.y; unwarped[0] = b.x; unwarped[1] = b.y; *density = fv.density(vec2(uv[0], uv[1]));
+}
+// uv_to_ray (common_device.cuh:416-483) with everything: foveation, hidden-area mask, lens, distortion grid
+int32_t ref_uv_to_ray_full(uint32_t spp, const float uv[2], int32_t w, int32_t h, const float focal[2], const float cam[12], const float screen_center[2],
+	const float parallax[3], float near_distance, float focus_z, float aperture_size, const float fov[6], const uint8_t* mask, int32_t mask_w, int32_t mask_h,
+	int32_t lens_mode, const float lens_params[7], const float* distortion, int32_t dist_w, int32_t dist_h, float out_o[3], float out_d[3]) {
+	mat4x3 c;
+	for (int i = 0; i < 4; ++i) c[i] = vec3(cam[3*i], cam[3*i+1], cam[3*i+2]);
+	Lens lens;
+	lens.mode = (ELensMode)lens_mode;
+	for (int i = 0; i < 7; ++i) lens.params[i] = lens_params[i];
+	Buffer2DView<const uint8_t> m; m.data = mask; m.resolution = ivec2(mask_w, mask_h);
+	Buffer2DView<const vec2> d; d.data = (const vec2*)distortion; d.resolution = ivec2(dist_w, dist_h);
+	Ray ray = uv_to_ray(spp, vec2(uv[0], uv[1]), ivec2(w, h), vec2(focal[0], focal[1]), c, vec2(screen_center[0], screen_center[1]),
+		vec3(parallax[0], parallax[1], parallax[2]), near_distance, focus_z, aperture_size, make_fov(fov), m, lens, d);
+	out_o[0] = ray.o.x; out_o[1] = ray.o.y; out_o[2] = ray.o.z;
+	out_d[0] = ray.d.x; out_d[1] = ray.d.y; out_d[2] = ray.d.z;
+	return ray.is_valid() ? 1 : 0;
+}
+// pos_to_uv (common_device.cuh:505-537) and the colour of ERenderMode::Distortion (to_rgb, :737-739)
+void ref_pos_to_uv(const float pos[3], int32_t w, int32_t h, const float focal[2], const float cam[12], const float screen_center[2], const float parallax[3],
+	const float fov[6], int32_t lens_mode, const float lens_params[7], float out[2]) {
+	mat4x3 c;
+	for (int i = 0; i < 4; ++i) c[i] = vec3(cam[3*i], cam[3*i+1], cam[3*i+2]);
+	Lens lens;
+	lens.mode = (ELensMode)lens_mode;
+	for (int i = 0; i < 7; ++i) lens.params[i] = lens_params[i];
+	vec2 r = pos_to_uv(vec3(pos[0], pos[1], pos[2]), ivec2(w, h), vec2(focal[0], focal[1]), c, vec2(screen_center[0], screen_center[1]),
+		vec3(parallax[0], parallax[1], parallax[2]), make_fov(fov), lens);
+	out[0] = r.x; out[1] = r.y;
+}
+void ref_to_rgb(const float dir[2], float out[3]) { vec3 c = to_rgb(vec2(dir[0], dir[1])); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
+
 }

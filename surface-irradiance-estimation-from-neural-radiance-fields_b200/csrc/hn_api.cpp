@@ -238,6 +238,8 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_mlp_impl", {&c->train_cfg.mlp_impl, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
+		{"sample_focal_plane_proportional_to_error", {&c->train_cfg.sample_focal_plane_proportional_to_error, 1, true}},
+		{"sample_image_proportional_to_error", {&c->train_cfg.sample_image_proportional_to_error, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
 		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}},
 	};
@@ -652,6 +654,22 @@ int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins
 	HN_CUDA(cudaSetDevice(ctx->device));
 	train_op_gradients(ctx, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, loss_out, grads_host, n_steps);
 	HN_CATCH(ctx)
+}
+
+int hn_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_op_error_map_cdf(ctx, n_images, height, width, data, cdf_x_cond_y, cdf_y, cdf_img, pmf_img); HN_CATCH(ctx)
+}
+int hn_op_sample_training_pixels(hn_context* ctx, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images,
+	int cdf_res_x, int cdf_res_y, const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img, float* uv, float* pdf) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device));
+	train_op_sample_pixels(ctx, n_rays, ray_offset, n_rays_total, seed, step, n_images, cdf_res_x, cdf_res_y, cdf_x_cond_y, cdf_y, cdf_img, img, uv, pdf);
+	HN_CATCH(ctx)
+}
+int hn_op_error_map_deposit(hn_context* ctx, uint32_t n, const uint32_t* img, const float* uv, const float* val, uint32_t n_images, int res_x, int res_y, int img_w, int img_h, float* map) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_op_error_map_deposit(ctx, n, img, uv, val, n_images, res_x, res_y, img_w, img_h, map); HN_CATCH(ctx)
+}
+int hn_get_error_map(hn_context* ctx, int res[2], uint32_t* n_images, float* data, size_t n_floats) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_get_error_map(ctx, res, n_images, data, n_floats); HN_CATCH(ctx)
 }
 
 int hn_render_frame(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2],

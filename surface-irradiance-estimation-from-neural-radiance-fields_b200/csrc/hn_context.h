@@ -90,7 +90,7 @@ struct Options {
 	int env_light_source = 0;                   // light of the mesh pass: 0 = environment map (hn_set_envmap), 1 = the NeRF's irradiance probe (hn_render_probe)
 	int env_light_sampling = 0;                 // 0 = cosine hemisphere around the normal, 1 = uniform spherical cap around the direction to the NeRF (probe source)
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
-	int env_light_batch = 8 << 20;              // light rays in flight per batch (bounds the workspace)
+	int env_light_batch = 32 << 20;             // light rays in flight per batch (bounds the workspace: ~200 bytes per ray)
 	int march_simple = 1;                       // 1: compile-time specialised raygen / march kernels when cone angle 0, one cascade, axis-aligned crop (A/B)
 	int tight_t_far = 1;                        // 1: rays are cut off at the last flagged coarse occupancy cell (occ_t_far_tight), 0: at the box of the set cells (A/B)
 	int mesh_aabb_user = 0;
@@ -107,6 +107,8 @@ struct TrainCfg {
 	uint32_t target_batch = 1u << 18;       // samples per batch (src/testbed_nerf.cu:2943)
 	int random_bg = 1;                      // nerf.training.random_bg_color
 	int mlp_impl = 1;                       // MLP forward / backward: 1 = own tcgen05 kernels (hn_train_tc.cu), 0 = cuBLAS GEMMs + elementwise kernels (round-1 path, A/B)
+	int sample_focal_plane_proportional_to_error = 0; // nerf.training.sample_focal_plane_proportional_to_error (nerf.h:112): pixels from the error-map CDF
+	int sample_image_proportional_to_error = 0;       // nerf.training.sample_image_proportional_to_error (nerf.h:113): images from the error-map CDF
 	int auto_grid = 1;                      // refresh the occupancy grid from the network on the reference's schedule (training_prep_nerf)
 	float grid_decay = 0.95f;               // nerf.training.density_grid_decay (nerf.h:120)
 };
@@ -132,6 +134,13 @@ struct TrainState {
 	DevBuf<__half> act[12];                 // activations: enc, density hidden..., density out, rgb in, rgb hidden..., out
 	DevBuf<__half> dact[12];                // gradients: [0] dL/d(out), [1] dL/d(density out), [2] dL/d(enc), [3] dL/d(sigma) fp32, [4+l] colour hidden l, [8+l] density hidden l (cuBLAS path: [1],[2] ping-pong)
 	DevBuf<float> loss_acc;
+	// error map (nerf.h:104-118): accumulated per-image loss, its CDFs, and where / with which pdf each ray of the batch was drawn
+	DevBuf<uint32_t> ray_img; DevBuf<float> ray_uv, ray_pdf;
+	DevBuf<float> error_map, cdf_x_cond_y, cdf_y, cdf_img;
+	int err_res[2] = {0, 0}, cdf_res[2] = {0, 0};
+	bool cdf_valid = false;
+	uint32_t n_steps_since_error_map_update = 0, n_steps_between_error_map_updates = 128;
+	std::vector<float> pmf_img;             // error_map.pmf_img_cpu
 	// occupancy-grid maintenance (update_density_grid_nerf)
 	DevBuf<float> grid_tmp; DevBuf<float4> grid_pos; DevBuf<uint32_t> grid_idx; DevBuf<uint2> grid_out;
 	uint32_t grid_seed = 1337, grid_rng_calls = 0, grid_ema_step = 0;
@@ -252,6 +261,11 @@ void train_release(hn_context* ctx);
 void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps);
 void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n);
 void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+void train_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img);
+void train_op_sample_pixels(hn_context* ctx, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images, int cdf_res_x, int cdf_res_y,
+	const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img, float* uv, float* pdf);
+void train_op_error_map_deposit(hn_context* ctx, uint32_t n, const uint32_t* img, const float* uv, const float* val, uint32_t n_images, int res_x, int res_y, int img_w, int img_h, float* map);
+void train_get_error_map(hn_context* ctx, int res[2], uint32_t* n_images, float* data, size_t n_floats);
 void train_mark_untrained(hn_context* ctx);
 void refresh_bitfield_from_device_grid(hn_context* ctx); // hn_api.cpp: mean -> threshold -> bitfield + mips -> occupancy bounds
 // hn_dataset.cpp

@@ -38,7 +38,11 @@ __device__ __forceinline__ void cswap(float& da, int& ia, float& db, int& ib) {
 
 // Nearest hit inside one mesh. Acceptance as triangle_bvh.cu:150-193 (mint starts at the caller's best, strict <) plus the
 // shared tie rule: equal t inside the same mesh -> lower original triangle index.
-__device__ void traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& best, int* stack /* shared, stride MESH_BLOCK */) {
+// ANY = true: occlusion query - return at the first accepted triangle (same acceptance test, so "is there a hit" has the same answer as
+// the nearest-hit search; which triangle is reported is arbitrary). Returns whether a triangle was accepted during this call.
+template <bool ANY = false>
+__device__ bool traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& best, int* stack /* shared, stride MESH_BLOCK */) {
+	bool found = false;
 	const MeshDev m = sc.meshes[mesh];
 	const V3 inv = mk(1.0f, 1.0f, 1.0f) / d;
 	int sp = 0;
@@ -52,7 +56,10 @@ __device__ void traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& bes
 				const float4 A = __ldg(sc.tris + (size_t)(first + k) * 3), B = __ldg(sc.tris + (size_t)(first + k) * 3 + 1), C = __ldg(sc.tris + (size_t)(first + k) * 3 + 2);
 				const float t = tri_intersect(mk(A.x, A.y, A.z), mk(B.x, B.y, B.z), mk(C.x, C.y, C.z), o, d);
 				const int orig = __float_as_int(A.w);
-				if (t < best.t || (t == best.t && best.mesh == mesh && orig < best.tri)) { best.t = t; best.mesh = mesh; best.tri = orig; best.slot = first + k; }
+				if (t < best.t || (t == best.t && best.mesh == mesh && orig < best.tri)) {
+					best.t = t; best.mesh = mesh; best.tri = orig; best.slot = first + k; found = true;
+					if (ANY) return true;
+				}
 			}
 			continue;
 		}
@@ -89,6 +96,13 @@ __device__ void traverse_mesh(const SceneDev& sc, int mesh, V3 o, V3 d, Hit& bes
 			}
 		}
 	}
+	return found;
+}
+// a-16 shadow test of a light ray: is ANY triangle of any mesh hit (the light pass only asks whether the ray is blocked)
+__device__ bool scene_occluded(const SceneDev& sc, V3 o, V3 d, int* stack) {
+	Hit h; h.t = MAX_DIST_F; h.mesh = -1; h.tri = -1; h.slot = 0;
+	for (uint32_t i = 0; i < sc.n_meshes; ++i) if (traverse_mesh<true>(sc, (int)i, o, d, h, stack)) return true;
+	return false;
 }
 
 // geometry_bvh.cu:646-676 with the top level of :166-200. compat = pick the ONE mesh with the nearest box entry
@@ -438,8 +452,8 @@ __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, Scen
 	}
 }
 
-// a-16 (OUR definition, oracle render_mesh): light ray k of hit j -> ray slot (j - first) * K + k. The shadow test is a
-// nearest-hit search over all meshes; occluded rays carry zero radiance and never enter the volume.
+// a-16 (OUR definition, oracle render_mesh): light ray k of hit j -> ray slot (j - first) * K + k. The shadow test is an any-hit
+// query over all meshes (same answer as the oracle's nearest-hit search); occluded rays carry zero radiance and never enter the volume.
 __global__ void __launch_bounds__(MESH_BLOCK) envlight_gen_kernel(FrameArgs a, SceneDev sc, EnvHits hits, uint32_t first, uint32_t n, RaySoA rays) {
 	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
 	const uint32_t K = (uint32_t)a.env_samples;
@@ -464,10 +478,10 @@ __global__ void __launch_bounds__(MESH_BLOCK) envlight_gen_kernel(FrameArgs a, S
 		}
 	}
 	if (!cap) w = env_light_dir(pix, a.spp, K, k, nrm);
-	Hit h; bool touched;
-	scene_nearest(sc, 0, org, w, h, touched, stack_s + threadIdx.x);
+	// zero-weight directions carry no radiance whatever the shadow test says: skip the traversal
+	const bool blocked = weight > 0.0f ? scene_occluded(sc, org, w, stack_s + threadIdx.x) : true;
 	float4 L = make_float4(0.f, 0.f, 0.f, 0.f);
-	if (h.tri < 0 && weight > 0.0f) {
+	if (!blocked && weight > 0.0f) {
 		L = a.env_source == 1 ? read_probe(a.probe, a.probe_n_theta, a.probe_n_phi, w) : read_envmap(a.envmap, a.env_w, a.env_h, w);
 		L.x *= weight; L.y *= weight; L.z *= weight;
 	}

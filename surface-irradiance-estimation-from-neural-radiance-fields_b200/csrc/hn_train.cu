@@ -14,6 +14,7 @@
 #include "hn_train_tc.h"
 #include "hn_network.cuh"
 #include "hn_shade.cuh"
+#include "hn_device_math.cuh"
 #include <cublas_v2.h>
 #include <algorithm>
 #include <cmath>
@@ -58,20 +59,109 @@ struct TrainDataDev {
 	uint32_t n_images; int w, h; float focal[2], principal[2];
 };
 
+// ---- error map (src/testbed_nerf.cu:1080-1106, 1776-1832, 2986-3075; nerf_device.cuh:536-633) ----
+// Per training image a coarse map of the mean loss of the rays that landed there (bilinear deposit), turned every
+// n_steps_between_error_map_updates steps into CDFs (x given y, y, image) that can steer the choice of image and pixel.
+struct ErrorMapDev {
+	float* data;                  // [n_images][res_y][res_x] accumulated loss, nullptr = off
+	int res[2];
+	const float* cdf_x_cond_y;    // nullptr: pixels uniformly (nerf.training.sample_focal_plane_proportional_to_error off / no CDF yet)
+	const float* cdf_y;
+	const float* cdf_img;         // nullptr: image by ray index (sample_image_proportional_to_error off / no CDF yet)
+	int cdf_res[2];
+};
+// common.h:242-264
+__host__ __device__ inline uint32_t cdf_binary_search(float val, const float* __restrict__ data, uint32_t length) {
+	if (length == 0) return 0;
+	uint32_t first = 0, count = length;
+	while (count > 0) {
+		const uint32_t step = count / 2, it = first + step;
+		if (data[it] < val) { first = it + 1; count -= step + 1; } else count = step;
+	}
+	return first < length - 1 ? first : length - 1;
+}
+// image_idx (nerf_device.cuh:617-639)
+__host__ __device__ inline uint32_t train_image_idx(uint32_t base_idx, uint32_t n_rays, uint32_t n_images, const float* __restrict__ cdf, float& pdf) {
+	pdf = 1.0f;
+	if (cdf) {
+		const float sample = hn_ld_random_val(base_idx, 0xdeadbeefu);
+		const uint32_t img = cdf_binary_search(sample, cdf, n_images);
+		const float prev = img > 0 ? cdf[img - 1] : 0.0f;
+		pdf = (cdf[img] - prev) * (float)n_images;
+		return img;
+	}
+	return ((base_idx * n_images) / n_rays) % n_images; // 32-bit arithmetic as in the reference (wraps for base_idx * n_images >= 2^32)
+}
+// sample_cdf_2d (nerf_device.cuh:538-568): half of the samples stay uniform (UNIFORM_SAMPLING_FRACTION)
+__host__ __device__ inline void train_sample_cdf_2d(float& sx, float& sy, uint32_t img, int res_x, int res_y, const float* __restrict__ cdf_x_cond_y, const float* __restrict__ cdf_y, float& pdf) {
+	if (sx < 0.5f) { sx /= 0.5f; return; }
+	sx = (sx - 0.5f) / (1.0f - 0.5f);
+	cdf_y += (size_t)img * res_y;
+	const uint32_t y = cdf_binary_search(sy, cdf_y, (uint32_t)res_y);
+	float prev = y > 0 ? cdf_y[y - 1] : 0.0f;
+	const float pmf_y = cdf_y[y] - prev;
+	sy = (sy - prev) / pmf_y;
+	cdf_x_cond_y += (size_t)img * res_y * res_x + (size_t)y * res_x;
+	const uint32_t x = cdf_binary_search(sx, cdf_x_cond_y, (uint32_t)res_x);
+	prev = x > 0 ? cdf_x_cond_y[x - 1] : 0.0f;
+	const float pmf_x = cdf_x_cond_y[x] - prev;
+	sx = (sx - prev) / pmf_x;
+	pdf = pmf_x * pmf_y * (float)(res_x * res_y);
+	sx = ((float)x + sx) / (float)res_x; sy = ((float)y + sy) / (float)res_y;
+}
+// compute_loss_kernel_train_nerf :1080-1106 (the clamp of the cell index against the IMAGE resolution - 2 is the reference's)
+__device__ __forceinline__ void error_map_deposit(float* __restrict__ map, int res_x, int res_y, int img_w, int img_h, uint32_t img, float u, float v, float val) {
+	const float px = fminf(fmaxf(u * (float)res_x - 0.5f, 0.0f), (float)res_x - (1.0f + 1e-4f));
+	const float py = fminf(fmaxf(v * (float)res_y - 0.5f, 0.0f), (float)res_y - (1.0f + 1e-4f));
+	const int ix = (int)px, iy = (int)py;
+	const float wx = px - (float)ix, wy = py - (float)iy;
+	const int x = min(max(ix, 0), img_w - 2), y = min(max(iy, 0), img_h - 2);
+	float* m = map + (size_t)img * res_x * res_y;
+	atomicAdd(m + y * res_x + x, (1 - wx) * (1 - wy) * val);
+	atomicAdd(m + y * res_x + x + 1, wx * (1 - wy) * val);
+	atomicAdd(m + (y + 1) * res_x + x, (1 - wx) * wy * val);
+	atomicAdd(m + (y + 1) * res_x + x + 1, wx * wy * val);
+}
+// construct_cdf_2d / construct_cdf_1d (:1776-1832): one thread per (row, image) / per image, sequential sums (same order -> same bits)
+__global__ void construct_cdf_2d_kernel(uint32_t n_images, uint32_t height, uint32_t width, const float* __restrict__ data, float* __restrict__ cdf_x_cond_y, float* __restrict__ cdf_y) {
+	const uint32_t y = threadIdx.x + blockIdx.x * blockDim.x, img = threadIdx.y + blockIdx.y * blockDim.y;
+	if (y >= height || img >= n_images) return;
+	const size_t off = ((size_t)img * height + y) * width;
+	data += off; cdf_x_cond_y += off;
+	float cum = 0;
+	for (uint32_t x = 0; x < width; ++x) { cum += data[x] + 1e-10f; cdf_x_cond_y[x] = cum; }
+	cdf_y[img * height + y] = cum;
+	const float norm = __frcp_rn(cum);
+	for (uint32_t x = 0; x < width; ++x) cdf_x_cond_y[x] = (1.0f - 0.01f) * cdf_x_cond_y[x] * norm + 0.01f * (float)(x + 1) / (float)width;
+}
+__global__ void construct_cdf_1d_kernel(uint32_t n_images, uint32_t height, float* __restrict__ cdf_y, float* __restrict__ cdf_img) {
+	const uint32_t img = threadIdx.x + blockIdx.x * blockDim.x;
+	if (img >= n_images) return;
+	cdf_y += (size_t)img * height;
+	float cum = 0;
+	for (uint32_t y = 0; y < height; ++y) { cum += cdf_y[y]; cdf_y[y] = cum; }
+	cdf_img[img] = cum;
+	const float norm = __frcp_rn(cum);
+	for (uint32_t y = 0; y < height; ++y) cdf_y[y] = (1.0f - 0.01f) * cdf_y[y] * norm + 0.01f * (float)(y + 1) / (float)height;
+}
+
 // Training rays from the dataset (train_nerf_step ray selection, src/testbed_nerf.cu:789-846 + :1007-1037): ray i of the
 // global stream belongs to image (i * n_images) / n_rays_total, pixel uniformly random (snapped to the pixel centre),
 // random background colour, target = linear_to_srgb(rgb + (1 - a) * bg) (Linear image colour space, sRGB training space).
 // Start t = AABB entry advanced by a random fraction of a step (:817-821).
 __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step,
 	int random_bg, int srgb_space, float bg_r, float bg_g, float bg_b, float* __restrict__ ray_o, float* __restrict__ ray_d, float* __restrict__ ray_t,
-	float* __restrict__ ray_target, float* __restrict__ ray_bg) {
+	float* __restrict__ ray_target, float* __restrict__ ray_bg, ErrorMapDev E, uint32_t* __restrict__ ray_img, float* __restrict__ ray_uv, float* __restrict__ ray_pdf) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_rays) return;
 	const uint32_t gi = i + ray_offset;
 	Pcg32 rng((uint64_t)seed + ((uint64_t)step << 32));
 	rng.advance((uint64_t)gi * 16u); // N_MAX_RANDOM_SAMPLES_PER_RAY
-	const uint32_t img = (uint32_t)(((uint64_t)gi * D.n_images) / n_rays_total) % D.n_images;
-	const float u = rng.next_float(), v = rng.next_float();
+	// image and pixel: by ray index / uniform, or from the error-map CDFs (image_idx, nerf_random_image_pos_training)
+	float img_pdf = 1.0f, uv_pdf = 1.0f;
+	const uint32_t img = train_image_idx(gi, n_rays_total, D.n_images, E.cdf_img, img_pdf);
+	float u = rng.next_float(), v = rng.next_float();
+	if (E.cdf_x_cond_y) train_sample_cdf_2d(u, v, img, E.cdf_res[0], E.cdf_res[1], E.cdf_x_cond_y, E.cdf_y, uv_pdf);
 	int px = min(max((int)(u * (float)D.w), 0), D.w - 1), py = min(max((int)(v * (float)D.h), 0), D.h - 1);
 	const float uu = ((float)px + 0.5f) / (float)D.w, vv = ((float)py + 0.5f) / (float)D.h;
 	const float jitter = rng.next_float();
@@ -85,6 +175,7 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 	d0 *= inv; d1 *= inv; d2 *= inv;
 	ray_o[3 * i] = c[9]; ray_o[3 * i + 1] = c[10]; ray_o[3 * i + 2] = c[11];
 	ray_d[3 * i] = d0; ray_d[3 * i + 1] = d1; ray_d[3 * i + 2] = d2;
+	ray_img[i] = img; ray_uv[2 * i] = uu; ray_uv[2 * i + 1] = vv; ray_pdf[i] = img_pdf * uv_pdf;
 	// slab test against the render box
 	float tmin = -1e30f, tmax = 1e30f;
 	const float oo[3] = {c[9], c[10], c[11]}, dd[3] = {d0, d1, d2};
@@ -214,7 +305,8 @@ __device__ __forceinline__ float warp_incl_prod(float v, uint32_t lane) {
 __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32_t n_rays_total, const uint32_t* __restrict__ numsteps_in, const uint32_t* __restrict__ base_in,
 	const float4* __restrict__ coords, const __half* __restrict__ out, const __half* __restrict__ density_out, const float* __restrict__ ray_target,
 	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, float l1_reg_density, __half* __restrict__ d_out, float* __restrict__ d_sigma,
-	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc) {
+	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc, ErrorMapDev E, const uint32_t* __restrict__ ray_img, const float* __restrict__ ray_uv,
+	const float* __restrict__ ray_pdf, int img_w, int img_h) {
 	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const uint32_t lane = threadIdx.x & 31u;
 	if (i >= n_rays) return; // warp-uniform
@@ -254,7 +346,13 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 	if (used_out && lane == 0) used_out[i] = compacted;
 	float gr, gg, gb;
 	const float l = loss_grad(loss_type, ray_target[3 * i], rr, gr) + loss_grad(loss_type, ray_target[3 * i + 1], rg, gg) + loss_grad(loss_type, ray_target[3 * i + 2], rb, gb);
-	if (lane == 0 && numsteps) atomicAdd(loss_acc, l / 3.0f / (float)n_rays_total);
+	if (lane == 0 && numsteps) {
+		// :1061-1106: the REPORTED loss is divided by the sampling pdf (the gradient is not: importance sampling is meant to re-weight the
+		// objective); the same mean loss goes into the error map at the ray's image position
+		const float mean_loss = l / 3.0f / (ray_pdf ? ray_pdf[i] : 1.0f);
+		atomicAdd(loss_acc, mean_loss / (float)n_rays_total);
+		if (E.data && ray_img) error_map_deposit(E.data, E.res[0], E.res[1], img_w, img_h, ray_img[i], ray_uv[2 * i], ray_uv[2 * i + 1], mean_loss);
+	}
 	const float ls = loss_scale / (float)n_rays_total;
 	const float l2_reg = rgb_act == 3 ? 1e-4f : 0.0f;
 	// ---- pass 2: gradients
@@ -478,6 +576,7 @@ void ensure_batch(hn_context* ctx, uint32_t n_rays, uint32_t max_samples) {
 	t.ray_o.ensure((size_t)n_rays * 3); t.ray_d.ensure((size_t)n_rays * 3); t.ray_t.ensure(n_rays);
 	t.ray_target.ensure((size_t)n_rays * 3); t.ray_bg.ensure((size_t)n_rays * 3);
 	t.ray_numsteps.ensure(n_rays); t.ray_base.ensure(n_rays); t.counters.ensure(4); t.loss_acc.ensure(4);
+	t.ray_img.ensure(n_rays); t.ray_uv.ensure((size_t)n_rays * 2); t.ray_pdf.ensure(n_rays);
 	t.coords.ensure(max_samples); t.sample_ray.ensure(max_samples);
 	const uint32_t Hd = ctx->net.density_hidden, Hr = ctx->net.rgb_hidden;
 	if (Hd + Hr + 4 > 12) throw std::runtime_error("training supports at most 8 hidden layers in total");
@@ -486,7 +585,7 @@ void ensure_batch(hn_context* ctx, uint32_t n_rays, uint32_t max_samples) {
 }
 
 // march (samples) -> forward -> loss -> backward into t.grads. Rays are already in t.ray_*.
-void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, uint32_t max_samples, int loss_type, float loss_scale, uint32_t* used_dev) {
+void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, uint32_t max_samples, int loss_type, float loss_scale, uint32_t* used_dev, const ErrorMapDev* emap = nullptr) {
 	TrainState& t = ctx->train;
 	cudaStream_t s = ctx->stream;
 	const NetCfg& net = ctx->net;
@@ -556,7 +655,8 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	__half* g_out = t.dact[0].p;               // [n][16]
 	float* d_sigma = (float*)t.dact[3].p;      // [n] fp32 (buffer holds n*64 halfs)
 	train_loss_kernel<<<blocks((size_t)n_rays * 32, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
-		loss_type, loss_scale, a.rgb_act, a.density_act, ctx->density_grid_mean < 0.01f ? 1e-4f : 0.0f, g_out, d_sigma, used_dev, t.loss_acc.p);
+		loss_type, loss_scale, a.rgb_act, a.density_act, ctx->density_grid_mean < 0.01f ? 1e-4f : 0.0f, g_out, d_sigma, used_dev, t.loss_acc.p,
+		emap ? *emap : ErrorMapDev{}, emap ? t.ray_img.p : nullptr, emap ? t.ray_uv.p : nullptr, emap ? t.ray_pdf.p : nullptr, t.img_w, t.img_h);
 	ev.stop(t.ms[2]);
 	// ---- backward
 	ev.start();
@@ -615,6 +715,38 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	HN_CUDA(cudaGetLastError());
 }
 
+// image CDF on the host from the per-image sums (:3052-3067): MIN_PMF = 0.1 of the mass stays uniform
+void image_cdf_host(std::vector<float>& cdf /* in: unnormalised per-image mass, out: cdf */, std::vector<float>& pmf) {
+	pmf = cdf;
+	float cum = 0;
+	for (float& f : cdf) { cum += f; f = cum; }
+	const float norm = 1.0f / cum;
+	const float n = (float)cdf.size();
+	for (size_t i = 0; i < cdf.size(); ++i) {
+		pmf[i] = (1.0f - 0.1f) * pmf[i] * norm + 0.1f / n;
+		cdf[i] = (1.0f - 0.1f) * cdf[i] * norm + 0.1f * (float)(i + 1) / n;
+	}
+}
+void launch_error_cdfs(uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, std::vector<float>& pmf, cudaStream_t s) {
+	const dim3 threads(16, 8, 1), grid((height + 15) / 16, (n_images + 7) / 8, 1);
+	construct_cdf_2d_kernel<<<grid, threads, 0, s>>>(n_images, height, width, data, cdf_x_cond_y, cdf_y);
+	construct_cdf_1d_kernel<<<blocks(n_images), 256, 0, s>>>(n_images, height, cdf_y, cdf_img);
+	std::vector<float> cdf(n_images);
+	HN_CUDA(cudaMemcpyAsync(cdf.data(), cdf_img, n_images * sizeof(float), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	image_cdf_host(cdf, pmf);
+	HN_CUDA(cudaMemcpyAsync(cdf_img, cdf.data(), n_images * sizeof(float), cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaStreamSynchronize(s)); // `cdf` lives on this stack frame
+}
+void build_error_cdfs(hn_context* ctx) {
+	TrainState& t = ctx->train;
+	t.cdf_res[0] = t.err_res[0]; t.cdf_res[1] = t.err_res[1];
+	const size_t n_cells = (size_t)t.cdf_res[0] * t.cdf_res[1] * t.n_images;
+	t.cdf_x_cond_y.ensure(n_cells); t.cdf_y.ensure((size_t)t.cdf_res[1] * t.n_images); t.cdf_img.ensure(t.n_images);
+	launch_error_cdfs(t.n_images, (uint32_t)t.cdf_res[1], (uint32_t)t.cdf_res[0], t.error_map.p, t.cdf_x_cond_y.p, t.cdf_y.p, t.cdf_img.p, t.pmf_img, ctx->stream);
+	t.cdf_valid = true;
+}
+
 void check_ready(hn_context* ctx, bool need_dataset) {
 	if (!ctx->has_net || !ctx->has_params) throw std::runtime_error("training needs a network config and parameters");
 	if (!ctx->has_bitfield) throw std::runtime_error("training needs an occupancy grid (hn_set_density_grid)");
@@ -650,6 +782,7 @@ void train_init(hn_context* ctx, uint32_t seed) {
 	HN_CUDA(cudaMemsetAsync(t.param_steps.p, 0, n * sizeof(uint32_t), s));
 	HN_CUDA(cudaStreamSynchronize(s));
 	t.seed = seed; t.step = 0; t.ema_step = 0; t.rays_per_batch = 4096; t.loss_last = 0.f;
+	t.n_steps_since_error_map_update = 0; t.n_steps_between_error_map_updates = 128; t.cdf_valid = false; // Testbed::reset_network, src/testbed.cu:3857-3860
 	t.ready = true;
 }
 
@@ -678,9 +811,31 @@ void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
 	FrameArgs a = train_frame_args(ctx);
 	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
 	const float* bg = ctx->opt.background_color;
+	// error map: a fresh, zeroed map whenever a new accumulation period starts (train_nerf, src/testbed_nerf.cu:2986-2992); each rank keeps its own
+	if (t.n_steps_since_error_map_update == 0) {
+		const uint32_t n_samples_per_image = (uint32_t)(((uint64_t)t.n_steps_between_error_map_updates * t.rays_per_batch) / t.n_images);
+		const int r = (int)(std::sqrt(std::sqrt((float)n_samples_per_image)) * 3.5f);
+		t.err_res[0] = std::max(std::min(r, t.img_w), 2); t.err_res[1] = std::max(std::min(r, t.img_h), 2);
+		const size_t n_cells = (size_t)t.err_res[0] * t.err_res[1] * t.n_images;
+		t.error_map.ensure(n_cells);
+		HN_CUDA(cudaMemsetAsync(t.error_map.p, 0, n_cells * sizeof(float), s));
+	}
+	ErrorMapDev E = {};
+	E.data = t.error_map.p; E.res[0] = t.err_res[0]; E.res[1] = t.err_res[1];
+	if (t.cdf_valid) {
+		E.cdf_res[0] = t.cdf_res[0]; E.cdf_res[1] = t.cdf_res[1];
+		if (c.sample_focal_plane_proportional_to_error) { E.cdf_x_cond_y = t.cdf_x_cond_y.p; E.cdf_y = t.cdf_y.p; }
+		if (c.sample_image_proportional_to_error) E.cdf_img = t.cdf_img.p;
+	}
 	train_raygen_kernel<<<blocks(n_rays), 256, 0, s>>>(D, a, n_rays, rank * n_rays, n_rays * world, t.seed, t.step, c.random_bg, t.srgb_space, bg[0], bg[1], bg[2],
-		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p);
-	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr);
+		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p, E, t.ray_img.p, t.ray_uv.p, t.ray_pdf.p);
+	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr, &E);
+	// CDFs from the error map every n_steps_between_error_map_updates steps, then a 1.5x longer period (:3023-3075)
+	if (++t.n_steps_since_error_map_update >= t.n_steps_between_error_map_updates) {
+		build_error_cdfs(ctx);
+		t.n_steps_since_error_map_update = 0;
+		t.n_steps_between_error_map_updates = (uint32_t)(t.n_steps_between_error_map_updates * 1.5f);
+	}
 	float loss = 0.f;
 	HN_CUDA(cudaMemcpyAsync(&loss, t.loss_acc.p, sizeof(float), cudaMemcpyDeviceToHost, s));
 	HN_CUDA(cudaStreamSynchronize(s));
@@ -811,6 +966,99 @@ void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const f
 	HN_CUDA(cudaMemcpy(t.ema.p, t.master.p, n * sizeof(float), cudaMemcpyDeviceToDevice)); // accumulator = weights, debias 1
 	t.step = step;
 	t.ema_step = 1u << 20; // 1 - decay^step == 1: the restored accumulator is already debiased
+}
+
+// ---- error-map operators (test entry points: the same device functions the training kernels call) ----
+namespace {
+__global__ void op_sample_pixels_kernel(uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images, ErrorMapDev E,
+	uint32_t* __restrict__ img_out, float* __restrict__ uv_out, float* __restrict__ pdf_out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_rays) return;
+	const uint32_t gi = i + ray_offset;
+	Pcg32 rng((uint64_t)seed + ((uint64_t)step << 32));
+	rng.advance((uint64_t)gi * 16u);
+	float img_pdf = 1.0f, uv_pdf = 1.0f;
+	const uint32_t img = train_image_idx(gi, n_rays_total, n_images, E.cdf_img, img_pdf);
+	float u = rng.next_float(), v = rng.next_float();
+	if (E.cdf_x_cond_y) train_sample_cdf_2d(u, v, img, E.cdf_res[0], E.cdf_res[1], E.cdf_x_cond_y, E.cdf_y, uv_pdf);
+	img_out[i] = img; uv_out[2 * i] = u; uv_out[2 * i + 1] = v; pdf_out[i] = img_pdf * uv_pdf;
+}
+__global__ void op_deposit_kernel(uint32_t n, const uint32_t* __restrict__ img, const float* __restrict__ uv, const float* __restrict__ val, int res_x, int res_y, int img_w, int img_h, float* __restrict__ map) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) error_map_deposit(map, res_x, res_y, img_w, img_h, img[i], uv[2 * i], uv[2 * i + 1], val[i]);
+}
+template <typename T> struct Tmp { // scoped device buffer of the operator entry points
+	T* p = nullptr;
+	explicit Tmp(size_t n) { if (n) HN_CUDA(cudaMalloc((void**)&p, n * sizeof(T))); }
+	~Tmp() { if (p) cudaFree(p); }
+	Tmp(const Tmp&) = delete; Tmp& operator=(const Tmp&) = delete;
+};
+} // namespace
+
+void train_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img) {
+	if (!n_images || !height || !width || !data) throw std::runtime_error("bad error-map arguments");
+	cudaStream_t s = ctx->stream;
+	const size_t n = (size_t)n_images * height * width;
+	Tmp<float> d_data(n), d_x(n), d_y((size_t)n_images * height), d_i(n_images);
+	HN_CUDA(cudaMemcpyAsync(d_data.p, data, n * sizeof(float), cudaMemcpyHostToDevice, s));
+	std::vector<float> pmf;
+	launch_error_cdfs(n_images, height, width, d_data.p, d_x.p, d_y.p, d_i.p, pmf, s);
+	if (cdf_x_cond_y) HN_CUDA(cudaMemcpyAsync(cdf_x_cond_y, d_x.p, n * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (cdf_y) HN_CUDA(cudaMemcpyAsync(cdf_y, d_y.p, (size_t)n_images * height * sizeof(float), cudaMemcpyDeviceToHost, s));
+	if (cdf_img) HN_CUDA(cudaMemcpyAsync(cdf_img, d_i.p, n_images * sizeof(float), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	if (pmf_img) std::copy(pmf.begin(), pmf.end(), pmf_img);
+	HN_CUDA(cudaGetLastError());
+}
+void train_op_sample_pixels(hn_context* ctx, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images, int cdf_res_x, int cdf_res_y,
+	const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img, float* uv, float* pdf) {
+	if (!n_rays || !n_images || !n_rays_total) throw std::runtime_error("bad sampling arguments");
+	if ((cdf_x_cond_y != nullptr) != (cdf_y != nullptr)) throw std::runtime_error("cdf_x_cond_y and cdf_y come together");
+	cudaStream_t s = ctx->stream;
+	const size_t n = cdf_x_cond_y ? (size_t)n_images * cdf_res_x * cdf_res_y : 0;
+	Tmp<float> d_x(n), d_y(cdf_y ? (size_t)n_images * cdf_res_y : 0), d_i(cdf_img ? n_images : 0), d_uv((size_t)n_rays * 2), d_pdf(n_rays);
+	Tmp<uint32_t> d_img(n_rays);
+	if (cdf_x_cond_y) {
+		HN_CUDA(cudaMemcpyAsync(d_x.p, cdf_x_cond_y, n * sizeof(float), cudaMemcpyHostToDevice, s));
+		HN_CUDA(cudaMemcpyAsync(d_y.p, cdf_y, (size_t)n_images * cdf_res_y * sizeof(float), cudaMemcpyHostToDevice, s));
+	}
+	if (cdf_img) HN_CUDA(cudaMemcpyAsync(d_i.p, cdf_img, n_images * sizeof(float), cudaMemcpyHostToDevice, s));
+	ErrorMapDev E = {};
+	E.cdf_x_cond_y = d_x.p; E.cdf_y = d_y.p; E.cdf_img = d_i.p; E.cdf_res[0] = cdf_res_x; E.cdf_res[1] = cdf_res_y;
+	op_sample_pixels_kernel<<<blocks(n_rays), 256, 0, s>>>(n_rays, ray_offset, n_rays_total, seed, step, n_images, E, d_img.p, d_uv.p, d_pdf.p);
+	HN_CUDA(cudaMemcpyAsync(img, d_img.p, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaMemcpyAsync(uv, d_uv.p, (size_t)n_rays * 8, cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaMemcpyAsync(pdf, d_pdf.p, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	HN_CUDA(cudaGetLastError());
+}
+void train_op_error_map_deposit(hn_context* ctx, uint32_t n, const uint32_t* img, const float* uv, const float* val, uint32_t n_images, int res_x, int res_y, int img_w, int img_h, float* map) {
+	if (!n || !n_images || res_x < 2 || res_y < 2 || img_w < 2 || img_h < 2) throw std::runtime_error("bad error-map arguments");
+	for (uint32_t i = 0; i < n; ++i) if (img[i] >= n_images) throw std::runtime_error("image index out of range");
+	cudaStream_t s = ctx->stream;
+	const size_t cells = (size_t)n_images * res_x * res_y;
+	Tmp<float> d_map(cells), d_uv((size_t)n * 2), d_val(n);
+	Tmp<uint32_t> d_img(n);
+	HN_CUDA(cudaMemsetAsync(d_map.p, 0, cells * sizeof(float), s));
+	HN_CUDA(cudaMemcpyAsync(d_img.p, img, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(d_uv.p, uv, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+	HN_CUDA(cudaMemcpyAsync(d_val.p, val, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+	op_deposit_kernel<<<blocks(n), 256, 0, s>>>(n, d_img.p, d_uv.p, d_val.p, res_x, res_y, img_w, img_h, d_map.p);
+	HN_CUDA(cudaMemcpyAsync(map, d_map.p, cells * sizeof(float), cudaMemcpyDeviceToHost, s));
+	HN_CUDA(cudaStreamSynchronize(s));
+	HN_CUDA(cudaGetLastError());
+}
+// m_nerf.training.error_map.{resolution, data} (the "Training view error" overlays of the reference GUI read these)
+void train_get_error_map(hn_context* ctx, int res[2], uint32_t* n_images, float* data, size_t n_floats) {
+	TrainState& t = ctx->train;
+	res[0] = t.err_res[0]; res[1] = t.err_res[1];
+	if (n_images) *n_images = t.n_images;
+	if (!data) return;
+	const size_t n = (size_t)t.err_res[0] * t.err_res[1] * t.n_images;
+	if (!n || !t.error_map.p) throw std::runtime_error("no error map yet (train at least one step)");
+	if (n_floats < n) throw std::runtime_error("error map buffer too small");
+	HN_CUDA(cudaMemcpyAsync(data, t.error_map.p, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	HN_CUDA(cudaStreamSynchronize(ctx->stream));
 }
 
 void train_release(hn_context* ctx) {

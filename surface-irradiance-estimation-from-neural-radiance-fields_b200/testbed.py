@@ -73,6 +73,7 @@ EXPORTS = [
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
+    "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -100,6 +101,10 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_get_error_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+_lib.hn_op_error_map_cdf.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5
+_lib.hn_op_sample_training_pixels.argtypes = [C.c_void_p] + [C.c_uint32] * 6 + [C.c_int, C.c_int] + [C.c_void_p] * 6
+_lib.hn_op_error_map_deposit.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
 _lib.hn_op_encode_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_network.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
 _lib.hn_op_trace.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 5
@@ -506,6 +511,42 @@ class Testbed:
         self._check(_lib.hn_op_train_gradients(self._h, n, _ptr(o), _ptr(d), _ptr(t), _ptr(tg), _ptr(bg), int(loss_type), float(loss_scale),
                                                C.byref(loss), _ptr(grads), _ptr(steps)))
         return float(loss.value), grads, steps
+
+    # ---- error map (m_nerf.training.error_map; nerf.h:104-118)
+    def error_map(self):
+        """-> float32 [n_images][res_y][res_x]: mean training loss deposited where the rays of the current accumulation period landed"""
+        res = (C.c_int * 2)()
+        n = C.c_uint32(0)
+        self._check(_lib.hn_get_error_map(self._h, res, C.byref(n), None, 0))
+        out = np.empty((int(n.value), int(res[1]), int(res[0])), np.float32)
+        self._check(_lib.hn_get_error_map(self._h, res, C.byref(n), _ptr(out), out.size))
+        return out
+
+    def op_error_map_cdf(self, data):
+        d = _f32(data)
+        assert d.ndim == 3
+        n, h, w = d.shape
+        cx, cy, ci, pi = np.empty_like(d), np.empty((n, h), np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        self._check(_lib.hn_op_error_map_cdf(self._h, n, h, w, _ptr(d), _ptr(cx), _ptr(cy), _ptr(ci), _ptr(pi)))
+        return cx, cy, ci, pi
+
+    def op_sample_training_pixels(self, n_rays, n_images, seed=1337, step=0, ray_offset=0, n_rays_total=None, cdf_x_cond_y=None, cdf_y=None, cdf_img=None):
+        total = int(n_rays_total if n_rays_total is not None else n_rays)
+        cx = _f32(cdf_x_cond_y) if cdf_x_cond_y is not None else None
+        cy = _f32(cdf_y) if cdf_y is not None else None
+        ci = _f32(cdf_img) if cdf_img is not None else None
+        rx, ry = (cx.shape[2], cx.shape[1]) if cx is not None else (0, 0)
+        img, uv, pdf = np.empty(n_rays, np.uint32), np.empty((n_rays, 2), np.float32), np.empty(n_rays, np.float32)
+        self._check(_lib.hn_op_sample_training_pixels(self._h, int(n_rays), int(ray_offset), total, int(seed), int(step), int(n_images), rx, ry,
+                                                      _ptr(cx) if cx is not None else None, _ptr(cy) if cy is not None else None, _ptr(ci) if ci is not None else None,
+                                                      _ptr(img), _ptr(uv), _ptr(pdf)))
+        return img, uv, pdf
+
+    def op_error_map_deposit(self, img, uv, val, n_images, res, image_res):
+        i, u, v = np.ascontiguousarray(img, np.uint32).reshape(-1), _f32(uv).reshape(-1, 2), _f32(val).reshape(-1)
+        out = np.empty((int(n_images), int(res[1]), int(res[0])), np.float32)
+        self._check(_lib.hn_op_error_map_deposit(self._h, i.size, _ptr(i), _ptr(u), _ptr(v), int(n_images), int(res[0]), int(res[1]), int(image_res[0]), int(image_res[1]), _ptr(out)))
+        return out
 
     # ---- a-16 environment map (Testbed::m_envmap, testbed.h:1227-1241)
     def set_envmap(self, rgba: np.ndarray | None):

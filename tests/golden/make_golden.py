@@ -217,6 +217,49 @@ def make_ref_lens():
     print("ref_host_lens.npz:", len(out), "arrays")
 
 
+def make_ref_cdf():
+    """binary_search / sample_cdf_2d / image_idx of the reference (common.h:242-264, nerf_device.cuh:538-568,617-639) -> ref_host_cdf.npz.
+    The CDFs fed to them are committed in the file (built by the oracle from a seeded error map), so the test needs nothing else."""
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_sample_cdf_2d"):
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing or stale: run `make -C oracle ref`")
+    ref.ref_binary_search.restype = C.c_uint32
+    ref.ref_image_idx.restype = C.c_uint32
+    rng = np.random.default_rng(20261107)
+    n_img, h, w = 3, 12, 16
+    data = (rng.random((n_img, h, w)) ** 4).astype(f32)
+    data[1, 3:5, 10:13] += 5.0      # a hot spot
+    data[2] *= 0.05                 # an image with little error
+    data[0, 7] = 0.0                # an empty row
+    cx, cy, ci, pi = orc.error_map_cdf(data)
+    n = 512
+    samples = rng.random((n, 2)).astype(f32)
+    samples[:6] = [[0.0, 0.0], [0.5, 0.0], [0.49999997, 0.3], [0.99999994, 0.99999994], [0.75, 0.5], [0.5, 0.99999994]]
+    out = {"data": data, "cdf_x_cond_y": cx, "cdf_y": cy, "cdf_img": ci, "samples": samples}
+    for img in range(n_img):
+        uv = np.zeros((n, 2), f32); pdf = np.zeros(n, f32)
+        for i in range(n):
+            s = (C.c_float * 2)(*samples[i]); p = C.c_float(0)
+            ref.ref_sample_cdf_2d(s, C.c_uint32(img), w, h, P(cx), P(cy), C.byref(p))
+            uv[i] = s[:]; pdf[i] = p.value
+        out[f"uv_{img}"], out[f"pdf_{img}"] = uv, pdf
+    vals = np.concatenate([rng.random(200).astype(f32), ci, np.array([0.0, 1.0, 2.0, -1.0], f32), cy[1][:5]])
+    out["bs_vals"] = vals
+    out["bs_img"] = np.array([ref.ref_binary_search(C.c_float(v), P(ci), C.c_uint32(n_img)) for v in vals], np.uint32)
+    out["bs_row"] = np.array([ref.ref_binary_search(C.c_float(v), P(cy[1]), C.c_uint32(h)) for v in vals], np.uint32)
+    base = np.concatenate([np.arange(300), rng.integers(0, 2 ** 31, 100)]).astype(np.uint32)
+    out["ii_base"] = base
+    for tag, cdf in (("cdf", ci), ("none", None)):
+        ii = np.zeros(base.size, np.uint32); pp = np.zeros(base.size, f32)
+        for k, b in enumerate(base):
+            p = C.c_float(0)
+            ii[k] = ref.ref_image_idx(C.c_uint32(int(b)), C.c_uint32(4096), C.c_uint32(n_img), P(cdf) if cdf is not None else None, C.byref(p))
+            pp[k] = p.value
+        out[f"ii_img_{tag}"], out[f"ii_pdf_{tag}"] = ii, pp
+    np.savez_compressed(os.path.join(HERE, "ref_host_cdf.npz"), **out)
+    print("ref_host_cdf.npz:", len(out), "arrays")
+
+
 def make_ref_tri():
     """Triangle::distance_sq / closest_point (triangle.cuh:66-147) of the reference, host-callable -> ref_host_tri.npz"""
     ref = orc.ref
@@ -297,7 +340,10 @@ if __name__ == "__main__":
         make_ref_lens()
     elif len(sys.argv) > 1 and sys.argv[1] == "tri":
         make_ref_tri()
+    elif len(sys.argv) > 1 and sys.argv[1] == "cdf":
+        make_ref_cdf()
     else:
+        make_ref_cdf()
         make_ref_tri()
         make_ref_lens()
         make_ref_host()

@@ -431,3 +431,52 @@ def render_reference_frame(tb, params, grid, n_cascades, meshes, cam, w, h, mesh
     out[..., 3] = out[..., 3] + (1.0 - out[..., 3]) * 1.0
     out = np.clip(out, 0.0, 1.0)
     return out, depth, steps
+
+
+# ---- training error map (oracle/orc_errmap.inc)
+def binary_search(val, data):
+    d = np.ascontiguousarray(data, np.float32)
+    lib.orc_binary_search.restype = C.c_uint32
+    return int(lib.orc_binary_search(C.c_float(val), P(d), u32(d.size)))
+
+
+def image_idx(base_idx, n_rays, n_images, cdf=None):
+    pdf = C.c_float(0)
+    c = np.ascontiguousarray(cdf, np.float32) if cdf is not None else None
+    lib.orc_image_idx.restype = C.c_uint32
+    img = lib.orc_image_idx(u32(base_idx), u32(n_rays), u32(n_images), P(c) if c is not None else None, C.byref(pdf))
+    return int(img), float(pdf.value)
+
+
+def sample_cdf_2d(sample, img, cdf_x_cond_y, cdf_y):
+    cx, cy = np.ascontiguousarray(cdf_x_cond_y, np.float32), np.ascontiguousarray(cdf_y, np.float32)
+    s = np.array(sample, np.float32); pdf = C.c_float(0)
+    lib.orc_sample_cdf_2d(P(s), u32(img), C.c_int32(cx.shape[2]), C.c_int32(cx.shape[1]), P(cx), P(cy), C.byref(pdf))
+    return s, float(pdf.value)
+
+
+def error_map_cdf(data):
+    d = np.ascontiguousarray(data, np.float32)
+    n, h, w = d.shape
+    cx, cy, ci, pi = np.empty_like(d), np.empty((n, h), np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+    lib.orc_error_map_cdf(u32(n), u32(h), u32(w), P(d), P(cx), P(cy), P(ci), P(pi))
+    return cx, cy, ci, pi
+
+
+def sample_training_pixels(n_rays, n_images, seed=1337, step=0, ray_offset=0, n_rays_total=None, cdf_x_cond_y=None, cdf_y=None, cdf_img=None):
+    total = n_rays if n_rays_total is None else n_rays_total
+    cx = np.ascontiguousarray(cdf_x_cond_y, np.float32) if cdf_x_cond_y is not None else None
+    cy = np.ascontiguousarray(cdf_y, np.float32) if cdf_y is not None else None
+    ci = np.ascontiguousarray(cdf_img, np.float32) if cdf_img is not None else None
+    rx, ry = (cx.shape[2], cx.shape[1]) if cx is not None else (0, 0)
+    img, uv, pdf = np.empty(n_rays, np.uint32), np.empty((n_rays, 2), np.float32), np.empty(n_rays, np.float32)
+    lib.orc_sample_training_pixels(u32(n_rays), u32(ray_offset), u32(total), u32(seed), u32(step), u32(n_images), C.c_int32(rx), C.c_int32(ry),
+                                   P(cx) if cx is not None else None, P(cy) if cy is not None else None, P(ci) if ci is not None else None, P(img), P(uv), P(pdf))
+    return img, uv, pdf
+
+
+def error_map_deposit(img, uv, val, n_images, res, image_res):
+    i, u, v = np.ascontiguousarray(img, np.uint32).reshape(-1), np.ascontiguousarray(uv, np.float32).reshape(-1, 2), np.ascontiguousarray(val, np.float32).reshape(-1)
+    out = np.zeros((n_images, res[1], res[0]), np.float32)
+    lib.orc_error_map_deposit(u32(i.size), P(i), P(u), P(v), C.c_int32(res[0]), C.c_int32(res[1]), C.c_int32(image_res[0]), C.c_int32(image_res[1]), P(out))
+    return out

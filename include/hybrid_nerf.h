@@ -78,6 +78,26 @@ int hn_get_scene_aabb(const hn_context* ctx, float out[6]);                     
  * rgba == NULL removes the map. */
 int hn_set_envmap(hn_context* ctx, const float* rgba, int width, int height);
 
+/* ---- VR pieces of uv_to_ray (common_device.cuh:117-246,416-483) and the 2-D render modes ----
+ * option "foveation"[6] = Foveation(center_pixel_steepness xy, center_inverse_piecewise_y xy, center_radius xy) of the view
+ * (Testbed::m_views[i].foveation, src/testbed.cu:3150-3164); all zero = none. Camera rays of the NeRF pass and of the mesh pass are
+ * generated at foveation.warp(uv); the frame that comes out is the WARPED one, hn_unwarp_foveated resamples it.
+ * hn_set_hidden_area_mask: render_buffer.hidden_area_mask (uint8 [height][width], 0 = no ray for that pixel); NULL removes it.
+ * hn_set_distortion_map: m_distortion.inference_view() with m_nerf.render_with_lens_distortion (vec2 [height][width], added to the
+ * camera-space direction of NeRF rays, bilinear); NULL removes it.
+ * render_mode 8 (Distortion, src/testbed_nerf.cu:1513-1521) and 10 (Slice, :1500-1510,2431-2459; plane at camera depth "focus_z" =
+ * m_slice_plane_z + m_scale) are 2-D modes of the NeRF pass: every valid pixel is shaded at once, nothing is traced. */
+int hn_set_hidden_area_mask(hn_context* ctx, const uint8_t* mask, int width, int height);
+int hn_set_distortion_map(hn_context* ctx, const float* grid, int width, int height);
+/* Testbed::blit_texture + its fragment shader (src/testbed.cu:2600-2640,2664-2720) as a CUDA kernel: output pixel centre uv ->
+ * foveation.unwarp(uv) -> bilinear fetch of the rendered (warped) frame / depth (device pointers; depth may be NULL). The GL y flip
+ * of the shader is a window-system convention and is left out; the GL path itself is unavailable on this box. */
+int hn_unwarp_foveated(hn_context* ctx, const float foveation[6], int width_in, int height_in, const float* frame_in_dev, const float* depth_in_dev,
+	int width_out, int height_out, float* frame_out_dev, float* depth_out_dev, void* cuda_stream);
+/* FoveationPiecewiseQuadratic's constructor (common_device.cuh:119-182) as the library runs it on the host: coefficients [2][12] =
+ * al bl cl am bm ar br cr switch_left switch_right inv_switch_left inv_switch_right per axis */
+int hn_op_foveation(hn_context* ctx, const float foveation[6], float coeffs[24]);
+
 /* a-16 irradiance probes. What the reference ships of this path: the probe ray set-up NerfTracer::init_rays_from_center /
  * init_rays_from_center_outward / init_rays_from_multiple_center (src/testbed_nerf.cu:1924-2019, kernels :1559-1773,
  * cylindrical_to_dir_nerf :1546-1557, halton<2/3/5> random_val.cuh:338-350) and NerfTracer::trace_mesh (:2146-2262: t = 0, no start

@@ -75,6 +75,14 @@ typedef struct {
 	// the direction to the bounding sphere of the NeRF box (train_aabb)
 	int32_t env_source, env_sampling, probe_n_theta, probe_n_phi;
 	const float* probe;
+	// VR / 2-D pieces of uv_to_ray (common_device.cuh:117-246,416-483): foveation = center_pixel_steepness xy, center_inverse_piecewise_y xy,
+	// center_radius xy (all zero = none); hidden-area mask uint8 [hidden_h][hidden_w] (NULL = none, 0 = hidden); distortion grid of vec2
+	// [distortion_h][distortion_w][2] (NULL = none, NeRF rays only). render_mode 8 = Distortion, 10 = Slice (plane at camera depth focus_z).
+	float foveation[6];
+	int32_t hidden_w, hidden_h;
+	const uint8_t* hidden_area_mask;
+	int32_t distortion_w, distortion_h;
+	const float* distortion;
 } orc_render_params;
 
 // ---- scalar pieces (pinned against oracle/_ref) ----
@@ -91,6 +99,11 @@ float orc_srgb_to_linear(float v);
 // ---- a-16 sampling helpers (random_val.cuh:62-72,130-185; pinned against oracle/_ref) and the envmap lookup ----
 // uv_to_ray with the lens / depth-of-field / parallax fields of p (direction not normalised); returns 0 for an invalid ray
 int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]);
+// foveation pieces and the 2-D helpers (orc_fov.inc): coefficients [2][12] (al bl cl am bm ar br cr switch_left switch_right inv_switch_left inv_switch_right)
+void orc_foveation_coeffs(const float f[6], float out[24]);
+void orc_foveation_warp(const float f[6], const float uv[2], float warped[2], float unwarped[2], float* density);
+void orc_pos_to_uv(const orc_render_params* p, const float pos[3], float out[2]);
+void orc_to_rgb(const float dir[2], float out[3]);
 // tonemap_kernel (src/render_buffer.cu:529-560) on a linear accumulation buffer; curve = ETonemapCurve (0 Identity, 1 ACES, 2 Hable, 3 Reinhard)
 float orc_density_input_gradient(const orc_net_config* c, const uint16_t* params, const float wp[3], float grad[3]);
 float orc_density_raw_f32(const orc_net_config* c, const uint16_t* params, const float wp[3]);

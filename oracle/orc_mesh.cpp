@@ -247,8 +247,12 @@ static void render_mesh(const orc_scene& s, const orc_render_params& p, float* f
 			// :488-579 init_rays_with_payload_kernel_mesh_geometry (pixel_to_ray: no rolling shutter, camera_matrix as is)
 			vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
 			vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
-			Ray ray = uv_to_ray(p, p.spp, uv, cam, false, nullptr); // no Lens on this ray init (:520-536); parallax shift + depth of field apply
+			bool valid = true;
+			Ray ray = uv_to_ray(p, p.spp, uv, cam, false, &valid); // no Lens on this ray init (:520-536); foveation, hidden-area mask, parallax shift + depth of field apply
 			depth[idx] = MAX_DEPTH;
+			// a pixel the hidden-area mask hides: the reference marks the payload dead (:544-551) and still pushes its zero ray through the
+			// trace / shade kernels (colour undefined); here such a pixel simply stays cleared
+			if (!valid) continue;
 			ray.d = normalize(ray.d);
 			float t0 = std::max(aabb.ray_intersect(ray.o, ray.d).x, 0.0f);
 			vec3 pos = ray.o + (t0 + 1e-6f) * ray.d;

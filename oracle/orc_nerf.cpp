@@ -180,14 +180,34 @@ static vec2 square2disk_shirley(vec2 sq) {
 	return {r * std::cos(phi), r * std::sin(phi)};
 }
 
-// common_device.cuh:416-483 uv_to_ray without foveation / hidden-area mask / distortion grid (VR only) — direction not
-// normalised; valid = false for an f-theta pixel outside the image circle. lens_mode follows ELensMode (common.h:223-230).
-Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& cam, bool use_lens, bool* valid) {
+#include "orc_fov.inc"
+static vec2 pos_to_uv(vec3 pos, int w, int h, vec2 focal, const cam_t& cam, vec2 sc, const float parallax[3], const Fov& fov, int lens_mode, const float* lp) {
+	vec3 head_pos = {parallax[0], parallax[1], 0.0f};
+	mat3 m = {{cam.c[0], cam.c[1], cam.c[2]}};
+	vec3 origin = mul(m, head_pos) + cam.c[3];
+	vec3 dir = pos - origin;
+	dir = mul(inverse3(m), dir);
+	dir = dir / dir.z;
+	dir = dir + head_pos * parallax[2];
+	float du = 0.0f, dv = 0.0f;
+	if (lens_mode == 1) opencv_distortion_delta(lp, dir.x, dir.y, &du, &dv);
+	else if (lens_mode == 4) fisheye_distortion_delta(lp, dir.x, dir.y, &du, &dv);
+	dir.x += du; dir.y += dv;
+	vec2 uv = {dir.x * focal.x / (float)w + sc.x, dir.y * focal.y / (float)h + sc.y};
+	return fov.unwarp(uv);
+}
+
+// common_device.cuh:416-483 uv_to_ray - direction not normalised; valid = false for an f-theta pixel outside the image circle or a
+// pixel the hidden-area mask hides. lens_mode follows ELensMode (common.h:223-230). The mesh pass (use_lens = false) takes
+// foveation and the mask but neither Lens nor distortion grid (src/testbed_geometry_training.cu:520-536).
+Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv_in, const cam_t& cam, bool use_lens, bool* valid) {
 	const int w = p.width, h = p.height;
 	const vec2 focal = {p.focal[0], p.focal[1]}, sc = {p.screen_center[0], p.screen_center[1]};
 	const int mode = use_lens ? p.lens_mode : 0;
 	const float* lp = p.lens_params;
 	if (valid) *valid = true;
+	const vec2 uv = Fov(p.foveation).warp(uv_in); // warped_uv; the depth-of-field pixel hash below keeps the un-warped uv (:470)
+	if (p.hidden_area_mask && !mask_at(p.hidden_area_mask, p.hidden_w, p.hidden_h, uv)) { if (valid) *valid = false; return {{0, 0, 0}, {0, 0, 0}}; }
 	vec3 dir;
 	if (mode == 2) { // f_theta_undistortion :360-374
 		float xpix = (uv.x - sc.x) * lp[5], ypix = (uv.y - sc.y) * lp[6];
@@ -211,6 +231,7 @@ Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& ca
 		if (mode == 1) iterative_undistortion(lp, &dir.x, &dir.y, opencv_distortion_delta);
 		else if (mode == 4) iterative_undistortion(lp, &dir.x, &dir.y, fisheye_distortion_delta);
 	}
+	if (use_lens && p.distortion) { vec2 dd = grid_at_lerp(p.distortion, p.distortion_w, p.distortion_h, uv); dir.x += dd.x; dir.y += dd.y; }
 	vec3 head_pos = {p.parallax_shift[0], p.parallax_shift[1], 0.0f};
 	dir = dir - head_pos * p.parallax_shift[2];
 	mat3 m = {{cam.c[0], cam.c[1], cam.c[2]}};
@@ -218,7 +239,7 @@ Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& ca
 	vec3 origin = mul(m, head_pos) + cam.c[3];
 	if (p.aperture_size != 0.0f) {
 		vec3 lookat = origin + dir * p.focus_z;
-		int px = (int)(uv.x * (float)w), py = (int)(uv.y * (float)h);
+		int px = (int)(uv_in.x * (float)w), py = (int)(uv_in.y * (float)h);
 		vec2 rnd = ld_random_val_2d(spp, (uint32_t)px * 19349663u + (uint32_t)py * 96925573u);
 		vec2 disk = square2disk_shirley({rnd.x * 2.0f - 1.0f, rnd.y * 2.0f - 1.0f});
 		float bx = p.aperture_size * disk.x, by = p.aperture_size * disk.y;
@@ -233,14 +254,18 @@ Ray uv_to_ray(const orc_render_params& p, uint32_t spp, vec2 uv, const cam_t& ca
 }
 
 // testbed_nerf.cu:1428-1476: uv + per-pixel rolling-shutter camera
-Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y, bool* valid) {
+static void pixel_uv_cam(const orc_render_params& p, uint32_t x, uint32_t y, vec2& uv, cam_t& cam) {
 	uint32_t idx = x + (uint32_t)p.width * y;
 	vec2 off = ld_random_pixel_offset(p.snap_to_pixel_centers ? 0 : p.spp);
-	vec2 uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
+	uv = {((float)x + off.x) / (float)p.width, ((float)y + off.y) / (float)p.height};
 	float mb = ld_random_val(p.spp, idx * 72239731u);
 	const float* rs = p.rolling_shutter;
 	float pixel_t = rs[0] + rs[1] * uv.x + rs[2] * uv.y + rs[3] * mb;
-	cam_t cam = camera_slerp(cam_from(p.cam0), cam_from(p.cam1), pixel_t);
+	cam = camera_slerp(cam_from(p.cam0), cam_from(p.cam1), pixel_t);
+}
+Ray pixel_ray(const orc_render_params& p, uint32_t x, uint32_t y, bool* valid) {
+	vec2 uv; cam_t cam;
+	pixel_uv_cam(p, x, y, uv, cam);
 	return uv_to_ray(p, p.spp, uv, cam, true, valid);
 }
 
@@ -749,6 +774,42 @@ uint64_t render_nerf(const orc_render_params& p, const Net& net, const uint8_t* 
 			uint32_t idx = x + p.width * y;
 			if (n_steps_out) n_steps_out[idx] = 0;
 			if (p.pixel_mask && !p.pixel_mask[idx]) continue;
+			if (p.render_mode == 8 || p.render_mode == 10) { // the 2-D modes never trace (render_nerf :2397-2460): every valid pixel is shaded at once
+				vec2 uv; cam_t cam;
+				pixel_uv_cam(p, x, y, uv, cam);
+				orc_render_params q = p;
+				if (p.render_mode == 10) q.aperture_size = 0.0f; // plane_z < 0 (:1465-1467)
+				bool valid = true;
+				Ray ray = uv_to_ray(q, p.spp, uv, cam, true, &valid);
+				if (depth[idx] < 0.01f) depth[idx] = MAX_DEPTH;
+				if (!valid) continue;
+				float* fb = frame + 4 * (size_t)idx;
+				if (p.render_mode == 10) { // Slice (:1500-1510, 2431-2459): the network at the point where the pixel's ray meets the plane z = focus_z
+					float nlen = length(ray.d);
+					vec3 dir = (1.0f / nlen) * ray.d;
+					float t = p.focus_z * nlen;
+					depth[idx] = p.focus_z;
+					vec3 wp = train_aabb.relative_pos(ray.o + dir * t);
+					vec3 wd = (dir + 1.0f) * 0.5f;
+					float coord[7] = {wp.x, wp.y, wp.z, warp_dt(MIN_CONE_STEPSIZE), wd.x, wd.y, wd.z};
+					half_t out[4];
+					network_one(net, coord, out);
+					row_total += 1;
+					if (n_steps_out) n_steps_out[idx] = 1;
+					// compute_nerf_rgba(depth = 0.01, :408-421) then shade_kernel_nerf (:1361-1401; Slice leaves the depth buffer alone)
+					float alpha = clampf(1.f - std::exp(-network_to_density(h2f(out[3]), p.density_activation) * 0.01f), 0.0f, 1.0f);
+					vec4 tmp = {network_to_rgb(h2f(out[0]), p.rgb_activation) * alpha, network_to_rgb(h2f(out[1]), p.rgb_activation) * alpha, network_to_rgb(h2f(out[2]), p.rgb_activation) * alpha, alpha};
+					if (!p.linear_colors) { tmp.x = srgb_to_linear(tmp.x); tmp.y = srgb_to_linear(tmp.y); tmp.z = srgb_to_linear(tmp.z); }
+					float ia = 1.0f - tmp.w;
+					fb[0] = tmp.x + fb[0] * ia; fb[1] = tmp.y + fb[1] * ia; fb[2] = tmp.z + fb[2] * ia; fb[3] = tmp.w + fb[3] * ia;
+				} else { // Distortion (:1513-1521): where the lens + distortion grid moved the pixel, as a hue
+					vec2 after = pos_to_uv(ray.at(1.0f), p.width, p.height, {p.focal[0], p.focal[1]}, cam, {p.screen_center[0], p.screen_center[1]}, p.parallax_shift, Fov(p.foveation), 0, p.lens_params);
+					vec3 c = dir_to_rgb({(after.x - uv.x) * 64.0f, (after.y - uv.y) * 64.0f});
+					fb[0] = c.x; fb[1] = c.y; fb[2] = c.z; fb[3] = 1.0f;
+					depth[idx] = 1.0f;
+				}
+				continue;
+			}
 			RayState r = init_ray(p, bits, x, y, &depth[idx]);
 			// :1526-1528 envmap -> frame buffer for every valid ray; in hybrid frames only where the mesh pass left nothing
 			if (p.envmap && (r.d.x != 0.0f || r.d.y != 0.0f || r.d.z != 0.0f) && !(depth_test && depth[idx] < MAX_DEPTH)) { // invalid rays return before this (:1494-1498)
@@ -883,6 +944,26 @@ float orc_advance_to_occupied(float t, float cone_angle, const float o[3], const
 float orc_calc_dt(float t, float cone_angle) { return calc_dt(t, cone_angle); }
 float orc_srgb_to_linear(float v) { return srgb_to_linear(v); }
 
+void orc_foveation_coeffs(const float f[6], float out[24]) {
+	Fov fv(f);
+	const FovWarp* w[2] = {&fv.x, &fv.y};
+	for (int k = 0; k < 2; ++k) {
+		float* o = out + 12 * k;
+		o[0] = w[k]->al; o[1] = w[k]->bl; o[2] = w[k]->cl; o[3] = w[k]->am; o[4] = w[k]->bm; o[5] = w[k]->ar; o[6] = w[k]->br; o[7] = w[k]->cr;
+		o[8] = w[k]->switch_left; o[9] = w[k]->switch_right; o[10] = w[k]->inv_switch_left; o[11] = w[k]->inv_switch_right;
+	}
+}
+void orc_foveation_warp(const float f[6], const float uv[2], float warped[2], float unwarped[2], float* density) {
+	Fov fv(f);
+	vec2 a = fv.warp({uv[0], uv[1]}), b = fv.unwarp({uv[0], uv[1]});
+	warped[0] = a.x; warped[1] = a.y; unwarped[0] = b.x; unwarped[1] = b.y; *density = fv.density({uv[0], uv[1]});
+}
+void orc_pos_to_uv(const orc_render_params* p, const float pos[3], float out[2]) {
+	vec2 r = pos_to_uv({pos[0], pos[1], pos[2]}, p->width, p->height, {p->focal[0], p->focal[1]}, cam_from(p->cam0), {p->screen_center[0], p->screen_center[1]},
+		p->parallax_shift, Fov(p->foveation), p->lens_mode, p->lens_params);
+	out[0] = r.x; out[1] = r.y;
+}
+void orc_to_rgb(const float dir[2], float out[3]) { vec3 c = dir_to_rgb({dir[0], dir[1]}); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
 int32_t orc_uv_to_ray(const orc_render_params* p, uint32_t spp, const float uv[2], int32_t use_lens, float out_o[3], float out_d[3]) {
 	bool valid = true;
 	Ray r = uv_to_ray(*p, spp, {uv[0], uv[1]}, cam_from(p->cam0), use_lens != 0, &valid);

@@ -224,7 +224,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 	return {
 		{"snap_to_pixel_centers", {&o.snap_to_pixel_centers, 1, true}}, {"render_near_distance", {&o.near_distance, 1, false}},
 		{"lens_mode", {&o.lens_mode, 1, true}}, {"lens_params", {o.lens_params, 7, false}}, {"aperture_size", {&o.aperture_size, 1, false}},
-		{"focus_z", {&o.focus_z, 1, false}}, {"parallax_shift", {o.parallax_shift, 3, false}},
+		{"focus_z", {&o.focus_z, 1, false}}, {"parallax_shift", {o.parallax_shift, 3, false}}, {"foveation", {o.foveation, 6, false}},
 		{"render_aabb", {o.render_aabb, 6, false}}, {"render_aabb_to_local", {o.render_aabb_to_local, 9, false}}, {"nerf_aabb", {o.train_aabb, 6, false}}, {"max_cascade", {&o.max_cascade, 1, true}},
 		{"cone_angle_constant", {&o.cone_angle_constant, 1, false}}, {"render_min_transmittance", {&o.min_transmittance, 1, false}},
 		{"rgb_activation", {&o.rgb_activation, 1, true}}, {"density_activation", {&o.density_activation, 1, true}},
@@ -311,6 +311,7 @@ void ld_random_pixel_offset(uint32_t spp, float out[2]) {
 	for (int i = 0; i < 2; ++i) { float o = 0.5f - a[i] + b[i]; out[i] = o - std::floor(o); }
 }
 
+bool foveation_coeffs(const float f[6], float out[24]);
 FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12], const float screen_center[2], const float rel_focal[2],
 	const float rolling_shutter[4], uint32_t spp, int w, int h) {
 	const Options& o = ctx->opt;
@@ -330,6 +331,9 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 	for (int i = 0; i < 7; ++i) a.lens_params[i] = o.lens_params[i];
 	a.aperture_size = o.aperture_size; a.focus_z = o.focus_z;
 	for (int i = 0; i < 3; ++i) a.parallax_shift[i] = o.parallax_shift[i];
+	a.foveated = foveation_coeffs(o.foveation, &a.fov[0][0]) ? 1 : 0;
+	a.hidden_mask = ctx->hidden_w > 0 ? ctx->hidden_mask.p : nullptr; a.hidden_w = ctx->hidden_w; a.hidden_h = ctx->hidden_h;
+	a.distortion = ctx->dist_w > 0 ? ctx->distortion.p : nullptr; a.dist_w = ctx->dist_w; a.dist_h = ctx->dist_h;
 	std::memcpy(a.render_aabb, o.render_aabb, 24); std::memcpy(a.train_aabb, o.train_aabb, 24);
 	{
 		static const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
@@ -367,6 +371,47 @@ FrameArgs make_args(hn_context* ctx, const float cam0[12], const float cam1[12],
 		a.env_samples = std::max(o.env_light_samples, 0);
 	}
 	return a;
+}
+
+// FoveationPiecewiseQuadratic's constructor (common_device.cuh:119-182) on the host: 12 coefficients of one axis
+// (al bl cl am bm ar br cr switch_left switch_right inv_switch_left inv_switch_right)
+void foveation_axis(float center_pixel_steepness, float center_inverse_piecewise_y, float center_radius, float c[12]) {
+	const float ident[12] = {0, 0, 0, 1, 0, 0, 0, 0, 0, 1, 0, 1};
+	std::memcpy(c, ident, sizeof(ident));
+	const float center_inverse_radius = center_radius * center_pixel_steepness;
+	float left_inv = center_inverse_piecewise_y - center_inverse_radius, right_inv = center_inverse_piecewise_y + center_inverse_radius;
+	if (left_inv < 0) left_inv = 0.0f;
+	if (right_inv > 1) right_inv = 1.0f;
+	const float am = center_pixel_steepness;
+	const float d = (right_inv - left_inv) / center_pixel_steepness / 2;
+	float bm = 0.0f, m_min = 0.0f, m_max = 1.0f;
+	for (uint32_t i = 0; i < 20; i++) {
+		const float m = (m_min + m_max) / 2.0f;
+		const float l = m - d, r = m + d;
+		bm = -((am - 1) * l * l) / (r * r - 2 * r + l * l + 1);
+		const float l_actual = (left_inv - bm) / am, r_actual = (right_inv - bm) / am;
+		const float m_actual = (l_actual + r_actual) / 2;
+		if (m_actual > m) m_min = m; else m_max = m;
+	}
+	const float l = (left_inv - bm) / am, r = (right_inv - bm) / am;
+	if ((l == 0.0f && r == 1.0f) || (am == 1.0f)) return; // fully linear
+	c[8] = l; c[9] = r;
+	c[3] = am;
+	c[0] = (am - 1) / (r * r - 2 * r + l * l + 1);
+	c[1] = (am * (r * r - 2 * r + 1) + am * l * l + (2 - 2 * am) * l) / (r * r - 2 * r + l * l + 1);
+	c[2] = 0;
+	c[4] = -((am - 1) * l * l) / (r * r - 2 * r + l * l + 1);
+	c[5] = -(am - 1) / (r * r - 2 * r + l * l + 1);
+	c[6] = (am * (r * r + 1) - 2 * r + am * l * l) / (r * r - 2 * r + l * l + 1);
+	c[7] = -(am * r * r - r * r + (am - 1) * l * l) / (r * r - 2 * r + l * l + 1);
+	c[10] = c[3] * c[8] + c[4];
+	c[11] = c[3] * c[9] + c[4];
+}
+bool foveation_coeffs(const float f[6], float out[24]) {
+	const bool on = f[0] != 0.0f || f[1] != 0.0f;
+	if (on) { foveation_axis(f[0], f[2], f[4], out); foveation_axis(f[1], f[3], f[5], out + 12); }
+	else { foveation_axis(1.0f, 0.5f, 0.5f, out); foveation_axis(1.0f, 0.5f, 0.5f, out + 12); }
+	return on;
 }
 
 RaySoA ray_soa(hn_context* ctx) {
@@ -507,6 +552,29 @@ void env_light_pass(hn_context* ctx, const FrameArgs& a_in, float4* frame, float
 	}
 }
 
+// ERenderMode::Distortion / Slice of the NeRF pass. Slice: one network sample per pixel, in batches of 1 Mi pixels (a chunk of the
+// network kernel carries one direction, so each pixel takes a chunk of its own with one valid sample).
+void render_2d(hn_context* ctx, const FrameArgs& a_in, float4* frame, float* depth, cudaStream_t s) {
+	hn_frame_stats& st = ctx->stats;
+	if (a_in.render_mode == 8) { launch_distortion(a_in, frame, depth, s); st.n_kernel_launches += 1; return; }
+	FrameArgs a = a_in;
+	a.aperture_size = 0.0f; // plane_z < 0 switches depth of field off (:1465-1467)
+	a.render_mode = 1;
+	const uint32_t n_threads = owned_pixel_threads(a), batch = 1u << 20;
+	const uint32_t cap = std::min(n_threads, batch);
+	ctx->samples.ensure((size_t)cap * CHUNK); ctx->net_out.ensure((size_t)cap * CHUNK); ctx->sample_counts.ensure(cap);
+	ctx->slice_dirs.ensure((size_t)cap * 3); ctx->slice_pixels.ensure(cap);
+	RaySoA none = {};
+	for (uint32_t first = 0; first < n_threads; first += batch) {
+		const uint32_t n = std::min(batch, n_threads - first);
+		launch_slice_raygen(a, ctx->opt.focus_z, first, n, ctx->samples.p, ctx->sample_counts.p, ctx->slice_dirs.p, ctx->slice_pixels.p, depth, s);
+		launch_eval(ctx->net, ctx->levels, ctx->params.p, a, ctx->samples.p, ctx->sample_counts.p, nullptr, none, ctx->slice_dirs.p, nullptr, n, ctx->net_out.p,
+			ctx->opt.eval_impl, nullptr, nullptr, nullptr, nullptr, s, false, param_textures(ctx));
+		launch_slice_shade(n, ctx->slice_pixels.p, ctx->net_out.p, a.rgb_act, a.density_act, a.linear_colors, frame, s);
+		st.n_kernel_launches += 3; st.n_samples += n;
+	}
+}
+
 void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame, float* depth, cudaStream_t s) {
 	FrameArgs a = args_in;
 	const size_t n_px = (size_t)a.w * a.h;
@@ -542,9 +610,16 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 	if (ctx->opt.render_nerf && ctx->has_net) {
 		need(ctx->has_params, "network parameters not set");
 		need(ctx->has_bitfield, "occupancy grid not set");
+		if (ctx->opt.render_mode == 8 || ctx->opt.render_mode == 10) { // the 2-D modes never trace (render_nerf, src/testbed_nerf.cu:2397-2460)
+			need(ctx->has_params, "network parameters not set");
+			render_2d(ctx, a, frame, depth, s);
+			total.stop(st.ms_total);
+			HN_CUDA(cudaGetLastError());
+			return;
+		}
 		{
 			const int m = ctx->opt.render_mode;
-			need(m == 0 || (m >= 1 && m <= 7) || m == 9 || m == 12, "render_mode: AO, Shade, Normals, Positions, Depth, Cost and EncodingVis are built; Distortion and Slice are not");
+			need(m == 0 || (m >= 1 && m <= 7) || m == 9 || m == 12, "render_mode must be one of ERenderMode: 0-10 or 12 (EncodingVis)");
 			need(m != 5 || ctx->net.density_hidden <= 2, "render_mode Normals: at most two hidden layers in the density network");
 			need((m >= 1 && m <= 4) || (ctx->opt.composite_impl == 1 && !ctx->opt.fuse_composite) || (ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite), "visualisation render modes need composite_impl 1");
 		}
@@ -680,6 +755,42 @@ int hn_render_frame(hn_context* ctx, const float cam0[12], const float cam1[12],
 	HN_CUDA(cudaSetDevice(ctx->device));
 	FrameArgs a = make_args(ctx, cam0, cam1, screen_center, relative_focal_length, rolling_shutter, spp_index, width, height);
 	render_frame_impl(ctx, a, (float4*)frame_dev, depth_dev, (cudaStream_t)cuda_stream);
+	HN_CATCH(ctx)
+}
+
+int hn_set_hidden_area_mask(hn_context* ctx, const uint8_t* mask, int width, int height) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (!mask || width <= 0 || height <= 0) { ctx->hidden_w = ctx->hidden_h = 0; return 0; }
+	ctx->hidden_mask.ensure((size_t)width * height);
+	HN_CUDA(cudaMemcpy(ctx->hidden_mask.p, mask, (size_t)width * height, cudaMemcpyHostToDevice));
+	ctx->hidden_w = width; ctx->hidden_h = height;
+	HN_CATCH(ctx)
+}
+int hn_set_distortion_map(hn_context* ctx, const float* grid, int width, int height) {
+	HN_TRY(ctx)
+	HN_CUDA(cudaSetDevice(ctx->device));
+	if (!grid || width <= 0 || height <= 0) { ctx->dist_w = ctx->dist_h = 0; return 0; }
+	ctx->distortion.ensure((size_t)width * height);
+	HN_CUDA(cudaMemcpy(ctx->distortion.p, grid, (size_t)width * height * sizeof(float2), cudaMemcpyHostToDevice));
+	ctx->dist_w = width; ctx->dist_h = height;
+	HN_CATCH(ctx)
+}
+int hn_unwarp_foveated(hn_context* ctx, const float foveation[6], int width_in, int height_in, const float* frame_in_dev, const float* depth_in_dev,
+	int width_out, int height_out, float* frame_out_dev, float* depth_out_dev, void* cuda_stream) {
+	HN_TRY(ctx)
+	need(foveation && frame_in_dev && frame_out_dev && width_in > 0 && height_in > 0 && width_out > 0 && height_out > 0, "bad unwarp arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	float c[24];
+	foveation_coeffs(foveation, c);
+	launch_unwarp_foveated(c, width_in, height_in, (const float4*)frame_in_dev, depth_in_dev, width_out, height_out, (float4*)frame_out_dev, depth_out_dev, (cudaStream_t)cuda_stream);
+	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+int hn_op_foveation(hn_context* ctx, const float foveation[6], float coeffs[24]) {
+	HN_TRY(ctx)
+	need(foveation && coeffs, "bad foveation arguments");
+	foveation_coeffs(foveation, coeffs);
 	HN_CATCH(ctx)
 }
 

@@ -283,6 +283,60 @@ void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const
 	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out);
 }
 
+// ERenderMode::Slice, second half (compute_nerf_rgba with depth 0.01, src/testbed_nerf.cu:408-421, then shade_kernel_nerf :1361-1401):
+// alpha = clamp(1 - exp(-0.01 sigma)), colour premultiplied, taken to linear like Shade; the depth buffer is left alone
+__global__ void __launch_bounds__(256) slice_shade_kernel(uint32_t n, const uint32_t* __restrict__ pixels, const uint2* __restrict__ net_out, int rgb_act, int density_act,
+	int linear_colors, float4* __restrict__ frame) {
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= n) return;
+	const uint32_t idx = pixels[p];
+	if (idx == 0xffffffffu) return;
+	const uint2 o = __ldg(net_out + (size_t)p * CHUNK);
+	const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
+	const float alpha = fminf(fmaxf(1.f - __expf(-act_density(__high2float(bs), density_act) * 0.01f), 0.0f), 1.0f);
+	float r = act_rgb(__low2float(rg), rgb_act) * alpha, g = act_rgb(__high2float(rg), rgb_act) * alpha, b = act_rgb(__low2float(bs), rgb_act) * alpha;
+	if (!linear_colors) { r = srgb_to_linear(r); g = srgb_to_linear(g); b = srgb_to_linear(b); }
+	const float4 fb = frame[idx];
+	const float ia = 1.0f - alpha;
+	frame[idx] = make_float4(r + fb.x * ia, g + fb.y * ia, b + fb.z * ia, alpha + fb.w * ia);
+}
+void launch_slice_shade(uint32_t n, const uint32_t* pixels, const uint2* net_out, int rgb_act, int density_act, int linear_colors, float4* frame, cudaStream_t s) {
+	if (n) slice_shade_kernel<<<(n + 255) / 256, 256, 0, s>>>(n, pixels, net_out, rgb_act, density_act, linear_colors, frame);
+}
+// the blit of a foveated frame (Testbed::blit_texture + its fragment shader, src/testbed.cu:2600-2640, without the GL y flip): output
+// pixel centre uv -> unwarp(uv) -> bilinear fetch (GL_LINEAR, clamp to edge) of the rendered, warped frame and depth
+struct FovCoeffs { float c[2][12]; };
+__device__ __forceinline__ float fovc_unwarp(const float* c, float y) { // FoveationPiecewiseQuadratic::unwarp, common_device.cuh:210-219
+	y = fminf(fmaxf(y, 0.0f), 1.0f);
+	if (y < c[10]) return (sqrtf(-4 * c[0] * c[2] + 4 * c[0] * y + c[1] * c[1]) - c[1]) / (2 * c[0]);
+	if (y > c[11]) return (sqrtf(-4 * c[5] * c[7] + 4 * c[5] * y + c[6] * c[6]) - c[6]) / (2 * c[5]);
+	return (y - c[4]) / c[3];
+}
+__global__ void __launch_bounds__(256) unwarp_foveated_kernel(FovCoeffs f, int w_in, int h_in, const float4* __restrict__ frame_in, const float* __restrict__ depth_in,
+	int w_out, int h_out, float4* __restrict__ frame_out, float* __restrict__ depth_out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= (uint32_t)w_out * (uint32_t)h_out) return;
+	const int x = (int)(i % (uint32_t)w_out), y = (int)(i / (uint32_t)w_out);
+	const float u = fovc_unwarp(f.c[0], ((float)x + 0.5f) / (float)w_out), v = fovc_unwarp(f.c[1], ((float)y + 0.5f) / (float)h_out);
+	// GL_LINEAR: texel centres at (k + 0.5) / N
+	const float sx = u * (float)w_in - 0.5f, sy = v * (float)h_in - 0.5f;
+	const float fx0 = floorf(sx), fy0 = floorf(sy);
+	const float wx = sx - fx0, wy = sy - fy0;
+	const int x0 = min(max((int)fx0, 0), w_in - 1), x1 = min(max((int)fx0 + 1, 0), w_in - 1), y0 = min(max((int)fy0, 0), h_in - 1), y1 = min(max((int)fy0 + 1, 0), h_in - 1);
+	const float w00 = (1 - wx) * (1 - wy), w10 = wx * (1 - wy), w01 = (1 - wx) * wy, w11 = wx * wy;
+	const float4 a = frame_in[x0 + y0 * w_in], b = frame_in[x1 + y0 * w_in], c = frame_in[x0 + y1 * w_in], d = frame_in[x1 + y1 * w_in];
+	frame_out[i] = make_float4(w00 * a.x + w10 * b.x + w01 * c.x + w11 * d.x, w00 * a.y + w10 * b.y + w01 * c.y + w11 * d.y,
+		w00 * a.z + w10 * b.z + w01 * c.z + w11 * d.z, w00 * a.w + w10 * b.w + w01 * c.w + w11 * d.w);
+	if (depth_in && depth_out)
+		depth_out[i] = w00 * depth_in[x0 + y0 * w_in] + w10 * depth_in[x1 + y0 * w_in] + w01 * depth_in[x0 + y1 * w_in] + w11 * depth_in[x1 + y1 * w_in];
+}
+void launch_unwarp_foveated(const float coeffs[24], int w_in, int h_in, const float4* frame_in, const float* depth_in, int w_out, int h_out, float4* frame_out, float* depth_out, cudaStream_t s) {
+	FovCoeffs f;
+	for (int i = 0; i < 24; ++i) f.c[i / 12][i % 12] = coeffs[i];
+	const uint32_t n = (uint32_t)w_out * (uint32_t)h_out;
+	if (n) unwarp_foveated_kernel<<<(n + 255) / 256, 256, 0, s>>>(f, w_in, h_in, frame_in, depth_in, w_out, h_out, frame_out, depth_out);
+}
+
 // a-16 light rays: one warp per ray chunk, lane j = sample j. T_j = T_in * prod_{k<=j} exp(-sigma_k dt_k) (warp product scan);
 // the ray ends at the first sample with T_j < min_transmittance (oracle nerf_transmittance) or when it leaves the volume.
 __global__ void __launch_bounds__(512) transmittance_kernel(FrameArgs a, RaySoA rays, const uint32_t* __restrict__ alive_list,

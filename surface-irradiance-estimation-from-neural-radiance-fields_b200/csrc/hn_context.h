@@ -50,6 +50,7 @@ struct Options {
 	float aperture_size = 0.0f;                 // m_aperture_size
 	float focus_z = 1.0f;                       // m_slice_plane_z + m_scale
 	float parallax_shift[3] = {0, 0, 0};        // m_parallax_shift
+	float foveation[6] = {0, 0, 0, 0, 0, 0};    // Foveation(center_pixel_steepness xy, center_inverse_piecewise_y xy, center_radius xy); all zero = Foveation{} (none)
 	float render_aabb[6] = {0, 0, 0, 1, 1, 1};
 	float render_aabb_to_local[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; // m_render_aabb_to_local, column-major (crop box rotation)
 	float train_aabb[6] = {0, 0, 0, 1, 1, 1};   // m_geometry.nerfBoundingBox / m_aabb
@@ -190,6 +191,9 @@ struct hn_context {
 	hn::DevBuf<hn::MeshDev> d_meshes;
 
 	// environment map (a-16)
+	hn::DevBuf<uint8_t> hidden_mask; int hidden_w = 0, hidden_h = 0;   // render_buffer.hidden_area_mask (0 = hidden), empty = none
+	hn::DevBuf<float2> distortion; int dist_w = 0, dist_h = 0;         // m_distortion.inference_view() (m_nerf.render_with_lens_distortion), empty = none
+	hn::DevBuf<float> slice_dirs; hn::DevBuf<uint32_t> slice_pixels;   // ERenderMode::Slice workspace
 	hn::DevBuf<float4> envmap;
 	int env_w = 0, env_h = 0;
 	hn::DevBuf<float4> hit_pos_pix, hit_nrm, hit_albedo;

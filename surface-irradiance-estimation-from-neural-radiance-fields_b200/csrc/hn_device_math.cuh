@@ -177,12 +177,43 @@ __device__ __forceinline__ float2 square2disk_shirley(float a, float b) { // ran
 	sincosf(phi, &sp, &cp);
 	return make_float2(r * cp, r * sp);
 }
-// uv_to_ray (common_device.cuh:416-483) without foveation / hidden-area mask / distortion grid (VR only). c0..c2 = camera
-// rotation columns, pos = camera[3]. `use_lens` is false on the mesh pass (its ray init takes no Lens, geometry :520-536).
-// Returns false for an invalid ray (f-theta outside the image circle). The direction is NOT normalised.
-__device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, float u, float v, V3 c0, V3 c1, V3 c2, V3 pos, V3& origin, V3& dir) {
+// ---- foveation (common_device.cuh:117-246): one axis; c = al bl cl am bm ar br cr switch_left switch_right inv_switch_left inv_switch_right
+__host__ __device__ __forceinline__ float fov_warp(const float* c, float x) {
+	x = fminf(fmaxf(x, 0.0f), 1.0f);
+	if (x < c[8]) return c[0] * x * x + c[1] * x + c[2];
+	if (x > c[9]) return c[5] * x * x + c[6] * x + c[7];
+	return c[3] * x + c[4];
+}
+__host__ __device__ __forceinline__ float fov_unwarp(const float* c, float y) {
+	y = fminf(fmaxf(y, 0.0f), 1.0f);
+	if (y < c[10]) return (sqrtf(-4 * c[0] * c[2] + 4 * c[0] * y + c[1] * c[1]) - c[1]) / (2 * c[0]);
+	if (y > c[11]) return (sqrtf(-4 * c[5] * c[7] + 4 * c[5] * y + c[6] * c[6]) - c[6]) / (2 * c[5]);
+	return (y - c[4]) / c[3];
+}
+// Buffer2DView::at / at_lerp (common.h:268-305)
+__device__ __forceinline__ uint8_t mask_at(const uint8_t* __restrict__ data, int w, int h, float u, float v) {
+	const int px = min(max((int)((float)w * u), 0), w - 1), py = min(max((int)((float)h * v), 0), h - 1);
+	return __ldg(data + px + py * w);
+}
+__device__ __forceinline__ float2 grid_at_lerp(const float2* __restrict__ data, int w, int h, float u, float v) {
+	const float fx = (float)w * u, fy = (float)h * v;
+	const int px = (int)fx, py = (int)fy;
+	const float wx = fx - (float)px, wy = fy - (float)py;
+	const int x0 = min(max(px, 0), w - 1), x1 = min(max(px + 1, 0), w - 1), y0 = min(max(py, 0), h - 1), y1 = min(max(py + 1, 0), h - 1);
+	const float2 a = __ldg(data + x0 + y0 * w), b = __ldg(data + x1 + y0 * w), c = __ldg(data + x0 + y1 * w), d = __ldg(data + x1 + y1 * w);
+	const float w00 = (1 - wx) * (1 - wy), w10 = wx * (1 - wy), w01 = (1 - wx) * wy, w11 = wx * wy;
+	return make_float2(w00 * a.x + w10 * b.x + w01 * c.x + w11 * d.x, w00 * a.y + w10 * b.y + w01 * c.y + w11 * d.y);
+}
+
+// uv_to_ray (common_device.cuh:416-483). c0..c2 = camera rotation columns, pos = camera[3]. `use_lens` is false on the mesh pass
+// (its ray init takes foveation and the hidden-area mask but neither Lens nor distortion grid, geometry :520-536).
+// Returns false for an invalid ray (f-theta outside the image circle, or a pixel the mask hides). The direction is NOT normalised.
+__device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, float u_in, float v_in, V3 c0, V3 c1, V3 c2, V3 pos, V3& origin, V3& dir) {
 	V3 d;
 	const int mode = use_lens ? a.lens_mode : 0;
+	float u = u_in, v = v_in; // warped_uv; the depth-of-field pixel hash below keeps the un-warped uv (:470)
+	if (a.foveated) { u = fov_warp(a.fov[0], u_in); v = fov_warp(a.fov[1], v_in); }
+	if (a.hidden_mask && !mask_at(a.hidden_mask, a.hidden_w, a.hidden_h, u, v)) return false;
 	if (mode == 2) {
 		const float xpix = (u - a.screen_center[0]) * a.lens_params[5], ypix = (v - a.screen_center[1]) * a.lens_params[6];
 		const float norm = sqrtf(xpix * xpix + ypix * ypix);
@@ -208,6 +239,7 @@ __device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, fl
 		if (mode == 1) iterative_undistortion<false>(a.lens_params, &d.x, &d.y);
 		else if (mode == 4) iterative_undistortion<true>(a.lens_params, &d.x, &d.y);
 	}
+	if (use_lens && a.distortion) { const float2 g = grid_at_lerp(a.distortion, a.dist_w, a.dist_h, u, v); d.x += g.x; d.y += g.y; }
 	const V3 head = mk(a.parallax_shift[0], a.parallax_shift[1], 0.0f);
 	d = d - head * a.parallax_shift[2];
 	V3 r = mk(0.0f, 0.0f, 0.0f);
@@ -222,7 +254,7 @@ __device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, fl
 	o = o + pos;
 	if (a.aperture_size != 0.0f) {
 		const V3 lookat = o + d * a.focus_z;
-		const int px = (int)(u * (float)a.w), py = (int)(v * (float)a.h);
+		const int px = (int)(u_in * (float)a.w), py = (int)(v_in * (float)a.h);
 		const float2 rnd = hn_ld_random_val_2d(a.spp, (uint32_t)px * 19349663u + (uint32_t)py * 96925573u);
 		const float2 disk = square2disk_shirley(rnd.x * 2.0f - 1.0f, rnd.y * 2.0f - 1.0f);
 		const float bx = a.aperture_size * disk.x, by = a.aperture_size * disk.y;
@@ -235,6 +267,52 @@ __device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, fl
 	origin = o + d * a.near_distance;
 	dir = d;
 	return true;
+}
+
+// pos_to_uv (common_device.cuh:505-537) with a perspective lens, as ERenderMode::Distortion calls it (init_rays :1513-1515);
+// inverse(mat3) = adjoint / determinant in tcnn's operation order (vec.h:771-829,861-864)
+__device__ __forceinline__ float det2(float a, float b, float c, float d) { return a * d - b * c; }
+__device__ __forceinline__ float2 pos_to_uv(const FrameArgs& a, V3 p, V3 c0, V3 c1, V3 c2, V3 cpos) {
+	const V3 head = mk(a.parallax_shift[0], a.parallax_shift[1], 0.0f);
+	V3 o = mk(0.0f, 0.0f, 0.0f);
+	o.x += c0.x * head.x; o.y += c0.y * head.x; o.z += c0.z * head.x;
+	o.x += c1.x * head.y; o.y += c1.y * head.y; o.z += c1.z * head.y;
+	o.x += c2.x * head.z; o.y += c2.y * head.z; o.z += c2.z * head.z;
+	o = o + cpos;
+	const V3 d = p - o;
+	// m(c, r): column c, row r
+	const float m00_ = c0.x, m01_ = c0.y, m02_ = c0.z, m10_ = c1.x, m11_ = c1.y, m12_ = c1.z, m20_ = c2.x, m21_ = c2.y, m22_ = c2.z;
+	const float det = m00_ * (m11_ * m22_ - m21_ * m12_) + -m10_ * (m01_ * m22_ - m21_ * m02_) + m20_ * (m01_ * m12_ - m11_ * m02_);
+	const float a00 = det2(m11_, m21_, m12_, m22_), a01 = det2(m01_, m21_, m02_, m22_), a02 = det2(m01_, m11_, m02_, m12_);
+	const float a10 = det2(m10_, m20_, m12_, m22_), a11 = det2(m00_, m20_, m02_, m22_), a12 = det2(m00_, m10_, m02_, m12_);
+	const float a20 = det2(m10_, m20_, m11_, m21_), a21 = det2(m00_, m20_, m01_, m21_), a22 = det2(m00_, m10_, m01_, m11_);
+	const V3 i0 = mk(a00, -a01, a02) / det, i1 = mk(-a10, a11, -a12) / det, i2 = mk(a20, -a21, a22) / det;
+	V3 r = mk(0.0f, 0.0f, 0.0f);
+	r.x += i0.x * d.x; r.y += i0.y * d.x; r.z += i0.z * d.x;
+	r.x += i1.x * d.y; r.y += i1.y * d.y; r.z += i1.z * d.y;
+	r.x += i2.x * d.z; r.y += i2.y * d.z; r.z += i2.z * d.z;
+	r = r / r.z;
+	r = r + head * a.parallax_shift[2];
+	float u = r.x * a.focal[0] / (float)a.w + a.screen_center[0], v = r.y * a.focal[1] / (float)a.h + a.screen_center[1];
+	if (a.foveated) { u = fov_unwarp(a.fov[0], u); v = fov_unwarp(a.fov[1], v); }
+	return make_float2(u, v);
+}
+// hsv_to_rgb / to_rgb (common_device.cuh:713-739)
+__device__ __forceinline__ V3 dir_to_rgb(float dx, float dy) {
+	float h = atan2f(dy, dx) / (2.0f * HN_PI_F) + 0.5f;
+	const float v = sqrtf(dx * dx + dy * dy); // s = 1
+	h = fmodf(h, 1.0f) * 6.0f;
+	const int i = (int)h;
+	const float f = h - (float)i;
+	const float p = v * (1.0f - 1.0f), q = v * (1.0f - 1.0f * f), t = v * (1.0f - 1.0f * (1.0f - f));
+	switch (i) {
+		case 0: return mk(v, t, p);
+		case 1: return mk(q, v, p);
+		case 2: return mk(p, v, t);
+		case 3: return mk(p, q, v);
+		case 4: return mk(t, p, v);
+		default: return mk(v, p, q);
+	}
 }
 
 // ---- a-16: environment map + light-direction sampling (random_val.cuh:62-72,130-185, envmap.cuh:24-50) ----

@@ -54,6 +54,12 @@ struct FrameArgs {
 	float lens_params[7];
 	float aperture_size, focus_z;  // depth of field: focus_z = slice_plane_z + scale (src/testbed_nerf.cu:2342)
 	float parallax_shift[3];
+	// VR pieces of uv_to_ray (common_device.cuh:117-246,416-483): foveation coefficients per axis (al bl cl am bm ar br cr switch_left
+	// switch_right inv_switch_left inv_switch_right; computed on the host by FoveationPiecewiseQuadratic's constructor), hidden-area mask
+	// (0 = hidden) and the distortion grid of the NeRF rays
+	int foveated; float fov[2][12];
+	const uint8_t* hidden_mask; int hidden_w, hidden_h;
+	const float2* distortion; int dist_w, dist_h;
 	float render_aabb[6], train_aabb[6];
 	float aabb_to_local[9]; int crop_rotated; // m_render_aabb_to_local (column-major); crop_rotated = 0 -> identity, skipped
 	float occ_aabb[6];     // inflated bounds of every set occupancy cell of mips 0..max_mip (empty: lo > hi)
@@ -132,6 +138,12 @@ void launch_grid_to_bitfield(const float* grid, uint32_t n_cascades, float thres
 void launch_grid_mean(const float* grid, float* mean_out, cudaStream_t s);
 void launch_occ_bounds(const uint8_t* bits, int* out, cudaStream_t s);
 void launch_occ_coarse(const uint8_t* bits, uint32_t* coarse, cudaStream_t s);
+// 2-D render modes and the foveated blit (hn_march.cu / hn_composite.cu)
+void launch_distortion(const FrameArgs& a, float4* frame, float* depth_buffer, cudaStream_t s);
+void launch_slice_raygen(const FrameArgs& a, float plane_z, uint32_t first, uint32_t n, float4* samples, uint32_t* sample_counts, float* dirs, uint32_t* pixels,
+	float* depth_buffer, cudaStream_t s);
+void launch_slice_shade(uint32_t n, const uint32_t* pixels, const uint2* net_out, int rgb_act, int density_act, int linear_colors, float4* frame, cudaStream_t s);
+void launch_unwarp_foveated(const float coeffs[24], int w_in, int h_in, const float4* frame_in, const float* depth_in, int w_out, int h_out, float4* frame_out, float* depth_out, cudaStream_t s);
 void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t* alive_list, uint32_t* counters,
 	float* depth_buffer, float4* frame, cudaStream_t s);
 void launch_raygen_debug(const FrameArgs& a, const uint8_t* bits, float* o, float* d, float* t, uint8_t* alive, cudaStream_t s);

@@ -85,18 +85,22 @@ __device__ __forceinline__ M3 quat_to_mat3(Quat q) {
 }
 
 // init_rays_with_payload_kernel_nerf (src/testbed_nerf.cu:1428-1476) + uv_to_ray pinhole (common_device.cuh:416-483)
-__device__ bool pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& dir) {
+// the un-normalised ray of a pixel together with its uv and its (rolling-shutter) camera: what the 2-D render modes need
+__device__ bool pixel_ray_raw(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& d, float& u, float& v, M3& rot, V3& pos) {
 	uint32_t idx = x + (uint32_t)a.w * y;
-	float u = ((float)x + a.pixel_offset[0]) / (float)a.w;
-	float v = ((float)y + a.pixel_offset[1]) / (float)a.h;
+	u = ((float)x + a.pixel_offset[0]) / (float)a.w;
+	v = ((float)y + a.pixel_offset[1]) / (float)a.h;
 	float mb = hn_ld_random_val(a.spp, idx * 72239731u);
 	float pixel_t = a.rolling_shutter[0] + a.rolling_shutter[1] * u + a.rolling_shutter[2] * v + a.rolling_shutter[3] * mb;
 	Cam c0 = ldcam(a.cam0), c1 = ldcam(a.cam1);
 	M3 m0 = {{c0.c[0], c0.c[1], c0.c[2]}}, m1 = {{c1.c[0], c1.c[1], c1.c[2]}};
-	M3 rot = quat_to_mat3(qnormalize(qslerp(qnormalize(quat_from(m0)), qnormalize(quat_from(m1)), pixel_t)));
-	V3 pos = mix3(c0.c[3], c1.c[3], pixel_t);
-	V3 d;
-	if (!camera_ray(a, true, u, v, rot.c[0], rot.c[1], rot.c[2], pos, origin, d)) { origin = mk(0.0f, 0.0f, 0.0f); dir = mk(0.0f, 0.0f, 0.0f); return false; } // Ray::invalid()
+	rot = quat_to_mat3(qnormalize(qslerp(qnormalize(quat_from(m0)), qnormalize(quat_from(m1)), pixel_t)));
+	pos = mix3(c0.c[3], c1.c[3], pixel_t);
+	return camera_ray(a, true, u, v, rot.c[0], rot.c[1], rot.c[2], pos, origin, d);
+}
+__device__ bool pixel_ray(const FrameArgs& a, uint32_t x, uint32_t y, V3& origin, V3& dir) {
+	V3 d, pos; M3 rot; float u, v;
+	if (!pixel_ray_raw(a, x, y, origin, d, u, v, rot, pos)) { origin = mk(0.0f, 0.0f, 0.0f); dir = mk(0.0f, 0.0f, 0.0f); return false; } // Ray::invalid()
 	dir = normalize3(d);
 	return true;
 }
@@ -345,6 +349,47 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 		rays.t_far[r] = t_far;
 		alive_list[r] = r;
 	}
+}
+
+// ERenderMode::Distortion (init_rays_with_payload_kernel_nerf, src/testbed_nerf.cu:1513-1521): no tracing - every valid pixel shows, as a
+// hue, where the lens model + distortion grid moved it: to_rgb((pos_to_uv(ray(1)) - uv) * 64), alpha 1, depth 1.
+__global__ void __launch_bounds__(256) distortion_kernel(FrameArgs a, float4* __restrict__ frame, float* __restrict__ depth_buffer) {
+	uint32_t x = 0, y = 0;
+	if (!owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) return;
+	const uint32_t idx = x + (uint32_t)a.w * y;
+	if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
+	V3 o, d, pos; M3 rot; float u, v;
+	if (!pixel_ray_raw(a, x, y, o, d, u, v, rot, pos)) return;
+	const float2 after = pos_to_uv(a, o + 1.0f * d, rot.c[0], rot.c[1], rot.c[2], pos);
+	const V3 c = dir_to_rgb((after.x - u) * 64.0f, (after.y - v) * 64.0f);
+	frame[idx] = make_float4(c.x, c.y, c.z, 1.0f);
+	depth_buffer[idx] = 1.0f;
+}
+// ERenderMode::Slice (:1500-1510, 2431-2459): the point where the pixel's ray meets the plane at camera depth plane_z becomes ONE network
+// sample (list slot p of this batch: chunk p holds it in lane 0), the depth buffer gets plane_z. The caller passes aperture_size = 0.
+__global__ void __launch_bounds__(256) slice_raygen_kernel(FrameArgs a, float plane_z, uint32_t first, uint32_t n, float4* __restrict__ samples, uint32_t* __restrict__ sample_counts,
+	float* __restrict__ dirs, uint32_t* __restrict__ pixels, float* __restrict__ depth_buffer) {
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= n) return;
+	uint32_t x = 0, y = 0, count = 0, idx = 0xffffffffu;
+	V3 dir = mk(0.f, 0.f, 1.f);
+	if (owned_pixel(a, first + p, x, y)) {
+		idx = x + (uint32_t)a.w * y;
+		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
+		V3 o, d, pos; M3 rot; float u, v;
+		if (pixel_ray_raw(a, x, y, o, d, u, v, rot, pos)) {
+			const float len = length3(d);
+			dir = (1.0f / len) * d;
+			const float t = plane_z * len;
+			const V3 q = o + dir * t;
+			samples[(size_t)p * CHUNK] = make_float4(q.x, q.y, q.z, HN_STEPSIZE);
+			depth_buffer[idx] = plane_z;
+			count = 1;
+		} else idx = 0xffffffffu;
+	}
+	sample_counts[p] = count;
+	pixels[p] = idx;
+	dirs[3 * p] = dir.x; dirs[3 * p + 1] = dir.y; dirs[3 * p + 2] = dir.z;
 }
 
 // a-16: light rays that carry radiance enter the volume like camera rays (AABB entry, advance to the first occupied voxel;
@@ -784,6 +829,14 @@ void launch_raygen(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_
 	if (!n) return;
 	if (simple_walk(a, bits)) raygen_kernel<true><<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
 	else raygen_kernel<false><<<(n + 255) / 256, 256, 0, s>>>(a, bits, rays, alive_list, counters, depth_buffer, frame);
+}
+void launch_distortion(const FrameArgs& a, float4* frame, float* depth_buffer, cudaStream_t s) {
+	const uint32_t n = owned_pixel_threads(a);
+	if (n) distortion_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, frame, depth_buffer);
+}
+void launch_slice_raygen(const FrameArgs& a, float plane_z, uint32_t first, uint32_t n, float4* samples, uint32_t* sample_counts, float* dirs, uint32_t* pixels,
+	float* depth_buffer, cudaStream_t s) {
+	if (n) slice_raygen_kernel<<<(n + 255) / 256, 256, 0, s>>>(a, plane_z, first, n, samples, sample_counts, dirs, pixels, depth_buffer);
 }
 void launch_secondary_start(const FrameArgs& a, const uint8_t* bits, RaySoA rays, uint32_t n_rays, uint32_t* alive_list, uint32_t* counters, cudaStream_t s) {
 	if (!n_rays) return;

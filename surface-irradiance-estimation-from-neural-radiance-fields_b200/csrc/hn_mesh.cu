@@ -377,8 +377,9 @@ __device__ bool mesh_pixel(const FrameArgs& a, const SceneDev& sc, float4* __res
 	const float u = ((float)x + a.pixel_offset[0]) / (float)a.w, v = ((float)y + a.pixel_offset[1]) / (float)a.h;
 	const V3 c0 = ld3(a.cam0), c1 = ld3(a.cam0 + 3), c2 = ld3(a.cam0 + 6), cam_pos = ld3(a.cam0 + 9);
 	V3 org, dir;
-	camera_ray(a, false, u, v, c0, c1, c2, cam_pos, org, dir); // no Lens on this ray init; parallax shift and depth of field apply
+	const bool valid = camera_ray(a, false, u, v, c0, c1, c2, cam_pos, org, dir); // no Lens on this ray init; foveation, hidden-area mask, parallax shift and depth of field apply
 	depth_buffer[idx] = MAX_DEPTH_F;
+	if (!valid) return false; // hidden by the mask: the pixel stays cleared (the reference pushes a zero ray through its trace / shade kernels: undefined colour)
 	dir = normalize3(dir);
 	const float t0 = fmaxf(box_ray_intersect(aabb, org, dir).x, 0.0f);
 	V3 pos = org + (t0 + 1e-6f) * dir;

@@ -74,6 +74,7 @@ EXPORTS = [
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
     "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
+    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -101,6 +102,10 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_set_hidden_area_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+_lib.hn_set_distortion_map.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+_lib.hn_unwarp_foveated.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_op_foveation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_get_error_map.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
 _lib.hn_op_error_map_cdf.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5
 _lib.hn_op_sample_training_pixels.argtypes = [C.c_void_p] + [C.c_uint32] * 6 + [C.c_int, C.c_int] + [C.c_void_p] * 6
@@ -396,6 +401,43 @@ class Testbed:
         rs = _f32(rolling_shutter)
         self._check(_lib.hn_op_init_rays(self._h, _ptr(c0), _ptr(c1), _ptr(sc), _ptr(rf), _ptr(rs), spp_index, width, height, _ptr(o), _ptr(d), _ptr(t), _ptr(alive)))
         return o, d, t, alive
+
+    # ---- VR pieces of the camera model (Testbed::m_views[i].foveation, render_buffer.hidden_area_mask, m_distortion)
+    def set_hidden_area_mask(self, mask):
+        """uint8 [h][w], 0 = hidden (no ray); None removes it"""
+        if mask is None:
+            self._check(_lib.hn_set_hidden_area_mask(self._h, None, 0, 0)); return
+        m = np.ascontiguousarray(mask, np.uint8)
+        self._check(_lib.hn_set_hidden_area_mask(self._h, _ptr(m), m.shape[1], m.shape[0]))
+
+    def set_distortion_map(self, grid):
+        """float32 [h][w][2] offsets added to the camera-space direction of NeRF rays (bilinear); None removes it"""
+        if grid is None:
+            self._check(_lib.hn_set_distortion_map(self._h, None, 0, 0)); return
+        g = _f32(grid)
+        assert g.ndim == 3 and g.shape[2] == 2
+        self._check(_lib.hn_set_distortion_map(self._h, _ptr(g), g.shape[1], g.shape[0]))
+
+    def op_foveation(self, foveation):
+        f = _f32(foveation).reshape(6); out = np.empty((2, 12), np.float32)
+        self._check(_lib.hn_op_foveation(self._h, _ptr(f), _ptr(out)))
+        return out
+
+    def unwarp_foveated(self, frame, foveation, out_res=None, depth=None):
+        """frame float32 [h][w][4] rendered with option `foveation` -> the un-warped image at out_res (w, h); host arrays in / out"""
+        import torch
+        f = _f32(foveation).reshape(6)
+        fin = torch.from_numpy(_f32(frame)).cuda()
+        h, w = fin.shape[0], fin.shape[1]
+        ow, oh = (w, h) if out_res is None else out_res
+        fout = torch.empty(oh, ow, 4, device="cuda")
+        din = torch.from_numpy(_f32(depth)).cuda() if depth is not None else None
+        dout = torch.empty(oh, ow, device="cuda") if depth is not None else None
+        torch.cuda.synchronize()
+        self._check(_lib.hn_unwarp_foveated(self._h, _ptr(f), w, h, fin.data_ptr(), din.data_ptr() if din is not None else None, ow, oh, fout.data_ptr(),
+                                            dout.data_ptr() if dout is not None else None, None))
+        torch.cuda.synchronize()
+        return (fout.cpu().numpy(), dout.cpu().numpy()) if depth is not None else fout.cpu().numpy()
 
     def op_march_all(self, origins, dirs, t0, alive, max_per_ray=0):
         o, d, t = _f32(origins), _f32(dirs), _f32(t0)

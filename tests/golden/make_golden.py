@@ -260,6 +260,72 @@ def make_ref_cdf():
     print("ref_host_cdf.npz:", len(out), "arrays")
 
 
+FOV_CASES = [  # tag, foveation (steepness xy, inverse-piecewise y xy, radius xy), lens mode, lens params
+    ("none", (1, 1, 0.5, 0.5, 0.5, 0.5), 0, (0,) * 7),                     # steepness 1 = the fully linear case = Foveation{}
+    ("fov_mild", (0.5, 0.6, 0.45, 0.5, 0.2, 0.25), 0, (0,) * 7),
+    ("fov_strong", (0.25, 0.3, 0.5, 0.6, 0.15, 0.1), 0, (0,) * 7),
+    ("fov_edge", (0.5, 0.5, 0.1, 0.95, 0.3, 0.3), 0, (0,) * 7),          # the linear piece is clipped at 0 / at 1
+    ("fov_opencv", (0.5, 0.6, 0.45, 0.5, 0.2, 0.25), 1, (0.05, -0.02, 0.001, -0.002, 0, 0, 0)),
+]
+
+
+def make_ref_fov():
+    """Foveation (constructor, warp, unwarp, density), uv_to_ray with foveation + hidden-area mask + distortion grid, pos_to_uv and to_rgb of
+    the reference (common_device.cuh:117-246,416-483,505-537,713-739) -> ref_host_fov.npz"""
+    ref = orc.ref
+    if ref is None or not hasattr(ref, "ref_uv_to_ray_full"):
+        raise SystemExit("oracle/_ref/libngp_ref_host.so missing or stale: run `make -C oracle ref`")
+    ref.ref_uv_to_ray_full.restype = C.c_int32
+    rng = np.random.default_rng(20261108)
+    n = 256
+    uv = rng.uniform(0, 1, (n, 2)).astype(f32)
+    uv[:6] = [[0.5, 0.5], [0, 0], [1, 1], [0.5, 0.0], [0.05, 0.95], [0.999, 0.001]]
+    cam = synthetic.look_at_camera((1.4, 1.2, 1.6), (0.5, 0.5, 0.5)).astype(f32).reshape(12)
+    w, h = 800, 600
+    focal = np.array([700.0, 710.0], f32); sc = np.array([0.48, 0.53], f32); par = np.array([0.01, -0.02, 0.5], f32)
+    mask = (rng.random((9, 12)) > 0.25).astype(np.uint8)
+    dist = (rng.normal(size=(32, 32, 2)) * 0.02).astype(f32)
+    out = {"uv": uv, "cam": cam, "res": np.array([w, h], np.int32), "focal": focal, "screen_center": sc, "parallax": par, "near": np.array([0.05], f32),
+           "spp": np.array([3], np.uint32), "mask": mask, "distortion": dist}
+    for tag, fov, mode, lp in FOV_CASES:
+        co = (C.c_float * 24)()
+        ref.ref_foveation_coeffs(fa(*fov), co)
+        out[f"{tag}_coeffs"] = np.array(co[:], f32).reshape(2, 12)
+        wv, un, de = np.zeros((n, 2), f32), np.zeros((n, 2), f32), np.zeros(n, f32)
+        for i in range(n):
+            a, b, d = (C.c_float * 2)(), (C.c_float * 2)(), C.c_float(0)
+            ref.ref_foveation_warp(fa(*fov), fa(*uv[i]), a, b, C.byref(d))
+            wv[i], un[i], de[i] = a[:], b[:], d.value
+        out[f"{tag}_warp"], out[f"{tag}_unwarp"], out[f"{tag}_density"] = wv, un, de
+        for sub, use_mask, use_dist in (("plain", False, False), ("mask", True, False), ("dist", False, True), ("all", True, True)):
+            o = np.zeros((n, 3), f32); d = np.zeros((n, 3), f32); ok = np.zeros(n, np.int32)
+            for i in range(n):
+                to, td = (C.c_float * 3)(), (C.c_float * 3)()
+                ok[i] = ref.ref_uv_to_ray_full(C.c_uint32(3), fa(*uv[i]), w, h, fa(*focal), fa(*cam), fa(*sc), fa(*par), C.c_float(0.05), C.c_float(1.3), C.c_float(0.0),
+                                               fa(*fov), P(mask) if use_mask else None, mask.shape[1], mask.shape[0], mode, fa(*lp),
+                                               P(dist) if use_dist else None, dist.shape[1], dist.shape[0], to, td)
+                o[i], d[i] = to[:], td[:]
+            out[f"{tag}_{sub}_o"], out[f"{tag}_{sub}_d"], out[f"{tag}_{sub}_valid"] = o, d, ok
+        # pos_to_uv of the point at t = 1 on the un-distorted-grid ray: with a perspective or OpenCV lens this inverts uv_to_ray
+        pts = out[f"{tag}_plain_o"] + out[f"{tag}_plain_d"]
+        back = np.zeros((n, 2), f32)
+        for i in range(n):
+            r = (C.c_float * 2)()
+            ref.ref_pos_to_uv(fa(*pts[i]), w, h, fa(*focal), fa(*cam), fa(*sc), fa(*par), fa(*fov), mode, fa(*lp), r)
+            back[i] = r[:]
+        out[f"{tag}_pos_to_uv"] = back
+    dirs = (rng.normal(size=(128, 2)) * 0.7).astype(f32)
+    dirs[:5] = [[0, 0], [1, 0], [-1, 0], [0, 1], [0, -1e-3]]
+    cols = np.zeros((128, 3), f32)
+    for i in range(128):
+        c = (C.c_float * 3)()
+        ref.ref_to_rgb(fa(*dirs[i]), c)
+        cols[i] = c[:]
+    out["rgb_dirs"], out["rgb"] = dirs, cols
+    np.savez_compressed(os.path.join(HERE, "ref_host_fov.npz"), **out)
+    print("ref_host_fov.npz:", len(out), "arrays")
+
+
 def make_ref_tri():
     """Triangle::distance_sq / closest_point (triangle.cuh:66-147) of the reference, host-callable -> ref_host_tri.npz"""
     ref = orc.ref
@@ -342,7 +408,10 @@ if __name__ == "__main__":
         make_ref_tri()
     elif len(sys.argv) > 1 and sys.argv[1] == "cdf":
         make_ref_cdf()
+    elif len(sys.argv) > 1 and sys.argv[1] == "fov":
+        make_ref_fov()
     else:
+        make_ref_fov()
         make_ref_cdf()
         make_ref_tri()
         make_ref_lens()

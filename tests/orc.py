@@ -44,7 +44,9 @@ class RenderParams(C.Structure):
                 ("lens_mode", i32), ("lens_params", f32 * 7), ("aperture_size", f32), ("focus_z", f32), ("parallax_shift", f32 * 3),
                 ("crop_rotated", i32), ("render_aabb_to_local", f32 * 9), ("mask_pad", i32), ("pixel_mask", C.c_void_p),
                 ("density_grid_mean", f32), ("pad2", i32),
-                ("env_source", i32), ("env_sampling", i32), ("probe_n_theta", i32), ("probe_n_phi", i32), ("probe", C.c_void_p)]
+                ("env_source", i32), ("env_sampling", i32), ("probe_n_theta", i32), ("probe_n_phi", i32), ("probe", C.c_void_p),
+                ("foveation", f32 * 6), ("hidden_w", i32), ("hidden_h", i32), ("hidden_area_mask", C.c_void_p),
+                ("distortion_w", i32), ("distortion_h", i32), ("distortion", C.c_void_p)]
 
 
 def P(a):
@@ -128,7 +130,8 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
                   sun_dir=(0.57735026919, 0.57735026919, 0.57735026919), up_dir=(0, 1, 0), floor_y=-10000.0, brdf=None, compat=False,
                   clip=False, rolling_shutter=(0, 0, 0, 1), near=0.0, n_threads=None, envmap=None, env_samples=0, render_mode=1, depth_scale=1.0 / 0.33,
                   lens_mode=0, lens_params=(0,) * 7, aperture_size=0.0, focus_z=1.0, parallax_shift=(0, 0, 0),
-                  render_aabb_to_local=None, pixel_mask=None, density_grid_mean=0.0, probe=None, env_sampling=0) -> RenderParams:
+                  render_aabb_to_local=None, pixel_mask=None, density_grid_mean=0.0, probe=None, env_sampling=0,
+                  foveation=None, hidden_area_mask=None, distortion=None) -> RenderParams:
     from math import tan, pi
     p = RenderParams()
     p.width, p.height, p.spp = w, h, spp
@@ -166,6 +169,17 @@ def render_params(w, h, cam0, cam1=None, spp=0, rel_focal=None, fov_axis=1, zoom
     p.render_aabb_to_local[:] = R
     p.crop_rotated = int(any(abs(a - b) > 0 for a, b in zip(R, ident)))
     p.density_grid_mean = float(density_grid_mean)
+    if foveation is not None:       # center_pixel_steepness xy, center_inverse_piecewise_y xy, center_radius xy
+        p.foveation[:] = [float(v) for v in foveation]
+    if hidden_area_mask is not None:   # uint8 [h][w], 0 = hidden
+        hm = np.ascontiguousarray(hidden_area_mask, np.uint8)
+        p._hidden_keep = hm
+        p.hidden_area_mask, p.hidden_h, p.hidden_w = hm.ctypes.data, hm.shape[0], hm.shape[1]
+    if distortion is not None:         # float32 [h][w][2]
+        dm = np.ascontiguousarray(distortion, np.float32)
+        assert dm.ndim == 3 and dm.shape[2] == 2
+        p._dist_keep = dm
+        p.distortion, p.distortion_h, p.distortion_w = dm.ctypes.data, dm.shape[0], dm.shape[1]
     if probe is not None:  # a-16: the NeRF's probe texture [n_phi][n_theta][4] lights the meshes
         pt = np.ascontiguousarray(probe, np.float32)
         assert pt.ndim == 3 and pt.shape[2] == 4
@@ -479,4 +493,35 @@ def error_map_deposit(img, uv, val, n_images, res, image_res):
     i, u, v = np.ascontiguousarray(img, np.uint32).reshape(-1), np.ascontiguousarray(uv, np.float32).reshape(-1, 2), np.ascontiguousarray(val, np.float32).reshape(-1)
     out = np.zeros((n_images, res[1], res[0]), np.float32)
     lib.orc_error_map_deposit(u32(i.size), P(i), P(u), P(v), C.c_int32(res[0]), C.c_int32(res[1]), C.c_int32(image_res[0]), C.c_int32(image_res[1]), P(out))
+    return out
+
+
+# ---- foveation / 2-D helpers (oracle/orc_fov.inc)
+def foveation_coeffs(f6):
+    f = np.asarray(f6, np.float32); out = np.zeros(24, np.float32)
+    lib.orc_foveation_coeffs(P(f), P(out))
+    return out.reshape(2, 12)
+
+
+def foveation_warp(f6, uv):
+    f = np.asarray(f6, np.float32); u = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    w, un, dens = np.zeros_like(u), np.zeros_like(u), np.zeros(u.shape[0], np.float32)
+    for i in range(u.shape[0]):
+        d = C.c_float(0)
+        lib.orc_foveation_warp(P(f), P(u[i]), P(w[i]), P(un[i]), C.byref(d))
+        dens[i] = d.value
+    return w, un, dens
+
+
+def pos_to_uv(p: RenderParams, pos):
+    q = np.ascontiguousarray(pos, np.float32).reshape(-1, 3); out = np.zeros((q.shape[0], 2), np.float32)
+    for i in range(q.shape[0]):
+        lib.orc_pos_to_uv(C.byref(p), P(q[i]), P(out[i]))
+    return out
+
+
+def to_rgb(dirs):
+    d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 2); out = np.zeros((d.shape[0], 3), np.float32)
+    for i in range(d.shape[0]):
+        lib.orc_to_rgb(P(d[i]), P(out[i]))
     return out

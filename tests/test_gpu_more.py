@@ -217,9 +217,9 @@ def test_visualisation_render_modes(base, hn, orc, mode, name):
         assert np.abs(img - ref).max() <= 1e-2 and psnr(img, ref) >= 50.0, (name, np.abs(img - ref).max())
 
 
-def test_unbuilt_render_modes_fail_loudly(base, hn):
+def test_unknown_render_modes_fail_loudly(base, hn):
     tb, _, _, _ = base
-    for mode in (8, 10):  # Distortion, Slice
+    for mode in (11, 13):  # NumRenderModes and beyond EncodingVis (Distortion and Slice: tests/test_gpu_vr.py)
         tb.set_option("render_mode", float(mode))
         try:
             with pytest.raises(RuntimeError):

@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : (G == 3 ? 2 : 4)) eval_
 		const uint32_t count = chunk < n_chunks ? (a.sample_counts ? a.sample_counts[chunk] : CHUNK) : 0u;
 		// ---- (b) gather: 32 features of this thread's sample -> A planes 0..3
 		if (GV != 0) {
-			if ((uint32_t)lane < count) {
+			if ((uint32_t)lane < count && a.tex_split != 9) { // eval_texsplit 9 / 8: profiling switches - MLPs only (zero features) / gather only
 				const float4 s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
 				float px = s.x, py = s.y, pz = s.z;
 				if (!a.unit_box) { // warp_position; (p - 0) / 1 is the identity, so the unit cube skips three IEEE divisions
@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(TILE * G, G >= 4 ? 2 : (G == 3 ? 2 : 4)) eval_
 			for (int c = 0; c < 4; ++c)
 				*reinterpret_cast<uint4*>(a_row + c * A_PLANE) = make_uint4(enc[4 * c], enc[4 * c + 1], enc[4 * c + 2], enc[4 * c + 3]);
 		}
+		if (GV != 0 && a.tex_split == 8) continue;
 		// ---- (c) density MLP
 		uint32_t w_addr = wd_addr;
 		HN_ROUND(32, 64, w_addr); w_addr += 64 * 32 * 2;

@@ -167,6 +167,9 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 
 // ---- occupancy-grid maintenance from the live network (orc_grid.inc) ----
 void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]);
+// per-image focal [n][2] / principal [n][2] / ELensMode [n] / lens params [n][7] (TrainingImageMetadata); lens arrays may be NULL
+void orc_mark_untrained_grid_per_image(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float* focal, const float* principal,
+	const int32_t* lens_mode, const float* lens_params);
 void orc_update_density_grid(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, float* grid, uint32_t n_cascades, uint32_t ema_step,
 	uint32_t n_uniform, uint32_t n_nonuniform, float decay, uint32_t seed, uint32_t rng_calls);
 uint32_t orc_pcg32(uint64_t seed, uint64_t advance, uint32_t n, uint32_t* out);

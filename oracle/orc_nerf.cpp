@@ -1057,6 +1057,12 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]) {
 	mark_untrained_grid(grid, n_cascades, n_images, cams, w, h, focal, principal);
 }
+void orc_mark_untrained_grid_per_image(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float* focal, const float* principal,
+	const int32_t* lens_mode, const float* lens_params) {
+	ImageCams pc = {focal, principal, lens_mode, lens_params};
+	const float f0[2] = {1.0f, 1.0f}, p0[2] = {0.5f, 0.5f};
+	mark_untrained_grid(grid, n_cascades, n_images, cams, w, h, f0, p0, &pc);
+}
 void orc_update_density_grid(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, float* grid, uint32_t n_cascades, uint32_t ema_step,
 	uint32_t n_uniform, uint32_t n_nonuniform, float decay, uint32_t seed, uint32_t rng_calls) {
 	Net net = make_net(*c, params);

@@ -666,6 +666,9 @@ int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, 
 	const float focal_px[2], const float principal[2]) {
 	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_dataset(ctx, rgba, n_images, width, height, cameras, focal_px, principal); HN_CATCH(ctx)
 }
+int hn_train_set_image_metadata(hn_context* ctx, uint32_t n_images, const float* focal_px, const float* principal, const int32_t* lens_mode, const float* lens_params) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_image_metadata(ctx, n_images, focal_px, principal, lens_mode, lens_params); HN_CATCH(ctx)
+}
 int hn_load_training_data(hn_context* ctx, const char* path) {
 	HN_TRY(ctx) need(path != nullptr, "null path"); HN_CUDA(cudaSetDevice(ctx->device)); load_training_data_file(ctx, path); HN_CATCH(ctx)
 }

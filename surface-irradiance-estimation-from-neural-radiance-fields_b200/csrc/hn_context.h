@@ -121,6 +121,7 @@ struct TrainState {
 	float ms[5] = {0, 0, 0, 0, 0};
 	// dataset
 	DevBuf<float4> images; DevBuf<float> cams;
+	DevBuf<ImageMeta> meta; std::vector<ImageMeta> meta_host; // per-image focal length, principal point, lens
 	uint32_t n_images = 0; int img_w = 0, img_h = 0; float focal[2] = {0, 0}, principal[2] = {0.5f, 0.5f};
 	// parameters
 	DevBuf<float> master, m1, m2, ema, grads;
@@ -265,6 +266,7 @@ void train_release(hn_context* ctx);
 void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps);
 void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n);
 void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
+void train_set_image_metadata(hn_context* ctx, uint32_t n, const float* focal, const float* principal, const int32_t* lens_mode, const float* lens_params);
 void train_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img);
 void train_op_sample_pixels(hn_context* ctx, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step, uint32_t n_images, int cdf_res_x, int cdf_res_y,
 	const float* cdf_x_cond_y, const float* cdf_y, const float* cdf_img, uint32_t* img, float* uv, float* pdf);

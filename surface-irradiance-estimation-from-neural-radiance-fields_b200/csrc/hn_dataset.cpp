@@ -4,8 +4,9 @@
 //   NerfDataset::nerf_matrix_to_ngp include/neural-graphics-primitives/nerf_loader.h:101-120
 //   read_rgba (Byte images)        include/neural-graphics-primitives/common_device.cuh:797-816 (sRGB bytes, straight alpha)
 // The reference decodes images with stb_image; here a PNG reader (8-bit grey / grey+alpha / RGB / RGBA, non-interlaced) sits on
-// the DEFLATE decoder the snapshot reader already has. One resolution and one set of pinhole intrinsics for the whole set
-// (per-frame intrinsics, lens distortion, depth / ray files, EXR and JPEG are not on this path: they raise an error).
+// the DEFLATE decoder the snapshot reader already has. One resolution for the whole set; focal length, principal point and lens
+// (read_lens, :175-241: OpenCV / fisheye coefficients, f-theta polynomial, latlong / equirectangular) per frame over the file-level
+// values, as the reference layers them (:678-696). Depth / ray files, rolling-shutter frame pairs, EXR and JPEG are not on this path.
 #include "hn_context.h"
 #include "hn_json.h"
 #include <cmath>
@@ -108,6 +109,36 @@ float focal_from(const Json& j, int res, const char* axis) {
 	return 0.f;
 }
 
+// read_focal_length (src/nerf_loader.cu:243-271): x_fov | fl_x | camera_angle_x (and y); one axis fills both
+bool read_focal(const Json& j, int w, int h, float focal[2]) {
+	const float fx = focal_from(j, w, "x"), fy = focal_from(j, h, "y");
+	if (fx != 0.f) { focal[0] = focal[1] = fx; if (fy != 0.f) focal[1] = fy; return true; }
+	if (fy != 0.f) { focal[0] = focal[1] = fy; return true; }
+	return false;
+}
+// read_lens (src/nerf_loader.cu:175-241): OpenCV k1 k2 p1 p2 (k3 k4 for is_fisheye), principal point cx / w, cy / h, f-theta polynomial,
+// latlong / equirectangular flags. A json object without lens keys leaves what the outer level set.
+void read_lens(const Json& j, hn::ImageMeta& m) {
+	int mode = 0;
+	const Json* fe = j.find("is_fisheye");
+	const int opencv_mode = (fe && fe->type == Json::Bool && fe->b) ? 4 : 1;
+	auto opencv = [&](const char* name, int idx) {
+		if (const Json* v = j.find(name)) { m.lens_params[idx] = (float)v->num; if (m.lens_params[idx] != 0.f) mode = opencv_mode; }
+	};
+	opencv("k1", 0); opencv("k2", 1); opencv("k3", 2); opencv("k4", 3);
+	opencv("p1", 2); opencv("p2", 3);
+	if (j.contains("cx")) { if (!j.contains("w")) throw std::runtime_error("transforms.json: cx needs w beside it"); m.principal[0] = (float)j.at("cx").num / (float)j.at("w").num; }
+	if (j.contains("cy")) { if (!j.contains("h")) throw std::runtime_error("transforms.json: cy needs h beside it"); m.principal[1] = (float)j.at("cy").num / (float)j.at("h").num; }
+	if (j.contains("ftheta_p0")) {
+		for (int k = 0; k < 5; ++k) m.lens_params[k] = (float)j.at(std::string("ftheta_p") + char('0' + k)).num;
+		m.lens_params[5] = (float)j.at("w").num; m.lens_params[6] = (float)j.at("h").num;
+		mode = 2;
+	}
+	if (j.contains("latlong")) mode = 3;
+	if (j.contains("equirectangular")) mode = 5;
+	if (mode != 0) m.lens_mode = mode; // an outer distortion mode is not overridden by nothing
+}
+
 } // namespace
 
 void load_training_data_file(hn_context* ctx, const std::string& path_in) {
@@ -126,10 +157,10 @@ void load_training_data_file(hn_context* ctx, const std::string& path_in) {
 		if (o->is_array() && o->arr.size() == 3) for (int k = 0; k < 3; ++k) offset[k] = (float)o->arr[k].num;
 		else if (o->type == Json::Number) offset[0] = offset[1] = offset[2] = (float)o->num;
 	}
-	for (const char* key : {"k1", "k2", "p1", "p2", "k3", "k4", "is_fisheye", "ftheta_p0"}) {
-		const Json* v = root.find(key);
-		if (v && ((v->type == Json::Number && v->num != 0.0) || (v->type == Json::Bool && v->b))) throw std::runtime_error(std::string("transforms.json: lens parameter '") + key + "' is not supported on this path (pinhole only)");
-	}
+	hn::ImageMeta global_meta = {};
+	global_meta.principal[0] = global_meta.principal[1] = 0.5f;
+	read_lens(root, global_meta);
+	std::vector<hn::ImageMeta> metas(frames.size(), global_meta);
 	std::vector<float> pixels, cams;
 	int w = 0, h = 0;
 	for (size_t i = 0; i < frames.size(); ++i) {
@@ -139,9 +170,12 @@ void load_training_data_file(hn_context* ctx, const std::string& path_in) {
 		if (!has_extension(fp)) fp += ".png"; // nerf_loader.cu:560-563
 		const std::string ext = lower_ext(fp);
 		if (ext != "png") throw std::runtime_error("image '" + fp + "': only PNG images are supported on this path");
-		for (const char* key : {"fl_x", "fl_y", "camera_angle_x", "camera_angle_y", "x_fov", "y_fov", "cx", "cy", "w", "h"})
-			if (fr.contains(key)) throw std::runtime_error("transforms.json: per-frame intrinsics are not supported on this path");
 		const Image8 img = decode_png(fp[0] == '/' ? fp : base + "/" + fp);
+		// per-frame intrinsics and lens over the file-level ones (nerf_loader.cu:678-696)
+		bool got_fl = read_focal(root, img.w, img.h, metas[i].focal);
+		got_fl |= read_focal(fr, img.w, img.h, metas[i].focal);
+		if (!got_fl) throw std::runtime_error("Couldn't read fov."); // nerf_loader.cu:680-682
+		read_lens(fr, metas[i]);
 		if (i == 0) { w = img.w; h = img.h; pixels.resize(frames.size() * (size_t)w * h * 4); cams.resize(frames.size() * 12); }
 		else if (img.w != w || img.h != h) throw std::runtime_error("training images of different resolutions are not supported on this path");
 		float* dst = pixels.data() + i * (size_t)w * h * 4;
@@ -162,14 +196,7 @@ void load_training_data_file(hn_context* ctx, const std::string& path_in) {
 		float* cam = cams.data() + 12 * i;
 		for (int c = 0; c < 4; ++c) { cam[3 * c + 0] = col[c][1]; cam[3 * c + 1] = col[c][2]; cam[3 * c + 2] = col[c][0]; } // cycle axes xyz <- yzx
 	}
-	float focal[2];
-	const float fx = focal_from(root, w, "x"), fy = focal_from(root, h, "y");
-	if (fx != 0.f) { focal[0] = focal[1] = fx; if (fy != 0.f) focal[1] = fy; }
-	else if (fy != 0.f) focal[0] = focal[1] = fy;
-	else throw std::runtime_error("Couldn't read fov."); // nerf_loader.cu:680-682
-	float principal[2] = {0.5f, 0.5f};
-	if (root.contains("cx")) principal[0] = (float)root.at("cx").num / (float)root.value("w", (double)w);
-	if (root.contains("cy")) principal[1] = (float)root.at("cy").num / (float)root.value("h", (double)h);
+	const float focal[2] = {metas[0].focal[0], metas[0].focal[1]}, principal[2] = {metas[0].principal[0], metas[0].principal[1]};
 	// aabb_scale drives the boxes, cascades and the cone angle exactly as hn_set_aabb_scale does (load_nerf_post, testbed_nerf.cu:2718-2745)
 	const int aabb_scale = (int)root.value("aabb_scale", 1.0);
 	if (aabb_scale < 1 || aabb_scale > 128 || (aabb_scale & (aabb_scale - 1))) throw std::runtime_error("transforms.json: aabb_scale must be a power of two in [1, 128]");
@@ -182,6 +209,17 @@ void load_training_data_file(hn_context* ctx, const std::string& path_in) {
 		}
 	}
 	train_set_dataset(ctx, pixels.data(), (uint32_t)frames.size(), w, h, cams.data(), focal, principal);
+	{
+		const size_t n = frames.size();
+		std::vector<float> f(2 * n), pp(2 * n), lp(7 * n);
+		std::vector<int32_t> lm(n);
+		for (size_t i = 0; i < n; ++i) {
+			f[2 * i] = metas[i].focal[0]; f[2 * i + 1] = metas[i].focal[1]; pp[2 * i] = metas[i].principal[0]; pp[2 * i + 1] = metas[i].principal[1];
+			lm[i] = metas[i].lens_mode;
+			for (int k = 0; k < 7; ++k) lp[7 * i + k] = metas[i].lens_params[k];
+		}
+		train_set_image_metadata(ctx, (uint32_t)n, f.data(), pp.data(), lm.data(), lp.data());
+	}
 	ctx->train.srgb_space = 1; // byte images live in sRGB: the target is blended there (compute_loss_kernel_train_nerf :1031-1037)
 }
 

@@ -205,19 +205,14 @@ __device__ __forceinline__ float2 grid_at_lerp(const float2* __restrict__ data, 
 	return make_float2(w00 * a.x + w10 * b.x + w01 * c.x + w11 * d.x, w00 * a.y + w10 * b.y + w01 * c.y + w11 * d.y);
 }
 
-// uv_to_ray (common_device.cuh:416-483). c0..c2 = camera rotation columns, pos = camera[3]. `use_lens` is false on the mesh pass
-// (its ray init takes foveation and the hidden-area mask but neither Lens nor distortion grid, geometry :520-536).
-// Returns false for an invalid ray (f-theta outside the image circle, or a pixel the mask hides). The direction is NOT normalised.
-__device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, float u_in, float v_in, V3 c0, V3 c1, V3 c2, V3 pos, V3& origin, V3& dir) {
-	V3 d;
-	const int mode = use_lens ? a.lens_mode : 0;
-	float u = u_in, v = v_in; // warped_uv; the depth-of-field pixel hash below keeps the un-warped uv (:470)
-	if (a.foveated) { u = fov_warp(a.fov[0], u_in); v = fov_warp(a.fov[1], v_in); }
-	if (a.hidden_mask && !mask_at(a.hidden_mask, a.hidden_w, a.hidden_h, u, v)) return false;
+// the lens models of uv_to_ray (common_device.cuh:439-463): camera-space direction of (u, v); false = invalid ray (f-theta outside its
+// image circle). mode = ELensMode (0 Perspective, 1 OpenCV, 2 FTheta, 3 LatLong, 4 OpenCVFisheye, 5 Equirectangular). Shared by the
+// render-time camera (camera_ray) and the per-image cameras of the training set (hn_train.cu).
+__device__ __forceinline__ bool lens_direction(int mode, const float* __restrict__ lp, float u, float v, float sc0, float sc1, int w, int h, float f0, float f1, V3& d) {
 	if (mode == 2) {
-		const float xpix = (u - a.screen_center[0]) * a.lens_params[5], ypix = (v - a.screen_center[1]) * a.lens_params[6];
+		const float xpix = (u - sc0) * lp[5], ypix = (v - sc1) * lp[6];
 		const float norm = sqrtf(xpix * xpix + ypix * ypix);
-		const float alpha = a.lens_params[0] + norm * (a.lens_params[1] + norm * (a.lens_params[2] + norm * (a.lens_params[3] + norm * a.lens_params[4])));
+		const float alpha = lp[0] + norm * (lp[1] + norm * (lp[2] + norm * (lp[3] + norm * lp[4])));
 		float sa, ca;
 		sincosf(alpha, &sa, &ca);
 		if (ca <= FLT_MIN || norm == 0.f) return false;
@@ -235,10 +230,23 @@ __device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, fl
 		sincosf(phi, &sp, &cp);
 		d = mk(sp * st, ct, cp * st);
 	} else {
-		d = mk((u - a.screen_center[0]) * (float)a.w / a.focal[0], (v - a.screen_center[1]) * (float)a.h / a.focal[1], 1.0f);
-		if (mode == 1) iterative_undistortion<false>(a.lens_params, &d.x, &d.y);
-		else if (mode == 4) iterative_undistortion<true>(a.lens_params, &d.x, &d.y);
+		d = mk((u - sc0) * (float)w / f0, (v - sc1) * (float)h / f1, 1.0f);
+		if (mode == 1) iterative_undistortion<false>(lp, &d.x, &d.y);
+		else if (mode == 4) iterative_undistortion<true>(lp, &d.x, &d.y);
 	}
+	return true;
+}
+
+// uv_to_ray (common_device.cuh:416-483). c0..c2 = camera rotation columns, pos = camera[3]. `use_lens` is false on the mesh pass
+// (its ray init takes foveation and the hidden-area mask but neither Lens nor distortion grid, geometry :520-536).
+// Returns false for an invalid ray (f-theta outside the image circle, or a pixel the mask hides). The direction is NOT normalised.
+__device__ __forceinline__ bool camera_ray(const FrameArgs& a, bool use_lens, float u_in, float v_in, V3 c0, V3 c1, V3 c2, V3 pos, V3& origin, V3& dir) {
+	V3 d;
+	const int mode = use_lens ? a.lens_mode : 0;
+	float u = u_in, v = v_in; // warped_uv; the depth-of-field pixel hash below keeps the un-warped uv (:470)
+	if (a.foveated) { u = fov_warp(a.fov[0], u_in); v = fov_warp(a.fov[1], v_in); }
+	if (a.hidden_mask && !mask_at(a.hidden_mask, a.hidden_w, a.hidden_h, u, v)) return false;
+	if (!lens_direction(mode, a.lens_params, u, v, a.screen_center[0], a.screen_center[1], a.w, a.h, a.focal[0], a.focal[1], d)) return false;
 	if (use_lens && a.distortion) { const float2 g = grid_at_lerp(a.distortion, a.dist_w, a.dist_h, u, v); d.x += g.x; d.y += g.y; }
 	const V3 head = mk(a.parallax_shift[0], a.parallax_shift[1], 0.0f);
 	d = d - head * a.parallax_shift[2];

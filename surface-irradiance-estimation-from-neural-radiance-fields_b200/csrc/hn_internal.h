@@ -90,6 +90,14 @@ struct FrameArgs {
 	int probe_n_theta, probe_n_phi, env_source, env_sampling;
 };
 
+// per-image camera of the training set (TrainingImageMetadata, nerf.h: focal_length, principal_point, lens)
+struct ImageMeta {
+	float focal[2];       // pixels
+	float principal[2];   // fraction of the image
+	int lens_mode;        // ELensMode
+	float lens_params[7];
+};
+
 // mesh hits that gather environment light: filled by the mesh pass (one entry per shaded triangle hit, warp-aggregated append)
 struct EnvHits {
 	float4* pos_pix;   // hit position (already offset along the facing normal), pixel index bits in .w

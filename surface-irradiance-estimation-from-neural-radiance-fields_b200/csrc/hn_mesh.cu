@@ -127,6 +127,27 @@ __device__ void scene_nearest(const SceneDev& sc, int compat, V3 o, V3 d, Hit& h
 	touched = true;
 	for (uint32_t i = 0; i < sc.n_meshes; ++i) traverse_mesh(sc, (int)i, o, d, h, stack);
 }
+// scene_nearest for a ray of which only "is anything hit, and is that point inside the shading box" is asked (the sun shadow ray,
+// write_shadow_ray_result_geometry): the same mesh choice, the traversal stops at the first accepted triangle. Every triangle lies inside
+// the mesh box, which lies inside the shading box, so the answer is the nearest-hit search's.
+__device__ void scene_any(const SceneDev& sc, int compat, V3 o, V3 d, Hit& h, bool& touched, int* stack) {
+	h.t = MAX_DIST_F; h.mesh = -1; h.tri = -1; h.slot = 0;
+	touched = false;
+	if (compat) {
+		float mint = MAX_DIST_F; int mesh = -1;
+		for (uint32_t i = 0; i < sc.n_meshes; ++i) {
+			Box b = ldbox(sc.meshes[i].bb);
+			float2 tt = box_ray_intersect(b, o, d);
+			if (tt.x < mint && tt.x > -FLT_MAX) { mint = tt.x; mesh = (int)i; }
+		}
+		if (mesh < 0) return;
+		touched = true;
+		traverse_mesh<true>(sc, mesh, o, d, h, stack);
+		return;
+	}
+	touched = true;
+	for (uint32_t i = 0; i < sc.n_meshes; ++i) if (traverse_mesh<true>(sc, (int)i, o, d, h, stack)) return;
+}
 
 __global__ void __launch_bounds__(MESH_BLOCK) trace_kernel(SceneDev sc, int compat, uint32_t n, const float* __restrict__ o_in, const float* __restrict__ d_in,
 	int32_t* __restrict__ mesh_out, int32_t* __restrict__ tri_out, float* __restrict__ t_out) {
@@ -401,7 +422,7 @@ __device__ bool mesh_pixel(const FrameArgs& a, const SceneDev& sc, float4* __res
 		view_pos = view_pos + ts * sun;
 		const V3 sdir = box_contains(aabb, view_pos) ? sun : dir; // an origin outside the box keeps payload.dir (:239-244)
 		Hit sh; bool st;
-		scene_nearest(sc, a.compat_nearest_aabb_only, view_pos, sdir, sh, st, stack);
+		scene_any(sc, a.compat_nearest_aabb_only, view_pos, sdir, sh, st, stack);
 		const V3 end = st ? view_pos + sh.t * sdir : view_pos;
 		shadow = box_contains(aabb, end) ? 0.0f : 1.0f; // write_shadow_ray_result_geometry
 	}

@@ -56,7 +56,8 @@ struct Pcg32 {
 
 struct TrainDataDev {
 	const float4* images; const float* cams;
-	uint32_t n_images; int w, h; float focal[2], principal[2];
+	uint32_t n_images; int w, h;
+	const ImageMeta* meta; // [n_images] focal length, principal point and lens of every image (TrainingImageMetadata)
 };
 
 // ---- error map (src/testbed_nerf.cu:1080-1106, 1776-1832, 2986-3075; nerf_device.cuh:536-633) ----
@@ -169,8 +170,12 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 	if (random_bg) { bg[0] = rng.next_float(); bg[1] = rng.next_float(); bg[2] = rng.next_float(); }
 	const float4 tex = __ldg(D.images + ((size_t)img * D.h + py) * D.w + px);
 	const float* c = D.cams + 12 * img;
-	float dx = (uu - D.principal[0]) * (float)D.w / D.focal[0], dy = (vv - D.principal[1]) * (float)D.h / D.focal[1];
-	float d0 = c[0] * dx + c[3] * dy + c[6], d1 = c[1] * dx + c[4] * dy + c[7], d2 = c[2] * dx + c[5] * dy + c[8];
+	// uv_to_ray with the image's own focal length, principal point and lens (generate_training_samples_nerf, src/testbed_nerf.cu:806-808)
+	const ImageMeta m = D.meta[img];
+	V3 dc;
+	const bool valid_ray = lens_direction(m.lens_mode, m.lens_params, uu, vv, m.principal[0], m.principal[1], D.w, D.h, m.focal[0], m.focal[1], dc);
+	if (!valid_ray) dc = mk(0.f, 0.f, 1.f);
+	float d0 = c[0] * dc.x + c[3] * dc.y + c[6] * dc.z, d1 = c[1] * dc.x + c[4] * dc.y + c[7] * dc.z, d2 = c[2] * dc.x + c[5] * dc.y + c[8] * dc.z;
 	const float inv = rsqrtf(d0 * d0 + d1 * d1 + d2 * d2);
 	d0 *= inv; d1 *= inv; d2 *= inv;
 	ray_o[3 * i] = c[9]; ray_o[3 * i + 1] = c[10]; ray_o[3 * i + 2] = c[11];
@@ -185,7 +190,7 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 		tmin = fmaxf(tmin, fminf(t0, t1)); tmax = fminf(tmax, fmaxf(t0, t1));
 	}
 	const float step_sz = HN_MIN_STEP; // cone angle 0 (aabb_scale 1); larger scenes start a fraction of the local step later
-	ray_t[i] = tmin <= tmax ? fmaxf(tmin, 0.0f) + jitter * step_sz : 3.0e4f; // beyond MAX_DEPTH: the march finds nothing
+	ray_t[i] = (tmin <= tmax && valid_ray) ? fmaxf(tmin, 0.0f) + jitter * step_sz : 3.0e4f; // beyond MAX_DEPTH: the march finds nothing (:812-815 drops invalid rays)
 	#pragma unroll
 	for (int k = 0; k < 3; ++k) {
 		const float texc = k == 0 ? tex.x : (k == 1 ? tex.y : tex.z);
@@ -520,14 +525,33 @@ __global__ void mark_untrained_kernel(uint32_t n_elements, float* __restrict__ g
 	bool seen = false;
 	for (uint32_t j = 0; j < D.n_images && !seen; ++j) {
 		const float* c = D.cams + 12 * j;
+		const ImageMeta m = D.meta[j];
+		// lenses without a forward mapping (f-theta) or that see everything (lat-long, equirectangular) count as seeing the cell (:115-120)
+		if (m.lens_mode == 2 || m.lens_mode == 3 || m.lens_mode == 5) { seen = true; break; }
 		for (uint32_t k = 0; k < 8 && !seen; ++k) {
 			const float rx = px + ((k & 1) ? voxel : 0.f) - c[9], ry = py + ((k & 2) ? voxel : 0.f) - c[10], rz = pz + ((k & 4) ? voxel : 0.f) - c[11];
 			const float len = sqrtf(rx * rx + ry * ry + rz * rz);
 			const float cz = rx * c[6] + ry * c[7] + rz * c[8];
 			if (cz / len < 1e-4f) continue;
 			const float cx = rx * c[0] + ry * c[1] + rz * c[2], cy = rx * c[3] + ry * c[4] + rz * c[5];
-			const float u = cx / cz * D.focal[0] / (float)D.w + D.principal[0], v = cy / cz * D.focal[1] / (float)D.h + D.principal[1];
-			if (u > 0.f && v > 0.f && u < 1.f && v < 1.f) seen = true;
+			float ux = cx / cz, uy = cy / cz;
+			if (m.lens_mode == 1 || m.lens_mode == 4) { // pos_to_uv adds the lens's distortion delta (common_device.cuh:521-531)
+				float du, dv;
+				if (m.lens_mode == 1) opencv_distortion_delta(m.lens_params, ux, uy, &du, &dv); else fisheye_distortion_delta(m.lens_params, ux, uy, &du, &dv);
+				ux += du; uy += dv;
+			}
+			const float u = ux * m.focal[0] / (float)D.w + m.principal[0], v = uy * m.focal[1] / (float)D.h + m.principal[1];
+			if (!(u > 0.f && v > 0.f && u < 1.f && v < 1.f)) continue;
+			if (m.lens_mode == 1 || m.lens_mode == 4) {
+				// pos_to_uv is not injective under lens distortion: the ray of that uv must point back at the corner (:131-137)
+				V3 dc;
+				lens_direction(m.lens_mode, m.lens_params, u, v, m.principal[0], m.principal[1], D.w, D.h, m.focal[0], m.focal[1], dc);
+				float bx = c[0] * dc.x + c[3] * dc.y + c[6] * dc.z, by = c[1] * dc.x + c[4] * dc.y + c[7] * dc.z, bz = c[2] * dc.x + c[5] * dc.y + c[8] * dc.z;
+				const float bl = sqrtf(bx * bx + by * by + bz * bz);
+				bx = bx / bl - rx / len; by = by / bl - ry / len; bz = bz / bl - rz / len;
+				if (!(sqrtf(bx * bx + by * by + bz * bz) < 1e-3f)) continue;
+			}
+			seen = true;
 		}
 	}
 	grid[i] = seen ? 0.f : -1.f;
@@ -765,8 +789,34 @@ void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, in
 	HN_CUDA(cudaMemcpy(t.cams.p, cams, (size_t)n * 12 * sizeof(float), cudaMemcpyHostToDevice));
 	t.n_images = n; t.img_w = w; t.img_h = h;
 	t.focal[0] = focal[0]; t.focal[1] = focal[1]; t.principal[0] = principal[0]; t.principal[1] = principal[1];
+	{ // every image starts with the shared pinhole camera; hn_train_set_image_metadata / the loader refine it per image
+		ImageMeta m = {};
+		m.focal[0] = focal[0]; m.focal[1] = focal[1]; m.principal[0] = principal[0]; m.principal[1] = principal[1];
+		t.meta_host.assign(n, m);
+		t.meta.ensure(n);
+		HN_CUDA(cudaMemcpy(t.meta.p, t.meta_host.data(), (size_t)n * sizeof(ImageMeta), cudaMemcpyHostToDevice));
+	}
 	t.has_dataset = true;
 	t.srgb_space = 0;
+}
+
+// TrainingImageMetadata per image (nerf.h; read_focal_length / read_lens of the loader, src/nerf_loader.cu:175-271,678-696)
+void train_set_image_metadata(hn_context* ctx, uint32_t n, const float* focal, const float* principal, const int32_t* lens_mode, const float* lens_params) {
+	TrainState& t = ctx->train;
+	if (!t.has_dataset || n != t.n_images) throw std::runtime_error("image metadata: set the dataset first, one entry per image");
+	if (!focal) throw std::runtime_error("image metadata: focal lengths are required");
+	for (uint32_t i = 0; i < n; ++i) {
+		ImageMeta& m = t.meta_host[i];
+		m.focal[0] = focal[2 * i]; m.focal[1] = focal[2 * i + 1];
+		if (!(m.focal[0] > 0.f) || !(m.focal[1] > 0.f)) throw std::runtime_error("image metadata: focal lengths must be positive");
+		if (principal) { m.principal[0] = principal[2 * i]; m.principal[1] = principal[2 * i + 1]; }
+		if (lens_mode) {
+			if (lens_mode[i] < 0 || lens_mode[i] > 5) throw std::runtime_error("image metadata: lens mode must be an ELensMode (0..5)");
+			m.lens_mode = lens_mode[i];
+		}
+		if (lens_params) for (int k = 0; k < 7; ++k) m.lens_params[k] = lens_params[7 * i + k];
+	}
+	HN_CUDA(cudaMemcpy(t.meta.p, t.meta_host.data(), (size_t)n * sizeof(ImageMeta), cudaMemcpyHostToDevice));
 }
 
 void train_init(hn_context* ctx, uint32_t seed) {
@@ -809,7 +859,7 @@ void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
 	const uint32_t max_samples = c.target_batch * 2u;
 	ensure_batch(ctx, n_rays, max_samples);
 	FrameArgs a = train_frame_args(ctx);
-	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
+	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, t.meta.p};
 	const float* bg = ctx->opt.background_color;
 	// error map: a fresh, zeroed map whenever a new accumulation period starts (train_nerf, src/testbed_nerf.cu:2986-2992); each rank keeps its own
 	if (t.n_steps_since_error_map_update == 0) {
@@ -938,7 +988,7 @@ void train_mark_untrained(hn_context* ctx) {
 	const uint32_t n_cascades = (uint32_t)ctx->opt.max_cascade + 1u, n_elements = GRID_CELLS * n_cascades;
 	ctx->density_grid.ensure(n_elements);
 	ctx->grid_cascades = n_cascades;
-	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, {t.focal[0], t.focal[1]}, {t.principal[0], t.principal[1]}};
+	TrainDataDev D = {t.images.p, t.cams.p, t.n_images, t.img_w, t.img_h, t.meta.p};
 	mark_untrained_kernel<<<blocks(n_elements), 256, 0, ctx->stream>>>(n_elements, ctx->density_grid.p, D);
 	t.grid_ema_step = 0;
 	HN_CUDA(cudaGetLastError());

@@ -74,7 +74,7 @@ EXPORTS = [
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
     "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
-    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation",
+    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -102,6 +102,7 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_train_set_image_metadata.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_set_hidden_area_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
 _lib.hn_set_distortion_map.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
 _lib.hn_unwarp_foveated.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -479,6 +480,15 @@ class Testbed:
         f = _f32(np.broadcast_to(np.asarray(focal_px, np.float32), (2,)).copy())
         pp = _f32(principal)
         self._check(_lib.hn_train_set_dataset(self._h, _ptr(im), im.shape[0], im.shape[2], im.shape[1], _ptr(cams), _ptr(f), _ptr(pp)))
+
+    def set_image_metadata(self, focal_px, principal=None, lens_mode=None, lens_params=None):
+        """per-image cameras after set_training_data: focal_px [n][2], principal [n][2], lens_mode [n] (ELensMode), lens_params [n][7]"""
+        f = _f32(focal_px).reshape(-1, 2)
+        pp = _f32(principal).reshape(-1, 2) if principal is not None else None
+        lm = np.ascontiguousarray(lens_mode, np.int32).reshape(-1) if lens_mode is not None else None
+        lp = _f32(lens_params).reshape(-1, 7) if lens_params is not None else None
+        self._check(_lib.hn_train_set_image_metadata(self._h, f.shape[0], _ptr(f), _ptr(pp) if pp is not None else None, _ptr(lm) if lm is not None else None,
+                                                     _ptr(lp) if lp is not None else None))
 
     def load_training_data(self, path: str):
         """pyngp Testbed.load_training_data (src/python_api.cu:409): transforms.json (or its folder) with PNG frames."""

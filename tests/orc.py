@@ -392,6 +392,17 @@ def mark_untrained_grid(n_cascades, cams, w, h, focal, principal=(0.5, 0.5)):
     return g
 
 
+def mark_untrained_grid_per_image(n_cascades, cams, w, h, focal, principal, lens_mode=None, lens_params=None):
+    g = np.zeros(128 ** 3 * n_cascades, np.float32)
+    c = np.ascontiguousarray(cams, np.float32).reshape(-1, 12)
+    f, pp = np.ascontiguousarray(focal, np.float32).reshape(-1, 2), np.ascontiguousarray(principal, np.float32).reshape(-1, 2)
+    lm = np.ascontiguousarray(lens_mode, np.int32) if lens_mode is not None else None
+    lp = np.ascontiguousarray(lens_params, np.float32).reshape(-1, 7) if lens_params is not None else None
+    lib.orc_mark_untrained_grid_per_image.argtypes = [C.c_void_p, u32, u32, C.c_void_p, i32, i32] + [C.c_void_p] * 4
+    lib.orc_mark_untrained_grid_per_image(P(g), n_cascades, c.shape[0], P(c), w, h, P(f), P(pp), P(lm) if lm is not None else None, P(lp) if lp is not None else None)
+    return g
+
+
 def render_frame(p: RenderParams, cfg, params, bits, scene: Scene | None):
     n = p.width * p.height
     frame = np.zeros((p.height, p.width, 4), np.float32)

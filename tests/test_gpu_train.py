@@ -320,3 +320,91 @@ def test_load_training_data_transforms_json_png(hn, root, tmp_path):
     assert abs(l_png - l_f32) <= 2e-5 * max(abs(l_f32), 1e-6) + 1e-7, (l_png, l_f32)
     with pytest.raises(RuntimeError):
         tb_png.load_training_data(str(tmp_path / "missing"))
+
+
+def test_per_image_cameras_mark_untrained_and_rays(hn, orc, root):
+    """TrainingImageMetadata per image (hn_train_set_image_metadata): mark_untrained_density_grid projects every cell corner with the image's
+    own focal length, principal point and lens (src/testbed_nerf.cu:111-139), the training rays go through it (:806-808)."""
+    imgs, _, focal = hn.synthetic.sphere_dataset(3, 32)
+    cams = np.stack([np.asarray(hn.synthetic.look_at_camera((0.5, 0.5, 0.95), (0.5, 0.5, 0.5)), f32).reshape(12),
+                     np.asarray(hn.synthetic.look_at_camera((0.1, 0.6, 0.4), (0.6, 0.5, 0.5)), f32).reshape(12),
+                     np.asarray(hn.synthetic.look_at_camera((0.9, 0.2, 0.3), (0.5, 0.5, 0.6)), f32).reshape(12)])
+    tb, _, _ = nerf_setup(hn, root, 0.5)
+    tb.set_training_data(imgs, cams, focal)
+    f = np.array([[focal, focal], [2.5 * focal, 2.0 * focal], [1.5 * focal, 1.5 * focal]], f32)      # a tele view among them
+    pp = np.array([[0.5, 0.5], [0.4, 0.55], [0.5, 0.5]], f32)
+    lm = np.array([0, 0, 1], np.int32)                                                                 # the third image through an OpenCV lens
+    lp = np.zeros((3, 7), f32); lp[2, :4] = [0.08, -0.03, 0.002, -0.001]
+    tb.set_image_metadata(f, pp, lm, lp)
+    tb.mark_untrained_density_grid()
+    got = tb.get_density_grid(1)
+    want = orc.mark_untrained_grid_per_image(1, cams, 32, 32, f, pp, lm, lp)
+    shared = orc.mark_untrained_grid(1, cams, 32, 32, focal)
+    assert np.mean(got == want) > 0.9995 and np.mean(want != shared) > 0.01   # the narrower frusta see fewer cells
+    # a lat-long image sees everything
+    tb.set_image_metadata(f, pp, np.array([0, 3, 0], np.int32), lp)
+    tb.mark_untrained_density_grid()
+    assert np.all(tb.get_density_grid(1) == 0.0)
+    with pytest.raises(RuntimeError):
+        tb.set_image_metadata(f[:2])
+    # rays: with all images given the SAME intrinsics explicitly, a step equals the shared-pinhole step bit for bit; a different focal length changes it
+    def first_loss(meta):
+        t, _, _ = nerf_setup(hn, root, 0.3)
+        t.set_option("train_auto_grid", 0.0)
+        t.set_training_data(imgs, cams, focal)
+        if meta is not None:
+            t.set_image_metadata(*meta)
+        t.reset_trainer(5)
+        return t.train_accumulate(1024), t.train_stats().n_samples_last
+    base = first_loss(None)
+    same = first_loss((np.full((3, 2), focal, f32), np.full((3, 2), 0.5, f32), np.zeros(3, np.int32), np.zeros((3, 7), f32)))
+    tele = first_loss((f, pp, lm, lp))
+    assert same == base and tele != base and np.isfinite(tele[0])
+
+
+def test_loader_per_frame_intrinsics_and_lens(hn, root, tmp_path):
+    """read_focal_length / read_lens per frame over the file-level values (src/nerf_loader.cu:175-271,678-696): the loaded set trains
+    exactly like the same images with hn_train_set_image_metadata called by hand."""
+    import json
+    n, res = 4, 32
+    imgs, cams, focal = hn.synthetic.sphere_dataset(n, res)
+    rgba8 = np.concatenate([np.round(np.clip(imgs[..., :3], 0, 1) * 255), np.round(imgs[..., 3:4] * 255)], -1).astype(np.uint8)
+    frames = []
+    for i in range(n):
+        _write_png(str(tmp_path / f"r_{i}.png"), rgba8[i], None)
+        c = cams[i].reshape(4, 3).astype(np.float64)
+        col = np.stack([c[:, 2], c[:, 0], c[:, 1]], 1)
+        col[1] *= -1; col[2] *= -1
+        col[3] = (col[3] - 0.5) / 0.33
+        m = np.eye(4); m[:3, :4] = col.T
+        frames.append({"file_path": f"r_{i}.png", "transform_matrix": m.tolist()})
+    frames[1].update({"fl_x": 60.0, "fl_y": 55.0, "cx": 14.0, "cy": 18.0, "w": res, "h": res})
+    frames[2].update({"k1": 0.05, "k2": -0.01, "p1": 0.001, "p2": 0.002})
+    frames[3].update({"is_fisheye": True, "k1": 0.02, "k2": 0.01, "k3": 0.0, "k4": 0.001, "camera_angle_x": 1.1})
+    meta = {"fl_x": float(focal), "aabb_scale": 1, "k1": 0.01, "frames": frames}   # a file-level OpenCV lens that frames inherit
+    (tmp_path / "transforms.json").write_text(json.dumps(meta))
+    lin = np.where(rgba8[..., :3] / 255.0 <= 0.04045, rgba8[..., :3] / 255.0 / 12.92, np.power((rgba8[..., :3] / 255.0 + 0.055) / 1.055, 2.4))
+    q = np.concatenate([lin, rgba8[..., 3:4] / 255.0], -1).astype(f32)
+    fl3 = 0.5 * res / np.tan(0.5 * 1.1)
+    f = np.array([[focal, focal], [60.0, 55.0], [focal, focal], [fl3, fl3]], f32)
+    pp = np.array([[0.5, 0.5], [14.0 / res, 18.0 / res], [0.5, 0.5], [0.5, 0.5]], f32)
+    lm = np.array([1, 1, 1, 4], np.int32)
+    lp = np.zeros((n, 7), f32)
+    lp[0, 0] = 0.01; lp[1, 0] = 0.01; lp[2, :4] = [0.05, -0.01, 0.001, 0.002]; lp[3, :4] = [0.02, 0.01, 0.0, 0.001]
+
+    def first_loss(loader):
+        tb, _, _ = nerf_setup(hn, root, 0.3)
+        tb.set_option("train_auto_grid", 0.0)
+        loader(tb)
+        tb.reset_trainer(5)
+        return tb.train_accumulate(1024), tb.train_stats().n_samples_last
+
+    def by_hand(tb):
+        tb.set_training_data(q, cams, focal)
+        tb.set_image_metadata(f, pp, lm, lp)
+    l_file, n_file = first_loss(lambda tb: tb.load_training_data(str(tmp_path)))
+    l_hand, n_hand = first_loss(by_hand)
+    assert n_file == n_hand and n_file > 5000
+    assert abs(l_file - l_hand) <= 2e-5 * max(abs(l_hand), 1e-6) + 1e-7, (l_file, l_hand)
+    l_plain, _ = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
+    assert abs(l_plain - l_file) > 1e-6      # the per-frame cameras are really in use

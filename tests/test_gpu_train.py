@@ -347,7 +347,7 @@ def test_per_image_cameras_mark_untrained_and_rays(hn, orc, root):
     assert np.all(tb.get_density_grid(1) == 0.0)
     with pytest.raises(RuntimeError):
         tb.set_image_metadata(f[:2])
-    # rays: with all images given the SAME intrinsics explicitly, a step equals the shared-pinhole step bit for bit; a different focal length changes it
+    # rays: with all images given the SAME intrinsics explicitly a step equals the shared-pinhole step (same rays, same samples); other cameras change it
     def first_loss(meta):
         t, _, _ = nerf_setup(hn, root, 0.3)
         t.set_option("train_auto_grid", 0.0)
@@ -359,7 +359,9 @@ def test_per_image_cameras_mark_untrained_and_rays(hn, orc, root):
     base = first_loss(None)
     same = first_loss((np.full((3, 2), focal, f32), np.full((3, 2), 0.5, f32), np.zeros(3, np.int32), np.zeros((3, 7), f32)))
     tele = first_loss((f, pp, lm, lp))
-    assert same == base and tele != base and np.isfinite(tele[0])
+    # (the loss is a sum of float atomics: equal up to the order of the additions)
+    assert same[1] == base[1] and abs(same[0] - base[0]) <= 1e-5 * base[0]
+    assert tele[1] != base[1] and abs(tele[0] - base[0]) > 1e-4 * base[0] and np.isfinite(tele[0])
 
 
 def test_loader_per_frame_intrinsics_and_lens(hn, root, tmp_path):
@@ -404,7 +406,9 @@ def test_loader_per_frame_intrinsics_and_lens(hn, root, tmp_path):
         tb.set_image_metadata(f, pp, lm, lp)
     l_file, n_file = first_loss(lambda tb: tb.load_training_data(str(tmp_path)))
     l_hand, n_hand = first_loss(by_hand)
-    assert n_file == n_hand and n_file > 5000
-    assert abs(l_file - l_hand) <= 2e-5 * max(abs(l_hand), 1e-6) + 1e-7, (l_file, l_hand)
-    l_plain, _ = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
-    assert abs(l_plain - l_file) > 1e-6      # the per-frame cameras are really in use
+    # the loader derives frame 3's focal length from camera_angle_x in float32 (through degrees, like the reference), this test in
+    # float64: the two sets may differ by a sample on a cell boundary
+    assert abs(n_file - n_hand) <= 4 and n_file > 5000
+    assert abs(l_file - l_hand) <= 1e-3 * max(abs(l_hand), 1e-6), (l_file, l_hand)
+    l_plain, n_plain = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
+    assert abs(n_plain - n_file) > 100 and abs(l_plain - l_file) > 10 * abs(l_file - l_hand) + 1e-6      # the per-frame cameras are really in use

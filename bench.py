@@ -520,6 +520,9 @@ def main():
     hn = importlib.import_module("surface-irradiance-estimation-from-neural-radiance-fields_b200")
     mesh, grid, cam = build_scene_inputs(hn)
     tb = hn.Testbed(device=local)
+    for kv in args.opt:  # options that act at scene-build time (bvh_sah) are set before the scene is built; all are applied again below
+        k, v = kv.split("=")
+        tb.set_option(k, [float(x) for x in v.split(",")])
     tb.reload_network_from_file(os.path.join(ROOT, "configs", "nerf", "base.json"))
     info = tb.network_info()
     tb.set_params(hn.synthetic.random_params(info, 1337, 1e-4))

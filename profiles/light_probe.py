@@ -9,6 +9,8 @@ hn = importlib.import_module("surface-irradiance-estimation-from-neural-radiance
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 5
 W, H = 3840, 2160
 tb = hn.Testbed(device=0)
+for kv in sys.argv[(3 if "shard" in __file__ else 2):]:   # options that act at scene-build time (bvh_sah) must be set before build_scene
+    k, v = kv.split("="); tb.set_option(k, float(v))
 tb.reload_network_from_file(os.path.join(ROOT, "configs", "nerf", "base.json"))
 info = tb.network_info()
 tb.set_params(hn.synthetic.random_params(info, 1337, 1e-4))

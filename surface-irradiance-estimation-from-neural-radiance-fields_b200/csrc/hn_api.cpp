@@ -241,7 +241,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"sample_focal_plane_proportional_to_error", {&c->train_cfg.sample_focal_plane_proportional_to_error, 1, true}},
 		{"sample_image_proportional_to_error", {&c->train_cfg.sample_image_proportional_to_error, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
-		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}}, {"bvh_sah", {&o.bvh_sah, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {

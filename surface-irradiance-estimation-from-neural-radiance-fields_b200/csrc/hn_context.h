@@ -92,6 +92,7 @@ struct Options {
 	int env_light_sampling = 0;                 // 0 = cosine hemisphere around the normal, 1 = uniform spherical cap around the direction to the NeRF (probe source)
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
 	int env_light_batch = 32 << 20;             // light rays in flight per batch (bounds the workspace: ~200 bytes per ray)
+	int bvh_sah = 1;                            // BVH build: 1 = binned surface-area heuristic, 0 = the reference's median split (A/B); read by hn_build_scene
 	int march_simple = 1;                       // 1: compile-time specialised raygen / march kernels when cone angle 0, one cascade, axis-aligned crop (A/B)
 	int tight_t_far = 1;                        // 1: rays are cut off at the last flagged coarse occupancy cell (occ_t_far_tight), 0: at the box of the set cells (A/B)
 	int mesh_aabb_user = 0;

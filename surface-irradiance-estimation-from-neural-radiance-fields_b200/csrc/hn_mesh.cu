@@ -15,7 +15,7 @@
 namespace hn {
 
 constexpr int MESH_BLOCK = 128;
-constexpr int STACK_DEPTH = 40;
+constexpr int STACK_DEPTH = 64; // the surface-area-heuristic tree is less balanced than the median one: deeper stacks (32 KB of shared memory per block)
 
 struct Hit { float t; int mesh; int tri; uint32_t slot; }; // tri = ORIGINAL triangle index, slot = position in the leaf-ordered array
 

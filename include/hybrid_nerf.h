@@ -128,12 +128,17 @@ int hn_op_transmittance(hn_context* ctx, uint32_t n_rays, const float* origins, 
 int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, int width, int height, const float* cameras,
 	const float focal_px[2], const float principal[2]);
 /* Testbed::load_training_data(path) (testbed.h:600, src/testbed_nerf.cu:2674-2716 -> load_nerf, src/nerf_loader.cu:273-770):
- * a transforms.json (or the folder holding one) with 8-bit PNG frames: camera matrices through nerf_matrix_to_ngp (scale 0.33,
+ * a transforms.json (or the folder holding one) with 8-bit PNG or baseline-JPEG frames: camera matrices through nerf_matrix_to_ngp (scale 0.33,
  * offset 0.5), aabb_scale; focal length from x_fov | fl_x | camera_angle_x (and y), principal point cx / w, cy / h and the lens
  * (read_lens, :175-241: k1 k2 p1 p2 / is_fisheye k1..k4, ftheta_p0..4, latlong, equirectangular) at file level AND per frame, the
  * frame's values over the file's (:678-696). One resolution for all frames; JPEG / EXR, depth or ray files and rolling-shutter
  * frame pairs are errors / ignored. Call it before hn_set_params when aabb_scale != 1: a new aabb_scale re-derives the network layout. */
 int hn_load_training_data(hn_context* ctx, const char* transforms_json_or_dir);
+/* The loader's image decoder on its own (stbi_load(path, &w, &h, &comp, 4) in src/nerf_loader.cu:575-590): 8-bit PNG (grey, grey + alpha,
+ * RGB, RGBA, non-interlaced) or baseline / extended-sequential JPEG (grey, YCbCr, Adobe RGB; any sampling up to 4:1, restart intervals)
+ * -> RGBA8, row-major. Needs no context and no GPU. rgba may be NULL to query the size; on failure returns 1 and writes the reason to
+ * `error`. EXR and progressive JPEG are not read. */
+int hn_decode_image_file(const char* path, int* width, int* height, uint8_t* rgba, size_t capacity_bytes, char* error, size_t error_capacity);
 /* TrainingImageMetadata of every image after hn_train_set_dataset (which gives all images one pinhole): focal_px [n][2], principal [n][2]
  * (may be NULL = keep), lens_mode [n] = ELensMode 0..5 (may be NULL), lens_params [n][7] (may be NULL). Training rays go through the
  * image's own lens (generate_training_samples_nerf, src/testbed_nerf.cu:806-808); mark_untrained_density_grid projects with it (:111-139). */

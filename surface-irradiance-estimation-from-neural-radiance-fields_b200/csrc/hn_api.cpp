@@ -669,6 +669,21 @@ int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, 
 int hn_train_set_image_metadata(hn_context* ctx, uint32_t n_images, const float* focal_px, const float* principal, const int32_t* lens_mode, const float* lens_params) {
 	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_image_metadata(ctx, n_images, focal_px, principal, lens_mode, lens_params); HN_CATCH(ctx)
 }
+int hn_decode_image_file(const char* path, int* width, int* height, uint8_t* rgba, size_t capacity_bytes, char* error, size_t error_capacity) {
+	try {
+		if (!path || !width || !height) throw std::runtime_error("bad arguments");
+		std::vector<uint8_t> px;
+		decode_image_file(path, *width, *height, px);
+		if (rgba) {
+			if (capacity_bytes < px.size()) throw std::runtime_error("pixel buffer too small");
+			std::memcpy(rgba, px.data(), px.size());
+		}
+		return 0;
+	} catch (const std::exception& e) {
+		if (error && error_capacity) { std::strncpy(error, e.what(), error_capacity - 1); error[error_capacity - 1] = 0; }
+		return 1;
+	}
+}
 int hn_load_training_data(hn_context* ctx, const char* path) {
 	HN_TRY(ctx) need(path != nullptr, "null path"); HN_CUDA(cudaSetDevice(ctx->device)); load_training_data_file(ctx, path); HN_CATCH(ctx)
 }

@@ -266,6 +266,8 @@ void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const 
 void train_release(hn_context* ctx);
 void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps);
 void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n);
+void decode_jpeg(const std::string& path, const std::string& file_bytes, int& w, int& h, std::vector<uint8_t>& rgba); // hn_jpeg.cpp
+void decode_image_file(const std::string& path, int& w, int& h, std::vector<uint8_t>& rgba);                        // hn_dataset.cpp: PNG or JPEG by content
 void train_update_density_grid(hn_context* ctx, float decay, uint32_t n_uniform, uint32_t n_nonuniform);
 void train_set_image_metadata(hn_context* ctx, uint32_t n, const float* focal, const float* principal, const int32_t* lens_mode, const float* lens_params);
 void train_op_error_map_cdf(hn_context* ctx, uint32_t n_images, uint32_t height, uint32_t width, const float* data, float* cdf_x_cond_y, float* cdf_y, float* cdf_img, float* pmf_img);

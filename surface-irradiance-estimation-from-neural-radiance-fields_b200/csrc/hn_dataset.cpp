@@ -4,7 +4,7 @@
 //   NerfDataset::nerf_matrix_to_ngp include/neural-graphics-primitives/nerf_loader.h:101-120
 //   read_rgba (Byte images)        include/neural-graphics-primitives/common_device.cuh:797-816 (sRGB bytes, straight alpha)
 // The reference decodes images with stb_image; here a PNG reader (8-bit grey / grey+alpha / RGB / RGBA, non-interlaced) sits on
-// the DEFLATE decoder the snapshot reader already has. One resolution for the whole set; focal length, principal point and lens
+// the DEFLATE decoder the snapshot reader already has, and hn_jpeg.cpp reads baseline / sequential JPEG. One resolution for the whole set; focal length, principal point and lens
 // (read_lens, :175-241: OpenCV / fisheye coefficients, f-theta polynomial, latlong / equirectangular) per frame over the file-level
 // values, as the reference layers them (:678-696). Depth / ray files, rolling-shutter frame pairs, EXR and JPEG are not on this path.
 #include "hn_context.h"
@@ -82,6 +82,16 @@ Image8 decode_png(const std::string& path) {
 	}
 	return img;
 }
+
+} // namespace
+// 8-bit image file -> RGBA8 (stbi_load(path, ..., 4) of the reference's loader): PNG or JPEG, told apart by their signatures
+void decode_image_file(const std::string& path, int& w, int& h, std::vector<uint8_t>& rgba) {
+	const std::string f = read_text_file(path);
+	if (f.size() >= 2 && (uint8_t)f[0] == 0xFF && (uint8_t)f[1] == 0xD8) { decode_jpeg(path, f, w, h, rgba); return; }
+	Image8 img = decode_png(path);
+	w = img.w; h = img.h; rgba.swap(img.rgba);
+}
+namespace {
 
 float srgb_to_linear_host(float s) { return s <= 0.04045f ? s / 12.92f : std::pow((s + 0.055f) / 1.055f, 2.4f); }
 
@@ -169,8 +179,9 @@ void load_training_data_file(hn_context* ctx, const std::string& path_in) {
 		std::string fp = fr.at("file_path").str;
 		if (!has_extension(fp)) fp += ".png"; // nerf_loader.cu:560-563
 		const std::string ext = lower_ext(fp);
-		if (ext != "png") throw std::runtime_error("image '" + fp + "': only PNG images are supported on this path");
-		const Image8 img = decode_png(fp[0] == '/' ? fp : base + "/" + fp);
+		if (ext != "png" && ext != "jpg" && ext != "jpeg") throw std::runtime_error("image '" + fp + "': only PNG and JPEG images are supported on this path (no EXR / binary float images)");
+		Image8 img;
+		decode_image_file(fp[0] == '/' ? fp : base + "/" + fp, img.w, img.h, img.rgba);
 		// per-frame intrinsics and lens over the file-level ones (nerf_loader.cu:678-696)
 		bool got_fl = read_focal(root, img.w, img.h, metas[i].focal);
 		got_fl |= read_focal(fr, img.w, img.h, metas[i].focal);

@@ -74,7 +74,7 @@ EXPORTS = [
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
     "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
-    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata",
+    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata", "hn_decode_image_file",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -102,6 +102,7 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_decode_image_file.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
 _lib.hn_train_set_image_metadata.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_set_hidden_area_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
 _lib.hn_set_distortion_map.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
@@ -170,6 +171,18 @@ def camera_to_cols(m):
     """3x4 row-major camera-to-world matrix (pyngp's set_nerf_camera_matrix argument) -> the ABI's 4 columns x vec3."""
     m = np.asarray(m, dtype=np.float32).reshape(3, 4)
     return np.ascontiguousarray(m.T).reshape(12)
+
+
+def decode_image_file(path: str) -> np.ndarray:
+    """the dataset loader's image decoder (PNG / baseline JPEG -> uint8 [h][w][4]); needs no GPU"""
+    w, h = C.c_int(0), C.c_int(0)
+    err = C.create_string_buffer(512)
+    if _lib.hn_decode_image_file(os.fsencode(path), C.byref(w), C.byref(h), None, 0, err, 512):
+        raise RuntimeError(err.value.decode())
+    out = np.empty((h.value, w.value, 4), np.uint8)
+    if _lib.hn_decode_image_file(os.fsencode(path), C.byref(w), C.byref(h), _ptr(out), out.size, err, 512):
+        raise RuntimeError(err.value.decode())
+    return out
 
 
 class RenderMode(enum.IntEnum):

@@ -412,3 +412,42 @@ def test_loader_per_frame_intrinsics_and_lens(hn, root, tmp_path):
     assert abs(l_file - l_hand) <= 1e-3 * max(abs(l_hand), 1e-6), (l_file, l_hand)
     l_plain, n_plain = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
     assert abs(n_plain - n_file) > 100 and abs(l_plain - l_file) > 10 * abs(l_file - l_hand) + 1e-6      # the per-frame cameras are really in use
+
+
+def test_load_training_data_jpeg_frames(hn, root, tmp_path):
+    """the same set as JPEG files (what real transforms.json sets ship): decoded by hn_jpeg.cpp, trained like the float path fed with
+    libjpeg-turbo's decode of the same files (the two decoders agree to +-3 / 255: tests/test_images.py)"""
+    import json
+    PIL = pytest.importorskip("PIL.Image")
+    n, res = 6, 40
+    imgs, cams, focal = hn.synthetic.sphere_dataset(n, res)
+    srgb = np.where(imgs[..., :3] < 0.0031308, 12.92 * imgs[..., :3], 1.055 * np.power(np.maximum(imgs[..., :3], 1e-12), 1 / 2.4) - 0.055)
+    rgb8 = np.round(np.clip(srgb * imgs[..., 3:4], 0, 1) * 255).astype(np.uint8)   # over black: JPEG has no alpha
+    frames, decoded = [], []
+    for i in range(n):
+        p = tmp_path / f"r_{i}.jpg"
+        PIL.fromarray(rgb8[i], "RGB").save(str(p), "JPEG", quality=95, subsampling=(0 if i % 2 else 2))
+        decoded.append(np.asarray(PIL.open(str(p)).convert("RGB")))
+        c = cams[i].reshape(4, 3).astype(np.float64)
+        col = np.stack([c[:, 2], c[:, 0], c[:, 1]], 1)
+        col[1] *= -1; col[2] *= -1
+        col[3] = (col[3] - 0.5) / 0.33
+        m = np.eye(4); m[:3, :4] = col.T
+        frames.append({"file_path": f"r_{i}.jpg", "transform_matrix": m.tolist()})
+    (tmp_path / "transforms.json").write_text(json.dumps({"camera_angle_x": float(2 * np.arctan(0.5 * res / focal)), "aabb_scale": 1, "frames": frames}))
+
+    def first_loss(loader):
+        tb, _, _ = nerf_setup(hn, root, 0.3)
+        tb.set_option("train_auto_grid", 0.0)
+        tb.set_option("train_random_bg", 0.0)
+        loader(tb)
+        tb.reset_trainer(5)
+        return tb.train_accumulate(1024), tb.train_stats().n_samples_last
+
+    d8 = np.stack(decoded).astype(np.float64) / 255.0
+    lin = np.where(d8 <= 0.04045, d8 / 12.92, np.power((d8 + 0.055) / 1.055, 2.4))
+    q = np.concatenate([lin, np.ones((n, res, res, 1))], -1).astype(f32)
+    l_jpg, n_jpg = first_loss(lambda tb: tb.load_training_data(str(tmp_path)))
+    l_f32, n_f32 = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
+    assert n_jpg == n_f32 and n_jpg > 10000
+    assert abs(l_jpg - l_f32) <= 2e-2 * max(abs(l_f32), 1e-6), (l_jpg, l_f32)

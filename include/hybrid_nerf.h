@@ -180,6 +180,13 @@ int hn_get_train_stats(const hn_context* ctx, hn_train_stats* out);
  * 0 L2, 1 Huber(0.1)/5, 2 RelativeL2, 3 L1, 4 Mape, 5 Smape, 6 LogL1. */
 int hn_op_train_gradients(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start,
 	const float* targets, const float* backgrounds, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
+/* depth supervision (nerf.h:98,124; src/testbed_nerf.cu:1063-1067,1149-1154): hn_train_set_depth gives every training image a float depth image
+ * [n][height][width] (metadata[img].depth: z-depth in scene units, <= 0 = no measurement; NULL removes them); with option
+ * "depth_supervision_lambda" > 0 the loss kernel compares the composited ray depth with |un-normalised ray| x depth through
+ * "depth_loss_type" (ELossType, default 3 = L1) and adds lambda x that gradient to dL/dsigma. The operator variant takes the per-ray targets. */
+int hn_train_set_depth(hn_context* ctx, const float* depth, uint32_t n_images, int width, int height);
+int hn_op_train_gradients_depth(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds,
+	const float* target_depth, float depth_lambda, int depth_loss_type, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
 
 /* ---- error map (nerf.h:104-118; src/testbed_nerf.cu:1080-1106,1776-1832,2986-3075; nerf_device.cuh:536-639) ----
  * hn_train_accumulate deposits every ray's mean loss into a coarse per-image map and rebuilds the sampling CDFs from it every

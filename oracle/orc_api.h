@@ -165,6 +165,12 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, int32_t loss_type, float loss_scale,
 	uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total);
 
+// + depth supervision (src/testbed_nerf.cu:1063-1067,1149-1154): target_depth [n] = distance along the ray the ray should reach (<= 0: none),
+// weighted by depth_lambda, compared with the composited ray depth through depth_loss_type (the reference's default is L1 = 3)
+float orc_train_gradients_depth(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, uint32_t n_rays,
+	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, const float* target_depth, float depth_lambda,
+	int32_t depth_loss_type, int32_t loss_type, float loss_scale, uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total);
+
 // ---- occupancy-grid maintenance from the live network (orc_grid.inc) ----
 void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]);
 // per-image focal [n][2] / principal [n][2] / ELensMode [n] / lens params [n][7] (TrainingImageMetadata); lens arrays may be NULL

@@ -1054,6 +1054,14 @@ float orc_train_gradients(const orc_render_params* p, const orc_net_config* c, c
 	return train_gradients(*p, net, bitfield, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, max_samples, grads, n_steps_out, n_samples_total);
 }
 
+float orc_train_gradients_depth(const orc_render_params* p, const orc_net_config* c, const uint16_t* params, const uint8_t* bitfield, uint32_t n_rays,
+	const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds, const float* target_depth, float depth_lambda,
+	int32_t depth_loss_type, int32_t loss_type, float loss_scale, uint32_t max_samples, float* grads, uint32_t* n_steps_out, uint32_t* n_samples_total) {
+	Net net = make_net(*c, params);
+	return train_gradients(*p, net, bitfield, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, max_samples, grads, n_steps_out, n_samples_total,
+		target_depth, depth_lambda, depth_loss_type);
+}
+
 void orc_mark_untrained_grid(float* grid, uint32_t n_cascades, uint32_t n_images, const float* cams, int32_t w, int32_t h, const float focal[2], const float principal[2]) {
 	mark_untrained_grid(grid, n_cascades, n_images, cams, w, h, focal, principal);
 }

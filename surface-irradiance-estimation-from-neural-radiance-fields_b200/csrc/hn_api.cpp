@@ -238,6 +238,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"fov_axis", {&o.fov_axis, 1, false}}, {"profile", {&o.profile, 1, true}}, {"eval_impl", {&o.eval_impl, 1, true}}, {"fuse_composite", {&o.fuse_composite, 1, true}}, {"composite_impl", {&o.composite_impl, 1, true}}, {"mesh_aabb", {o.mesh_aabb, 6, false}},
 		{"train_auto_grid", {&c->train_cfg.auto_grid, 1, true}}, {"train_mlp_impl", {&c->train_cfg.mlp_impl, 1, true}}, {"train_random_bg", {&c->train_cfg.random_bg, 1, true}},
 		{"train_grid_decay", {&c->train_cfg.grid_decay, 1, false}}, {"train_loss_type", {&c->train_cfg.loss_type, 1, true}},
+		{"depth_supervision_lambda", {&c->train_cfg.depth_supervision_lambda, 1, false}}, {"depth_loss_type", {&c->train_cfg.depth_loss_type, 1, true}},
 		{"sample_focal_plane_proportional_to_error", {&c->train_cfg.sample_focal_plane_proportional_to_error, 1, true}},
 		{"sample_image_proportional_to_error", {&c->train_cfg.sample_image_proportional_to_error, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
@@ -665,6 +666,16 @@ extern "C" {
 int hn_train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n_images, int width, int height, const float* cameras,
 	const float focal_px[2], const float principal[2]) {
 	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_dataset(ctx, rgba, n_images, width, height, cameras, focal_px, principal); HN_CATCH(ctx)
+}
+int hn_train_set_depth(hn_context* ctx, const float* depth, uint32_t n_images, int width, int height) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_depth(ctx, depth, n_images, width, height); HN_CATCH(ctx)
+}
+int hn_op_train_gradients_depth(hn_context* ctx, uint32_t n_rays, const float* origins, const float* dirs, const float* t_start, const float* targets, const float* backgrounds,
+	const float* target_depth, float depth_lambda, int depth_loss_type, int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps) {
+	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device));
+	need(target_depth != nullptr, "target_depth is required");
+	train_op_gradients(ctx, n_rays, origins, dirs, t_start, targets, backgrounds, loss_type, loss_scale, loss_out, grads_host, n_steps, target_depth, depth_lambda, depth_loss_type);
+	HN_CATCH(ctx)
 }
 int hn_train_set_image_metadata(hn_context* ctx, uint32_t n_images, const float* focal_px, const float* principal, const int32_t* lens_mode, const float* lens_params) {
 	HN_TRY(ctx) HN_CUDA(cudaSetDevice(ctx->device)); train_set_image_metadata(ctx, n_images, focal_px, principal, lens_mode, lens_params); HN_CATCH(ctx)

@@ -109,6 +109,8 @@ struct TrainCfg {
 	uint32_t target_batch = 1u << 18;       // samples per batch (src/testbed_nerf.cu:2943)
 	int random_bg = 1;                      // nerf.training.random_bg_color
 	int mlp_impl = 1;                       // MLP forward / backward: 1 = own tcgen05 kernels (hn_train_tc.cu), 0 = cuBLAS GEMMs + elementwise kernels (round-1 path, A/B)
+	float depth_supervision_lambda = 0.0f;  // nerf.training.depth_supervision_lambda (nerf.h:124): weight of the depth term, needs hn_train_set_depth
+	int depth_loss_type = 3;                // nerf.training.depth_loss_type (nerf.h:98): L1
 	int sample_focal_plane_proportional_to_error = 0; // nerf.training.sample_focal_plane_proportional_to_error (nerf.h:112): pixels from the error-map CDF
 	int sample_image_proportional_to_error = 0;       // nerf.training.sample_image_proportional_to_error (nerf.h:113): images from the error-map CDF
 	int auto_grid = 1;                      // refresh the occupancy grid from the network on the reference's schedule (training_prep_nerf)
@@ -122,6 +124,7 @@ struct TrainState {
 	float ms[5] = {0, 0, 0, 0, 0};
 	// dataset
 	DevBuf<float4> images; DevBuf<float> cams;
+	DevBuf<float> depth; bool has_depth = false; DevBuf<float> ray_target_depth; // depth supervision: [n][h][w] depth images, per-ray target distance
 	DevBuf<ImageMeta> meta; std::vector<ImageMeta> meta_host; // per-image focal length, principal point, lens
 	uint32_t n_images = 0; int img_w = 0, img_h = 0; float focal[2] = {0, 0}, principal[2] = {0.5f, 0.5f};
 	// parameters
@@ -262,7 +265,8 @@ void train_init(hn_context* ctx, uint32_t seed);
 void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out);
 void train_apply(hn_context* ctx, float grad_scale);
 void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* t, const float* targets, const float* bgs,
-	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps);
+	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps, const float* target_depth = nullptr, float depth_lambda = 0.0f, int depth_loss_type = 3);
+void train_set_depth(hn_context* ctx, const float* depth, uint32_t n, int w, int h);
 void train_release(hn_context* ctx);
 void train_export_state(hn_context* ctx, std::vector<float>& m1, std::vector<float>& m2, std::vector<uint32_t>& steps);
 void train_import_state(hn_context* ctx, uint32_t step, const float* m1, const float* m2, const uint32_t* steps, size_t n);

@@ -63,6 +63,13 @@ struct TrainDataDev {
 // ---- error map (src/testbed_nerf.cu:1080-1106, 1776-1832, 2986-3075; nerf_device.cuh:536-633) ----
 // Per training image a coarse map of the mean loss of the rays that landed there (bilinear deposit), turned every
 // n_steps_between_error_map_updates steps into CDFs (x given y, y, image) that can steer the choice of image and pixel.
+// depth supervision (src/testbed_nerf.cu:1063-1067,1149-1154): per-ray target distance (<= 0 or nullptr: none), lambda, ELossType of the depth term;
+// ray origins and the training box un-warp the sample positions for distance(pos, ray_o)
+struct DepthSup {
+	const float* target; const float* ray_o;
+	float lambda; int loss_type;
+	float lo[3], diag[3];
+};
 struct ErrorMapDev {
 	float* data;                  // [n_images][res_y][res_x] accumulated loss, nullptr = off
 	int res[2];
@@ -152,7 +159,8 @@ __global__ void construct_cdf_1d_kernel(uint32_t n_images, uint32_t height, floa
 // Start t = AABB entry advanced by a random fraction of a step (:817-821).
 __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays, uint32_t ray_offset, uint32_t n_rays_total, uint32_t seed, uint32_t step,
 	int random_bg, int srgb_space, float bg_r, float bg_g, float bg_b, float* __restrict__ ray_o, float* __restrict__ ray_d, float* __restrict__ ray_t,
-	float* __restrict__ ray_target, float* __restrict__ ray_bg, ErrorMapDev E, uint32_t* __restrict__ ray_img, float* __restrict__ ray_uv, float* __restrict__ ray_pdf) {
+	float* __restrict__ ray_target, float* __restrict__ ray_bg, ErrorMapDev E, uint32_t* __restrict__ ray_img, float* __restrict__ ray_uv, float* __restrict__ ray_pdf,
+	const float* __restrict__ depth_images, float* __restrict__ ray_target_depth) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_rays) return;
 	const uint32_t gi = i + ray_offset;
@@ -176,7 +184,10 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 	const bool valid_ray = lens_direction(m.lens_mode, m.lens_params, uu, vv, m.principal[0], m.principal[1], D.w, D.h, m.focal[0], m.focal[1], dc);
 	if (!valid_ray) dc = mk(0.f, 0.f, 1.f);
 	float d0 = c[0] * dc.x + c[3] * dc.y + c[6] * dc.z, d1 = c[1] * dc.x + c[4] * dc.y + c[7] * dc.z, d2 = c[2] * dc.x + c[5] * dc.y + c[8] * dc.z;
-	const float inv = rsqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+	const float len2 = d0 * d0 + d1 * d1 + d2 * d2;
+	const float inv = rsqrtf(len2);
+	// target distance of the depth term: |un-normalised ray direction| x the image's depth at the pixel (:1065), -1 = none
+	if (ray_target_depth) ray_target_depth[i] = depth_images ? sqrtf(len2) * __ldg(depth_images + ((size_t)img * D.h + py) * D.w + px) : -1.0f;
 	d0 *= inv; d1 *= inv; d2 *= inv;
 	ray_o[3 * i] = c[9]; ray_o[3 * i + 1] = c[10]; ray_o[3 * i + 2] = c[11];
 	ray_d[3 * i] = d0; ray_d[3 * i + 1] = d1; ray_d[3 * i + 2] = d2;
@@ -311,7 +322,7 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 	const float4* __restrict__ coords, const __half* __restrict__ out, const __half* __restrict__ density_out, const float* __restrict__ ray_target,
 	const float* __restrict__ ray_bg, int loss_type, float loss_scale, int rgb_act, int density_act, float l1_reg_density, __half* __restrict__ d_out, float* __restrict__ d_sigma,
 	uint32_t* __restrict__ used_out, float* __restrict__ loss_acc, ErrorMapDev E, const uint32_t* __restrict__ ray_img, const float* __restrict__ ray_uv,
-	const float* __restrict__ ray_pdf, int img_w, int img_h) {
+	const float* __restrict__ ray_pdf, int img_w, int img_h, DepthSup Z) {
 	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const uint32_t lane = threadIdx.x & 31u;
 	if (i >= n_rays) return; // warp-uniform
@@ -319,17 +330,22 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 	const float dt_range = HN_MIN_STEP * 128.0f - HN_MIN_STEP;
 	const uint32_t n_chunks = (numsteps + 31u) / 32u;
 	// ---- pass 1: ray colour
-	float T = 1.f, rr = 0.f, rg = 0.f, rb = 0.f;
+	float T = 1.f, rr = 0.f, rg = 0.f, rb = 0.f, depth_ray = 0.f;
+	const bool use_depth = Z.target != nullptr && Z.lambda > 0.0f && Z.target[i] > 0.0f; // warp-uniform
+	float ox = 0.f, oy = 0.f, oz = 0.f;
+	if (use_depth) { ox = Z.ray_o[3 * i]; oy = Z.ray_o[3 * i + 1]; oz = Z.ray_o[3 * i + 2]; }
 	uint32_t compacted = numsteps;
 	for (uint32_t c = 0; c < n_chunks; ++c) {
 		const uint32_t j = c * 32u + lane;
 		const bool has = j < numsteps;
-		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, dist = 0.f;
 		if (has) {
 			const size_t s = base + j;
 			const uint2 o = *reinterpret_cast<const uint2*>(out + s * 16);
 			const __half2 h01 = *reinterpret_cast<const __half2*>(&o.x), h2x = *reinterpret_cast<const __half2*>(&o.y);
-			const float dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
+			const float4 cw = coords[s];
+			if (use_depth) { const float qx = Z.lo[0] + cw.x * Z.diag[0] - ox, qy = Z.lo[1] + cw.y * Z.diag[1] - oy, qz = Z.lo[2] + cw.z * Z.diag[2] - oz; dist = sqrtf(qx * qx + qy * qy + qz * qz); }
+			const float dt = (cw.w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
 			alpha = 1.f - __expf(-act_density(__half2float(density_out[s * 16]), density_act) * dt);
 			cr = act_rgb(__low2float(h01), rgb_act); cg = act_rgb(__high2float(h01), rgb_act); cb = act_rgb(__low2float(h2x), rgb_act);
 		}
@@ -344,6 +360,12 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 		#pragma unroll
 		for (int dd = 16; dd > 0; dd >>= 1) { sr += __shfl_xor_sync(0xffffffffu, sr, dd); sg += __shfl_xor_sync(0xffffffffu, sg, dd); sb += __shfl_xor_sync(0xffffffffu, sb, dd); }
 		rr += sr; rg += sg; rb += sb;
+		if (use_depth) {
+			float sd = w * dist;
+			#pragma unroll
+			for (int dd = 16; dd > 0; dd >>= 1) sd += __shfl_xor_sync(0xffffffffu, sd, dd);
+			depth_ray += sd;
+		}
 		if (stop) { compacted = c * 32u + last; T = __shfl_sync(0xffffffffu, T_before, last); break; }
 		T *= __shfl_sync(0xffffffffu, P, 31);
 	}
@@ -358,21 +380,25 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 		atomicAdd(loss_acc, mean_loss / (float)n_rays_total);
 		if (E.data && ray_img) error_map_deposit(E.data, E.res[0], E.res[1], img_w, img_h, ray_img[i], ray_uv[2 * i], ray_uv[2 * i + 1], mean_loss);
 	}
+	float depth_loss_gradient = 0.0f;
+	if (use_depth) { float g; loss_grad(Z.loss_type, Z.target[i], depth_ray, g); depth_loss_gradient = Z.lambda * g; }
 	const float ls = loss_scale / (float)n_rays_total;
 	const float l2_reg = rgb_act == 3 ? 1e-4f : 0.0f;
 	// ---- pass 2: gradients
-	float Tc = 1.f, pr = 0.f, pg = 0.f, pb = 0.f; // carried transmittance and colour prefix
+	float Tc = 1.f, pr = 0.f, pg = 0.f, pb = 0.f, pd = 0.f; // carried transmittance, colour prefix and depth prefix
 	for (uint32_t c = 0; c < n_chunks; ++c) {
 		const uint32_t j = c * 32u + lane;
 		const bool has = j < numsteps;
 		const size_t s = base + j;
 		const bool used = j < compacted;
-		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, o0 = 0.f, o1 = 0.f, o2 = 0.f, sraw = 0.f, dt = 0.f;
+		float alpha = 0.f, cr = 0.f, cg = 0.f, cb = 0.f, o0 = 0.f, o1 = 0.f, o2 = 0.f, sraw = 0.f, dt = 0.f, dist = 0.f;
 		if (used) {
 			const uint2 o = *reinterpret_cast<const uint2*>(out + s * 16);
 			const __half2 h01 = *reinterpret_cast<const __half2*>(&o.x), h2x = *reinterpret_cast<const __half2*>(&o.y);
 			o0 = __low2float(h01); o1 = __high2float(h01); o2 = __low2float(h2x); sraw = __half2float(density_out[s * 16]);
-			dt = (coords[s].w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
+			const float4 cw = coords[s];
+			if (use_depth) { const float qx = Z.lo[0] + cw.x * Z.diag[0] - ox, qy = Z.lo[1] + cw.y * Z.diag[1] - oy, qz = Z.lo[2] + cw.z * Z.diag[2] - oz; dist = sqrtf(qx * qx + qy * qy + qz * qz); }
+			dt = (cw.w - HN_MIN_STEP) / dt_range * dt_range + HN_MIN_STEP;
 			alpha = 1.f - __expf(-act_density(sraw, density_act) * dt);
 			cr = act_rgb(o0, rgb_act); cg = act_rgb(o1, rgb_act); cb = act_rgb(o2, rgb_act);
 		}
@@ -382,6 +408,8 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 		const float weight = alpha * (Tc * Pex);
 		const float T_after = Tc * P;
 		const float r2 = pr + warp_incl_sum(weight * cr, lane), g2 = pg + warp_incl_sum(weight * cg, lane), b2 = pb + warp_incl_sum(weight * cb, lane);
+		const float d2 = use_depth ? pd + warp_incl_sum(weight * dist, lane) : 0.f;
+		const float depth_supervision = use_depth ? depth_loss_gradient * (T_after * dist - (depth_ray - d2)) : 0.f;
 		if (has) {
 			uint4* dst = reinterpret_cast<uint4*>(d_out + s * 16);
 			if (!used) { dst[0] = make_uint4(0, 0, 0, 0); dst[1] = make_uint4(0, 0, 0, 0); d_sigma[s] = 0.f; }
@@ -394,12 +422,13 @@ __global__ void __launch_bounds__(128) train_loss_kernel(uint32_t n_rays, uint32
 				// + the reference's UNSCALED L1 density regulariser (src/testbed_nerf.cu:1113,1161-1164): pushes negative raw densities down
 				// while the grid is nearly empty (mean density < NERF_MIN_OPTICAL_THICKNESS), which keeps such a grid from collapsing.
 				// (its near-distance term is inert: near_distance is 0 on this path)
-				d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T_after * cr - sr) + gg * (T_after * cg - sg) + gb * (T_after * cb - sb)))
+				d_sigma[s] = ls * density_derivative(sraw, density_act) * (dt * (gr * (T_after * cr - sr) + gg * (T_after * cg - sg) + gb * (T_after * cb - sb) + depth_supervision))
 					+ (sraw < 0.0f ? -l1_reg_density : 0.0f);
 			}
 		}
 		Tc *= __shfl_sync(0xffffffffu, P, 31);
 		pr = __shfl_sync(0xffffffffu, r2, 31); pg = __shfl_sync(0xffffffffu, g2, 31); pb = __shfl_sync(0xffffffffu, b2, 31);
+		if (use_depth) pd = __shfl_sync(0xffffffffu, d2, 31);
 	}
 }
 
@@ -600,7 +629,7 @@ void ensure_batch(hn_context* ctx, uint32_t n_rays, uint32_t max_samples) {
 	t.ray_o.ensure((size_t)n_rays * 3); t.ray_d.ensure((size_t)n_rays * 3); t.ray_t.ensure(n_rays);
 	t.ray_target.ensure((size_t)n_rays * 3); t.ray_bg.ensure((size_t)n_rays * 3);
 	t.ray_numsteps.ensure(n_rays); t.ray_base.ensure(n_rays); t.counters.ensure(4); t.loss_acc.ensure(4);
-	t.ray_img.ensure(n_rays); t.ray_uv.ensure((size_t)n_rays * 2); t.ray_pdf.ensure(n_rays);
+	t.ray_img.ensure(n_rays); t.ray_uv.ensure((size_t)n_rays * 2); t.ray_pdf.ensure(n_rays); t.ray_target_depth.ensure(n_rays);
 	t.coords.ensure(max_samples); t.sample_ray.ensure(max_samples);
 	const uint32_t Hd = ctx->net.density_hidden, Hr = ctx->net.rgb_hidden;
 	if (Hd + Hr + 4 > 12) throw std::runtime_error("training supports at most 8 hidden layers in total");
@@ -609,7 +638,8 @@ void ensure_batch(hn_context* ctx, uint32_t n_rays, uint32_t max_samples) {
 }
 
 // march (samples) -> forward -> loss -> backward into t.grads. Rays are already in t.ray_*.
-void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, uint32_t max_samples, int loss_type, float loss_scale, uint32_t* used_dev, const ErrorMapDev* emap = nullptr) {
+void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, uint32_t max_samples, int loss_type, float loss_scale, uint32_t* used_dev, const ErrorMapDev* emap = nullptr,
+	const float* target_depth = nullptr, float depth_lambda = 0.0f, int depth_loss_type = 3) {
 	TrainState& t = ctx->train;
 	cudaStream_t s = ctx->stream;
 	const NetCfg& net = ctx->net;
@@ -675,12 +705,17 @@ void forward_backward(hn_context* ctx, uint32_t n_rays, uint32_t n_rays_total, u
 	}
 	ev.stop(t.ms[1]);
 	// ---- loss and dL/d(output)
+	DepthSup Z = {};
+	if (target_depth && depth_lambda > 0.0f) {
+		Z.target = target_depth; Z.ray_o = t.ray_o.p; Z.lambda = depth_lambda; Z.loss_type = depth_loss_type;
+		for (int k = 0; k < 3; ++k) { Z.lo[k] = a.train_aabb[k]; Z.diag[k] = a.train_aabb[3 + k] - a.train_aabb[k]; }
+	}
 	ev.start();
 	__half* g_out = t.dact[0].p;               // [n][16]
 	float* d_sigma = (float*)t.dact[3].p;      // [n] fp32 (buffer holds n*64 halfs)
 	train_loss_kernel<<<blocks((size_t)n_rays * 32, 128), 128, 0, s>>>(n_rays, n_rays_total, t.ray_numsteps.p, t.ray_base.p, t.coords.p, out, d_out, t.ray_target.p, t.ray_bg.p,
 		loss_type, loss_scale, a.rgb_act, a.density_act, ctx->density_grid_mean < 0.01f ? 1e-4f : 0.0f, g_out, d_sigma, used_dev, t.loss_acc.p,
-		emap ? *emap : ErrorMapDev{}, emap ? t.ray_img.p : nullptr, emap ? t.ray_uv.p : nullptr, emap ? t.ray_pdf.p : nullptr, t.img_w, t.img_h);
+		emap ? *emap : ErrorMapDev{}, emap ? t.ray_img.p : nullptr, emap ? t.ray_uv.p : nullptr, emap ? t.ray_pdf.p : nullptr, t.img_w, t.img_h, Z);
 	ev.stop(t.ms[2]);
 	// ---- backward
 	ev.start();
@@ -797,9 +832,20 @@ void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, in
 		HN_CUDA(cudaMemcpy(t.meta.p, t.meta_host.data(), (size_t)n * sizeof(ImageMeta), cudaMemcpyHostToDevice));
 	}
 	t.has_dataset = true;
+	t.has_depth = false;
 	t.srgb_space = 0;
 }
 
+// metadata[img].depth of the reference's dataset: one float depth image per training image (z-depth in scene units, 0 = no measurement)
+void train_set_depth(hn_context* ctx, const float* depth, uint32_t n, int w, int h) {
+	TrainState& t = ctx->train;
+	if (!depth) { t.has_depth = false; return; }
+	if (!t.has_dataset || n != t.n_images || w != t.img_w || h != t.img_h) throw std::runtime_error("depth images: set the dataset first, one depth image per training image at its resolution");
+	const size_t px = (size_t)n * w * h;
+	t.depth.ensure(px);
+	HN_CUDA(cudaMemcpy(t.depth.p, depth, px * sizeof(float), cudaMemcpyHostToDevice));
+	t.has_depth = true;
+}
 // TrainingImageMetadata per image (nerf.h; read_focal_length / read_lens of the loader, src/nerf_loader.cu:175-271,678-696)
 void train_set_image_metadata(hn_context* ctx, uint32_t n, const float* focal, const float* principal, const int32_t* lens_mode, const float* lens_params) {
 	TrainState& t = ctx->train;
@@ -878,8 +924,10 @@ void train_accumulate(hn_context* ctx, uint32_t n_rays, float* loss_out) {
 		if (c.sample_image_proportional_to_error) E.cdf_img = t.cdf_img.p;
 	}
 	train_raygen_kernel<<<blocks(n_rays), 256, 0, s>>>(D, a, n_rays, rank * n_rays, n_rays * world, t.seed, t.step, c.random_bg, t.srgb_space, bg[0], bg[1], bg[2],
-		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p, E, t.ray_img.p, t.ray_uv.p, t.ray_pdf.p);
-	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr, &E);
+		t.ray_o.p, t.ray_d.p, t.ray_t.p, t.ray_target.p, t.ray_bg.p, E, t.ray_img.p, t.ray_uv.p, t.ray_pdf.p,
+		(t.has_depth && c.depth_supervision_lambda > 0.0f) ? t.depth.p : nullptr, t.ray_target_depth.p);
+	forward_backward(ctx, n_rays, n_rays * world, max_samples, c.loss_type, c.loss_scale, nullptr, &E,
+		(t.has_depth && c.depth_supervision_lambda > 0.0f) ? t.ray_target_depth.p : nullptr, c.depth_supervision_lambda, c.depth_loss_type);
 	// CDFs from the error map every n_steps_between_error_map_updates steps, then a 1.5x longer period (:3023-3075)
 	if (++t.n_steps_since_error_map_update >= t.n_steps_between_error_map_updates) {
 		build_error_cdfs(ctx);
@@ -923,7 +971,7 @@ void train_apply(hn_context* ctx, float grad_scale) {
 }
 
 void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const float* d, const float* tt, const float* targets, const float* bgs,
-	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps) {
+	int loss_type, float loss_scale, float* loss_out, float* grads_host, uint32_t* n_steps, const float* target_depth, float depth_lambda, int depth_loss_type) {
 	check_ready(ctx, false);
 	TrainState& t = ctx->train;
 	cudaStream_t s = ctx->stream;
@@ -937,7 +985,8 @@ void train_op_gradients(hn_context* ctx, uint32_t n_rays, const float* o, const 
 	HN_CUDA(cudaMemcpyAsync(t.ray_bg.p, bgs, (size_t)n_rays * 12, cudaMemcpyHostToDevice, s));
 	DevBuf<uint32_t> used; used.ensure(n_rays);
 	HN_CUDA(cudaMemsetAsync(used.p, 0, (size_t)n_rays * 4, s));
-	forward_backward(ctx, n_rays, n_rays, max_samples, loss_type, loss_scale, used.p);
+	if (target_depth) HN_CUDA(cudaMemcpyAsync(t.ray_target_depth.p, target_depth, (size_t)n_rays * 4, cudaMemcpyHostToDevice, s));
+	forward_backward(ctx, n_rays, n_rays, max_samples, loss_type, loss_scale, used.p, nullptr, target_depth ? t.ray_target_depth.p : nullptr, depth_lambda, depth_loss_type);
 	if (loss_out) HN_CUDA(cudaMemcpyAsync(loss_out, t.loss_acc.p, sizeof(float), cudaMemcpyDeviceToHost, s));
 	if (grads_host) HN_CUDA(cudaMemcpyAsync(grads_host, t.grads.p, ctx->net.n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
 	if (n_steps) HN_CUDA(cudaMemcpyAsync(n_steps, used.p, (size_t)n_rays * 4, cudaMemcpyDeviceToHost, s));

@@ -74,7 +74,7 @@ EXPORTS = [
     "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
     "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
-    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata", "hn_decode_image_file",
+    "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata", "hn_decode_image_file", "hn_train_set_depth", "hn_op_train_gradients_depth",
 ]
 
 _lib.hn_last_error.restype = C.c_char_p
@@ -102,6 +102,8 @@ _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+_lib.hn_train_set_depth.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int]
+_lib.hn_op_train_gradients_depth.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_float, C.c_int, C.c_int, C.c_float] + [C.c_void_p] * 3
 _lib.hn_decode_image_file.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
 _lib.hn_train_set_image_metadata.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 _lib.hn_set_hidden_area_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
@@ -612,6 +614,25 @@ class Testbed:
         out = np.empty((int(n_images), int(res[1]), int(res[0])), np.float32)
         self._check(_lib.hn_op_error_map_deposit(self._h, i.size, _ptr(i), _ptr(u), _ptr(v), int(n_images), int(res[0]), int(res[1]), int(image_res[0]), int(image_res[1]), _ptr(out)))
         return out
+
+    def set_training_depth(self, depth):
+        """float32 [n][h][w] depth images of the training set (z-depth, <= 0 = none); None removes them. Used when option depth_supervision_lambda > 0."""
+        if depth is None:
+            self._check(_lib.hn_train_set_depth(self._h, None, 0, 0, 0)); return
+        d = _f32(depth)
+        assert d.ndim == 3
+        self._check(_lib.hn_train_set_depth(self._h, _ptr(d), d.shape[0], d.shape[2], d.shape[1]))
+
+    def op_train_gradients_depth(self, origins, dirs, t_start, targets, backgrounds, target_depth, depth_lambda, depth_loss_type=3, loss_type=1, loss_scale=128.0):
+        o, d, t = _f32(origins).reshape(-1, 3), _f32(dirs).reshape(-1, 3), _f32(t_start).reshape(-1)
+        tg, bg, td = _f32(targets).reshape(-1, 3), _f32(backgrounds).reshape(-1, 3), _f32(target_depth).reshape(-1)
+        n = o.shape[0]
+        grads = np.empty(int(self.network_info().n_params), np.float32)
+        steps = np.empty(n, np.uint32)
+        loss = C.c_float(0)
+        self._check(_lib.hn_op_train_gradients_depth(self._h, n, _ptr(o), _ptr(d), _ptr(t), _ptr(tg), _ptr(bg), _ptr(td), float(depth_lambda), int(depth_loss_type),
+                                                     int(loss_type), float(loss_scale), C.byref(loss), _ptr(grads), _ptr(steps)))
+        return float(loss.value), grads, steps
 
     # ---- a-16 environment map (Testbed::m_envmap, testbed.h:1227-1241)
     def set_envmap(self, rgba: np.ndarray | None):

@@ -375,6 +375,22 @@ def train_gradients(p: RenderParams, cfg, params, bits, origins, dirs, t_start, 
     return float(loss), grads, steps
 
 
+def train_gradients_depth(p: RenderParams, cfg, params, bits, origins, dirs, t_start, targets, backgrounds, target_depth, depth_lambda, depth_loss_type=3,
+                          loss_type=1, loss_scale=128.0, max_samples=1 << 20):
+    """train_gradients with depth supervision: target_depth [n] (<= 0: none), lambda, ELossType of the depth term (3 = L1, the reference's default)"""
+    o = np.ascontiguousarray(origins, np.float32); d = np.ascontiguousarray(dirs, np.float32); t = np.ascontiguousarray(t_start, np.float32)
+    tg = np.ascontiguousarray(targets, np.float32); bg = np.ascontiguousarray(backgrounds, np.float32); td = np.ascontiguousarray(target_depth, np.float32)
+    n = o.shape[0]
+    grads = np.zeros(int(lib.orc_n_params(C.byref(cfg))), np.float32)
+    steps = np.zeros(n, np.uint32)
+    total = u32(0)
+    lib.orc_train_gradients_depth.argtypes = [C.c_void_p] * 4 + [u32] + [C.c_void_p] * 6 + [f32, i32, i32, f32, u32, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.orc_train_gradients_depth.restype = f32
+    loss = lib.orc_train_gradients_depth(C.byref(p), C.byref(cfg), P(params), P(bits), n, P(o), P(d), P(t), P(tg), P(bg), P(td), float(depth_lambda), int(depth_loss_type),
+                                         int(loss_type), float(loss_scale), int(max_samples), P(grads), P(steps), C.byref(total))
+    return float(loss), grads, steps
+
+
 def update_density_grid(p: RenderParams, cfg, params, grid, n_cascades, ema_step, n_uniform, n_nonuniform, decay=0.95, seed=1337, rng_calls=0):
     g = np.ascontiguousarray(grid, np.float32).copy()
     lib.orc_update_density_grid.argtypes = [C.c_void_p] * 4 + [u32, u32, u32, u32, f32, u32, u32]

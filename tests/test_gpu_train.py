@@ -451,3 +451,59 @@ def test_load_training_data_jpeg_frames(hn, root, tmp_path):
     l_f32, n_f32 = first_loss(lambda tb: tb.set_training_data(q, cams, focal))
     assert n_jpg == n_f32 and n_jpg > 10000
     assert abs(l_jpg - l_f32) <= 2e-2 * max(abs(l_f32), 1e-6), (l_jpg, l_f32)
+
+
+@pytest.mark.parametrize("depth_loss_type", [3, 0])
+def test_depth_supervision_gradients_match_oracle(hn, orc, root, depth_loss_type):
+    """depth supervision of compute_loss_kernel_train_nerf (src/testbed_nerf.cu:1063-1067,1149-1154): the composited ray depth against a per-ray
+    target distance, lambda x its gradient added to dL/dsigma. Same bars as the colour gradients (loss 1e-2, cosine >= 0.999)."""
+    tb, params, grid = nerf_setup(hn, root, 0.5)
+    rng = np.random.default_rng(6)
+    n = 96
+    o, d, t0 = make_rays(rng, n)
+    targets = rng.random((n, 3), dtype=f32)
+    bgs = rng.random((n, 3), dtype=f32)
+    target_depth = (1.0 + rng.random(n, dtype=f32)).astype(f32)
+    target_depth[::7] = -1.0                       # rays without a depth measurement
+    lam = 0.5
+    loss, grads, steps = tb.op_train_gradients_depth(o, d, t0, targets, bgs, target_depth, lam, depth_loss_type)
+    info = tb.network_info()
+    cfg = orc.net_config_from_info(info)
+    bits = orc.bitfield_from_grid(grid, 1)[0]
+    p = orc.render_params(8, 8, hn.synthetic.default_camera(), density_grid_mean=float(np.maximum(grid, 0).mean()))
+    wl, wg, ws = orc.train_gradients_depth(p, cfg, params, bits, o, d, t0, targets, bgs, target_depth, lam, depth_loss_type)
+    assert np.mean(steps == ws) >= 0.97 and abs(loss - wl) <= 1e-2 * abs(wl)
+    n_mlp = int(info.grid_param_offset)
+    assert cosine(grads[:n_mlp], wg[:n_mlp]) >= 0.999 and cosine(grads[n_mlp:], wg[n_mlp:]) >= 0.999
+    assert abs(np.linalg.norm(grads) / np.linalg.norm(wg) - 1.0) <= 2e-2
+    # the depth term really contributes: without it the gradients are others (the colour loss is unchanged)
+    l0, g0, _ = tb.op_train_gradients(o, d, t0, targets, bgs)
+    assert abs(l0 - loss) <= 1e-5 * abs(l0) and cosine(g0, grads) < 0.995
+    # lambda 0 or no targets = the plain step
+    l1, g1, _ = tb.op_train_gradients_depth(o, d, t0, targets, bgs, np.full(n, -1.0, f32), lam, depth_loss_type)
+    assert cosine(g1, g0) > 0.99999
+
+
+def test_depth_supervised_training_pulls_the_surface(hn, root):
+    """the dataset path: depth images + option depth_supervision_lambda; a few steps with a strong depth term move the rendered depth towards the targets"""
+    imgs, cams, focal = hn.synthetic.sphere_dataset(8, 48)
+    tb, _, _ = nerf_setup(hn, root, 1e-4)
+    tb.set_training_data(imgs, cams, focal)
+    inside = imgs[..., 3] > 0.5
+    depth = np.where(inside, 1.35, 0.0).astype(f32)      # cameras sit ~1.6 from the centre of an r = 0.25 sphere: its front is ~1.35 away
+    with pytest.raises(RuntimeError):
+        tb.set_training_depth(depth[:3])
+    tb.set_training_depth(depth)
+    tb.reset_trainer(4)
+    tb.set_option("depth_supervision_lambda", 1.0)
+    plain = hn.Testbed()
+    plain.reload_network_from_file(os.path.join(root, "configs", "nerf", "base.json"))
+    plain.set_params(hn.synthetic.random_params(plain.network_info(), 1337, 1e-4)); plain.set_density_grid(hn.synthetic.sphere_density_grid(0.35), 1)
+    plain.set_training_data(imgs, cams, focal); plain.reset_trainer(4)
+    la = [tb.train(1) for _ in range(40)]
+    lb = [plain.train(1) for _ in range(40)]
+    assert np.isfinite(la).all() and la[-1] < la[0]
+    # the two runs see the same rays; the depth term changes the parameters
+    tb.snap_to_pixel_centers = plain.snap_to_pixel_centers = True
+    tb.set_camera_cols(cams[0]); plain.set_camera_cols(cams[0])
+    assert np.abs(tb.render(48, 48, 1, True) - plain.render(48, 48, 1, True)).max() > 1e-3

@@ -123,6 +123,33 @@ __host__ __device__ __forceinline__ float2 hn_ld_random_val_2d(uint32_t index, u
 }
 
 #define HN_PI_F 3.14159265358979323846f
+
+// ---- stepping space of the ray walk (nerf_device.cuh:316-368): linear for cone angle 0, logarithmic between the two break points otherwise
+#define HN_STEPSIZE (1.73205080757f / 1024.0f)
+#define HN_MAX_CONE_STEPSIZE (HN_STEPSIZE * 128 * 1024u / 128u)
+__device__ __forceinline__ float to_stepping_space(float t, float cone) {
+	if (cone <= 1e-5f) return t / HN_STEPSIZE;
+	float log1p_c = logf(1.0f + cone);
+	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+	if (t <= at) return (t - at) / HN_STEPSIZE + a;
+	if (t <= bt) return logf(t) / log1p_c;
+	return (t - bt) / HN_MAX_CONE_STEPSIZE + b;
+}
+__device__ __forceinline__ float from_stepping_space(float n, float cone) {
+	if (cone <= 1e-5f) return n * HN_STEPSIZE;
+	float log1p_c = logf(1.0f + cone);
+	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
+	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
+	if (n <= a) return (n - a) * HN_STEPSIZE + at;
+	if (n <= b) return expf(n * log1p_c);
+	return (n - b) * HN_MAX_CONE_STEPSIZE + bt;
+}
+__device__ __forceinline__ float advance_n_steps(float t, float cone, float n) { return from_stepping_space(to_stepping_space(t, cone) + n, cone); }
+__device__ __forceinline__ float calc_dt(float t, float cone) { return advance_n_steps(t, cone, 1.0f) - t; }
+
 // ---- camera models (common_device.cuh:249-483): lens undistortion, parallax shift, depth of field ----
 // ELensMode (common.h:223-230): 0 Perspective, 1 OpenCV, 2 FTheta, 3 LatLong, 4 OpenCVFisheye, 5 Equirectangular
 __device__ __forceinline__ void opencv_distortion_delta(const float* k, float u, float v, float* du, float* dv) {

@@ -132,30 +132,7 @@ __device__ __forceinline__ bool occupied_at(V3 pos, const uint8_t* __restrict__ 
 	uint32_t idx = morton3D(ix, iy, iz);
 	return __ldg(bits + idx / 8 + (GRID_CELLS * mip) / 8) & (1 << (idx % 8));
 }
-#define HN_STEPSIZE (1.73205080757f / 1024.0f)
-#define HN_MAX_CONE_STEPSIZE (HN_STEPSIZE * 128 * 1024u / 128u)
-__device__ __forceinline__ float to_stepping_space(float t, float cone) {
-	if (cone <= 1e-5f) return t / HN_STEPSIZE;
-	float log1p_c = logf(1.0f + cone);
-	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
-	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
-	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
-	if (t <= at) return (t - at) / HN_STEPSIZE + a;
-	if (t <= bt) return logf(t) / log1p_c;
-	return (t - bt) / HN_MAX_CONE_STEPSIZE + b;
-}
-__device__ __forceinline__ float from_stepping_space(float n, float cone) {
-	if (cone <= 1e-5f) return n * HN_STEPSIZE;
-	float log1p_c = logf(1.0f + cone);
-	float a = (logf(HN_STEPSIZE) - logf(log1p_c)) / log1p_c;
-	float b = (logf(HN_MAX_CONE_STEPSIZE) - logf(log1p_c)) / log1p_c;
-	float at = expf(a * log1p_c), bt = expf(b * log1p_c);
-	if (n <= a) return (n - a) * HN_STEPSIZE + at;
-	if (n <= b) return expf(n * log1p_c);
-	return (n - b) * HN_MAX_CONE_STEPSIZE + bt;
-}
-__device__ __forceinline__ float advance_n_steps(float t, float cone, float n) { return from_stepping_space(to_stepping_space(t, cone) + n, cone); }
-__device__ __forceinline__ float calc_dt(float t, float cone) { return advance_n_steps(t, cone, 1.0f) - t; }
+// to_stepping_space / from_stepping_space / advance_n_steps / calc_dt: hn_device_math.cuh (shared with the training ray generator)
 __device__ __forceinline__ float min_ba(float a, float b) { return b < a ? b : a; } // std::min
 __device__ __forceinline__ float distance_to_next_voxel(V3 pos, V3 dir, V3 idir, float res) {
 	V3 p = res * (pos - 0.5f);

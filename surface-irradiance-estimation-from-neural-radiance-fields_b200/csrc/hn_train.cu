@@ -200,8 +200,8 @@ __global__ void train_raygen_kernel(TrainDataDev D, FrameArgs a, uint32_t n_rays
 		const float t0 = (a.render_aabb[k] - oo[k]) / dd[k], t1 = (a.render_aabb[3 + k] - oo[k]) / dd[k];
 		tmin = fmaxf(tmin, fminf(t0, t1)); tmax = fminf(tmax, fmaxf(t0, t1));
 	}
-	const float step_sz = HN_MIN_STEP; // cone angle 0 (aabb_scale 1); larger scenes start a fraction of the local step later
-	ray_t[i] = (tmin <= tmax && valid_ray) ? fmaxf(tmin, 0.0f) + jitter * step_sz : 3.0e4f; // beyond MAX_DEPTH: the march finds nothing (:812-815 drops invalid rays)
+	// startt = advance_n_steps(tmin, cone_angle, random) (:833): a random fraction of the LOCAL step, which grows with t when the cone angle is > 0 (aabb_scale > 1)
+	ray_t[i] = (tmin <= tmax && valid_ray) ? advance_n_steps(fmaxf(tmin, 0.0f), a.cone_angle, jitter) : 3.0e4f; // beyond MAX_DEPTH: the march finds nothing (:812-815 drops invalid rays)
 	#pragma unroll
 	for (int k = 0; k < 3; ++k) {
 		const float texc = k == 0 ? tex.x : (k == 1 ? tex.y : tex.z);

@@ -816,7 +816,7 @@ void check_ready(hn_context* ctx, bool need_dataset) {
 } // namespace
 
 void train_set_dataset(hn_context* ctx, const float* rgba, uint32_t n, int w, int h, const float* cams, const float focal[2], const float principal[2]) {
-	if (!rgba || !cams || n == 0 || w <= 0 || h <= 0 || !(focal[0] > 0.f) || !(focal[1] > 0.f)) throw std::runtime_error("bad training dataset arguments");
+	if (!rgba || !cams || n == 0 || w < 2 || h < 2 || !(focal[0] > 0.f) || !(focal[1] > 0.f)) throw std::runtime_error("bad training dataset arguments");
 	TrainState& t = ctx->train;
 	const size_t px = (size_t)n * w * h;
 	t.images.ensure(px); t.cams.ensure((size_t)n * 12);

@@ -52,19 +52,52 @@ def test_trace_matches_brute_force(hn, orc, compat):
     assert np.array_equal(ot, bt) and np.array_equal(ott.view(np.uint32), btt.view(np.uint32))
 
 
-def test_reference_fixture_meshes(hn, orc, root):
-    """bunny.obj x3 as in data/geometry/geometrypaths.json (when the reference tree is mounted) else a procedural stand-in."""
-    path = "/root/reference/data/geometry/objs/bunny.obj"
-    tb = hn.Testbed()
+def _parse_obj_triangles(path):
+    """a plain OBJ reader for the test (v / f with optional vt / vn indices, polygons fanned): [n][9] float32"""
+    verts, tris = [], []
+    for line in open(path):
+        t = line.split()
+        if not t:
+            continue
+        if t[0] == "v":
+            verts.append([float(x) for x in t[1:4]])
+        elif t[0] == "f":
+            idx = [int(x.split("/")[0]) for x in t[1:]]
+            idx = [i - 1 if i > 0 else len(verts) + i for i in idx]
+            for k in range(1, len(idx) - 1):
+                tris.append(verts[idx[0]] + verts[idx[k]] + verts[idx[k + 1]])
+    return np.asarray(tris, np.float32)
+
+
+@pytest.mark.parametrize("compat", [False, True])
+def test_reference_fixture_meshes(hn, orc, root, compat):
+    """bunny.obj x3 with the centres of the reference's data/geometry/geometrypaths.json: the product's OBJ loader + load_mesh normalisation +
+    BVH against the oracle's brute-force search on triangles parsed independently here. The fixture is read from the reference tree, or from
+    oracle/_ref/fixtures/ (`make -C oracle ref` puts it there; git-ignored, it travels to the GPU box with the built checker)."""
+    cands = ["/root/reference/data/geometry/objs/bunny.obj", os.path.join(root, "oracle", "_ref", "fixtures", "bunny.obj")]
+    path = next((p for p in cands if os.path.exists(p)), None)
+    if path is None:
+        pytest.skip("bunny.obj neither under /root/reference nor under oracle/_ref/fixtures (make -C oracle ref)")
     centers = [(0.0, 0.0, 0.0), (1.0, 1.0, 1.0), (-1.0, 1.0, 1.0)]
-    if os.path.exists(path):
-        for c in centers:
-            tb._check(hn.testbed._lib.hn_load_mesh_file(tb._h, path.encode(), hn.testbed._ptr(np.asarray(c, np.float32))))
-    else:
-        pytest.skip("reference fixtures not mounted on this box")
+    tb = hn.Testbed()
+    for c in centers:
+        tb._check(hn.testbed._lib.hn_load_mesh_file(tb._h, path.encode(), hn.testbed._ptr(np.asarray(c, np.float32))))
     tb.build_scene()
-    bb = tb.scene_aabb()
-    assert bb[0] < -0.4 and bb[3] > 1.4
+    tb.set_option("compat_nearest_aabb_only", float(compat))
+    raw = _parse_obj_triangles(path)
+    assert raw.shape[0] == 4968
+    meshes = [orc.normalize_mesh(raw, c) for c in centers]
+    scene = orc.Scene(meshes)
+    assert np.array_equal(tb.scene_aabb(), scene.aabb())          # load_mesh normalisation bit-identical
+    rng = np.random.default_rng(31)
+    o, d = rays_towards(rng, 30000, centre=(0.5, 1.0, 1.0), spread=1.6, dist=4.0)
+    o[:64] = [0.5, 0.5, 4.0]; d[:64] = [0, 0, -1]
+    p = orc.render_params(8, 8, hn.synthetic.default_camera(), compat=compat, n_threads=8)
+    mesh, tri, t = tb.op_trace(o, d)
+    bm, bt, btt = scene.trace(p, o, d, brute=True)
+    assert np.array_equal(tri, bt) and np.array_equal(mesh, bm) and np.array_equal(t.view(np.uint32), btt.view(np.uint32))
+    assert (bt >= 0).sum() > 3000 and len(set(bm[bt >= 0].tolist())) == 3     # all three bunnies are hit
+    assert tb.frame_stats().n_bvh_stack_overflows == 0
 
 
 def hybrid_setup(hn, root, mesh, mesh_aabb, blob_scale=1.0):

@@ -68,6 +68,9 @@ int hn_create(hn_context** out, int cuda_device) {
 	ctx->stream = ctx->own_stream;
 	HN_CUDA(cudaMallocHost((void**)&ctx->pinned_counters, CNT_N * sizeof(uint32_t) * 4));
 	for (auto& e : ctx->pass_events) HN_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	HN_CUDA(cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
+	HN_CUDA(cudaEventCreateWithFlags(&ctx->fork_event, cudaEventDisableTiming));
+	HN_CUDA(cudaEventCreateWithFlags(&ctx->join_event, cudaEventDisableTiming));
 	ctx->counters.ensure(CNT_N);
 	ctx->bitfield.ensure(BITFIELD_BYTES);
 	HN_CATCH(ctx)
@@ -81,6 +84,9 @@ void hn_destroy(hn_context* ctx) {
 	release_param_textures(ctx);
 	if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
 	for (auto& e : ctx->pass_events) if (e) cudaEventDestroy(e);
+	if (ctx->fork_event) cudaEventDestroy(ctx->fork_event);
+	if (ctx->join_event) cudaEventDestroy(ctx->join_event);
+	if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
 	if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
@@ -242,7 +248,7 @@ static std::map<std::string, OptRef> option_table(hn_context* c) {
 		{"sample_focal_plane_proportional_to_error", {&c->train_cfg.sample_focal_plane_proportional_to_error, 1, true}},
 		{"sample_image_proportional_to_error", {&c->train_cfg.sample_image_proportional_to_error, 1, true}},
 		{"snapshot_optimizer_state", {&o.snapshot_optimizer_state, 1, true}},
-		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}}, {"bvh_sah", {&o.bvh_sah, 1, true}},
+		{"env_light_samples", {&o.env_light_samples, 1, true}}, {"env_light_source", {&o.env_light_source, 1, true}}, {"env_light_sampling", {&o.env_light_sampling, 1, true}}, {"env_light_batch", {&o.env_light_batch, 1, true}}, {"tight_t_far", {&o.tight_t_far, 1, true}}, {"march_simple", {&o.march_simple, 1, true}}, {"overlap_raygen", {&o.overlap_raygen, 1, true}}, {"bvh_sah", {&o.bvh_sah, 1, true}},
 	};
 }
 int hn_set_option(hn_context* ctx, const char* name, const float* values, int n_values) {
@@ -587,19 +593,60 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 	HN_CUDA(cudaMemsetAsync(frame, 0, n_px * sizeof(float4), s));
 	HN_CUDA(cudaMemsetAsync(depth, 0, n_px * sizeof(float), s));
 	const bool do_mesh = ctx->opt.render_mesh && !ctx->meshes.empty();
+	const bool do_nerf = ctx->opt.render_nerf && ctx->has_net;
+	const bool nerf_2d = ctx->opt.render_mode == 8 || ctx->opt.render_mode == 10;
+	const bool env_light = do_mesh && (a.envmap || a.env_source == 1) && a.env_samples > 0;
+	if (do_mesh) need(ctx->scene_built, "scene has meshes but hn_build_scene was not called");
+	if (do_nerf) {
+		need(ctx->has_params, "network parameters not set");
+		need(ctx->has_bitfield, "occupancy grid not set");
+		if (!nerf_2d) {
+			const int m = ctx->opt.render_mode;
+			need(m == 0 || (m >= 1 && m <= 7) || m == 9 || m == 12, "render_mode must be one of ERenderMode: 0-10 or 12 (EncodingVis)");
+			need(m != 5 || ctx->net.density_hidden <= 2, "render_mode Normals: at most two hidden layers in the density network");
+			need((m >= 1 && m <= 4) || (ctx->opt.composite_impl == 1 && !ctx->opt.fuse_composite) || (ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite), "visualisation render modes need composite_impl 1");
+		}
+	}
+	// init rays + advance to the first occupied cell (+ SH of the direction) for every pixel; depth_or_null: see raygen_kernel
+	RaySoA rays = {};
+	auto set_up_rays = [&](const FrameArgs& fa, float* depth_or_null, cudaStream_t rs) {
+		uint32_t* cnt = ctx->counters.p;
+		HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), rs));
+		launch_raygen(fa, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth_or_null, frame, rs);
+		st.n_kernel_launches += 1;
+		if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) { // SH input of the colour MLP, once per ray instead of once per sample
+			launch_ray_sh(ctx->alive_a.p, cnt + CNT_ALIVE_A, (uint32_t)n_px, rays.d_mw, ctx->ray_sh.p, rs);
+			st.n_kernel_launches += 1;
+		}
+	};
+	if (do_nerf && !nerf_2d) { // buffers first: growing one is a cudaMalloc, which would serialise the two streams below
+		ensure_rays(ctx, n_px);
+		rays = ray_soa(ctx);
+		if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) { ctx->ray_sh.ensure(2 * n_px); rays.sh = ctx->ray_sh.p; }
+	}
+	// Hybrid frame: the ray set-up needs nothing from the mesh pass (the mesh depth only clips the march), so it runs beside it on a second
+	// stream - both kernels are latency-bound walks (BVH / occupancy grid) that leave issue slots free. Not with an environment map (its
+	// background write looks at the mesh depth) and not when per-kernel times are being taken.
+	const bool overlap = do_mesh && do_nerf && !nerf_2d && ctx->opt.overlap_raygen && !ctx->opt.profile && !env_light && !a.envmap;
 	if (do_mesh) {
-		need(ctx->scene_built, "scene has meshes but hn_build_scene was not called");
-		const bool env_light = (a.envmap || a.env_source == 1) && a.env_samples > 0;
 		EnvHits hits = {nullptr, nullptr, nullptr, nullptr};
 		if (env_light) {
 			ctx->hit_pos_pix.ensure(n_px); ctx->hit_nrm.ensure(n_px); ctx->hit_albedo.ensure(n_px); ctx->hit_count.ensure(1);
 			HN_CUDA(cudaMemsetAsync(ctx->hit_count.p, 0, sizeof(uint32_t), s));
 			hits = env_hits(ctx);
 		}
+		if (overlap) {
+			FrameArgs fa = a; fa.depth_test = 1;
+			HN_CUDA(cudaEventRecord(ctx->fork_event, s));
+			HN_CUDA(cudaStreamWaitEvent(ctx->side_stream, ctx->fork_event, 0));
+			set_up_rays(fa, nullptr, ctx->side_stream);
+			HN_CUDA(cudaEventRecord(ctx->join_event, ctx->side_stream));
+		}
 		tm.start();
 		launch_mesh_pass(a, ctx->scene_dev(), frame, depth, hits, s);
 		st.n_kernel_launches += 1;
 		tm.stop(st.ms_mesh);
+		if (overlap) HN_CUDA(cudaStreamWaitEvent(s, ctx->join_event, 0));
 		if (env_light) {
 			Timer te(ctx->opt.profile != 0, s);
 			te.start();
@@ -608,36 +655,20 @@ void render_frame_impl(hn_context* ctx, const FrameArgs& args_in, float4* frame,
 		}
 		a.depth_test = 1;
 	}
-	if (ctx->opt.render_nerf && ctx->has_net) {
-		need(ctx->has_params, "network parameters not set");
-		need(ctx->has_bitfield, "occupancy grid not set");
-		if (ctx->opt.render_mode == 8 || ctx->opt.render_mode == 10) { // the 2-D modes never trace (render_nerf, src/testbed_nerf.cu:2397-2460)
-			need(ctx->has_params, "network parameters not set");
+	if (do_nerf) {
+		if (nerf_2d) { // the 2-D modes never trace (render_nerf, src/testbed_nerf.cu:2397-2460)
 			render_2d(ctx, a, frame, depth, s);
 			total.stop(st.ms_total);
 			HN_CUDA(cudaGetLastError());
 			return;
 		}
-		{
-			const int m = ctx->opt.render_mode;
-			need(m == 0 || (m >= 1 && m <= 7) || m == 9 || m == 12, "render_mode must be one of ERenderMode: 0-10 or 12 (EncodingVis)");
-			need(m != 5 || ctx->net.density_hidden <= 2, "render_mode Normals: at most two hidden layers in the density network");
-			need((m >= 1 && m <= 4) || (ctx->opt.composite_impl == 1 && !ctx->opt.fuse_composite) || (ctx->opt.eval_impl == 1 && ctx->opt.fuse_composite), "visualisation render modes need composite_impl 1");
+		if (!overlap) {
+			rays = ray_soa(ctx); // the light pass may have grown (moved) the ray buffers
+			if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) rays.sh = ctx->ray_sh.p;
+			tm.start();
+			set_up_rays(a, depth, s);
+			tm.stop(st.ms_raygen);
 		}
-		ensure_rays(ctx, n_px);
-		uint32_t* cnt = ctx->counters.p;
-		HN_CUDA(cudaMemsetAsync(cnt, 0, CNT_N * sizeof(uint32_t), s));
-		RaySoA rays = ray_soa(ctx);
-		tm.start();
-		launch_raygen(a, ctx->bitfield.p, rays, ctx->alive_a.p, cnt, depth, frame, s);
-		st.n_kernel_launches += 1;
-		if (ctx->opt.eval_impl == 1 && ctx->opt.eval_ray_sh) { // SH input of the colour MLP, once per ray instead of once per sample
-			ctx->ray_sh.ensure(2 * n_px);
-			launch_ray_sh(ctx->alive_a.p, cnt + CNT_ALIVE_A, (uint32_t)n_px, rays.d_mw, ctx->ray_sh.p, s);
-			rays.sh = ctx->ray_sh.p;
-			st.n_kernel_launches += 1;
-		}
-		tm.stop(st.ms_raygen);
 		st.n_rays_alive = run_passes(ctx, a, rays, frame, depth, false, s, tm);
 		st.n_samples = (uint64_t)ctx->pinned_counters[CNT_SAMPLES_LO] | ((uint64_t)ctx->pinned_counters[CNT_SAMPLES_HI] << 32);
 		st.n_samples_composited = (uint64_t)ctx->pinned_counters[CNT_COMPOSITED_LO] | ((uint64_t)ctx->pinned_counters[CNT_COMPOSITED_HI] << 32);

@@ -261,26 +261,41 @@ CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_
 // kernel runs at memory latency x waves instead of 32 dependent round trips per warp (composite_kernel above keeps 32 rays
 // per warp and is latency-bound by its serial ray loop). Survivors are flagged; compact_kernel builds the next list.
 __global__ void __launch_bounds__(512) composite_ray_kernel(const __grid_constant__ CompArgs a, const uint32_t* __restrict__ n_alive_ptr,
-	const uint32_t* __restrict__ sample_counts, const uint2* __restrict__ net_out) {
+	const uint32_t* __restrict__ sample_counts, const uint2* __restrict__ net_out, uint32_t max_rays) {
 	__shared__ uint32_t block_total;
 	if (threadIdx.x == 0) block_total = 0;
 	__syncthreads();
 	const uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
-	if (chunk < *n_alive_ptr) { // warp-uniform
-		const uint32_t count = sample_counts[chunk];
-		uint2 o = make_uint2(0u, 0u);
-		if ((uint32_t)lane < count) o = __ldg(net_out + (size_t)chunk * CHUNK + lane);
-		const RayPre pre = composite_prefetch(a, chunk, count, lane);
-		const uint32_t n = composite_chunk(a, pre, chunk, count, lane, o);
-		if (lane == 0 && n) atomicAdd(&block_total, n);
+	if (chunk < max_rays) { // warp-uniform; max_rays = the host's upper bound of the live count, the size every buffer below was grown to
+		// The kernel is bound by its chain of dependent loads (live count -> sample count -> sample / network output, list slot -> ray state),
+		// not by bandwidth: everything indexed by the chunk alone is requested at once, whether or not the chunk turns out to be live or the
+		// lane to hold a sample (stale rows of an earlier pass sit there: read, never used). Only the ray state waits for the list slot.
+		// (volatile asm: the compiler otherwise sinks these loads back behind the branches that use them)
+		uint2 o_raw; float4 s_raw; uint32_t count;
+		asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(o_raw.x), "=r"(o_raw.y) : "l"(net_out + (size_t)chunk * CHUNK + lane));
+		asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(s_raw.x), "=f"(s_raw.y), "=f"(s_raw.z), "=f"(s_raw.w) : "l"(a.samples + (size_t)chunk * CHUNK + lane));
+		asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(count) : "l"(sample_counts + chunk));
+		if (chunk < *n_alive_ptr) {
+			RayPre pre;
+			pre.r = a.alive_list[chunk];
+			pre.rgba = a.rays.rgba[pre.r];
+			pre.depth = a.rays.depth[pre.r];
+			pre.max_weight = a.rays.d_mw[pre.r].w;
+			pre.n_steps = a.rays.n_steps[pre.r];
+			pre.o_t = a.render_mode == 7 ? a.rays.o_t[pre.r] : make_float4(0.f, 0.f, 0.f, 0.f);
+			const bool has = (uint32_t)lane < count;
+			pre.s = has ? s_raw : make_float4(0.f, 0.f, 0.f, 0.f);
+			const uint32_t n = composite_chunk(a, pre, chunk, count, lane, has ? o_raw : make_uint2(0u, 0u));
+			if (lane == 0 && n) atomicAdd(&block_total, n);
+		}
 	}
 	__syncthreads();
 	if (threadIdx.x == 0 && block_total) atomicAdd((unsigned long long*)&a.counters[CNT_COMPOSITED_LO], (unsigned long long)block_total);
 }
 void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const uint32_t* sample_counts, const uint2* net_out, uint32_t max_rays, cudaStream_t s) {
 	if (!max_rays) return;
-	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out);
+	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out, max_rays);
 }
 
 // ERenderMode::Slice, second half (compute_nerf_rgba with depth 0.01, src/testbed_nerf.cu:408-421, then shade_kernel_nerf :1361-1401):
@@ -341,21 +356,24 @@ void launch_unwarp_foveated(const float coeffs[24], int w_in, int h_in, const fl
 // the ray ends at the first sample with T_j < min_transmittance (oracle nerf_transmittance) or when it leaves the volume.
 __global__ void __launch_bounds__(512) transmittance_kernel(FrameArgs a, RaySoA rays, const uint32_t* __restrict__ alive_list,
 	const uint32_t* __restrict__ n_alive_ptr, const float4* __restrict__ samples, const uint32_t* __restrict__ sample_counts,
-	const uint2* __restrict__ net_out, uint32_t* __restrict__ survive, uint32_t* __restrict__ counters) {
+	const uint2* __restrict__ net_out, uint32_t* __restrict__ survive, uint32_t* __restrict__ counters, uint32_t max_rays) {
 	__shared__ uint32_t block_total;
 	if (threadIdx.x == 0) block_total = 0;
 	__syncthreads();
 	const uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const uint32_t lane = threadIdx.x & 31u;
-	if (chunk < *n_alive_ptr) { // warp-uniform
-		const uint32_t count = sample_counts[chunk];
+	uint2 o = make_uint2(0u, 0u); float dt_in = 0.0f; uint32_t count = 0;
+	if (chunk < max_rays) { // as composite_ray_kernel: what the chunk index alone addresses is requested before the dependent loads
+		const size_t si = (size_t)chunk * CHUNK + lane;
+		asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(o.x), "=r"(o.y) : "l"(net_out + si));
+		asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(dt_in) : "l"(&samples[si].w));
+		asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(count) : "l"(sample_counts + chunk));
+	}
+	if (chunk < max_rays && chunk < *n_alive_ptr) { // warp-uniform
 		const uint32_t r = alive_list[chunk];
 		const float T_in = rays.rgba[r].w;
 		float f = 1.0f;
 		if (lane < count) {
-			const size_t si = (size_t)chunk * CHUNK + lane;
-			const uint2 o = __ldg(net_out + si);
-			const float dt_in = __ldg(&samples[si].w);
 			const __half2 bs = *reinterpret_cast<const __half2*>(&o.y);
 			const float sigma = act_density(__high2float(bs), a.density_act);
 			const float dt_range = __fsub_rn(__fmul_rn(HN_MIN_STEP, 128.0f), HN_MIN_STEP);
@@ -383,7 +401,7 @@ __global__ void __launch_bounds__(512) transmittance_kernel(FrameArgs a, RaySoA 
 void launch_transmittance(const FrameArgs& a, RaySoA rays, const uint32_t* alive_list, const uint32_t* n_alive_ptr, const float4* samples,
 	const uint32_t* sample_counts, const uint2* net_out, uint32_t* survive, uint32_t* counters, uint32_t max_rays, cudaStream_t s) {
 	if (!max_rays) return;
-	transmittance_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, rays, alive_list, n_alive_ptr, samples, sample_counts, net_out, survive, counters);
+	transmittance_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, rays, alive_list, n_alive_ptr, samples, sample_counts, net_out, survive, counters, max_rays);
 }
 
 // next pass's live-ray list from the survive flags of the fused network+composite kernel (one atomic per warp)

@@ -93,6 +93,7 @@ struct Options {
 	int env_light_samples = 16;                 // K light rays per mesh hit when an envmap is set (0 = background only)
 	int env_light_batch = 32 << 20;             // light rays in flight per batch (bounds the workspace: ~200 bytes per ray)
 	int bvh_sah = 1;                            // BVH build: 1 = binned surface-area heuristic, 0 = the reference's median split (A/B); read by hn_build_scene
+	int overlap_raygen = 1;                     // 1: hybrid frames set their NeRF rays up on a second stream while the mesh pass runs (A/B)
 	int march_simple = 1;                       // 1: compile-time specialised raygen / march kernels when cone angle 0, one cascade, axis-aligned crop (A/B)
 	int tight_t_far = 1;                        // 1: rays are cut off at the last flagged coarse occupancy cell (occ_t_far_tight), 0: at the box of the set cells (A/B)
 	int mesh_aabb_user = 0;
@@ -222,6 +223,8 @@ struct hn_context {
 	hn::DevBuf<uint32_t> survive;
 	uint32_t* pinned_counters = nullptr; // ring of 4 x CNT_N uint32 (pass-loop read-backs)
 	cudaEvent_t pass_events[4] = {nullptr, nullptr, nullptr, nullptr};
+	cudaStream_t side_stream = nullptr;     // ray set-up of a hybrid frame runs here beside the mesh pass (option overlap_raygen)
+	cudaEvent_t fork_event = nullptr, join_event = nullptr;
 	// render_to_host buffers
 	hn::DevBuf<float4> frame, accum, tonemapped;
 	hn::DevBuf<float> depth;

@@ -304,7 +304,8 @@ __global__ void __launch_bounds__(256) raygen_kernel(FrameArgs a, const uint8_t*
 	if (owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) {
 		idx = x + (uint32_t)a.w * y;
 		// src/testbed_nerf.cu:1490-1493: a cleared depth (0) becomes "nothing", a mesh depth survives
-		if (depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
+		// (depth_buffer == nullptr: the mesh pass, which writes every pixel's depth itself, is running beside this kernel)
+		if (depth_buffer && depth_buffer[idx] < 0.01f) depth_buffer[idx] = MAX_DEPTH_F;
 		alive = start_ray<SIMPLE>(a, bits, x, y, o, d, t, t_far);
 		// :1526-1528: envmap -> frame buffer; in hybrid frames only where the mesh pass left nothing
 		if (a.envmap && !(a.depth_test && depth_buffer[idx] < MAX_DEPTH_F)) if (d.x != 0.0f || d.y != 0.0f || d.z != 0.0f) frame[idx] = read_envmap(a.envmap, a.env_w, a.env_h, d);

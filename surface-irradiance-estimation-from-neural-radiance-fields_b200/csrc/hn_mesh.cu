@@ -452,12 +452,43 @@ __device__ bool mesh_pixel(const FrameArgs& a, const SceneDev& sc, float4* __res
 	return true;
 }
 
+// Thread -> pixel of the mesh pass: a warp covers an 8 x 4 pixel patch and a block of 128 threads a 16 x 8 one (camera rays of a patch stay
+// together deeper into the tree than those of a 32 x 1 row segment). One rank: patches row-major over the frame. Tile-sharded: the same patches
+// inside each of the rank's tiles when the tile size allows it, else the row-major order of owned_pixel. Results are keyed by pixel, so the
+// order changes nothing but the speed.
+__device__ __forceinline__ void patch_xy(uint32_t k, uint32_t patches_x, uint32_t& x, uint32_t& y) {
+	const uint32_t patch = k / MESH_BLOCK, t = k % MESH_BLOCK, warp = t >> 5, lane = t & 31u;
+	x = (patch % patches_x) * 16u + (warp & 1u) * 8u + (lane & 7u);
+	y = (patch / patches_x) * 8u + (warp >> 1) * 4u + (lane >> 3);
+}
+__device__ __forceinline__ bool mesh_thread_pixel(const FrameArgs& a, uint32_t i, uint32_t& x, uint32_t& y) {
+	const uint32_t w = (uint32_t)a.w, h = (uint32_t)a.h;
+	if (a.world <= 1) {
+		const uint32_t px = (w + 15u) / 16u, py = (h + 7u) / 8u;
+		if (i >= px * py * MESH_BLOCK) return false;
+		patch_xy(i, px, x, y);
+		return x < w && y < h;
+	}
+	const uint32_t tw = (uint32_t)a.tile_w, th = (uint32_t)a.tile_h;
+	if ((tw % 16u) || (th % 8u)) return owned_pixel(a, i, x, y);
+	const uint32_t per_tile = tw * th, tiles_x = (w + tw - 1) / tw, tiles_y = (h + th - 1) / th;
+	const uint32_t tile = (i / per_tile) * (uint32_t)a.world + (uint32_t)a.rank;
+	if (tile >= tiles_x * tiles_y) return false;
+	patch_xy(i % per_tile, tw / 16u, x, y);
+	x += (tile % tiles_x) * tw; y += (tile / tiles_x) * th;
+	return x < w && y < h;
+}
+__host__ inline uint32_t mesh_pass_threads(const FrameArgs& a) {
+	if (a.world <= 1) return (uint32_t)((a.w + 15) / 16) * (uint32_t)((a.h + 7) / 8) * MESH_BLOCK;
+	return owned_pixel_threads(a);
+}
+
 __global__ void __launch_bounds__(MESH_BLOCK) mesh_pass_kernel(FrameArgs a, SceneDev sc, float4* __restrict__ frame, float* __restrict__ depth_buffer, EnvHits hits) {
 	__shared__ int stack_s[STACK_DEPTH * MESH_BLOCK];
 	uint32_t x = 0, y = 0;
 	bool lit = false;
 	V3 org, nrm, alb;
-	if (owned_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) lit = mesh_pixel(a, sc, frame, depth_buffer, stack_s + threadIdx.x, x, y, org, nrm, alb);
+	if (mesh_thread_pixel(a, blockIdx.x * blockDim.x + threadIdx.x, x, y)) lit = mesh_pixel(a, sc, frame, depth_buffer, stack_s + threadIdx.x, x, y, org, nrm, alb);
 	if (!hits.count) return; // warp-uniform
 	const uint32_t mask = __ballot_sync(0xffffffffu, lit);
 	if (!mask) return;
@@ -532,7 +563,7 @@ __global__ void __launch_bounds__(256) envlight_reduce_kernel(FrameArgs a, EnvHi
 }
 
 void launch_mesh_pass(const FrameArgs& a, SceneDev scene, float4* frame, float* depth_buffer, EnvHits hits, cudaStream_t s) {
-	uint32_t n = owned_pixel_threads(a);
+	uint32_t n = mesh_pass_threads(a);
 	if (!n) return;
 	mesh_pass_kernel<<<(n + MESH_BLOCK - 1) / MESH_BLOCK, MESH_BLOCK, 0, s>>>(a, scene, frame, depth_buffer, hits);
 }

@@ -490,6 +490,7 @@ def main():
     ap.add_argument("--crop-unit-cube", action="store_true", help="render box = the NeRF's unit cube instead of the Geometry-mode default (mesh box + 4)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"], help="multi-GPU frame gather: peer-memory tile scatter (default) or the round-1 NCCL all-gather")
     ap.add_argument("--opt", action="append", default=[], help="name=value library option (hn_set_option) for A/B runs, e.g. --opt eval_gather=2")
+    ap.add_argument("--e2e-delivery", default="host", choices=["host", "gather"], help="N>1 e2e: tiles scattered straight to a shared host frame / gathered on rank 0 then copied")
     ap.add_argument("--workload", default="config3", choices=["config2", "config3", "config4", "config5"],
                     help="BASELINE.json configs[1] NeRF-only 1080p / configs[2] hybrid 1080p (default, the headline) / configs[3] 4K hybrid + envmap light")
     args = ap.parse_args()
@@ -708,20 +709,56 @@ def main():
             tb.render(W, H, 1, True, out=host_out)
         e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
     else:
-        # multi-GPU e2e: the gathered frame is read back on rank 0
-        host = torch.empty(H, W, 4, pin_memory=True) if rank == 0 else None
+        # multi-GPU e2e: the frame is delivered to HOST memory. "host" (default): one shared-memory frame every rank has mapped and
+        # page-locked (hn_host_register); each rank scatters the tiles it owns straight into it over its own PCIe link (hn_scatter_tiles,
+        # one launch), then stream sync + barrier - no gather on rank 0, no 33 MB read-back through one link. "gather": the round-1 path
+        # (peer gather into rank 0's device frame, then rank 0 copies it to pinned host memory), kept for A/B.
+        n_e2e = max(3, min(args.steps, 10))
+        if args.e2e_delivery == "host":
+            from importlib import import_module
+            tiles_mod = import_module(hn.__name__ + ".tiles")
+            names = [f"hn_e2e_{os.getpid()}" if rank == 0 else None]
+            shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=True) if rank == 0 else None
+            dist.broadcast_object_list(names, src=0)
+            if rank != 0:
+                shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=False)
+            host_dev = tb.host_register(shared.host_ptr, shared.n_bytes)
+
+            def e2e_step():
+                tb.set_camera_cols(cam)
+                tb.render_frame(cam, cam, W, H, frame.data_ptr(), depth.data_ptr(), 0, stream)
+                tb.scatter_tiles(W, H, rank, world, frame.data_ptr(), 0, host_dev, 0, stream)
+                torch.cuda.synchronize()
+                dist.barrier()
+        else:
+            host = torch.empty(H, W, 4, pin_memory=True) if rank == 0 else None
+
+            def e2e_step():
+                step()
+                if rank == 0:
+                    host.copy_(frame, non_blocking=False)
+                barrier()
+        e2e_step()
         barrier()
         t0 = time.perf_counter()
-        n_e2e = max(3, min(args.steps, 10))
         for _ in range(n_e2e):
-            step()
-            if rank == 0:
-                host.copy_(frame, non_blocking=False)
-            barrier()
+            e2e_step()
         e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
         t = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
+        if args.e2e_delivery == "host":
+            # the host frame must be the frame the peer gather assembles on rank 0 (untimed check)
+            step(); barrier()
+            if rank == 0:
+                e2e_check = float(np.abs(shared.array - frame.cpu().numpy()).max())
+                if breakdown is not None:
+                    breakdown["e2e_host_frame_max_abs_vs_gathered_frame"] = e2e_check
+                    breakdown["e2e_delivery"] = "every rank scatters its tiles into one page-locked shared host frame (hn_host_register + hn_scatter_tiles)"
+            barrier()
+            tb.host_unregister(shared.host_ptr)
+            barrier()
+            shared.close()
 
     cpu_baseline, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "config3":

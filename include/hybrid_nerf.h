@@ -241,6 +241,14 @@ int hn_shared_open(hn_context* ctx, const unsigned char handle[64], void** dev_p
 int hn_shared_release(hn_context* ctx, void* dev_ptr, int owner);
 int hn_scatter_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev,
 	float* frame_remote, float* depth_remote, void* cuda_stream);
+/* The same scatter with HOST memory as its target - the sharded counterpart of render_to_cpu's device -> host copy
+ * (src/python_api.cu:124-202). host_ptr: `bytes` of host memory every rank's process has mapped (one POSIX shared-memory segment);
+ * hn_host_register page-locks it and maps it into this process's device address space, the pointer returned is a valid frame_remote /
+ * depth_remote (depth_remote may be NULL: colour only) of hn_scatter_tiles. Every rank then writes the tiles it owns straight into host
+ * memory over its own PCIe link, instead of the root rank reading the whole gathered frame back through one link. The stores are
+ * complete on the host once the scattering stream has been synchronised. */
+int hn_host_register(hn_context* ctx, void* host_ptr, size_t bytes, void** dev_ptr);
+int hn_host_unregister(hn_context* ctx, void* host_ptr);
 
 typedef struct {
 	uint64_t n_samples;        /* network samples evaluated in the last frame (ERenderMode::Cost sum) */

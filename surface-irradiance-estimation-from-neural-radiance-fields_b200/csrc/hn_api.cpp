@@ -939,10 +939,32 @@ int hn_shared_release(hn_context* ctx, void* dev_ptr, int owner) {
 }
 int hn_scatter_tiles(hn_context* ctx, int width, int height, int rank, int world, const float* frame_dev, const float* depth_dev, float* frame_remote, float* depth_remote, void* cuda_stream) {
 	HN_TRY(ctx)
-	need(frame_dev && depth_dev && frame_remote && depth_remote && world >= 1 && rank >= 0 && rank < world, "hn_scatter_tiles: bad arguments");
+	need(frame_dev && frame_remote && (depth_dev || !depth_remote) && world >= 1 && rank >= 0 && rank < world, "hn_scatter_tiles: bad arguments");
 	HN_CUDA(cudaSetDevice(ctx->device));
 	launch_scatter_tiles(width, height, rank, world, ctx->tile_w, ctx->tile_h, (const float4*)frame_dev, depth_dev, (float4*)frame_remote, depth_remote, (cudaStream_t)cuda_stream);
 	HN_CUDA(cudaGetLastError());
+	HN_CATCH(ctx)
+}
+
+// Host delivery of a sharded frame: the caller's host buffer (one POSIX shared-memory segment mapped by every rank's process) is page-locked
+// and mapped into this process's device address space; the pointer returned is a valid frame_remote / depth_remote of hn_scatter_tiles, so
+// every rank writes the tiles it owns straight into host memory over its own PCIe link (coalesced 16-byte stores, 1 KB per tile row)
+// instead of the root rank reading the whole gathered frame back through one link.
+int hn_host_register(hn_context* ctx, void* host_ptr, size_t bytes, void** dev_ptr) {
+	HN_TRY(ctx)
+	need(host_ptr && bytes > 0 && dev_ptr, "hn_host_register: bad arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaHostRegister(host_ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped));
+	cudaError_t e = cudaHostGetDevicePointer(dev_ptr, host_ptr, 0);
+	if (e != cudaSuccess) { cudaHostUnregister(host_ptr); HN_CUDA(e); }
+	HN_CATCH(ctx)
+}
+int hn_host_unregister(hn_context* ctx, void* host_ptr) {
+	HN_TRY(ctx)
+	need(host_ptr != nullptr, "hn_host_unregister: bad arguments");
+	HN_CUDA(cudaSetDevice(ctx->device));
+	HN_CUDA(cudaDeviceSynchronize());
+	HN_CUDA(cudaHostUnregister(host_ptr));
 	HN_CATCH(ctx)
 }
 

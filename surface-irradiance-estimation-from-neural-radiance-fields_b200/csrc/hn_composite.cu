@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(256) scatter_tiles_kernel(int w, int h, int ra
 		if (x >= (uint32_t)w || y >= (uint32_t)h) continue;
 		const uint32_t pix = x + w * y;
 		frame_remote[pix] = frame[pix];
-		depth_remote[pix] = depth[pix];
+		if (depth_remote) depth_remote[pix] = depth[pix];
 	}
 }
 void launch_scatter_tiles(int w, int h, int rank, int world, int tw, int th, const float4* frame, const float* depth, float4* frame_remote, float* depth_remote, cudaStream_t s) {

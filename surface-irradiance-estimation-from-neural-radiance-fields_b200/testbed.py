@@ -71,7 +71,7 @@ EXPORTS = [
     "hn_op_march_all", "hn_op_encode", "hn_op_network", "hn_op_trace", "hn_set_envmap", "hn_op_read_envmap", "hn_op_env_light_dirs",
     "hn_op_transmittance", "hn_train_set_dataset", "hn_train_init", "hn_train_accumulate", "hn_train_gradient_buffer", "hn_train_apply",
     "hn_train_step", "hn_get_train_stats", "hn_op_train_gradients", "hn_update_density_grid", "hn_mark_untrained_density_grid",
-    "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles",
+    "hn_get_density_grid", "hn_load_training_data", "hn_shared_alloc", "hn_shared_open", "hn_shared_release", "hn_scatter_tiles", "hn_host_register", "hn_host_unregister",
     "hn_render_probe", "hn_set_probe", "hn_op_probe_rays", "hn_set_stream", "hn_op_encode_noalloc",
     "hn_get_error_map", "hn_op_error_map_cdf", "hn_op_sample_training_pixels", "hn_op_error_map_deposit",
     "hn_set_hidden_area_mask", "hn_set_distortion_map", "hn_unwarp_foveated", "hn_op_foveation", "hn_train_set_image_metadata", "hn_decode_image_file", "hn_train_set_depth", "hn_op_train_gradients_depth",
@@ -99,6 +99,8 @@ _lib.hn_shared_alloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p), 
 _lib.hn_shared_open.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
 _lib.hn_shared_release.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 _lib.hn_scatter_tiles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+_lib.hn_host_register.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+_lib.hn_host_unregister.argtypes = [C.c_void_p, C.c_void_p]
 _lib.hn_op_init_rays.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32, C.c_int, C.c_int] + [C.c_void_p] * 4
 _lib.hn_op_march_all.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 6 + [C.c_uint32]
 _lib.hn_op_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
@@ -403,9 +405,19 @@ class Testbed:
         self._check(_lib.hn_shared_release(self._h, C.c_void_p(ptr), int(owner)))
 
     def scatter_tiles(self, width, height, rank, world, frame_ptr, depth_ptr, frame_remote, depth_remote, stream=0):
-        """copy this rank's tiles of the local frame / depth into the root rank's buffers (mapped with shared_open)"""
+        """copy this rank's tiles of the local frame / depth into the root rank's buffers (mapped with shared_open) or into host memory
+        (mapped with host_register; depth_remote may be 0 there: colour only)"""
         self._check(_lib.hn_scatter_tiles(self._h, width, height, rank, world, C.c_void_p(frame_ptr), C.c_void_p(depth_ptr),
-                                          C.c_void_p(frame_remote), C.c_void_p(depth_remote), C.c_void_p(stream)))
+                                          C.c_void_p(frame_remote), C.c_void_p(depth_remote or None), C.c_void_p(stream)))
+
+    def host_register(self, host_ptr: int, n_bytes: int) -> int:
+        """page-lock + map host memory (e.g. tiles.SharedHostFrame) -> pointer scatter_tiles accepts as frame_remote / depth_remote"""
+        ptr = C.c_void_p(0)
+        self._check(_lib.hn_host_register(self._h, C.c_void_p(host_ptr), n_bytes, C.byref(ptr)))
+        return int(ptr.value)
+
+    def host_unregister(self, host_ptr: int):
+        self._check(_lib.hn_host_unregister(self._h, C.c_void_p(host_ptr)))
 
     # ---- operator-level entry points (parity tests)
     def op_init_rays(self, cam0, cam1, width, height, spp_index=0, screen_center=(0.5, 0.5), relative_focal_length=None, rolling_shutter=(0, 0, 0, 1)):

@@ -71,3 +71,46 @@ def train_ray_shard(n_rays_per_rank: int, rank: int, world: int, n_images: int) 
     g = rank * n_rays_per_rank + np.arange(n_rays_per_rank, dtype=np.int64)
     img = (g * n_images) // (n_rays_per_rank * world) % n_images
     return g, img.astype(np.int64)
+
+
+class SharedHostFrame:
+    """One frame in host memory that every rank's process of a box has mapped (POSIX shared memory): the target of the sharded
+    render-to-host path - each rank page-locks the mapping (Testbed.host_register) and scatters the tiles it owns into it over its own
+    PCIe link (Testbed.scatter_tiles); any rank can read `array` once all ranks have synchronised their streams and passed a barrier.
+
+    create=True on one rank (it owns and finally unlinks the segment), create=False with the same name on the others."""
+
+    def __init__(self, name: str, height: int, width: int, channels: int = 4, create: bool = False):
+        from multiprocessing import shared_memory
+        n_bytes = height * width * channels * 4
+        self._shm = shared_memory.SharedMemory(name=name, create=create, size=n_bytes if create else 0)
+        self._owner = create
+        if not create:
+            # Python < 3.13 registers attached segments with the resource tracker too, which then unlinks them (and warns) when this
+            # process exits although the creator still owns them
+            try:
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self._shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.name = name
+        self.n_bytes = n_bytes
+        self.array = np.ndarray((height, width, channels), np.float32, buffer=self._shm.buf)
+        if create:
+            self.array[...] = 0.0
+
+    @property
+    def host_ptr(self) -> int:
+        return self.array.ctypes.data
+
+    def close(self):
+        self.array = None
+        try:
+            self._shm.close()
+        except BufferError:
+            pass
+        if self._owner:
+            try:
+                self._shm.unlink()
+            except FileNotFoundError:
+                pass

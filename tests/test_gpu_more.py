@@ -140,6 +140,43 @@ def test_tile_shards_reassemble(base, hn):
     assert torch.equal(out_f, full_f) and torch.equal(out_d, full_d)
 
 
+def test_tile_shards_scatter_to_host_memory(base, hn):
+    """The sharded render-to-host path: every rank scatters the tiles it owns straight into one page-locked shared host frame
+    (hn_host_register + hn_scatter_tiles); the host frame must equal the single-rank frame bit for bit, with and without depth."""
+    import torch
+    from importlib import import_module
+    tiles = import_module(hn.__name__ + ".tiles")
+    tb, _, _, _ = base
+    w, h, world = 200, 150, 3
+    cam = hn.synthetic.look_at_camera((1.6, 0.9, 1.8), (0.5, 0.5, 0.5))
+    dev = torch.device("cuda", 0)
+    full_f, full_d = torch.zeros(h, w, 4, device=dev), torch.zeros(h, w, device=dev)
+    tb.set_tile_shard(0, 1)
+    tb.render_frame(cam, cam, w, h, full_f.data_ptr(), full_d.data_ptr())
+    torch.cuda.synchronize()
+    host_f = tiles.SharedHostFrame(f"hn_gpu_test_f_{os.getpid()}", h, w, 4, create=True)
+    host_d = tiles.SharedHostFrame(f"hn_gpu_test_d_{os.getpid()}", h, w, 1, create=True)
+    try:
+        pf, pd = tb.host_register(host_f.host_ptr, host_f.n_bytes), tb.host_register(host_d.host_ptr, host_d.n_bytes)
+        for with_depth in (True, False):
+            host_f.array[...] = -1.0; host_d.array[...] = -1.0
+            for r in range(world):
+                f, d = torch.zeros_like(full_f), torch.zeros_like(full_d)
+                tb.set_tile_shard(r, world)
+                tb.render_frame(cam, cam, w, h, f.data_ptr(), d.data_ptr())
+                tb.scatter_tiles(w, h, r, world, f.data_ptr(), d.data_ptr() if with_depth else 0, pf, pd if with_depth else 0)
+                torch.cuda.synchronize()
+            assert np.array_equal(host_f.array, full_f.cpu().numpy())
+            if with_depth: assert np.array_equal(host_d.array[..., 0], full_d.cpu().numpy())
+            else: assert np.all(host_d.array == -1.0)
+        tb.host_unregister(host_f.host_ptr); tb.host_unregister(host_d.host_ptr)
+        with pytest.raises(RuntimeError):
+            tb.host_register(0, 16)
+    finally:
+        tb.set_tile_shard(0, 1)
+        host_f.close(); host_d.close()
+
+
 def test_empty_inputs(base, hn):
     tb, _, grid, _ = base
     # camera looking away from the volume: no ray enters, the frame is the cleared buffer + background alpha

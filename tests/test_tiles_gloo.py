@@ -79,3 +79,41 @@ def test_pack_roundtrip_single_process():
         for r in range(world):
             tiles.unpack_tiles_host(tiles.pack_tiles_host(f, d, 64, 32, r, world), out_f, out_d, 64, 32, r, world)
         assert np.array_equal(out_f, f) and np.array_equal(out_d, d)
+
+
+def _host_worker(rank, world, port, w, h, tw, th, q):
+    """the sharded render-to-host path of bench.py (e2e, N > 1) on CPU: one shared host frame, every rank writes the tiles it owns"""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    tiles = _tiles()
+    names = [f"hn_test_{os.getpid()}_{port}" if rank == 0 else None]
+    shared = tiles.SharedHostFrame(names[0], h, w, 4, create=True) if rank == 0 else None
+    dist.broadcast_object_list(names, src=0)
+    if rank != 0:
+        shared = tiles.SharedHostFrame(names[0], h, w, 4, create=False)
+    full_f, _ = _full_frame(w, h)
+    own = tiles.owner_map(w, h, tw, th, world) == rank
+    shared.array[own] = full_f[own]          # what scatter_tiles_kernel does with a host-mapped target
+    dist.barrier()
+    ok = np.array_equal(shared.array, full_f) if rank == 0 else True
+    n_bytes_ok = shared.n_bytes == w * h * 16 and shared.host_ptr != 0
+    dist.barrier()
+    shared.close()
+    dist.destroy_process_group()
+    q.put((rank, bool(ok and n_bytes_ok)))
+
+
+@pytest.mark.parametrize("world,w,h", [(2, 200, 70), (3, 130, 100)])
+def test_shared_host_frame_gloo(world, w, h):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000) + world
+    procs = [ctx.Process(target=_host_worker, args=(r, world, port, w, h, 64, 32, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in res)

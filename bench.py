@@ -714,16 +714,42 @@ def main():
         # one launch), then stream sync + barrier - no gather on rank 0, no 33 MB read-back through one link. "gather": the round-1 path
         # (peer gather into rank 0's device frame, then rank 0 copies it to pinned host memory), kept for A/B.
         n_e2e = max(3, min(args.steps, 10))
-        if args.e2e_delivery == "host":
+        delivery = args.e2e_delivery
+        shared, host_dev = None, 0
+        if delivery == "host":
+            # set-up may fail on a box whose /dev/shm is too small or that refuses to page-lock the mapping: every rank then agrees to
+            # fall back to the gather path (and the line says so)
             from importlib import import_module
             tiles_mod = import_module(hn.__name__ + ".tiles")
-            names = [f"hn_e2e_{os.getpid()}" if rank == 0 else None]
-            shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=True) if rank == 0 else None
+            ok = 1.0
+            names = [None]
+            if rank == 0:
+                try:
+                    names = [f"hn_e2e_{os.getpid()}"]
+                    shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=True)
+                except Exception as e:
+                    print(f"[bench] shared host frame unavailable: {e}", file=sys.stderr)
+                    names, ok = [None], 0.0
             dist.broadcast_object_list(names, src=0)
-            if rank != 0:
-                shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=False)
-            host_dev = tb.host_register(shared.host_ptr, shared.n_bytes)
-
+            try:
+                if names[0] is None:
+                    ok = 0.0
+                else:
+                    if rank != 0:
+                        shared = tiles_mod.SharedHostFrame(names[0], H, W, 4, create=False)
+                    host_dev = tb.host_register(shared.host_ptr, shared.n_bytes)
+            except Exception as e:
+                print(f"[bench] rank {rank}: host delivery set-up failed: {e}", file=sys.stderr)
+                ok = 0.0
+            flag = torch.tensor([ok], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if float(flag.item()) < 1.0:
+                if host_dev:
+                    tb.host_unregister(shared.host_ptr)
+                if shared is not None:
+                    shared.close()
+                shared, host_dev, delivery = None, 0, "gather"
+        if delivery == "host":
             def e2e_step():
                 tb.set_camera_cols(cam)
                 tb.render_frame(cam, cam, W, H, frame.data_ptr(), depth.data_ptr(), 0, stream)
@@ -747,7 +773,9 @@ def main():
         t = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-        if args.e2e_delivery == "host":
+        if breakdown is not None:
+            breakdown["e2e_delivery"] = "peer gather on rank 0, then one device -> host copy there"
+        if delivery == "host":
             # the host frame must be the frame the peer gather assembles on rank 0 (untimed check)
             step(); barrier()
             if rank == 0:

@@ -106,17 +106,28 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 		const uint32_t last = term ? (uint32_t)(__ffs(term_mask) - 1) : count - 1;
 		const bool use = has && (uint32_t)lane <= last;
 		float sw = use ? weight : 0.f, sr = use ? cr * weight : 0.f, sg = use ? cg * weight : 0.f, sb = use ? cb * weight : 0.f;
+		// Arg-max of the weights: one warp-wide float max (redux.sync.max.f32 = CREDUX on sm_100a), then the lowest lane that holds it (ties go
+		// to the earlier sample). The four sums share one butterfly: after the first two exchanges a lane carries ONE of the four totals (lanes
+		// 0-7 alpha, 8-15 red, 16-23 green, 24-31 blue), three more exchanges finish it and four broadcasts hand every lane all four - 10
+		// shuffles instead of 30, in a kernel that is bound by its issue slots.
 		float bw = use ? weight : -1.f;
-		uint32_t bj = (uint32_t)lane;
-		#pragma unroll
-		for (int d = 16; d > 0; d >>= 1) {
-			sw += __shfl_xor_sync(0xffffffffu, sw, d);
-			sr += __shfl_xor_sync(0xffffffffu, sr, d);
-			sg += __shfl_xor_sync(0xffffffffu, sg, d);
-			sb += __shfl_xor_sync(0xffffffffu, sb, d);
-			const float ow = __shfl_xor_sync(0xffffffffu, bw, d);
-			const uint32_t oj = __shfl_xor_sync(0xffffffffu, bj, d);
-			if (ow > bw || (ow == bw && oj < bj)) { bw = ow; bj = oj; }
+		uint32_t bj;
+		{
+			float wmax;
+			asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(wmax) : "f"(bw));
+			bj = (uint32_t)(__ffs(__ballot_sync(0xffffffffu, bw == wmax)) - 1) & 31u;
+			bw = wmax;
+		}
+		{
+			const bool hi16 = (lane & 16) != 0, hi8 = (lane & 8) != 0;
+			const float x0 = (hi16 ? sg : sw) + __shfl_xor_sync(0xffffffffu, hi16 ? sw : sg, 16);
+			const float x1 = (hi16 ? sb : sr) + __shfl_xor_sync(0xffffffffu, hi16 ? sr : sb, 16);
+			float y = (hi8 ? x1 : x0) + __shfl_xor_sync(0xffffffffu, hi8 ? x0 : x1, 8);
+			y += __shfl_xor_sync(0xffffffffu, y, 4);
+			y += __shfl_xor_sync(0xffffffffu, y, 2);
+			y += __shfl_xor_sync(0xffffffffu, y, 1);
+			sw = __shfl_sync(0xffffffffu, y, 0); sr = __shfl_sync(0xffffffffu, y, 8);
+			sg = __shfl_sync(0xffffffffu, y, 16); sb = __shfl_sync(0xffffffffu, y, 24);
 		}
 		const float zbest = __shfl_sync(0xffffffffu, zview, bj);
 		rgba.x += sr; rgba.y += sg; rgba.z += sb; rgba.w += sw;

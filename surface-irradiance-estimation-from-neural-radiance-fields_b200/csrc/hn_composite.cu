@@ -260,6 +260,7 @@ CompArgs make_comp_args(const FrameArgs& fa, RaySoA rays, const uint32_t* alive_
 // One warp per live ray (lane j = sample j of this pass's chunk): every load of the kernel is issued up front, so the
 // kernel runs at memory latency x waves instead of 32 dependent round trips per warp (composite_kernel above keeps 32 rays
 // per warp and is latency-bound by its serial ray loop). Survivors are flagged; compact_kernel builds the next list.
+template <bool PLAIN>
 __global__ void __launch_bounds__(512) composite_ray_kernel(const __grid_constant__ CompArgs a, const uint32_t* __restrict__ n_alive_ptr,
 	const uint32_t* __restrict__ sample_counts, const uint2* __restrict__ net_out, uint32_t max_rays) {
 	__shared__ uint32_t block_total;
@@ -283,10 +284,10 @@ __global__ void __launch_bounds__(512) composite_ray_kernel(const __grid_constan
 			pre.depth = a.rays.depth[pre.r];
 			pre.max_weight = a.rays.d_mw[pre.r].w;
 			pre.n_steps = a.rays.n_steps[pre.r];
-			pre.o_t = a.render_mode == 7 ? a.rays.o_t[pre.r] : make_float4(0.f, 0.f, 0.f, 0.f);
+			pre.o_t = (!PLAIN && a.render_mode == 7) ? a.rays.o_t[pre.r] : make_float4(0.f, 0.f, 0.f, 0.f);
 			const bool has = (uint32_t)lane < count;
 			pre.s = has ? s_raw : make_float4(0.f, 0.f, 0.f, 0.f);
-			const uint32_t n = composite_chunk(a, pre, chunk, count, lane, has ? o_raw : make_uint2(0u, 0u));
+			const uint32_t n = composite_chunk<PLAIN>(a, pre, chunk, count, lane, has ? o_raw : make_uint2(0u, 0u));
 			if (lane == 0 && n) atomicAdd(&block_total, n);
 		}
 	}
@@ -295,7 +296,9 @@ __global__ void __launch_bounds__(512) composite_ray_kernel(const __grid_constan
 }
 void launch_composite_rays(const CompArgs& a, const uint32_t* n_alive_ptr, const uint32_t* sample_counts, const uint2* net_out, uint32_t max_rays, cudaStream_t s) {
 	if (!max_rays) return;
-	composite_ray_kernel<<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out, max_rays);
+	const bool plain = a.render_mode >= 1 && a.render_mode <= 4 && a.rgb_act == 2 && a.density_act == 3;
+	if (plain) composite_ray_kernel<true><<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out, max_rays);
+	else composite_ray_kernel<false><<<(max_rays + 15) / 16, 512, 0, s>>>(a, n_alive_ptr, sample_counts, net_out, max_rays);
 }
 
 // ERenderMode::Slice, second half (compute_nerf_rgba with depth 0.01, src/testbed_nerf.cu:408-421, then shade_kernel_nerf :1361-1401):

@@ -63,7 +63,11 @@ __device__ __forceinline__ RayPre composite_prefetch(const CompArgs& a, uint32_t
 	if ((uint32_t)lane < count) p.s = __ldg(a.samples + (size_t)chunk * CHUNK + lane);
 	return p;
 }
+// PLAIN = the common frame fixed at compile time (ERenderMode::Shade, logistic colour, exponential density - configs/*/base.json): the
+// run-time switches on activation and render mode cost ~15 % of the instructions of a kernel that is bound by its issue slots.
+template <bool PLAIN = false>
 __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const RayPre& pre, uint32_t chunk, uint32_t count, int lane, uint2 o) {
+	const int render_mode = PLAIN ? 1 : a.render_mode, rgb_act = PLAIN ? 2 : a.rgb_act, density_act = PLAIN ? 3 : a.density_act;
 	const uint32_t r = pre.r;
 	float4 rgba = pre.rgba;
 	float depth = pre.depth;
@@ -77,18 +81,18 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 		if (has) {
 			const float4 s = pre.s;
 			const __half2 rg = *reinterpret_cast<const __half2*>(&o.x), bs = *reinterpret_cast<const __half2*>(&o.y);
-			const float sigma = act_density(__high2float(bs), a.density_act);
+			const float sigma = act_density(__high2float(bs), density_act);
 			// the reference sends dt and the position through warp/unwarp (network input); that round trip moves them by at most an
 			// ulp, far below the compositing tolerance, and costs five IEEE divisions per sample: use the marched values directly
 			alpha = 1.f - __expf(-sigma * s.w);
-			cr = act_rgb(__low2float(rg), a.rgb_act); cg = act_rgb(__high2float(rg), a.rgb_act); cb = act_rgb(__low2float(bs), a.rgb_act);
+			cr = act_rgb(__low2float(rg), rgb_act); cg = act_rgb(__high2float(rg), rgb_act); cb = act_rgb(__low2float(bs), rgb_act);
 			zview = a.cam_fwd[0] * (s.x - a.cam_pos[0]) + a.cam_fwd[1] * (s.y - a.cam_pos[1]) + a.cam_fwd[2] * (s.z - a.cam_pos[2]);
 			// per-sample colour of the visualisation modes (composite_kernel_nerf, src/testbed_nerf.cu:686-702)
-			if (a.render_mode == 6) { cr = (s.x - 0.5f) / 2.0f + 0.5f; cg = (s.y - 0.5f) / 2.0f + 0.5f; cb = (s.z - 0.5f) / 2.0f + 0.5f; }
-			else if (a.render_mode == 12) { cr = (s.x - a.train_lo[0]) / a.train_diag[0]; cg = (s.y - a.train_lo[1]) / a.train_diag[1]; cb = (s.z - a.train_lo[2]) / a.train_diag[2]; }
-			else if (a.render_mode == 7) { cr = cg = cb = (a.cam_fwd[0] * (s.x - pre.o_t.x) + a.cam_fwd[1] * (s.y - pre.o_t.y) + a.cam_fwd[2] * (s.z - pre.o_t.z)) * a.depth_scale; }
-			else if (a.render_mode == 0) { cr = cg = cb = alpha; }
-			else if (a.render_mode == 5) { cr = __low2float(rg); cg = __high2float(rg); cb = __low2float(bs); } // unit normal written by normals_kernel (:688-693)
+			if (render_mode == 6) { cr = (s.x - 0.5f) / 2.0f + 0.5f; cg = (s.y - 0.5f) / 2.0f + 0.5f; cb = (s.z - 0.5f) / 2.0f + 0.5f; }
+			else if (render_mode == 12) { cr = (s.x - a.train_lo[0]) / a.train_diag[0]; cg = (s.y - a.train_lo[1]) / a.train_diag[1]; cb = (s.z - a.train_lo[2]) / a.train_diag[2]; }
+			else if (render_mode == 7) { cr = cg = cb = (a.cam_fwd[0] * (s.x - pre.o_t.x) + a.cam_fwd[1] * (s.y - pre.o_t.y) + a.cam_fwd[2] * (s.z - pre.o_t.z)) * a.depth_scale; }
+			else if (render_mode == 0) { cr = cg = cb = alpha; }
+			else if (render_mode == 5) { cr = __low2float(rg); cg = __high2float(rg); cb = __low2float(bs); } // unit normal written by normals_kernel (:688-693)
 		}
 		float P = 1.f - alpha; // inclusive product scan of (1 - alpha)
 		#pragma unroll
@@ -145,9 +149,9 @@ __device__ __forceinline__ uint32_t composite_chunk(const CompArgs& a, const Ray
 	// ray (three powf, ~50 instructions each) is spread over lanes 0..2 so the warp issues it once instead of three times
 	const bool finished = !alive_next && rgba.w > 0.001f; // compact_kernel_nerf keeps finished rays with alpha > 0.001
 	float4 tmp = rgba;
-	const bool shade_mode = a.render_mode >= 1 && a.render_mode <= 4; // only Shade (and Slice) accumulate in linear colours (shade_kernel_nerf :1391-1394)
-	if (a.render_mode == 9) { const float col = (float)n_steps / 128.0f; tmp = make_float4(col, col, col, 1.0f); } // Cost (:1381-1383)
-	if (a.render_mode == 5) { // Normals (:1379-1381): (0.5 n + 0.5) * alpha
+	const bool shade_mode = render_mode >= 1 && render_mode <= 4; // only Shade (and Slice) accumulate in linear colours (shade_kernel_nerf :1391-1394)
+	if (render_mode == 9) { const float col = (float)n_steps / 128.0f; tmp = make_float4(col, col, col, 1.0f); } // Cost (:1381-1383)
+	if (render_mode == 5) { // Normals (:1379-1381): (0.5 n + 0.5) * alpha
 		const float len = sqrtf(rgba.x * rgba.x + rgba.y * rgba.y + rgba.z * rgba.z);
 		tmp.x = (0.5f * (rgba.x / len) + 0.5f) * rgba.w; tmp.y = (0.5f * (rgba.y / len) + 0.5f) * rgba.w; tmp.z = (0.5f * (rgba.z / len) + 0.5f) * rgba.w;
 	}

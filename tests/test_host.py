@@ -43,6 +43,15 @@ def test_exports_match_header(hn, root):
     assert text.count("testbed.h:") + text.count(".cu:") >= 10
 
 
+def test_integration_map_lists_every_entry_point(root):
+    """INTEGRATION.md is the binding guide: every function the header declares has a row there"""
+    text = open(os.path.join(root, "include", "hybrid_nerf.h")).read()
+    declared = sorted(set(re.findall(r"\b(hn_[a-z0-9_]+)\s*\(", text)))
+    guide = open(os.path.join(root, "INTEGRATION.md")).read()
+    missing = [s for s in declared if s not in guide]
+    assert not missing, f"INTEGRATION.md does not mention {missing}"
+
+
 def test_no_cpu_fallback(hn, raw):
     lib, h, rc, _ = raw
     if not _no_gpu():
